@@ -1,0 +1,91 @@
+/* ORACLE (test infrastructure, not product code; only tests/, smoke() and
+ * bench.py's cpu_baseline/reference legs may load it).
+ *
+ * Plain-C, fp64 restatement of the hot path: BlueSky traffic substep
+ * (SURVEY.md A.3/A.6), state-based CD (A.5), MVP + resumenav (A.7), and the
+ * reference env layer's action/obs/reward/termination
+ * (/root/reference/bluesky_gym/envs/{horizontal,vertical,sector}_cr_env.py).
+ * Tier A (env layer) is pinned by goldens generated from the unmodified
+ * reference classes run on oracle/refshim; Tier B (BlueSky) is a restatement:
+ * parity unpinned vs upstream bluesky-simulator==1.0.3.
+ *
+ * Data model (shared with the CUDA core's set/get-state interface):
+ *   ac   : double [E][BSGO_NF][N]   per-aircraft fields, field-major inside an env
+ *   reso : uint64 [E][N]            resopairs bit rows (bit j of row i = pair (i,j) kept), N <= 64
+ *   nac  : int32  [E]               live aircraft per env (<= N); aircraft 0 is the agent
+ *   ev   : double [E][BSGO_NE]      env-level slots
+ */
+#ifndef BSGO_H
+#define BSGO_H
+#include <stdint.h>
+
+enum { F_LAT, F_LON, F_ALT, F_HDG, F_TAS, F_VS, F_CAS, F_SELSPD, F_SELALT, F_SELVS, F_APTRK, F_AX,
+       F_ASAS_TRK, F_ASAS_TAS, F_ASAS_VS, F_ASAS_ALT, F_ASAS_ACTIVE,
+       F_PHASE /* flight phase of the last perf.update (MVP caps use it one substep later) */, BSGO_NF };
+
+#define BSGO_MAXV 32
+enum { EV_WPT_LAT, EV_WPT_LON, EV_WPT_REACH, EV_AC_HDG,      /* Horizontal */
+       EV_TARGET_ALT,                                         /* Vertical */
+       EV_WPT_X, EV_WPT_Y, EV_NVERT,                          /* Sector: own waypoint [NM], polygon size */
+       EV_TOTAL_REWARD, EV_TOTAL_INTR, EV_DRIFT_SUM, EV_DRIFT_CNT, EV_FINAL_ALT, EV_STEPS,
+       EV_POLY,                                               /* 2*BSGO_MAXV slots: lat0,lon0,lat1,lon1,... */
+       BSGO_NE = EV_POLY + 2 * BSGO_MAXV };
+
+enum { KIND_H = 0, KIND_V = 1, KIND_S = 2, KIND_RAW = 3 };
+
+typedef struct {
+    int32_t kind, n, substeps, asas_on, reso_on, reso_off_own;
+    double simdt, rpz, hpz, dtlook, resofach, resofacv;
+} bsgo_cfg;
+
+/* per-aircraft CD outputs of the last detection of a step */
+typedef struct {
+    uint8_t *inconf;      /* [E][N] */
+    int32_t *nconf;       /* [E][N] conflict pairs in row i */
+    int32_t *nlos;        /* [E][N] LoS pairs in row i */
+    int32_t *near_idx;    /* [E][N] argmin_j tcpa over conflict pairs, -1 if none (ties: lowest j) */
+    double *near_tcpa, *near_dcpa, *near_tin;   /* [E][N] */
+    double *tcpamax;      /* [E][N] */
+} bsgo_cdout;
+
+int bsgo_obs_dim(int kind, int n);
+
+/* aero */
+double bsgo_vcas2tas(double cas, double h);
+double bsgo_vtas2cas(double tas, double h);
+double bsgo_vcasormach2tas(double spd, double h);
+/* geo */
+void bsgo_kwikqdrdist(double lata, double lona, double latb, double lonb, double *qdr, double *dist_nm);
+
+/* one full CD matrix for one env (dense outputs, row-major n x n); any pointer may be NULL */
+void bsgo_detect_dense(int n, const double *lat, const double *lon, const double *alt,
+                       const double *trk, const double *gs, const double *vs,
+                       double rpz, double hpz, double dtlook,
+                       double *tcpa, double *dcpa2, double *tinconf, double *toutconf,
+                       uint8_t *swconfl, uint8_t *swlos, double *margin_conf, double *margin_los);
+
+/* batched CD row outputs from raw state (KIND_RAW sweep; rows [row0,row1) of each env) */
+void bsgo_cd_rows(int E, int n, const double *lat, const double *lon, const double *alt,
+                  const double *trk, const double *gs, const double *vs,
+                  double rpz, double hpz, double dtlook, int row0, int row1,
+                  bsgo_cdout out, int nthreads);
+
+/* K traffic substeps (+CD/MVP when enabled) then the env layer, for E envs */
+void bsgo_step(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, const int32_t *nac, double *ev,
+               const double *actions, double *obs, double *reward, int32_t *term, int32_t *trunc,
+               bsgo_cdout cd, int nthreads);
+/* obs/info only (what reset() returns) */
+void bsgo_observe(const bsgo_cfg *cfg, int E, const double *ac, const int32_t *nac, double *ev, double *obs);
+
+/* ND-map (builder-owned spec): fp32 sample arithmetic, integer grid */
+typedef struct {
+    int32_t nx, ny, nz, nt;
+    float x0, y0, z0, inv_cx, inv_cy, inv_cz, dt;
+} bsgo_ndcfg;
+void bsgo_ndmap(const bsgo_ndcfg *g, int E, int n, const float *rec /* [E][6][n]: x,y,z,u,v,w */,
+                uint8_t *occ /* [E][nt][nz][ny][nx] */, uint8_t *conf /* same shape, 0/1 */,
+                int32_t *ncell /* [E][nt] conflict cells per time slab */, int nthreads);
+
+/* Philox4x32-10 scenario generator (same stream on host and device) */
+void bsgo_philox(uint32_t key0, uint32_t key1, uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t out[4]);
+#endif

@@ -1,0 +1,128 @@
+/* ORACLE (test infrastructure, not product code).
+ * Per-env ASAS pass = StateBased.detect -> MVP.resolve (if any conflict) -> resumenav,
+ * restating oracle/refshim/bluesky/traffic/{asas,mvp}.py.
+ * parity unpinned vs upstream bluesky-simulator==1.0.3. */
+#include <math.h>
+#include <stdlib.h>
+#include <string.h>
+#include "bsgo_int.h"
+
+static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
+                     double alt1, double alt2, const double v1[3], const double v2[3],
+                     double rpz, double hpz, double dtlook, double fach, double facv,
+                     double dv[3], double *tsolV_o) {
+    double rpz_m = rpz * fach, hpz_m = hpz * facv;
+    double q = qdr * C_D2R;
+    double drel[3] = { sin(q) * dist, cos(q) * dist, alt2 - alt1 };
+    double vrel[3] = { v2[0] - v1[0], v2[1] - v1[1], v2[2] - v1[2] };
+    double dcpa[3] = { drel[0] + vrel[0] * tcpa, drel[1] + vrel[1] * tcpa, drel[2] + vrel[2] * tcpa };
+    double dabsH = sqrt(dcpa[0] * dcpa[0] + dcpa[1] * dcpa[1]);
+    double iH = rpz_m - dabsH;
+    if (dabsH <= 10.0) {
+        dabsH = 10.0;
+        dcpa[0] = drel[1] / dist * dabsH;
+        dcpa[1] = -drel[0] / dist * dabsH;
+    }
+    if (rpz_m < dist && dabsH < dist) {
+        double erratum = cos(asin(rpz_m / dist) - asin(dabsH / dist));
+        dv[0] = ((rpz_m / erratum - dabsH) * dcpa[0]) / (fabs(tcpa) * dabsH);
+        dv[1] = ((rpz_m / erratum - dabsH) * dcpa[1]) / (fabs(tcpa) * dabsH);
+    } else {
+        dv[0] = (iH * dcpa[0]) / (fabs(tcpa) * dabsH);
+        dv[1] = (iH * dcpa[1]) / (fabs(tcpa) * dabsH);
+    }
+    double iV, tsolV;
+    if (fabs(vrel[2]) > 0.0) { iV = hpz_m; tsolV = fabs(drel[2] / vrel[2]); }
+    else { iV = hpz_m - fabs(drel[2]); tsolV = tLOS; }
+    if (tsolV > dtlook) { tsolV = tLOS; iV = hpz_m; }
+    if (fabs(vrel[2]) > 0.0) dv[2] = (iV / tsolV) * (-vrel[2] / fabs(vrel[2]));
+    else dv[2] = iV / tsolV;
+    *tsolV_o = tsolV;
+}
+
+void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bsgo_row *rows) {
+    int n = cfg->n;
+#define A(f, i) a[(f) * n + (i)]
+    double *u = malloc(sizeof(double) * nlive * 5);
+    double *v = u + nlive, *dve = v + nlive, *dvn = dve + nlive, *dvz = dvn + nlive;
+    uint64_t *confrow = calloc(nlive, sizeof(uint64_t));
+    int anyconf = 0;
+    for (int i = 0; i < nlive; i++) {
+        /* gs = tas, trk = hdg (no wind) */
+        u[i] = A(F_TAS, i) * sin(A(F_HDG, i) * C_D2R);
+        v[i] = A(F_TAS, i) * cos(A(F_HDG, i) * C_D2R);
+        dve[i] = dvn[i] = dvz[i] = 0.0;
+    }
+    for (int i = 0; i < nlive; i++) {
+        bsgo_row *r = &rows[i];
+        r->inconf = 0; r->nconf = 0; r->nlos = 0; r->near_idx = -1;
+        r->near_tcpa = r->near_dcpa = r->near_tin = r->tcpamax = 0.0;
+        /* velocity vectors as MVP sees them: gseast/gsnorth of the last update_groundspeed */
+        double v1[3] = { A(F_TAS, i) * sin(A(F_HDG, i) * C_D2R), A(F_TAS, i) * cos(A(F_HDG, i) * C_D2R), A(F_VS, i) };
+        for (int j = 0; j < nlive; j++) {
+            if (j == i) continue;
+            double qdr, dist, tcpa, dcpa2, tin;
+            int sw, los;
+            bsgo_pair(A(F_LAT, i), A(F_LON, i), A(F_ALT, i), u[i], v[i], A(F_VS, i),
+                      A(F_LAT, j), A(F_LON, j), A(F_ALT, j), u[j], v[j], A(F_VS, j),
+                      cfg->rpz, cfg->hpz, cfg->dtlook, &qdr, &dist, &tcpa, &dcpa2, &tin, 0, &sw, &los, 0, 0);
+            if (los) r->nlos++;
+            if (!sw) continue;
+            anyconf = 1;
+            r->inconf = 1; r->nconf++;
+            if (tcpa > r->tcpamax) r->tcpamax = tcpa;
+            if (r->near_idx < 0 || tcpa < r->near_tcpa) {
+                r->near_idx = j; r->near_tcpa = tcpa; r->near_dcpa = sqrt(dcpa2); r->near_tin = tin;
+            }
+            if (n <= 64) confrow[i] |= (uint64_t)1 << j;
+            if (cfg->reso_on) {
+                double v2[3] = { A(F_TAS, j) * sin(A(F_HDG, j) * C_D2R), A(F_TAS, j) * cos(A(F_HDG, j) * C_D2R), A(F_VS, j) };
+                double dv[3], tsolV;
+                mvp_pair(qdr, dist, tcpa, tin, A(F_ALT, i), A(F_ALT, j), v1, v2,
+                         cfg->rpz, cfg->hpz, cfg->dtlook, cfg->resofach, cfg->resofacv, dv, &tsolV);
+                dv[2] = 0.5 * dv[2];
+                dve[i] = dve[i] - dv[0]; dvn[i] = dvn[i] - dv[1]; dvz[i] = dvz[i] - dv[2];
+                if (cfg->reso_off_own && i == 0) { dve[i] = 0.0; dvn[i] = 0.0; dvz[i] = 0.0; }
+            }
+        }
+    }
+    if (cfg->reso_on) {
+        if (anyconf) {
+            for (int i = 0; i < nlive; i++) {
+                double ge = A(F_TAS, i) * sin(A(F_HDG, i) * C_D2R), gn = A(F_TAS, i) * cos(A(F_HDG, i) * C_D2R);
+                double ne = ge + dve[i], nn = gn + dvn[i];
+                double newtrack = bsgo_pymod(atan2(ne, nn) * 180 / C_PI, 360);
+                double newgs = sqrt(ne * ne + nn * nn);
+                double vmin, vmax;
+                bsgo_vlimits((int)A(F_PHASE, i), &vmin, &vmax);
+                A(F_ASAS_TRK, i) = newtrack;
+                A(F_ASAS_TAS, i) = fmax(vmin, fmin(vmax, newgs));
+                A(F_ASAS_VS, i) = fmax(ENV_VSMIN, fmin(ENV_VSMAX, A(F_VS, i)));
+                A(F_ASAS_ALT, i) = A(F_SELALT, i);
+            }
+        }
+        /* resumenav: resopairs |= confpairs; keep a pair while not past CPA, or in horizontal LoS, or bouncing */
+        for (int i = 0; i < nlive && n <= 64; i++) {
+            uint64_t row = reso[i] | confrow[i];
+            uint64_t keep = 0;
+            int touched = 0, active = 0;
+            for (int j = 0; j < nlive; j++) {
+                if (!((row >> j) & 1)) continue;
+                touched = 1;
+                double dx = C_RE * ((A(F_LON, j) - A(F_LON, i)) * C_D2R * cos(0.5 * ((A(F_LAT, j) + A(F_LAT, i)) * C_D2R)));
+                double dy = C_RE * ((A(F_LAT, j) - A(F_LAT, i)) * C_D2R);
+                double vx = u[j] - u[i], vy = v[j] - v[i];
+                int past_cpa = (dx * vx + dy * vy) > 0.0;
+                double hdist = sqrt(dx * dx + dy * dy);
+                int hor_los = hdist < cfg->rpz;
+                int bouncing = fabs(A(F_HDG, i) - A(F_HDG, j)) < 30.0 && hdist < cfg->rpz * cfg->resofach;
+                if (!past_cpa || hor_los || bouncing) { active = 1; keep |= (uint64_t)1 << j; }
+            }
+            if (touched) A(F_ASAS_ACTIVE, i) = active ? 1.0 : 0.0;
+            reso[i] = keep;
+        }
+    }
+    free(u);
+    free(confrow);
+#undef A
+}

@@ -1,0 +1,100 @@
+"""CPU: the C oracle (oracle/c) against the golden fixtures recorded from the UNMODIFIED
+reference env classes run on oracle/refshim (tests/golden/make_golden.py).  One reference
+step is replayed from every recorded pre-state; obs / reward / terminated / truncated / info
+and the full post-state must agree to 1e-11 relative."""
+import sys
+import os
+import numpy as np
+import pytest
+from conftest import load_golden, ROOT
+
+KIND = {'H': 0, 'V': 1, 'S': 2}
+TOL = 1e-11
+
+
+def rel(a, b):
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1.0))) if a.size else 0.0
+
+
+@pytest.mark.parametrize('name', ['H', 'V', 'S', 'H_asas', 'S_asas'])
+def test_c_oracle_replays_reference_steps(orc, name):
+    g = load_golden(name)
+    kind = name[0]
+    asas = int('asas' in name)
+    n = g['ac0'].shape[2]
+    cfg = orc.make_cfg(KIND[kind], n, asas_on=asas, reso_on=asas, reso_off_own=asas)
+    nac = g['nac'].astype(np.int32)
+    na = 2 if kind == 'S' else 1
+    obs0 = orc.observe(cfg, g['ac0'].copy(), nac, g['ev0'].copy())
+    assert rel(obs0, g['obs0']) < TOL
+    ac, reso, ev = g['ac0'].copy(), g['reso0'].copy(), g['ev0'].copy()
+    obs, rew, term, trunc, cd = orc.step(cfg, ac, reso, nac, ev, np.ascontiguousarray(g['act'][:, :na]), nthreads=2)
+    assert rel(obs, g['obs1']) < TOL
+    assert rel(rew, g['rew']) < TOL
+    assert np.array_equal(term, g['term']) and np.array_equal(trunc, g['trunc'])
+    live = g['term'] == 0
+    assert rel(ac[live], g['ac1'][live]) < TOL
+    assert np.array_equal(reso[live], g['reso1'][live])
+    assert rel(ev[:, orc.EV['total_reward']], g['info'][:, 0]) < TOL
+    assert np.array_equal(ev[:, orc.EV['total_intr']], g['info'][:, 1])
+    if kind in 'HS':   # average_drift = mean of the appended drifts (nan right after reset)
+        avg = ev[:, orc.EV['drift_sum']] / ev[:, orc.EV['drift_cnt']]
+        assert rel(avg, g['info'][:, 2]) < 1e-9
+    else:
+        assert rel(ev[:, orc.EV['final_alt']], g['info'][:, 2]) < TOL
+    # every golden file must exercise its branches
+    if name == 'H':
+        assert g['term'].sum() >= 1
+    if name == 'S':
+        assert g['trunc'].sum() >= 1
+    if asas:
+        assert (g['ac1'][:, orc.F['asas_active']].sum(1) > 0).sum() > 10
+
+
+def test_functions_kat():
+    """Closed-form helper KAT observed in the survey: get_point_at_distance(52,4,100,0)."""
+    g = load_golden('functions')
+    assert abs(g['gpad'][0] - 52.89932160591875) < 1e-12 and g['gpad'][1] == 4.0
+    assert list(g['bound']) == [181.0, 160.0, 10.0, -179.0]
+
+
+def test_numpy_detect_matches_c_dense(orc):
+    """oracle/refshim's numpy StateBased.detect (A.5 line by line) == the C pair loop."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle', 'refshim'))
+    from bluesky.traffic.asas import detect
+    rng = np.random.default_rng(5)
+    n = 40
+    lat = 52 + rng.uniform(-0.6, 0.6, n); lon = 4 + rng.uniform(-1, 1, n)
+    alt = rng.choice([3000.0, 3300.0, 3600.0], n) + rng.uniform(-50, 50, n)
+    trk = rng.uniform(0, 360, n); gs = rng.uniform(120, 250, n); vs = rng.choice([-8.0, 0.0, 8.0], n)
+    rpz, hpz = 5 * 1852.0, 1000 * 0.3048
+    r = detect(lat, lon, alt, trk, gs, vs, np.full(n, rpz), np.full(n, hpz), np.full(n, 300.0))
+    d = orc.detect_dense(lat, lon, alt, trk, gs, vs, rpz, hpz, 300.0)
+    off = ~np.eye(n, dtype=bool)
+    assert r['swconfl'].sum() > 5
+    assert np.array_equal(r['swconfl'], d['swconfl'].astype(bool))
+    assert np.array_equal(r['swlos'][off], d['swlos'].astype(bool)[off])
+    assert rel(d['tcpa'][off], r['tcpa'][off]) < 1e-12
+    assert rel(d['dcpa2'][off], r['dcpa2'][off]) < 1e-10
+    c = r['swconfl']
+    assert rel(d['tinconf'][c], r['tinconf'][c]) < 1e-12
+
+
+def test_creconfs_known_answer(orc):
+    """Analytic KAT: an intruder built by creconfs(dpsi, dcpa, tlosh) must be detected with
+    dcpa == cpa*1852 m and tinconf == tlosh on the first CD call."""
+    sys.path.insert(0, os.path.join(ROOT, 'oracle', 'refshim'))
+    import bluesky as bs
+    bs.init()
+    bs.traf.cre('KL001', actype='A320', acalt=3000, acspd=150)
+    cases = [(90, 2, 200), (200, 0, 150), (300, 4, 280), (60, 3, 120)]
+    for k, (dpsi, cpa, tlosh) in enumerate(cases):
+        bs.traf.creconfs(acid=f'I{k}', actype='A320', targetidx=0, dpsi=dpsi, dcpa=cpa, tlosh=tlosh)
+    t = bs.traf
+    d = orc.detect_dense(t.lat, t.lon, t.alt, t.trk, t.gs, t.vs)
+    for k, (dpsi, cpa, tlosh) in enumerate(cases):
+        j = k + 1
+        assert d['swconfl'][0, j] == 1
+        # kwikpos scales dlon by cos(lat_ref), kwikqdrdist by cos(mean lat): ~0.3 % of the offset
+        assert abs(np.sqrt(d['dcpa2'][0, j]) - cpa * 1852.0) < 300.0
+        assert abs(d['tinconf'][0, j] - tlosh) < 3.0
