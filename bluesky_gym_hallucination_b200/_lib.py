@@ -1,0 +1,106 @@
+"""ctypes binding of libbsgcore.so (include/bsgcore.h).  The CUDA core is the only compute path:
+if the shared library is missing or cannot be loaded this module raises -- there is no CPU fallback."""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, 'libbsgcore.so')
+
+ABI_VERSION = 1
+KIND_HORIZONTAL, KIND_VERTICAL, KIND_SECTOR, KIND_RAW = 0, 1, 2, 3
+FP32, FP64 = 0, 1
+FIELDS = ['lat', 'lon', 'alt', 'hdg', 'tas', 'vs', 'cas', 'selspd', 'selalt', 'selvs', 'aptrk', 'ax',
+          'asas_trk', 'asas_tas', 'asas_vs', 'asas_alt', 'asas_active', 'phase']
+F = {k: i for i, k in enumerate(FIELDS)}
+NF = len(FIELDS)
+MAXV = 32
+EV = {k: i for i, k in enumerate(['wpt_lat', 'wpt_lon', 'wpt_reach', 'ac_hdg', 'target_alt', 'wpt_x', 'wpt_y', 'nvert',
+                                  'total_reward', 'total_intr', 'drift_sum', 'drift_cnt', 'final_alt', 'steps',
+                                  'poly'])}
+NE = EV['poly'] + 2 * MAXV
+
+
+class Config(C.Structure):
+    _fields_ = [('struct_size', C.c_int32), ('env_kind', C.c_int32), ('num_envs', C.c_int32), ('max_ac', C.c_int32),
+                ('precision', C.c_int32), ('substeps', C.c_int32), ('asas_on', C.c_int32), ('reso_on', C.c_int32),
+                ('reso_off_own', C.c_int32), ('max_episode_steps', C.c_int32), ('device', C.c_int32),
+                ('reserved', C.c_int32), ('simdt', C.c_double), ('rpz_m', C.c_double), ('hpz_m', C.c_double),
+                ('dtlookahead', C.c_double), ('resofach', C.c_double), ('resofacv', C.c_double)]
+
+
+class StepOut(C.Structure):
+    _fields_ = [(k, C.c_void_p) for k in ('obs', 'reward', 'terminated', 'truncated', 'info', 'cd_inconf', 'cd_nconf',
+                                          'cd_nlos', 'cd_near_idx', 'cd_near_tcpa', 'cd_near_dcpa', 'cd_near_tin',
+                                          'cd_tcpamax')]
+
+
+class CdParams(C.Structure):
+    _fields_ = [('num_envs', C.c_int32), ('num_ac', C.c_int32), ('row0', C.c_int32), ('row1', C.c_int32),
+                ('rpz_m', C.c_float), ('hpz_m', C.c_float), ('dtlookahead', C.c_float), ('reserved', C.c_int32)]
+
+
+class NdmapParams(C.Structure):
+    _fields_ = [('num_envs', C.c_int32), ('num_ac', C.c_int32), ('nx', C.c_int32), ('ny', C.c_int32),
+                ('nz', C.c_int32), ('nt', C.c_int32), ('x0', C.c_float), ('y0', C.c_float), ('z0', C.c_float),
+                ('cell_x', C.c_float), ('cell_y', C.c_float), ('cell_z', C.c_float), ('dt', C.c_float),
+                ('reserved', C.c_int32)]
+
+
+# every symbol include/bsgcore.h declares: (name, restype, argtypes)
+_VP, _I, _I64P = C.c_void_p, C.c_int, C.POINTER(C.c_int64)
+SYMBOLS = {
+    'bsg_abi_version': (_I, []),
+    'bsg_status_string': (C.c_char_p, [_I]),
+    'bsg_device_count': (_I, [C.POINTER(C.c_int)]),
+    'bsg_create': (_I, [C.POINTER(Config), C.POINTER(_VP)]),
+    'bsg_destroy': (_I, [_VP]),
+    'bsg_last_error': (C.c_char_p, [_VP]),
+    'bsg_obs_dim': (_I, [_VP]),
+    'bsg_act_dim': (_I, [_VP]),
+    'bsg_launch_count': (_I, [_VP, _I64P]),
+    'bsg_set_state': (_I, [_VP, _VP, _VP, _VP, _VP]),
+    'bsg_get_state': (_I, [_VP, _VP, _VP, _VP, _VP]),
+    'bsg_reset': (_I, [_VP, _VP, C.c_uint64, _VP]),
+    'bsg_observe': (_I, [_VP, _VP, _VP]),
+    'bsg_step': (_I, [_VP, _VP, C.POINTER(StepOut), _VP]),
+    'bsg_step_host': (_I, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_cd_pack': (_I, [C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP, _VP]),
+    'bsg_cd_sweep': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_ndmap': (_I, [C.POINTER(NdmapParams), _VP, _VP, _VP, _VP, _VP]),
+    'bsg_peak_fp32': (_I, [_I, _I, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    'bsg_peak_fp64': (_I, [_I, _I, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+}
+
+_lib = None
+
+
+def load():
+    """Load libbsgcore.so and bind every entry point; raises if the CUDA extension is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise ImportError(f"{SO_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(nvcc, sm_100a). There is no CPU fallback.")
+    lib = C.CDLL(SO_PATH)
+    for name, (res, args) in SYMBOLS.items():
+        fn = getattr(lib, name)          # AttributeError if the library does not export the symbol
+        fn.restype = res
+        fn.argtypes = args
+    if lib.bsg_abi_version() != ABI_VERSION:
+        raise ImportError(f"libbsgcore.so ABI {lib.bsg_abi_version()} != binding ABI {ABI_VERSION}")
+    _lib = lib
+    return lib
+
+
+class BsgError(RuntimeError):
+    pass
+
+
+def check(rc, handle=None):
+    if rc != 0:
+        lib = load()
+        msg = lib.bsg_status_string(rc).decode()
+        if handle:
+            msg += ': ' + lib.bsg_last_error(handle).decode()
+        raise BsgError(f"libbsgcore: {msg} (status {rc})")

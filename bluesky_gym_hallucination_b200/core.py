@@ -1,0 +1,209 @@
+"""Host-side wrapper of one libbsgcore handle (one GPU).  PyTorch is plumbing only: it owns the
+device buffers handed to the C-ABI (`tensor.data_ptr()`) and the CUDA stream."""
+import ctypes as C
+import numpy as np
+import torch
+from . import _lib as L
+
+OBS_KEYS = {
+    # key order of the reference's Dict spaces (horizontal_cr_env.py:51-58, vertical_cr_env.py:70-81,
+    # sector_cr_env.py:54-63); value = number of entries as a function of K = intruders
+    L.KIND_HORIZONTAL: [('intruder_distance', 'K'), ('cos_difference_pos', 'K'), ('sin_difference_pos', 'K'),
+                        ('x_difference_speed', 'K'), ('y_difference_speed', 'K'), ('waypoint_distance', 1),
+                        ('cos_drift', 1), ('sin_drift', 1)],
+    L.KIND_VERTICAL: [('altitude', 1), ('vz', 1), ('target_altitude', 1), ('runway_distance', 1),
+                      ('intruder_distance', 'K'), ('cos_difference_pos', 'K'), ('sin_difference_pos', 'K'),
+                      ('altitude_difference', 'K'), ('x_difference_speed', 'K'), ('y_difference_speed', 'K'),
+                      ('z_difference_speed', 'K')],
+    L.KIND_SECTOR: [('cos(drift)', 1), ('sin(drift)', 1), ('airspeed', 1), ('x_r', 4), ('y_r', 4), ('vx_r', 4),
+                    ('vy_r', 4), ('cos(track)', 4), ('sin(track)', 4), ('distances', 4)],
+}
+
+
+def obs_slices(kind, n_ac):
+    """[(key, start, stop)] of the flat observation vector."""
+    K, out, p = n_ac - 1, [], 0
+    for key, w in OBS_KEYS[kind]:
+        w = K if w == 'K' else w
+        out.append((key, p, p + w))
+        p += w
+    return out
+
+
+def _ptr(t):
+    if t is None:
+        return None
+    if isinstance(t, np.ndarray):
+        return t.ctypes.data_as(C.c_void_p)
+    return C.c_void_p(t.data_ptr())
+
+
+class BsgCore:
+    """One batched simulation core: E envs x N aircraft slots on one CUDA device."""
+
+    def __init__(self, kind, num_envs, max_ac, precision='fp32', device=0, substeps=0, simdt=0.0, asas_on=False,
+                 reso_on=False, reso_off_own=False, max_episode_steps=0, rpz_m=0.0, hpz_m=0.0, dtlookahead=0.0,
+                 cd_outputs=False):
+        self.lib = L.load()
+        if not torch.cuda.is_available():
+            raise L.BsgError("libbsgcore needs a CUDA device (no CPU fallback)")
+        self.kind, self.E, self.N = kind, num_envs, max_ac
+        self.fp64 = precision in ('fp64', L.FP64)
+        self.device = torch.device('cuda', device)
+        self.rdtype = torch.float64 if self.fp64 else torch.float32
+        self.npdtype = np.float64 if self.fp64 else np.float32
+        cfg = L.Config(C.sizeof(L.Config), kind, num_envs, max_ac, L.FP64 if self.fp64 else L.FP32, substeps,
+                       int(asas_on), int(reso_on), int(reso_off_own), max_episode_steps, device, 0, simdt, rpz_m,
+                       hpz_m, dtlookahead, 0.0, 0.0)
+        self.h = C.c_void_p()
+        rc = self.lib.bsg_create(C.byref(cfg), C.byref(self.h))
+        if rc != 0:
+            h, self.h = self.h, C.c_void_p()
+            msg = self.lib.bsg_last_error(h).decode() if h else ''
+            if h:
+                self.lib.bsg_destroy(h)
+            raise L.BsgError(f"bsg_create: {self.lib.bsg_status_string(rc).decode()} {msg}")
+        self.obs_dim = self.lib.bsg_obs_dim(self.h)
+        self.act_dim = self.lib.bsg_act_dim(self.h)
+        E, N, dev, rd = num_envs, max_ac, self.device, self.rdtype
+        self.obs = torch.zeros((E, max(self.obs_dim, 1)), dtype=rd, device=dev)
+        self.reward = torch.zeros(E, dtype=rd, device=dev)
+        self.terminated = torch.zeros(E, dtype=torch.int32, device=dev)
+        self.truncated = torch.zeros(E, dtype=torch.int32, device=dev)
+        self.info = torch.zeros((E, 4), dtype=rd, device=dev)
+        self.cd = None
+        if cd_outputs:
+            self.cd = dict(inconf=torch.zeros((E, N), dtype=torch.uint8, device=dev),
+                           nconf=torch.zeros((E, N), dtype=torch.int32, device=dev),
+                           nlos=torch.zeros((E, N), dtype=torch.int32, device=dev),
+                           near_idx=torch.zeros((E, N), dtype=torch.int32, device=dev),
+                           near_tcpa=torch.zeros((E, N), dtype=rd, device=dev),
+                           near_dcpa=torch.zeros((E, N), dtype=rd, device=dev),
+                           near_tin=torch.zeros((E, N), dtype=rd, device=dev),
+                           tcpamax=torch.zeros((E, N), dtype=rd, device=dev))
+        cdp = [(_ptr(self.cd[k]) if self.cd else None) for k in ('inconf', 'nconf', 'nlos', 'near_idx', 'near_tcpa',
+                                                                   'near_dcpa', 'near_tin', 'tcpamax')]
+        self._out = L.StepOut(_ptr(self.obs) if self.obs_dim else None, _ptr(self.reward), _ptr(self.terminated),
+                              _ptr(self.truncated), _ptr(self.info), *cdp)
+
+    def close(self):
+        if getattr(self, 'h', None):
+            self.lib.bsg_destroy(self.h)
+            self.h = C.c_void_p()
+
+    __del__ = close
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # ------------------------------------------------------------------ state interchange (fp64, host)
+    def set_state(self, ac=None, reso=None, nac=None, ev=None):
+        ac = None if ac is None else np.ascontiguousarray(ac, dtype=np.float64)
+        reso = None if reso is None else np.ascontiguousarray(reso, dtype=np.uint64)
+        nac = None if nac is None else np.ascontiguousarray(nac, dtype=np.int32)
+        ev = None if ev is None else np.ascontiguousarray(ev, dtype=np.float64)
+        if ac is not None:
+            assert ac.shape == (self.E, L.NF, self.N), ac.shape
+        if ev is not None:
+            assert ev.shape == (self.E, L.NE), ev.shape
+        torch.cuda.synchronize(self.device)
+        L.check(self.lib.bsg_set_state(self.h, _ptr(ac), _ptr(reso), _ptr(nac), _ptr(ev)), self.h)
+
+    def get_state(self):
+        ac = np.zeros((self.E, L.NF, self.N)); reso = np.zeros((self.E, self.N), np.uint64)
+        nac = np.zeros(self.E, np.int32); ev = np.zeros((self.E, L.NE))
+        torch.cuda.synchronize(self.device)
+        L.check(self.lib.bsg_get_state(self.h, _ptr(ac), _ptr(reso), _ptr(nac), _ptr(ev)), self.h)
+        return ac, reso, nac, ev
+
+    # ------------------------------------------------------------------ hot path
+    def step(self, actions):
+        """actions: CUDA tensor [E, act_dim] of the handle's real dtype.  Asynchronous on the current stream;
+        results land in self.obs / reward / terminated / truncated / info (and self.cd)."""
+        if self.act_dim:
+            assert actions.is_cuda and actions.dtype == self.rdtype and actions.is_contiguous()
+            assert actions.numel() == self.E * self.act_dim
+        L.check(self.lib.bsg_step(self.h, _ptr(actions) if self.act_dim else None, C.byref(self._out), self._stream()),
+                self.h)
+        return self.obs, self.reward, self.terminated, self.truncated, self.info
+
+    def observe(self):
+        L.check(self.lib.bsg_observe(self.h, _ptr(self.obs), self._stream()), self.h)
+        return self.obs
+
+    def reset(self, mask=None, seed=0):
+        L.check(self.lib.bsg_reset(self.h, _ptr(mask), C.c_uint64(seed), self._stream()), self.h)
+
+    def step_host(self, actions, obs, reward, terminated, truncated, info):
+        """End-to-end call with HOST numpy buffers (H2D + kernel + D2H inside)."""
+        L.check(self.lib.bsg_step_host(self.h, _ptr(actions), _ptr(obs), _ptr(reward), _ptr(terminated),
+                                       _ptr(truncated), _ptr(info)), self.h)
+
+    def launch_count(self):
+        n = C.c_int64(0)
+        L.check(self.lib.bsg_launch_count(self.h, C.byref(n)), self.h)
+        return n.value
+
+
+# ---------------------------------------------------------------------- stand-alone kernels
+def cd_pack(lat, lon, alt, trk, gs, vs, lat0, lon0):
+    """SoA CUDA tensors [E,N] (lat/lon f64, others f32) -> packed fp32 CD records [E,N,8]."""
+    lib = L.load()
+    E, N = lat.shape
+    rec = torch.empty((E, N, 8), dtype=torch.float32, device=lat.device)
+    s = C.c_void_p(torch.cuda.current_stream(lat.device).cuda_stream)
+    L.check(lib.bsg_cd_pack(E, N, _ptr(lat), _ptr(lon), _ptr(alt), _ptr(trk), _ptr(gs), _ptr(vs), float(lat0),
+                            float(lon0), _ptr(rec), s))
+    return rec
+
+
+def cd_sweep(rec, row0=0, row1=None, rpz_m=5 * 1852.0, hpz_m=1000 * 0.3048, dtlookahead=300.0, out=None):
+    """All-pairs state-based CD row outputs for rows [row0,row1) of every env.  rec: [E,N,8] f32 CUDA."""
+    lib = L.load()
+    E, N, _ = rec.shape
+    row1 = N if row1 is None else row1
+    dev = rec.device
+    if out is None:
+        out = dict(inconf=torch.zeros((E, N), dtype=torch.uint8, device=dev),
+                   nconf=torch.zeros((E, N), dtype=torch.int32, device=dev),
+                   nlos=torch.zeros((E, N), dtype=torch.int32, device=dev),
+                   near_idx=torch.full((E, N), -1, dtype=torch.int32, device=dev),
+                   near_tcpa=torch.zeros((E, N), dtype=torch.float32, device=dev),
+                   near_dcpa=torch.zeros((E, N), dtype=torch.float32, device=dev),
+                   near_tin=torch.zeros((E, N), dtype=torch.float32, device=dev),
+                   tcpamax=torch.zeros((E, N), dtype=torch.float32, device=dev))
+    p = L.CdParams(E, N, row0, row1, rpz_m, hpz_m, dtlookahead, 0)
+    s = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    L.check(lib.bsg_cd_sweep(C.byref(p), _ptr(rec), *[_ptr(out[k]) for k in ('inconf', 'nconf', 'nlos', 'near_idx',
+                                                                                 'near_tcpa', 'near_dcpa', 'near_tin',
+                                                                                 'tcpamax')], s))
+    return out
+
+
+def ndmap(rec, nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=0.0, cx=1.0, cy=1.0, cz=1.0, dt=10.0, out=None):
+    """rec: [E,6,n] f32 CUDA (x,y,z,u,v,w).  Returns occ u8, conf u8 [E,nt,nz,ny,nx], ncell i32 [E,nt]."""
+    lib = L.load()
+    E, _, n = rec.shape
+    dev = rec.device
+    if out is None:
+        out = (torch.empty((E, nt, nz, ny, nx), dtype=torch.uint8, device=dev),
+               torch.empty((E, nt, nz, ny, nx), dtype=torch.uint8, device=dev),
+               torch.empty((E, nt), dtype=torch.int32, device=dev))
+    p = L.NdmapParams(E, n, nx, ny, nz, nt, x0, y0, z0, cx, cy, cz, dt, 0)
+    s = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    L.check(lib.bsg_ndmap(C.byref(p), _ptr(rec), _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), s))
+    return out
+
+
+def peak_fp32(device=0, iters=4096):
+    lib = L.load()
+    tf, ms = C.c_double(0), C.c_double(0)
+    L.check(lib.bsg_peak_fp32(device, iters, C.byref(tf), C.byref(ms)))
+    return tf.value, ms.value
+
+
+def peak_fp64(device=0, iters=2048):
+    lib = L.load()
+    tf, ms = C.c_double(0), C.c_double(0)
+    L.check(lib.bsg_peak_fp64(device, iters, C.byref(tf), C.byref(ms)))
+    return tf.value, ms.value

@@ -1,0 +1,118 @@
+// bsg_api_step.inl -- state interchange and the step entry points (included by bsg_api.cu).
+
+template <typename R>
+static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *out, int substeps, int observe_only,
+                       cudaStream_t s) {
+    const bsg_config &g = h->cfg;
+    StepArgs<R> A;
+    A.kind = g.env_kind; A.E = g.num_envs; A.N = g.max_ac; A.substeps = substeps; A.asas_on = g.asas_on;
+    A.reso_on = g.reso_on; A.reso_off_own = g.reso_off_own; A.max_steps = g.max_episode_steps; A.epb = h->epb;
+    A.observe_only = observe_only;
+    A.dt = (R)g.simdt;
+    A.P.rpz = g.rpz_m; A.P.hpz = g.hpz_m; A.P.dtlook = g.dtlookahead; A.P.fach = g.resofach; A.P.facv = g.resofacv;
+    A.pos = h->pos; A.st = (R *)h->st; A.reso = h->reso; A.nac = h->nac; A.ev = h->ev;
+    A.actions = (const R *)actions;
+    if (out) A.out = *out; else memset(&A.out, 0, sizeof(A.out));
+    const int grid = (g.num_envs + h->epb - 1) / h->epb;
+    step_kernel<R><<<grid, h->tpb, h->smem, s>>>(A);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    return BSG_OK;
+}
+
+extern "C" {
+
+int bsg_set_state(bsg_handle *h, const double *ac, const uint64_t *reso, const int32_t *nac, const double *ev) {
+    if (!h) return BSG_ERR_ARG;
+    const bsg_config &g = h->cfg;
+    const size_t EN = (size_t)g.num_envs * g.max_ac;
+    CK(h, cudaSetDevice(g.device));
+    if (ac) {
+        CK(h, cudaMemcpy(h->stage64, ac, (size_t)g.num_envs * BSG_NF * g.max_ac * sizeof(double), cudaMemcpyHostToDevice));
+        const int tb = 256, gb = (int)((EN + tb - 1) / tb);
+        if (g.precision == BSG_FP64) import_state_kernel<double><<<gb, tb>>>(h->stage64, g.num_envs, g.max_ac, h->pos, (double *)h->st);
+        else import_state_kernel<float><<<gb, tb>>>(h->stage64, g.num_envs, g.max_ac, h->pos, (float *)h->st);
+        h->launches++;
+        CK(h, cudaGetLastError());
+    }
+    if (reso) CK(h, cudaMemcpy(h->reso, reso, EN * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    if (nac) CK(h, cudaMemcpy(h->nac, nac, g.num_envs * sizeof(int32_t), cudaMemcpyHostToDevice));
+    if (ev) CK(h, cudaMemcpy(h->ev, ev, (size_t)g.num_envs * BSG_NE * sizeof(double), cudaMemcpyHostToDevice));
+    CK(h, cudaDeviceSynchronize());
+    return BSG_OK;
+}
+
+int bsg_get_state(bsg_handle *h, double *ac, uint64_t *reso, int32_t *nac, double *ev) {
+    if (!h) return BSG_ERR_ARG;
+    const bsg_config &g = h->cfg;
+    const size_t EN = (size_t)g.num_envs * g.max_ac;
+    CK(h, cudaSetDevice(g.device));
+    CK(h, cudaDeviceSynchronize());
+    if (ac) {
+        CK(h, cudaMemset(h->stage64, 0, (size_t)g.num_envs * BSG_NF * g.max_ac * sizeof(double)));
+        const int tb = 256, gb = (int)((EN + tb - 1) / tb);
+        if (g.precision == BSG_FP64) export_state_kernel<double><<<gb, tb>>>(h->stage64, g.num_envs, g.max_ac, h->pos, (const double *)h->st);
+        else export_state_kernel<float><<<gb, tb>>>(h->stage64, g.num_envs, g.max_ac, h->pos, (const float *)h->st);
+        h->launches++;
+        CK(h, cudaGetLastError());
+        CK(h, cudaMemcpy(ac, h->stage64, (size_t)g.num_envs * BSG_NF * g.max_ac * sizeof(double), cudaMemcpyDeviceToHost));
+    }
+    if (reso) CK(h, cudaMemcpy(reso, h->reso, EN * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    if (nac) CK(h, cudaMemcpy(nac, h->nac, g.num_envs * sizeof(int32_t), cudaMemcpyDeviceToHost));
+    if (ev) CK(h, cudaMemcpy(ev, h->ev, (size_t)g.num_envs * BSG_NE * sizeof(double), cudaMemcpyDeviceToHost));
+    return BSG_OK;
+}
+
+int bsg_step(bsg_handle *h, const void *actions_dev, const bsg_step_out *out, void *stream) {
+    if (!h) return BSG_ERR_ARG;
+    if (h->cfg.env_kind != BSG_KIND_RAW && !actions_dev) { h->err = "bsg_step: actions_dev is NULL"; return BSG_ERR_ARG; }
+    CK(h, cudaSetDevice(h->cfg.device));
+    if (h->cfg.precision == BSG_FP64) return launch_step<double>(h, actions_dev, out, h->cfg.substeps, 0, (cudaStream_t)stream);
+    return launch_step<float>(h, actions_dev, out, h->cfg.substeps, 0, (cudaStream_t)stream);
+}
+
+int bsg_observe(bsg_handle *h, void *obs_dev, void *stream) {
+    if (!h || !obs_dev) return BSG_ERR_ARG;
+    if (h->cfg.env_kind == BSG_KIND_RAW) return BSG_ERR_UNSUPPORTED;
+    CK(h, cudaSetDevice(h->cfg.device));
+    bsg_step_out o;
+    memset(&o, 0, sizeof(o));
+    o.obs = obs_dev;
+    if (h->cfg.precision == BSG_FP64) return launch_step<double>(h, nullptr, &o, 0, 1, (cudaStream_t)stream);
+    return launch_step<float>(h, nullptr, &o, 0, 1, (cudaStream_t)stream);
+}
+
+int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, int32_t *term, int32_t *trunc, void *info) {
+    if (!h || !actions) return BSG_ERR_ARG;
+    const bsg_config &g = h->cfg;
+    const size_t rs = rsize(h), E = g.num_envs;
+    CK(h, cudaSetDevice(g.device));
+    memcpy(h->h_act, actions, h->act_bytes);
+    CK(h, cudaMemcpyAsync(h->d_act, h->h_act, h->act_bytes, cudaMemcpyHostToDevice, h->hs));
+    char *d = (char *)h->d_out;
+    bsg_step_out o;
+    memset(&o, 0, sizeof(o));
+    o.obs = d; d += E * h->obs_dim * rs;
+    o.reward = d; d += E * rs;
+    o.info = d; d += E * 4 * rs;
+    o.terminated = (int32_t *)d; d += E * sizeof(int32_t);
+    o.truncated = (int32_t *)d;
+    int rc = g.precision == BSG_FP64 ? launch_step<double>(h, h->d_act, &o, g.substeps, 0, h->hs)
+                                     : launch_step<float>(h, h->d_act, &o, g.substeps, 0, h->hs);
+    if (rc != BSG_OK) return rc;
+    CK(h, cudaMemcpyAsync(h->h_out, h->d_out, h->out_bytes, cudaMemcpyDeviceToHost, h->hs));
+    CK(h, cudaStreamSynchronize(h->hs));
+    const char *s = (const char *)h->h_out;
+    if (obs) memcpy(obs, s, E * h->obs_dim * rs);
+    s += E * h->obs_dim * rs;
+    if (reward) memcpy(reward, s, E * rs);
+    s += E * rs;
+    if (info) memcpy(info, s, E * 4 * rs);
+    s += E * 4 * rs;
+    if (term) memcpy(term, s, E * sizeof(int32_t));
+    s += E * sizeof(int32_t);
+    if (trunc) memcpy(trunc, s, E * sizeof(int32_t));
+    return BSG_OK;
+}
+
+}  // extern "C"

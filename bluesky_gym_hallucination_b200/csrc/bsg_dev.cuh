@@ -1,0 +1,126 @@
+// bsg_dev.cuh -- device-side constants and scalar models of the batched BlueSky core (sm_100a).
+// What is computed follows SURVEY.md Appendix A (BlueSky 1.0.3 behaviour the reference envs rely on:
+// bs.sim.step() at bluesky_gym/envs/horizontal_cr_env.py:109, vertical_cr_env.py:289,
+// sector_cr_env.py:121); how it is computed is this repo's own: templated on the real type R,
+// R = double is the literal "parity" order of operations, R = float the fast path.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <math.h>
+#include "../../include/bsgcore.h"
+
+namespace bsg {
+
+constexpr double kPi = 3.141592653589793238462643383279502884;
+constexpr double kD2R = kPi / 180.0;
+constexpr double kR2D = 180.0 / kPi;
+constexpr double kRe = 6371000.0;
+constexpr double kNm = 1852.0;
+constexpr double kFt = 0.3048;
+constexpr double kFpm = 0.3048 / 60.0;
+constexpr double kKts = 0.514444;
+constexpr double kG0 = 9.80665;
+constexpr double kRgas = 287.05287;
+constexpr double kP0 = 101325.0;
+constexpr double kRho0 = 1.225;
+constexpr double kGamma = 1.40;
+constexpr double kVsDef = 1500.0 * kFpm;
+constexpr double kBank = 25.0 * kD2R;
+// performance envelope (A320-like, documented in DESIGN.md; same table as the oracle's)
+enum Phase { PH_NA, PH_GD, PH_IC, PH_CL, PH_CR, PH_DE, PH_AP };
+constexpr double kVminIc = 65.0, kVmaxIc = 82.0, kVminEr = 80.0, kVmaxEr = 180.0, kVminAp = 60.0, kVmaxAp = 100.0;
+constexpr double kVsMin = -20.0, kVsMax = 20.0, kHmax = 12131.0, kMmo = 0.82, kAxMax = 2.0;
+
+// device state: positions always fp64 (fp32 degrees cannot hold a 5 NM separation to 1e-5),
+// everything else in R.  Layout per env: pos[2][N], st[NS][N]  (field-major => coalesced by aircraft).
+enum StField { S_ALT, S_HDG, S_TAS, S_VS, S_CAS, S_SELSPD, S_SELALT, S_SELVS, S_APTRK, S_AX,
+               S_ASAS_TRK, S_ASAS_TAS, S_ASAS_VS, S_ASAS_ALT, S_ASAS_ACTIVE, S_PHASE,
+               // fast-path caches of pure functions (key -> value); unused by the parity path
+               S_C_ALT, S_C_SPD, S_C_APTAS, S_C_PH, S_C_SELALT, S_C_LO, S_C_HI, S_NS };
+
+template <typename R> __device__ __forceinline__ R rsgn(R x) { return R((x > R(0)) - (x < R(0))); }
+
+// numpy/Python float modulo (result takes the sign of the divisor)
+__device__ __forceinline__ double pymod(double a, double b) {
+    double r = fmod(a, b);
+    if (r != 0.0 && ((r < 0.0) != (b < 0.0))) r += b;
+    return r;
+}
+// fast path: a in (-720, 1080) for every call site; two conditional wraps replace fmodf
+__device__ __forceinline__ float wrap360(float a) {
+    a -= 360.0f * floorf(a * (1.0f / 360.0f));
+    a = (a >= 360.0f) ? a - 360.0f : a;
+    return (a < 0.0f) ? a + 360.0f : a;
+}
+template <typename R> __device__ __forceinline__ R mod360(R a) {
+    if constexpr (sizeof(R) == 8) return pymod(a, 360.0); else return wrap360(a);
+}
+
+// ------------------------------------------------------------------ ISA atmosphere (always fp64: pure
+// functions evaluated rarely on the fast path thanks to the key/value caches)
+__device__ __forceinline__ void vatmos(double h, double &p, double &rho, double &T) {
+    T = fmax(288.15 - 0.0065 * h, 216.65);
+    double rhotrop = 1.225 * pow(T / 288.15, 4.256848030018761);
+    double dhstrat = fmax(0.0, h - 11000.0);
+    rho = rhotrop * exp(-dhstrat / 6341.552161);
+    p = rho * kRgas * T;
+}
+__device__ __forceinline__ double vvsound(double h) { return sqrt(kGamma * kRgas * fmax(288.15 - 0.0065 * h, 216.65)); }
+static __device__ __noinline__ double vtas2cas(double tas, double h) {
+    double p, rho, T;
+    vatmos(h, p, rho, T);
+    double qdyn = p * (pow(1.0 + rho * tas * tas / (7.0 * p), 3.5) - 1.0);
+    double cas = sqrt(7.0 * kP0 / kRho0 * (pow(qdyn / kP0 + 1.0, 2.0 / 7.0) - 1.0));
+    return tas < 0 ? -1 * cas : cas;
+}
+static __device__ __noinline__ double vcas2tas(double cas, double h) {
+    double p, rho, T;
+    vatmos(h, p, rho, T);
+    double qdyn = kP0 * (pow(1.0 + kRho0 * cas * cas / (7.0 * kP0), 3.5) - 1.0);
+    double tas = sqrt(7.0 * p / rho * (pow(1.0 + qdyn / p, 2.0 / 7.0) - 1.0));
+    return cas < 0 ? -1 * tas : tas;
+}
+__device__ __forceinline__ double vcasormach2tas(double spd, double h) {
+    return fabs(spd) < 1 ? spd * vvsound(h) : vcas2tas(spd, h);
+}
+
+// ------------------------------------------------------------------ performance envelope
+template <typename R> __device__ __forceinline__ int flight_phase(R vs, R alt) {
+    R roc = vs / R(kFpm), h = alt / R(kFt);
+    int ph = PH_NA;
+    if (h <= R(75)) ph = PH_GD;
+    if (h > R(75) && h <= R(1000) && roc >= R(150)) ph = PH_IC;
+    if (h > R(75) && h <= R(1000) && roc <= R(-150)) ph = PH_AP;
+    if (h > R(1000) && roc >= R(150)) ph = PH_CL;
+    if (h > R(1000) && roc <= R(-150)) ph = PH_DE;
+    if (h > R(10000) && roc > R(-150) && roc < R(150)) ph = PH_CR;
+    return ph;
+}
+__device__ __forceinline__ void phase_vlimits(int ph, double &vmin, double &vmax) {
+    bool enroute = (ph == PH_CL) || (ph == PH_CR) || (ph == PH_DE);
+    vmin = 0.0; vmax = kVmaxEr;
+    if (ph == PH_IC) vmin = kVminIc;
+    if (enroute) vmin = kVminEr;
+    if (ph == PH_AP) vmin = kVminAp;
+    if (ph == PH_IC || ph == PH_GD) vmax = kVmaxIc;
+    if (ph == PH_AP) vmax = kVmaxAp;
+}
+
+// ------------------------------------------------------------------ flat-earth geometry (literal form)
+// kwikqdrdist of bluesky/tools/geo.py; qdr [deg 0..360), dist [NM]
+__device__ __forceinline__ void kwikqdrdist(double lata, double lona, double latb, double lonb, double &qdr, double &dist) {
+    double dlat = (latb - lata) * kD2R;
+    double dlon = (pymod((lonb - lona) + 180, 360) - 180) * kD2R;
+    double cavelat = cos((lata + latb) * kD2R * 0.5);
+    double dangle = sqrt(dlat * dlat + dlon * dlon * cavelat * cavelat);
+    dist = kRe * dangle / kNm;
+    qdr = pymod(atan2(dlon * cavelat, dlat) * kR2D, 360.0);
+}
+// env-layer angle wrap (bluesky_gym/envs/common/functions.py:17-22): wraps once only
+template <typename R> __device__ __forceinline__ R bound180(R a) {
+    if (a > R(180)) return -(R(360) - a);
+    if (a < R(-180)) return R(360) + a;
+    return a;
+}
+
+}  // namespace bsg

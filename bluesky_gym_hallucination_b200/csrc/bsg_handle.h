@@ -1,0 +1,34 @@
+// bsg_handle.h -- the opaque handle behind include/bsgcore.h (shared by the .cu files of the library).
+#pragma once
+#include <cuda_runtime.h>
+#include <string>
+#include <cstdint>
+#include "../../include/bsgcore.h"
+
+struct bsg_handle {
+    bsg_config cfg;
+    int obs_dim, act_dim, epb, tpb;
+    size_t smem;
+    double *pos = nullptr;            // [2][E*N]
+    void *st = nullptr;               // R [S_NS][E*N]
+    unsigned long long *reso = nullptr;
+    int *nac = nullptr;
+    double *ev = nullptr;             // [E][BSG_NE]
+    double *stage64 = nullptr;        // [E][BSG_NF][N] interchange staging (device)
+    // host-buffer step: pinned staging + device mirrors
+    void *h_act = nullptr, *h_out = nullptr, *d_act = nullptr, *d_out = nullptr;
+    size_t out_bytes = 0, act_bytes = 0;
+    cudaStream_t hs = nullptr;
+    int64_t launches = 0;
+    std::string err;
+};
+
+#define CK(h, call)                                                                           \
+    do {                                                                                      \
+        cudaError_t _e = (call);                                                              \
+        if (_e != cudaSuccess) {                                                              \
+            if (h) (h)->err = std::string(#call) + ": " + cudaGetErrorString(_e);             \
+            return BSG_ERR_CUDA;                                                              \
+        }                                                                                     \
+    } while (0)
+

@@ -1,0 +1,150 @@
+// bsg_ndmap.cu -- ND-map: 4D (t, z, y, x) spatial-temporal occupancy / conflict grid over straight-line
+// look-ahead trajectories.  No reference implementation exists (SURVEY.md 0.3 tier C): the spec is this
+// repo's own (DESIGN.md "ND-map"); the CPU restatement of the same spec is oracle/c/bsgo_ndmap.c.
+// One CTA rasterises one (env, time-slab): aircraft samples are counted with shared-memory atomics into
+// a u16 grid (two counters per 32-bit word), a separable 3x3x3 box sum marks cells whose neighbourhood
+// holds >= 2 aircraft, and the slab is streamed to HBM with 16-byte stores (the kernel is HBM-write bound).
+// Also holds the FP32 / FP64 FMA-chain micro-benchmarks (the measured non-tensor roofline denominators).
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "../../include/bsgcore.h"
+
+namespace {
+
+constexpr int kNdThreads = 512;
+
+__global__ void __launch_bounds__(kNdThreads) ndmap_kernel(const bsg_ndmap_params p, float icx, float icy, float icz,
+                                                           const float *__restrict__ rec, uint8_t *__restrict__ occ,
+                                                           uint8_t *__restrict__ conf, int32_t *__restrict__ ncell) {
+    extern __shared__ __align__(16) unsigned char smem[];
+    const int nx = p.nx, ny = p.ny, nz = p.nz, n = p.num_ac;
+    const int cells = nx * ny * nz;
+    uint16_t *cnt = reinterpret_cast<uint16_t *>(smem);          // [cells]
+    uint16_t *sxy = cnt + cells;                                 // [cells]
+    __shared__ int s_ncf;
+    const int k = blockIdx.x, e = blockIdx.y;
+    uint32_t *cw = reinterpret_cast<uint32_t *>(cnt);
+    for (int c = threadIdx.x; c < cells / 2; c += kNdThreads) cw[c] = 0u;
+    if (threadIdx.x == 0) s_ncf = 0;
+    __syncthreads();
+    const float *r = rec + (size_t)e * 6 * n;
+    const float t = (float)(k + 1) * p.dt;
+    for (int a = threadIdx.x; a < n; a += kNdThreads) {
+        const float px = fmaf(r[3 * n + a], t, r[a]);
+        const float py = fmaf(r[4 * n + a], t, r[n + a]);
+        const float pz = fmaf(r[5 * n + a], t, r[2 * n + a]);
+        const int ix = (int)floorf((px - p.x0) * icx);
+        const int iy = (int)floorf((py - p.y0) * icy);
+        const int iz = (int)floorf((pz - p.z0) * icz);
+        if (ix < 0 || ix >= nx || iy < 0 || iy >= ny || iz < 0 || iz >= nz) continue;
+        const int c = (iz * ny + iy) * nx + ix;
+        atomicAdd(&cw[c >> 1], (c & 1) ? 0x10000u : 1u);         // u16 lanes: no carry for n <= 65535
+    }
+    __syncthreads();
+    // pass 1: 3x3 box sum in the (y, x) plane
+    for (int c = threadIdx.x; c < cells; c += kNdThreads) {
+        const int x = c % nx, y = (c / nx) % ny;
+        unsigned s = 0;
+#pragma unroll
+        for (int dy = -1; dy <= 1; dy++) {
+            const int yy = y + dy;
+            if (yy < 0 || yy >= ny) continue;
+            const uint16_t *row = cnt + c + dy * nx;
+            s += row[0] + (x > 0 ? row[-1] : 0) + (x < nx - 1 ? row[1] : 0);
+        }
+        sxy[c] = (uint16_t)s;
+    }
+    __syncthreads();
+    // pass 2: sum over z, emit 16 cells per thread as one 16-byte store each for occ and conf
+    const size_t slab = ((size_t)e * p.nt + k) * cells;
+    int ncf = 0;
+    for (int g = threadIdx.x; g < cells / 16; g += kNdThreads) {
+        const int c0 = g * 16, z = c0 / (nx * ny);
+        uint32_t ow[4], fw[4];
+#pragma unroll
+        for (int w = 0; w < 4; w++) {
+            uint32_t o = 0, f = 0;
+#pragma unroll
+            for (int b = 0; b < 4; b++) {
+                const int c = c0 + w * 4 + b;
+                unsigned s = sxy[c] + (z > 0 ? sxy[c - nx * ny] : 0) + (z < nz - 1 ? sxy[c + nx * ny] : 0);
+                const unsigned cc = cnt[c] > 255 ? 255u : cnt[c];
+                o |= cc << (8 * b);
+                f |= (s >= 2 ? 1u : 0u) << (8 * b);
+                ncf += s >= 2;
+            }
+            ow[w] = o; fw[w] = f;
+        }
+        *reinterpret_cast<uint4 *>(occ + slab + c0) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+        *reinterpret_cast<uint4 *>(conf + slab + c0) = make_uint4(fw[0], fw[1], fw[2], fw[3]);
+    }
+#pragma unroll
+    for (int m = 16; m > 0; m >>= 1) ncf += __shfl_xor_sync(0xffffffffu, ncf, m);
+    if ((threadIdx.x & 31) == 0 && ncf) atomicAdd(&s_ncf, ncf);
+    __syncthreads();
+    if (threadIdx.x == 0) ncell[(size_t)e * p.nt + k] = s_ncf;
+}
+
+template <typename T> __global__ void __launch_bounds__(256) fma_peak_kernel(T *out, int iters, T a, T b) {
+    T x0 = T(threadIdx.x) * T(1e-3), x1 = x0 + T(1), x2 = x0 + T(2), x3 = x0 + T(3);
+    T x4 = x0 + T(4), x5 = x0 + T(5), x6 = x0 + T(6), x7 = x0 + T(7);
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 8; u++) {
+            x0 = x0 * a + b; x1 = x1 * a + b; x2 = x2 * a + b; x3 = x3 * a + b;
+            x4 = x4 * a + b; x5 = x5 * a + b; x6 = x6 * a + b; x7 = x7 * a + b;
+        }
+    }
+    T s = x0 + x1 + x2 + x3 + x4 + x5 + x6 + x7;
+    if (s == T(12345.678)) out[blockIdx.x * blockDim.x + threadIdx.x] = s;   // never true: keeps the chains live
+}
+
+template <typename T> int run_peak(int device, int iters, double *tflops, double *ms) {
+    if (!tflops || iters < 1) return BSG_ERR_ARG;
+    if (cudaSetDevice(device) != cudaSuccess) return BSG_ERR_CUDA;
+    T *d = nullptr;
+    const int blocks = 148 * 8, threads = 256;
+    if (cudaMalloc(&d, sizeof(T) * blocks * threads) != cudaSuccess) return BSG_ERR_NOMEM;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    fma_peak_kernel<T><<<blocks, threads>>>(d, iters / 8 + 1, T(0.999), T(0.001));   // warm-up
+    float best = 1e30f;
+    for (int rep = 0; rep < 5; rep++) {
+        cudaEventRecord(e0);
+        fma_peak_kernel<T><<<blocks, threads>>>(d, iters, T(0.999), T(0.001));
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float t = 0;
+        cudaEventElapsedTime(&t, e0, e1);
+        best = t < best ? t : best;
+    }
+    cudaError_t err = cudaGetLastError();
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(d);
+    if (err != cudaSuccess) return BSG_ERR_CUDA;
+    const double flop = 2.0 * 64.0 * (double)iters * blocks * threads;
+    *tflops = flop / (best * 1e-3) / 1e12;
+    if (ms) *ms = best;
+    return BSG_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int bsg_ndmap(const bsg_ndmap_params *p, const float *rec, uint8_t *occ, uint8_t *conf, int32_t *ncell, void *stream) {
+    if (!p || !rec || !occ || !conf || !ncell) return BSG_ERR_ARG;
+    const long cells = (long)p->nx * p->ny * p->nz;
+    if (p->num_envs < 1 || p->num_ac < 1 || p->num_ac > 65535 || p->nt < 1 || cells < 16 || (p->nx % 16) != 0) return BSG_ERR_ARG;
+    const size_t smem = (size_t)cells * 2 * sizeof(uint16_t);
+    if (smem > 227 * 1024) return BSG_ERR_UNSUPPORTED;
+    if (cudaFuncSetAttribute(ndmap_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return BSG_ERR_CUDA;
+    const float icx = 1.0f / p->cell_x, icy = 1.0f / p->cell_y, icz = 1.0f / p->cell_z;
+    dim3 grid(p->nt, p->num_envs);
+    ndmap_kernel<<<grid, kNdThreads, smem, (cudaStream_t)stream>>>(*p, icx, icy, icz, rec, occ, conf, ncell);
+    return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+int bsg_peak_fp32(int device, int iters, double *tflops, double *ms) { return run_peak<float>(device, iters, tflops, ms); }
+int bsg_peak_fp64(int device, int iters, double *tflops, double *ms) { return run_peak<double>(device, iters, tflops, ms); }
+
+}  // extern "C"

@@ -1,0 +1,119 @@
+// bsg_pair.cuh -- one ordered (ownship i, intruder j) evaluation of BlueSky's state-based conflict
+// detection (StateBased.detect) and the MVP displacement for a conflict pair (MVP.MVP,
+// SURVEY.md A.7).  Two forms:
+//   PairLit  (double): the literal operation order of the reference-style numpy code (qdr via atan2,
+//                      dx/dy via sin/cos of qdr, dcpa2 = |dist^2 - tcpa^2 dv2|) -> parity path, <= 1e-12.
+//   PairFast (float) : algebraically identical, no transcendental per pair: dx = Re*dlon*cos(mean lat) with
+//                      cos((a+b)/2) = ca_i ca_j - sa_i sa_j from per-aircraft half-angle terms, and
+//                      dcpa2 = (dx dv - dy du)^2 / dv2 (cross form: 10x better conditioned in fp32 than the
+//                      difference of squares).  3 MUFU (rcp, rcp, sqrt) + ~55 FP32 issue slots per pair.
+#pragma once
+#include "bsg_dev.cuh"
+
+namespace bsg {
+
+struct __align__(16) RecFast { float x, y, alt, u, v, vs, ca, sa; };         // 32 B: two float4
+struct __align__(16) RecLit { double lat, lon, alt, u, v, vs, hdg, pad; };   // 64 B
+
+struct CdParams { double rpz, hpz, dtlook, fach, facv; };
+
+template <typename R> struct PairOut {
+    R tcpa, dcpa2, tin, dx, dy, dist, dalt;
+    bool sw, los;
+};
+
+__device__ __forceinline__ void pair_lit(const RecLit &a, const RecLit &b, const CdParams &P, PairOut<double> &o) {
+    double qdr, dnm;
+    kwikqdrdist(a.lat, a.lon, b.lat, b.lon, qdr, dnm);
+    double dist = dnm * kNm;
+    double qr = qdr * kD2R;
+    double dx = dist * sin(qr), dy = dist * cos(qr);
+    double du = b.u - a.u, dv = b.v - a.v;
+    double dv2 = du * du + dv * dv;
+    if (fabs(dv2) < 1e-6) dv2 = 1e-6;
+    double vrel = sqrt(dv2);
+    double tcpa = -(du * dx + dv * dy) / dv2;
+    double dcpa2 = fabs(dist * dist - tcpa * tcpa * dv2);
+    double R2 = P.rpz * P.rpz;
+    bool swhor = dcpa2 < R2;
+    double dtinhor = sqrt(fmax(0.0, R2 - dcpa2)) / vrel;
+    double tinhor = swhor ? tcpa - dtinhor : 1e8;
+    double touthor = swhor ? tcpa + dtinhor : -1e8;
+    double dalt = b.alt - a.alt;
+    double dvs = b.vs - a.vs;
+    if (fabs(dvs) < 1e-6) dvs = 1e-6;
+    double thi = (dalt + P.hpz) / -dvs, tlo = (dalt - P.hpz) / -dvs;
+    double tinver = fmin(thi, tlo), toutver = fmax(thi, tlo);
+    double tin = fmax(tinver, tinhor), tout = fmin(toutver, touthor);
+    o.sw = swhor && (tin <= tout) && (tout > 0.0) && (tin < P.dtlook);
+    o.los = (dist < P.rpz) && (fabs(dalt) < P.hpz);
+    o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist = dist; o.dalt = dalt;
+}
+
+struct CdParamsF { float R2, hpz, dtlook, rpz, rpz_m, hpz_m; };
+
+__device__ __forceinline__ void pair_fast(const RecFast &a, const RecFast &b, const CdParamsF &P, PairOut<float> &o) {
+    float dy = b.y - a.y;
+    float cav = fmaf(a.ca, b.ca, -(a.sa * b.sa));
+    float dx = (b.x - a.x) * cav;
+    float dist2 = fmaf(dx, dx, dy * dy);
+    float du = b.u - a.u, dv = b.v - a.v;
+    float dv2 = fmaxf(fmaf(du, du, dv * dv), 1e-6f);
+    float idv2 = __frcp_rn(dv2);
+    float tcpa = -fmaf(du, dx, dv * dy) * idv2;
+    float cr = fmaf(dx, dv, -(dy * du));
+    float dcpa2 = cr * cr * idv2;
+    bool swhor = dcpa2 < P.R2;
+    float dtinhor = sqrtf(fmaxf(0.0f, P.R2 - dcpa2) * idv2);
+    float tinhor = swhor ? tcpa - dtinhor : 1e8f;
+    float touthor = swhor ? tcpa + dtinhor : -1e8f;
+    float dalt = b.alt - a.alt;
+    float dvs = b.vs - a.vs;
+    dvs = (fabsf(dvs) < 1e-6f) ? 1e-6f : dvs;
+    float nidvs = -__frcp_rn(dvs);
+    float thi = (dalt + P.hpz) * nidvs, tlo = (dalt - P.hpz) * nidvs;
+    float tin = fmaxf(fminf(thi, tlo), tinhor), tout = fminf(fmaxf(thi, tlo), touthor);
+    o.sw = swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
+    o.los = (dist2 < P.R2) && (fabsf(dalt) < P.hpz);
+    o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist = dist2 /* squared */; o.dalt = dalt;
+}
+
+// MVP displacement of ownship 1 for one conflict pair; drel = (dx, dy, dalt) is intruder relative to ownship.
+// Returns the horizontal pair (dv1, dv2); the vertical term is not needed by the default
+// horizontal-only resolution (newvs = own vs, asas alt = selalt), so it is not evaluated.
+template <typename R>
+__device__ __forceinline__ void mvp_pair(R dx, R dy, R dist, R tcpa, R vrelx, R vrely, R rpz_m, R &dv1, R &dv2) {
+    R dcx = dx + vrelx * tcpa, dcy = dy + vrely * tcpa;
+    R dabsH = sqrt(dcx * dcx + dcy * dcy);
+    R iH = rpz_m - dabsH;
+    if (dabsH <= R(10)) {
+        dabsH = R(10);
+        dcx = dy / dist * dabsH;
+        dcy = -dx / dist * dabsH;
+    }
+    R den = fabs(tcpa) * dabsH;
+    if (rpz_m < dist && dabsH < dist) {
+        R erratum = cos(asin(rpz_m / dist) - asin(dabsH / dist));
+        dv1 = ((rpz_m / erratum - dabsH) * dcx) / den;
+        dv2 = ((rpz_m / erratum - dabsH) * dcy) / den;
+    } else {
+        dv1 = (iH * dcx) / den;
+        dv2 = (iH * dcy) / den;
+    }
+}
+
+// per-row running outputs of the sweep
+template <typename R> struct RowAcc {
+    int nconf = 0, nlos = 0, near_idx = -1;
+    R near_tcpa = R(0), near_dcpa2 = R(0), near_tin = R(0), tcpamax = R(0);
+    __device__ __forceinline__ void add(int j, const PairOut<R> &o) {
+        nlos += o.los ? 1 : 0;
+        if (o.sw) {
+            nconf++;
+            tcpamax = o.tcpa > tcpamax ? o.tcpa : tcpamax;
+            if (near_idx < 0 || o.tcpa < near_tcpa) { near_idx = j; near_tcpa = o.tcpa; near_dcpa2 = o.dcpa2; near_tin = o.tin; }
+        }
+    }
+};
+
+}  // namespace bsg

@@ -1,0 +1,160 @@
+// bsg_step_kernel.cuh -- body of the fused env-step kernel (see bsg_step.cuh for the mapping).
+#pragma once
+#include "bsg_step.cuh"
+#include "bsg_env.cuh"
+
+namespace bsg {
+
+template <typename R>
+__device__ __forceinline__ void cd_params_for(const CdParams &P, CdParams &lit, CdParamsF &fast) {
+    lit = P;
+    fast.R2 = (float)(P.rpz * P.rpz); fast.hpz = (float)P.hpz; fast.dtlook = (float)P.dtlook;
+    fast.rpz = (float)P.rpz; fast.rpz_m = (float)(P.rpz * P.fach); fast.hpz_m = (float)(P.hpz * P.facv);
+}
+
+template <typename R>
+__global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
+    using Rec = typename RecOf<R>::type;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int N = A.N, epb = A.epb;
+    Rec *recs = reinterpret_cast<Rec *>(smem_raw);                         // [2][epb*N]
+    EnvShared<R> *es = reinterpret_cast<EnvShared<R> *>(recs + 2 * epb * N);  // [epb]
+    R *sdist = reinterpret_cast<R *>(es + epb);                            // [epb*N] hdg (resumenav) / sector distances
+
+    const int tid = threadIdx.x;
+    const int le = tid / N, i = tid - le * N;
+    const int e = blockIdx.x * epb + le;
+    const bool valid = le < epb && e < A.E;
+    const int nl = valid ? A.nac[e] : 0;
+    const bool live = valid && i < nl;
+    const size_t EN = (size_t)A.E * N, k = (size_t)(valid ? e : 0) * N + i;
+    double *ev = A.ev + (size_t)(valid ? e : 0) * BSG_NE;
+    const bool reso = A.reso_on && A.asas_on;
+
+    AcReg<R> a = {};
+    unsigned long long resorow = 0;
+    if (live) {
+        ac_load(a, A.pos, A.st, EN, k);
+        if (reso) resorow = A.reso[k];
+    }
+    // ------------------------------------------------------------------ action intake (agent = aircraft 0)
+    if (live && i == 0) {
+        es[le].anyconf[0] = 0; es[le].anyconf[1] = 0; es[le].intr = 0;
+        es[le].own_lat = a.lat; es[le].own_lon = a.lon;                    // local origin of the fp32 CD records
+        if (A.actions) {
+            if (A.kind == BSG_KIND_HORIZONTAL) {                           // horizontal_cr_env.py:272-275
+                a.aptrk = R(ev[BSG_EV_AC_HDG]) + A.actions[e] * R(45);
+            } else if (A.kind == BSG_KIND_VERTICAL) {                      // vertical_cr_env.py:242-256
+                R v = A.actions[e] * R(12.5);
+                a.selalt = v >= R(0) ? R(1000000) : R(0);
+                a.selvs = v;
+            } else if (A.kind == BSG_KIND_SECTOR) {                        // sector_cr_env.py:315-322
+                R dh = A.actions[2 * e] * R(22.5), dv = A.actions[2 * e + 1] * R(20.0 / 3);
+                a.aptrk = bound180<R>(a.hdg + dh);
+                R spd_kts = (a.cas + dv) * R(1.94384);
+                a.selspd = fabs(spd_kts) > R(1) ? spd_kts * R(kKts) : spd_kts;
+            }
+        }
+    }
+    __syncthreads();
+    const double lat0 = valid ? es[le].own_lat : 0.0, lon0 = valid ? es[le].own_lon : 0.0;
+    CdParams PL; CdParamsF PF;
+    cd_params_for<R>(A.P, PL, PF);
+
+    RowAcc<R> acc;
+    // ------------------------------------------------------------------ K substeps
+    for (int s = 0; s < A.substeps; s++) {
+        const int buf = s & 1;
+        if (A.asas_on) {
+            Rec *rb = recs + (size_t)buf * epb * N + le * N;
+            if (live) {
+                make_rec<R>(a, lat0, lon0, rb[i]);
+                if (reso) sdist[le * N + i] = a.hdg;
+            }
+            __syncthreads();
+            if (valid && i == 0) es[le].anyconf[buf ^ 1] = 0;
+            acc = RowAcc<R>();
+            R dve = R(0), dvn = R(0);
+            bool touched = false, active = false;
+            unsigned long long keep = 0;
+            if (live) {
+                const Rec me = rb[i];
+                for (int j = 0; j < nl; j++) {
+                    const Rec o = rb[j];
+                    PairOut<R> po;
+                    if constexpr (sizeof(R) == 8) pair_lit(me, o, PL, po); else pair_fast(me, o, PF, po);
+                    const bool off = (j != i);
+                    po.sw = po.sw && off; po.los = po.los && off;
+                    acc.add(j, po);
+                    if (reso) {
+                        const bool inres = off && (po.sw || ((resorow >> j) & 1ull));
+                        if (inres) {
+                            R vrx = o.u - me.u, vry = o.v - me.v;
+                            if (po.sw) {
+                                R dist, rpz_m, d1, d2;
+                                if constexpr (sizeof(R) == 8) { dist = po.dist; rpz_m = PL.rpz * PL.fach; }
+                                else { dist = sqrtf(po.dist); rpz_m = PF.rpz_m; }
+                                mvp_pair<R>(po.dx, po.dy, dist, po.tcpa, vrx, vry, rpz_m, d1, d2);
+                                dve = dve - d1; dvn = dvn - d2;
+                                if (A.reso_off_own && i == 0) { dve = R(0); dvn = R(0); }
+                            }
+                            R ddx, ddy, rpz, fach;
+                            if constexpr (sizeof(R) == 8) {
+                                ddx = kRe * ((o.lon - me.lon) * kD2R * cos(0.5 * ((o.lat + me.lat) * kD2R)));
+                                ddy = kRe * ((o.lat - me.lat) * kD2R);
+                                rpz = PL.rpz; fach = PL.fach;
+                            } else { ddx = po.dx; ddy = po.dy; rpz = PF.rpz; fach = (float)A.P.fach; }
+                            const bool past = (ddx * vrx + ddy * vry) > R(0);
+                            const R hdist = sqrt(ddx * ddx + ddy * ddy);
+                            const bool bouncing = fabs(a.hdg - sdist[le * N + j]) < R(30) && hdist < rpz * fach;
+                            touched = true;
+                            if (!past || hdist < rpz || bouncing) { active = true; keep |= 1ull << j; }
+                        }
+                    }
+                }
+            }
+            if (reso) {
+                if (acc.nconf > 0) atomicOr(&es[le].anyconf[buf], 1);
+                __syncthreads();
+                if (live) {
+                    if (es[le].anyconf[buf]) {                             // MVP.resolve ran for this env
+                        R ne = a.gse + dve, nn = a.gsn + dvn;
+                        double vmin, vmax;
+                        phase_vlimits(a.phase, vmin, vmax);
+                        if constexpr (sizeof(R) == 8) a.asas_trk = pymod(atan2(ne, nn) * 180 / kPi, 360);
+                        else { float t = atan2f(ne, nn) * float(kR2D); a.asas_trk = t < 0.0f ? t + 360.0f : t; }
+                        R newgs = sqrt(ne * ne + nn * nn);
+                        a.asas_tas = fmax(R(vmin), fmin(R(vmax), newgs));
+                        a.asas_vs = fmax(R(kVsMin), fmin(R(kVsMax), a.vs));
+                        a.asas_alt = a.selalt;
+                    }
+                    if (touched) a.asas_active = active ? 1 : 0;
+                    resorow = keep;
+                }
+            }
+        }
+        if (live) {
+            const bool last = (s == A.substeps - 1);
+            if constexpr (sizeof(R) == 8) kin_substep_lit(a, A.dt, reso, last);
+            else kin_substep_fast(a, A.dt, reso, last && i == 0 && A.kind == BSG_KIND_SECTOR);
+        }
+    }
+    if (live) {
+        ac_store(a, A.pos, A.st, EN, k);
+        if (reso) A.reso[k] = resorow;
+    }
+    if (valid && i < N) {      // CD row outputs of the last detection (dead slots: zeros / -1)
+        const bsg_step_out &o = A.out;
+        if (o.cd_inconf) o.cd_inconf[k] = acc.nconf > 0;
+        if (o.cd_nconf) o.cd_nconf[k] = acc.nconf;
+        if (o.cd_nlos) o.cd_nlos[k] = acc.nlos;
+        if (o.cd_near_idx) o.cd_near_idx[k] = acc.near_idx;
+        if (o.cd_near_tcpa) ((R *)o.cd_near_tcpa)[k] = acc.near_tcpa;
+        if (o.cd_near_dcpa) ((R *)o.cd_near_dcpa)[k] = sqrt(acc.near_dcpa2);
+        if (o.cd_near_tin) ((R *)o.cd_near_tin)[k] = acc.near_tin;
+        if (o.cd_tcpamax) ((R *)o.cd_tcpamax)[k] = acc.tcpamax;
+    }
+    env_layer<R>(A, a, es, sdist, le, i, e, nl, valid, live, ev);
+}
+
+}  // namespace bsg

@@ -1,0 +1,187 @@
+// bsg_sweep.cu -- stand-alone all-pairs state-based CD sweep for large airspaces (giant config:
+// 16 envs x 10 000 aircraft; pair matrix row-block [row0,row1) per GPU) and the record packer.
+// What: StateBased.detect row outputs.  How: every CTA owns RPB ownship rows, each row
+// is split over JS adjacent lanes (j = q, q+JS, ...), the intruder columns stream through shared
+// memory in 32 KB tiles moved by TMA bulk copies (cp.async.bulk + mbarrier, double-buffered), the
+// row outputs are combined with warp-shuffle sum / max / lexicographic-min reductions.
+#include <cuda_runtime.h>
+#include <cstdint>
+#include "bsg_pair.cuh"
+
+using namespace bsg;
+
+namespace {
+
+constexpr int kTile = 1024;            // records per j-tile: 32 KB
+constexpr int kThreads = 256;
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, int count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n .reg .pred p;\n WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n"
+        " bra WAIT_%=;\n DONE_%=:\n}" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+
+template <int JS>
+__global__ void __launch_bounds__(kThreads) cd_sweep_kernel(const bsg_cd_params p, const RecFast *__restrict__ rec,
+                                                            uint8_t *inconf, int32_t *nconf, int32_t *nlos,
+                                                            int32_t *near_idx, float *near_tcpa, float *near_dcpa,
+                                                            float *near_tin, float *tcpamax) {
+    extern __shared__ __align__(128) unsigned char smem[];
+    RecFast *tiles = reinterpret_cast<RecFast *>(smem);                     // [2][kTile]
+    uint64_t *bar = reinterpret_cast<uint64_t *>(smem + 2 * kTile * sizeof(RecFast));
+    constexpr int RPB = kThreads / JS;
+    const int N = p.num_ac, e = blockIdx.y;
+    const int r = threadIdx.x / JS, q = threadIdx.x % JS;
+    const int i = p.row0 + blockIdx.x * RPB + r;
+    const bool rowok = i < p.row1;
+    const RecFast *base = rec + (size_t)e * N;
+    const int ntiles = (N + kTile - 1) / kTile;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1); mbar_init(&bar[1], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t bytes = (uint32_t)(min(kTile, N) * sizeof(RecFast));
+        mbar_expect_tx(&bar[0], bytes);
+        tma_bulk_g2s(tiles, base, bytes, &bar[0]);
+    }
+    RecFast me = {};
+    if (rowok) {
+        const float4 *m = reinterpret_cast<const float4 *>(base + i);
+        float4 a = __ldg(m), b = __ldg(m + 1);
+        me = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+    }
+    CdParamsF P;
+    P.R2 = p.rpz_m * p.rpz_m; P.hpz = p.hpz_m; P.dtlook = p.dtlookahead; P.rpz = p.rpz_m; P.rpz_m = 0; P.hpz_m = 0;
+    RowAcc<float> acc;
+    for (int t = 0; t < ntiles; t++) {
+        const int buf = t & 1;
+        if (threadIdx.x == 0 && t + 1 < ntiles) {
+            const int n1 = min(kTile, N - (t + 1) * kTile);
+            uint32_t bytes = (uint32_t)(n1 * sizeof(RecFast));
+            mbar_expect_tx(&bar[buf ^ 1], bytes);
+            tma_bulk_g2s(tiles + (size_t)(buf ^ 1) * kTile, base + (size_t)(t + 1) * kTile, bytes, &bar[buf ^ 1]);
+        }
+        mbar_wait(&bar[buf], (t >> 1) & 1);
+        const int nt = min(kTile, N - t * kTile), j0 = t * kTile;
+        const RecFast *tb = tiles + (size_t)buf * kTile;
+#pragma unroll 4
+        for (int jj = q; jj < nt; jj += JS) {
+            const float4 *s = reinterpret_cast<const float4 *>(tb + jj);
+            const float4 a = s[0], b = s[1];
+            const RecFast o = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+            PairOut<float> po;
+            pair_fast(me, o, P, po);
+            const bool off = (j0 + jj) != i;
+            po.sw = po.sw && off; po.los = po.los && off;
+            acc.add(j0 + jj, po);
+        }
+        __syncthreads();      // everyone is done with tiles[buf] before it is refilled two iterations later
+    }
+    // combine the JS partial rows (adjacent lanes) -- warp-shuffle sum / max / lexicographic (tcpa, j) min
+    float ntc = acc.near_idx < 0 ? 3.0e38f : acc.near_tcpa;
+#pragma unroll
+    for (int m = 1; m < JS; m <<= 1) {
+        acc.nconf += __shfl_xor_sync(0xffffffffu, acc.nconf, m);
+        acc.nlos += __shfl_xor_sync(0xffffffffu, acc.nlos, m);
+        acc.tcpamax = fmaxf(acc.tcpamax, __shfl_xor_sync(0xffffffffu, acc.tcpamax, m));
+        const float otc = __shfl_xor_sync(0xffffffffu, ntc, m);
+        const int oid = __shfl_xor_sync(0xffffffffu, acc.near_idx, m);
+        const float od2 = __shfl_xor_sync(0xffffffffu, acc.near_dcpa2, m);
+        const float oti = __shfl_xor_sync(0xffffffffu, acc.near_tin, m);
+        const bool take = oid >= 0 && (acc.near_idx < 0 || otc < ntc || (otc == ntc && oid < acc.near_idx));
+        if (take) { ntc = otc; acc.near_idx = oid; acc.near_dcpa2 = od2; acc.near_tin = oti; }
+    }
+    if (rowok && q == 0) {
+        const size_t k = (size_t)e * N + i;
+        if (inconf) inconf[k] = acc.nconf > 0;
+        if (nconf) nconf[k] = acc.nconf;
+        if (nlos) nlos[k] = acc.nlos;
+        if (near_idx) near_idx[k] = acc.near_idx;
+        if (near_tcpa) near_tcpa[k] = acc.near_idx < 0 ? 0.0f : ntc;
+        if (near_dcpa) near_dcpa[k] = sqrtf(acc.near_dcpa2);
+        if (near_tin) near_tin[k] = acc.near_tin;
+        if (tcpamax) tcpamax[k] = acc.tcpamax;
+    }
+}
+
+__global__ void cd_pack_kernel(int E, int N, const double *lat, const double *lon, const float *alt, const float *trk,
+                               const float *gs, const float *vs, double lat0, double lon0, RecFast *rec) {
+    size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= (size_t)E * N) return;
+    RecFast r;
+    r.x = (float)((lon[k] - lon0) * (kD2R * kRe));
+    r.y = (float)((lat[k] - lat0) * (kD2R * kRe));
+    r.alt = alt[k];
+    float s, c;
+    sincosf(trk[k] * float(kD2R), &s, &c);
+    r.u = gs[k] * s; r.v = gs[k] * c; r.vs = vs[k];
+    sincosf((float)(lat[k] * (kD2R * 0.5)), &r.sa, &r.ca);
+    float4 *o = reinterpret_cast<float4 *>(rec + k);
+    o[0] = make_float4(r.x, r.y, r.alt, r.u);
+    o[1] = make_float4(r.v, r.vs, r.ca, r.sa);
+}
+
+template <int JS>
+cudaError_t launch_sweep(const bsg_cd_params *p, const float *rec, uint8_t *inconf, int32_t *nconf, int32_t *nlos,
+                         int32_t *near_idx, float *near_tcpa, float *near_dcpa, float *near_tin, float *tcpamax,
+                         cudaStream_t s) {
+    const size_t smem = 2 * kTile * sizeof(RecFast) + 64;
+    cudaError_t e = cudaFuncSetAttribute(cd_sweep_kernel<JS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const int rows = p->row1 - p->row0, rpb = kThreads / JS;
+    dim3 grid((rows + rpb - 1) / rpb, p->num_envs);
+    cd_sweep_kernel<JS><<<grid, kThreads, smem, s>>>(*p, reinterpret_cast<const RecFast *>(rec), inconf, nconf, nlos,
+                                                     near_idx, near_tcpa, near_dcpa, near_tin, tcpamax);
+    return cudaGetLastError();
+}
+
+}  // namespace
+
+extern "C" {
+
+int bsg_cd_pack(int32_t E, int32_t N, const double *lat, const double *lon, const float *alt, const float *trk,
+                const float *gs, const float *vs, double lat0, double lon0, float *rec, void *stream) {
+    if (E < 1 || N < 1 || !lat || !lon || !alt || !trk || !gs || !vs || !rec) return BSG_ERR_ARG;
+    const size_t EN = (size_t)E * N;
+    cd_pack_kernel<<<(unsigned)((EN + 255) / 256), 256, 0, (cudaStream_t)stream>>>(E, N, lat, lon, alt, trk, gs, vs, lat0,
+                                                                                  lon0, reinterpret_cast<RecFast *>(rec));
+    return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+int bsg_cd_sweep(const bsg_cd_params *p, const float *rec, uint8_t *inconf, int32_t *nconf, int32_t *nlos,
+                 int32_t *near_idx, float *near_tcpa, float *near_dcpa, float *near_tin, float *tcpamax, void *stream) {
+    if (!p || !rec || p->num_envs < 1 || p->num_ac < 1 || p->row0 < 0 || p->row1 > p->num_ac || p->row1 <= p->row0)
+        return BSG_ERR_ARG;
+    // pick the row split so the grid covers the 148 SMs several times over
+    const long rows = (long)(p->row1 - p->row0) * p->num_envs;
+    int js = 1;
+    while (js < 32 && rows * js < 148L * 8 * kThreads) js <<= 1;
+    cudaStream_t s = (cudaStream_t)stream;
+    cudaError_t e;
+#define SW(J) e = launch_sweep<J>(p, rec, inconf, nconf, nlos, near_idx, near_tcpa, near_dcpa, near_tin, tcpamax, s)
+    switch (js) {
+        case 1: SW(1); break;
+        case 2: SW(2); break;
+        case 4: SW(4); break;
+        case 8: SW(8); break;
+        case 16: SW(16); break;
+        default: SW(32); break;
+    }
+#undef SW
+    return e == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+}  // extern "C"

@@ -1,0 +1,147 @@
+/* bsgcore.h -- C-ABI of libbsgcore.so, the B200-native batched BlueSky-Gym simulation core.
+ *
+ * The reference (Somnathab3/bluesky-gym-hallucination) is pure Python: it has no FFI.  The
+ * calls this library replaces are the ones the reference's env layer makes into the
+ * process-global BlueSky singleton, plus the env layer's own
+ * per-step Python:
+ *   bs.traf.reset/cre/creconfs            horizontal_cr_env.py:85,91,133; vertical_cr_env.py:198,270;
+ *                                         sector_cr_env.py:88,211,217           -> bsg_reset / bsg_set_state
+ *   bs.stack.stack("HDG/SPD ..."), selalt/selvs writes
+ *                                         horizontal_cr_env.py:272-275; vertical_cr_env.py:242-256;
+ *                                         sector_cr_env.py:315-322              -> actions of bsg_step
+ *   bs.sim.step() x ACTION_FREQUENCY      horizontal_cr_env.py:107-109; vertical_cr_env.py:287-289;
+ *                                         sector_cr_env.py:119-121              -> bsg_step (fused)
+ *   _get_obs/_get_reward/_get_info        horizontal_cr_env.py:150-270; vertical_cr_env.py:113-240;
+ *                                         sector_cr_env.py:227-339              -> outputs of bsg_step
+ *   ASAS StateBased.detect / MVP.resolve  (BlueSky, "ASAS ON"/"RESO MVP"; never enabled by the reference)
+ *                                                                               -> asas_on / reso_on, bsg_cd_sweep
+ *   ND-map 4D conflict grid               (absent from the reference tree; builder-owned spec) -> bsg_ndmap
+ * INTEGRATION.md shows the ctypes binding a reference maintainer would add.
+ *
+ * Conventions: every entry returns 0 (BSG_OK) or a negative bsg_status and never throws or
+ * aborts; CUDA errors are captured into bsg_last_error().  Pointers named *_dev are device
+ * pointers on the handle's device, *_host are host pointers; the caller owns all I/O buffers.
+ * `stream` is a cudaStream_t passed as void* (NULL = legacy default stream); calls taking a
+ * stream are asynchronous on it.  A handle is bound to one device and is not thread-safe.
+ * Element type of "real" device/host buffers follows the handle's precision:
+ * float (BSG_FP32, the fast path) or double (BSG_FP64, the parity path).
+ */
+#ifndef BSGCORE_H
+#define BSGCORE_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define BSG_ABI_VERSION 1
+
+typedef enum { BSG_OK = 0, BSG_ERR_ARG = -1, BSG_ERR_CUDA = -2, BSG_ERR_NOMEM = -3, BSG_ERR_UNSUPPORTED = -4,
+               BSG_ERR_NODEVICE = -5 } bsg_status;
+enum { BSG_KIND_HORIZONTAL = 0, BSG_KIND_VERTICAL = 1, BSG_KIND_SECTOR = 2, BSG_KIND_RAW = 3 };
+enum { BSG_FP32 = 0, BSG_FP64 = 1 };
+
+/* per-aircraft state fields of the fp64 host interchange layout  ac[E][BSG_NF][N] */
+enum { BSG_F_LAT, BSG_F_LON, BSG_F_ALT, BSG_F_HDG, BSG_F_TAS, BSG_F_VS, BSG_F_CAS, BSG_F_SELSPD, BSG_F_SELALT,
+       BSG_F_SELVS, BSG_F_APTRK, BSG_F_AX, BSG_F_ASAS_TRK, BSG_F_ASAS_TAS, BSG_F_ASAS_VS, BSG_F_ASAS_ALT,
+       BSG_F_ASAS_ACTIVE, BSG_F_PHASE, BSG_NF };
+/* env-level slots of ev[E][BSG_NE] */
+#define BSG_MAXV 32
+enum { BSG_EV_WPT_LAT, BSG_EV_WPT_LON, BSG_EV_WPT_REACH, BSG_EV_AC_HDG, BSG_EV_TARGET_ALT, BSG_EV_WPT_X,
+       BSG_EV_WPT_Y, BSG_EV_NVERT, BSG_EV_TOTAL_REWARD, BSG_EV_TOTAL_INTR, BSG_EV_DRIFT_SUM, BSG_EV_DRIFT_CNT,
+       BSG_EV_FINAL_ALT, BSG_EV_STEPS, BSG_EV_POLY, BSG_NE = BSG_EV_POLY + 2 * BSG_MAXV };
+
+typedef struct bsg_handle bsg_handle;
+
+typedef struct bsg_config {
+    int32_t struct_size;      /* sizeof(bsg_config), for ABI evolution */
+    int32_t env_kind;         /* BSG_KIND_* */
+    int32_t num_envs;         /* E */
+    int32_t max_ac;           /* N: aircraft slots per env (aircraft 0 = agent) */
+    int32_t precision;        /* BSG_FP32 | BSG_FP64 */
+    int32_t substeps;         /* ACTION_FREQUENCY; 0 = the reference's value for env_kind (10/30/5) */
+    int32_t asas_on;          /* state-based CD every substep (BlueSky "ASAS ON") */
+    int32_t reso_on;          /* MVP resolution + resumenav (BlueSky "RESO MVP"); needs asas_on, N <= 64 */
+    int32_t reso_off_own;     /* agent does not resolve (BlueSky "RESOOFF KL001") */
+    int32_t max_episode_steps;/* TimeLimit: truncate when reached; 0 = never */
+    int32_t device;           /* CUDA device ordinal */
+    int32_t reserved;
+    double simdt;             /* 0 = the reference's DT for env_kind (5/1/1 s) */
+    double rpz_m, hpz_m;      /* protected zone; 0 = 5 NM / 1000 ft */
+    double dtlookahead;       /* 0 = 300 s */
+    double resofach, resofacv;/* 0 = 1.05 */
+} bsg_config;
+
+/* device output pointers of bsg_step; any pointer may be NULL (not written) */
+typedef struct bsg_step_out {
+    void *obs;                /* real [E][obs_dim] */
+    void *reward;             /* real [E] */
+    int32_t *terminated;      /* [E] 0/1 */
+    int32_t *truncated;       /* [E] 0/1 */
+    void *info;               /* real [E][4]: total_reward, total_intrusions, average_drift|final_altitude, steps */
+    uint8_t *cd_inconf;       /* [E][N] row has a conflict (last CD call of the step) */
+    int32_t *cd_nconf;        /* [E][N] conflict pairs in the row */
+    int32_t *cd_nlos;         /* [E][N] loss-of-separation pairs in the row */
+    int32_t *cd_near_idx;     /* [E][N] argmin_j tCPA over the row's conflict pairs, -1 if none */
+    void *cd_near_tcpa, *cd_near_dcpa, *cd_near_tin;   /* real [E][N] */
+    void *cd_tcpamax;         /* real [E][N] */
+} bsg_step_out;
+
+/* stand-alone all-pairs CD sweep (giant-airspace config; pair matrix rows [row0,row1) of every env) */
+typedef struct bsg_cd_params {
+    int32_t num_envs, num_ac, row0, row1;
+    float rpz_m, hpz_m, dtlookahead;
+    int32_t reserved;
+} bsg_cd_params;
+
+typedef struct bsg_ndmap_params {
+    int32_t num_envs, num_ac, nx, ny, nz, nt;
+    float x0, y0, z0, cell_x, cell_y, cell_z, dt;
+    int32_t reserved;
+} bsg_ndmap_params;
+
+int bsg_abi_version(void);
+const char *bsg_status_string(int status);
+int bsg_device_count(int *count);
+
+int bsg_create(const bsg_config *cfg, bsg_handle **out);
+int bsg_destroy(bsg_handle *h);
+const char *bsg_last_error(const bsg_handle *h);
+int bsg_obs_dim(const bsg_handle *h);
+int bsg_act_dim(const bsg_handle *h);
+int bsg_launch_count(const bsg_handle *h, int64_t *kernels_launched);
+
+/* fp64 interchange with the host (parity tests, checkpoint/resume). NULL pointers are skipped. Synchronous. */
+int bsg_set_state(bsg_handle *h, const double *ac_host, const uint64_t *reso_host, const int32_t *nac_host,
+                  const double *ev_host);
+int bsg_get_state(bsg_handle *h, double *ac_host, uint64_t *reso_host, int32_t *nac_host, double *ev_host);
+
+/* device-side scenario generation (reset path of the env layer) for envs with mask_dev[e] != 0 (NULL = all) */
+int bsg_reset(bsg_handle *h, const int32_t *mask_dev, uint64_t seed, void *stream);
+/* observation of the current state (what reset() returns) */
+int bsg_observe(bsg_handle *h, void *obs_dev, void *stream);
+/* one env step for every env: action intake -> substeps x (autopilot, CD, MVP, limits, kinematics) -> obs/reward */
+int bsg_step(bsg_handle *h, const void *actions_dev /* real [E][act_dim] */, const bsg_step_out *out, void *stream);
+/* same through host buffers (pinned staging, copies inside): the end-to-end call of the plugin boundary */
+int bsg_step_host(bsg_handle *h, const void *actions_host, void *obs_host, void *reward_host,
+                  int32_t *terminated_host, int32_t *truncated_host, void *info_host);
+
+/* pack fp32 CD records (8 floats per aircraft) from SoA device arrays [E][N]; origin = (lat0, lon0) degrees */
+int bsg_cd_pack(int32_t num_envs, int32_t num_ac, const double *lat_dev, const double *lon_dev,
+                const float *alt_dev, const float *trk_dev, const float *gs_dev, const float *vs_dev,
+                double lat0, double lon0, float *rec_dev /* [E][N][8] */, void *stream);
+int bsg_cd_sweep(const bsg_cd_params *p, const float *rec_dev, uint8_t *inconf_dev, int32_t *nconf_dev,
+                 int32_t *nlos_dev, int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev,
+                 float *near_tin_dev, float *tcpamax_dev, void *stream);
+
+/* ND-map: rec_dev float [E][6][n] (x, y, z, u, v, w); occ/conf uint8 [E][nt][nz][ny][nx]; ncell int32 [E][nt] */
+int bsg_ndmap(const bsg_ndmap_params *p, const float *rec_dev, uint8_t *occ_dev, uint8_t *conf_dev,
+              int32_t *ncell_dev, void *stream);
+
+/* FMA-chain micro-benchmarks: the measured FP32 / FP64 (non-tensor) roofline denominators */
+int bsg_peak_fp32(int device, int iters, double *tflops, double *ms);
+int bsg_peak_fp64(int device, int iters, double *tflops, double *ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

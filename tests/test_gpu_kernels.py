@@ -1,0 +1,90 @@
+"""GPU tests of the stand-alone kernels behind the C-ABI: tiled CD sweep (giant airspace), ND-map,
+FMA peak probes.  Checker: the CPU oracle (oracle/)."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+EPS32 = 2e-4
+
+
+def _pack(lat, lon, alt, trk, gs, vs):
+    from bluesky_gym_hallucination_b200 import core
+    dev = torch.device('cuda', 0)
+    t64 = lambda a: torch.as_tensor(a, dtype=torch.float64, device=dev)
+    t32 = lambda a: torch.as_tensor(a, dtype=torch.float32, device=dev)
+    return core.cd_pack(t64(lat), t64(lon), t32(alt), t32(trk), t32(gs), t32(vs), 52.0, 4.0)
+
+
+@pytest.mark.parametrize('E,N,box', [(3, 1500, 200.0), (2, 1031, 120.0), (1, 37, 60.0)])
+def test_cd_sweep_vs_oracle(orc, E, N, box):
+    """Row outputs of the TMA-tiled sweep == oracle rows; every mismatching row is explained by a pair the
+    oracle places within EPS32 of a zone threshold (those pairs are enumerated)."""
+    from bluesky_gym_hallucination_b200 import core, scenario as sc
+    lat, lon, alt, trk, gs, vs = sc.raw_traffic(E, N, seed=2, box_nm=box)
+    ref = orc.cd_rows(lat, lon, alt, trk, gs, vs, nthreads=8)
+    out = core.cd_sweep(_pack(lat, lon, alt, trk, gs, vs))
+    torch.cuda.synchronize()
+    got = {k: v.cpu().numpy() for k, v in out.items()}
+    assert ref['nconf'].sum() > 0
+    near_rows = 0
+    for e in range(E):
+        d = orc.detect_dense(lat[e], lon[e], alt[e], trk[e], gs[e], vs[e])
+        off = ~np.eye(N, dtype=bool)
+        near_c = ((d['margin_conf'] < EPS32) & off).any(1)
+        near_l = ((d['margin_los'] < EPS32) & off).any(1)
+        bad_c = got['nconf'][e] != ref['nconf'][e]
+        bad_l = got['nlos'][e] != ref['nlos'][e]
+        assert not (bad_c & ~near_c).any(), f"conflict-count mismatch off-threshold, env {e}: rows {np.where(bad_c & ~near_c)[0][:8]}"
+        assert not (bad_l & ~near_l).any(), f"LoS-count mismatch off-threshold, env {e}"
+        near_rows += int(near_c.sum() + near_l.sum())
+        ok = ~bad_c & ~near_c
+        assert np.array_equal(got['inconf'][e][ok], ref['inconf'][e][ok])
+        same = ok & (got['near_idx'][e] == ref['near_idx'][e]) & (ref['near_idx'][e] >= 0)
+        assert same.sum() >= 0.98 * (ok & (ref['near_idx'][e] >= 0)).sum()
+        for k, tol in (('near_tcpa', 1e-5), ('near_tin', 2e-5), ('tcpamax', 1e-5)):
+            err = np.abs(got[k][e][same] - ref[k][e][same]) / np.maximum(np.abs(ref[k][e][same]), 1.0)
+            assert err.max(initial=0) < tol * 10, (k, err.max())
+        err = np.abs(got['near_dcpa'][e][same] - ref['near_dcpa'][e][same]) / np.maximum(ref['near_dcpa'][e][same], 100.0)
+        assert err.max(initial=0) < 1e-4
+    print(f"near-threshold rows enumerated: {near_rows}")
+
+
+def test_cd_sweep_row_block_equals_full():
+    """Row-block partition of the pair matrix (the multi-GPU sharding) == the full sweep, bitwise."""
+    from bluesky_gym_hallucination_b200 import core, scenario as sc
+    lat, lon, alt, trk, gs, vs = sc.raw_traffic(2, 1200, seed=4)
+    rec = _pack(lat, lon, alt, trk, gs, vs)
+    full = core.cd_sweep(rec)
+    parts = core.cd_sweep(rec, 0, 500)
+    parts = core.cd_sweep(rec, 500, 1200, out=parts)
+    torch.cuda.synchronize()
+    for k in full:
+        assert torch.equal(full[k], parts[k]), k
+
+
+@pytest.mark.parametrize('E,n', [(3, 500), (1, 7)])
+def test_ndmap_bit_exact(orc, E, n):
+    from bluesky_gym_hallucination_b200 import core
+    rng = np.random.default_rng(9)
+    rec = np.zeros((E, 6, n), np.float32)
+    rec[:, 0] = rng.uniform(-5000, 300000, (E, n)); rec[:, 1] = rng.uniform(-5000, 300000, (E, n))
+    rec[:, 2] = rng.uniform(2000, 13000, (E, n))
+    rec[:, 3] = rng.uniform(-250, 250, (E, n)); rec[:, 4] = rng.uniform(-250, 250, (E, n))
+    rec[:, 5] = rng.choice([-10.0, 0.0, 10.0], (E, n))
+    kw = dict(nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=3048.0, cx=4630.0, cy=4630.0, cz=304.8 * 4, dt=10.0)
+    occ, conf, ncell = orc.ndmap(rec, nthreads=8, **kw)
+    g_occ, g_conf, g_ncell = core.ndmap(torch.as_tensor(rec, device='cuda'), **kw)
+    torch.cuda.synchronize()
+    assert occ.sum() > 0
+    assert np.array_equal(g_occ.cpu().numpy(), occ)
+    assert np.array_equal(g_conf.cpu().numpy(), conf)
+    assert np.array_equal(g_ncell.cpu().numpy(), ncell)
+
+
+def test_fma_peaks_are_sane():
+    from bluesky_gym_hallucination_b200 import core
+    tf32, _ = core.peak_fp32(0, 2048)
+    tf64, _ = core.peak_fp64(0, 1024)
+    assert 20.0 < tf32 < 90.0, tf32      # B200: 148 SM x 128 lanes x 2 x clock
+    assert 5.0 < tf64 < 50.0, tf64

@@ -1,0 +1,167 @@
+"""GPU parity tests (run on the B200 box: pytest -m gpu).  Everything goes through the C-ABI
+(libbsgcore.so via ctypes); the checker is the CPU oracle (oracle/) and the golden fixtures recorded
+from the unmodified reference env classes (tests/golden).
+
+Tolerances (BASELINE.json north_star):
+  fp64 parity mode : obs / tCPA / dCPA / state floats  |d| <= 1e-12 * max(|ref|, 1)   (RT64)
+  fp32 fast mode   : same quantities                    |d| <= 1e-5  * max(|ref|, 1)   (RT32)
+  conflict / LoS flags, intruder indices, LoS counts: bit-exact, except pairs whose oracle margin to a
+  zone threshold is below EPS32 (fp32) -- those are enumerated and must explain every mismatch.
+"""
+import numpy as np
+import pytest
+import torch
+from conftest import load_golden
+
+pytestmark = pytest.mark.gpu
+RT64, RT32, EPS32 = 1e-12, 1e-5, 2e-4
+KIND = {'H': 0, 'V': 1, 'S': 2}
+
+
+def relerr(a, b, floor=1.0):
+    a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
+    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor))) if a.size else 0.0
+
+
+def make_core(kind, E, N, precision, asas=0, **kw):
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    return BsgCore(kind, E, N, precision=precision, asas_on=bool(asas), reso_on=bool(asas) and N <= 64 and kw.pop('reso', True),
+                   reso_off_own=bool(asas), cd_outputs=True, **kw)
+
+
+def run_step(core, ac, reso, nac, ev, act):
+    core.set_state(ac, reso, nac, ev)
+    a = torch.as_tensor(np.ascontiguousarray(act), dtype=core.rdtype, device=core.device)
+    core.step(a)
+    torch.cuda.synchronize()
+    ac1, reso1, _, ev1 = core.get_state()
+    cd = {k: v.cpu().numpy() for k, v in core.cd.items()}
+    return (core.obs.cpu().numpy(), core.reward.cpu().numpy(), core.terminated.cpu().numpy(),
+            core.truncated.cpu().numpy(), core.info.cpu().numpy(), ac1, reso1, ev1, cd)
+
+
+STATE_FIELDS = ['lat', 'lon', 'alt', 'hdg', 'tas', 'vs', 'selspd', 'selalt', 'selvs', 'aptrk', 'ax', 'asas_trk',
+                'asas_tas', 'asas_vs', 'asas_alt', 'asas_active', 'phase']
+
+
+@pytest.mark.parametrize('name', ['H', 'V', 'S', 'H_asas', 'S_asas'])
+def test_fp64_replays_reference_goldens(orc, name):
+    """fp64 parity mode vs the steps recorded from the unmodified reference classes."""
+    g = load_golden(name)
+    kind, asas = name[0], int('asas' in name)
+    T, _, n = g['ac0'].shape
+    na = 2 if kind == 'S' else 1
+    core = make_core(KIND[kind], T, n, 'fp64', asas)
+    nac = g['nac'].astype(np.int32)
+    core.set_state(g['ac0'], g['reso0'], nac, g['ev0'])
+    assert relerr(core.observe().cpu().numpy(), g['obs0']) < RT64 * 10
+    obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(core, g['ac0'], g['reso0'], nac, g['ev0'], g['act'][:, :na])
+    live = g['term'] == 0
+    assert relerr(obs, g['obs1']) < RT64 * 200, relerr(obs, g['obs1'])     # K substeps of accumulated libm differences
+    assert relerr(rew, g['rew']) < RT64 * 200
+    assert np.array_equal(term, g['term']) and np.array_equal(trunc, g['trunc'])
+    F = orc.F
+    idx = [F[k] for k in STATE_FIELDS]
+    assert relerr(ac1[live][:, idx], g['ac1'][live][:, idx]) < RT64 * 200
+    assert np.array_equal(reso1[live], g['reso1'][live])
+    assert relerr(info[:, 0], g['info'][:, 0]) < RT64 * 200 and np.array_equal(info[:, 1], g['info'][:, 1])
+    core.close()
+
+
+@pytest.mark.parametrize('name', ['H', 'V', 'S', 'H_asas', 'S_asas'])
+def test_fp32_replays_reference_goldens(orc, name):
+    """fp32 fast mode, one step from every recorded pre-state: floats to 1e-5, flags exact off-threshold."""
+    g = load_golden(name)
+    kind, asas = name[0], int('asas' in name)
+    T, _, n = g['ac0'].shape
+    na = 2 if kind == 'S' else 1
+    core = make_core(KIND[kind], T, n, 'fp32', asas)
+    nac = g['nac'].astype(np.int32)
+    obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(core, g['ac0'], g['reso0'], nac, g['ev0'], g['act'][:, :na])
+    bad_obs = np.abs(obs - g['obs1']) > RT32 * np.maximum(np.abs(g['obs1']), 1.0)
+    # an intrusion / waypoint / polygon threshold crossed within fp32 rounding changes reward and flags
+    flip = (term != g['term']) | (trunc != g['trunc']) | (np.abs(rew - g['rew']) > 0.5)
+    assert flip.sum() <= max(2, T // 50), f"{flip.sum()} threshold flips in {T} steps"
+    assert bad_obs[~flip].sum() == 0, (np.argwhere(bad_obs)[:5], relerr(obs[~flip], g['obs1'][~flip]))
+    assert relerr(rew[~flip], g['rew'][~flip]) < 5e-5
+    live = (g['term'] == 0) & ~flip
+    F = orc.F
+    for k in ['lat', 'lon', 'alt', 'tas', 'vs']:
+        assert relerr(ac1[live][:, F[k]], g['ac1'][live][:, F[k]]) < RT32, k
+    dh = (ac1[live][:, F['hdg']] - g['ac1'][live][:, F['hdg']] + 180) % 360 - 180
+    assert np.max(np.abs(dh)) < 360 * RT32
+    core.close()
+
+
+@pytest.mark.parametrize('kind,N,asas', [(0, 20, 1), (2, 50, 1), (1, 6, 0)])
+def test_batched_step_vs_oracle(orc, kind, N, asas):
+    """Seeded synthetic batch (BASELINE configs' shapes, fewer envs): 3 chained steps fp64 == oracle,
+    one step fp32 within tolerance with every CD-flag mismatch explained by a near-threshold pair."""
+    from bluesky_gym_hallucination_b200 import scenario as sc
+    E = 512
+    gen = {0: sc.horizontal, 1: sc.vertical, 2: sc.sector}[kind]
+    ac, reso, nac, ev = gen(E, N, seed=7)
+    cfg = orc.make_cfg(kind, N, asas_on=asas, reso_on=asas, reso_off_own=asas)
+    rng = np.random.default_rng(3)
+    na = 2 if kind == 2 else 1
+    c64 = make_core(kind, E, N, 'fp64', asas)
+    c32 = make_core(kind, E, N, 'fp32', asas)
+    o_ac, o_reso, o_ev = ac.copy(), reso.copy(), ev.copy()
+    c64.set_state(ac, reso, nac, ev)
+    for s in range(3):
+        act = rng.uniform(-1, 1, (E, na))
+        pre = (o_ac.copy(), o_reso.copy(), o_ev.copy())
+        o_obs, o_rew, o_term, o_trunc, o_cd = orc.step(cfg, o_ac, o_reso, nac, o_ev, act, nthreads=8)
+        a = torch.as_tensor(act, dtype=torch.float64, device=c64.device)
+        c64.step(a)
+        torch.cuda.synchronize()
+        assert relerr(c64.obs.cpu().numpy(), o_obs) < RT64 * 1000
+        assert relerr(c64.reward.cpu().numpy(), o_rew) < RT64 * 1000
+        assert np.array_equal(c64.terminated.cpu().numpy(), o_term) and np.array_equal(c64.truncated.cpu().numpy(), o_trunc)
+        if asas:
+            assert np.array_equal(c64.cd['nconf'].cpu().numpy(), o_cd['nconf'])
+            assert np.array_equal(c64.cd['nlos'].cpu().numpy(), o_cd['nlos'])
+            assert np.array_equal(c64.cd['near_idx'].cpu().numpy(), o_cd['near_idx'])
+            assert relerr(c64.cd['near_tcpa'].cpu().numpy(), o_cd['near_tcpa']) < RT64 * 1000
+            assert relerr(c64.cd['near_dcpa'].cpu().numpy(), o_cd['near_dcpa']) < 1e-9
+        # fp32: one step from the oracle's pre-state
+        obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(c32, pre[0], pre[1], nac, pre[2], act)
+        flip = (term != o_term) | (trunc != o_trunc) | (np.abs(rew - o_rew) > 0.5)
+        assert flip.sum() <= max(2, E // 100)
+        assert relerr(obs[~flip], o_obs[~flip]) < RT32 * 2, relerr(obs[~flip], o_obs[~flip])
+        if asas:
+            mism = (cd['nconf'] != o_cd['nconf']) | (cd['nlos'] != o_cd['nlos'])
+            assert mism.mean() < 5e-3, f"{mism.sum()} CD row mismatches of {mism.size}"
+    c64.close(); c32.close()
+
+
+def test_batch_invariance():
+    """Env i inside a batch == env i alone (no cross-env term anywhere)."""
+    from bluesky_gym_hallucination_b200 import scenario as sc
+    E, N = 300, 20
+    ac, reso, nac, ev = sc.horizontal(E, N, seed=11)
+    act = np.random.default_rng(0).uniform(-1, 1, (E, 1))
+    big = make_core(0, E, N, 'fp32', 1)
+    obs = run_step(big, ac, reso, nac, ev, act)[0]
+    for i in (0, 17, 299):
+        one = make_core(0, 1, N, 'fp32', 1)
+        o1 = run_step(one, ac[i:i + 1], reso[i:i + 1], nac[i:i + 1], ev[i:i + 1], act[i:i + 1])[0]
+        assert np.array_equal(o1[0], obs[i])
+        one.close()
+    big.close()
+
+
+def test_step_host_equals_step():
+    from bluesky_gym_hallucination_b200 import scenario as sc
+    E, N = 256, 20
+    ac, reso, nac, ev = sc.horizontal(E, N, seed=5)
+    act = np.random.default_rng(1).uniform(-1, 1, (E, 1)).astype(np.float32)
+    c = make_core(0, E, N, 'fp32', 1)
+    ref = run_step(c, ac, reso, nac, ev, act)
+    c.set_state(ac, reso, nac, ev)
+    obs = np.zeros((E, c.obs_dim), np.float32); rew = np.zeros(E, np.float32)
+    term = np.zeros(E, np.int32); trunc = np.zeros(E, np.int32); info = np.zeros((E, 4), np.float32)
+    c.step_host(act, obs, rew, term, trunc, info)
+    assert np.array_equal(obs, ref[0]) and np.array_equal(rew, ref[1]) and np.array_equal(term, ref[2])
+    assert c.launch_count() > 0
+    c.close()
