@@ -19,6 +19,7 @@ struct bsg_handle {
     void *h_act = nullptr, *h_out = nullptr, *d_act = nullptr, *d_out = nullptr;
     size_t out_bytes = 0, act_bytes = 0;
     cudaStream_t hs = nullptr;
+    uint32_t *episode = nullptr;      // [E] reset counter (Philox counter word)
     int64_t launches = 0;
     std::string err;
 };

@@ -78,7 +78,11 @@ def test_fp32_replays_reference_goldens(orc, name):
     core = make_core(KIND[kind], T, n, 'fp32', asas)
     nac = g['nac'].astype(np.int32)
     obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(core, g['ac0'], g['reso0'], nac, g['ev0'], g['act'][:, :na])
-    bad_obs = np.abs(obs - g['obs1']) > RT32 * np.maximum(np.abs(g['obs1']), 1.0)
+    tol = RT32 * np.maximum(np.abs(g['obs1']), 1.0)
+    if kind == 'S':   # cos/sin(track) = direction of a velocity DIFFERENCE: condition number ~ 150 / |v_rel|
+        vrel = np.hypot(g['obs1'][:, 11:15] * 32, g['obs1'][:, 15:19] * 66)
+        tol[:, 19:23] *= np.maximum(1.0, 600.0 / vrel); tol[:, 23:27] *= np.maximum(1.0, 600.0 / vrel)
+    bad_obs = np.abs(obs - g['obs1']) > tol
     # an intrusion / waypoint / polygon threshold crossed within fp32 rounding changes reward and flags
     flip = (term != g['term']) | (trunc != g['trunc']) | (np.abs(rew - g['rew']) > 0.5)
     assert flip.sum() <= max(2, T // 50), f"{flip.sum()} threshold flips in {T} steps"
