@@ -1,0 +1,287 @@
+#!/usr/bin/env python
+"""bench.py -- BASELINE.json metric: env-steps/sec (and CPA pair-evals/sec) of the batched BlueSky-Gym core.
+
+  python bench.py --gpus N --steps K --warmup W                (our arm; torchrun launches N ranks for N > 1)
+  python bench.py --impl reference --gpus N --steps K --warmup W   (the reference's numpy/BlueSky CPU path)
+
+Workload at N = 1 (config.workload "c2"): BASELINE.json configs[1] -- HorizontalCREnv-v0, 4096 envs x 20
+aircraft, state-based CD every substep + CPA obs, fp32 fast path, next-step auto-reset on the device.
+A "step" = one fused bsg_step (+ the masked bsg_reset) over the whole batch = 4096 env-steps.
+For N > 1 the envs shard across ranks with no data-path collective (weak scaling: 4096 envs per GPU).
+Other workloads (--workload c3|c4|c5) time the other BASELINE configs; they are not the driver's line.
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every field.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+FLOP_PER_PAIR = 74.0          # algorithmic FP32 flop per ordered CD pair
+WORKLOADS = {
+    # name: (kind, envs per GPU, aircraft, asas, reso, description)
+    'c2': (0, 4096, 20, 1, 0, "HorizontalCREnv-v0 4096 envs x 20 aircraft, state-based CD + CPA obs"),
+    'c3': (2, 65536, 50, 1, 1, "SectorCREnv-v0 65536 envs x 50 aircraft, CD + MVP (intruders) + reward"),
+}
+SUBSTEPS = {0: 10, 1: 30, 2: 5}
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows, self.proc, self.idx = [], None, gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(['nvidia-smi', f'--query-gpu={self.Q}', '--format=csv,noheader,nounits',
+                                          '-i', str(self.idx), '-lms', '100'], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        names = ['hw_slowdown', 'hw_thermal_slowdown', 'sw_thermal_slowdown', 'sw_power_cap']
+        for r in self.rows:
+            p = [x.strip() for x in r.split(',')]
+            if len(p) < 9:
+                continue
+            try:
+                sm.append(float(p[1])); mx.append(float(p[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, p[5:9]):
+                if v.lower().startswith('active'):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_baselines(n_ac, asas, budget_s=12.0):
+    """Rank 0, N = 1 only: the oracle timed on the host cores on a bounded sample of the same workload."""
+    import numpy as np
+    from oracle import oracle as orc, envs_np
+    from bluesky_gym_hallucination_b200 import scenario
+    cores = len(os.sched_getaffinity(0))
+    # (a) reference-style path: numpy BlueSky stand-in + Python env loops, one simulator per process
+    per_proc = 24
+    v_np, total_np, wall_np = envs_np.timed_sample(n_ac - 1, bool(asas), per_proc, cores)
+    # (b) plain-C fp64 port, OpenMP over envs
+    E = 256
+    ac, reso, nac, ev = scenario.horizontal(E, n_ac, seed=99)
+    cfg = orc.make_cfg(orc.KIND_H, n_ac, asas_on=asas)
+    act = np.random.default_rng(0).uniform(-1, 1, (E, 1))
+    orc.step(cfg, ac, reso, nac, ev, act, nthreads=cores)
+    t0 = time.perf_counter(); n = 0
+    while time.perf_counter() - t0 < budget_s / 3:
+        orc.step(cfg, ac, reso, nac, ev, act, nthreads=cores); n += E
+    v_c = n / (time.perf_counter() - t0)
+    return ({"value": v_np, "unit": "env-steps/s", "cores": cores, "kind": "port",
+             "sample": f"{cores} processes x {per_proc} env-steps of HorizontalCREnv with {n_ac} aircraft, "
+                       f"ASAS {'ON' if asas else 'OFF'}; numpy BlueSky stand-in (oracle/refshim) + Python env port "
+                       f"(oracle/envs_np.py), the reference's SubprocVecEnv style"},
+            {"value": v_c, "unit": "env-steps/s", "cores": cores, "kind": "port",
+             "sample": f"plain-C fp64 port (oracle/c), OpenMP over {E} envs x {n_ac} aircraft, {n} env-steps"})
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path = numpy BlueSky-style simulator +
+    per-step Python env loops, one simulator singleton per process, all host cores (the reference's own
+    scaling method, scripts/multi_processing_example.py:51-53).  /root/reference is Python and cannot travel
+    to the GPU box, so this times the oracle port of it (oracle/refshim + oracle/envs_np.py)."""
+    rank = env_int('RANK', 0)
+    if rank != 0:
+        return
+    from oracle import envs_np
+    kind, E, N, asas, reso, desc = WORKLOADS[args.workload]
+    cores = len(os.sched_getaffinity(0))
+    per_proc = 8                                  # env-steps per process per bench "step" (bounded sample)
+    steps = min(args.steps, 12); warm = min(args.warmup, 2)
+    for _ in range(warm):
+        envs_np.timed_sample(N - 1, bool(asas), per_proc, cores)
+    tot, busy = 0, 0.0
+    for k in range(steps):
+        v, n, wall = envs_np.timed_sample(N - 1, bool(asas), per_proc, cores, seed=1000 * k)
+        tot += n; busy += n / v
+    value = tot / busy
+    pairs = value * SUBSTEPS[kind] * N * (N - 1)
+    line = {"impl": "reference", "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": args.gpus,
+            "steps": steps, "warmup": warm, "ms_per_step": 1e3 * busy / steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+            "config": {"workload": args.workload, "description": desc, "envs_per_step": cores * per_proc,
+                       "aircraft": N, "asas": bool(asas)},
+            "pair_evals_per_sec": pairs,
+            "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": "port",
+                             "sample": f"{cores} processes x {per_proc} env-steps per bench step, numpy BlueSky "
+                                       f"stand-in + Python env port (oracle/refshim, oracle/envs_np.py)"},
+            "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from bluesky_gym_hallucination_b200 import core as bc, _lib as L
+    rank, world, local = env_int('RANK', 0), env_int('WORLD_SIZE', 1), env_int('LOCAL_RANK', 0)
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    kind, E, N, asas, reso, desc = WORKLOADS[args.workload]
+    if args.envs:
+        E = args.envs
+    K, W = args.steps, max(args.warmup, 3)
+    c = bc.BsgCore(kind, E, N, precision='fp32', device=local, asas_on=bool(asas), reso_on=bool(reso),
+                   reso_off_own=True, max_episode_steps={0: 300, 1: 300, 2: 200}[kind], cd_outputs=True)
+    c.reset(seed=1234 + rank)
+    c.set_autoreset(True, seed=99 + rank)
+    gen = torch.Generator(device=dev); gen.manual_seed(7 + rank)
+    acts = [torch.rand((E, c.act_dim), device=dev, generator=gen) * 2 - 1 for _ in range(16)]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)       # > 126 MB L2
+    peak32, _ = bc.peak_fp32(local, 4096)
+    for w in range(W):
+        c.step(acts[w % 16])
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    lib, h, out, stream = c.lib, c.h, c._out, c._stream()
+    import ctypes as C
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    l0 = c.launch_count()
+    t_wall0 = time.perf_counter()
+    for k in range(K):
+        flush.zero_()                                   # L2 flush between timed iterations (not timed)
+        ev[k][0].record()
+        c.step(acts[k % 16])                            # step kernel + masked reset kernel (auto-reset)
+        ev[k][1].record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t_wall = time.perf_counter() - t_wall0
+    launches = c.launch_count() - l0
+    dev_ms = sum(ev[k][0].elapsed_time(ev[k][1]) for k in range(K))
+    # the dominant kernel alone (same stream, CUDA events): step kernel without the reset launch
+    c.set_autoreset(False)
+    kms = []
+    for k in range(min(K, 200)):
+        flush.zero_()
+        ev[k][0].record(); c.step(acts[k % 16]); ev[k][2].record()
+    torch.cuda.synchronize()
+    kms = [ev[k][0].elapsed_time(ev[k][2]) for k in range(min(K, 200))]
+    kernel_ms = float(np.mean(kms))
+    c.set_autoreset(True, seed=99 + rank)
+    clocks = sampler.stop() if rank == 0 else None
+    tmax = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    dev_ms_max = float(tmax.item())
+    # ---------------------------------------------------------------- end-to-end through host buffers
+    Ke = min(K, 300)
+    a_host = [a.cpu().numpy().copy() for a in acts]
+    obs = np.zeros((E, c.obs_dim), np.float32); rew = np.zeros(E, np.float32)
+    term = np.zeros(E, np.int32); trunc = np.zeros(E, np.int32); info = np.zeros((E, 4), np.float32)
+    for k in range(3):
+        c.step_host(a_host[k], obs, rew, term, trunc, info)
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    for k in range(Ke):
+        c.step_host(a_host[k % 16], obs, rew, term, trunc, info)
+    t_e2e = time.perf_counter() - t0
+    te = torch.tensor([t_e2e], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_value = world * E * Ke / float(te.item())
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    sub = SUBSTEPS[kind]
+    pairs_per_launch = float(E) * sub * N * (N - 1)
+    value = world * E * K / (dev_ms_max * 1e-3)
+    achieved = FLOP_PER_PAIR * pairs_per_launch / (kernel_ms * 1e-3) / 1e12
+    bytes_per_envstep = 128.0 * N + 4 * c.obs_dim + 4 * c.act_dim + 20
+    line = {
+        "metric": "env-steps/sec", "value": value, "unit": "env-steps/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": dev_ms_max / K, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload, "description": desc, "envs_per_gpu": E, "aircraft": N,
+                   "substeps": sub, "asas": bool(asas), "mvp": bool(reso), "autoreset": "next-step, on device",
+                   "l2": "256 MB buffer zeroed between timed iterations (L2 flush)", "sharding": "envs, no collective"},
+        "pair_evals_per_sec": world * pairs_per_launch * K / (dev_ms_max * 1e-3),
+        "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak32, "unit": "TFLOP/s", "frac": achieved / peak32,
+                     "traffic": None, "kernel": "bsg::step_kernel<float>", "kernel_ms": kernel_ms,
+                     "flop_per_pair": FLOP_PER_PAIR, "pairs_per_launch": pairs_per_launch,
+                     "peak_source": "bsg_peak_fp32 FMA chain measured in this run (burst); MEASURED_PEAKS.json holds no FP32 figure",
+                     "hbm_achieved_gbs": bytes_per_envstep * E / (kernel_ms * 1e-3) / 1e9,
+                     "hbm_peak_gbs": load_peaks().get("hbm_gbs")},
+        "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(c.act_dim * E * 4),
+                "d2h_bytes_per_step": int(E * (c.obs_dim + 5) * 4 + E * 8), "steps": Ke,
+                "api": "bsg_step_host (pinned staging, H2D actions + D2H obs/reward/info/flags inside)"},
+        "gpu_launches": int(launches), "clocks": clocks, "wall_s_timed_region": t_wall,
+    }
+    if world == 1 and not args.no_cpu:
+        np_b, c_b = cpu_baselines(N, asas)
+        line["cpu_baseline"] = np_b
+        line["cpu_baseline_c_openmp"] = c_b
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def load_peaks():
+    try:
+        with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
+            return json.load(f)
+    except (OSError, ValueError):
+        return {"hbm_gbs": 6650.0, "source": "fallback"}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=2000)
+    ap.add_argument('--warmup', type=int, default=20)
+    ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
+    ap.add_argument('--envs', type=int, default=0, help='override envs per GPU')
+    ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
+    args = ap.parse_args()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == '__main__':
+    main()

@@ -31,7 +31,7 @@ class Config(C.Structure):
 class StepOut(C.Structure):
     _fields_ = [(k, C.c_void_p) for k in ('obs', 'reward', 'terminated', 'truncated', 'info', 'cd_inconf', 'cd_nconf',
                                           'cd_nlos', 'cd_near_idx', 'cd_near_tcpa', 'cd_near_dcpa', 'cd_near_tin',
-                                          'cd_tcpamax')]
+                                          'cd_tcpamax', 'done')]
 
 
 class CdParams(C.Structure):
@@ -61,6 +61,7 @@ SYMBOLS = {
     'bsg_set_state': (_I, [_VP, _VP, _VP, _VP, _VP]),
     'bsg_get_state': (_I, [_VP, _VP, _VP, _VP, _VP]),
     'bsg_reset': (_I, [_VP, _VP, C.c_uint64, _VP]),
+    'bsg_set_autoreset': (_I, [_VP, C.c_int32, C.c_uint64]),
     'bsg_observe': (_I, [_VP, _VP, _VP]),
     'bsg_step': (_I, [_VP, _VP, C.POINTER(StepOut), _VP]),
     'bsg_step_host': (_I, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),

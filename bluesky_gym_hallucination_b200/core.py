@@ -71,6 +71,7 @@ class BsgCore:
         self.terminated = torch.zeros(E, dtype=torch.int32, device=dev)
         self.truncated = torch.zeros(E, dtype=torch.int32, device=dev)
         self.info = torch.zeros((E, 4), dtype=rd, device=dev)
+        self.done = torch.zeros(E, dtype=torch.int32, device=dev)
         self.cd = None
         if cd_outputs:
             self.cd = dict(inconf=torch.zeros((E, N), dtype=torch.uint8, device=dev),
@@ -84,7 +85,7 @@ class BsgCore:
         cdp = [(_ptr(self.cd[k]) if self.cd else None) for k in ('inconf', 'nconf', 'nlos', 'near_idx', 'near_tcpa',
                                                                    'near_dcpa', 'near_tin', 'tcpamax')]
         self._out = L.StepOut(_ptr(self.obs) if self.obs_dim else None, _ptr(self.reward), _ptr(self.terminated),
-                              _ptr(self.truncated), _ptr(self.info), *cdp)
+                              _ptr(self.truncated), _ptr(self.info), *cdp, _ptr(self.done))
 
     def close(self):
         if getattr(self, 'h', None):
@@ -133,6 +134,9 @@ class BsgCore:
 
     def reset(self, mask=None, seed=0):
         L.check(self.lib.bsg_reset(self.h, _ptr(mask), C.c_uint64(seed), self._stream()), self.h)
+
+    def set_autoreset(self, enable=True, seed=0):
+        L.check(self.lib.bsg_set_autoreset(self.h, int(enable), C.c_uint64(seed)), self.h)
 
     def step_host(self, actions, obs, reward, terminated, truncated, info):
         """End-to-end call with HOST numpy buffers (H2D + kernel + D2H inside)."""

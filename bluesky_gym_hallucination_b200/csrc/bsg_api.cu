@@ -140,7 +140,7 @@ int bsg_destroy(bsg_handle *h) {
     if (!h) return BSG_ERR_ARG;
     cudaSetDevice(h->cfg.device);
     cudaFree(h->pos); cudaFree(h->st); cudaFree(h->reso); cudaFree(h->nac); cudaFree(h->ev); cudaFree(h->stage64);
-    cudaFree(h->d_act); cudaFree(h->d_out); cudaFree(h->episode);
+    cudaFree(h->d_act); cudaFree(h->d_out); cudaFree(h->episode); cudaFree(h->done_buf[0]); cudaFree(h->done_buf[1]);
     if (h->h_act) cudaFreeHost(h->h_act);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->hs) cudaStreamDestroy(h->hs);

@@ -13,14 +13,38 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     A.pos = h->pos; A.st = (R *)h->st; A.reso = h->reso; A.nac = h->nac; A.ev = h->ev;
     A.actions = (const R *)actions;
     if (out) A.out = *out; else memset(&A.out, 0, sizeof(A.out));
+    const bool ar = h->autoreset && !observe_only && g.env_kind != BSG_KIND_RAW;
+    A.skip = ar ? h->done_buf[h->flip] : nullptr;
+    int32_t *done_now = nullptr;
+    if (ar) { done_now = h->done_buf[h->flip ^ 1]; if (!A.out.done) A.out.done = done_now; }
     const int grid = (g.num_envs + h->epb - 1) / h->epb;
     step_kernel<R><<<grid, h->tpb, h->smem, s>>>(A);
     h->launches++;
     CK(h, cudaGetLastError());
+    if (ar) {
+        if (A.out.done != done_now)
+            CK(h, cudaMemcpyAsync(done_now, A.out.done, g.num_envs * sizeof(int32_t), cudaMemcpyDeviceToDevice, s));
+        h->flip ^= 1;
+        int rc = bsg_reset(h, done_now, h->ar_seed, (void *)s);
+        if (rc != BSG_OK) return rc;
+    }
     return BSG_OK;
 }
 
 extern "C" {
+
+int bsg_set_autoreset(bsg_handle *h, int32_t enable, uint64_t seed) {
+    if (!h) return BSG_ERR_ARG;
+    CK(h, cudaSetDevice(h->cfg.device));
+    for (int b = 0; b < 2; b++) {
+        if (!h->done_buf[b]) CK(h, cudaMalloc(&h->done_buf[b], h->cfg.num_envs * sizeof(int32_t)));
+        CK(h, cudaMemset(h->done_buf[b], 0, h->cfg.num_envs * sizeof(int32_t)));
+    }
+    h->autoreset = enable ? 1 : 0;
+    h->ar_seed = seed;
+    h->flip = 0;
+    return BSG_OK;
+}
 
 int bsg_set_state(bsg_handle *h, const double *ac, const uint64_t *reso, const int32_t *nac, const double *ev) {
     if (!h) return BSG_ERR_ARG;

@@ -11,7 +11,7 @@ namespace bsg {
 
 template <typename R>
 __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &a, EnvShared<R> *es, R *sdist,
-                                          int le, int i, int e, int nl, bool valid, bool live, double *ev) {
+                                          int le, int i, int e, int nl, bool valid, bool live, bool skip, double *ev) {
     const int N = A.N, K = N - 1, kind = A.kind;
     if (kind == BSG_KIND_RAW) return;                                  // uniform: no barrier skipped
     R *obs = A.out.obs ? (R *)A.out.obs : nullptr;
@@ -126,7 +126,17 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
         }
     }
     // ------------------------------------------------------------------ reward / termination / info (agent thread)
-    if (live && i == 0 && !A.observe_only) {
+    if (live && i == 0 && skip && !A.observe_only) {                 // first observation of a fresh episode
+        if (A.out.reward) ((R *)A.out.reward)[e] = R(0);
+        if (A.out.terminated) A.out.terminated[e] = 0;
+        if (A.out.truncated) A.out.truncated[e] = 0;
+        if (A.out.done) A.out.done[e] = 0;
+        if (A.out.info) {
+            R *inf = (R *)A.out.info + (size_t)e * 4;
+            inf[0] = R(0); inf[1] = R(0); inf[2] = kind == BSG_KIND_VERTICAL ? R(0) : R(NAN); inf[3] = R(0);
+        }
+    }
+    if (live && i == 0 && !skip && !A.observe_only) {
         const int intr = es[le].intr;
         double rew = 0.0;
         int term = 0, trunc = 0;
@@ -158,6 +168,7 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
         if (A.out.reward) ((R *)A.out.reward)[e] = (R)rew;
         if (A.out.terminated) A.out.terminated[e] = term;
         if (A.out.truncated) A.out.truncated[e] = trunc;
+        if (A.out.done) A.out.done[e] = term | trunc;
         if (A.out.info) {
             R *inf = (R *)A.out.info + (size_t)e * 4;
             inf[0] = (R)ev[BSG_EV_TOTAL_REWARD]; inf[1] = (R)ev[BSG_EV_TOTAL_INTR];

@@ -19,7 +19,10 @@ struct bsg_handle {
     void *h_act = nullptr, *h_out = nullptr, *d_act = nullptr, *d_out = nullptr;
     size_t out_bytes = 0, act_bytes = 0;
     cudaStream_t hs = nullptr;
-    uint32_t *episode = nullptr;      // [E] reset counter (Philox counter word)
+    uint32_t *episode = nullptr;
+    int autoreset = 0, flip = 0;      // next-step auto-reset: done_buf[flip] = envs reset after the last step
+    uint64_t ar_seed = 0;
+    int32_t *done_buf[2] = { nullptr, nullptr };      // [E] reset counter (Philox counter word)
     int64_t launches = 0;
     std::string err;
 };

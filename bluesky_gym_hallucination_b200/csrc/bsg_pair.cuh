@@ -29,11 +29,12 @@ __device__ __forceinline__ void pair_lit(const RecLit &a, const RecLit &b, const
     double qr = qdr * kD2R;
     double dx = dist * sin(qr), dy = dist * cos(qr);
     double du = b.u - a.u, dv = b.v - a.v;
-    double dv2 = du * du + dv * dv;
+    // explicit round-to-nearest mul/add: no FMA contraction, the cancelling sums round exactly like numpy's
+    double dv2 = __dadd_rn(__dmul_rn(du, du), __dmul_rn(dv, dv));
     if (fabs(dv2) < 1e-6) dv2 = 1e-6;
     double vrel = sqrt(dv2);
-    double tcpa = -(du * dx + dv * dy) / dv2;
-    double dcpa2 = fabs(dist * dist - tcpa * tcpa * dv2);
+    double tcpa = -__dadd_rn(__dmul_rn(du, dx), __dmul_rn(dv, dy)) / dv2;
+    double dcpa2 = fabs(__dsub_rn(__dmul_rn(dist, dist), __dmul_rn(__dmul_rn(tcpa, tcpa), dv2)));
     double R2 = P.rpz * P.rpz;
     bool swhor = dcpa2 < R2;
     double dtinhor = sqrt(fmax(0.0, R2 - dcpa2)) / vrel;

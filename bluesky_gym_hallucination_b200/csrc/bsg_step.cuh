@@ -20,6 +20,7 @@ template <typename R> struct StepArgs {
     CdParams P;
     double *pos; R *st; unsigned long long *reso; const int *nac; double *ev;
     const R *actions;
+    const int *skip;      // envs reset after the previous step (auto-reset): observe only, reward 0
     bsg_step_out out;
 };
 

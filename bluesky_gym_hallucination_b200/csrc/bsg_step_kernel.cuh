@@ -27,6 +27,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
     const bool valid = le < epb && e < A.E;
     const int nl = valid ? A.nac[e] : 0;
     const bool live = valid && i < nl;
+    const bool skip = valid && A.skip && A.skip[e];                       // fresh episode: no action, no integration
     const size_t EN = (size_t)A.E * N, k = (size_t)(valid ? e : 0) * N + i;
     double *ev = A.ev + (size_t)(valid ? e : 0) * BSG_NE;
     const bool reso = A.reso_on && A.asas_on;
@@ -41,7 +42,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
     if (live && i == 0) {
         es[le].anyconf[0] = 0; es[le].anyconf[1] = 0; es[le].intr = 0;
         es[le].own_lat = a.lat; es[le].own_lon = a.lon;                    // local origin of the fp32 CD records
-        if (A.actions) {
+        if (A.actions && !skip) {
             if (A.kind == BSG_KIND_HORIZONTAL) {                           // horizontal_cr_env.py:272-275
                 a.aptrk = R(ev[BSG_EV_AC_HDG]) + A.actions[e] * R(45);
             } else if (A.kind == BSG_KIND_VERTICAL) {                      // vertical_cr_env.py:242-256
@@ -67,7 +68,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
         const int buf = s & 1;
         if (A.asas_on) {
             Rec *rb = recs + (size_t)buf * epb * N + le * N;
-            if (live) {
+            if (live && !skip) {
                 make_rec<R>(a, lat0, lon0, rb[i]);
                 if (reso) sdist[le * N + i] = a.hdg;
             }
@@ -77,7 +78,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
             R dve = R(0), dvn = R(0);
             bool touched = false, active = false;
             unsigned long long keep = 0;
-            if (live) {
+            if (live && !skip) {
                 const Rec me = rb[i];
                 for (int j = 0; j < nl; j++) {
                     const Rec o = rb[j];
@@ -116,7 +117,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
             if (reso) {
                 if (acc.nconf > 0) atomicOr(&es[le].anyconf[buf], 1);
                 __syncthreads();
-                if (live) {
+                if (live && !skip) {
                     if (es[le].anyconf[buf]) {                             // MVP.resolve ran for this env
                         R ne = a.gse + dve, nn = a.gsn + dvn;
                         double vmin, vmax;
@@ -133,13 +134,13 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
                 }
             }
         }
-        if (live) {
+        if (live && !skip) {
             const bool last = (s == A.substeps - 1);
             if constexpr (sizeof(R) == 8) kin_substep_lit(a, A.dt, reso, last);
             else kin_substep_fast(a, A.dt, reso, last && i == 0 && A.kind == BSG_KIND_SECTOR);
         }
     }
-    if (live) {
+    if (live && !skip) {
         ac_store(a, A.pos, A.st, EN, k);
         if (reso) A.reso[k] = resorow;
     }
@@ -154,7 +155,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
         if (o.cd_near_tin) ((R *)o.cd_near_tin)[k] = acc.near_tin;
         if (o.cd_tcpamax) ((R *)o.cd_tcpamax)[k] = acc.tcpamax;
     }
-    env_layer<R>(A, a, es, sdist, le, i, e, nl, valid, live, ev);
+    env_layer<R>(A, a, es, sdist, le, i, e, nl, valid, live, skip, ev);
 }
 
 }  // namespace bsg

@@ -84,6 +84,7 @@ typedef struct bsg_step_out {
     int32_t *cd_near_idx;     /* [E][N] argmin_j tCPA over the row's conflict pairs, -1 if none */
     void *cd_near_tcpa, *cd_near_dcpa, *cd_near_tin;   /* real [E][N] */
     void *cd_tcpamax;         /* real [E][N] */
+    int32_t *done;            /* [E] terminated | truncated: the mask bsg_reset takes for auto-reset */
 } bsg_step_out;
 
 /* stand-alone all-pairs CD sweep (giant-airspace config; pair matrix rows [row0,row1) of every env) */
@@ -117,6 +118,10 @@ int bsg_get_state(bsg_handle *h, double *ac_host, uint64_t *reso_host, int32_t *
 
 /* device-side scenario generation (reset path of the env layer) for envs with mask_dev[e] != 0 (NULL = all) */
 int bsg_reset(bsg_handle *h, const int32_t *mask_dev, uint64_t seed, void *stream);
+/* Gymnasium "next-step" auto-reset: when enabled, every bsg_step is followed on the same stream by a
+ * bsg_reset of the envs it reported done, and the NEXT bsg_step returns for those envs the first
+ * observation of the new episode with reward 0 / terminated 0 / truncated 0 (their action is ignored). */
+int bsg_set_autoreset(bsg_handle *h, int32_t enable, uint64_t seed);
 /* observation of the current state (what reset() returns) */
 int bsg_observe(bsg_handle *h, void *obs_dev, void *stream);
 /* one env step for every env: action intake -> substeps x (autopilot, CD, MVP, limits, kinematics) -> obs/reward */

@@ -110,7 +110,7 @@ def test_device_reset_properties(orc):
                              dtlook=1e9)
         assert d['swconfl'][0, 1:].all()
         assert np.all((d['tinconf'][0, 1:] > 95) & (d['tinconf'][0, 1:] < 1005))
-        assert np.all(np.sqrt(d['dcpa2'][0, 1:]) < 4.2 * 1852.0)
+        assert np.all(np.sqrt(d['dcpa2'][0, 1:]) < 5 * 1852.0)
     c2 = BsgCore(L.KIND_HORIZONTAL, E, N, precision='fp64')
     c2.reset(seed=77)
     assert np.array_equal(c2.get_state()[0], ac)

