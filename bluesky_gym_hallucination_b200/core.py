@@ -136,7 +136,7 @@ class BsgCore:
         L.check(self.lib.bsg_reset(self.h, _ptr(mask), C.c_uint64(seed), self._stream()), self.h)
 
     def set_autoreset(self, enable=True, seed=0):
-        L.check(self.lib.bsg_set_autoreset(self.h, int(enable), C.c_uint64(seed)), self.h)
+        L.check(self.lib.bsg_set_autoreset(self.h, int(enable), C.c_uint64(seed)), self.h)   # 0 off, 1 next-step, 2 same-step
 
     def step_host(self, actions, obs, reward, terminated, truncated, info):
         """End-to-end call with HOST numpy buffers (H2D + kernel + D2H inside)."""

@@ -101,11 +101,11 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     h->obs_dim = g.env_kind == BSG_KIND_HORIZONTAL ? 5 * K + 3 : g.env_kind == BSG_KIND_VERTICAL ? 4 + 7 * K
                  : g.env_kind == BSG_KIND_SECTOR ? 31 : 0;
     h->act_dim = g.env_kind == BSG_KIND_SECTOR ? 2 : (g.env_kind == BSG_KIND_RAW ? 0 : 1);
-    h->tpb = N <= 128 ? 256 : ((N + 31) / 32) * 32;
+    h->tpb = N <= 128 ? 128 : 256;
     h->epb = h->tpb / N;
-    const size_t rs = rsize(h), recsz = g.precision == BSG_FP64 ? sizeof(RecLit) : sizeof(RecFast);
+    const size_t rs = rsize(h), rowb = g.precision == BSG_FP64 ? rec_row_bytes<double>(N) : rec_row_bytes<float>(N);
     const size_t essz = g.precision == BSG_FP64 ? sizeof(EnvShared<double>) : sizeof(EnvShared<float>);
-    h->smem = 2 * (size_t)h->epb * N * recsz + h->epb * essz + (size_t)h->epb * N * rs;
+    h->smem = 2 * (size_t)h->epb * rowb + h->epb * essz + (size_t)h->epb * N * rs;
     CK(h, cudaSetDevice(g.device));
     const size_t EN = (size_t)E * N;
     CK(h, cudaMalloc(&h->pos, 2 * EN * sizeof(double)));
@@ -127,12 +127,7 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     CK(h, cudaMalloc(&h->d_act, h->act_bytes));
     CK(h, cudaMalloc(&h->d_out, h->out_bytes));
     CK(h, cudaStreamCreateWithFlags(&h->hs, cudaStreamNonBlocking));
-    if (h->smem > 48 * 1024) {
-        if (g.precision == BSG_FP64)
-            CK(h, cudaFuncSetAttribute(step_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem));
-        else
-            CK(h, cudaFuncSetAttribute(step_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem));
-    }
+    if (h->smem > 48 * 1024) { h->err = "shared memory per CTA above 48 KB"; return BSG_ERR_UNSUPPORTED; }
     return BSG_OK;
 }
 

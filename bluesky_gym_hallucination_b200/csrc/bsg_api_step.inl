@@ -14,11 +14,18 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     A.actions = (const R *)actions;
     if (out) A.out = *out; else memset(&A.out, 0, sizeof(A.out));
     const bool ar = h->autoreset && !observe_only && g.env_kind != BSG_KIND_RAW;
-    A.skip = ar ? h->done_buf[h->flip] : nullptr;
+    A.skip = (ar && h->autoreset == 1) ? h->done_buf[h->flip] : nullptr;
     int32_t *done_now = nullptr;
     if (ar) { done_now = h->done_buf[h->flip ^ 1]; if (!A.out.done) A.out.done = done_now; }
     const int grid = (g.num_envs + h->epb - 1) / h->epb;
-    step_kernel<R><<<grid, h->tpb, h->smem, s>>>(A);
+    const bool reso = g.reso_on && g.asas_on;
+    if (h->tpb == 128) {
+        if (reso) step_kernel<R, 128, true><<<grid, 128, h->smem, s>>>(A);
+        else step_kernel<R, 128, false><<<grid, 128, h->smem, s>>>(A);
+    } else {
+        if (reso) step_kernel<R, 256, true><<<grid, 256, h->smem, s>>>(A);
+        else step_kernel<R, 256, false><<<grid, 256, h->smem, s>>>(A);
+    }
     h->launches++;
     CK(h, cudaGetLastError());
     if (ar) {
@@ -40,7 +47,7 @@ int bsg_set_autoreset(bsg_handle *h, int32_t enable, uint64_t seed) {
         if (!h->done_buf[b]) CK(h, cudaMalloc(&h->done_buf[b], h->cfg.num_envs * sizeof(int32_t)));
         CK(h, cudaMemset(h->done_buf[b], 0, h->cfg.num_envs * sizeof(int32_t)));
     }
-    h->autoreset = enable ? 1 : 0;
+    h->autoreset = enable == 2 ? 2 : (enable ? 1 : 0);
     h->ar_seed = seed;
     h->flip = 0;
     return BSG_OK;

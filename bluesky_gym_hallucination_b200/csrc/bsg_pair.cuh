@@ -53,27 +53,32 @@ __device__ __forceinline__ void pair_lit(const RecLit &a, const RecLit &b, const
 
 struct CdParamsF { float R2, hpz, dtlook, rpz, rpz_m, hpz_m; };
 
+// MUFU approximations (1-2 ulp): the IEEE forms (__frcp_rn, sqrtf) expand to range checks + a slow-path
+// call each and break the software pipelining of the pair loop
+__device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float sqrt_approx(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
 __device__ __forceinline__ void pair_fast(const RecFast &a, const RecFast &b, const CdParamsF &P, PairOut<float> &o) {
-    float dy = b.y - a.y;
-    float cav = fmaf(a.ca, b.ca, -(a.sa * b.sa));
-    float dx = (b.x - a.x) * cav;
-    float dist2 = fmaf(dx, dx, dy * dy);
-    float du = b.u - a.u, dv = b.v - a.v;
-    float dv2 = fmaxf(fmaf(du, du, dv * dv), 1e-6f);
-    float idv2 = __frcp_rn(dv2);
-    float tcpa = -fmaf(du, dx, dv * dy) * idv2;
-    float cr = fmaf(dx, dv, -(dy * du));
-    float dcpa2 = cr * cr * idv2;
-    bool swhor = dcpa2 < P.R2;
-    float dtinhor = sqrtf(fmaxf(0.0f, P.R2 - dcpa2) * idv2);
-    float tinhor = swhor ? tcpa - dtinhor : 1e8f;
-    float touthor = swhor ? tcpa + dtinhor : -1e8f;
-    float dalt = b.alt - a.alt;
+    const float dy = b.y - a.y;
+    const float cav = fmaf(a.ca, b.ca, -(a.sa * b.sa));
+    const float dx = (b.x - a.x) * cav;
+    const float dist2 = fmaf(dx, dx, dy * dy);
+    const float du = b.u - a.u, dv = b.v - a.v;
+    const float dv2 = fmaxf(fmaf(du, du, dv * dv), 1e-6f);
+    const float idv2 = rcp_approx(dv2);
+    const float tcpa = -fmaf(du, dx, dv * dy) * idv2;
+    const float cr = fmaf(dx, dv, -(dy * du));
+    const float dcpa2 = cr * cr * idv2;
+    const bool swhor = dcpa2 < P.R2;
+    const float dtinhor = sqrt_approx(fmaxf(0.0f, P.R2 - dcpa2) * idv2);
+    const float tinhor = swhor ? tcpa - dtinhor : 1e8f;
+    const float touthor = swhor ? tcpa + dtinhor : -1e8f;
+    const float dalt = b.alt - a.alt;
     float dvs = b.vs - a.vs;
     dvs = (fabsf(dvs) < 1e-6f) ? 1e-6f : dvs;
-    float nidvs = -__frcp_rn(dvs);
-    float thi = (dalt + P.hpz) * nidvs, tlo = (dalt - P.hpz) * nidvs;
-    float tin = fmaxf(fminf(thi, tlo), tinhor), tout = fminf(fmaxf(thi, tlo), touthor);
+    const float n = -rcp_approx(dvs), hn = P.hpz * n;
+    const float thi = fmaf(dalt, n, hn), tlo = fmaf(dalt, n, -hn);
+    const float tin = fmaxf(fminf(thi, tlo), tinhor), tout = fminf(fmaxf(thi, tlo), touthor);
     o.sw = swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
     o.los = (dist2 < P.R2) && (fabsf(dalt) < P.hpz);
     o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist = dist2 /* squared */; o.dalt = dalt;
@@ -103,18 +108,22 @@ __device__ __forceinline__ void mvp_pair(R dx, R dy, R dist, R tcpa, R vrelx, R 
     }
 }
 
-// per-row running outputs of the sweep
+// per-row running outputs of the sweep (branch-free: the pair loop stays software-pipelined).
+// best = tCPA of the soonest conflict so far (+inf while there is none; ties keep the lower j).
 template <typename R> struct RowAcc {
     int nconf = 0, nlos = 0, near_idx = -1;
-    R near_tcpa = R(0), near_dcpa2 = R(0), near_tin = R(0), tcpamax = R(0);
+    R near_tcpa = R(INFINITY), near_dcpa2 = R(0), near_tin = R(0), tcpamax = R(0);
     __device__ __forceinline__ void add(int j, const PairOut<R> &o) {
         nlos += o.los ? 1 : 0;
-        if (o.sw) {
-            nconf++;
-            tcpamax = o.tcpa > tcpamax ? o.tcpa : tcpamax;
-            if (near_idx < 0 || o.tcpa < near_tcpa) { near_idx = j; near_tcpa = o.tcpa; near_dcpa2 = o.dcpa2; near_tin = o.tin; }
-        }
+        nconf += o.sw ? 1 : 0;
+        tcpamax = fmax(tcpamax, o.sw ? o.tcpa : R(0));
+        const bool take = o.sw && (o.tcpa < near_tcpa);
+        near_idx = take ? j : near_idx;
+        near_tcpa = take ? o.tcpa : near_tcpa;
+        near_dcpa2 = take ? o.dcpa2 : near_dcpa2;
+        near_tin = take ? o.tin : near_tin;
     }
+    __device__ __forceinline__ R tcpa_out() const { return near_idx < 0 ? R(0) : near_tcpa; }
 };
 
 }  // namespace bsg

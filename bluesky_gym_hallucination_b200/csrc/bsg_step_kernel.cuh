@@ -12,13 +12,26 @@ __device__ __forceinline__ void cd_params_for(const CdParams &P, CdParams &lit, 
     fast.rpz = (float)P.rpz; fast.rpz_m = (float)(P.rpz * P.fach); fast.hpz_m = (float)(P.hpz * P.facv);
 }
 
-template <typename R>
-__global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
+// CTA size / residency: 128-thread CTAs keep the small-N configs in one balanced wave
+// (C2: 683 CTAs over 148 SMs x 5 resident), 256 threads only when one env needs them (N > 128).
+template <typename R, int TPB> struct StepBounds {
+    static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : (sizeof(R) == 4 ? 2 : 1);
+};
+// per-env row of CD records in shared memory: N records + 16 B so that the rows of the envs sharing a
+// warp start in different banks (N * 32 B is a multiple of 128 B for N = 20: 2-way LDS.128 conflicts)
+template <typename R> __host__ __device__ constexpr size_t rec_row_bytes(int N) {
+    return (size_t)N * sizeof(typename RecOf<R>::type) + 16;
+}
+
+// RESO (MVP + resumenav) is a compile-time switch: without it the pair loop is a clean, unrollable FP32 body
+template <typename R, int TPB, bool RESO>
+__global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_kernel(const StepArgs<R> A) {
     using Rec = typename RecOf<R>::type;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int N = A.N, epb = A.epb;
-    Rec *recs = reinterpret_cast<Rec *>(smem_raw);                         // [2][epb*N]
-    EnvShared<R> *es = reinterpret_cast<EnvShared<R> *>(recs + 2 * epb * N);  // [epb]
+    const size_t rowb = rec_row_bytes<R>(N);
+    unsigned char *recs = smem_raw;                                        // [2][epb] rows of rowb bytes
+    EnvShared<R> *es = reinterpret_cast<EnvShared<R> *>(recs + 2 * epb * rowb);  // [epb]
     R *sdist = reinterpret_cast<R *>(es + epb);                            // [epb*N] hdg (resumenav) / sector distances
 
     const int tid = threadIdx.x;
@@ -30,7 +43,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
     const bool skip = valid && A.skip && A.skip[e];                       // fresh episode: no action, no integration
     const size_t EN = (size_t)A.E * N, k = (size_t)(valid ? e : 0) * N + i;
     double *ev = A.ev + (size_t)(valid ? e : 0) * BSG_NE;
-    const bool reso = A.reso_on && A.asas_on;
+    constexpr bool reso = RESO;
 
     AcReg<R> a = {};
     unsigned long long resorow = 0;
@@ -67,19 +80,20 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
     for (int s = 0; s < A.substeps; s++) {
         const int buf = s & 1;
         if (A.asas_on) {
-            Rec *rb = recs + (size_t)buf * epb * N + le * N;
+            Rec *rb = reinterpret_cast<Rec *>(recs + ((size_t)buf * epb + le) * rowb);
             if (live && !skip) {
                 make_rec<R>(a, lat0, lon0, rb[i]);
                 if (reso) sdist[le * N + i] = a.hdg;
             }
             __syncthreads();
-            if (valid && i == 0) es[le].anyconf[buf ^ 1] = 0;
+            if (RESO && valid && i == 0) es[le].anyconf[buf ^ 1] = 0;
             acc = RowAcc<R>();
             R dve = R(0), dvn = R(0);
             bool touched = false, active = false;
             unsigned long long keep = 0;
             if (live && !skip) {
                 const Rec me = rb[i];
+#pragma unroll 4
                 for (int j = 0; j < nl; j++) {
                     const Rec o = rb[j];
                     PairOut<R> po;
@@ -87,7 +101,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
                     const bool off = (j != i);
                     po.sw = po.sw && off; po.los = po.los && off;
                     acc.add(j, po);
-                    if (reso) {
+                    if constexpr (RESO) {
                         const bool inres = off && (po.sw || ((resorow >> j) & 1ull));
                         if (inres) {
                             R vrx = o.u - me.u, vry = o.v - me.v;
@@ -114,7 +128,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
                     }
                 }
             }
-            if (reso) {
+            if constexpr (RESO) {
                 if (acc.nconf > 0) atomicOr(&es[le].anyconf[buf], 1);
                 __syncthreads();
                 if (live && !skip) {
@@ -150,7 +164,7 @@ __global__ void __launch_bounds__(256) step_kernel(const StepArgs<R> A) {
         if (o.cd_nconf) o.cd_nconf[k] = acc.nconf;
         if (o.cd_nlos) o.cd_nlos[k] = acc.nlos;
         if (o.cd_near_idx) o.cd_near_idx[k] = acc.near_idx;
-        if (o.cd_near_tcpa) ((R *)o.cd_near_tcpa)[k] = acc.near_tcpa;
+        if (o.cd_near_tcpa) ((R *)o.cd_near_tcpa)[k] = acc.tcpa_out();
         if (o.cd_near_dcpa) ((R *)o.cd_near_dcpa)[k] = sqrt(acc.near_dcpa2);
         if (o.cd_near_tin) ((R *)o.cd_near_tin)[k] = acc.near_tin;
         if (o.cd_tcpamax) ((R *)o.cd_tcpamax)[k] = acc.tcpamax;

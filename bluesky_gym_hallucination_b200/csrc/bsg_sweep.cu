@@ -91,7 +91,7 @@ __global__ void __launch_bounds__(kThreads) cd_sweep_kernel(const bsg_cd_params 
         __syncthreads();      // everyone is done with tiles[buf] before it is refilled two iterations later
     }
     // combine the JS partial rows (adjacent lanes) -- warp-shuffle sum / max / lexicographic (tcpa, j) min
-    float ntc = acc.near_idx < 0 ? 3.0e38f : acc.near_tcpa;
+    float ntc = acc.near_tcpa;          // +inf while the partial row has no conflict
 #pragma unroll
     for (int m = 1; m < JS; m <<= 1) {
         acc.nconf += __shfl_xor_sync(0xffffffffu, acc.nconf, m);

@@ -1,0 +1,138 @@
+"""BlueSkyVecEnv -- thousands of independent BlueSky-Gym envs behind the Gymnasium VectorEnv API, one
+fused CUDA launch per step (libbsgcore.so).  Host-side mirror of the reference's env interface:
+same env ids, observation keys, action shapes, reward / terminated / truncated / info semantics as
+  bluesky_gym/envs/horizontal_cr_env.py:49-62,82-125,215-223
+  bluesky_gym/envs/vertical_cr_env.py:67-85,203-211,258-305
+  bluesky_gym/envs/sector_cr_env.py:52-67,87-132,219-225
+and the registrations of bluesky_gym/__init__.py:18-34 (max_episode_steps 300 / 300 / 200).
+PyTorch appears only as the tensor hand-off to RL libraries (`step_tensors`)."""
+import numpy as np
+import torch
+from . import _lib as L
+from .core import BsgCore, obs_slices
+from .gym_compat import spaces
+
+ENV_SPECS = {
+    # id: (kind, reference aircraft count, max_episode_steps, action dim)
+    'HorizontalCREnv-v0': (L.KIND_HORIZONTAL, 6, 300, 1),
+    'VerticalCREnv-v0': (L.KIND_VERTICAL, 6, 300, 1),
+    'SectorCREnv-v0': (L.KIND_SECTOR, 32, 200, 2),
+}
+INFO_KEYS = {L.KIND_HORIZONTAL: ('total_reward', 'total_intrusions', 'average_drift'),
+             L.KIND_VERTICAL: ('total_reward', 'total_intrusions', 'final_altitude'),
+             L.KIND_SECTOR: ('total_reward', 'total_intrusions', 'average_drift')}
+
+
+def single_spaces(kind, n_ac):
+    """The reference's Dict observation space (float64 Boxes) and action Box for one env."""
+    K = n_ac - 1
+    d = {}
+    for key, a, b in obs_slices(kind, n_ac):
+        bounded = kind == L.KIND_SECTOR and key in ('cos(drift)', 'sin(drift)', 'airspeed')   # sector_cr_env.py:54-56
+        d[key] = spaces.Box(-1 if bounded else -np.inf, 1 if bounded else np.inf, shape=(b - a,), dtype=np.float64)
+    act = spaces.Box(-1, 1, shape=(2 if kind == L.KIND_SECTOR else 1,), dtype=np.float64)
+    return spaces.Dict(d), act
+
+
+class BlueSkyVecEnv:
+    """Batched env.  reset()/step() speak numpy (Gymnasium VectorEnv semantics, next-step auto-reset);
+    step_tensors() keeps everything on the GPU for RL libraries that take torch tensors."""
+    metadata = {"render_modes": [], "autoreset_mode": "next_step"}
+
+    def __init__(self, env_id, num_envs, num_aircraft=None, device=0, precision='fp32', asas=False, mvp=False,
+                 seed=0, cd_outputs=False, max_episode_steps=None):
+        if env_id not in ENV_SPECS:
+            raise ValueError(f"unknown env id {env_id!r}; the batched core covers {sorted(ENV_SPECS)}")
+        kind, n_ref, max_steps, act_dim = ENV_SPECS[env_id]
+        self.env_id, self.kind, self.num_envs = env_id, kind, int(num_envs)
+        self.num_aircraft = int(num_aircraft or n_ref)
+        self.core = BsgCore(kind, self.num_envs, self.num_aircraft, precision=precision, device=device,
+                            asas_on=asas or mvp, reso_on=mvp, reso_off_own=mvp,
+                            max_episode_steps=max_steps if max_episode_steps is None else max_episode_steps,
+                            cd_outputs=cd_outputs)
+        self.single_observation_space, self.single_action_space = single_spaces(kind, self.num_aircraft)
+        self.observation_space, self.action_space = self.single_observation_space, self.single_action_space
+        self._slices = obs_slices(kind, self.num_aircraft)
+        self._seed = int(seed)
+        self._act = torch.zeros((self.num_envs, act_dim), dtype=self.core.rdtype, device=self.core.device)
+        self.closed = False
+
+    # ------------------------------------------------------------------ Gymnasium VectorEnv API
+    def _obs_dict(self, flat):
+        flat = np.asarray(flat, dtype=np.float64)
+        return {k: flat[:, a:b] for k, a, b in self._slices}
+
+    def _infos(self, info):
+        info = np.asarray(info, dtype=np.float64)
+        keys = INFO_KEYS[self.kind]
+        return {keys[0]: info[:, 0], keys[1]: info[:, 1].astype(np.int64), keys[2]: info[:, 2]}
+
+    def reset(self, seed=None, options=None):
+        if seed is not None:
+            self._seed = int(seed)
+        self.core.reset(seed=self._seed)
+        self.core.set_autoreset(True, seed=self._seed + 1)
+        obs = self.core.observe().cpu().numpy()
+        E = self.num_envs
+        nan = np.full(E, np.nan)
+        third = np.zeros(E) if self.kind == L.KIND_VERTICAL else nan       # average_drift of an empty list is nan
+        keys = INFO_KEYS[self.kind]
+        return self._obs_dict(obs), {keys[0]: np.zeros(E), keys[1]: np.zeros(E, np.int64), keys[2]: third}
+
+    def step(self, actions):
+        a = np.asarray(actions, dtype=np.float64).reshape(self.num_envs, -1)
+        self._act.copy_(torch.from_numpy(a).to(self.core.rdtype), non_blocking=False)
+        obs, rew, term, trunc, info = self.core.step(self._act)
+        out = (obs.cpu().numpy(), rew.cpu().numpy().astype(np.float64), term.cpu().numpy().astype(bool),
+               trunc.cpu().numpy().astype(bool), info.cpu().numpy())
+        return self._obs_dict(out[0]), out[1], out[2], out[3], self._infos(out[4])
+
+    def step_tensors(self, actions):
+        """actions: CUDA tensor [E, act_dim] in the core's dtype.  Returns the core's output tensors
+        (obs [E, obs_dim], reward, terminated, truncated, info) without leaving the device or syncing."""
+        return self.core.step(actions)
+
+    def close(self):
+        if not self.closed:
+            self.core.close()
+            self.closed = True
+
+
+class SB3VecEnvAdapter:
+    """stable-baselines3 VecEnv protocol (dict obs batched on axis 0, dones = terminated | truncated,
+    same-step auto-reset with infos[i]['terminal_observation'] and infos[i]['TimeLimit.truncated']), the
+    contract scripts/multi_processing_example.py:51-54 and bluesky_gym/utils/logger.py:15-35 rely on."""
+
+    def __init__(self, venv: BlueSkyVecEnv):
+        self.venv, self.num_envs = venv, venv.num_envs
+        self.observation_space, self.action_space = venv.single_observation_space, venv.single_action_space
+        self._actions = None
+
+    def reset(self):
+        obs, _ = self.venv.reset()
+        self.venv.core.set_autoreset(2, seed=self.venv._seed + 1)          # same-step: reset now, no skipped step
+        return obs
+
+    def step_async(self, actions):
+        self._actions = actions
+
+    def step_wait(self):
+        v = self.venv
+        obs, rew, term, trunc, info = v.step(self._actions)
+        dones = term | trunc
+        keys = INFO_KEYS[v.kind]
+        infos = [{keys[0]: float(info[keys[0]][i]), keys[1]: int(info[keys[1]][i]), keys[2]: float(info[keys[2]][i]),
+                  'TimeLimit.truncated': bool(trunc[i] and not term[i])} for i in range(self.num_envs)]
+        if dones.any():
+            fresh = v._obs_dict(v.core.observe().cpu().numpy())            # the device already reset those envs
+            for i in np.where(dones)[0]:
+                infos[i]['terminal_observation'] = {k: obs[k][i].copy() for k in obs}
+            obs = {k: np.where(dones[:, None], fresh[k], obs[k]) for k in obs}
+        return obs, rew, dones, infos
+
+    def step(self, actions):
+        self.step_async(actions)
+        return self.step_wait()
+
+    def close(self):
+        self.venv.close()

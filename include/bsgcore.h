@@ -120,7 +120,9 @@ int bsg_get_state(bsg_handle *h, double *ac_host, uint64_t *reso_host, int32_t *
 int bsg_reset(bsg_handle *h, const int32_t *mask_dev, uint64_t seed, void *stream);
 /* Gymnasium "next-step" auto-reset: when enabled, every bsg_step is followed on the same stream by a
  * bsg_reset of the envs it reported done, and the NEXT bsg_step returns for those envs the first
- * observation of the new episode with reward 0 / terminated 0 / truncated 0 (their action is ignored). */
+ * observation of the new episode with reward 0 / terminated 0 / truncated 0 (their action is ignored).
+ * enable = 2 is the same-step flavour SB3's VecEnv uses: the reset still follows the step, but the next step
+ * integrates the fresh episode normally (the caller fetches its first observation with bsg_observe). */
 int bsg_set_autoreset(bsg_handle *h, int32_t enable, uint64_t seed);
 /* observation of the current state (what reset() returns) */
 int bsg_observe(bsg_handle *h, void *obs_dev, void *stream);

@@ -32,6 +32,16 @@ def relerr(a, b, floor=1.0):
     return float(np.max(np.abs(a[ok] - b[ok]) / np.maximum(np.abs(b[ok]), floor))) if ok.any() else 0.0
 
 
+def obs_tol32(kind, ref):
+    """Per-entry fp32 tolerance: 1e-5 * max(|ref|, 1); Sector cos/sin(track) are the direction of a velocity
+    DIFFERENCE (sector_cr_env.py:294-296), condition number ~ 150 m/s / |v_rel|, so they scale with it."""
+    tol = RT32 * np.maximum(np.abs(ref), 1.0)
+    if kind in ('S', 2):
+        vrel = np.hypot(ref[:, 11:15] * 32, ref[:, 15:19] * 66)
+        tol[:, 19:23] *= np.maximum(1.0, 600.0 / vrel); tol[:, 23:27] *= np.maximum(1.0, 600.0 / vrel)
+    return tol
+
+
 def make_core(kind, E, N, precision, asas=0, **kw):
     from bluesky_gym_hallucination_b200.core import BsgCore
     return BsgCore(kind, E, N, precision=precision, asas_on=bool(asas), reso_on=bool(asas) and N <= 64 and kw.pop('reso', True),
@@ -87,11 +97,7 @@ def test_fp32_replays_reference_goldens(orc, name):
     core = make_core(KIND[kind], T, n, 'fp32', asas)
     nac = g['nac'].astype(np.int32)
     obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(core, g['ac0'], g['reso0'], nac, g['ev0'], g['act'][:, :na])
-    tol = RT32 * np.maximum(np.abs(g['obs1']), 1.0)
-    if kind == 'S':   # cos/sin(track) = direction of a velocity DIFFERENCE: condition number ~ 150 / |v_rel|
-        vrel = np.hypot(g['obs1'][:, 11:15] * 32, g['obs1'][:, 15:19] * 66)
-        tol[:, 19:23] *= np.maximum(1.0, 600.0 / vrel); tol[:, 23:27] *= np.maximum(1.0, 600.0 / vrel)
-    bad_obs = np.abs(obs - g['obs1']) > tol
+    bad_obs = np.abs(obs - g['obs1']) > obs_tol32(kind, g['obs1'])
     # an intrusion / waypoint / polygon threshold crossed within fp32 rounding changes reward and flags
     flip = (term != g['term']) | (trunc != g['trunc']) | (np.abs(rew - g['rew']) > 0.5)
     assert flip.sum() <= max(2, T // 50), f"{flip.sum()} threshold flips in {T} steps"
@@ -140,9 +146,13 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
             assert relerr(c64.cd['near_dcpa'].cpu().numpy() ** 2, o_cd['near_dcpa'] ** 2, floor=(5 * 1852.0) ** 2) < RT64 * 100
         # fp32: one step from the oracle's pre-state
         obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(c32, pre[0], pre[1], nac, pre[2], act)
-        flip = (term != o_term) | (trunc != o_trunc) | (np.abs(rew - o_rew) > 0.5) | np.isnan(o_obs).any(1)
-        assert flip.sum() <= max(2, E // 50)
-        assert relerr(obs[~flip], o_obs[~flip]) < RT32 * 2, relerr(obs[~flip], o_obs[~flip])
+        # envs poisoned by coincident creconfs intruders (NaN from MVP's division by a zero distance) are
+        # excluded from the fp32 float comparison; the fp64 path above matched their NaN pattern exactly
+        nanenv = np.isnan(o_obs).any(1) | np.isnan(obs).any(1)
+        flip = (term != o_term) | (trunc != o_trunc) | (np.abs(rew - o_rew) > 0.5) | nanenv
+        assert flip.sum() <= max(2, E // 50), flip.sum()
+        bad = np.abs(obs[~flip] - o_obs[~flip]) > 2 * obs_tol32(kind, o_obs[~flip])
+        assert bad.sum() == 0, (np.argwhere(bad)[:5], relerr(obs[~flip], o_obs[~flip]))
         if asas:
             mism = (cd['nconf'] != o_cd['nconf']) | (cd['nlos'] != o_cd['nlos'])
             assert mism.mean() < 5e-3, f"{mism.sum()} CD row mismatches of {mism.size}"
