@@ -259,6 +259,123 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+def run_giant(args):
+    """--workload c5: giant airspace, 16 envs x 10 000 aircraft, one all-pairs CD sweep per step.  N > 1: the
+    pair matrix is row-block sharded; every rank packs the records of its own aircraft, ONE NCCL all-gather
+    of the packed state (32 B/aircraft), then each rank sweeps its rows (row outputs are local: no reduce)."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from bluesky_gym_hallucination_b200 import core as bc, scenario
+    rank, world, local = env_int('RANK', 0), env_int('WORLD_SIZE', 1), env_int('LOCAL_RANK', 0)
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    if world > 1:
+        dist.init_process_group('nccl', device_id=dev)
+    E, N = 16, 10000
+    K, W = args.steps, max(args.warmup, 3)
+    lat, lon, alt, trk, gs, vs = scenario.raw_traffic(E, N, seed=3, box_nm=1000.0)       # same traffic on every rank
+    r0, r1 = rank * N // world, (rank + 1) * N // world
+    t64 = lambda a: torch.as_tensor(np.ascontiguousarray(a[:, r0:r1]), dtype=torch.float64, device=dev)
+    t32 = lambda a: torch.as_tensor(np.ascontiguousarray(a[:, r0:r1]), dtype=torch.float32, device=dev)
+    mine = (t64(lat), t64(lon), t32(alt), t32(trk), t32(gs), t32(vs))
+    rec_all = torch.empty((world, E, r1 - r0, 8), dtype=torch.float32, device=dev) if world > 1 else None
+    out = None
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    peak32, _ = bc.peak_fp32(local, 4096)
+
+    def one():
+        nonlocal out
+        rec = bc.cd_pack(*mine, 52.0, 4.0)                                   # [E, rows, 8]
+        if world > 1:
+            dist.all_gather_into_tensor(rec_all, rec)
+            full = rec_all.permute(1, 0, 2, 3).reshape(E, N, 8).contiguous()   # rank-major -> aircraft-major
+        else:
+            full = rec
+        out = bc.cd_sweep(full, r0, r1, out=out)
+    for _ in range(W):
+        one()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(K)]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    for k in range(K):
+        flush.zero_()
+        ev[k][0].record(); one(); ev[k][1].record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    dev_ms = sum(ev[k][0].elapsed_time(ev[k][1]) for k in range(K))
+    clocks = sampler.stop() if rank == 0 else None
+    t = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        pairs = float(E) * N * (N - 1)
+        ms = float(t.item()) / K
+        ach = FLOP_PER_PAIR * pairs / world / (ms * 1e-3) / 1e12
+        print(json.dumps({
+            "metric": "pair-evals/sec", "value": pairs / (ms * 1e-3), "unit": "pair-evals/s", "n_gpus": world, "steps": K,
+            "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "c5", "description": "giant airspace 16 envs x 10000 aircraft all-pairs CPA, row-block sharded",
+                       "collective": "one NCCL all-gather of packed state per step" if world > 1 else "none",
+                       "l2": "256 MB flush between timed iterations"},
+            "roofline": {"bound": "fp32", "achieved": ach, "peak": peak32, "unit": "TFLOP/s", "frac": ach / peak32,
+                         "traffic": None, "kernel": "cd_sweep_kernel (+ pack, all-gather inside the timed step)"},
+            "gpu_launches": 2 * K, "clocks": clocks}), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_ndmap(args):
+    """--workload c4: ND-map, 1024 envs x 500 aircraft x 30 look-ahead steps, 64x64x8 grid (HBM-write bound)."""
+    import numpy as np
+    import torch
+    from bluesky_gym_hallucination_b200 import core as bc
+    local = env_int('LOCAL_RANK', 0)
+    torch.cuda.set_device(local)
+    dev = torch.device('cuda', local)
+    E, n, K, W = args.envs or 1024, 500, args.steps, max(args.warmup, 3)
+    rng = np.random.default_rng(4)
+    rec = np.zeros((E, 6, n), np.float32)
+    box = 200 * 1852.0
+    rec[:, 0] = rng.uniform(0, box, (E, n)); rec[:, 1] = rng.uniform(0, box, (E, n))
+    rec[:, 2] = rng.uniform(3048, 12192, (E, n))
+    hdg = rng.uniform(0, 2 * np.pi, (E, n)); gs = rng.uniform(120, 250, (E, n))
+    rec[:, 3] = gs * np.sin(hdg); rec[:, 4] = gs * np.cos(hdg); rec[:, 5] = rng.choice([-10.0, 0.0, 0.0, 10.0], (E, n))
+    d_rec = torch.as_tensor(rec, device=dev)
+    kw = dict(nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=3048.0, cx=box / 64, cy=box / 64, cz=9144.0 / 8, dt=10.0)
+    out = bc.ndmap(d_rec, **kw)
+    for _ in range(W):
+        bc.ndmap(d_rec, out=out, **kw)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local); sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(K):
+        bc.ndmap(d_rec, out=out, **kw)                   # 2 GB written per build >> L2
+    e1.record(); torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / K
+    clocks = sampler.stop()
+    cells = E * 30 * 64 * 64 * 8
+    gbs = (2.0 * cells + 24.0 * n * E + 4 * 30 * E) / (ms * 1e-3) / 1e9
+    peak = load_peaks().get("hbm_gbs", 6650.0)
+    print(json.dumps({
+        "metric": "ndmap-samples/sec", "value": E * n * 30 / (ms * 1e-3), "unit": "trajectory samples/s", "n_gpus": 1,
+        "steps": K, "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32+u16", "data": "synthetic",
+        "config": {"workload": "c4", "description": f"ND-map {E} envs x 500 aircraft x 30 steps, grid 64x64x8",
+                   "l2": "2 GB written per build (>> 126 MB L2)"},
+        "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": None,
+                     "kernel": "ndmap_kernel", "bytes_per_build": 2.0 * cells},
+        "gpu_launches": K, "clocks": clocks}), flush=True)
+
+
 def load_peaks():
     try:
         with open(os.path.join(ROOT, 'MEASURED_PEAKS.json')) as f:
@@ -273,12 +390,16 @@ def main():
     ap.add_argument('--steps', type=int, default=2000)
     ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS))
+    ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS) + ['c4', 'c5'])
     ap.add_argument('--envs', type=int, default=0, help='override envs per GPU')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')
     args = ap.parse_args()
     if args.impl == 'reference':
         run_reference(args)
+    elif args.workload == 'c5':
+        run_giant(args)
+    elif args.workload == 'c4':
+        run_ndmap(args)
     else:
         run_ours(args)
 

@@ -88,9 +88,10 @@ class BsgCore:
                               _ptr(self.truncated), _ptr(self.info), *cdp, _ptr(self.done))
 
     def close(self):
-        if getattr(self, 'h', None):
-            self.lib.bsg_destroy(self.h)
-            self.h = C.c_void_p()
+        h = getattr(self, 'h', None)
+        if h:
+            self.h = None
+            self.lib.bsg_destroy(h)
 
     __del__ = close
 

@@ -3,6 +3,7 @@
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstring>
+#include <cstdlib>
 #include <string>
 #include <new>
 #include "bsg_step_kernel.cuh"
@@ -101,7 +102,10 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     h->obs_dim = g.env_kind == BSG_KIND_HORIZONTAL ? 5 * K + 3 : g.env_kind == BSG_KIND_VERTICAL ? 4 + 7 * K
                  : g.env_kind == BSG_KIND_SECTOR ? 31 : 0;
     h->act_dim = g.env_kind == BSG_KIND_SECTOR ? 2 : (g.env_kind == BSG_KIND_RAW ? 0 : 1);
-    h->tpb = N <= 128 ? 128 : 256;
+    // CTA size: the one of {128, 256} that wastes fewer lanes on whole envs (ties -> 128: better balance)
+    h->tpb = 128;
+    if (N > 128 || (256 / N) * N * 128 > (128 / N) * N * 256) h->tpb = 256;
+    if (const char *f = getenv("BSG_FORCE_TPB")) { int t = atoi(f); if ((t == 128 || t == 256) && t >= N) h->tpb = t; }
     h->epb = h->tpb / N;
     const size_t rs = rsize(h), rowb = g.precision == BSG_FP64 ? rec_row_bytes<double>(N) : rec_row_bytes<float>(N);
     const size_t essz = g.precision == BSG_FP64 ? sizeof(EnvShared<double>) : sizeof(EnvShared<float>);

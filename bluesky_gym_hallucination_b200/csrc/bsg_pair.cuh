@@ -64,11 +64,14 @@ __device__ __forceinline__ void pair_fast(const RecFast &a, const RecFast &b, co
     const float dx = (b.x - a.x) * cav;
     const float dist2 = fmaf(dx, dx, dy * dy);
     const float du = b.u - a.u, dv = b.v - a.v;
-    const float dv2 = fmaxf(fmaf(du, du, dv * dv), 1e-6f);
+    const float dv2r = fmaf(du, du, dv * dv);
+    const float dv2 = fmaxf(dv2r, 1e-6f);                   // the reference's lower clamp on |v_rel|^2
     const float idv2 = rcp_approx(dv2);
     const float tcpa = -fmaf(du, dx, dv * dy) * idv2;
     const float cr = fmaf(dx, dv, -(dy * du));
-    const float dcpa2 = cr * cr * idv2;
+    // dist^2 - tcpa^2 dv2 = (cr^2 + dist^2 (dv2 - dv2r)) / dv2: the second term is exactly 0 unless the clamp
+    // is active (equal velocity vectors, common with integer dpsi draws), where dCPA must come out as dist
+    const float dcpa2 = fmaf(dist2 * (dv2 - dv2r), idv2, cr * cr * idv2);
     const bool swhor = dcpa2 < P.R2;
     const float dtinhor = sqrt_approx(fmaxf(0.0f, P.R2 - dcpa2) * idv2);
     const float tinhor = swhor ? tcpa - dtinhor : 1e8f;

@@ -146,3 +146,17 @@ def test_device_reset_properties(orc):
     torch.cuda.synchronize()
     assert c.truncated.sum().item() <= E // 10
     c.close()
+
+
+def test_cd_sweep_equal_velocity_pairs(orc):
+    """Pairs with identical velocity vectors (|v_rel|^2 under the reference's 1e-6 clamp): dCPA must equal the
+    current distance, not 0 -- the cross-product form needs its clamp correction term."""
+    from bluesky_gym_hallucination_b200 import core, scenario as sc
+    lat, lon, alt, trk, gs, vs = sc.raw_traffic(2, 400, seed=8, box_nm=150.0)
+    trk[:] = np.round(trk / 45.0) * 45.0       # 8 headings
+    gs[:] = 150.0                              # one speed -> thousands of equal-velocity pairs
+    ref = orc.cd_rows(lat, lon, alt, trk, gs, vs, nthreads=8)
+    out = core.cd_sweep(_pack(lat, lon, alt, trk, gs, vs))
+    torch.cuda.synchronize()
+    mism = (out['nconf'].cpu().numpy() != ref['nconf']).sum()
+    assert mism <= 4, mism
