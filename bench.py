@@ -266,7 +266,7 @@ def run_giant(args):
     import numpy as np
     import torch
     import torch.distributed as dist
-    from bluesky_gym_hallucination_b200 import core as bc, scenario
+    from bluesky_gym_hallucination_b200 import core as bc, scenario, sharding
     rank, world, local = env_int('RANK', 0), env_int('WORLD_SIZE', 1), env_int('LOCAL_RANK', 0)
     torch.cuda.set_device(local)
     dev = torch.device('cuda', local)
@@ -275,7 +275,7 @@ def run_giant(args):
     E, N = 16, 10000
     K, W = args.steps, max(args.warmup, 3)
     lat, lon, alt, trk, gs, vs = scenario.raw_traffic(E, N, seed=3, box_nm=1000.0)       # same traffic on every rank
-    r0, r1 = rank * N // world, (rank + 1) * N // world
+    r0, r1 = sharding.row_block(N, rank, world)
     t64 = lambda a: torch.as_tensor(np.ascontiguousarray(a[:, r0:r1]), dtype=torch.float64, device=dev)
     t32 = lambda a: torch.as_tensor(np.ascontiguousarray(a[:, r0:r1]), dtype=torch.float32, device=dev)
     mine = (t64(lat), t64(lon), t32(alt), t32(trk), t32(gs), t32(vs))
@@ -287,11 +287,7 @@ def run_giant(args):
     def one():
         nonlocal out
         rec = bc.cd_pack(*mine, 52.0, 4.0)                                   # [E, rows, 8]
-        if world > 1:
-            dist.all_gather_into_tensor(rec_all, rec)
-            full = rec_all.permute(1, 0, 2, 3).reshape(E, N, 8).contiguous()   # rank-major -> aircraft-major
-        else:
-            full = rec
+        full = sharding.gather_records(rec, N, world, buf=rec_all)
         out = bc.cd_sweep(full, r0, r1, out=out)
     for _ in range(W):
         one()
