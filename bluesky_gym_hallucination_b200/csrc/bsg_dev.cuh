@@ -86,7 +86,9 @@ __device__ __forceinline__ double vcasormach2tas(double spd, double h) {
 
 // ------------------------------------------------------------------ performance envelope
 template <typename R> __device__ __forceinline__ int flight_phase(R vs, R alt) {
-    R roc = vs / R(kFpm), h = alt / R(kFt);
+    R roc, h;
+    if constexpr (sizeof(R) == 8) { roc = vs / kFpm; h = alt / kFt; }               // literal order (numpy divides)
+    else { roc = vs * float(1.0 / kFpm); h = alt * float(1.0 / kFt); }              // fast path: no IEEE division
     int ph = PH_NA;
     if (h <= R(75)) ph = PH_GD;
     if (h > R(75) && h <= R(1000) && roc >= R(150)) ph = PH_IC;

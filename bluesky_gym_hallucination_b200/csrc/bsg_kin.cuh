@@ -5,6 +5,7 @@
 // memoised in the state (key -> value) so the steady state costs no pow() at all.
 #pragma once
 #include "bsg_dev.cuh"
+#include "bsg_pair.cuh"
 
 namespace bsg {
 
@@ -33,7 +34,7 @@ __device__ __forceinline__ void ac_load(AcReg<R> &a, const double *pos, const R 
     }
     R s, c;
     if constexpr (sizeof(R) == 8) { s = sin(a.hdg * kD2R); c = cos(a.hdg * kD2R); }
-    else sincosf(a.hdg * float(kD2R), &s, &c);
+    else sincospif(a.hdg * (1.0f / 180.0f), &s, &c);
     a.gsn = a.tas * c; a.gse = a.tas * s;
 }
 
@@ -132,7 +133,7 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     float tas = need_ax ? fmaf(ax, dt, a.tas) : atas;
     a.ax = ax;
     const float kTurn = float(9.80665 * 0.46630765815499864 * kR2D);   // g0 * tan(25 deg) in deg/s * m/s
-    float turn = dt * kTurn / fmaxf(tas, 1e-8f);
+    float turn = dt * kTurn * rcp_approx(fmaxf(tas, 1e-8f));
     float delhdg = wrap360(t_hdg - a.hdg + 180.0f) - 180.0f;
     bool swhdg = fabsf(delhdg) > turn;
     float hdg = wrap360(swhdg ? a.hdg + copysignf(turn, delhdg) : t_hdg);
@@ -143,13 +144,13 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     bool need_az = fabsf(dvs) > float(300 * kFpm);
     float vs = need_az ? a.vs + copysignf(float(300 * kFpm), dvs) * dt : tvs;
     float s, c;
-    sincosf(hdg * float(kD2R), &s, &c);
+    sincospif(hdg * (1.0f / 180.0f), &s, &c);                // hdg in [0, 360): exact range reduction in sincospi
     float gsn = tas * c, gse = tas * s;
     float alt_old = a.alt;
     a.alt = swalt ? fmaf(vs, dt, a.alt) : allow_h;
     a.lat = a.lat + (double)(dt * gsn) * (kR2D / kRe);
-    float coslat = cosf((float)(a.lat * kD2R));
-    a.lon = a.lon + (double)(dt * gse / coslat) * (kR2D / kRe);
+    float coslat = cospif((float)(a.lat * (1.0 / 180.0)));
+    a.lon = a.lon + (double)(dt * gse * rcp_approx(coslat)) * (kR2D / kRe);
     if (want_cas) a.cas = (float)vtas2cas((double)tas, (double)alt_old);
     a.tas = tas; a.hdg = hdg; a.vs = vs; a.gsn = gsn; a.gse = gse;
 }

@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(kNdThreads) ndmap_kernel(const bsg_ndmap_param
     __shared__ int s_ncf;
     const int k = blockIdx.x, e = blockIdx.y;
     uint32_t *cw = reinterpret_cast<uint32_t *>(cnt);
-    for (int c = threadIdx.x; c < cells / 2; c += kNdThreads) cw[c] = 0u;
+    for (int c = threadIdx.x; c < cells / 8; c += kNdThreads) reinterpret_cast<uint4 *>(cw)[c] = make_uint4(0u, 0u, 0u, 0u);
     if (threadIdx.x == 0) s_ncf = 0;
     __syncthreads();
     const float *r = rec + (size_t)e * 6 * n;
@@ -41,42 +41,58 @@ __global__ void __launch_bounds__(kNdThreads) ndmap_kernel(const bsg_ndmap_param
         atomicAdd(&cw[c >> 1], (c & 1) ? 0x10000u : 1u);         // u16 lanes: no carry for n <= 65535
     }
     __syncthreads();
-    // pass 1: 3x3 box sum in the (y, x) plane
-    for (int c = threadIdx.x; c < cells; c += kNdThreads) {
-        const int x = c % nx, y = (c / nx) % ny;
-        unsigned s = 0;
+    // pass 1: 3x3 box sum in the (y, x) plane, 8 cells (one 16-byte vector of packed u16 pairs) per item.
+    // Packed u16 lanes add as plain u32 (counts <= 65535 / 27); the +-1 neighbours in x come from funnel shifts.
+    const int gx = nx >> 3;                                   // 16-byte groups per row
+    uint32_t *sw = reinterpret_cast<uint32_t *>(sxy);
+    for (int g = threadIdx.x; g < cells / 8; g += kNdThreads) {
+        const int x8 = g % gx, yz = g / gx, y = yz % ny;
+        uint32_t rs[6] = { 0u, 0u, 0u, 0u, 0u, 0u };
 #pragma unroll
         for (int dy = -1; dy <= 1; dy++) {
             const int yy = y + dy;
             if (yy < 0 || yy >= ny) continue;
-            const uint16_t *row = cnt + c + dy * nx;
-            s += row[0] + (x > 0 ? row[-1] : 0) + (x < nx - 1 ? row[1] : 0);
+            const int wb = ((yz + dy) * nx + x8 * 8) >> 1;    // first word of the group in row yy
+            const uint4 m = *reinterpret_cast<const uint4 *>(cw + wb);
+            rs[0] += x8 > 0 ? cw[wb - 1] : 0u;
+            rs[1] += m.x; rs[2] += m.y; rs[3] += m.z; rs[4] += m.w;
+            rs[5] += x8 < gx - 1 ? cw[wb + 4] : 0u;
         }
-        sxy[c] = (uint16_t)s;
+        uint4 o;
+        o.x = rs[1] + __funnelshift_l(rs[0], rs[1], 16) + __funnelshift_r(rs[1], rs[2], 16);
+        o.y = rs[2] + __funnelshift_l(rs[1], rs[2], 16) + __funnelshift_r(rs[2], rs[3], 16);
+        o.z = rs[3] + __funnelshift_l(rs[2], rs[3], 16) + __funnelshift_r(rs[3], rs[4], 16);
+        o.w = rs[4] + __funnelshift_l(rs[3], rs[4], 16) + __funnelshift_r(rs[4], rs[5], 16);
+        *reinterpret_cast<uint4 *>(sw + (g << 2)) = o;
     }
     __syncthreads();
-    // pass 2: sum over z, emit 16 cells per thread as one 16-byte store each for occ and conf
+    // pass 2: sum over z, emit 16 cells per item as one 16-byte store each for occ and conf
     const size_t slab = ((size_t)e * p.nt + k) * cells;
+    const int plane_w = (nx * ny) >> 1;                       // words per z plane
     int ncf = 0;
     for (int g = threadIdx.x; g < cells / 16; g += kNdThreads) {
-        const int c0 = g * 16, z = c0 / (nx * ny);
+        const int w0 = g << 3, z = (g << 4) / (nx * ny);
+        uint32_t sv[8], cv[8];
+#pragma unroll
+        for (int h = 0; h < 2; h++) {
+            uint4 a = *reinterpret_cast<const uint4 *>(sw + w0 + 4 * h);
+            if (z > 0) { const uint4 q = *reinterpret_cast<const uint4 *>(sw + w0 + 4 * h - plane_w); a.x += q.x; a.y += q.y; a.z += q.z; a.w += q.w; }
+            if (z < nz - 1) { const uint4 q = *reinterpret_cast<const uint4 *>(sw + w0 + 4 * h + plane_w); a.x += q.x; a.y += q.y; a.z += q.z; a.w += q.w; }
+            sv[4 * h] = a.x; sv[4 * h + 1] = a.y; sv[4 * h + 2] = a.z; sv[4 * h + 3] = a.w;
+            const uint4 c = *reinterpret_cast<const uint4 *>(cw + w0 + 4 * h);
+            cv[4 * h] = c.x; cv[4 * h + 1] = c.y; cv[4 * h + 2] = c.z; cv[4 * h + 3] = c.w;
+        }
         uint32_t ow[4], fw[4];
 #pragma unroll
         for (int w = 0; w < 4; w++) {
-            uint32_t o = 0, f = 0;
-#pragma unroll
-            for (int b = 0; b < 4; b++) {
-                const int c = c0 + w * 4 + b;
-                unsigned s = sxy[c] + (z > 0 ? sxy[c - nx * ny] : 0) + (z < nz - 1 ? sxy[c + nx * ny] : 0);
-                const unsigned cc = cnt[c] > 255 ? 255u : cnt[c];
-                o |= cc << (8 * b);
-                f |= (s >= 2 ? 1u : 0u) << (8 * b);
-                ncf += s >= 2;
-            }
-            ow[w] = o; fw[w] = f;
+            const uint32_t f0 = __vcmpgeu2(sv[2 * w], 0x00020002u) & 0x00010001u;
+            const uint32_t f1 = __vcmpgeu2(sv[2 * w + 1], 0x00020002u) & 0x00010001u;
+            fw[w] = __byte_perm(f0, f1, 0x6420);
+            ow[w] = __byte_perm(__vminu2(cv[2 * w], 0x00ff00ffu), __vminu2(cv[2 * w + 1], 0x00ff00ffu), 0x6420);
+            ncf += __popc(fw[w]);
         }
-        *reinterpret_cast<uint4 *>(occ + slab + c0) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
-        *reinterpret_cast<uint4 *>(conf + slab + c0) = make_uint4(fw[0], fw[1], fw[2], fw[3]);
+        *reinterpret_cast<uint4 *>(occ + slab + ((size_t)g << 4)) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+        *reinterpret_cast<uint4 *>(conf + slab + ((size_t)g << 4)) = make_uint4(fw[0], fw[1], fw[2], fw[3]);
     }
 #pragma unroll
     for (int m = 16; m > 0; m >>= 1) ncf += __shfl_xor_sync(0xffffffffu, ncf, m);

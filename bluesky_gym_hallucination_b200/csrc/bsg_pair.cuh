@@ -58,7 +58,17 @@ struct CdParamsF { float R2, hpz, dtlook, rpz, rpz_m, hpz_m; };
 __device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float sqrt_approx(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-__device__ __forceinline__ void pair_fast(const RecFast &a, const RecFast &b, const CdParamsF &P, PairOut<float> &o) {
+// Hot form of the fp32 pair: only what decides the conflict flag.  Instruction budget per pair (B200: the ALU
+// pipe -- FSETP/FSEL/FMNMX/integer -- issues at half the rate of the FMA pipe, so comparisons are the scarce
+// resource): ~31 FMA-pipe ops, 3 MUFU, 10 ALU ops.  Everything needed only for conflicting pairs (LoS test,
+// row min/argmin/max, MVP) is evaluated by the caller under a warp-uniform `any(sw)` branch.
+//  * no select of tinhor/touthor: when dcpa2 >= R2 the sqrt argument is negative -> NaN, FMNMX drops it and
+//    the flag is gated by swhor anyway;
+//  * no clamp of |dvs|: rcp(0) = inf gives tinver/toutver = -/+inf (vertically inside) or both beyond the
+//    look-ahead / in the past, the same decisions the reference's 1e-6 clamp produces.
+struct PairCore { float tcpa, dcpa2, tin, dx, dy, dist2, dalt; };
+
+__device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &b, const CdParamsF &P, bool off, PairCore &o) {
     const float dy = b.y - a.y;
     const float cav = fmaf(a.ca, b.ca, -(a.sa * b.sa));
     const float dx = (b.x - a.x) * cav;
@@ -72,19 +82,22 @@ __device__ __forceinline__ void pair_fast(const RecFast &a, const RecFast &b, co
     // dist^2 - tcpa^2 dv2 = (cr^2 + dist^2 (dv2 - dv2r)) / dv2: the second term is exactly 0 unless the clamp
     // is active (equal velocity vectors, common with integer dpsi draws), where dCPA must come out as dist
     const float dcpa2 = fmaf(dist2 * (dv2 - dv2r), idv2, cr * cr * idv2);
-    const bool swhor = dcpa2 < P.R2;
-    const float dtinhor = sqrt_approx(fmaxf(0.0f, P.R2 - dcpa2) * idv2);
-    const float tinhor = swhor ? tcpa - dtinhor : 1e8f;
-    const float touthor = swhor ? tcpa + dtinhor : -1e8f;
+    const bool swhor = (dcpa2 < P.R2) && off;
+    const float dtinhor = sqrt_approx((P.R2 - dcpa2) * idv2);
     const float dalt = b.alt - a.alt;
-    float dvs = b.vs - a.vs;
-    dvs = (fabsf(dvs) < 1e-6f) ? 1e-6f : dvs;
-    const float n = -rcp_approx(dvs), hn = P.hpz * n;
-    const float thi = fmaf(dalt, n, hn), tlo = fmaf(dalt, n, -hn);
-    const float tin = fmaxf(fminf(thi, tlo), tinhor), tout = fminf(fmaxf(thi, tlo), touthor);
-    o.sw = swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
-    o.los = (dist2 < P.R2) && (fabsf(dalt) < P.hpz);
-    o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist = dist2 /* squared */; o.dalt = dalt;
+    const float n = -rcp_approx(b.vs - a.vs);
+    const float thi = (dalt + P.hpz) * n, tlo = (dalt - P.hpz) * n;
+    const float tin = fmaxf(fminf(thi, tlo), tcpa - dtinhor), tout = fminf(fmaxf(thi, tlo), tcpa + dtinhor);
+    o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist2 = dist2; o.dalt = dalt;
+    return swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
+}
+
+// full form (used where every output is wanted): flag + LoS + the PairOut fields
+__device__ __forceinline__ void pair_fast(const RecFast &a, const RecFast &b, const CdParamsF &P, PairOut<float> &o) {
+    PairCore c;
+    o.sw = pair_fast_core(a, b, P, true, c);
+    o.los = (c.dist2 < P.R2) && (fabsf(c.dalt) < P.hpz);
+    o.tcpa = c.tcpa; o.dcpa2 = c.dcpa2; o.tin = c.tin; o.dx = c.dx; o.dy = c.dy; o.dist = c.dist2 /* squared */; o.dalt = c.dalt;
 }
 
 // MVP displacement of ownship 1 for one conflict pair; drel = (dx, dy, dalt) is intruder relative to ownship.
@@ -125,6 +138,13 @@ template <typename R> struct RowAcc {
         near_tcpa = take ? o.tcpa : near_tcpa;
         near_dcpa2 = take ? o.dcpa2 : near_dcpa2;
         near_tin = take ? o.tin : near_tin;
+    }
+    // called only for conflicting pairs (under the caller's rare branch); LoS implies conflict off-threshold
+    __device__ __forceinline__ void add_conflict(int j, R tcpa, R dcpa2, R tin, bool los) {
+        nconf++;
+        nlos += los ? 1 : 0;
+        tcpamax = fmax(tcpamax, tcpa);
+        if (tcpa < near_tcpa) { near_idx = j; near_tcpa = tcpa; near_dcpa2 = dcpa2; near_tin = tin; }
     }
     __device__ __forceinline__ R tcpa_out() const { return near_idx < 0 ? R(0) : near_tcpa; }
 };

@@ -97,10 +97,20 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 for (int j = 0; j < nl; j++) {
                     const Rec o = rb[j];
                     PairOut<R> po;
-                    if constexpr (sizeof(R) == 8) pair_lit(me, o, PL, po); else pair_fast(me, o, PF, po);
                     const bool off = (j != i);
-                    po.sw = po.sw && off; po.los = po.los && off;
-                    acc.add(j, po);
+                    if constexpr (sizeof(R) == 8) {
+                        pair_lit(me, o, PL, po);
+                        po.sw = po.sw && off; po.los = po.los && off;
+                        acc.add(j, po);
+                    } else {
+                        PairCore pc;
+                        po.sw = pair_fast_core(me, o, PF, off, pc);
+                        po.los = false;
+                        po.tcpa = pc.tcpa; po.dcpa2 = pc.dcpa2; po.tin = pc.tin; po.dx = pc.dx; po.dy = pc.dy; po.dist = pc.dist2;
+                        if (__any_sync(__activemask(), po.sw)) {   // conflicting pairs only: row reductions off the hot path
+                            if (po.sw) acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
+                        }
+                    }
                     if constexpr (RESO) {
                         const bool inres = off && (po.sw || ((resorow >> j) & 1ull));
                         if (inres) {

@@ -82,11 +82,11 @@ __global__ void __launch_bounds__(kThreads) cd_sweep_kernel(const bsg_cd_params 
             const float4 *s = reinterpret_cast<const float4 *>(tb + jj);
             const float4 a = s[0], b = s[1];
             const RecFast o = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
-            PairOut<float> po;
-            pair_fast(me, o, P, po);
-            const bool off = (j0 + jj) != i;
-            po.sw = po.sw && off; po.los = po.los && off;
-            acc.add(j0 + jj, po);
+            PairCore pc;
+            const bool sw = pair_fast_core(me, o, P, (j0 + jj) != i, pc);
+            if (__any_sync(__activemask(), sw)) {               // conflicts are rare: row reductions off the hot path
+                if (sw) acc.add_conflict(j0 + jj, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < P.R2) && (fabsf(pc.dalt) < P.hpz));
+            }
         }
         __syncthreads();      // everyone is done with tiles[buf] before it is refilled two iterations later
     }
