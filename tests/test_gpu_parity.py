@@ -141,7 +141,9 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
             assert np.array_equal(c64.cd['nconf'].cpu().numpy(), o_cd['nconf'])
             assert np.array_equal(c64.cd['nlos'].cpu().numpy(), o_cd['nlos'])
             assert np.array_equal(c64.cd['near_idx'].cpu().numpy(), o_cd['near_idx'])
-            assert relerr(c64.cd['near_tcpa'].cpu().numpy(), o_cd['near_tcpa']) < RT64 * 1000
+            # tCPA = -(du dx + dv dy)/dv2 with dx, dy rebuilt from sin/cos(atan2(.)): libm differences (glibc vs CUDA)
+            # of 1 ulp on 1e5 m offsets, amplified by the cancellation in the dot product
+            assert relerr(c64.cd['near_tcpa'].cpu().numpy(), o_cd['near_tcpa']) < 1e-8
             # dCPA^2 = |dist^2 - tcpa^2 dv2| cancels: its error scales with dist^2, so compare squares against R^2
             assert relerr(c64.cd['near_dcpa'].cpu().numpy() ** 2, o_cd['near_dcpa'] ** 2, floor=(5 * 1852.0) ** 2) < RT64 * 100
         # fp32: one step from the oracle's pre-state
@@ -149,7 +151,10 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
         # envs poisoned by coincident creconfs intruders (NaN from MVP's division by a zero distance) are
         # excluded from the fp32 float comparison; the fp64 path above matched their NaN pattern exactly
         nanenv = np.isnan(o_obs).any(1) | np.isnan(obs).any(1)
-        flip = (term != o_term) | (trunc != o_trunc) | (np.abs(rew - o_rew) > 0.5) | nanenv
+        # resumenav decisions (past CPA: sign of r.v_rel ~ 0, horizontal LoS, bouncing) are thresholds too: an
+        # aircraft whose ASAS-active flag differs from the oracle's follows different targets for the step
+        act_flip = (ac1[:, orc.F['asas_active']] != o_ac[:, orc.F['asas_active']]).any(1) if asas else np.zeros(E, bool)
+        flip = (term != o_term) | (trunc != o_trunc) | (np.abs(rew - o_rew) > 0.5) | nanenv | act_flip
         assert flip.sum() <= max(2, E // 50), flip.sum()
         err, tol = np.abs(obs[~flip] - o_obs[~flip]), obs_tol32(kind, o_obs[~flip])
         if asas:
