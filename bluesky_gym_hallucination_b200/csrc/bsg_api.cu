@@ -107,9 +107,8 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     if (N > 128 || (256 / N) * N * 128 > (128 / N) * N * 256) h->tpb = 256;
     if (const char *f = getenv("BSG_FORCE_TPB")) { int t = atoi(f); if ((t == 128 || t == 256) && t >= N) h->tpb = t; }
     h->epb = h->tpb / N;
-    const size_t rs = rsize(h), rowb = g.precision == BSG_FP64 ? rec_row_bytes<double>(N) : rec_row_bytes<float>(N);
-    const size_t essz = g.precision == BSG_FP64 ? sizeof(EnvShared<double>) : sizeof(EnvShared<float>);
-    h->smem = 2 * (size_t)h->epb * rowb + h->epb * essz + (size_t)h->epb * N * rs;
+    const size_t rs = rsize(h);
+    h->smem = g.precision == BSG_FP64 ? step_smem<double>(N, h->epb).total : step_smem<float>(N, h->epb).total;
     CK(h, cudaSetDevice(g.device));
     const size_t EN = (size_t)E * N;
     CK(h, cudaMalloc(&h->pos, 2 * EN * sizeof(double)));

@@ -19,13 +19,22 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     if (ar) { done_now = h->done_buf[h->flip ^ 1]; if (!A.out.done) A.out.done = done_now; }
     const int grid = (g.num_envs + h->epb - 1) / h->epb;
     const bool reso = g.reso_on && g.asas_on;
-    if (h->tpb == 128) {
-        if (reso) step_kernel<R, 128, true><<<grid, 128, h->smem, s>>>(A);
-        else step_kernel<R, 128, false><<<grid, 128, h->smem, s>>>(A);
+    const dim3 gd(grid), bd(h->tpb);
+#define BSG_LAUNCH(TPB, RESO, SYM) step_kernel<R, TPB, RESO, SYM><<<gd, bd, h->smem, s>>>(A)
+    if constexpr (sizeof(R) == 4) {
+        const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM");          // symmetric half-ring sweep (fp32 fast path)
+        if (h->tpb == 128) {
+            if (sym) { if (reso) BSG_LAUNCH(128, true, true); else BSG_LAUNCH(128, false, true); }
+            else if (reso) BSG_LAUNCH(128, true, false); else BSG_LAUNCH(128, false, false);
+        } else {
+            if (sym) { if (reso) BSG_LAUNCH(256, true, true); else BSG_LAUNCH(256, false, true); }
+            else if (reso) BSG_LAUNCH(256, true, false); else BSG_LAUNCH(256, false, false);
+        }
     } else {
-        if (reso) step_kernel<R, 256, true><<<grid, 256, h->smem, s>>>(A);
-        else step_kernel<R, 256, false><<<grid, 256, h->smem, s>>>(A);
+        if (h->tpb == 128) { if (reso) BSG_LAUNCH(128, true, false); else BSG_LAUNCH(128, false, false); }
+        else { if (reso) BSG_LAUNCH(256, true, false); else BSG_LAUNCH(256, false, false); }
     }
+#undef BSG_LAUNCH
     h->launches++;
     CK(h, cudaGetLastError());
     if (ar) {

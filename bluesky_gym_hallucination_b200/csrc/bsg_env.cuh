@@ -13,6 +13,7 @@ template <typename R>
 __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &a, EnvShared<R> *es, R *sdist,
                                           int le, int i, int e, int nl, bool valid, bool live, bool skip, double *ev) {
     const int N = A.N, K = N - 1, kind = A.kind;
+    double *sev = es[valid ? le : 0].ev;                               // staged scalar slots (shared memory)
     if (kind == BSG_KIND_RAW) return;                                  // uniform: no barrier skipped
     R *obs = A.out.obs ? (R *)A.out.obs : nullptr;
     int od = kind == BSG_KIND_HORIZONTAL ? 5 * K + 3 : (kind == BSG_KIND_VERTICAL ? 4 + 7 * K : 31);
@@ -56,11 +57,11 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
             } else if (live) {
                 if (kind == BSG_KIND_HORIZONTAL) {
                     R qdr, d;
-                    env_qdrdist<R>(olat, olon, ev[BSG_EV_WPT_LAT], ev[BSG_EV_WPT_LON], qdr, d);
+                    env_qdrdist<R>(olat, olon, sev[BSG_EV_WPT_LAT], sev[BSG_EV_WPT_LON], qdr, d);
                     R drift = bound180<R>(ohdg - qdr), sd, cd;
                     rsincos_deg<R>(drift, sd, cd);
                     es[le].drift = drift; es[le].wdist = d * R(1.852);
-                    ev[BSG_EV_AC_HDG] = (double)a.hdg;
+                    sev[BSG_EV_AC_HDG] = (double)a.hdg;
                     if (obs) { obs[5 * K] = d * R(1.852) / R(150); obs[5 * K + 1] = cd; obs[5 * K + 2] = sd; }
                 } else {
                     R qdr, d;
@@ -68,7 +69,7 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
                     es[le].wdist = R(200) - d * R(1.852);              // runway distance
                     if (obs) {
                         obs[0] = (a.alt - R(1500)) / R(3000); obs[1] = (a.vs - R(0)) / R(5);
-                        obs[2] = (R(ev[BSG_EV_TARGET_ALT]) - R(1500)) / R(3000);
+                        obs[2] = (R(sev[BSG_EV_TARGET_ALT]) - R(1500)) / R(3000);
                         obs[3] = (es[le].wdist - R(100)) / R(200);
                     }
                 }
@@ -89,7 +90,7 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
                 env_qdrdist<R>(olat, olon, a.lat, a.lon, qdr, d);
                 if (d < R(5)) atomicAdd(&es[le].intr, 1);
             } else if (live) {
-                const double wlat = kCenterLat + ev[BSG_EV_WPT_X] / 60, wlon = kCenterLon + ev[BSG_EV_WPT_Y] / (60 * ccl);
+                const double wlat = kCenterLat + sev[BSG_EV_WPT_X] / 60, wlon = kCenterLon + sev[BSG_EV_WPT_Y] / (60 * ccl);
                 R qdr, d;
                 env_qdrdist<R>(olat, olon, wlat, wlon, qdr, d);
                 R drift = bound180<R>(ohdg - qdr), sd, cd;
@@ -142,28 +143,28 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
         int term = 0, trunc = 0;
         if (kind == BSG_KIND_HORIZONTAL) {
             double reach = 0.0;
-            if (es[le].wdist < R(5) && ev[BSG_EV_WPT_REACH] != 1.0) { ev[BSG_EV_WPT_REACH] = 1.0; reach = 1.0; }
+            if (es[le].wdist < R(5) && sev[BSG_EV_WPT_REACH] != 1.0) { sev[BSG_EV_WPT_REACH] = 1.0; reach = 1.0; }
             const double dr = fabs((double)es[le].drift * kD2R);
-            ev[BSG_EV_DRIFT_SUM] += dr; ev[BSG_EV_DRIFT_CNT] += 1.0;
+            sev[BSG_EV_DRIFT_SUM] += dr; sev[BSG_EV_DRIFT_CNT] += 1.0;
             rew = reach + dr * -0.1 + (double)(-intr);
-            term = ev[BSG_EV_WPT_REACH] == 1.0;
+            term = sev[BSG_EV_WPT_REACH] == 1.0;
         } else if (kind == BSG_KIND_VERTICAL) {
             const double rwy = (double)es[le].wdist, alt = (double)a.alt;
             double pen = 0.0;
-            if (rwy > 0 && alt > 0) pen = fabs(ev[BSG_EV_TARGET_ALT] - alt) * (-5.0 / 3000);
-            else if (alt <= 0) { pen = -100; ev[BSG_EV_FINAL_ALT] = -100; term = 1; }
-            else if (rwy <= 0) { pen = alt * (-50.0 / 3000); ev[BSG_EV_FINAL_ALT] = alt; term = 1; }
+            if (rwy > 0 && alt > 0) pen = fabs(sev[BSG_EV_TARGET_ALT] - alt) * (-5.0 / 3000);
+            else if (alt <= 0) { pen = -100; sev[BSG_EV_FINAL_ALT] = -100; term = 1; }
+            else if (rwy <= 0) { pen = alt * (-50.0 / 3000); sev[BSG_EV_FINAL_ALT] = alt; term = 1; }
             rew = pen + (double)(-50 * intr);
         } else {
             const double dr = fabs((double)es[le].drift * kD2R);
-            ev[BSG_EV_DRIFT_SUM] += dr; ev[BSG_EV_DRIFT_CNT] += 1.0;
+            sev[BSG_EV_DRIFT_SUM] += dr; sev[BSG_EV_DRIFT_CNT] += 1.0;
             rew = dr * -0.1 + (double)(-intr);
-            trunc = poly_inside(ev + BSG_EV_POLY, (int)ev[BSG_EV_NVERT], a.lat, a.lon) ? 0 : 1;
+            trunc = poly_inside(ev + BSG_EV_POLY, (int)sev[BSG_EV_NVERT], a.lat, a.lon) ? 0 : 1;
         }
-        ev[BSG_EV_TOTAL_INTR] += (double)intr;
-        ev[BSG_EV_TOTAL_REWARD] += rew;
-        const double steps = ev[BSG_EV_STEPS] + 1.0;
-        ev[BSG_EV_STEPS] = steps;
+        sev[BSG_EV_TOTAL_INTR] += (double)intr;
+        sev[BSG_EV_TOTAL_REWARD] += rew;
+        const double steps = sev[BSG_EV_STEPS] + 1.0;
+        sev[BSG_EV_STEPS] = steps;
         if (A.max_steps > 0 && steps >= (double)A.max_steps) trunc = 1;
         if (A.out.reward) ((R *)A.out.reward)[e] = (R)rew;
         if (A.out.terminated) A.out.terminated[e] = term;
@@ -171,10 +172,14 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
         if (A.out.done) A.out.done[e] = term | trunc;
         if (A.out.info) {
             R *inf = (R *)A.out.info + (size_t)e * 4;
-            inf[0] = (R)ev[BSG_EV_TOTAL_REWARD]; inf[1] = (R)ev[BSG_EV_TOTAL_INTR];
-            inf[2] = kind == BSG_KIND_VERTICAL ? (R)ev[BSG_EV_FINAL_ALT] : (R)(ev[BSG_EV_DRIFT_SUM] / ev[BSG_EV_DRIFT_CNT]);
+            inf[0] = (R)sev[BSG_EV_TOTAL_REWARD]; inf[1] = (R)sev[BSG_EV_TOTAL_INTR];
+            inf[2] = kind == BSG_KIND_VERTICAL ? (R)sev[BSG_EV_FINAL_ALT] : (R)(sev[BSG_EV_DRIFT_SUM] / sev[BSG_EV_DRIFT_CNT]);
             inf[3] = (R)steps;
         }
+    }
+    if (live && i == 0) {                                              // write the staged slots back (fire and forget)
+#pragma unroll
+        for (int s = 0; s < BSG_EV_POLY; s++) ev[s] = sev[s];
     }
 }
 

@@ -18,15 +18,17 @@ template <typename R> struct AcReg {
     R gsn, gse;                                            // derived: tas*cos(hdg), tas*sin(hdg)
 };
 
-template <typename R>
+template <typename R, bool RESO = true>
 __device__ __forceinline__ void ac_load(AcReg<R> &a, const double *pos, const R *st, size_t EN, size_t k) {
     a.lat = pos[k]; a.lon = pos[EN + k];
     a.alt = st[S_ALT * EN + k]; a.hdg = st[S_HDG * EN + k]; a.tas = st[S_TAS * EN + k]; a.vs = st[S_VS * EN + k];
     a.cas = st[S_CAS * EN + k]; a.selspd = st[S_SELSPD * EN + k]; a.selalt = st[S_SELALT * EN + k];
     a.selvs = st[S_SELVS * EN + k]; a.aptrk = st[S_APTRK * EN + k]; a.ax = st[S_AX * EN + k];
-    a.asas_trk = st[S_ASAS_TRK * EN + k]; a.asas_tas = st[S_ASAS_TAS * EN + k]; a.asas_vs = st[S_ASAS_VS * EN + k];
-    a.asas_alt = st[S_ASAS_ALT * EN + k];
-    a.asas_active = (int)st[S_ASAS_ACTIVE * EN + k]; a.phase = (int)st[S_PHASE * EN + k];
+    if constexpr (RESO) {         // the ASAS command slots only matter (and only change) with MVP on
+        a.asas_trk = st[S_ASAS_TRK * EN + k]; a.asas_tas = st[S_ASAS_TAS * EN + k]; a.asas_vs = st[S_ASAS_VS * EN + k];
+        a.asas_alt = st[S_ASAS_ALT * EN + k]; a.asas_active = (int)st[S_ASAS_ACTIVE * EN + k];
+    }
+    a.phase = (int)st[S_PHASE * EN + k];
     if constexpr (sizeof(R) == 4) {
         a.c_alt = st[S_C_ALT * EN + k]; a.c_spd = st[S_C_SPD * EN + k]; a.c_aptas = st[S_C_APTAS * EN + k];
         a.c_ph = st[S_C_PH * EN + k]; a.c_selalt = st[S_C_SELALT * EN + k]; a.c_lo = st[S_C_LO * EN + k];
@@ -38,15 +40,17 @@ __device__ __forceinline__ void ac_load(AcReg<R> &a, const double *pos, const R 
     a.gsn = a.tas * c; a.gse = a.tas * s;
 }
 
-template <typename R>
+template <typename R, bool RESO = true>
 __device__ __forceinline__ void ac_store(const AcReg<R> &a, double *pos, R *st, size_t EN, size_t k) {
     pos[k] = a.lat; pos[EN + k] = a.lon;
     st[S_ALT * EN + k] = a.alt; st[S_HDG * EN + k] = a.hdg; st[S_TAS * EN + k] = a.tas; st[S_VS * EN + k] = a.vs;
     st[S_CAS * EN + k] = a.cas; st[S_SELSPD * EN + k] = a.selspd; st[S_SELALT * EN + k] = a.selalt;
     st[S_SELVS * EN + k] = a.selvs; st[S_APTRK * EN + k] = a.aptrk; st[S_AX * EN + k] = a.ax;
-    st[S_ASAS_TRK * EN + k] = a.asas_trk; st[S_ASAS_TAS * EN + k] = a.asas_tas; st[S_ASAS_VS * EN + k] = a.asas_vs;
-    st[S_ASAS_ALT * EN + k] = a.asas_alt;
-    st[S_ASAS_ACTIVE * EN + k] = R(a.asas_active); st[S_PHASE * EN + k] = R(a.phase);
+    if constexpr (RESO) {
+        st[S_ASAS_TRK * EN + k] = a.asas_trk; st[S_ASAS_TAS * EN + k] = a.asas_tas; st[S_ASAS_VS * EN + k] = a.asas_vs;
+        st[S_ASAS_ALT * EN + k] = a.asas_alt; st[S_ASAS_ACTIVE * EN + k] = R(a.asas_active);
+    }
+    st[S_PHASE * EN + k] = R(a.phase);
     if constexpr (sizeof(R) == 4) {
         st[S_C_ALT * EN + k] = a.c_alt; st[S_C_SPD * EN + k] = a.c_spd; st[S_C_APTAS * EN + k] = a.c_aptas;
         st[S_C_PH * EN + k] = a.c_ph; st[S_C_SELALT * EN + k] = a.c_selalt; st[S_C_LO * EN + k] = a.c_lo;

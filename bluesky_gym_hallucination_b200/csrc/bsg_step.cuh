@@ -33,6 +33,7 @@ template <typename R> struct EnvShared {
     R own_hdg, own_tas, own_alt, own_vs, drift, wdist;
     int anyconf[2];
     int intr;
+    double ev[BSG_EV_POLY];          // the env-level scalar slots, staged once per launch by the agent thread
 };
 
 template <typename R>

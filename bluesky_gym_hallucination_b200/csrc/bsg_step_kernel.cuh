@@ -23,16 +23,34 @@ template <typename R> __host__ __device__ constexpr size_t rec_row_bytes(int N) 
     return (size_t)N * sizeof(typename RecOf<R>::type) + 16;
 }
 
-// RESO (MVP + resumenav) is a compile-time switch: without it the pair loop is a clean, unrollable FP32 body
-template <typename R, int TPB, bool RESO>
+// shared-memory carve-up of one CTA (host and device agree through this one function)
+struct StepSmem { size_t es_off, sd_off, cr_off, total; };
+template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int epb) {
+    StepSmem L;
+    L.es_off = 2 * (size_t)epb * rec_row_bytes<R>(N);                      // [2][epb] record rows
+    L.sd_off = L.es_off + (size_t)epb * sizeof(EnvShared<R>);              // [epb] env scratch
+    L.cr_off = (L.sd_off + (size_t)epb * N * sizeof(R) + 7) & ~(size_t)7;  // [epb*N] hdg / sector distances
+    L.total = L.cr_off + 2 * (size_t)epb * N * sizeof(unsigned long long); // [2][epb*N] conflict bit rows (SYM)
+    return L;
+}
+
+// RESO (MVP + resumenav) is a compile-time switch: without it the pair loop is a clean, unrollable FP32 body.
+// SYM (fp32, N <= 64): every unordered pair is evaluated ONCE -- thread i sweeps the half ring j = i+1 .. i+N/2
+// (the fp32 pair form is exactly symmetric under i <-> j, so the ordered matrix it stands for is bit-identical
+// to the full sweep); a conflict sets bit j of row i and bit i of row j with shared-memory atomics, and after
+// one more barrier each thread finishes its own row (row reductions, MVP, resumenav) from its conflict bit row.
+template <typename R, int TPB, bool RESO, bool SYM>
 __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_kernel(const StepArgs<R> A) {
     using Rec = typename RecOf<R>::type;
+    static_assert(!SYM || sizeof(R) == 4, "the symmetric sweep is the fp32 fast path");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int N = A.N, epb = A.epb;
     const size_t rowb = rec_row_bytes<R>(N);
+    const StepSmem SL = step_smem<R>(N, epb);
     unsigned char *recs = smem_raw;                                        // [2][epb] rows of rowb bytes
-    EnvShared<R> *es = reinterpret_cast<EnvShared<R> *>(recs + 2 * epb * rowb);  // [epb]
-    R *sdist = reinterpret_cast<R *>(es + epb);                            // [epb*N] hdg (resumenav) / sector distances
+    EnvShared<R> *es = reinterpret_cast<EnvShared<R> *>(smem_raw + SL.es_off);   // [epb]
+    R *sdist = reinterpret_cast<R *>(smem_raw + SL.sd_off);                // [epb*N] hdg (resumenav) / sector distances
+    unsigned long long *crow = reinterpret_cast<unsigned long long *>(smem_raw + SL.cr_off);   // [2][epb*N]
 
     const int tid = threadIdx.x;
     const int le = tid / N, i = tid - le * N;
@@ -48,16 +66,19 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     AcReg<R> a = {};
     unsigned long long resorow = 0;
     if (live) {
-        ac_load(a, A.pos, A.st, EN, k);
+        ac_load<R, RESO>(a, A.pos, A.st, EN, k);
         if (reso) resorow = A.reso[k];
     }
     // ------------------------------------------------------------------ action intake (agent = aircraft 0)
+    if (SYM && valid) { crow[le * N + i] = 0ull; crow[(size_t)epb * N + le * N + i] = 0ull; }
     if (live && i == 0) {
         es[le].anyconf[0] = 0; es[le].anyconf[1] = 0; es[le].intr = 0;
         es[le].own_lat = a.lat; es[le].own_lon = a.lon;                    // local origin of the fp32 CD records
+#pragma unroll
+        for (int s2 = 0; s2 < BSG_EV_POLY; s2++) es[le].ev[s2] = ev[s2];   // 14 independent loads, staged in smem
         if (A.actions && !skip) {
             if (A.kind == BSG_KIND_HORIZONTAL) {                           // horizontal_cr_env.py:272-275
-                a.aptrk = R(ev[BSG_EV_AC_HDG]) + A.actions[e] * R(45);
+                a.aptrk = R(es[le].ev[BSG_EV_AC_HDG]) + A.actions[e] * R(45);
             } else if (A.kind == BSG_KIND_VERTICAL) {                      // vertical_cr_env.py:242-256
                 R v = A.actions[e] * R(12.5);
                 a.selalt = v >= R(0) ? R(1000000) : R(0);
@@ -91,6 +112,59 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             R dve = R(0), dvn = R(0);
             bool touched = false, active = false;
             unsigned long long keep = 0;
+            if constexpr (SYM) {
+                unsigned long long *cr_now = crow + (size_t)buf * epb * N + le * N;
+                if (valid) crow[(size_t)(buf ^ 1) * epb * N + le * N + i] = 0ull;     // my row of the next substep
+                if (live && !skip) {                            // phase 1: half ring, flags only
+                    const RecFast me = rb[i];
+                    const int H = nl >> 1;
+#pragma unroll 2
+                    for (int d = 1; d <= H; d++) {
+                        int j = i + d;
+                        j = j >= nl ? j - nl : j;
+                        const RecFast o = rb[j];
+                        PairCore pc;
+                        const bool sw = pair_fast_core(me, o, PF, true, pc);
+                        if (__any_sync(__activemask(), sw)) {
+                            if (sw) {
+                                atomicOr(&cr_now[i], 1ull << j);
+                                atomicOr(&cr_now[j], 1ull << i);
+                                if (RESO) es[le].anyconf[buf] = 1;
+                            }
+                        }
+                    }
+                }
+                __syncthreads();
+                if (live && !skip) {                            // phase 2: my row, conflicting / resolving pairs only
+                    const RecFast me = rb[i];
+                    const unsigned long long cr = cr_now[i];
+                    unsigned long long S = RESO ? (cr | resorow) : cr;
+                    S &= ~(1ull << i);
+                    while (S) {
+                        const int j = __ffsll((long long)S) - 1;
+                        S &= S - 1;
+                        const RecFast o = rb[j];
+                        PairCore pc;
+                        pair_fast_core(me, o, PF, true, pc);
+                        const bool sw = (cr >> j) & 1ull;
+                        if (sw) acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
+                        if constexpr (RESO) {
+                            const float vrx = o.u - me.u, vry = o.v - me.v;
+                            if (sw) {
+                                float d1, d2;
+                                mvp_pair<float>(pc.dx, pc.dy, sqrtf(pc.dist2), pc.tcpa, vrx, vry, PF.rpz_m, d1, d2);
+                                dve = dve - d1; dvn = dvn - d2;
+                                if (A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }
+                            }
+                            const bool past = (pc.dx * vrx + pc.dy * vry) > 0.0f;
+                            const float hdist = sqrtf(pc.dist2);
+                            const bool bouncing = fabsf(a.hdg - sdist[le * N + j]) < 30.0f && hdist < PF.rpz * (float)A.P.fach;
+                            touched = true;
+                            if (!past || hdist < PF.rpz || bouncing) { active = true; keep |= 1ull << j; }
+                        }
+                    }
+                }
+            } else {
             if (live && !skip) {
                 const Rec me = rb[i];
 #pragma unroll 4
@@ -138,9 +212,12 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     }
                 }
             }
+            }
             if constexpr (RESO) {
-                if (acc.nconf > 0) atomicOr(&es[le].anyconf[buf], 1);
-                __syncthreads();
+                if constexpr (!SYM) {
+                    if (acc.nconf > 0) atomicOr(&es[le].anyconf[buf], 1);
+                    __syncthreads();
+                }
                 if (live && !skip) {
                     if (es[le].anyconf[buf]) {                             // MVP.resolve ran for this env
                         R ne = a.gse + dve, nn = a.gsn + dvn;
@@ -165,7 +242,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         }
     }
     if (live && !skip) {
-        ac_store(a, A.pos, A.st, EN, k);
+        ac_store<R, RESO>(a, A.pos, A.st, EN, k);
         if (reso) A.reso[k] = resorow;
     }
     if (valid && i < N) {      // CD row outputs of the last detection (dead slots: zeros / -1)
