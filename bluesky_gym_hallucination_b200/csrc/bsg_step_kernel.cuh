@@ -126,16 +126,20 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                         PairCore pc;
                         const bool sw = pair_fast_core(me, o, PF, true, pc);
                         if (__any_sync(__activemask(), sw)) {
-                            if (sw) {
-                                atomicOr(&cr_now[i], 1ull << j);
-                                atomicOr(&cr_now[j], 1ull << i);
+                            if (sw) {      // native 32-bit shared atomics (a 64-bit OR would be a CAS loop)
+                                unsigned *c32 = reinterpret_cast<unsigned *>(cr_now);
+                                atomicOr(&c32[2 * i + (j >> 5)], 1u << (j & 31));
+                                atomicOr(&c32[2 * j + (i >> 5)], 1u << (i & 31));
                                 if (RESO) es[le].anyconf[buf] = 1;
                             }
                         }
                     }
                 }
-                __syncthreads();
-                if (live && !skip) {                            // phase 2: my row, conflicting / resolving pairs only
+                // phase 2 feeds MVP / resumenav every substep; without MVP its only consumers are the CD row
+                // outputs, and those report the LAST detection of the step (what bs.traf.cd holds afterwards)
+                const bool need_rows = RESO || (s == A.substeps - 1);
+                if (need_rows) __syncthreads();
+                if (need_rows && live && !skip) {               // phase 2: my row, conflicting / resolving pairs only
                     const RecFast me = rb[i];
                     const unsigned long long cr = cr_now[i];
                     unsigned long long S = RESO ? (cr | resorow) : cr;
