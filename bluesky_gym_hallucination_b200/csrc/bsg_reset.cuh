@@ -1,0 +1,219 @@
+// bsg_reset.cuh -- device-side scenario generation shared by the stand-alone reset kernel (bsg_reset) and the
+// fused next-step auto-reset inside step_kernel.  Restates the reset path of the reference env layer:
+//   Horizontal  bluesky_gym/envs/horizontal_cr_env.py:82-148  (bs.traf.cre + creconfs x K + waypoint)
+//   Vertical    bluesky_gym/envs/vertical_cr_env.py:183-200,258-281
+//   Sector      bluesky_gym/envs/sector_cr_env.py:87-217      (polygon growth, density draw, perimeter
+//               waypoints, bounding-box rejection sampling, get_hdg)
+// Same value laws as the reference; the random stream is Philox4x32-10 keyed by (seed) with counter
+// (env, episode, draw index, stream) instead of numpy's global legacy generator (the global
+// draw order cannot be reproduced on a GPU; parity runs inject oracle state through bsg_set_state).
+// Two stages per env: reset_env_level (one thread: env-level draws, polygon into the ev slots) and
+// reset_aircraft (one thread per aircraft).  Both are __noinline__: rare, register-hungry fp64 code that
+// must not inflate the register allocation of the step kernel's hot loop.
+#pragma once
+#include "bsg_step.cuh"
+
+namespace bsg {
+
+struct Philox {
+    uint32_t k0, k1, c0, c1, c2, n;     // n = draw-block counter
+    uint32_t buf[4];
+    int have;
+    __device__ Philox(uint64_t seed, uint32_t env, uint32_t episode, uint32_t stream)
+        : k0((uint32_t)seed), k1((uint32_t)(seed >> 32)), c0(env), c1(episode), c2(stream), n(0), have(0) {}
+    __device__ void refill() {
+        uint32_t a = c0, b = c1, c = c2, d = n++, x = k0, y = k1;
+#pragma unroll
+        for (int r = 0; r < 10; r++) {
+            const uint32_t hi0 = __umulhi(0xD2511F53u, a), lo0 = 0xD2511F53u * a;
+            const uint32_t hi1 = __umulhi(0xCD9E8D57u, c), lo1 = 0xCD9E8D57u * c;
+            a = hi1 ^ b ^ x; b = lo1; c = hi0 ^ d ^ y; d = lo0;
+            x += 0x9E3779B9u; y += 0xBB67AE85u;
+        }
+        buf[0] = a; buf[1] = b; buf[2] = c; buf[3] = d;
+        have = 4;
+    }
+    __device__ uint32_t u32() { if (!have) refill(); return buf[--have]; }
+    __device__ double uniform() {                      // [0, 1) with 53 bits
+        const uint64_t hi = u32(), lo = u32();
+        return (double)(((hi << 32) | lo) >> 11) * (1.0 / 9007199254740992.0);
+    }
+    __device__ int randint(int lo, int hi) { return lo + (int)(uniform() * (double)(hi - lo)); }   // [lo, hi)
+    __device__ double normal(double mu, double sigma) {
+        const double u1 = 1.0 - uniform(), u2 = uniform();
+        return mu + sigma * sqrt(-2.0 * log(u1)) * cos(2.0 * kPi * u2);
+    }
+};
+
+struct AcInit { double lat, lon, alt, hdg, cas, tas, vs, selalt; };
+
+// Traffic.creconfs geometry for one intruder of a target at (lat0, lon0), track trk0, speed gs0
+__device__ void creconfs(double lat0, double lon0, double trk0_deg, double gs0, double dpsi, double cpa_nm, double tlosh,
+                         double &lat, double &lon, double &hdg) {
+    const double trkref = trk0_deg * kD2R, cpa = cpa_nm * kNm, pzr = 5.0 * kNm;
+    const double trk = trkref + dpsi * kD2R;
+    const double gsn = gs0 * cos(trk), gse = gs0 * sin(trk);
+    const double vreln = gs0 * cos(trkref) - gsn, vrele = gs0 * sin(trkref) - gse;
+    const double vrel = sqrt(vreln * vreln + vrele * vrele);
+    const double drelcpa = tlosh * vrel + (cpa > pzr ? 0.0 : sqrt(pzr * pzr - cpa * cpa));
+    const double dist = sqrt(drelcpa * drelcpa + cpa * cpa);
+    const double rd = drelcpa / dist, rx = cpa / dist;
+    const double brn = atan2(-rx * vreln + rd * vrele, rd * vreln + rx * vrele) * kR2D;
+    const double dnm = dist / kNm;
+    const double dx = dnm * sin(brn * kD2R), dy = dnm * cos(brn * kD2R);
+    lat = lat0 + dy / 60.0;
+    lon = pymod((lon0 + dx / fmax(0.01, 60.0 * cos(lat0 * kD2R))) + 180, 360) - 180;
+    hdg = atan2(gse, gsn) * kR2D;
+}
+
+template <typename R>
+__device__ void write_ac(double *pos, R *st, size_t EN, size_t k, const AcInit &a) {
+    pos[k] = a.lat; pos[EN + k] = a.lon;
+    for (int f = 0; f < S_NS; f++) st[(size_t)f * EN + k] = R(0);
+    st[S_ALT * EN + k] = (R)a.alt; st[S_HDG * EN + k] = (R)a.hdg; st[S_TAS * EN + k] = (R)a.tas;
+    st[S_VS * EN + k] = (R)a.vs; st[S_CAS * EN + k] = (R)a.cas; st[S_SELSPD * EN + k] = (R)a.cas;
+    st[S_SELALT * EN + k] = (R)a.selalt; st[S_APTRK * EN + k] = (R)a.hdg; st[S_AX * EN + k] = (R)kKts;
+    for (int f = S_C_ALT; f < S_NS; f++) st[(size_t)f * EN + k] = (R)NAN;
+}
+
+struct ResetEnv {                 // env-level results the per-aircraft stage needs
+    double alt0, target, gs0, minx, miny, maxx, maxy, perim;
+    int nv, nac;
+};
+
+__device__ inline bool inside_poly_ll(const double *poly, int nv, double tx, double ty) {
+    bool inside = false;
+    double x0 = poly[2 * (nv - 1)], y0 = poly[2 * (nv - 1) + 1];
+    bool f0 = y0 >= ty;
+    for (int k = 0; k < nv; k++) {
+        const double x1 = poly[2 * k], y1 = poly[2 * k + 1];
+        const bool f1 = y1 >= ty;
+        if (f0 != f1)
+            if ((((y1 - ty) * (x0 - x1)) >= ((x1 - tx) * (y0 - y1))) == f1) inside = !inside;
+        f0 = f1; x0 = x1; y0 = y1;
+    }
+    return inside;
+}
+
+// stage 1 (one thread per env): clears the scalar ev slots, draws the env-level quantities, grows the polygon
+static __device__ __noinline__ void reset_env_level(int kind, int N, int e, uint64_t seed, uint32_t ep, double *v, ResetEnv *Sp) {
+    ResetEnv S = {};
+    Philox g(seed, (uint32_t)e, ep, 0u);
+    const double ccl = cos(kCenterLat * kD2R);
+    for (int s = 0; s < BSG_EV_POLY; s++) v[s] = 0.0;
+    S.nac = N;
+    if (kind == BSG_KIND_HORIZONTAL) {
+        S.gs0 = vcas2tas(150.0, 0.0);
+        const double d = (double)g.randint(100, 150) / 6371.0, lat1 = 52.0 * kD2R;   // functions.py:24-42, bearing 0
+        v[BSG_EV_WPT_LAT] = asin(sin(lat1) * cos(d) + cos(lat1) * sin(d)) * kR2D;
+        v[BSG_EV_WPT_LON] = 4.0;
+    } else if (kind == BSG_KIND_VERTICAL) {
+        S.alt0 = (double)g.randint(2000, 4000);
+        S.target = S.alt0 + (double)g.randint(-500, 500);
+        S.gs0 = vcas2tas(150.0, S.alt0);
+        v[BSG_EV_TARGET_ALT] = S.target;
+    } else if (kind == BSG_KIND_SECTOR) {
+        const double Rr = sqrt(3750.0 / kPi);
+        double ang[BSG_MAXV];
+        int nv = 3;
+        double area = 0.0;
+        for (int k = 0; k < 3; k++) { const double al = 2 * kPi * g.uniform(); ang[k] = atan2(Rr * sin(al), Rr * cos(al)); }
+        for (;;) {
+            for (int a = 1; a < nv; a++) {            // insertion sort by polar angle (sort_points_clockwise)
+                const double t = ang[a]; int b = a - 1;
+                while (b >= 0 && ang[b] > t) { ang[b + 1] = ang[b]; b--; }
+                ang[b + 1] = t;
+            }
+            area = 0.0;
+            for (int k = 0; k < nv; k++) {
+                const int m = (k + 1) % nv;
+                area += Rr * cos(ang[k]) * Rr * sin(ang[m]) - Rr * sin(ang[k]) * Rr * cos(ang[m]);
+            }
+            area = fabs(area) / 2.0;
+            if (area >= 2400.0 || nv >= BSG_MAXV) break;
+            const double al = 2 * kPi * g.uniform();
+            ang[nv++] = atan2(Rr * sin(al), Rr * cos(al));
+        }
+        S.nv = nv;
+        const double dens = g.normal(0.005, 0.001);
+        const int na = (int)fmax(ceil(dens * area), 5.0);
+        S.nac = na > N ? N : na;
+        S.minx = S.maxx = Rr * cos(ang[0]); S.miny = S.maxy = Rr * sin(ang[0]);
+        S.perim = 0.0;
+        for (int k = 0; k < nv; k++) {
+            const int m = (k + 1) % nv;
+            const double px = Rr * cos(ang[k]), py = Rr * sin(ang[k]);
+            const double dx = Rr * cos(ang[m]) - px, dy = Rr * sin(ang[m]) - py;
+            S.perim += sqrt(dx * dx + dy * dy);
+            S.minx = fmin(S.minx, px); S.maxx = fmax(S.maxx, px);
+            S.miny = fmin(S.miny, py); S.maxy = fmax(S.maxy, py);
+            v[BSG_EV_POLY + 2 * k] = kCenterLat + px / 60;
+            v[BSG_EV_POLY + 2 * k + 1] = kCenterLon + py / (60 * ccl);
+        }
+        v[BSG_EV_NVERT] = nv;
+    }
+    *Sp = S;
+}
+
+// stage 2 (one thread per aircraft slot i of env e): creates the aircraft in the device state
+template <typename R>
+static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e, int i, uint64_t seed, uint32_t ep,
+                                                   const ResetEnv *Sp, double *v, double *pos, R *st,
+                                                   unsigned long long *reso) {
+    const ResetEnv S = *Sp;
+    const size_t EN = (size_t)E * N, k = (size_t)e * N + i;
+    const double ccl = cos(kCenterLat * kD2R);
+    reso[k] = 0ull;
+    AcInit a = {};
+    Philox g(seed, (uint32_t)e, ep, 1u + (uint32_t)i);
+    if (kind == BSG_KIND_HORIZONTAL || kind == BSG_KIND_VERTICAL) {
+        const double alt_own = kind == BSG_KIND_VERTICAL ? S.alt0 : 0.0;
+        if (i == 0) {
+            a.lat = 52.0; a.lon = 4.0; a.alt = alt_own; a.hdg = 0.0; a.cas = 150.0; a.tas = S.gs0; a.selalt = alt_own;
+        } else {
+            const double dpsi = g.randint(45, 315), cpa = g.randint(0, 5);
+            double tlosh, dH = 0.0;
+            if (kind == BSG_KIND_HORIZONTAL) tlosh = g.randint(100, 1000);
+            else {
+                tlosh = g.randint(100, (int)(180000.0 / S.gs0));
+                const double avg_tod = 200000.0 / S.gs0 - 2 * S.target / 12.5;
+                if (tlosh > avg_tod) dH = g.randint((int)(-alt_own + 500), (int)((S.target - alt_own) + 100));
+                else dH = g.randint((int)((S.target - alt_own) - 500), (int)((S.target - alt_own) + 500));
+            }
+            creconfs(52.0, 4.0, 0.0, S.gs0, dpsi, cpa, tlosh, a.lat, a.lon, a.hdg);
+            a.alt = alt_own + dH;
+            a.cas = vtas2cas(S.gs0, a.alt);
+            a.tas = vcas2tas(a.cas, a.alt);
+            a.selalt = a.alt;
+        }
+    } else if (kind == BSG_KIND_SECTOR && i < S.nac) {
+        // perimeter waypoint: the reference sorts its draws and hands waypoint i to aircraft i; any assignment of
+        // i.i.d. draws has the same law, so aircraft i keeps its own draw.  Vertices come back from the ev slots.
+        const double *poly = v + BSG_EV_POLY;
+        double d = g.uniform() * S.perim, wx = 0.0, wy = 0.0;
+        for (int s2 = 0; s2 < S.nv; s2++) {
+            const int m = (s2 + 1) % S.nv;
+            const double x0 = (poly[2 * s2] - kCenterLat) * 60, y0 = (poly[2 * s2 + 1] - kCenterLon) * (60 * ccl);
+            const double x1 = (poly[2 * m] - kCenterLat) * 60, y1 = (poly[2 * m + 1] - kCenterLon) * (60 * ccl);
+            const double len = sqrt((x1 - x0) * (x1 - x0) + (y1 - y0) * (y1 - y0));
+            if (d <= len || s2 == S.nv - 1) { const double fr = fmin(d / len, 1.0); wx = x0 + fr * (x1 - x0); wy = y0 + fr * (y1 - y0); break; }
+            d -= len;
+        }
+        double x, y;
+        do {
+            x = S.minx + g.uniform() * (S.maxx - S.minx);
+            y = S.miny + g.uniform() * (S.maxy - S.miny);
+        } while (!inside_poly_ll(poly, S.nv, kCenterLat + x / 60, kCenterLon + y / (60 * ccl)));
+        a.lat = kCenterLat + x / 60; a.lon = kCenterLon + y / (60 * ccl);
+        const double wlat = (kCenterLat + wx / 60) * kD2R, wlon = (kCenterLon + wy / (60 * ccl)) * kD2R;
+        const double l1 = a.lat * kD2R, o1 = a.lon * kD2R;                        // functions.get_hdg
+        const double hx = sin(wlon - o1) * cos(wlat);
+        const double hy = cos(l1) * sin(wlat) - sin(l1) * cos(wlat) * cos(wlon - o1);
+        a.hdg = pymod(atan2(hx, hy) * kR2D + 360, 360);
+        a.alt = 350.0; a.cas = 150.0; a.tas = vcas2tas(150.0, 350.0); a.selalt = 350.0;
+        if (i == 0) { v[BSG_EV_WPT_X] = wx; v[BSG_EV_WPT_Y] = wy; }
+    }
+    write_ac<R>(pos, st, EN, k, a);
+}
+
+}  // namespace bsg
