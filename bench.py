@@ -6,7 +6,7 @@
 
 Workload at N = 1 (config.workload "c2"): BASELINE.json configs[1] -- HorizontalCREnv-v0, 4096 envs x 20
 aircraft, state-based CD every substep + CPA obs, fp32 fast path, next-step auto-reset on the device.
-A "step" = one fused bsg_step (+ the masked bsg_reset) over the whole batch = 4096 env-steps.
+A "step" = one fused bsg_step launch (auto-reset inside) over the whole batch = 4096 env-steps.
 For N > 1 the envs shard across ranks with no data-path collective (weak scaling: 4096 envs per GPU).
 Other workloads (--workload c3|c4|c5) time the other BASELINE configs; they are not the driver's line.
 One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every field.
@@ -158,7 +158,8 @@ def run_ours(args):
         E = args.envs
     K, W = args.steps, max(args.warmup, 3)
     c = bc.BsgCore(kind, E, N, precision='fp32', device=local, asas_on=bool(asas), reso_on=bool(reso),
-                   reso_off_own=True, max_episode_steps={0: 300, 1: 300, 2: 200}[kind], cd_outputs=True)
+                   reso_off_own=True, max_episode_steps={0: 300, 1: 300, 2: 200}[kind], cd_outputs=True,
+                   fixed_nac=True)    # every aircraft slot live ("N fixed, mask all-active")
     c.reset(seed=1234 + rank)
     c.set_autoreset(True, seed=99 + rank)
     gen = torch.Generator(device=dev); gen.manual_seed(7 + rank)
@@ -171,7 +172,7 @@ def run_ours(args):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
-    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(K)]
+    ev = [[torch.cuda.Event(enable_timing=True) for _ in range(2)] for _ in range(K)]
     lib, h, out, stream = c.lib, c.h, c._out, c._stream()
     import ctypes as C
     if world > 1:
@@ -182,7 +183,7 @@ def run_ours(args):
     for k in range(K):
         flush.zero_()                                   # L2 flush between timed iterations (not timed)
         ev[k][0].record()
-        c.step(acts[k % 16])                            # step kernel + masked reset kernel (auto-reset)
+        c.step(acts[k % 16])                            # ONE launch: step kernel with the fused next-step auto-reset
         ev[k][1].record()
     torch.cuda.synchronize()
     if world > 1:
@@ -190,16 +191,9 @@ def run_ours(args):
     t_wall = time.perf_counter() - t_wall0
     launches = c.launch_count() - l0
     dev_ms = sum(ev[k][0].elapsed_time(ev[k][1]) for k in range(K))
-    # the dominant kernel alone (same stream, CUDA events): step kernel without the reset launch
-    c.set_autoreset(False)
-    kms = []
-    for k in range(min(K, 200)):
-        flush.zero_()
-        ev[k][0].record(); c.step(acts[k % 16]); ev[k][2].record()
-    torch.cuda.synchronize()
-    kms = [ev[k][0].elapsed_time(ev[k][2]) for k in range(min(K, 200))]
-    kernel_ms = float(np.mean(kms))
-    c.set_autoreset(True, seed=99 + rank)
+    # the dominant kernel: with the next-step auto-reset fused, a step IS one step_kernel launch, so its average
+    # launch duration is the event time of the timed region itself (steady-state traffic, resets included)
+    kernel_ms = dev_ms / K
     clocks = sampler.stop() if rank == 0 else None
     tmax = torch.tensor([dev_ms], dtype=torch.float64, device=dev)
     if world > 1:
@@ -227,7 +221,9 @@ def run_ours(args):
             dist.destroy_process_group()
         return
     sub = SUBSTEPS[kind]
-    pairs_per_launch = float(E) * sub * N * (N - 1)
+    nac = c.live_aircraft().astype(np.float64)                  # counted from the device state, not assumed
+    pairs_per_launch = float(sub * np.sum(nac * (nac - 1)))     # ordered CD entries one launch produces
+    assert nac.min() == N and nac.max() == N, (nac.min(), nac.max())
     value = world * E * K / (dev_ms_max * 1e-3)
     achieved = FLOP_PER_PAIR * pairs_per_launch / (kernel_ms * 1e-3) / 1e12
     bytes_per_envstep = 128.0 * N + 4 * c.obs_dim + 4 * c.act_dim + 20
@@ -237,7 +233,8 @@ def run_ours(args):
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload, "description": desc, "envs_per_gpu": E, "aircraft": N,
                    "substeps": sub, "asas": bool(asas), "mvp": bool(reso), "autoreset": "next-step, on device",
-                   "l2": "256 MB buffer zeroed between timed iterations (L2 flush)", "sharding": "envs, no collective"},
+                   "l2": "256 MB buffer zeroed between timed iterations (L2 flush)", "sharding": "envs, no collective",
+                   "live_aircraft_per_env": {"min": int(nac.min()), "mean": float(nac.mean()), "max": int(nac.max())}},
         "pair_evals_per_sec": world * pairs_per_launch * K / (dev_ms_max * 1e-3),
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak32, "unit": "TFLOP/s", "frac": achieved / peak32,
                      "traffic": None, "kernel": "bsg::step_kernel<float>", "kernel_ms": kernel_ms,

@@ -4,7 +4,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(_HERE, 'libbsgcore.so')
+SO_PATH = os.environ.get('BSG_LIB_PATH') or os.path.join(_HERE, 'libbsgcore.so')   # override: A/B of kernel variants (tools/ab.sh)
 
 ABI_VERSION = 1
 KIND_HORIZONTAL, KIND_VERTICAL, KIND_SECTOR, KIND_RAW = 0, 1, 2, 3
@@ -24,7 +24,7 @@ class Config(C.Structure):
     _fields_ = [('struct_size', C.c_int32), ('env_kind', C.c_int32), ('num_envs', C.c_int32), ('max_ac', C.c_int32),
                 ('precision', C.c_int32), ('substeps', C.c_int32), ('asas_on', C.c_int32), ('reso_on', C.c_int32),
                 ('reso_off_own', C.c_int32), ('max_episode_steps', C.c_int32), ('device', C.c_int32),
-                ('reserved', C.c_int32), ('simdt', C.c_double), ('rpz_m', C.c_double), ('hpz_m', C.c_double),
+                ('fixed_nac', C.c_int32), ('simdt', C.c_double), ('rpz_m', C.c_double), ('hpz_m', C.c_double),
                 ('dtlookahead', C.c_double), ('resofach', C.c_double), ('resofacv', C.c_double)]
 
 

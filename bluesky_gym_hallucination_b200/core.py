@@ -43,7 +43,7 @@ class BsgCore:
 
     def __init__(self, kind, num_envs, max_ac, precision='fp32', device=0, substeps=0, simdt=0.0, asas_on=False,
                  reso_on=False, reso_off_own=False, max_episode_steps=0, rpz_m=0.0, hpz_m=0.0, dtlookahead=0.0,
-                 cd_outputs=False):
+                 cd_outputs=False, fixed_nac=False):
         self.lib = L.load()
         if not torch.cuda.is_available():
             raise L.BsgError("libbsgcore needs a CUDA device (no CPU fallback)")
@@ -53,7 +53,7 @@ class BsgCore:
         self.rdtype = torch.float64 if self.fp64 else torch.float32
         self.npdtype = np.float64 if self.fp64 else np.float32
         cfg = L.Config(C.sizeof(L.Config), kind, num_envs, max_ac, L.FP64 if self.fp64 else L.FP32, substeps,
-                       int(asas_on), int(reso_on), int(reso_off_own), max_episode_steps, device, 0, simdt, rpz_m,
+                       int(asas_on), int(reso_on), int(reso_off_own), max_episode_steps, device, int(fixed_nac), simdt, rpz_m,
                        hpz_m, dtlookahead, 0.0, 0.0)
         self.h = C.c_void_p()
         rc = self.lib.bsg_create(C.byref(cfg), C.byref(self.h))
@@ -110,6 +110,12 @@ class BsgCore:
             assert ev.shape == (self.E, L.NE), ev.shape
         torch.cuda.synchronize(self.device)
         L.check(self.lib.bsg_set_state(self.h, _ptr(ac), _ptr(reso), _ptr(nac), _ptr(ev)), self.h)
+
+    def live_aircraft(self):
+        """nac[E]: live aircraft per env, read back from the device."""
+        nac = np.zeros(self.E, np.int32)
+        L.check(self.lib.bsg_get_state(self.h, None, None, _ptr(nac), None), self.h)
+        return nac
 
     def get_state(self):
         ac = np.zeros((self.E, L.NF, self.N)); reso = np.zeros((self.E, self.N), np.uint64)

@@ -15,6 +15,8 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     if (out) A.out = *out; else memset(&A.out, 0, sizeof(A.out));
     const bool ar = h->autoreset && !observe_only && g.env_kind != BSG_KIND_RAW;
     A.skip = (ar && h->autoreset == 1) ? h->done_buf[h->flip] : nullptr;
+    // next-step mode: the reset of the envs that ended in the previous step is fused into this launch
+    A.fuse_reset = (A.skip != nullptr) ? 1 : 0; A.fixed_nac = g.fixed_nac; A.ar_seed = h->ar_seed; A.episode = h->episode;
     int32_t *done_now = nullptr;
     if (ar) { done_now = h->done_buf[h->flip ^ 1]; if (!A.out.done) A.out.done = done_now; }
     const int grid = (g.num_envs + h->epb - 1) / h->epb;
@@ -41,8 +43,10 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
         if (A.out.done != done_now)
             CK(h, cudaMemcpyAsync(done_now, A.out.done, g.num_envs * sizeof(int32_t), cudaMemcpyDeviceToDevice, s));
         h->flip ^= 1;
-        int rc = bsg_reset(h, done_now, h->ar_seed, (void *)s);
-        if (rc != BSG_OK) return rc;
+        if (h->autoreset == 2) {                       // same-step mode: reset now (separate masked launch)
+            int rc = bsg_reset(h, done_now, h->ar_seed, (void *)s);
+            if (rc != BSG_OK) return rc;
+        }
     }
     return BSG_OK;
 }
@@ -55,6 +59,10 @@ int bsg_set_autoreset(bsg_handle *h, int32_t enable, uint64_t seed) {
     for (int b = 0; b < 2; b++) {
         if (!h->done_buf[b]) CK(h, cudaMalloc(&h->done_buf[b], h->cfg.num_envs * sizeof(int32_t)));
         CK(h, cudaMemset(h->done_buf[b], 0, h->cfg.num_envs * sizeof(int32_t)));
+    }
+    if (!h->episode) {
+        CK(h, cudaMalloc(&h->episode, h->cfg.num_envs * sizeof(uint32_t)));
+        CK(h, cudaMemset(h->episode, 0, h->cfg.num_envs * sizeof(uint32_t)));
     }
     h->autoreset = enable == 2 ? 2 : (enable ? 1 : 0);
     h->ar_seed = seed;

@@ -8,7 +8,7 @@ using namespace bsg;
 namespace {
 
 template <typename R>
-__global__ void reset_kernel(int kind, int E, int N, const int32_t *mask, uint64_t seed, uint32_t *episode,
+__global__ void reset_kernel(int kind, int fixed_nac, int E, int N, const int32_t *mask, uint64_t seed, uint32_t *episode,
                              double *pos, R *st, unsigned long long *reso, int *nac, double *ev) {
     const int e = blockIdx.x;
     if (mask && !mask[e]) return;                       // uniform per CTA
@@ -16,7 +16,7 @@ __global__ void reset_kernel(int kind, int E, int N, const int32_t *mask, uint64
     const uint32_t ep = episode[e];
     double *v = ev + (size_t)e * BSG_NE;
     if (threadIdx.x == 0) {
-        reset_env_level(kind, N, e, seed, ep, v, &S);
+        reset_env_level(kind, fixed_nac, N, e, seed, ep, v, &S);
         nac[e] = S.nac;
         episode[e] = ep + 1;
     }
@@ -37,10 +37,10 @@ extern "C" int bsg_reset(bsg_handle *h, const int32_t *mask_dev, uint64_t seed, 
     }
     cudaStream_t s = (cudaStream_t)stream;
     if (g.precision == BSG_FP64)
-        reset_kernel<double><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
+        reset_kernel<double><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.fixed_nac, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
                                                         (double *)h->st, h->reso, h->nac, h->ev);
     else
-        reset_kernel<float><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
+        reset_kernel<float><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.fixed_nac, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
                                                        (float *)h->st, h->reso, h->nac, h->ev);
     h->launches++;
     CK(h, cudaGetLastError());

@@ -48,7 +48,7 @@ struct Philox {
 struct AcInit { double lat, lon, alt, hdg, cas, tas, vs, selalt; };
 
 // Traffic.creconfs geometry for one intruder of a target at (lat0, lon0), track trk0, speed gs0
-__device__ void creconfs(double lat0, double lon0, double trk0_deg, double gs0, double dpsi, double cpa_nm, double tlosh,
+__device__ inline void creconfs(double lat0, double lon0, double trk0_deg, double gs0, double dpsi, double cpa_nm, double tlosh,
                          double &lat, double &lon, double &hdg) {
     const double trkref = trk0_deg * kD2R, cpa = cpa_nm * kNm, pzr = 5.0 * kNm;
     const double trk = trkref + dpsi * kD2R;
@@ -67,7 +67,7 @@ __device__ void creconfs(double lat0, double lon0, double trk0_deg, double gs0, 
 }
 
 template <typename R>
-__device__ void write_ac(double *pos, R *st, size_t EN, size_t k, const AcInit &a) {
+__device__ inline void write_ac(double *pos, R *st, size_t EN, size_t k, const AcInit &a) {
     pos[k] = a.lat; pos[EN + k] = a.lon;
     for (int f = 0; f < S_NS; f++) st[(size_t)f * EN + k] = R(0);
     st[S_ALT * EN + k] = (R)a.alt; st[S_HDG * EN + k] = (R)a.hdg; st[S_TAS * EN + k] = (R)a.tas;
@@ -96,7 +96,7 @@ __device__ inline bool inside_poly_ll(const double *poly, int nv, double tx, dou
 }
 
 // stage 1 (one thread per env): clears the scalar ev slots, draws the env-level quantities, grows the polygon
-static __device__ __noinline__ void reset_env_level(int kind, int N, int e, uint64_t seed, uint32_t ep, double *v, ResetEnv *Sp) {
+static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int N, int e, uint64_t seed, uint32_t ep, double *v, ResetEnv *Sp) {
     ResetEnv S = {};
     Philox g(seed, (uint32_t)e, ep, 0u);
     const double ccl = cos(kCenterLat * kD2R);
@@ -113,42 +113,46 @@ static __device__ __noinline__ void reset_env_level(int kind, int N, int e, uint
         S.gs0 = vcas2tas(150.0, S.alt0);
         v[BSG_EV_TARGET_ALT] = S.target;
     } else if (kind == BSG_KIND_SECTOR) {
+        // random points on the circle of area 3750 NM^2, kept sorted by polar angle, until the polygon they span
+        // covers >= 2400 NM^2 (sector_cr_env.py:141-160, functions.py:44-114).  Vertex coordinates are computed
+        // once per draw and carried through the insertion; the shoelace sum then needs no trigonometry.
         const double Rr = sqrt(3750.0 / kPi);
-        double ang[BSG_MAXV];
-        int nv = 3;
+        double ang[BSG_MAXV], px[BSG_MAXV], py[BSG_MAXV];
+        int nv = 0;
         double area = 0.0;
-        for (int k = 0; k < 3; k++) { const double al = 2 * kPi * g.uniform(); ang[k] = atan2(Rr * sin(al), Rr * cos(al)); }
         for (;;) {
-            for (int a = 1; a < nv; a++) {            // insertion sort by polar angle (sort_points_clockwise)
-                const double t = ang[a]; int b = a - 1;
-                while (b >= 0 && ang[b] > t) { ang[b + 1] = ang[b]; b--; }
-                ang[b + 1] = t;
-            }
+            const double al = 2 * kPi * g.uniform();
+            double sa, ca;
+            sincos(al, &sa, &ca);
+            const double t = al > kPi ? al - 2 * kPi : al;         // atan2(sin, cos): polar angle in (-pi, pi]
+            int b = nv - 1;
+            while (b >= 0 && ang[b] > t) { ang[b + 1] = ang[b]; px[b + 1] = px[b]; py[b + 1] = py[b]; b--; }
+            ang[b + 1] = t; px[b + 1] = Rr * ca; py[b + 1] = Rr * sa;
+            nv++;
+            if (nv < 3) continue;
             area = 0.0;
             for (int k = 0; k < nv; k++) {
-                const int m = (k + 1) % nv;
-                area += Rr * cos(ang[k]) * Rr * sin(ang[m]) - Rr * sin(ang[k]) * Rr * cos(ang[m]);
+                const int m = k + 1 == nv ? 0 : k + 1;
+                area += px[k] * py[m] - py[k] * px[m];
             }
             area = fabs(area) / 2.0;
             if (area >= 2400.0 || nv >= BSG_MAXV) break;
-            const double al = 2 * kPi * g.uniform();
-            ang[nv++] = atan2(Rr * sin(al), Rr * cos(al));
         }
         S.nv = nv;
+        S.gs0 = vcas2tas(150.0, 350.0);
         const double dens = g.normal(0.005, 0.001);
         const int na = (int)fmax(ceil(dens * area), 5.0);
-        S.nac = na > N ? N : na;
-        S.minx = S.maxx = Rr * cos(ang[0]); S.miny = S.maxy = Rr * sin(ang[0]);
+        S.nac = (fixed_nac || na > N) ? N : na;
+        S.minx = S.maxx = px[0]; S.miny = S.maxy = py[0];
         S.perim = 0.0;
         for (int k = 0; k < nv; k++) {
-            const int m = (k + 1) % nv;
-            const double px = Rr * cos(ang[k]), py = Rr * sin(ang[k]);
-            const double dx = Rr * cos(ang[m]) - px, dy = Rr * sin(ang[m]) - py;
+            const int m = k + 1 == nv ? 0 : k + 1;
+            const double dx = px[m] - px[k], dy = py[m] - py[k];
             S.perim += sqrt(dx * dx + dy * dy);
-            S.minx = fmin(S.minx, px); S.maxx = fmax(S.maxx, px);
-            S.miny = fmin(S.miny, py); S.maxy = fmax(S.maxy, py);
-            v[BSG_EV_POLY + 2 * k] = kCenterLat + px / 60;
-            v[BSG_EV_POLY + 2 * k + 1] = kCenterLon + py / (60 * ccl);
+            S.minx = fmin(S.minx, px[k]); S.maxx = fmax(S.maxx, px[k]);
+            S.miny = fmin(S.miny, py[k]); S.maxy = fmax(S.maxy, py[k]);
+            v[BSG_EV_POLY + 2 * k] = kCenterLat + px[k] / 60;
+            v[BSG_EV_POLY + 2 * k + 1] = kCenterLon + py[k] / (60 * ccl);
         }
         v[BSG_EV_NVERT] = nv;
     }
@@ -210,7 +214,7 @@ static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e
         const double hx = sin(wlon - o1) * cos(wlat);
         const double hy = cos(l1) * sin(wlat) - sin(l1) * cos(wlat) * cos(wlon - o1);
         a.hdg = pymod(atan2(hx, hy) * kR2D + 360, 360);
-        a.alt = 350.0; a.cas = 150.0; a.tas = vcas2tas(150.0, 350.0); a.selalt = 350.0;
+        a.alt = 350.0; a.cas = 150.0; a.tas = S.gs0; a.selalt = 350.0;
         if (i == 0) { v[BSG_EV_WPT_X] = wx; v[BSG_EV_WPT_Y] = wy; }
     }
     write_ac<R>(pos, st, EN, k, a);

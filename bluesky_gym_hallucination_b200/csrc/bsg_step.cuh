@@ -18,9 +18,12 @@ template <typename R> struct StepArgs {
     int kind, E, N, substeps, asas_on, reso_on, reso_off_own, max_steps, epb, observe_only;
     R dt;
     CdParams P;
-    double *pos; R *st; unsigned long long *reso; const int *nac; double *ev;
+    double *pos; R *st; unsigned long long *reso; int *nac; double *ev;
     const R *actions;
     const int *skip;      // envs reset after the previous step (auto-reset): observe only, reward 0
+    // fused next-step auto-reset: the envs flagged in `skip` draw their new episode at the head of this launch
+    // (bsg_reset.cuh stages) instead of in a separate reset launch; `nac` is written by that stage
+    int fuse_reset, fixed_nac; unsigned long long ar_seed; unsigned int *episode;
     bsg_step_out out;
 };
 

@@ -2,6 +2,7 @@
 #pragma once
 #include "bsg_step.cuh"
 #include "bsg_env.cuh"
+#include "bsg_reset.cuh"
 
 namespace bsg {
 
@@ -34,6 +35,28 @@ template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int e
     return L;
 }
 
+// Next-step auto-reset, fused: an env that ended in the previous step draws its new episode at the head of this
+// launch (rare: 1-3 % of the envs per step), so a step is ONE launch.  Called by every thread of a CTA that holds
+// such an env; kept out of line so the step kernel's register allocation does not see it.  The ResetEnv scratch
+// aliases the (not yet used) record rows.
+template <typename R>
+static __device__ __noinline__ void fused_reset(int kind, int fixed_nac, int E, int N, unsigned long long seed, unsigned int *episode,
+                                                double *ev, int *nac, double *pos, R *st, unsigned long long *reso,
+                                                unsigned char *smem_raw, bool skip, bool valid, int le, int i, int e) {
+    // (scalars by value: taking the address of the kernel's parameter struct would copy it to local memory)
+    ResetEnv *rs = reinterpret_cast<ResetEnv *>(smem_raw);
+    double *evr = ev + (size_t)(valid ? e : 0) * BSG_NE;
+    const unsigned int ep = skip ? episode[e] : 0u;
+    if (skip && i == 0) {
+        reset_env_level(kind, fixed_nac, N, e, seed, ep, evr, &rs[le]);
+        nac[e] = rs[le].nac;
+    }
+    __syncthreads();
+    if (skip) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &rs[le], evr, pos, st, reso);
+    __syncthreads();
+    if (skip && i == 0) episode[e] = ep + 1;
+}
+
 // RESO (MVP + resumenav) is a compile-time switch: without it the pair loop is a clean, unrollable FP32 body.
 // SYM (fp32, N <= 64): every unordered pair is evaluated ONCE -- thread i sweeps the half ring j = i+1 .. i+N/2
 // (the fp32 pair form is exactly symmetric under i <-> j, so the ordered matrix it stands for is bit-identical
@@ -56,9 +79,10 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     const int le = tid / N, i = tid - le * N;
     const int e = blockIdx.x * epb + le;
     const bool valid = le < epb && e < A.E;
+    const bool skip = valid && A.skip && A.skip[e];                       // fresh episode: no action, no integration
+    if (A.fuse_reset && __syncthreads_or(skip)) fused_reset<R>(A.kind, A.fixed_nac, A.E, A.N, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso, smem_raw, skip, valid, le, i, e);   // rare
     const int nl = valid ? A.nac[e] : 0;
     const bool live = valid && i < nl;
-    const bool skip = valid && A.skip && A.skip[e];                       // fresh episode: no action, no integration
     const size_t EN = (size_t)A.E * N, k = (size_t)(valid ? e : 0) * N + i;
     double *ev = A.ev + (size_t)(valid ? e : 0) * BSG_NE;
     constexpr bool reso = RESO;

@@ -64,7 +64,8 @@ typedef struct bsg_config {
     int32_t reso_off_own;     /* agent does not resolve (BlueSky "RESOOFF KL001") */
     int32_t max_episode_steps;/* TimeLimit: truncate when reached; 0 = never */
     int32_t device;           /* CUDA device ordinal */
-    int32_t reserved;
+    int32_t fixed_nac;        /* Sector reset: 1 = every env gets exactly max_ac aircraft (the synthetic scale-up
+                                 configs, SURVEY 8d C3 "N fixed"); 0 = the reference's density law (sector_cr_env.py:98-100) */
     double simdt;             /* 0 = the reference's DT for env_kind (5/1/1 s) */
     double rpz_m, hpz_m;      /* protected zone; 0 = 5 NM / 1000 ft */
     double dtlookahead;       /* 0 = 300 s */
