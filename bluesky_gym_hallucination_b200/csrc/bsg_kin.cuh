@@ -16,6 +16,7 @@ template <typename R> struct AcReg {
     int asas_active, phase;
     R c_alt, c_spd, c_aptas, c_ph, c_selalt, c_lo, c_hi;   // fast-path caches
     R gsn, gse;                                            // derived: tas*cos(hdg), tas*sin(hdg)
+    R sa, ca;                                              // fast path: sin, cos of lat/2 (CD record + cos(lat))
 };
 
 template <typename R, bool RESO = true>
@@ -36,7 +37,7 @@ __device__ __forceinline__ void ac_load(AcReg<R> &a, const double *pos, const R 
     }
     R s, c;
     if constexpr (sizeof(R) == 8) { s = sin(a.hdg * kD2R); c = cos(a.hdg * kD2R); }
-    else sincospif(a.hdg * (1.0f / 180.0f), &s, &c);
+    else { sincospif(a.hdg * (1.0f / 180.0f), &s, &c); sincospif((float)(a.lat * (1.0 / 360.0)), &a.sa, &a.ca); }
     a.gsn = a.tas * c; a.gse = a.tas * s;
 }
 
@@ -153,7 +154,8 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     float alt_old = a.alt;
     a.alt = swalt ? fmaf(vs, dt, a.alt) : allow_h;
     a.lat = a.lat + (double)(dt * gsn) * (kR2D / kRe);
-    float coslat = cospif((float)(a.lat * (1.0 / 180.0)));
+    sincospif((float)(a.lat * (1.0 / 360.0)), &a.sa, &a.ca);   // half-angle pair: next CD record, and cos(lat) here
+    float coslat = fmaf(a.ca, a.ca, -(a.sa * a.sa));
     a.lon = a.lon + (double)(dt * gse * rcp_approx(coslat)) * (kR2D / kRe);
     if (want_cas) a.cas = (float)vtas2cas((double)tas, (double)alt_old);
     a.tas = tas; a.hdg = hdg; a.vs = vs; a.gsn = gsn; a.gse = gse;

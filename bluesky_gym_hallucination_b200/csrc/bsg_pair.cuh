@@ -124,6 +124,36 @@ __device__ __forceinline__ void mvp_pair(R dx, R dy, R dist, R tcpa, R vrelx, R 
     }
 }
 
+// fp32 fast form of mvp_pair: same algebra, no inverse trigonometry and no IEEE divide.
+//   cos(asin a - asin b) = sqrt((1 - a^2)(1 - b^2)) + a b      (a = rpz_m/dist, b = |dcpa_h|/dist, both in [0, 1))
+// with 1 - a^2 = (dist^2 - rpz_m^2)/dist^2 taken from the squared quantities (no cancellation beyond the inputs').
+// The branch tests compare squares, so they do not depend on the rounding of the MUFU approximations.
+__device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+
+__device__ __forceinline__ void mvp_pair_fast(float dx, float dy, float dist2, float tcpa, float vrelx, float vrely,
+                                              float rpz_m, float &dv1, float &dv2) {
+    float dcx = fmaf(vrelx, tcpa, dx), dcy = fmaf(vrely, tcpa, dy);
+    float dabsH2 = fmaf(dcx, dcx, dcy * dcy);
+    float dabsH = sqrt_approx(dabsH2);
+    const float iH = rpz_m - dabsH;
+    const float idist = rsqrt_approx(dist2);
+    if (dabsH2 <= 100.0f) {
+        dabsH = 10.0f; dabsH2 = 100.0f;
+        dcx = dy * idist * 10.0f;
+        dcy = -dx * idist * 10.0f;
+    }
+    const float iden = rcp_approx(fabsf(tcpa) * dabsH);
+    float f = iH;
+    const float r2 = rpz_m * rpz_m;
+    if (r2 < dist2 && dabsH2 < dist2) {
+        const float id2 = idist * idist;
+        const float erratum = fmaf(rpz_m * idist, dabsH * idist, sqrt_approx((dist2 - r2) * (dist2 - dabsH2)) * id2);
+        f = fmaf(rpz_m, rcp_approx(erratum), -dabsH);
+    }
+    f *= iden;
+    dv1 = f * dcx; dv2 = f * dcy;
+}
+
 // per-row running outputs of the sweep (branch-free: the pair loop stays software-pipelined).
 // best = tCPA of the soonest conflict so far (+inf while there is none; ties keep the lower j).
 template <typename R> struct RowAcc {

@@ -47,7 +47,7 @@ __device__ __forceinline__ void make_rec(const AcReg<R> &a, double lat0, double 
         r.x = (float)((a.lon - lon0) * (kD2R * kRe));
         r.y = (float)((a.lat - lat0) * (kD2R * kRe));
         r.alt = a.alt; r.u = a.gse; r.v = a.gsn; r.vs = a.vs;
-        sincospif((float)(a.lat * (1.0 / 360.0)), &r.sa, &r.ca);
+        r.sa = a.sa; r.ca = a.ca;
     }
 }
 

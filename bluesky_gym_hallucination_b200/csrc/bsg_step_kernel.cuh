@@ -20,8 +20,14 @@ template <typename R, int TPB> struct StepBounds {
 };
 // per-env row of CD records in shared memory: N records + 16 B so that the rows of the envs sharing a
 // warp start in different banks (N * 32 B is a multiple of 128 B for N = 20: 2-way LDS.128 conflicts)
+// fp32 rows hold N + N/2 records: the symmetric sweep keeps a copy of the first half ring behind the last live
+// slot (j = i + d never wraps) and stores the records as two float4 arrays [N + N/2] (x,y,alt,u | v,vs,ca,sa)
+__host__ __device__ constexpr int sym_row_recs(int N) { return N + N / 2; }
 template <typename R> __host__ __device__ constexpr size_t rec_row_bytes(int N) {
-    return (size_t)N * sizeof(typename RecOf<R>::type) + 16;
+    return (size_t)(sizeof(R) == 4 ? sym_row_recs(N) : N) * sizeof(typename RecOf<R>::type) + 16;
+}
+__device__ __forceinline__ RecFast rec_from(const float4 &a, const float4 &b) {
+    RecFast r; r.x = a.x; r.y = a.y; r.alt = a.z; r.u = a.w; r.v = b.x; r.vs = b.y; r.ca = b.z; r.sa = b.w; return r;
 }
 
 // shared-memory carve-up of one CTA (host and device agree through this one function)
@@ -127,7 +133,14 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         if (A.asas_on) {
             Rec *rb = reinterpret_cast<Rec *>(recs + ((size_t)buf * epb + le) * rowb);
             if (live && !skip) {
-                make_rec<R>(a, lat0, lon0, rb[i]);
+                if constexpr (SYM) {                  // SoA halves (conflict-free LDS.128) + ring copy behind slot nl
+                    RecFast r;
+                    make_rec<R>(a, lat0, lon0, r);
+                    float4 *wA = reinterpret_cast<float4 *>(rb), *wB = wA + sym_row_recs(N);
+                    const float4 ha = make_float4(r.x, r.y, r.alt, r.u), hb = make_float4(r.v, r.vs, r.ca, r.sa);
+                    wA[i] = ha; wB[i] = hb;
+                    if (i < (nl >> 1)) { wA[nl + i] = ha; wB[nl + i] = hb; }
+                } else make_rec<R>(a, lat0, lon0, rb[i]);
                 if (reso) sdist[le * N + i] = a.hdg;
             }
             __syncthreads();
@@ -139,56 +152,64 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             if constexpr (SYM) {
                 unsigned long long *cr_now = crow + (size_t)buf * epb * N + le * N;
                 if (valid) crow[(size_t)(buf ^ 1) * epb * N + le * N + i] = 0ull;     // my row of the next substep
+                const float4 *rA = reinterpret_cast<const float4 *>(rb), *rB = rA + sym_row_recs(N);
+                RecFast me;
                 if (live && !skip) {                            // phase 1: half ring, flags only
-                    const RecFast me = rb[i];
+                    me = rec_from(rA[i], rB[i]);
                     const int H = nl >> 1;
+                    const float4 *pA = rA + i, *pB = rB + i;    // ring copy behind slot nl: j = i + d needs no wrap
 #pragma unroll 2
                     for (int d = 1; d <= H; d++) {
-                        int j = i + d;
-                        j = j >= nl ? j - nl : j;
-                        const RecFast o = rb[j];
+                        const RecFast o = rec_from(pA[d], pB[d]);
                         PairCore pc;
-                        const bool sw = pair_fast_core(me, o, PF, true, pc);
-                        if (__any_sync(__activemask(), sw)) {
-                            if (sw) {      // native 32-bit shared atomics (a 64-bit OR would be a CAS loop)
-                                unsigned *c32 = reinterpret_cast<unsigned *>(cr_now);
-                                atomicOr(&c32[2 * i + (j >> 5)], 1u << (j & 31));
-                                atomicOr(&c32[2 * j + (i >> 5)], 1u << (i & 31));
-                                if (RESO) es[le].anyconf[buf] = 1;
-                            }
+                        if (pair_fast_core(me, o, PF, true, pc)) {   // rare: native 32-bit shared atomics
+                            int j = i + d;
+                            j = j >= nl ? j - nl : j;
+                            unsigned *c32 = reinterpret_cast<unsigned *>(cr_now);
+                            atomicOr(&c32[2 * i + (j >> 5)], 1u << (j & 31));
+                            atomicOr(&c32[2 * j + (i >> 5)], 1u << (i & 31));
+                            if (RESO) es[le].anyconf[buf] = 1;
                         }
                     }
                 }
-                // phase 2 feeds MVP / resumenav every substep; without MVP its only consumers are the CD row
-                // outputs, and those report the LAST detection of the step (what bs.traf.cd holds afterwards)
-                const bool need_rows = RESO || (s == A.substeps - 1);
+                // phase 2 feeds MVP / resumenav every substep; the CD row outputs report the LAST detection of the
+                // step (what bs.traf.cd holds afterwards), so the row reductions run on the last substep only
+                const bool want_acc = (s == A.substeps - 1);
+                const bool need_rows = RESO || want_acc;
                 if (need_rows) __syncthreads();
                 if (need_rows && live && !skip) {               // phase 2: my row, conflicting / resolving pairs only
-                    const RecFast me = rb[i];
                     const unsigned long long cr = cr_now[i];
                     unsigned long long S = RESO ? (cr | resorow) : cr;
                     S &= ~(1ull << i);
+                    const float R2f = PF.rpz * PF.rpz, R2b = R2f * (float)(A.P.fach * A.P.fach);
                     while (S) {
                         const int j = __ffsll((long long)S) - 1;
                         S &= S - 1;
-                        const RecFast o = rb[j];
-                        PairCore pc;
-                        pair_fast_core(me, o, PF, true, pc);
+                        const RecFast o = rec_from(rA[j], rB[j]);
                         const bool sw = (cr >> j) & 1ull;
-                        if (sw) acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
+                        if (sw && want_acc) {
+                            PairCore pc;
+                            pair_fast_core(me, o, PF, true, pc);
+                            acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
+                        }
                         if constexpr (RESO) {
+                            // the same expressions as pair_fast_core (bit-identical dx, dy, dist2, tcpa)
+                            const float dy = o.y - me.y;
+                            const float dx = (o.x - me.x) * fmaf(me.ca, o.ca, -(me.sa * o.sa));
+                            const float dist2 = fmaf(dx, dx, dy * dy);
                             const float vrx = o.u - me.u, vry = o.v - me.v;
+                            const float dot = fmaf(vrx, dx, vry * dy);
                             if (sw) {
+                                const float tcpa = -dot * rcp_approx(fmaxf(fmaf(vrx, vrx, vry * vry), 1e-6f));
                                 float d1, d2;
-                                mvp_pair<float>(pc.dx, pc.dy, sqrtf(pc.dist2), pc.tcpa, vrx, vry, PF.rpz_m, d1, d2);
+                                mvp_pair_fast(dx, dy, dist2, tcpa, vrx, vry, PF.rpz_m, d1, d2);
                                 dve = dve - d1; dvn = dvn - d2;
                                 if (A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }
                             }
-                            const bool past = (pc.dx * vrx + pc.dy * vry) > 0.0f;
-                            const float hdist = sqrtf(pc.dist2);
-                            const bool bouncing = fabsf(a.hdg - sdist[le * N + j]) < 30.0f && hdist < PF.rpz * (float)A.P.fach;
+                            const bool past = dot > 0.0f;                     // resumenav (squared distance tests)
+                            const bool bouncing = fabsf(a.hdg - sdist[le * N + j]) < 30.0f && dist2 < R2b;
                             touched = true;
-                            if (!past || hdist < PF.rpz || bouncing) { active = true; keep |= 1ull << j; }
+                            if (!past || dist2 < R2f || bouncing) { active = true; keep |= 1ull << j; }
                         }
                     }
                 }
