@@ -103,10 +103,33 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
                  : g.env_kind == BSG_KIND_SECTOR ? 31 : 0;
     h->act_dim = g.env_kind == BSG_KIND_SECTOR ? 2 : (g.env_kind == BSG_KIND_RAW ? 0 : 1);
     // CTA size: the one of {128, 256} that wastes fewer lanes on whole envs (ties -> 128: better balance)
+    {   // ISA conversions of the fixed creation speeds (host fp64 replica of vcas2tas / vtas2cas)
+        auto atmos = [](double hh, double &p, double &rho) {
+            const double T = std::fmax(288.15 - 0.0065 * hh, 216.65);
+            rho = 1.225 * std::pow(T / 288.15, 4.256848030018761) * std::exp(-std::fmax(0.0, hh - 11000.0) / 6341.552161);
+            p = rho * kRgas * T;
+        };
+        auto cas2tas = [&](double cas, double hh) {
+            double p, rho; atmos(hh, p, rho);
+            const double q = kP0 * (std::pow(1.0 + kRho0 * cas * cas / (7.0 * kP0), 3.5) - 1.0);
+            return std::sqrt(7.0 * p / rho * (std::pow(1.0 + q / p, 2.0 / 7.0) - 1.0));
+        };
+        auto tas2cas = [&](double tas, double hh) {
+            double p, rho; atmos(hh, p, rho);
+            const double q = p * (std::pow(1.0 + rho * tas * tas / (7.0 * p), 3.5) - 1.0);
+            return std::sqrt(7.0 * kP0 / kRho0 * (std::pow(q / kP0 + 1.0, 2.0 / 7.0) - 1.0));
+        };
+        h->rc.tas_h = cas2tas(150.0, 0.0);
+        h->rc.cas_h = tas2cas(h->rc.tas_h, 0.0);
+        h->rc.tas_s = cas2tas(150.0, 350.0);
+        h->rc.coslat_hv = std::cos(52.0 * kD2R);
+        h->rc.ccl = std::cos(kCenterLat * kD2R);
+    }
     h->tpb = 128;
     if (N > 128 || (256 / N) * N * 128 > (128 / N) * N * 256) h->tpb = 256;
-    if (const char *f = getenv("BSG_FORCE_TPB")) { int t = atoi(f); if ((t == 128 || t == 256) && t >= N) h->tpb = t; }
+    if (const char *f = getenv("BSG_FORCE_TPB")) { int t = atoi(f); if ((t == 128 || t == 256 || (t == 320 && g.precision == BSG_FP32)) && t >= N) h->tpb = t; }
     h->epb = h->tpb / N;
+    if (const char *f = getenv("BSG_FORCE_EPB")) { int t = atoi(f); if (t >= 1 && t * N <= h->tpb) h->epb = t; }
     const size_t rs = rsize(h);
     h->smem = g.precision == BSG_FP64 ? step_smem<double>(N, h->epb).total : step_smem<float>(N, h->epb).total;
     CK(h, cudaSetDevice(g.device));
@@ -149,3 +172,9 @@ int bsg_destroy(bsg_handle *h) {
 }  // extern "C"
 
 #include "bsg_api_step.inl"
+
+#ifdef BSG_TRACE
+extern "C" int bsg_debug_trace(unsigned long long *out_host, int n_words) {
+    return cudaMemcpyFromSymbol(out_host, bsg::g_trace, (size_t)n_words * sizeof(unsigned long long)) == cudaSuccess ? 0 : -1;
+}
+#endif

@@ -16,21 +16,24 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     const bool ar = h->autoreset && !observe_only && g.env_kind != BSG_KIND_RAW;
     A.skip = (ar && h->autoreset == 1) ? h->done_buf[h->flip] : nullptr;
     // next-step mode: the reset of the envs that ended in the previous step is fused into this launch
-    A.fuse_reset = (A.skip != nullptr) ? 1 : 0; A.fixed_nac = g.fixed_nac; A.ar_seed = h->ar_seed; A.episode = h->episode;
+    A.fuse_reset = (A.skip != nullptr) ? 1 : 0; A.fixed_nac = g.fixed_nac; A.RC = h->rc; A.ar_seed = h->ar_seed; A.episode = h->episode;
     int32_t *done_now = nullptr;
     if (ar) { done_now = h->done_buf[h->flip ^ 1]; if (!A.out.done) A.out.done = done_now; }
     const int grid = (g.num_envs + h->epb - 1) / h->epb;
     const bool reso = g.reso_on && g.asas_on;
-    const dim3 gd(grid), bd(h->tpb);
+    const dim3 gd(grid), bd(((h->epb * g.max_ac + 31) / 32) * 32);      // whole warps covering the CTA's envs
 #define BSG_LAUNCH(TPB, RESO, SYM) step_kernel<R, TPB, RESO, SYM><<<gd, bd, h->smem, s>>>(A)
     if constexpr (sizeof(R) == 4) {
         const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM");          // symmetric half-ring sweep (fp32 fast path)
         if (h->tpb == 128) {
             if (sym) { if (reso) BSG_LAUNCH(128, true, true); else BSG_LAUNCH(128, false, true); }
             else if (reso) BSG_LAUNCH(128, true, false); else BSG_LAUNCH(128, false, false);
-        } else {
+        } else if (h->tpb == 256) {
             if (sym) { if (reso) BSG_LAUNCH(256, true, true); else BSG_LAUNCH(256, false, true); }
             else if (reso) BSG_LAUNCH(256, true, false); else BSG_LAUNCH(256, false, false);
+        } else {
+            if (sym) { if (reso) BSG_LAUNCH(320, true, true); else BSG_LAUNCH(320, false, true); }
+            else if (reso) BSG_LAUNCH(320, true, false); else BSG_LAUNCH(320, false, false);
         }
     } else {
         if (h->tpb == 128) { if (reso) BSG_LAUNCH(128, true, false); else BSG_LAUNCH(128, false, false); }

@@ -38,6 +38,10 @@ enum StField { S_ALT, S_HDG, S_TAS, S_VS, S_CAS, S_SELSPD, S_SELALT, S_SELVS, S_
                // fast-path caches of pure functions (key -> value); unused by the parity path
                S_C_ALT, S_C_SPD, S_C_APTAS, S_C_PH, S_C_SELALT, S_C_LO, S_C_HI, S_NS };
 
+// launch constants of the reset path: the ISA conversions of the fixed creation speeds, evaluated once on the
+// host at bsg_create (six pow() per aircraft would otherwise sit on the critical path of a fused reset)
+struct ResetConst { double tas_h, cas_h, tas_s, coslat_hv, ccl; };   // vcas2tas(150,0), vtas2cas(tas_h,0), vcas2tas(150,350), cos(52 deg), cos(sector centre lat)
+
 template <typename R> __device__ __forceinline__ R rsgn(R x) { return R((x > R(0)) - (x < R(0))); }
 
 // numpy/Python float modulo (result takes the sign of the divisor)

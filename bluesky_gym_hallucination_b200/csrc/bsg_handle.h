@@ -4,6 +4,7 @@
 #include <string>
 #include <cstdint>
 #include "../../include/bsgcore.h"
+#include "bsg_dev.cuh"
 
 struct bsg_handle {
     bsg_config cfg;
@@ -22,6 +23,7 @@ struct bsg_handle {
     uint32_t *episode = nullptr;
     int autoreset = 0, flip = 0;      // next-step auto-reset: done_buf[flip] = envs reset after the last step
     uint64_t ar_seed = 0;
+    bsg::ResetConst rc = {};          // host-evaluated ISA constants of the reset path
     int32_t *done_buf[2] = { nullptr, nullptr };      // [E] reset counter (Philox counter word)
     int64_t launches = 0;
     std::string err;

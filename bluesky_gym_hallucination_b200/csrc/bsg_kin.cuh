@@ -20,7 +20,7 @@ template <typename R> struct AcReg {
 };
 
 template <typename R, bool RESO = true>
-__device__ __forceinline__ void ac_load(AcReg<R> &a, const double *pos, const R *st, size_t EN, size_t k) {
+__device__ __forceinline__ void ac_load_raw(AcReg<R> &a, const double *pos, const R *st, size_t EN, size_t k) {
     a.lat = pos[k]; a.lon = pos[EN + k];
     a.alt = st[S_ALT * EN + k]; a.hdg = st[S_HDG * EN + k]; a.tas = st[S_TAS * EN + k]; a.vs = st[S_VS * EN + k];
     a.cas = st[S_CAS * EN + k]; a.selspd = st[S_SELSPD * EN + k]; a.selalt = st[S_SELALT * EN + k];
@@ -35,6 +35,9 @@ __device__ __forceinline__ void ac_load(AcReg<R> &a, const double *pos, const R 
         a.c_ph = st[S_C_PH * EN + k]; a.c_selalt = st[S_C_SELALT * EN + k]; a.c_lo = st[S_C_LO * EN + k];
         a.c_hi = st[S_C_HI * EN + k];
     }
+}
+// derived quantities, evaluated once the loads have landed
+template <typename R> __device__ __forceinline__ void ac_derive(AcReg<R> &a) {
     R s, c;
     if constexpr (sizeof(R) == 8) { s = sin(a.hdg * kD2R); c = cos(a.hdg * kD2R); }
     else { sincospif(a.hdg * (1.0f / 180.0f), &s, &c); sincospif((float)(a.lat * (1.0 / 360.0)), &a.sa, &a.ca); }

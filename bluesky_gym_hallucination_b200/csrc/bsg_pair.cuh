@@ -74,14 +74,16 @@ __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &
     const float dx = (b.x - a.x) * cav;
     const float dist2 = fmaf(dx, dx, dy * dy);
     const float du = b.u - a.u, dv = b.v - a.v;
-    const float dv2r = fmaf(du, du, dv * dv);
-    const float dv2 = fmaxf(dv2r, 1e-6f);                   // the reference's lower clamp on |v_rel|^2
+    // |v_rel|^2 with the reference's lower clamp (1e-6) folded in as an additive floor: for |v_rel|^2 > 16 the sum
+    // rounds to |v_rel|^2 itself, for equal velocity vectors (common: integer dpsi draws) it is the clamp value
+    // 1e-6 exactly; in between (relative speeds below 3 mm/s) the reference's own value is the arbitrary clamp.
+    const float dv2 = fmaf(du, du, fmaf(dv, dv, 1e-6f));
     const float idv2 = rcp_approx(dv2);
     const float tcpa = -fmaf(du, dx, dv * dy) * idv2;
     const float cr = fmaf(dx, dv, -(dy * du));
-    // dist^2 - tcpa^2 dv2 = (cr^2 + dist^2 (dv2 - dv2r)) / dv2: the second term is exactly 0 unless the clamp
-    // is active (equal velocity vectors, common with integer dpsi draws), where dCPA must come out as dist
-    const float dcpa2 = fmaf(dist2 * (dv2 - dv2r), idv2, cr * cr * idv2);
+    // dist^2 - tcpa^2 dv2 = (cr^2 + dist^2 (dv2 - |v_rel|^2)) / dv2 with dv2 - |v_rel|^2 = 1e-6: the second term is
+    // below one ulp of cr^2-scale values unless the velocities are equal, where dCPA must come out as dist
+    const float dcpa2 = fmaf(cr, cr, dist2 * 1e-6f) * idv2;
     const bool swhor = (dcpa2 < P.R2) && off;
     const float dtinhor = sqrt_approx((P.R2 - dcpa2) * idv2);
     const float dalt = b.alt - a.alt;

@@ -9,19 +9,19 @@ namespace {
 
 template <typename R>
 __global__ void reset_kernel(int kind, int fixed_nac, int E, int N, const int32_t *mask, uint64_t seed, uint32_t *episode,
-                             double *pos, R *st, unsigned long long *reso, int *nac, double *ev) {
+                             double *pos, R *st, unsigned long long *reso, int *nac, double *ev, const ResetConst RC) {
     const int e = blockIdx.x;
     if (mask && !mask[e]) return;                       // uniform per CTA
     __shared__ ResetEnv S;
     const uint32_t ep = episode[e];
     double *v = ev + (size_t)e * BSG_NE;
     if (threadIdx.x == 0) {
-        reset_env_level(kind, fixed_nac, N, e, seed, ep, v, &S);
+        reset_env_level(kind, fixed_nac, N, e, seed, ep, v, &S, RC);
         nac[e] = S.nac;
         episode[e] = ep + 1;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < N; i += blockDim.x) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &S, v, pos, st, reso);
+    for (int i = threadIdx.x; i < N; i += blockDim.x) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &S, v, pos, st, reso, RC);
 }
 
 }  // namespace
@@ -38,10 +38,10 @@ extern "C" int bsg_reset(bsg_handle *h, const int32_t *mask_dev, uint64_t seed, 
     cudaStream_t s = (cudaStream_t)stream;
     if (g.precision == BSG_FP64)
         reset_kernel<double><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.fixed_nac, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
-                                                        (double *)h->st, h->reso, h->nac, h->ev);
+                                                        (double *)h->st, h->reso, h->nac, h->ev, h->rc);
     else
         reset_kernel<float><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.fixed_nac, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
-                                                       (float *)h->st, h->reso, h->nac, h->ev);
+                                                       (float *)h->st, h->reso, h->nac, h->ev, h->rc);
     h->launches++;
     CK(h, cudaGetLastError());
     return BSG_OK;

@@ -47,23 +47,30 @@ struct Philox {
 
 struct AcInit { double lat, lon, alt, hdg, cas, tas, vs, selalt; };
 
-// Traffic.creconfs geometry for one intruder of a target at (lat0, lon0), track trk0, speed gs0
-__device__ inline void creconfs(double lat0, double lon0, double trk0_deg, double gs0, double dpsi, double cpa_nm, double tlosh,
-                         double &lat, double &lon, double &hdg) {
+// Traffic.creconfs geometry for one intruder of a target at (lat0, lon0), track trk0, speed gs0.
+// Same construction with the inverse trigonometry folded away: the bearing enters only through its sine and
+// cosine, which are the normalised components (hypot = |v_rel| because (rd, rx) is a unit vector), and
+// atan2(gse, gsn) of a speed vector built from trk is trk itself wrapped to (-180, 180].
+__device__ inline void creconfs(double lat0, double lon0, double coslat0, double trk0_deg, double gs0, double dpsi,
+                                double cpa_nm, double tlosh, double &lat, double &lon, double &hdg) {
     const double trkref = trk0_deg * kD2R, cpa = cpa_nm * kNm, pzr = 5.0 * kNm;
-    const double trk = trkref + dpsi * kD2R;
-    const double gsn = gs0 * cos(trk), gse = gs0 * sin(trk);
-    const double vreln = gs0 * cos(trkref) - gsn, vrele = gs0 * sin(trkref) - gse;
+    double st0, ct0, st, ct;
+    sincos(trkref, &st0, &ct0);
+    sincos(trkref + dpsi * kD2R, &st, &ct);
+    const double vreln = gs0 * (ct0 - ct), vrele = gs0 * (st0 - st);
     const double vrel = sqrt(vreln * vreln + vrele * vrele);
     const double drelcpa = tlosh * vrel + (cpa > pzr ? 0.0 : sqrt(pzr * pzr - cpa * cpa));
     const double dist = sqrt(drelcpa * drelcpa + cpa * cpa);
     const double rd = drelcpa / dist, rx = cpa / dist;
-    const double brn = atan2(-rx * vreln + rd * vrele, rd * vreln + rx * vrele) * kR2D;
-    const double dnm = dist / kNm;
-    const double dx = dnm * sin(brn * kD2R), dy = dnm * cos(brn * kD2R);
+    const double k = (dist / kNm) / vrel;                     // dnm * (sin, cos)(brn) = k * (y, x)
+    const double dx = k * (-rx * vreln + rd * vrele), dy = k * (rd * vreln + rx * vrele);
     lat = lat0 + dy / 60.0;
-    lon = pymod((lon0 + dx / fmax(0.01, 60.0 * cos(lat0 * kD2R))) + 180, 360) - 180;
-    hdg = atan2(gse, gsn) * kR2D;
+    double lo = lon0 + dx / fmax(0.01, 60.0 * coslat0);
+    lo = lo >= 180.0 ? lo - 360.0 : lo;
+    lon = lo < -180.0 ? lo + 360.0 : lo;
+    double h = trk0_deg + dpsi;
+    h -= 360.0 * floor((h + 180.0) * (1.0 / 360.0));          // (-180, 180] like degrees(arctan2(gse, gsn))
+    hdg = h <= -180.0 ? h + 360.0 : h;
 }
 
 template <typename R>
@@ -96,16 +103,18 @@ __device__ inline bool inside_poly_ll(const double *poly, int nv, double tx, dou
 }
 
 // stage 1 (one thread per env): clears the scalar ev slots, draws the env-level quantities, grows the polygon
-static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int N, int e, uint64_t seed, uint32_t ep, double *v, ResetEnv *Sp) {
+static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int N, int e, uint64_t seed, uint32_t ep, double *v,
+                                                    ResetEnv *Sp, const ResetConst &RC) {
     ResetEnv S = {};
     Philox g(seed, (uint32_t)e, ep, 0u);
-    const double ccl = cos(kCenterLat * kD2R);
+    const double ccl = RC.ccl;
     for (int s = 0; s < BSG_EV_POLY; s++) v[s] = 0.0;
     S.nac = N;
     if (kind == BSG_KIND_HORIZONTAL) {
-        S.gs0 = vcas2tas(150.0, 0.0);
-        const double d = (double)g.randint(100, 150) / 6371.0, lat1 = 52.0 * kD2R;   // functions.py:24-42, bearing 0
-        v[BSG_EV_WPT_LAT] = asin(sin(lat1) * cos(d) + cos(lat1) * sin(d)) * kR2D;
+        S.gs0 = RC.tas_h;
+        // functions.py:24-42 at bearing 0: asin(sin(lat1) cos d + cos(lat1) sin d) = lat1 + d
+        const double d = (double)g.randint(100, 150) / 6371.0, lat1 = 52.0 * kD2R;
+        v[BSG_EV_WPT_LAT] = (lat1 + d) * kR2D;
         v[BSG_EV_WPT_LON] = 4.0;
     } else if (kind == BSG_KIND_VERTICAL) {
         S.alt0 = (double)g.randint(2000, 4000);
@@ -139,7 +148,7 @@ static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int
             if (area >= 2400.0 || nv >= BSG_MAXV) break;
         }
         S.nv = nv;
-        S.gs0 = vcas2tas(150.0, 350.0);
+        S.gs0 = RC.tas_s;
         const double dens = g.normal(0.005, 0.001);
         const int na = (int)fmax(ceil(dens * area), 5.0);
         S.nac = (fixed_nac || na > N) ? N : na;
@@ -163,10 +172,10 @@ static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int
 template <typename R>
 static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e, int i, uint64_t seed, uint32_t ep,
                                                    const ResetEnv *Sp, double *v, double *pos, R *st,
-                                                   unsigned long long *reso) {
+                                                   unsigned long long *reso, const ResetConst &RC) {
     const ResetEnv S = *Sp;
     const size_t EN = (size_t)E * N, k = (size_t)e * N + i;
-    const double ccl = cos(kCenterLat * kD2R);
+    const double ccl = RC.ccl;
     reso[k] = 0ull;
     AcInit a = {};
     Philox g(seed, (uint32_t)e, ep, 1u + (uint32_t)i);
@@ -184,10 +193,12 @@ static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e
                 if (tlosh > avg_tod) dH = g.randint((int)(-alt_own + 500), (int)((S.target - alt_own) + 100));
                 else dH = g.randint((int)((S.target - alt_own) - 500), (int)((S.target - alt_own) + 500));
             }
-            creconfs(52.0, 4.0, 0.0, S.gs0, dpsi, cpa, tlosh, a.lat, a.lon, a.hdg);
+            creconfs(52.0, 4.0, RC.coslat_hv, 0.0, S.gs0, dpsi, cpa, tlosh, a.lat, a.lon, a.hdg);
             a.alt = alt_own + dH;
-            a.cas = vtas2cas(S.gs0, a.alt);
-            a.tas = vcas2tas(a.cas, a.alt);
+            // creconfs hands cre() the CAS of the target's ground speed at the intruder's altitude; the TAS that
+            // cre() derives back from it is that ground speed again (vcas2tas o vtas2cas = id)
+            a.cas = kind == BSG_KIND_HORIZONTAL ? RC.cas_h : vtas2cas(S.gs0, a.alt);
+            a.tas = S.gs0;
             a.selalt = a.alt;
         }
     } else if (kind == BSG_KIND_SECTOR && i < S.nac) {

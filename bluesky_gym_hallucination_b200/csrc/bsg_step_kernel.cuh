@@ -4,7 +4,20 @@
 #include "bsg_env.cuh"
 #include "bsg_reset.cuh"
 
+#ifndef BSG_PW
+#define BSG_PW 2          // pairs evaluated per trip of the half-ring loop
+#endif
+
 namespace bsg {
+
+// -DBSG_TRACE: per-CTA %globaltimer stamps at the phase boundaries of step_kernel (tools/gpu_trace.py)
+#ifdef BSG_TRACE
+__device__ unsigned long long g_trace[8 * 16384];
+#define BSG_STAMP(slot) do { if (threadIdx.x == 0 && blockIdx.x < 16384) { unsigned long long t_; \
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_)); g_trace[blockIdx.x * 8 + (slot)] = t_; } } while (0)
+#else
+#define BSG_STAMP(slot) do { } while (0)
+#endif
 
 template <typename R>
 __device__ __forceinline__ void cd_params_for(const CdParams &P, CdParams &lit, CdParamsF &fast) {
@@ -16,7 +29,7 @@ __device__ __forceinline__ void cd_params_for(const CdParams &P, CdParams &lit, 
 // CTA size / residency: 128-thread CTAs keep the small-N configs in one balanced wave
 // (C2: 683 CTAs over 148 SMs x 5 resident), 256 threads only when one env needs them (N > 128).
 template <typename R, int TPB> struct StepBounds {
-    static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : (sizeof(R) == 4 ? 2 : 1);
+    static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : (sizeof(R) == 4 ? 2 : 1);   // 320: 2 x 320 threads, <= 102 registers
 };
 // per-env row of CD records in shared memory: N records + 16 B so that the rows of the envs sharing a
 // warp start in different banks (N * 32 B is a multiple of 128 B for N = 20: 2-way LDS.128 conflicts)
@@ -48,17 +61,17 @@ template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int e
 template <typename R>
 static __device__ __noinline__ void fused_reset(int kind, int fixed_nac, int E, int N, unsigned long long seed, unsigned int *episode,
                                                 double *ev, int *nac, double *pos, R *st, unsigned long long *reso,
-                                                unsigned char *smem_raw, bool skip, bool valid, int le, int i, int e) {
+                                                const ResetConst RC, unsigned char *smem_raw, bool skip, bool valid, int le, int i, int e) {
     // (scalars by value: taking the address of the kernel's parameter struct would copy it to local memory)
     ResetEnv *rs = reinterpret_cast<ResetEnv *>(smem_raw);
     double *evr = ev + (size_t)(valid ? e : 0) * BSG_NE;
     const unsigned int ep = skip ? episode[e] : 0u;
     if (skip && i == 0) {
-        reset_env_level(kind, fixed_nac, N, e, seed, ep, evr, &rs[le]);
+        reset_env_level(kind, fixed_nac, N, e, seed, ep, evr, &rs[le], RC);
         nac[e] = rs[le].nac;
     }
     __syncthreads();
-    if (skip) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &rs[le], evr, pos, st, reso);
+    if (skip) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &rs[le], evr, pos, st, reso, RC);
     __syncthreads();
     if (skip && i == 0) episode[e] = ep + 1;
 }
@@ -81,12 +94,15 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     R *sdist = reinterpret_cast<R *>(smem_raw + SL.sd_off);                // [epb*N] hdg (resumenav) / sector distances
     unsigned long long *crow = reinterpret_cast<unsigned long long *>(smem_raw + SL.cr_off);   // [2][epb*N]
 
+    BSG_STAMP(0);
     const int tid = threadIdx.x;
     const int le = tid / N, i = tid - le * N;
     const int e = blockIdx.x * epb + le;
     const bool valid = le < epb && e < A.E;
     const bool skip = valid && A.skip && A.skip[e];                       // fresh episode: no action, no integration
-    if (A.fuse_reset && __syncthreads_or(skip)) fused_reset<R>(A.kind, A.fixed_nac, A.E, A.N, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso, smem_raw, skip, valid, le, i, e);   // rare
+    if (A.fuse_reset && __syncthreads_or(skip))                            // rare: some env of this CTA starts an episode
+        fused_reset<R>(A.kind, A.fixed_nac, A.E, A.N, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso, A.RC,
+                       smem_raw, skip, valid, le, i, e);
     const int nl = valid ? A.nac[e] : 0;
     const bool live = valid && i < nl;
     const size_t EN = (size_t)A.E * N, k = (size_t)(valid ? e : 0) * N + i;
@@ -96,7 +112,8 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     AcReg<R> a = {};
     unsigned long long resorow = 0;
     if (live) {
-        ac_load<R, RESO>(a, A.pos, A.st, EN, k);
+        ac_load_raw<R, RESO>(a, A.pos, A.st, EN, k);
+        ac_derive<R>(a);
         if (reso) resorow = A.reso[k];
     }
     // ------------------------------------------------------------------ action intake (agent = aircraft 0)
@@ -122,6 +139,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         }
     }
     __syncthreads();
+    BSG_STAMP(1);
     const double lat0 = valid ? es[le].own_lat : 0.0, lon0 = valid ? es[le].own_lon : 0.0;
     CdParams PL; CdParamsF PF;
     cd_params_for<R>(A.P, PL, PF);
@@ -158,18 +176,33 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     me = rec_from(rA[i], rB[i]);
                     const int H = nl >> 1;
                     const float4 *pA = rA + i, *pB = rB + i;    // ring copy behind slot nl: j = i + d needs no wrap
-#pragma unroll 2
-                    for (int d = 1; d <= H; d++) {
-                        const RecFast o = rec_from(pA[d], pB[d]);
-                        PairCore pc;
-                        if (pair_fast_core(me, o, PF, true, pc)) {   // rare: native 32-bit shared atomics
-                            int j = i + d;
-                            j = j >= nl ? j - nl : j;
-                            unsigned *c32 = reinterpret_cast<unsigned *>(cr_now);
-                            atomicOr(&c32[2 * i + (j >> 5)], 1u << (j & 31));
-                            atomicOr(&c32[2 * j + (i >> 5)], 1u << (i & 31));
-                            if (RESO) es[le].anyconf[buf] = 1;
+                    unsigned *c32 = reinterpret_cast<unsigned *>(cr_now);
+                    auto mark = [&](int d) {                    // rare: native 32-bit shared atomics
+                        int j = i + d;
+                        j = j >= nl ? j - nl : j;
+                        atomicOr(&c32[2 * i + (j >> 5)], 1u << (j & 31));
+                        atomicOr(&c32[2 * j + (i >> 5)], 1u << (i & 31));
+                        if (RESO) es[le].anyconf[buf] = 1;
+                    };
+                    // BSG_PW pairs per trip, flags first and ONE rare branch behind them: the independent
+                    // dependency chains interleave (the pair body is latency-bound at 4-5 warps per scheduler)
+                    int d = 1;
+                    for (; d + (BSG_PW - 1) <= H; d += BSG_PW) {
+                        bool sw[BSG_PW], any = false;
+#pragma unroll
+                        for (int q = 0; q < BSG_PW; q++) {
+                            PairCore pc;
+                            sw[q] = pair_fast_core(me, rec_from(pA[d + q], pB[d + q]), PF, true, pc);
+                            any |= sw[q];
                         }
+                        if (any) {
+#pragma unroll
+                            for (int q = 0; q < BSG_PW; q++) if (sw[q]) mark(d + q);
+                        }
+                    }
+                    for (; d <= H; d++) {
+                        PairCore pc;
+                        if (pair_fast_core(me, rec_from(pA[d], pB[d]), PF, true, pc)) mark(d);
                     }
                 }
                 // phase 2 feeds MVP / resumenav every substep; the CD row outputs report the LAST detection of the
@@ -200,7 +233,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                             const float vrx = o.u - me.u, vry = o.v - me.v;
                             const float dot = fmaf(vrx, dx, vry * dy);
                             if (sw) {
-                                const float tcpa = -dot * rcp_approx(fmaxf(fmaf(vrx, vrx, vry * vry), 1e-6f));
+                                const float tcpa = -dot * rcp_approx(fmaf(vrx, vrx, fmaf(vry, vry, 1e-6f)));
                                 float d1, d2;
                                 mvp_pair_fast(dx, dy, dist2, tcpa, vrx, vry, PF.rpz_m, d1, d2);
                                 dve = dve - d1; dvn = dvn - d2;
@@ -290,6 +323,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             else kin_substep_fast(a, A.dt, reso, last && i == 0 && A.kind == BSG_KIND_SECTOR);
         }
     }
+    BSG_STAMP(2);
     if (live && !skip) {
         ac_store<R, RESO>(a, A.pos, A.st, EN, k);
         if (reso) A.reso[k] = resorow;
@@ -305,7 +339,9 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         if (o.cd_near_tin) ((R *)o.cd_near_tin)[k] = acc.near_tin;
         if (o.cd_tcpamax) ((R *)o.cd_tcpamax)[k] = acc.tcpamax;
     }
+    BSG_STAMP(3);
     env_layer<R>(A, a, es, sdist, le, i, e, nl, valid, live, skip, ev);
+    BSG_STAMP(4);
 }
 
 }  // namespace bsg
