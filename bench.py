@@ -82,6 +82,15 @@ class ClockSampler:
         return {"sm_mhz": sm[len(sm) // 2], "sm_max_mhz": max(mx), "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def ncu_traffic(workload):
+    """DRAM bytes of one launch of the dominant kernel from the committed ncu capture (profiles/ncu_traffic.json)."""
+    try:
+        with open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')) as f:
+            return json.load(f).get(workload, {}).get('bytes')
+    except (OSError, ValueError):
+        return None
+
+
 def cpu_baselines(n_ac, asas, budget_s=12.0):
     """Rank 0, N = 1 only: the oracle timed on the host cores on a bounded sample of the same workload."""
     import numpy as np
@@ -237,7 +246,7 @@ def run_ours(args):
                    "live_aircraft_per_env": {"min": int(nac.min()), "mean": float(nac.mean()), "max": int(nac.max())}},
         "pair_evals_per_sec": world * pairs_per_launch * K / (dev_ms_max * 1e-3),
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak32, "unit": "TFLOP/s", "frac": achieved / peak32,
-                     "traffic": None, "kernel": "bsg::step_kernel<float>", "kernel_ms": kernel_ms,
+                     "traffic": ncu_traffic(args.workload), "kernel": "bsg::step_kernel<float>", "kernel_ms": kernel_ms,
                      "flop_per_pair": FLOP_PER_PAIR, "pairs_per_launch": pairs_per_launch,
                      "peak_source": "bsg_peak_fp32 FMA chain measured in this run (burst); MEASURED_PEAKS.json holds no FP32 figure",
                      "hbm_achieved_gbs": bytes_per_envstep * E / (kernel_ms * 1e-3) / 1e9,
