@@ -88,6 +88,54 @@ __device__ __forceinline__ double vcasormach2tas(double spd, double h) {
     return fabs(spd) < 1 ? spd * vvsound(h) : vcas2tas(spd, h);
 }
 
+
+// ------------------------------------------------------------------ pow-free ISA conversions (fast path)
+// The fp32 fast path rounds these to float, but the agent's commanded speed changes every step, so the memo
+// misses once per env-step and three fp64 pow() (~200 instructions each, one live lane) sat on the warp's
+// critical path.  Same functions, evaluated without pow (<= 1e-11 relative to the literal forms, i.e. identical
+// after rounding to fp32):  (1+x)^3.5 = (1+x)^3 sqrt(1+x);  (1+y)^(2/7) by one Newton step on z^7 = (1+y)^2 from
+// an fp32 exp2/log2 start (quadratic: 1e-6 -> 1e-11);  (T/T0)^4.2568 by its binomial series in z = 1 - T/T0
+// for z <= 0.1 (h <= 4433 m; 16 terms, remainder < 1e-15), the literal pow above that.
+__device__ __forceinline__ double pow35m1(double x) { const double o = 1.0 + x; return o * o * o * sqrt(o) - 1.0; }
+__device__ __forceinline__ double pow27m1(double y) {
+    const double o = 1.0 + y, c = o * o;
+    double z = (double)exp2f((2.0f / 7.0f) * log2f((float)o));
+    const double z2 = z * z, z6 = z2 * z2 * z2;
+    z -= (double)((float)(z6 * z - c) / (float)(7.0 * z6));
+    return z - 1.0;
+}
+__device__ __forceinline__ void vatmos_fast(double h, double &p, double &rho, double &T) {
+    T = fmax(288.15 - 0.0065 * h, 216.65);
+    const double z = 1.0 - T / 288.15;
+    double th;
+    if (z <= 0.1) {
+        const double c[16] = { 1.0, 4.256848030018761, 6.9319535603279245, 5.214788578935872, 1.6385491880999719, 0.08417162621046376, -0.010425384972471766, 0.00259614719322528, -0.0008902032859321487, 0.0003702406870467438, -0.00017561078441329702, 9.168722022301611e-05, -5.152173830574456e-05, 3.0687742266075684e-05, -1.9164828160565436e-05, 1.2448388883131001e-05 };
+        th = c[15];
+#pragma unroll
+        for (int k = 14; k >= 0; k--) th = fma(th, -z, c[k]);
+    } else th = pow(T / 288.15, 4.256848030018761);
+    rho = 1.225 * th;
+    if (h > 11000.0) rho *= exp(-(h - 11000.0) / 6341.552161);
+    p = rho * kRgas * T;
+}
+static __device__ __noinline__ double vtas2cas_fast(double tas, double h) {
+    double p, rho, T;
+    vatmos_fast(h, p, rho, T);
+    const double qdyn = p * pow35m1(rho * tas * tas / (7.0 * p));
+    const double cas = sqrt(7.0 * kP0 / kRho0 * pow27m1(qdyn / kP0));
+    return tas < 0 ? -cas : cas;
+}
+static __device__ __noinline__ double vcas2tas_fast(double cas, double h) {
+    double p, rho, T;
+    vatmos_fast(h, p, rho, T);
+    const double qdyn = kP0 * pow35m1(kRho0 * cas * cas / (7.0 * kP0));
+    const double tas = sqrt(7.0 * p / rho * pow27m1(qdyn / p));
+    return cas < 0 ? -tas : tas;
+}
+__device__ __forceinline__ double vcasormach2tas_fast(double spd, double h) {
+    return fabs(spd) < 1 ? spd * vvsound(h) : vcas2tas_fast(spd, h);
+}
+
 // ------------------------------------------------------------------ performance envelope
 template <typename R> __device__ __forceinline__ int flight_phase(R vs, R alt) {
     R roc, h;

@@ -114,7 +114,7 @@ __device__ __forceinline__ void kin_substep_lit(AcReg<double> &a, double dt, boo
 // fast substep (fp32 state, fp64 positions, memoised atmosphere)
 __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool reso_on, bool want_cas) {
     if (a.alt != a.c_alt || a.selspd != a.c_spd) {           // autopilot target TAS: pure f(selspd, alt)
-        a.c_aptas = (float)vcasormach2tas((double)a.selspd, (double)a.alt);
+        a.c_aptas = (float)vcasormach2tas_fast((double)a.selspd, (double)a.alt);
         a.c_alt = a.alt; a.c_spd = a.selspd;
     }
     float ap_vs = fabsf(a.selvs) > 0.1f ? a.selvs : float(kVsDef);
@@ -129,8 +129,8 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     if (float(ph) != a.c_ph || a.selalt != a.c_selalt) {     // TAS-domain clamp limits: pure f(phase, allow_h)
         double vmin, vmax;
         phase_vlimits(ph, vmin, vmax);
-        double lo = vmin > 0.0 ? vcas2tas(vmin, (double)allow_h) : 0.0;
-        double hi = fmin(vcas2tas(vmax, (double)allow_h), kMmo * vvsound((double)allow_h));
+        double lo = vmin > 0.0 ? vcas2tas_fast(vmin, (double)allow_h) : 0.0;
+        double hi = fmin(vcas2tas_fast(vmax, (double)allow_h), kMmo * vvsound((double)allow_h));
         a.c_lo = (float)lo; a.c_hi = (float)hi; a.c_ph = float(ph); a.c_selalt = a.selalt;
     }
     float atas = fminf(fmaxf(t_tas, a.c_lo), a.c_hi);
@@ -157,10 +157,15 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     float alt_old = a.alt;
     a.alt = swalt ? fmaf(vs, dt, a.alt) : allow_h;
     a.lat = a.lat + (double)(dt * gsn) * (kR2D / kRe);
-    sincospif((float)(a.lat * (1.0 / 360.0)), &a.sa, &a.ca);   // half-angle pair: next CD record, and cos(lat) here
+    // half-angle pair (sin, cos)(lat/2) for the next CD record and cos(lat) here: exact at the head of every launch
+    // (ac_derive), advanced within the step by the first-order rotation (half step 1e-4 rad: the dropped second-order
+    // term is 5e-9 relative, below fp32 resolution)
+    const float hr = dt * gsn * float(0.5 / kRe);
+    const float ca0 = a.ca;
+    a.ca = fmaf(-a.sa, hr, ca0); a.sa = fmaf(ca0, hr, a.sa);
     float coslat = fmaf(a.ca, a.ca, -(a.sa * a.sa));
     a.lon = a.lon + (double)(dt * gse * rcp_approx(coslat)) * (kR2D / kRe);
-    if (want_cas) a.cas = (float)vtas2cas((double)tas, (double)alt_old);
+    if (want_cas) a.cas = (float)vtas2cas_fast((double)tas, (double)alt_old);
     a.tas = tas; a.hdg = hdg; a.vs = vs; a.gsn = gsn; a.gse = gse;
 }
 
