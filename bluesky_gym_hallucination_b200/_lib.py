@@ -65,6 +65,7 @@ SYMBOLS = {
     'bsg_observe': (_I, [_VP, _VP, _VP]),
     'bsg_step': (_I, [_VP, _VP, C.POINTER(StepOut), _VP]),
     'bsg_step_host': (_I, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_host_views': (_I, [_VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_pack': (_I, [C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP, _VP]),
     'bsg_cd_sweep': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_ndmap': (_I, [C.POINTER(NdmapParams), _VP, _VP, _VP, _VP, _VP]),

@@ -150,6 +150,25 @@ class BsgCore:
         L.check(self.lib.bsg_step_host(self.h, _ptr(actions), _ptr(obs), _ptr(reward), _ptr(terminated),
                                        _ptr(truncated), _ptr(info)), self.h)
 
+    def host_views(self):
+        """numpy views of the pinned host block step_host fills: (obs [E, obs_dim], reward [E], terminated [E],
+        truncated [E], info [E, 4]).  Valid until the next step_host / close."""
+        if getattr(self, '_views', None) is None:
+            p = [C.c_void_p() for _ in range(5)]
+            L.check(self.lib.bsg_host_views(self.h, *[C.byref(x) for x in p]), self.h)
+            ct = C.c_double if self.fp64 else C.c_float
+            arr = lambda ptr, cty, *shape: np.ctypeslib.as_array((cty * int(np.prod(shape))).from_address(ptr.value)).reshape(shape)
+            E = self.E
+            self._views = (arr(p[0], ct, E, max(self.obs_dim, 1)), arr(p[1], ct, E), arr(p[3], C.c_int32, E),
+                           arr(p[4], C.c_int32, E), arr(p[2], ct, E, 4))
+        return self._views
+
+    def step_host_views(self, actions):
+        """End-to-end call with a HOST action array; results are returned as views of the pinned block
+        (no second host copy): H2D actions + kernel + D2H obs/reward/flags/info inside."""
+        L.check(self.lib.bsg_step_host(self.h, _ptr(actions), None, None, None, None, None), self.h)
+        return self.host_views()
+
     def launch_count(self):
         n = C.c_int64(0)
         L.check(self.lib.bsg_launch_count(self.h, C.byref(n)), self.h)

@@ -133,6 +133,22 @@ int bsg_observe(bsg_handle *h, void *obs_dev, void *stream) {
     return launch_step<float>(h, nullptr, &o, 0, 1, (cudaStream_t)stream);
 }
 
+int bsg_host_views(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated) {
+    if (!h) return BSG_ERR_ARG;
+    const size_t rs = rsize(h), E = h->cfg.num_envs;
+    char *s = (char *)h->h_out;
+    if (obs) *obs = s;
+    s += E * h->obs_dim * rs;
+    if (reward) *reward = s;
+    s += E * rs;
+    if (info) *info = s;
+    s += E * 4 * rs;
+    if (terminated) *terminated = (int32_t *)s;
+    s += E * sizeof(int32_t);
+    if (truncated) *truncated = (int32_t *)s;
+    return BSG_OK;
+}
+
 int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, int32_t *term, int32_t *trunc, void *info) {
     if (!h || !actions) return BSG_ERR_ARG;
     const bsg_config &g = h->cfg;

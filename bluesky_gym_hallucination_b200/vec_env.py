@@ -80,12 +80,11 @@ class BlueSkyVecEnv:
         return self._obs_dict(obs), {keys[0]: np.zeros(E), keys[1]: np.zeros(E, np.int64), keys[2]: third}
 
     def step(self, actions):
-        a = np.asarray(actions, dtype=np.float64).reshape(self.num_envs, -1)
-        self._act.copy_(torch.from_numpy(a).to(self.core.rdtype), non_blocking=False)
-        obs, rew, term, trunc, info = self.core.step(self._act)
-        out = (obs.cpu().numpy(), rew.cpu().numpy().astype(np.float64), term.cpu().numpy().astype(bool),
-               trunc.cpu().numpy().astype(bool), info.cpu().numpy())
-        return self._obs_dict(out[0]), out[1], out[2], out[3], self._infos(out[4])
+        # host path of the C-ABI: pinned H2D of the actions, one launch, one D2H of every output into pinned host
+        # memory; the views are converted (copied) to the reference's float64 / bool types before they are returned
+        a = np.ascontiguousarray(np.asarray(actions, dtype=self.core.npdtype).reshape(self.num_envs, -1))
+        obs, rew, term, trunc, info = self.core.step_host_views(a)
+        return (self._obs_dict(obs), rew.astype(np.float64), term.astype(bool), trunc.astype(bool), self._infos(info))
 
     def step_tensors(self, actions):
         """actions: CUDA tensor [E, act_dim] in the core's dtype.  Returns the core's output tensors

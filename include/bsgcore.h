@@ -130,6 +130,10 @@ int bsg_observe(bsg_handle *h, void *obs_dev, void *stream);
 /* one env step for every env: action intake -> substeps x (autopilot, CD, MVP, limits, kinematics) -> obs/reward */
 int bsg_step(bsg_handle *h, const void *actions_dev /* real [E][act_dim] */, const bsg_step_out *out, void *stream);
 /* same through host buffers (pinned staging, copies inside): the end-to-end call of the plugin boundary */
+/* The pinned host block bsg_step_host fills (obs | reward | info[4] | terminated | truncated), as pointers: a caller
+ * that passes NULL output pointers to bsg_step_host reads the results here without another host copy.  Valid
+ * until the next bsg_step_host / bsg_destroy on this handle. */
+int bsg_host_views(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated);
 int bsg_step_host(bsg_handle *h, const void *actions_host, void *obs_host, void *reward_host,
                   int32_t *terminated_host, int32_t *truncated_host, void *info_host);
 

@@ -205,5 +205,10 @@ def test_step_host_equals_step():
     term = np.zeros(E, np.int32); trunc = np.zeros(E, np.int32); info = np.zeros((E, 4), np.float32)
     c.step_host(act, obs, rew, term, trunc, info)
     assert np.array_equal(obs, ref[0], equal_nan=True) and np.array_equal(rew, ref[1], equal_nan=True) and np.array_equal(term, ref[2])
+    # the pinned views hold the same results without the second host copy
+    c.set_state(ac, reso, nac, ev)
+    v_obs, v_rew, v_term, v_trunc, v_info = c.step_host_views(act)
+    assert np.array_equal(v_obs, ref[0], equal_nan=True) and np.array_equal(v_rew, ref[1], equal_nan=True)
+    assert np.array_equal(v_term, ref[2]) and np.array_equal(v_info, info, equal_nan=True)
     assert c.launch_count() > 0
     c.close()
