@@ -68,6 +68,10 @@ __device__ __forceinline__ float sqrt_approx(float x) { float y; asm("sqrt.appro
 //    look-ahead / in the past, the same decisions the reference's 1e-6 clamp produces.
 struct PairCore { float tcpa, dcpa2, tin, dx, dy, dist2, dalt; };
 
+// VERT = false: the caller has established that every aircraft of the env is level (vs == 0 exactly) and within
+// hpz/2 of a common altitude; the vertical window of the generic form is then (-inf, +inf) identically
+// ((dalt +/- hpz) * (-1/0)), so tin / tout are the horizontal ones and the flag is bit-identical.
+template <bool VERT = true>
 __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &b, const CdParamsF &P, bool off, PairCore &o) {
     const float dy = b.y - a.y;
     const float cav = fmaf(a.ca, b.ca, -(a.sa * b.sa));
@@ -87,9 +91,12 @@ __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &
     const bool swhor = (dcpa2 < P.R2) && off;
     const float dtinhor = sqrt_approx((P.R2 - dcpa2) * idv2);
     const float dalt = b.alt - a.alt;
-    const float n = -rcp_approx(b.vs - a.vs);
-    const float thi = (dalt + P.hpz) * n, tlo = (dalt - P.hpz) * n;
-    const float tin = fmaxf(fminf(thi, tlo), tcpa - dtinhor), tout = fminf(fmaxf(thi, tlo), tcpa + dtinhor);
+    float tin = tcpa - dtinhor, tout = tcpa + dtinhor;
+    if constexpr (VERT) {
+        const float n = -rcp_approx(b.vs - a.vs);
+        const float thi = (dalt + P.hpz) * n, tlo = (dalt - P.hpz) * n;
+        tin = fmaxf(fminf(thi, tlo), tin); tout = fminf(fmaxf(thi, tlo), tout);
+    }
     o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist2 = dist2; o.dalt = dalt;
     return swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
 }

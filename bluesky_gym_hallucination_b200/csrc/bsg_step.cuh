@@ -35,6 +35,8 @@ template <typename R> struct EnvShared {
     double own_lat, own_lon;
     R own_hdg, own_tas, own_alt, own_vs, drift, wdist;
     int anyconf[2];
+    int vneed;                       // some aircraft of the env is not level / co-altitude: generic vertical window
+    R alt_ref;
     int intr;
     double ev[BSG_EV_POLY];          // the env-level scalar slots, staged once per launch by the agent thread
 };

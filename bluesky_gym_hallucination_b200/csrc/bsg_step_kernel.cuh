@@ -1,5 +1,6 @@
 // bsg_step_kernel.cuh -- body of the fused env-step kernel (see bsg_step.cuh for the mapping).
 #pragma once
+#include <type_traits>
 #include "bsg_step.cuh"
 #include "bsg_env.cuh"
 #include "bsg_reset.cuh"
@@ -119,7 +120,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     // ------------------------------------------------------------------ action intake (agent = aircraft 0)
     if (SYM && valid) { crow[le * N + i] = 0ull; crow[(size_t)epb * N + le * N + i] = 0ull; }
     if (live && i == 0) {
-        es[le].anyconf[0] = 0; es[le].anyconf[1] = 0; es[le].intr = 0;
+        es[le].anyconf[0] = 0; es[le].anyconf[1] = 0; es[le].intr = 0; es[le].vneed = 0; es[le].alt_ref = a.alt;
         es[le].own_lat = a.lat; es[le].own_lon = a.lon;                    // local origin of the fp32 CD records
 #pragma unroll
         for (int s2 = 0; s2 < BSG_EV_POLY; s2++) es[le].ev[s2] = ev[s2];   // 14 independent loads, staged in smem
@@ -141,6 +142,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     __syncthreads();
     BSG_STAMP(1);
     const double lat0 = valid ? es[le].own_lat : 0.0, lon0 = valid ? es[le].own_lon : 0.0;
+    const R alt_ref = valid ? es[le].alt_ref : R(0);
     CdParams PL; CdParamsF PF;
     cd_params_for<R>(A.P, PL, PF);
 
@@ -157,6 +159,8 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     float4 *wA = reinterpret_cast<float4 *>(rb), *wB = wA + sym_row_recs(N);
                     const float4 ha = make_float4(r.x, r.y, r.alt, r.u), hb = make_float4(r.v, r.vs, r.ca, r.sa);
                     wA[i] = ha; wB[i] = hb;
+                    // monotone within the launch: once any aircraft climbs, descends or leaves the common level
+                    if (a.vs != 0.0f || !(fabsf(a.alt - alt_ref) < 0.5f * (float)A.P.hpz)) es[le].vneed = 1;
                     if (i < (nl >> 1)) { wA[nl + i] = ha; wB[nl + i] = hb; }
                 } else make_rec<R>(a, lat0, lon0, rb[i]);
                 if (reso) sdist[le * N + i] = a.hdg;
@@ -186,24 +190,29 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     };
                     // BSG_PW pairs per trip, flags first and ONE rare branch behind them: the independent
                     // dependency chains interleave (the pair body is latency-bound at 4-5 warps per scheduler)
-                    int d = 1;
-                    for (; d + (BSG_PW - 1) <= H; d += BSG_PW) {
-                        bool sw[BSG_PW], any = false;
+                    auto sweep = [&](auto vt) {
+                        constexpr bool V = decltype(vt)::value;
+                        int d = 1;
+                        for (; d + (BSG_PW - 1) <= H; d += BSG_PW) {
+                            bool sw[BSG_PW], any = false;
 #pragma unroll
-                        for (int q = 0; q < BSG_PW; q++) {
+                            for (int q = 0; q < BSG_PW; q++) {
+                                PairCore pc;
+                                sw[q] = pair_fast_core<V>(me, rec_from(pA[d + q], pB[d + q]), PF, true, pc);
+                                any |= sw[q];
+                            }
+                            if (any) {
+#pragma unroll
+                                for (int q = 0; q < BSG_PW; q++) if (sw[q]) mark(d + q);
+                            }
+                        }
+                        for (; d <= H; d++) {
                             PairCore pc;
-                            sw[q] = pair_fast_core(me, rec_from(pA[d + q], pB[d + q]), PF, true, pc);
-                            any |= sw[q];
+                            if (pair_fast_core<V>(me, rec_from(pA[d], pB[d]), PF, true, pc)) mark(d);
                         }
-                        if (any) {
-#pragma unroll
-                            for (int q = 0; q < BSG_PW; q++) if (sw[q]) mark(d + q);
-                        }
-                    }
-                    for (; d <= H; d++) {
-                        PairCore pc;
-                        if (pair_fast_core(me, rec_from(pA[d], pB[d]), PF, true, pc)) mark(d);
-                    }
+                    };
+                    // level, co-altitude traffic (Horizontal and Sector envs): the vertical window is (-inf, inf)
+                    if (es[le].vneed) sweep(std::true_type{}); else sweep(std::false_type{});
                 }
                 // phase 2 feeds MVP / resumenav every substep; the CD row outputs report the LAST detection of the
                 // step (what bs.traf.cd holds afterwards), so the row reductions run on the last substep only
