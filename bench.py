@@ -292,11 +292,17 @@ def run_giant(args):
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
     peak32, _ = bc.peak_fp32(local, 4096)
 
+    sym = not args.ordered_sweep
+    grp = dist.group.WORLD if world > 1 else None
+
     def one():
         nonlocal out
         rec = bc.cd_pack(*mine, 52.0, 4.0)                                   # [E, rows, 8]
         full = sharding.gather_records(rec, N, world, buf=rec_all)
-        out = bc.cd_sweep(full, r0, r1, out=out)
+        if sym:      # every unordered pair once; tiles dealt round-robin to the ranks, outputs all-reduced
+            out = bc.cd_sweep_sym(full, out=out, group=grp, rank=rank, world=world)
+        else:        # ordered row block per rank, row outputs local
+            out = bc.cd_sweep(full, r0, r1, out=out)
     for _ in range(W):
         one()
     torch.cuda.synchronize()
@@ -327,11 +333,13 @@ def run_giant(args):
             "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "c5", "description": "giant airspace 16 envs x 10000 aircraft all-pairs CPA, row-block sharded",
-                       "collective": "one NCCL all-gather of packed state per step" if world > 1 else "none",
+                       "sweep": "symmetric: every unordered pair evaluated once, ordered entries reported" if sym else "ordered row block",
+                       "collective": ("none" if world == 1 else "one NCCL all-gather of packed state + "
+                                      + ("3 all-reduces of the row outputs (sum/max/min)" if sym else "no reduce") + " per step"),
                        "l2": "256 MB flush between timed iterations"},
             "roofline": {"bound": "fp32", "achieved": ach, "peak": peak32, "unit": "TFLOP/s", "frac": ach / peak32,
-                         "traffic": None, "kernel": "cd_sweep_kernel (+ pack, all-gather inside the timed step)"},
-            "gpu_launches": 2 * K, "clocks": clocks}), flush=True)
+                         "traffic": None, "kernel": ("cd_sym_sweep_kernel" if sym else "cd_sweep_kernel") + " (+ pack, collectives, init/finalize inside the timed step)"},
+            "gpu_launches": (4 if sym else 2) * K, "clocks": clocks}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -394,6 +402,7 @@ def main():
     ap.add_argument('--steps', type=int, default=2000)
     ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
+    ap.add_argument('--ordered-sweep', action='store_true', help='c5: ordered row-block sweep instead of the symmetric one')
     ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS) + ['c4', 'c5'])
     ap.add_argument('--envs', type=int, default=0, help='override envs per GPU')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')

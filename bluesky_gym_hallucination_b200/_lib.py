@@ -68,6 +68,9 @@ SYMBOLS = {
     'bsg_host_views': (_I, [_VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_pack': (_I, [C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP, _VP]),
     'bsg_cd_sweep': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_cd_sym_init': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP]),
+    'bsg_cd_sym_sweep': (_I, [C.POINTER(CdParams), _VP, C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_cd_sym_finalize': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_ndmap': (_I, [C.POINTER(NdmapParams), _VP, _VP, _VP, _VP, _VP]),
     'bsg_peak_fp32': (_I, [_I, _I, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     'bsg_peak_fp64': (_I, [_I, _I, C.POINTER(C.c_double), C.POINTER(C.c_double)]),

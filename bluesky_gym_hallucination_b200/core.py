@@ -210,6 +210,37 @@ def cd_sweep(rec, row0=0, row1=None, rpz_m=5 * 1852.0, hpz_m=1000 * 0.3048, dtlo
     return out
 
 
+def cd_sweep_sym(rec, rpz_m=5 * 1852.0, hpz_m=1000 * 0.3048, dtlookahead=300.0, out=None, group=None, rank=0, world=1):
+    """Symmetric all-pairs sweep (every unordered pair once): same row outputs as cd_sweep for ALL rows.
+    world > 1: the tiles of the upper triangle are dealt round-robin to the ranks of `group` and the partial outputs
+    are combined with three all-reduces (sum / max / min) before the finalize stage."""
+    lib = L.load()
+    E, N, _ = rec.shape
+    dev = rec.device
+    if out is None:
+        out = dict(inconf=torch.empty((E, N), dtype=torch.uint8, device=dev),
+                   cnt=torch.empty((2, E, N), dtype=torch.int32, device=dev),        # nconf, nlos (one SUM all-reduce)
+                   near_idx=torch.empty((E, N), dtype=torch.int32, device=dev),
+                   near_tcpa=torch.empty((E, N), dtype=torch.float32, device=dev),
+                   near_dcpa=torch.empty((E, N), dtype=torch.float32, device=dev),
+                   near_tin=torch.empty((E, N), dtype=torch.float32, device=dev),
+                   tcpamax=torch.empty((E, N), dtype=torch.float32, device=dev),
+                   key=torch.empty((E, N), dtype=torch.int64, device=dev))
+        out['nconf'], out['nlos'] = out['cnt'][0], out['cnt'][1]
+    p = L.CdParams(E, N, 0, N, rpz_m, hpz_m, dtlookahead, 0)
+    s = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    L.check(lib.bsg_cd_sym_init(C.byref(p), _ptr(out['nconf']), _ptr(out['nlos']), _ptr(out['tcpamax']), _ptr(out['key']), s))
+    L.check(lib.bsg_cd_sym_sweep(C.byref(p), _ptr(rec), rank, world, _ptr(out['nconf']), _ptr(out['nlos']),
+                                 _ptr(out['tcpamax']), _ptr(out['key']), s))
+    if world > 1:
+        from . import sharding
+        sharding.reduce_sym_outputs(out['cnt'], out['tcpamax'], out['key'], group)
+    L.check(lib.bsg_cd_sym_finalize(C.byref(p), _ptr(rec), _ptr(out['nconf']), _ptr(out['key']), _ptr(out['inconf']),
+                                    _ptr(out['near_idx']), _ptr(out['near_tcpa']), _ptr(out['near_dcpa']),
+                                    _ptr(out['near_tin']), s))
+    return out
+
+
 def ndmap(rec, nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=0.0, cx=1.0, cy=1.0, cz=1.0, dt=10.0, out=None):
     """rec: [E,6,n] f32 CUDA (x,y,z,u,v,w).  Returns occ u8, conf u8 [E,nt,nz,ny,nx], ncell i32 [E,nt]."""
     lib = L.load()

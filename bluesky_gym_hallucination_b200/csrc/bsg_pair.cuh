@@ -83,7 +83,8 @@ __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &
     // 1e-6 exactly; in between (relative speeds below 3 mm/s) the reference's own value is the arbitrary clamp.
     const float dv2 = fmaf(du, du, fmaf(dv, dv, 1e-6f));
     const float idv2 = rcp_approx(dv2);
-    const float tcpa = -fmaf(du, dx, dv * dy) * idv2;
+    const float ndot = -fmaf(du, dx, dv * dy);
+    const float tcpa = ndot * idv2;
     const float cr = fmaf(dx, dv, -(dy * du));
     // dist^2 - tcpa^2 dv2 = (cr^2 + dist^2 (dv2 - |v_rel|^2)) / dv2 with dv2 - |v_rel|^2 = 1e-6: the second term is
     // below one ulp of cr^2-scale values unless the velocities are equal, where dCPA must come out as dist
@@ -91,7 +92,9 @@ __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &
     const bool swhor = (dcpa2 < P.R2) && off;
     const float dtinhor = sqrt_approx((P.R2 - dcpa2) * idv2);
     const float dalt = b.alt - a.alt;
-    float tin = tcpa - dtinhor, tout = tcpa + dtinhor;
+    // explicit FMAs: the same rounding in every kernel this body is inlined into (the compiler would otherwise
+    // contract tcpa -/+ dtinhor in some contexts and not in others)
+    float tin = fmaf(ndot, idv2, -dtinhor), tout = fmaf(ndot, idv2, dtinhor);
     if constexpr (VERT) {
         const float n = -rcp_approx(b.vs - a.vs);
         const float thi = (dalt + P.hpz) * n, tlo = (dalt - P.hpz) * n;

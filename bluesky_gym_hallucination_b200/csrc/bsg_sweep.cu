@@ -77,16 +77,34 @@ __global__ void __launch_bounds__(kThreads) cd_sweep_kernel(const bsg_cd_params 
         mbar_wait(&bar[buf], (t >> 1) & 1);
         const int nt = min(kTile, N - t * kTile), j0 = t * kTile;
         const RecFast *tb = tiles + (size_t)buf * kTile;
-#pragma unroll 4
-        for (int jj = q; jj < nt; jj += JS) {
+        // 4 pairs per trip, flags first and one rare branch behind them (conflicts are rare: the row reductions
+        // stay off the hot path and the four dependency chains interleave)
+        int jj = q;
+        for (; jj + 3 * JS < nt; jj += 4 * JS) {
+            PairCore pc[4];
+            bool sw[4], any = false;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const float4 *s = reinterpret_cast<const float4 *>(tb + jj + u * JS);
+                const float4 a = s[0], b = s[1];
+                const RecFast o = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+                sw[u] = pair_fast_core(me, o, P, (j0 + jj + u * JS) != i, pc[u]);
+                any |= sw[u];
+            }
+            if (any) {
+#pragma unroll
+                for (int u = 0; u < 4; u++)
+                    if (sw[u]) acc.add_conflict(j0 + jj + u * JS, pc[u].tcpa, pc[u].dcpa2, pc[u].tin,
+                                                (pc[u].dist2 < P.R2) && (fabsf(pc[u].dalt) < P.hpz));
+            }
+        }
+        for (; jj < nt; jj += JS) {
             const float4 *s = reinterpret_cast<const float4 *>(tb + jj);
             const float4 a = s[0], b = s[1];
             const RecFast o = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
             PairCore pc;
-            const bool sw = pair_fast_core(me, o, P, (j0 + jj) != i, pc);
-            if (__any_sync(__activemask(), sw)) {               // conflicts are rare: row reductions off the hot path
-                if (sw) acc.add_conflict(j0 + jj, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < P.R2) && (fabsf(pc.dalt) < P.hpz));
-            }
+            if (pair_fast_core(me, o, P, (j0 + jj) != i, pc))
+                acc.add_conflict(j0 + jj, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < P.R2) && (fabsf(pc.dalt) < P.hpz));
         }
         __syncthreads();      // everyone is done with tiles[buf] before it is refilled two iterations later
     }
@@ -115,6 +133,144 @@ __global__ void __launch_bounds__(kThreads) cd_sweep_kernel(const bsg_cd_params 
         if (near_tin) near_tin[k] = acc.near_tin;
         if (tcpamax) tcpamax[k] = acc.tcpamax;
     }
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Symmetric sweep: every UNORDERED pair is evaluated once.  The fp32 pair form is exactly symmetric under i <-> j
+// (bsg_pair.cuh), so the ordered N x N matrix it stands for is bit-identical to the full sweep's.  The pair matrix
+// of an env is cut into kSymT x kSymT tiles; a CTA owns one tile (bi <= bj) of the upper triangle, thread r holds
+// ownship row bi*T + r in registers and the tile's columns stream from shared memory as broadcast reads.  Conflicts
+// are rare: a conflict updates the row accumulators (registers) and the column accumulators (shared-memory
+// atomics); both are flushed with global atomics that are order-independent -- integer add / max / 64-bit min on
+// (tCPA as an order-preserving int32, intruder index) -- so the result is deterministic.  dCPA / tin of the winner
+// are recomputed by the finalize kernel (pure functions of the pair).  tile_rank/tile_stride deal the tiles to
+// GPUs round-robin; the partial outputs are then combined with one all-reduce (sum, max, min) before finalize.
+constexpr int kSymT = 256;
+
+__device__ __forceinline__ long long sym_key(float tcpa, int j) {
+    int b = __float_as_int(tcpa);
+    b ^= (b >> 31) & 0x7fffffff;                         // signed-int order == float order
+    return ((long long)b << 32) | (unsigned)j;
+}
+__device__ __forceinline__ float sym_key_tcpa(long long key) {
+    int b = (int)(key >> 32);
+    b ^= (b >> 31) & 0x7fffffff;
+    return __int_as_float(b);
+}
+
+__global__ void cd_sym_init_kernel(size_t n, int32_t *nconf, int32_t *nlos, int32_t *tcpamax_bits, long long *key) {
+    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    nconf[k] = 0; nlos[k] = 0; tcpamax_bits[k] = 0; key[k] = 0x7fffffffffffffffLL;
+}
+
+__global__ void __launch_bounds__(kSymT) cd_sym_sweep_kernel(const bsg_cd_params p, const RecFast *__restrict__ rec,
+                                                            int tile_rank, int tile_stride, int32_t *nconf,
+                                                            int32_t *nlos, int32_t *tcpamax_bits, long long *key) {
+    __shared__ float4 tA[kSymT], tB[kSymT];
+    __shared__ int c_nconf[kSymT], c_nlos[kSymT], c_tmax[kSymT];
+    __shared__ long long c_key[kSymT];
+    const int N = p.num_ac, e = blockIdx.y, nb = (N + kSymT - 1) / kSymT;
+    int t = blockIdx.x * tile_stride + tile_rank;          // linear index into the upper triangle, row-major
+    if (t >= nb * (nb + 1) / 2) return;
+    int bi = 0;
+    while (t >= nb - bi) { t -= nb - bi; bi++; }
+    const int bj = bi + t, r = threadIdx.x;
+    const RecFast *base = rec + (size_t)e * N;
+    const int i = bi * kSymT + r, j0 = bj * kSymT, nt = min(kSymT, N - j0);
+    const bool rowok = i < N;
+    if (r < nt) {
+        const float4 *m = reinterpret_cast<const float4 *>(base + j0 + r);
+        tA[r] = __ldg(m); tB[r] = __ldg(m + 1);
+    }
+    c_nconf[r] = 0; c_nlos[r] = 0; c_tmax[r] = 0; c_key[r] = 0x7fffffffffffffffLL;
+    RecFast me = {};
+    if (rowok) {
+        const float4 *m = reinterpret_cast<const float4 *>(base + i);
+        const float4 a = __ldg(m), b = __ldg(m + 1);
+        me = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+    }
+    CdParamsF P;
+    P.R2 = p.rpz_m * p.rpz_m; P.hpz = p.hpz_m; P.dtlook = p.dtlookahead; P.rpz = p.rpz_m; P.rpz_m = 0; P.hpz_m = 0;
+    __syncthreads();
+    RowAcc<float> acc;
+    const bool diag = bi == bj;
+    auto hit = [&](int jj, const PairCore &pc) {             // rare
+        const bool los = (pc.dist2 < P.R2) && (fabsf(pc.dalt) < P.hpz);
+        acc.add_conflict(j0 + jj, pc.tcpa, pc.dcpa2, pc.tin, los);
+        atomicAdd(&c_nconf[jj], 1);
+        if (los) atomicAdd(&c_nlos[jj], 1);
+        atomicMax(&c_tmax[jj], __float_as_int(fmaxf(pc.tcpa, 0.0f)));
+        atomicMin(&c_key[jj], sym_key(pc.tcpa, i));
+    };
+    if (rowok) {
+        int jj = 0;
+        for (; jj + 3 < nt; jj += 4) {
+            PairCore pc[4];
+            bool sw[4], any = false;
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const float4 a = tA[jj + u], b = tB[jj + u];
+                const RecFast o = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+                sw[u] = pair_fast_core(me, o, P, !diag || (jj + u > r), pc[u]);
+                any |= sw[u];
+            }
+            if (any) {
+#pragma unroll
+                for (int u = 0; u < 4; u++) if (sw[u]) hit(jj + u, pc[u]);
+            }
+        }
+        for (; jj < nt; jj++) {
+            const float4 a = tA[jj], b = tB[jj];
+            const RecFast o = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
+            PairCore pc;
+            if (pair_fast_core(me, o, P, !diag || (jj > r), pc)) hit(jj, pc);
+        }
+    }
+    __syncthreads();
+    if (rowok && acc.nconf > 0) {                            // rows of this tile
+        const size_t k = (size_t)e * N + i;
+        atomicAdd(&nconf[k], acc.nconf);
+        if (acc.nlos) atomicAdd(&nlos[k], acc.nlos);
+        atomicMax(&tcpamax_bits[k], __float_as_int(acc.tcpamax));
+        atomicMin(&key[k], sym_key(acc.near_tcpa, acc.near_idx));
+    }
+    if (r < nt && c_nconf[r] > 0) {                          // columns of this tile
+        const size_t k = (size_t)e * N + j0 + r;
+        atomicAdd(&nconf[k], c_nconf[r]);
+        if (c_nlos[r]) atomicAdd(&nlos[k], c_nlos[r]);
+        atomicMax(&tcpamax_bits[k], c_tmax[r]);
+        atomicMin(&key[k], c_key[r]);
+    }
+}
+
+__global__ void cd_sym_finalize_kernel(const bsg_cd_params p, const RecFast *__restrict__ rec, const int32_t *nconf,
+                                       const long long *key, uint8_t *inconf, int32_t *near_idx, float *near_tcpa,
+                                       float *near_dcpa, float *near_tin) {
+    const int N = p.num_ac;
+    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= (size_t)p.num_envs * N) return;
+    const long long ky = key[k];
+    int j = -1;
+    float tc = 0.0f, dc = 0.0f, ti = 0.0f;
+    if (nconf[k] > 0) {
+        j = (int)(unsigned)(ky & 0xffffffffLL);
+        tc = sym_key_tcpa(ky);
+        const size_t e = k / N;
+        const float4 *m = reinterpret_cast<const float4 *>(rec + k), *n = reinterpret_cast<const float4 *>(rec + e * N + j);
+        const float4 a = __ldg(m), b = __ldg(m + 1), c = __ldg(n), d = __ldg(n + 1);
+        const RecFast me = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w }, o = { c.x, c.y, c.z, c.w, d.x, d.y, d.z, d.w };
+        CdParamsF P;
+        P.R2 = p.rpz_m * p.rpz_m; P.hpz = p.hpz_m; P.dtlook = p.dtlookahead; P.rpz = p.rpz_m; P.rpz_m = 0; P.hpz_m = 0;
+        PairCore pc;
+        pair_fast_core(me, o, P, true, pc);
+        dc = sqrtf(pc.dcpa2); ti = pc.tin;
+    }
+    if (inconf) inconf[k] = nconf[k] > 0;
+    if (near_idx) near_idx[k] = j;
+    if (near_tcpa) near_tcpa[k] = tc;
+    if (near_dcpa) near_dcpa[k] = dc;
+    if (near_tin) near_tin[k] = ti;
 }
 
 __global__ void cd_pack_kernel(int E, int N, const double *lat, const double *lon, const float *alt, const float *trk,
@@ -182,6 +338,38 @@ int bsg_cd_sweep(const bsg_cd_params *p, const float *rec, uint8_t *inconf, int3
     }
 #undef SW
     return e == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+int bsg_cd_sym_init(const bsg_cd_params *p, int32_t *nconf, int32_t *nlos, float *tcpamax, int64_t *key, void *stream) {
+    if (!p || !nconf || !nlos || !tcpamax || !key || p->num_envs < 1 || p->num_ac < 1) return BSG_ERR_ARG;
+    const size_t n = (size_t)p->num_envs * p->num_ac;
+    cd_sym_init_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n, nconf, nlos, (int32_t *)tcpamax,
+                                                                                       (long long *)key);
+    return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+int bsg_cd_sym_sweep(const bsg_cd_params *p, const float *rec, int32_t tile_rank, int32_t tile_stride, int32_t *nconf,
+                     int32_t *nlos, float *tcpamax, int64_t *key, void *stream) {
+    if (!p || !rec || !nconf || !nlos || !tcpamax || !key || p->num_envs < 1 || p->num_ac < 1 || tile_stride < 1 ||
+        tile_rank < 0 || tile_rank >= tile_stride)
+        return BSG_ERR_ARG;
+    const int nb = (p->num_ac + kSymT - 1) / kSymT, ntile = nb * (nb + 1) / 2;
+    dim3 grid((ntile + tile_stride - 1) / tile_stride, p->num_envs);
+    cd_sym_sweep_kernel<<<grid, kSymT, 0, (cudaStream_t)stream>>>(*p, reinterpret_cast<const RecFast *>(rec), tile_rank,
+                                                                  tile_stride, nconf, nlos, (int32_t *)tcpamax,
+                                                                  (long long *)key);
+    return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+int bsg_cd_sym_finalize(const bsg_cd_params *p, const float *rec, const int32_t *nconf, const int64_t *key,
+                        uint8_t *inconf, int32_t *near_idx, float *near_tcpa, float *near_dcpa, float *near_tin,
+                        void *stream) {
+    if (!p || !rec || !nconf || !key || p->num_envs < 1 || p->num_ac < 1) return BSG_ERR_ARG;
+    const size_t n = (size_t)p->num_envs * p->num_ac;
+    cd_sym_finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        *p, reinterpret_cast<const RecFast *>(rec), nconf, (const long long *)key, inconf, near_idx, near_tcpa, near_dcpa,
+        near_tin);
+    return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
 }
 
 }  // extern "C"

@@ -5,6 +5,9 @@
 * giant airspace (C5): the N x N pair matrix is row-block partitioned; rank g owns ownship rows
   [g*N/G, (g+1)*N/G) of every env, packs the CD records of its own aircraft and ONE all-gather of the packed
   state (32 B per aircraft) gives every rank all intruder columns.  Row reductions are local: no reduce step.
+* giant airspace, symmetric sweep: every unordered pair is evaluated once; the tiles of the upper triangle are dealt
+  round-robin to the ranks (tile_of_rank), each rank accumulates partial row outputs for ALL rows and three
+  all-reduces (reduce_sym_outputs: sum / max / min, all order-independent integer operations) combine them.
 """
 import torch
 import torch.distributed as dist
@@ -37,3 +40,13 @@ def gather_records(rec_local, num_ac, world, buf=None):
         dist.all_gather(parts, rec_local.contiguous())
         buf = torch.stack(parts, 0)
     return buf.permute(1, 0, 2, 3).reshape(E, num_ac, w).contiguous()     # rank-major -> aircraft-major
+
+
+def reduce_sym_outputs(cnt, tcpamax, key, group=None):
+    """Combine the partial outputs of the symmetric sweep across ranks, in place:
+    cnt [2, E, N] int32 (nconf, nlos) SUM; tcpamax [E, N] float32 >= 0, MAX through its int32 bit pattern (order
+    preserving for non-negative floats); key [E, N] int64 = (order-preserving int32 of tCPA) << 32 | intruder, MIN."""
+    dist.all_reduce(cnt, op=dist.ReduceOp.SUM, group=group)
+    dist.all_reduce(tcpamax.view(torch.int32), op=dist.ReduceOp.MAX, group=group)
+    dist.all_reduce(key, op=dist.ReduceOp.MIN, group=group)
+    return cnt, tcpamax, key

@@ -145,6 +145,20 @@ int bsg_cd_sweep(const bsg_cd_params *p, const float *rec_dev, uint8_t *inconf_d
                  int32_t *nlos_dev, int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev,
                  float *near_tin_dev, float *tcpamax_dev, void *stream);
 
+/* Symmetric form of the same sweep: every unordered pair is evaluated once (the fp32 pair form is exactly
+ * symmetric, so the row outputs are bit-identical to bsg_cd_sweep's).  Three stages on caller-owned device buffers
+ * [E][N]: init, sweep (accumulates with order-independent integer atomics; tile_rank / tile_stride deal the tiles of
+ * the upper triangle to GPUs round-robin), finalize.  With tile_stride > 1 the caller combines the partial outputs
+ * across GPUs between sweep and finalize: nconf, nlos SUM (int32); tcpamax MAX (its float bits as int32: values are
+ * non-negative); key MIN (int64).  row0 / row1 of bsg_cd_params are ignored (all rows are produced). */
+int bsg_cd_sym_init(const bsg_cd_params *p, int32_t *nconf_dev, int32_t *nlos_dev, float *tcpamax_dev,
+                    int64_t *key_dev, void *stream);
+int bsg_cd_sym_sweep(const bsg_cd_params *p, const float *rec_dev, int32_t tile_rank, int32_t tile_stride,
+                     int32_t *nconf_dev, int32_t *nlos_dev, float *tcpamax_dev, int64_t *key_dev, void *stream);
+int bsg_cd_sym_finalize(const bsg_cd_params *p, const float *rec_dev, const int32_t *nconf_dev, const int64_t *key_dev,
+                        uint8_t *inconf_dev, int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev,
+                        float *near_tin_dev, void *stream);
+
 /* ND-map: rec_dev float [E][6][n] (x, y, z, u, v, w); occ/conf uint8 [E][nt][nz][ny][nx]; ncell int32 [E][nt] */
 int bsg_ndmap(const bsg_ndmap_params *p, const float *rec_dev, uint8_t *occ_dev, uint8_t *conf_dev,
               int32_t *ncell_dev, void *stream);

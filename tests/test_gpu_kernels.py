@@ -64,6 +64,39 @@ def test_cd_sweep_row_block_equals_full():
         assert torch.equal(full[k], parts[k]), k
 
 
+@pytest.mark.parametrize('E,N,box', [(2, 1200, 300.0), (3, 257, 60.0), (1, 20, 30.0), (2, 700, 150.0)])
+def test_cd_sweep_symmetric_equals_ordered(E, N, box):
+    """Symmetric sweep (every unordered pair once, integer atomics) == the ordered sweep, bitwise, on dense and
+    sparse traffic; and the tile-dealt partial sweeps (the multi-GPU split) combine to the same result."""
+    from bluesky_gym_hallucination_b200 import core, scenario as sc, _lib as L
+    import ctypes as C
+    lat, lon, alt, trk, gs, vs = sc.raw_traffic(E, N, seed=11, box_nm=box)
+    rec = _pack(lat, lon, alt, trk, gs, vs)
+    full = core.cd_sweep(rec)
+    sym = core.cd_sweep_sym(rec)
+    torch.cuda.synchronize()
+    assert int(full['nconf'].sum()) > 0
+    for k in ('inconf', 'nconf', 'nlos', 'near_idx', 'near_tcpa', 'near_dcpa', 'near_tin', 'tcpamax'):
+        assert torch.equal(full[k], sym[k]), k
+    # three "ranks": partial outputs combined by sum / max / min like the all-reduce would
+    lib = L.load()
+    p = L.CdParams(E, N, 0, N, 5 * 1852.0, 1000 * 0.3048, 300.0, 0)
+    ptr = lambda t: C.c_void_p(t.data_ptr())
+    parts = []
+    for r in range(3):
+        o = dict(nconf=torch.empty((E, N), dtype=torch.int32, device='cuda'), nlos=torch.empty((E, N), dtype=torch.int32, device='cuda'),
+                 tcpamax=torch.empty((E, N), dtype=torch.float32, device='cuda'), key=torch.empty((E, N), dtype=torch.int64, device='cuda'))
+        assert lib.bsg_cd_sym_init(C.byref(p), ptr(o['nconf']), ptr(o['nlos']), ptr(o['tcpamax']), ptr(o['key']), None) == 0
+        assert lib.bsg_cd_sym_sweep(C.byref(p), ptr(rec), r, 3, ptr(o['nconf']), ptr(o['nlos']), ptr(o['tcpamax']), ptr(o['key']), None) == 0
+        parts.append(o)
+    torch.cuda.synchronize()
+    nconf = sum(o['nconf'] for o in parts)
+    key = torch.stack([o['key'] for o in parts]).min(0).values
+    tmax = torch.stack([o['tcpamax'].view(torch.int32) for o in parts]).max(0).values.view(torch.float32)
+    assert torch.equal(nconf, full['nconf']) and torch.equal(sum(o['nlos'] for o in parts), full['nlos'])
+    assert torch.equal(tmax, full['tcpamax']) and torch.equal(key, sym['key'])
+
+
 @pytest.mark.parametrize('E,n', [(3, 500), (1, 7)])
 def test_ndmap_bit_exact(orc, E, n):
     from bluesky_gym_hallucination_b200 import core

@@ -91,7 +91,14 @@ def _gloo_worker(rank, world, port, q):
     r0, r1 = sharding.row_block(N, rank, world)
     got = sharding.gather_records(full[:, r0:r1].contiguous(), N, world)
     e0, e1 = sharding.env_shard(10, rank, world)
-    q.put((rank, bool(torch.equal(got, full)), (r0, r1), (e0, e1)))
+    # symmetric sweep: partial outputs of two ranks -> sum / max (float bits) / min (packed key)
+    cnt = torch.full((2, E, N), rank + 1, dtype=torch.int32)
+    tmax = torch.full((E, N), 10.0 * (rank + 1)); tmax[0, 0] = 0.0
+    key = torch.full((E, N), (100 - rank) << 32 | 7, dtype=torch.int64); key[1, 1] = -(5 + rank) << 32
+    sharding.reduce_sym_outputs(cnt, tmax, key)
+    ok = bool((cnt == 3).all()) and float(tmax[0, 0]) == 0.0 and float(tmax[1, 1]) == 20.0 \
+        and int(key[0, 0]) == (99 << 32 | 7) and int(key[1, 1]) == -(6 << 32)
+    q.put((rank, bool(torch.equal(got, full)) and ok, (r0, r1), (e0, e1)))
     dist.destroy_process_group()
 
 
