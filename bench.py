@@ -292,11 +292,19 @@ def run_giant(args):
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
     peak32, _ = bc.peak_fp32(local, 4096)
 
-    sym = not args.ordered_sweep
+    # sweep modes: "peer" (default) = symmetric sweep over NVLink peer memory, loads / atomics to the owners inside the
+    # kernel, two cross-GPU barriers per step; "allreduce" = symmetric sweep + NCCL all-gather + 3 all-reduces;
+    # "ordered" = ordered row block + NCCL all-gather (the baseline design)
+    mode = args.c5_mode
+    sym = mode != 'ordered'
     grp = dist.group.WORLD if world > 1 else None
+    peer = bc.PeerSweep(E, N, rank, world, grp, dev) if mode == 'peer' else None
 
     def one():
         nonlocal out
+        if mode == 'peer':
+            out = peer.step(*mine, 52.0, 4.0)
+            return
         rec = bc.cd_pack(*mine, 52.0, 4.0)                                   # [E, rows, 8]
         full = sharding.gather_records(rec, N, world, buf=rec_all)
         if sym:      # every unordered pair once; tiles dealt round-robin to the ranks, outputs all-reduced
@@ -334,12 +342,15 @@ def run_giant(args):
             "dtype": "f32", "data": "synthetic",
             "config": {"workload": "c5", "description": "giant airspace 16 envs x 10000 aircraft all-pairs CPA, row-block sharded",
                        "sweep": "symmetric: every unordered pair evaluated once, ordered entries reported" if sym else "ordered row block",
-                       "collective": ("none" if world == 1 else "one NCCL all-gather of packed state + "
-                                      + ("3 all-reduces of the row outputs (sum/max/min)" if sym else "no reduce") + " per step"),
+                       "mode": mode,
+                       "collective": ("none" if world == 1 else
+                                      {"peer": "none: records read from / conflict updates flushed to the owning GPU over NVLink peer memory inside the sweep kernel; 2 symmetric-memory barriers per step",
+                                       "allreduce": "one NCCL all-gather of packed state + 3 all-reduces of the row outputs (sum/max/min) per step",
+                                       "ordered": "one NCCL all-gather of packed state per step, no reduce"}[mode]),
                        "l2": "256 MB flush between timed iterations"},
             "roofline": {"bound": "fp32", "achieved": ach, "peak": peak32, "unit": "TFLOP/s", "frac": ach / peak32,
                          "traffic": None, "kernel": ("cd_sym_sweep_kernel" if sym else "cd_sweep_kernel") + " (+ pack, collectives, init/finalize inside the timed step)"},
-            "gpu_launches": (4 if sym else 2) * K, "clocks": clocks}), flush=True)
+            "gpu_launches": (4 if sym else 2) * K + (2 * K if (mode == "peer" and world > 1) else 0), "clocks": clocks}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
@@ -402,7 +413,7 @@ def main():
     ap.add_argument('--steps', type=int, default=2000)
     ap.add_argument('--warmup', type=int, default=20)
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
-    ap.add_argument('--ordered-sweep', action='store_true', help='c5: ordered row-block sweep instead of the symmetric one')
+    ap.add_argument('--c5-mode', default='peer', choices=['peer', 'allreduce', 'ordered'])
     ap.add_argument('--workload', default='c2', choices=sorted(WORKLOADS) + ['c4', 'c5'])
     ap.add_argument('--envs', type=int, default=0, help='override envs per GPU')
     ap.add_argument('--no-cpu', action='store_true', help='skip the cpu_baseline leg')

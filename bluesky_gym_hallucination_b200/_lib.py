@@ -39,6 +39,15 @@ class CdParams(C.Structure):
                 ('rpz_m', C.c_float), ('hpz_m', C.c_float), ('dtlookahead', C.c_float), ('reserved', C.c_int32)]
 
 
+MAX_PEERS = 8
+
+
+class CdPeers(C.Structure):
+    _fields_ = [('num_ranks', C.c_int32), ('rows_per_rank', C.c_int32), ('rec', C.c_void_p * MAX_PEERS),
+                ('nconf', C.c_void_p * MAX_PEERS), ('nlos', C.c_void_p * MAX_PEERS), ('tcpamax', C.c_void_p * MAX_PEERS),
+                ('key', C.c_void_p * MAX_PEERS)]
+
+
 class NdmapParams(C.Structure):
     _fields_ = [('num_envs', C.c_int32), ('num_ac', C.c_int32), ('nx', C.c_int32), ('ny', C.c_int32),
                 ('nz', C.c_int32), ('nt', C.c_int32), ('x0', C.c_float), ('y0', C.c_float), ('z0', C.c_float),
@@ -70,6 +79,8 @@ SYMBOLS = {
     'bsg_cd_sweep': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_init': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_sweep': (_I, [C.POINTER(CdParams), _VP, C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_cd_sym_sweep_peers': (_I, [C.POINTER(CdParams), C.POINTER(CdPeers), C.c_int32, C.c_int32, _VP]),
+    'bsg_cd_sym_finalize_peers': (_I, [C.POINTER(CdParams), C.POINTER(CdPeers), C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_finalize': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_ndmap': (_I, [C.POINTER(NdmapParams), _VP, _VP, _VP, _VP, _VP]),
     'bsg_peak_fp32': (_I, [_I, _I, C.POINTER(C.c_double), C.POINTER(C.c_double)]),

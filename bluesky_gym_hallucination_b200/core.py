@@ -268,3 +268,71 @@ def peak_fp64(device=0, iters=2048):
     tf, ms = C.c_double(0), C.c_double(0)
     L.check(lib.bsg_peak_fp64(device, iters, C.byref(tf), C.byref(ms)))
     return tf.value, ms.value
+
+
+class PeerSweep:
+    """Giant-airspace symmetric sweep over NVLink peer memory (one process per GPU).
+
+    Every rank owns aircraft rows [rank*rows, (rank+1)*rows) of every env.  Its packed records and its row-output
+    accumulators live in ONE symmetric-memory block that every peer maps; the sweep kernel reads the intruder
+    records straight from their owners and flushes the (rare) conflict updates to the owners' accumulators with
+    system-scope atomics, so a step is: pack + init (local) -> barrier -> sweep -> barrier -> finalize (own rows).
+    No all-gather, no all-reduce.  world == 1 uses plain device memory and no barrier."""
+
+    def __init__(self, E, N, rank=0, world=1, group=None, device=None):
+        import torch.distributed as dist
+        if N % world:
+            raise ValueError(f"{N} aircraft do not split into {world} equal row blocks")
+        self.lib = L.load()
+        self.E, self.N, self.rank, self.world, self.rows = E, N, rank, world, N // world
+        dev = torch.device('cuda', torch.cuda.current_device()) if device is None else device
+        n = E * self.rows
+        # block layout (bytes): rec [n][8] f32 | nconf [n] i32 | nlos [n] i32 | tcpamax [n] f32 | key [n] i64
+        off = {'rec': 0, 'nconf': 32 * n, 'nlos': 36 * n, 'tcpamax': 40 * n, 'key': 48 * n}   # key 8-aligned: 44 n -> 48 n
+        nbytes = 56 * n
+        self.h = None
+        if world > 1:
+            import torch.distributed._symmetric_memory as symm
+            self.block = symm.empty((nbytes,), dtype=torch.uint8, device=dev)
+            self.h = symm.rendezvous(self.block, (group or dist.group.WORLD).group_name)
+            bases = list(self.h.buffer_ptrs)
+        else:
+            self.block = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
+            bases = [self.block.data_ptr()]
+        view = lambda key, dt, *shape: self.block[off[key]:off[key] + int(np.prod(shape)) * torch.empty((), dtype=dt).element_size()].view(dt).view(*shape)
+        self.rec = view('rec', torch.float32, E, self.rows, 8)
+        self.nconf = view('nconf', torch.int32, E, self.rows)
+        self.nlos = view('nlos', torch.int32, E, self.rows)
+        self.tcpamax = view('tcpamax', torch.float32, E, self.rows)
+        self.key = view('key', torch.int64, E, self.rows)
+        self.peers = L.CdPeers()
+        self.peers.num_ranks, self.peers.rows_per_rank = world, self.rows
+        for g in range(world):
+            for f in ('rec', 'nconf', 'nlos', 'tcpamax', 'key'):
+                getattr(self.peers, f)[g] = bases[g] + off[f]
+        self.out = dict(inconf=torch.empty((E, self.rows), dtype=torch.uint8, device=dev),
+                        near_idx=torch.empty((E, self.rows), dtype=torch.int32, device=dev),
+                        near_tcpa=torch.empty((E, self.rows), dtype=torch.float32, device=dev),
+                        near_dcpa=torch.empty((E, self.rows), dtype=torch.float32, device=dev),
+                        near_tin=torch.empty((E, self.rows), dtype=torch.float32, device=dev),
+                        nconf=self.nconf, nlos=self.nlos, tcpamax=self.tcpamax)
+
+    def step(self, lat, lon, alt, trk, gs, vs, lat0, lon0, rpz_m=5 * 1852.0, hpz_m=1000 * 0.3048, dtlookahead=300.0):
+        """SoA CUDA tensors [E, rows] of the OWN aircraft -> row outputs [E, rows] of the own rows."""
+        lib, E, dev = self.lib, self.E, self.block.device
+        s = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+        own = L.CdParams(E, self.rows, 0, self.rows, rpz_m, hpz_m, dtlookahead, 0)
+        full = L.CdParams(E, self.N, 0, self.N, rpz_m, hpz_m, dtlookahead, 0)
+        L.check(lib.bsg_cd_pack(E, self.rows, _ptr(lat), _ptr(lon), _ptr(alt), _ptr(trk), _ptr(gs), _ptr(vs), float(lat0),
+                                float(lon0), _ptr(self.rec), s))
+        L.check(lib.bsg_cd_sym_init(C.byref(own), _ptr(self.nconf), _ptr(self.nlos), _ptr(self.tcpamax), _ptr(self.key), s))
+        if self.h is not None:
+            self.h.barrier(channel=0)                  # every rank's records packed, accumulators initialised
+        L.check(lib.bsg_cd_sym_sweep_peers(C.byref(full), C.byref(self.peers), self.rank, self.world, s))
+        if self.h is not None:
+            self.h.barrier(channel=1)                  # every rank's atomics have landed
+        o = self.out
+        L.check(lib.bsg_cd_sym_finalize_peers(C.byref(full), C.byref(self.peers), self.rank, _ptr(o['inconf']),
+                                              _ptr(o['near_idx']), _ptr(o['near_tcpa']), _ptr(o['near_dcpa']),
+                                              _ptr(o['near_tin']), s))
+        return o

@@ -164,9 +164,23 @@ __global__ void cd_sym_init_kernel(size_t n, int32_t *nconf, int32_t *nlos, int3
     nconf[k] = 0; nlos[k] = 0; tcpamax_bits[k] = 0; key[k] = 0x7fffffffffffffffLL;
 }
 
-__global__ void __launch_bounds__(kSymT) cd_sym_sweep_kernel(const bsg_cd_params p, const RecFast *__restrict__ rec,
-                                                            int tile_rank, int tile_stride, int32_t *nconf,
-                                                            int32_t *nlos, int32_t *tcpamax_bits, long long *key) {
+// Peer tables: aircraft j of env e lives on rank g = j / rows at local slot j - g*rows; records are read from, and
+// row outputs flushed to, the owner's buffers (plain device pointers at G = 1, NVLink peer mappings of symmetric
+// memory at G > 1: the all-gather of the state and the reduce of the outputs become loads / atomics over NVLink
+// inside this one kernel).  System-scope atomics: the targets may live on another GPU.
+struct SymPeers {
+    int G, rows;
+    const RecFast *rec[BSG_MAX_PEERS];
+    int32_t *nconf[BSG_MAX_PEERS], *nlos[BSG_MAX_PEERS], *tmax[BSG_MAX_PEERS];
+    long long *key[BSG_MAX_PEERS];
+};
+__device__ __forceinline__ void sym_locate(const SymPeers &Q, int e, int j, int &g, size_t &k) {
+    g = Q.G == 1 ? 0 : j / Q.rows;
+    k = (size_t)e * Q.rows + (j - g * Q.rows);
+}
+
+__global__ void __launch_bounds__(kSymT) cd_sym_sweep_kernel(const bsg_cd_params p, const SymPeers Q, int tile_rank,
+                                                            int tile_stride) {
     __shared__ float4 tA[kSymT], tB[kSymT];
     __shared__ int c_nconf[kSymT], c_nlos[kSymT], c_tmax[kSymT];
     __shared__ long long c_key[kSymT];
@@ -176,18 +190,20 @@ __global__ void __launch_bounds__(kSymT) cd_sym_sweep_kernel(const bsg_cd_params
     int bi = 0;
     while (t >= nb - bi) { t -= nb - bi; bi++; }
     const int bj = bi + t, r = threadIdx.x;
-    const RecFast *base = rec + (size_t)e * N;
     const int i = bi * kSymT + r, j0 = bj * kSymT, nt = min(kSymT, N - j0);
     const bool rowok = i < N;
+    int g; size_t kk;
     if (r < nt) {
-        const float4 *m = reinterpret_cast<const float4 *>(base + j0 + r);
-        tA[r] = __ldg(m); tB[r] = __ldg(m + 1);
+        sym_locate(Q, e, j0 + r, g, kk);
+        const float4 *m = reinterpret_cast<const float4 *>(Q.rec[g] + kk);
+        tA[r] = m[0]; tB[r] = m[1];
     }
     c_nconf[r] = 0; c_nlos[r] = 0; c_tmax[r] = 0; c_key[r] = 0x7fffffffffffffffLL;
     RecFast me = {};
     if (rowok) {
-        const float4 *m = reinterpret_cast<const float4 *>(base + i);
-        const float4 a = __ldg(m), b = __ldg(m + 1);
+        sym_locate(Q, e, i, g, kk);
+        const float4 *m = reinterpret_cast<const float4 *>(Q.rec[g] + kk);
+        const float4 a = m[0], b = m[1];
         me = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w };
     }
     CdParamsF P;
@@ -229,36 +245,38 @@ __global__ void __launch_bounds__(kSymT) cd_sym_sweep_kernel(const bsg_cd_params
     }
     __syncthreads();
     if (rowok && acc.nconf > 0) {                            // rows of this tile
-        const size_t k = (size_t)e * N + i;
-        atomicAdd(&nconf[k], acc.nconf);
-        if (acc.nlos) atomicAdd(&nlos[k], acc.nlos);
-        atomicMax(&tcpamax_bits[k], __float_as_int(acc.tcpamax));
-        atomicMin(&key[k], sym_key(acc.near_tcpa, acc.near_idx));
+        sym_locate(Q, e, i, g, kk);
+        atomicAdd_system(&Q.nconf[g][kk], acc.nconf);
+        if (acc.nlos) atomicAdd_system(&Q.nlos[g][kk], acc.nlos);
+        atomicMax_system(&Q.tmax[g][kk], __float_as_int(acc.tcpamax));
+        atomicMin_system(&Q.key[g][kk], sym_key(acc.near_tcpa, acc.near_idx));
     }
     if (r < nt && c_nconf[r] > 0) {                          // columns of this tile
-        const size_t k = (size_t)e * N + j0 + r;
-        atomicAdd(&nconf[k], c_nconf[r]);
-        if (c_nlos[r]) atomicAdd(&nlos[k], c_nlos[r]);
-        atomicMax(&tcpamax_bits[k], c_tmax[r]);
-        atomicMin(&key[k], c_key[r]);
+        sym_locate(Q, e, j0 + r, g, kk);
+        atomicAdd_system(&Q.nconf[g][kk], c_nconf[r]);
+        if (c_nlos[r]) atomicAdd_system(&Q.nlos[g][kk], c_nlos[r]);
+        atomicMax_system(&Q.tmax[g][kk], c_tmax[r]);
+        atomicMin_system(&Q.key[g][kk], c_key[r]);
     }
 }
 
-__global__ void cd_sym_finalize_kernel(const bsg_cd_params p, const RecFast *__restrict__ rec, const int32_t *nconf,
-                                       const long long *key, uint8_t *inconf, int32_t *near_idx, float *near_tcpa,
-                                       float *near_dcpa, float *near_tin) {
-    const int N = p.num_ac;
+__global__ void cd_sym_finalize_kernel(const bsg_cd_params p, const SymPeers Q, int rank, uint8_t *inconf,
+                                       int32_t *near_idx, float *near_tcpa, float *near_dcpa, float *near_tin) {
+    // one thread per OWN row (e, il): outputs are [E][rows] of this rank
     const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (k >= (size_t)p.num_envs * N) return;
-    const long long ky = key[k];
+    if (k >= (size_t)p.num_envs * Q.rows) return;
+    const long long ky = Q.key[rank][k];
+    const int nc = Q.nconf[rank][k];
     int j = -1;
     float tc = 0.0f, dc = 0.0f, ti = 0.0f;
-    if (nconf[k] > 0) {
+    if (nc > 0) {
         j = (int)(unsigned)(ky & 0xffffffffLL);
         tc = sym_key_tcpa(ky);
-        const size_t e = k / N;
-        const float4 *m = reinterpret_cast<const float4 *>(rec + k), *n = reinterpret_cast<const float4 *>(rec + e * N + j);
-        const float4 a = __ldg(m), b = __ldg(m + 1), c = __ldg(n), d = __ldg(n + 1);
+        const int e = (int)(k / Q.rows);
+        int g; size_t kj;
+        sym_locate(Q, e, j, g, kj);
+        const float4 *m = reinterpret_cast<const float4 *>(Q.rec[rank] + k), *n = reinterpret_cast<const float4 *>(Q.rec[g] + kj);
+        const float4 a = m[0], b = m[1], c = n[0], d = n[1];
         const RecFast me = { a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w }, o = { c.x, c.y, c.z, c.w, d.x, d.y, d.z, d.w };
         CdParamsF P;
         P.R2 = p.rpz_m * p.rpz_m; P.hpz = p.hpz_m; P.dtlook = p.dtlookahead; P.rpz = p.rpz_m; P.rpz_m = 0; P.hpz_m = 0;
@@ -266,7 +284,7 @@ __global__ void cd_sym_finalize_kernel(const bsg_cd_params p, const RecFast *__r
         pair_fast_core(me, o, P, true, pc);
         dc = sqrtf(pc.dcpa2); ti = pc.tin;
     }
-    if (inconf) inconf[k] = nconf[k] > 0;
+    if (inconf) inconf[k] = nc > 0;
     if (near_idx) near_idx[k] = j;
     if (near_tcpa) near_tcpa[k] = tc;
     if (near_dcpa) near_dcpa[k] = dc;
@@ -348,28 +366,58 @@ int bsg_cd_sym_init(const bsg_cd_params *p, int32_t *nconf, int32_t *nlos, float
     return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
 }
 
-int bsg_cd_sym_sweep(const bsg_cd_params *p, const float *rec, int32_t tile_rank, int32_t tile_stride, int32_t *nconf,
-                     int32_t *nlos, float *tcpamax, int64_t *key, void *stream) {
-    if (!p || !rec || !nconf || !nlos || !tcpamax || !key || p->num_envs < 1 || p->num_ac < 1 || tile_stride < 1 ||
-        tile_rank < 0 || tile_rank >= tile_stride)
+static bool sym_peers_from(const bsg_cd_params *p, const bsg_cd_peers *q, SymPeers &Q) {
+    if (!q || q->num_ranks < 1 || q->num_ranks > BSG_MAX_PEERS || q->rows_per_rank < 1 ||
+        (long)q->rows_per_rank * q->num_ranks != p->num_ac)
+        return false;
+    Q.G = q->num_ranks; Q.rows = q->rows_per_rank;
+    for (int g = 0; g < Q.G; g++) {
+        if (!q->rec[g] || !q->nconf[g] || !q->nlos[g] || !q->tcpamax[g] || !q->key[g]) return false;
+        Q.rec[g] = reinterpret_cast<const RecFast *>(q->rec[g]);
+        Q.nconf[g] = q->nconf[g]; Q.nlos[g] = q->nlos[g]; Q.tmax[g] = (int32_t *)q->tcpamax[g]; Q.key[g] = (long long *)q->key[g];
+    }
+    return true;
+}
+
+int bsg_cd_sym_sweep_peers(const bsg_cd_params *p, const bsg_cd_peers *q, int32_t tile_rank, int32_t tile_stride, void *stream) {
+    SymPeers Q;
+    if (!p || p->num_envs < 1 || p->num_ac < 1 || tile_stride < 1 || tile_rank < 0 || tile_rank >= tile_stride ||
+        !sym_peers_from(p, q, Q))
         return BSG_ERR_ARG;
     const int nb = (p->num_ac + kSymT - 1) / kSymT, ntile = nb * (nb + 1) / 2;
     dim3 grid((ntile + tile_stride - 1) / tile_stride, p->num_envs);
-    cd_sym_sweep_kernel<<<grid, kSymT, 0, (cudaStream_t)stream>>>(*p, reinterpret_cast<const RecFast *>(rec), tile_rank,
-                                                                  tile_stride, nconf, nlos, (int32_t *)tcpamax,
-                                                                  (long long *)key);
+    cd_sym_sweep_kernel<<<grid, kSymT, 0, (cudaStream_t)stream>>>(*p, Q, tile_rank, tile_stride);
     return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+int bsg_cd_sym_finalize_peers(const bsg_cd_params *p, const bsg_cd_peers *q, int32_t rank, uint8_t *inconf,
+                              int32_t *near_idx, float *near_tcpa, float *near_dcpa, float *near_tin, void *stream) {
+    SymPeers Q;
+    if (!p || p->num_envs < 1 || p->num_ac < 1 || !sym_peers_from(p, q, Q) || rank < 0 || rank >= Q.G) return BSG_ERR_ARG;
+    const size_t n = (size_t)p->num_envs * Q.rows;
+    cd_sym_finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(*p, Q, rank, inconf, near_idx,
+                                                                                           near_tcpa, near_dcpa, near_tin);
+    return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+int bsg_cd_sym_sweep(const bsg_cd_params *p, const float *rec, int32_t tile_rank, int32_t tile_stride, int32_t *nconf,
+                     int32_t *nlos, float *tcpamax, int64_t *key, void *stream) {
+    if (!p) return BSG_ERR_ARG;
+    bsg_cd_peers q = {};
+    q.num_ranks = 1; q.rows_per_rank = p->num_ac;
+    q.rec[0] = rec; q.nconf[0] = nconf; q.nlos[0] = nlos; q.tcpamax[0] = tcpamax; q.key[0] = key;
+    return bsg_cd_sym_sweep_peers(p, &q, tile_rank, tile_stride, stream);
 }
 
 int bsg_cd_sym_finalize(const bsg_cd_params *p, const float *rec, const int32_t *nconf, const int64_t *key,
                         uint8_t *inconf, int32_t *near_idx, float *near_tcpa, float *near_dcpa, float *near_tin,
                         void *stream) {
-    if (!p || !rec || !nconf || !key || p->num_envs < 1 || p->num_ac < 1) return BSG_ERR_ARG;
-    const size_t n = (size_t)p->num_envs * p->num_ac;
-    cd_sym_finalize_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
-        *p, reinterpret_cast<const RecFast *>(rec), nconf, (const long long *)key, inconf, near_idx, near_tcpa, near_dcpa,
-        near_tin);
-    return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+    if (!p || !rec || !nconf || !key) return BSG_ERR_ARG;
+    bsg_cd_peers q = {};
+    q.num_ranks = 1; q.rows_per_rank = p->num_ac;
+    q.rec[0] = rec; q.nconf[0] = const_cast<int32_t *>(nconf); q.nlos[0] = const_cast<int32_t *>(nconf);
+    q.tcpamax[0] = reinterpret_cast<float *>(const_cast<int32_t *>(nconf)); q.key[0] = const_cast<int64_t *>(key);
+    return bsg_cd_sym_finalize_peers(p, &q, 0, inconf, near_idx, near_tcpa, near_dcpa, near_tin, stream);
 }
 
 }  // extern "C"

@@ -159,6 +159,27 @@ int bsg_cd_sym_finalize(const bsg_cd_params *p, const float *rec_dev, const int3
                         uint8_t *inconf_dev, int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev,
                         float *near_tin_dev, void *stream);
 
+/* The same symmetric sweep over PEER memory (one process per GPU, NVLink): aircraft j of every env lives on rank
+ * j / rows_per_rank; rec / nconf / nlos / tcpamax / key [g] are device pointers to rank g's [E][rows_per_rank] buffers
+ * as mapped into THIS process (symmetric-memory peer mappings; the local ones for g == own rank).  The sweep reads
+ * the records from their owners and flushes the (rare) conflict updates to the owners' outputs with system-scope
+ * atomics: no all-gather and no all-reduce, only a cross-GPU barrier before (records packed, outputs initialised
+ * with bsg_cd_sym_init on the own block) and after the sweep.  finalize writes the outputs of the OWN rows
+ * [E][rows_per_rank]. */
+#define BSG_MAX_PEERS 8
+typedef struct bsg_cd_peers {
+    int32_t num_ranks, rows_per_rank;
+    const float *rec[BSG_MAX_PEERS];
+    int32_t *nconf[BSG_MAX_PEERS], *nlos[BSG_MAX_PEERS];
+    float *tcpamax[BSG_MAX_PEERS];
+    int64_t *key[BSG_MAX_PEERS];
+} bsg_cd_peers;
+int bsg_cd_sym_sweep_peers(const bsg_cd_params *p, const bsg_cd_peers *peers, int32_t tile_rank, int32_t tile_stride,
+                           void *stream);
+int bsg_cd_sym_finalize_peers(const bsg_cd_params *p, const bsg_cd_peers *peers, int32_t rank, uint8_t *inconf_dev,
+                              int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev, float *near_tin_dev,
+                              void *stream);
+
 /* ND-map: rec_dev float [E][6][n] (x, y, z, u, v, w); occ/conf uint8 [E][nt][nz][ny][nx]; ncell int32 [E][nt] */
 int bsg_ndmap(const bsg_ndmap_params *p, const float *rec_dev, uint8_t *occ_dev, uint8_t *conf_dev,
               int32_t *ncell_dev, void *stream);

@@ -97,6 +97,23 @@ def test_cd_sweep_symmetric_equals_ordered(E, N, box):
     assert torch.equal(tmax, full['tcpamax']) and torch.equal(key, sym['key'])
 
 
+def test_peer_sweep_single_rank_equals_ordered():
+    """PeerSweep (peer-table form of the symmetric sweep; world 1 = plain device memory) == ordered sweep, bitwise."""
+    from bluesky_gym_hallucination_b200 import core, scenario as sc
+    E, N = 2, 900
+    lat, lon, alt, trk, gs, vs = sc.raw_traffic(E, N, seed=21, box_nm=250.0)
+    rec = _pack(lat, lon, alt, trk, gs, vs)
+    full = core.cd_sweep(rec)
+    t64 = lambda a: torch.as_tensor(np.ascontiguousarray(a), dtype=torch.float64, device='cuda')
+    t32 = lambda a: torch.as_tensor(np.ascontiguousarray(a), dtype=torch.float32, device='cuda')
+    ps = core.PeerSweep(E, N)
+    out = ps.step(t64(lat), t64(lon), t32(alt), t32(trk), t32(gs), t32(vs), 52.0, 4.0)
+    torch.cuda.synchronize()
+    assert int(full['nconf'].sum()) > 0
+    for k in ('inconf', 'nconf', 'nlos', 'near_idx', 'near_tcpa', 'near_dcpa', 'near_tin', 'tcpamax'):
+        assert torch.equal(full[k], out[k]), k
+
+
 @pytest.mark.parametrize('E,n', [(3, 500), (1, 7)])
 def test_ndmap_bit_exact(orc, E, n):
     from bluesky_gym_hallucination_b200 import core

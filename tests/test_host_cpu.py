@@ -26,6 +26,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(_lib.Config) == 12 * 4 + 6 * 8
     assert C.sizeof(_lib.StepOut) == 14 * 8
     assert C.sizeof(_lib.CdParams) == 32 and C.sizeof(_lib.NdmapParams) == 14 * 4
+    assert C.sizeof(_lib.CdPeers) == 8 + 5 * 8 * _lib.MAX_PEERS
     assert _lib.NF == 18 and _lib.NE == 14 + 64
 
 
