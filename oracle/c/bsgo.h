@@ -21,9 +21,13 @@
 
 enum { F_LAT, F_LON, F_ALT, F_HDG, F_TAS, F_VS, F_CAS, F_SELSPD, F_SELALT, F_SELVS, F_APTRK, F_AX,
        F_ASAS_TRK, F_ASAS_TAS, F_ASAS_VS, F_ASAS_ALT, F_ASAS_ACTIVE,
-       F_PHASE /* flight phase of the last perf.update (MVP caps use it one substep later) */, BSGO_NF };
+       F_PHASE /* flight phase of the last perf.update (MVP caps use it one substep later) */,
+       F_GSN, F_GSE /* ground-speed vector of the last update_groundspeed (= tas*(cos,sin)(hdg) without wind) */,
+       F_LNAV /* LNAV: index of the active route waypoint, -1 = LNAV off (Merge intruders: 0 = FAF, 1 = runway) */,
+       BSGO_NF };
 
 #define BSGO_MAXV 32
+/* Merge reuses: EV_WPT_LAT/LON = FAF, EV_WPT_X/Y = runway lat/lon, EV_WPT_REACH = wpt_reach, EV_FINAL_ALT = faf_reached */
 enum { EV_WPT_LAT, EV_WPT_LON, EV_WPT_REACH, EV_AC_HDG,      /* Horizontal */
        EV_TARGET_ALT,                                         /* Vertical */
        EV_WPT_X, EV_WPT_Y, EV_NVERT,                          /* Sector: own waypoint [NM], polygon size */
@@ -31,11 +35,16 @@ enum { EV_WPT_LAT, EV_WPT_LON, EV_WPT_REACH, EV_AC_HDG,      /* Horizontal */
        EV_POLY,                                               /* 2*BSGO_MAXV slots: lat0,lon0,lat1,lon1,... */
        BSGO_NE = EV_POLY + 2 * BSGO_MAXV };
 
-enum { KIND_H = 0, KIND_V = 1, KIND_S = 2, KIND_RAW = 3 };
+enum { KIND_H = 0, KIND_V = 1, KIND_S = 2, KIND_RAW = 3, KIND_M = 4 /* MergeEnv (merge_env.py) */ };
 
+#define BSGO_MAXWIND 8
 typedef struct {
     int32_t kind, n, substeps, asas_on, reso_on, reso_off_own;
     double simdt, rpz, hpz, dtlook, resofach, resofacv;
+    /* wind field of the WindFieldWrapper (bluesky_gym/wrappers/wind.py:28): nwind points, no altitude profile;
+     * wind_obs = augment_obs (two more observation slots: wind_u, wind_v) */
+    int32_t nwind, wind_obs;
+    double wlat[BSGO_MAXWIND], wlon[BSGO_MAXWIND], wvn[BSGO_MAXWIND], wve[BSGO_MAXWIND];
 } bsgo_cfg;
 
 /* per-aircraft CD outputs of the last detection of a step */
@@ -48,7 +57,8 @@ typedef struct {
     double *tcpamax;      /* [E][N] */
 } bsgo_cdout;
 
-int bsgo_obs_dim(int kind, int n);
+int bsgo_obs_dim(int kind, int n);   /* without the wind_obs slots */
+int bsgo_obs_dim_cfg(const bsgo_cfg *cfg);
 
 /* aero */
 double bsgo_vcas2tas(double cas, double h);
@@ -56,6 +66,8 @@ double bsgo_vtas2cas(double tas, double h);
 double bsgo_vcasormach2tas(double spd, double h);
 /* geo */
 void bsgo_kwikqdrdist(double lata, double lona, double latb, double lonb, double *qdr, double *dist_nm);
+void bsgo_qdrdist(double lat1, double lon1, double lat2, double lon2, double *qdr, double *dist_nm);   /* WGS-84 great circle */
+void bsgo_wind(const bsgo_cfg *cfg, double lat, double lon, double *vn, double *ve);
 
 /* one full CD matrix for one env (dense outputs, row-major n x n); any pointer may be NULL */
 void bsgo_detect_dense(int n, const double *lat, const double *lon, const double *alt,

@@ -47,10 +47,11 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
     double *v = u + nlive, *dve = v + nlive, *dvn = dve + nlive, *dvz = dvn + nlive;
     uint64_t *confrow = calloc(nlive, sizeof(uint64_t));
     int anyconf = 0;
+    const int wind = cfg->nwind > 0;
     for (int i = 0; i < nlive; i++) {
-        /* gs = tas, trk = hdg (no wind) */
-        u[i] = A(F_TAS, i) * sin(A(F_HDG, i) * C_D2R);
-        v[i] = A(F_TAS, i) * cos(A(F_HDG, i) * C_D2R);
+        /* gs = tas, trk = hdg (no wind); with a wind field the ground-speed vector of the last update */
+        u[i] = wind ? A(F_GSE, i) : A(F_TAS, i) * sin(A(F_HDG, i) * C_D2R);
+        v[i] = wind ? A(F_GSN, i) : A(F_TAS, i) * cos(A(F_HDG, i) * C_D2R);
         dve[i] = dvn[i] = dvz[i] = 0.0;
     }
     for (int i = 0; i < nlive; i++) {
@@ -58,7 +59,7 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
         r->inconf = 0; r->nconf = 0; r->nlos = 0; r->near_idx = -1;
         r->near_tcpa = r->near_dcpa = r->near_tin = r->tcpamax = 0.0;
         /* velocity vectors as MVP sees them: gseast/gsnorth of the last update_groundspeed */
-        double v1[3] = { A(F_TAS, i) * sin(A(F_HDG, i) * C_D2R), A(F_TAS, i) * cos(A(F_HDG, i) * C_D2R), A(F_VS, i) };
+        double v1[3] = { u[i], v[i], A(F_VS, i) };
         for (int j = 0; j < nlive; j++) {
             if (j == i) continue;
             double qdr, dist, tcpa, dcpa2, tin;
@@ -76,7 +77,7 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
             }
             if (n <= 64) confrow[i] |= (uint64_t)1 << j;
             if (cfg->reso_on) {
-                double v2[3] = { A(F_TAS, j) * sin(A(F_HDG, j) * C_D2R), A(F_TAS, j) * cos(A(F_HDG, j) * C_D2R), A(F_VS, j) };
+                double v2[3] = { u[j], v[j], A(F_VS, j) };
                 double dv[3], tsolV;
                 mvp_pair(qdr, dist, tcpa, tin, A(F_ALT, i), A(F_ALT, j), v1, v2,
                          cfg->rpz, cfg->hpz, cfg->dtlook, cfg->resofach, cfg->resofacv, dv, &tsolV);
@@ -89,7 +90,7 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
     if (cfg->reso_on) {
         if (anyconf) {
             for (int i = 0; i < nlive; i++) {
-                double ge = A(F_TAS, i) * sin(A(F_HDG, i) * C_D2R), gn = A(F_TAS, i) * cos(A(F_HDG, i) * C_D2R);
+                double ge = u[i], gn = v[i];
                 double ne = ge + dve[i], nn = gn + dvn[i];
                 double newtrack = bsgo_pymod(atan2(ne, nn) * 180 / C_PI, 360);
                 double newgs = sqrt(ne * ne + nn * nn);

@@ -3,6 +3,8 @@
  *   Horizontal: /root/reference/bluesky_gym/envs/horizontal_cr_env.py:150-275
  *   Vertical  : /root/reference/bluesky_gym/envs/vertical_cr_env.py:113-256
  *   Sector    : /root/reference/bluesky_gym/envs/sector_cr_env.py:134-139,227-339
+ *   Merge     : /root/reference/bluesky_gym/envs/merge_env.py:160-293 (19 intruders, the 5 nearest observed)
+ *   wind obs  : /root/reference/bluesky_gym/wrappers/wind.py:55-64
  *   helpers   : /root/reference/bluesky_gym/envs/common/functions.py:4-22,98-132
  * Pinned by the tests/golden npz fixtures (unmodified reference classes run on oracle/refshim). */
 #include <math.h>
@@ -20,7 +22,20 @@ int bsgo_obs_dim(int kind, int n) {
     if (kind == KIND_H) return 5 * k + 3;
     if (kind == KIND_V) return 4 + 7 * k;
     if (kind == KIND_S) return 3 + 7 * 4;
+    if (kind == KIND_M) return 5 + 7 * 5;
     return 0;
+}
+int bsgo_obs_dim_cfg(const bsgo_cfg *c) { return bsgo_obs_dim(c->kind, c->n) + (c->wind_obs ? 2 : 0); }
+/* AP.selhdgcmd: the HDG argument becomes the track it gives in the current wind (above 50 ft) */
+static double hdg_cmd(const bsgo_cfg *c, const double *a, double hdg) {
+    int n = c->n;
+    if (c->nwind > 0 && a[F_ALT * n] > 50.0 * C_FT) {
+        double vn, ve;
+        bsgo_wind(c, a[F_LAT * n], a[F_LON * n], &vn, &ve);
+        double gn = a[F_TAS * n] * cos(hdg * C_D2R) + vn, ge = a[F_TAS * n] * sin(hdg * C_D2R) + ve;
+        return bsgo_pymod(atan2(ge, gn) * C_R2D, 360.0);
+    }
+    return hdg;
 }
 static double bound180(double a) {  /* functions.py:17-22: wraps once only */
     if (a > 180) return -(360 - a);
@@ -50,14 +65,20 @@ static int poly_inside(const double *poly, int nv, double tx, double ty) {
 static void apply_action(const bsgo_cfg *c, double *a, double *ev, const double *act) {
     int n = c->n;
     if (c->kind == KIND_H) {            /* horizontal_cr_env.py:272-275: HDG from the cached ac_hdg */
-        A(F_APTRK, 0) = ev[EV_AC_HDG] + act[0] * 45;
+        A(F_APTRK, 0) = hdg_cmd(c, a, ev[EV_AC_HDG] + act[0] * 45);
     } else if (c->kind == KIND_V) {     /* vertical_cr_env.py:242-256 */
         double v = act[0] * 12.5;
         A(F_SELALT, 0) = v >= 0 ? 1000000 : 0;
         A(F_SELVS, 0) = v;
     } else if (c->kind == KIND_S) {     /* sector_cr_env.py:315-322 (SPD arg in kts, parsed back with kts) */
         double dh = act[0] * 22.5, dv = act[1] * (20.0 / 3);
-        A(F_APTRK, 0) = bound180(A(F_HDG, 0) + dh);
+        A(F_APTRK, 0) = hdg_cmd(c, a, bound180(A(F_HDG, 0) + dh));
+        double spd_kts = (A(F_CAS, 0) + dv) * 1.94384;
+        A(F_SELSPD, 0) = fabs(spd_kts) > 1.0 ? spd_kts * C_KTS : spd_kts;
+    } else if (c->kind == KIND_M) {     /* merge_env.py:285-293; the HDG command switches LNAV off */
+        double dh = act[0] * 15, dv = act[1] * 20;
+        A(F_APTRK, 0) = hdg_cmd(c, a, bound180(A(F_HDG, 0) + dh));
+        A(F_LNAV, 0) = -1.0;
         double spd_kts = (A(F_CAS, 0) + dv) * 1.94384;
         A(F_SELSPD, 0) = fabs(spd_kts) > 1.0 ? spd_kts * C_KTS : spd_kts;
     }
@@ -88,8 +109,13 @@ static double observe_env(const bsgo_cfg *c, const double *a, int nlive, double 
             o_cos[k] = cos(brg * C_D2R);
             o_sin[k] = sin(brg * C_D2R);
             double hd = hdg0 - A(F_HDG, j);
-            o_x[k] = (-cos(hd * C_D2R) * A(F_TAS, j)) / AC_SPD;
-            o_y[k] = (A(F_TAS, 0) - sin(hd * C_D2R) * A(F_TAS, j)) / AC_SPD;
+            double gsj = A(F_TAS, j), gs0 = A(F_TAS, 0);                  /* bs.traf.gs: the ground speed under wind */
+            if (c->nwind > 0) {
+                gsj = sqrt(A(F_GSN, j) * A(F_GSN, j) + A(F_GSE, j) * A(F_GSE, j));
+                gs0 = sqrt(A(F_GSN, 0) * A(F_GSN, 0) + A(F_GSE, 0) * A(F_GSE, 0));
+            }
+            o_x[k] = (-cos(hd * C_D2R) * gsj) / AC_SPD;
+            o_y[k] = (gs0 - sin(hd * C_D2R) * gsj) / AC_SPD;
             if (o_dalt) { o_dalt[k] = (A(F_ALT, j) - A(F_ALT, 0)) / 3000.0; o_z[k] = A(F_VS, j) - A(F_VS, 0); }
         }
         if (c->kind == KIND_H) {
@@ -154,6 +180,52 @@ static double observe_env(const bsgo_cfg *c, const double *a, int nlive, double 
             o[6 * 4 + s] = (dist[best] - 50000.) / 15000.;
         }
         free(dist);
+    } else if (c->kind == KIND_M) {     /* merge_env.py:160-236 */
+        int w = ev[EV_WPT_REACH] == 0.0 ? 0 : 1;
+        double wlat = w == 0 ? ev[EV_WPT_LAT] : ev[EV_WPT_X], wlon = w == 0 ? ev[EV_WPT_LON] : ev[EV_WPT_Y];
+        double qdr, d, hdg0 = A(F_HDG, 0);
+        bsgo_kwikqdrdist(A(F_LAT, 0), A(F_LON, 0), wlat, wlon, &qdr, &d);
+        drift = bound180(hdg0 - qdr);
+        obs[0] = cos(drift * C_D2R);
+        obs[1] = sin(drift * C_D2R);
+        obs[2] = A(F_TAS, 0);
+        obs[3] = d / 250;
+        obs[4] = ev[EV_WPT_REACH];
+        double vx = cos(hdg0 * C_D2R) * A(F_TAS, 0), vy = sin(hdg0 * C_D2R) * A(F_TAS, 0);
+        double *dist = malloc(sizeof(double) * (nlive > 1 ? nlive : 1));
+        for (int j = 1; j < nlive; j++) {
+            double q2;
+            bsgo_kwikqdrdist(A(F_LAT, 0), A(F_LON, 0), A(F_LAT, j), A(F_LON, j), &q2, &dist[j]);
+        }
+        for (int s = 0; s < 5; s++) {                /* stable argsort: rank by (distance, index) */
+            int best = -1;
+            for (int j = 1; j < nlive; j++) {
+                int rank = 0;
+                for (int m = 1; m < nlive; m++)
+                    if (dist[m] < dist[j] || (dist[m] == dist[j] && m < j)) rank++;
+                if (rank == s) { best = j; break; }
+            }
+            double *o = obs + 5;
+            if (best < 0) { for (int q = 0; q < 7; q++) o[q * 5 + s] = 0; continue; }
+            double brg, dd;
+            bsgo_kwikqdrdist(A(F_LAT, 0), A(F_LON, 0), A(F_LAT, best), A(F_LON, best), &brg, &dd);
+            double vxi = cos(A(F_HDG, best) * C_D2R) * A(F_TAS, best), vyi = sin(A(F_HDG, best) * C_D2R) * A(F_TAS, best);
+            double trk = atan2(vyi - vy, vxi - vx);
+            o[0 * 5 + s] = (dd * NM2KM * 1000) * cos(brg * C_D2R) / 1000000;
+            o[1 * 5 + s] = (dd * NM2KM * 1000) * sin(brg * C_D2R) / 1000000;
+            o[2 * 5 + s] = (vxi - vx) / 150;
+            o[3 * 5 + s] = (vyi - vy) / 150;
+            o[4 * 5 + s] = cos(trk);
+            o[5 * 5 + s] = sin(trk);
+            o[6 * 5 + s] = dist[best] / 250;
+        }
+        free(dist);
+    }
+    if (c->wind_obs) {                  /* wrappers/wind.py:55-64: wind in the agent's body axes / MAX_WIND */
+        double *o = obs + bsgo_obs_dim(c->kind, c->n), wn, we, h = A(F_HDG, 0) * C_D2R;
+        bsgo_wind(c, A(F_LAT, 0), A(F_LON, 0), &wn, &we);
+        o[0] = (wn * cos(h) + we * sin(h)) / 50;
+        o[1] = (-wn * sin(h) + we * cos(h)) / 50;
     }
     return drift;
 }
@@ -205,6 +277,25 @@ static void reward_env(const bsgo_cfg *c, const double *a, int nlive, double *ev
         *reward = dr * -0.1 + intr;
         ev[EV_TOTAL_REWARD] += *reward;
         *trunc = poly_inside(ev + EV_POLY, (int)ev[EV_NVERT], A(F_LAT, 0), A(F_LON, 0)) ? 0 : 1;
+    } else if (c->kind == KIND_M) {     /* merge_env.py:238-283 */
+        double reach = 0, wdist = obs[3] * 250;
+        double qdr, d;
+        {   /* self.waypoint_dist of the _get_obs that just ran: recompute exactly */
+            int w = ev[EV_WPT_REACH] == 0.0 ? 0 : 1;
+            bsgo_kwikqdrdist(A(F_LAT, 0), A(F_LON, 0), w == 0 ? ev[EV_WPT_LAT] : ev[EV_WPT_X],
+                             w == 0 ? ev[EV_WPT_LON] : ev[EV_WPT_Y], &qdr, &wdist);
+        }
+        if (wdist < 10 && ev[EV_WPT_REACH] != 1) { ev[EV_WPT_REACH] = 1; ev[EV_FINAL_ALT] = 1; reach += 1; }
+        else if (wdist < 20 && ev[EV_WPT_REACH] == 1) { ev[EV_FINAL_ALT] = 2; *term = 1; }
+        double dr = fabs(drift * C_D2R);
+        ev[EV_DRIFT_SUM] += dr; ev[EV_DRIFT_CNT] += 1;
+        double intr = 0;
+        for (int j = 1; j < nlive; j++) {
+            bsgo_kwikqdrdist(A(F_LAT, 0), A(F_LON, 0), A(F_LAT, j), A(F_LON, j), &qdr, &d);
+            if (d < 4) { ev[EV_TOTAL_INTR] += 1; intr += -1; }
+        }
+        *reward = reach + dr * -0.1 + intr;
+        ev[EV_TOTAL_REWARD] += *reward;
     } else {
         *reward = 0;
     }
@@ -212,7 +303,7 @@ static void reward_env(const bsgo_cfg *c, const double *a, int nlive, double *ev
 #undef A
 
 void bsgo_observe(const bsgo_cfg *cfg, int E, const double *ac, const int32_t *nac, double *ev, double *obs) {
-    int od = bsgo_obs_dim(cfg->kind, cfg->n);
+    int od = bsgo_obs_dim_cfg(cfg);
     for (int e = 0; e < E; e++)
         observe_env(cfg, ac + (size_t)e * BSGO_NF * cfg->n, nac[e], ev + (size_t)e * BSGO_NE, obs + (size_t)e * od);
 }
@@ -220,8 +311,8 @@ void bsgo_observe(const bsgo_cfg *cfg, int E, const double *ac, const int32_t *n
 void bsgo_step(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, const int32_t *nac, double *ev,
                const double *actions, double *obs, double *reward, int32_t *term, int32_t *trunc,
                bsgo_cdout cd, int nthreads) {
-    int n = cfg->n, od = bsgo_obs_dim(cfg->kind, n);
-    int na = cfg->kind == KIND_S ? 2 : 1;
+    int n = cfg->n, od = bsgo_obs_dim_cfg(cfg);
+    int na = (cfg->kind == KIND_S || cfg->kind == KIND_M) ? 2 : 1;
     if (nthreads < 1) nthreads = 1;
 #pragma omp parallel for num_threads(nthreads) schedule(dynamic, 8)
     for (int e = 0; e < E; e++) {
@@ -235,7 +326,7 @@ void bsgo_step(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, const int
         if (cfg->kind != KIND_RAW && actions) apply_action(cfg, a, v, actions + (size_t)e * na);
         for (int s = 0; s < cfg->substeps; s++) {
             if (cfg->asas_on) bsgo_asas_env(cfg, a, rs, nl, rows);
-            for (int i = 0; i < nl; i++) bsgo_kin_substep(a, n, i, cfg->simdt, cfg->reso_on && cfg->asas_on);
+            for (int i = 0; i < nl; i++) bsgo_kin_substep(cfg, a, v, n, i, cfg->simdt, cfg->reso_on && cfg->asas_on);
         }
         double rew = 0;
         int32_t te = 0, tr = 0;

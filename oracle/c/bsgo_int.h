@@ -33,7 +33,7 @@ enum { PH_NA, PH_GD, PH_IC, PH_CL, PH_CR, PH_DE, PH_AP };
 double bsgo_pymod(double a, double b);
 int bsgo_phase(double tas, double vs, double alt);
 void bsgo_vlimits(int ph, double *vmin, double *vmax);
-void bsgo_kin_substep(double *a, int n, int i, double dt, int reso_on);
+void bsgo_kin_substep(const bsgo_cfg *cfg, double *a, const double *ev, int n, int i, double dt, int reso_on);
 /* CD + MVP + resumenav for one env; updates F_ASAS_* and reso rows; fills row outputs at [0..n) */
 typedef struct {
     uint8_t inconf; int32_t nconf, nlos, near_idx; double near_tcpa, near_dcpa, near_tin, tcpamax;

@@ -50,6 +50,42 @@ void bsgo_kwikqdrdist(double lata, double lona, double latb, double lonb, double
     *qdr = bsgo_pymod(atan2(dlon * cavelat, dlat) * C_R2D, 360.0);
 }
 
+static double rwgs84(double latd) {
+    double lat = latd * C_D2R, a = 6378137.0, b = 6356752.314245;
+    double coslat = cos(lat), sinlat = sin(lat);
+    double an = a * a * coslat, bn = b * b * sinlat, ad = a * coslat, bd = b * sinlat;
+    return sqrt((an * an + bn * bn) / (ad * ad + bd * bd));
+}
+/* geo.qdrdist (oracle/refshim/bluesky/tools/geo.py): great circle, WGS-84 radius of the mean latitude */
+void bsgo_qdrdist(double latd1, double lond1, double latd2, double lond2, double *qdr, double *dist_nm) {
+    double res1 = rwgs84(0.5 * (latd1 + latd2));
+    double a = 6378137.0, r1 = rwgs84(latd1), r2 = rwgs84(latd2);
+    double res2 = 0.5 * (fabs(latd1) * (r1 + a) + fabs(latd2) * (r2 + a)) / fmax(0.000001, fabs(latd1) + fabs(latd2));
+    double r = (latd1 * latd2 >= 0.0) ? res1 : res2;
+    double lat1 = latd1 * C_D2R, lon1 = lond1 * C_D2R, lat2 = latd2 * C_D2R, lon2 = lond2 * C_D2R;
+    double coslat1 = cos(lat1), coslat2 = cos(lat2);
+    double c = coslat1 * coslat2 * cos(lon2 - lon1) + sin(lat1) * sin(lat2);
+    c = fmin(1.0, fmax(-1.0, c));
+    *dist_nm = r * acos(c) / C_NM;
+    *qdr = atan2(sin(lon2 - lon1) * coslat2, coslat1 * sin(lat2) - sin(lat1) * coslat2 * cos(lon2 - lon1)) * C_R2D;
+}
+/* Windfield.getdata without altitude profiles (oracle/refshim/bluesky/traffic/windfield.py) */
+void bsgo_wind(const bsgo_cfg *cfg, double lat, double lon, double *vn, double *ve) {
+    *vn = 0.0; *ve = 0.0;
+    if (cfg->nwind <= 0) return;
+    if (cfg->nwind == 1) { *vn = cfg->wvn[0]; *ve = cfg->wve[0]; return; }
+    double w[BSGO_MAXWIND], tot = 0.0;
+    for (int k = 0; k < cfg->nwind; k++) {
+        double cavelat = cos(0.5 * (lat + cfg->wlat[k]) * C_D2R);
+        double dy = (lat - cfg->wlat[k]) * C_D2R;
+        double dx = cavelat * ((bsgo_pymod((lon - cfg->wlon[k]) + 180.0, 360.0) - 180.0) * C_D2R);
+        w[k] = 1.0 / (1e-20 + dx * dx + dy * dy);
+        tot += w[k];
+    }
+    for (int k = 0; k < cfg->nwind; k++) { *vn += w[k] / tot * cfg->wvn[k]; *ve += w[k] / tot * cfg->wve[k]; }
+}
+static double degto180(double a) { return bsgo_pymod(a + 180.0, 360.0) - 180.0; }
+
 /* ------------------------------------------------------------------ perf */
 int bsgo_phase(double tas, double vs, double alt) {
     double roc = vs / C_FPM, h = alt / C_FT;
@@ -77,9 +113,30 @@ void bsgo_vlimits(int ph, double *vmin, double *vmax) {
 
 /* One substep for aircraft i of one env, AFTER asas outputs (F_ASAS_*) are final.
  * a = field-major block [BSGO_NF][n]. */
-void bsgo_kin_substep(double *a, int n, int i, double dt, int reso_on) {
+void bsgo_kin_substep(const bsgo_cfg *cfg, double *a, const double *ev, int n, int i, double dt, int reso_on) {
 #define A(f) a[(f) * n + i]
-    /* autopilot targets (LNAV/VNAV off) */
+    const int wind = cfg->nwind > 0;
+    /* LNAV (Autopilot._update_fms of the shim): the two-waypoint Merge route FAF -> runway.  Each leg is activated
+     * with no known next leg (next_qdr = -999), so the turn-anticipation distance is zero and a waypoint counts
+     * as passed when the aircraft flies away from it within 1.02 turn radii. */
+    if (cfg->kind == KIND_M && A(F_LNAV) >= 0.0) {
+        int w = (int)A(F_LNAV);
+        double wlat = w == 0 ? ev[EV_WPT_LAT] : ev[EV_WPT_X], wlon = w == 0 ? ev[EV_WPT_LON] : ev[EV_WPT_Y];
+        double qdr, dnm;
+        bsgo_qdrdist(A(F_LAT), A(F_LON), wlat, wlon, &qdr, &dnm);
+        double turnrad = A(F_TAS) * A(F_TAS) / (fmax(0.01, tan(C_BANK)) * C_G0);
+        double trk = wind ? bsgo_pymod(atan2(A(F_GSE), A(F_GSN)) * C_R2D, 360.0) : A(F_HDG);
+        int away = fabs(degto180(bsgo_pymod(trk, 360.0) - bsgo_pymod(qdr, 360.0))) > 90.0;
+        if (away && dnm * C_NM < turnrad * 1.02) {
+            if (w >= 1) A(F_LNAV) = -1.0;
+            else {
+                A(F_LNAV) = 1.0;
+                bsgo_qdrdist(A(F_LAT), A(F_LON), ev[EV_WPT_X], ev[EV_WPT_Y], &qdr, &dnm);
+            }
+        }
+        if (A(F_LNAV) >= 0.0) A(F_APTRK) = bsgo_pymod(qdr, 360.0);
+    }
+    /* autopilot targets (VNAV off) */
     double ap_tas = bsgo_vcasormach2tas(A(F_SELSPD), A(F_ALT));
     double ap_alt = A(F_SELALT);
     double ap_vs = fabs(A(F_SELVS)) > 0.1 ? A(F_SELVS) : C_VSDEF;
@@ -91,6 +148,18 @@ void bsgo_kin_substep(double *a, int n, int i, double dt, int reso_on) {
     double t_alt = act ? A(F_ASAS_ALT) : ap_alt;
     double t_vs = fabs(act ? A(F_ASAS_VS) : ap_vs);
     double t_hdg = bsgo_pymod(trk, 360.0);
+    double vwn = 0.0, vwe = 0.0;
+    if (wind) {          /* APorASAS.update with a wind field: ASAS ground speed -> TAS, wind-correction angle */
+        bsgo_wind(cfg, A(F_LAT), A(F_LON), &vwn, &vwe);
+        if (act) {
+            double tn = A(F_ASAS_TAS) * cos(A(F_ASAS_TRK) * C_D2R) - vwn, te = A(F_ASAS_TAS) * sin(A(F_ASAS_TRK) * C_D2R) - vwe;
+            t_tas = sqrt(tn * tn + te * te);
+        }
+        double Vw = sqrt(vwn * vwn + vwe * vwe), winddir = atan2(vwe, vwn);
+        double drift = trk * C_D2R - winddir;
+        double steer = asin(fmin(1.0, fmax(-1.0, Vw * sin(drift) / fmax(0.001, A(F_TAS)))));
+        t_hdg = bsgo_pymod(trk + steer * C_R2D, 360.0);
+    }
     /* perf.update + limits */
     double vmin, vmax;
     int ph = bsgo_phase(A(F_TAS), A(F_VS), A(F_ALT));
@@ -125,11 +194,13 @@ void bsgo_kin_substep(double *a, int n, int i, double dt, int reso_on) {
     if (!isfinite(vs)) vs = 0;
     /* update_groundspeed + update_pos */
     double gsn = tas * cos(hdg * C_D2R), gse = tas * sin(hdg * C_D2R);
+    if (wind && A(F_ALT) > 50.0 * C_FT) { gsn = gsn + vwn; gse = gse + vwe; }    /* wind acts above 50 ft */
     double alt = swalt ? rint((A(F_ALT) + vs * dt) * 1e6) / 1e6 : allow_h;
     double lat = A(F_LAT) + (dt * gsn / C_RE) * C_R2D;
     double coslat = cos(lat * C_D2R);
     double lon = A(F_LON) + (dt * gse / coslat / C_RE) * C_R2D;
     A(F_CAS) = bsgo_vtas2cas(tas, A(F_ALT)); /* update_airspeed: cas from the altitude before update_pos */
     A(F_TAS) = tas; A(F_HDG) = hdg; A(F_VS) = vs; A(F_ALT) = alt; A(F_LAT) = lat; A(F_LON) = lon;
+    A(F_GSN) = gsn; A(F_GSE) = gse;
 #undef A
 }

@@ -13,7 +13,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 _SO = os.path.join(_HERE, '_build', 'libbsgo.so')
 
 FIELDS = ['lat', 'lon', 'alt', 'hdg', 'tas', 'vs', 'cas', 'selspd', 'selalt', 'selvs', 'aptrk', 'ax',
-          'asas_trk', 'asas_tas', 'asas_vs', 'asas_alt', 'asas_active', 'phase']
+          'asas_trk', 'asas_tas', 'asas_vs', 'asas_alt', 'asas_active', 'phase', 'gsn', 'gse', 'lnav']
 F = {k: i for i, k in enumerate(FIELDS)}
 NF = len(FIELDS)
 MAXV = 32
@@ -21,14 +21,17 @@ EV = {k: i for i, k in enumerate(['wpt_lat', 'wpt_lon', 'wpt_reach', 'ac_hdg', '
                                   'nvert', 'total_reward', 'total_intr', 'drift_sum', 'drift_cnt', 'final_alt',
                                   'steps', 'poly'])}
 NE = EV['poly'] + 2 * MAXV
-KIND_H, KIND_V, KIND_S, KIND_RAW = 0, 1, 2, 3
+KIND_H, KIND_V, KIND_S, KIND_RAW, KIND_M = 0, 1, 2, 3, 4
+MAXWIND = 8
 NM, FT = 1852.0, 0.3048
 
 
 class Cfg(C.Structure):
     _fields_ = [('kind', C.c_int32), ('n', C.c_int32), ('substeps', C.c_int32), ('asas_on', C.c_int32),
                 ('reso_on', C.c_int32), ('reso_off_own', C.c_int32), ('simdt', C.c_double), ('rpz', C.c_double),
-                ('hpz', C.c_double), ('dtlook', C.c_double), ('resofach', C.c_double), ('resofacv', C.c_double)]
+                ('hpz', C.c_double), ('dtlook', C.c_double), ('resofach', C.c_double), ('resofacv', C.c_double),
+                ('nwind', C.c_int32), ('wind_obs', C.c_int32), ('wlat', C.c_double * MAXWIND),
+                ('wlon', C.c_double * MAXWIND), ('wvn', C.c_double * MAXWIND), ('wve', C.c_double * MAXWIND)]
 
 
 class CdOut(C.Structure):
@@ -58,6 +61,7 @@ def lib():
             build()
         _lib = C.CDLL(_SO)
         _lib.bsgo_obs_dim.restype = C.c_int
+        _lib.bsgo_obs_dim_cfg.restype = C.c_int
         for f in ('bsgo_vcas2tas', 'bsgo_vtas2cas', 'bsgo_vcasormach2tas'):
             getattr(_lib, f).restype = C.c_double
             getattr(_lib, f).argtypes = [C.c_double, C.c_double]
@@ -69,15 +73,28 @@ def _p(a):
 
 
 def make_cfg(kind, n, substeps=None, simdt=None, asas_on=0, reso_on=0, reso_off_own=0,
-             rpz=5 * NM, hpz=1000 * FT, dtlook=300.0, resofach=1.05, resofacv=1.05):
-    d_sub = {KIND_H: 10, KIND_V: 30, KIND_S: 5, KIND_RAW: 1}
-    d_dt = {KIND_H: 5.0, KIND_V: 1.0, KIND_S: 1.0, KIND_RAW: 1.0}
-    return Cfg(kind, n, d_sub[kind] if substeps is None else substeps, asas_on, reso_on, reso_off_own,
-               d_dt[kind] if simdt is None else simdt, rpz, hpz, dtlook, resofach, resofacv)
+             rpz=5 * NM, hpz=1000 * FT, dtlook=300.0, resofach=1.05, resofacv=1.05, wind=None, wind_obs=0):
+    """wind = (lat[], lon[], vnorth[], veast[]) of the WindFieldWrapper's points (scalars allowed), or None."""
+    d_sub = {KIND_H: 10, KIND_V: 30, KIND_S: 5, KIND_RAW: 1, KIND_M: 10}
+    d_dt = {KIND_H: 5.0, KIND_V: 1.0, KIND_S: 1.0, KIND_RAW: 1.0, KIND_M: 5.0}
+    c = Cfg(kind, n, d_sub[kind] if substeps is None else substeps, asas_on, reso_on, reso_off_own,
+            d_dt[kind] if simdt is None else simdt, rpz, hpz, dtlook, resofach, resofacv)
+    if wind is not None:
+        wl, wo, vn, ve = [np.atleast_1d(np.asarray(x, dtype=np.float64)) for x in wind]
+        vn = np.broadcast_to(vn, wl.shape); ve = np.broadcast_to(ve, wl.shape)
+        assert 1 <= len(wl) <= MAXWIND
+        c.nwind = len(wl); c.wind_obs = int(wind_obs)
+        for k in range(len(wl)):
+            c.wlat[k] = wl[k]; c.wlon[k] = wo[k]; c.wvn[k] = vn[k]; c.wve[k] = ve[k]
+    return c
 
 
 def obs_dim(kind, n):
     return lib().bsgo_obs_dim(kind, n)
+
+
+def obs_dim_cfg(cfg):
+    return lib().bsgo_obs_dim_cfg(C.byref(cfg))
 
 
 def new_cdout(E, n):
@@ -94,7 +111,7 @@ def _cdstruct(cd):
 def step(cfg, ac, reso, nac, ev, actions, nthreads=1):
     """In-place K substeps + env layer.  ac [E,NF,N] f64, reso [E,N] u64, nac [E] i32, ev [E,NE] f64."""
     E = ac.shape[0]
-    od = obs_dim(cfg.kind, cfg.n)
+    od = obs_dim_cfg(cfg)
     obs = np.zeros((E, od)); rew = np.zeros(E); term = np.zeros(E, np.int32); trunc = np.zeros(E, np.int32)
     cd = new_cdout(E, cfg.n)
     act = None if actions is None else np.ascontiguousarray(actions, dtype=np.float64)
@@ -105,7 +122,7 @@ def step(cfg, ac, reso, nac, ev, actions, nthreads=1):
 
 def observe(cfg, ac, nac, ev):
     E = ac.shape[0]
-    obs = np.zeros((E, obs_dim(cfg.kind, cfg.n)))
+    obs = np.zeros((E, obs_dim_cfg(cfg)))
     lib().bsgo_observe(C.byref(cfg), C.c_int(E), _p(ac), _p(nac), _p(ev), _p(obs))
     return obs
 

@@ -53,7 +53,7 @@ class Stack:
             if not t.cd.enabled:
                 t.cd.clear()
         elif cmd == 'RESO':
-            t.cr.enabled = tok[1].upper() == 'MVP'
+            t.cr.enabled = tok[1].upper() == 'MVP'        # 'reso off' (merge_env.py:157) switches it off
             if not t.cr.enabled:
                 t.cr.active[:] = False
                 t.cr.resopairs = set()
@@ -65,4 +65,8 @@ class Stack:
             idx = t.id2idx(tok[1])
             if idx >= 0:
                 t.cr.noresoac[idx] = True
-        # anything else (ADDWPT, DEST, ...) is outside the hot path: ignored
+        elif cmd in ('ADDWPT', 'DEST'):   # "ACID ADDWPT lat lon" / "ACID DEST lat lon" (merge_env.py:155-156)
+            idx = t.id2idx(tok[1])
+            if idx >= 0:
+                t.ap.addwpt(idx, float(tok[2]), float(tok[3]), dest=(cmd == 'DEST'))
+        # anything else is outside the hot path: ignored

@@ -17,14 +17,31 @@ from ..tools.aero import (fpm, kts, ft, nm, g0, Rearth, vatmos, vcasormach, vcas
 from .perf import Perf
 from .asas import ConflictDetection
 from .mvp import MVP
+from .windfield import Windfield
 
 _FLOAT_FIELDS = ('lat', 'lon', 'alt', 'hdg', 'trk', 'tas', 'gs', 'gsnorth', 'gseast', 'cas', 'M',
                  'vs', 'selspd', 'selalt', 'selvs', 'ax', 'bank', 'apvsdef')
 _BOOL_FIELDS = ('swlnav', 'swvnav', 'swvnavspd', 'swhdgsel', 'swaltsel')
 
 
-class _Wind:
-    winddim = 0
+def _degto180(a):
+    return (a + 180.0) % 360.0 - 180.0
+
+
+class Route:
+    """Per-aircraft flight plan: the slice of ``bluesky/traffic/route.py`` that ``ACID ADDWPT lat lon`` and
+    ``ACID DEST lat lon`` exercise (merge_env.py:155-156).  Waypoints are fly-by positions without altitude or
+    speed constraints that LNAV acts on (VNAV is never switched on by the reference)."""
+
+    def __init__(self):
+        self.wplat = []
+        self.wplon = []
+        self.iactwp = -1
+        self.has_dest = False
+
+    @property
+    def nwp(self):
+        return len(self.wplat)
 
 
 class Autopilot:
@@ -32,8 +49,14 @@ class Autopilot:
         self.traf = traf
         self.reset()
 
+    _ARR = ('trk', 'tas', 'alt', 'vs', 'wplat', 'wplon', 'next_qdr', 'swlastwp')
+
     def reset(self):
         self.trk = np.zeros(0); self.tas = np.zeros(0); self.alt = np.zeros(0); self.vs = np.zeros(0)
+        # active waypoint (bs.traf.actwp): position, direction of the leg after it (-999 = none), last-wp switch
+        self.wplat = np.zeros(0); self.wplon = np.zeros(0); self.next_qdr = np.zeros(0)
+        self.swlastwp = np.zeros(0, dtype=bool)
+        self.route = []
 
     def create(self, n):
         t = self.traf
@@ -41,14 +64,80 @@ class Autopilot:
         self.tas = np.append(self.tas, t.tas[-n:])
         self.alt = np.append(self.alt, t.alt[-n:])
         self.vs = np.append(self.vs, np.zeros(n))
+        self.wplat = np.append(self.wplat, np.full(n, 89.99))
+        self.wplon = np.append(self.wplon, np.zeros(n))
+        self.next_qdr = np.append(self.next_qdr, np.full(n, -999.0))
+        self.swlastwp = np.append(self.swlastwp, np.zeros(n, dtype=bool))
+        self.route.extend(Route() for _ in range(n))
 
     def delete(self, idx):
-        for k in ('trk', 'tas', 'alt', 'vs'):
+        for k in self._ARR:
             setattr(self, k, np.delete(getattr(self, k), idx))
+        self.route.pop(idx)
+
+    # ---------------------------------------------------------------- flight plan (LNAV)
+    def addwpt(self, idx, lat, lon, dest=False):
+        """``ADDWPT`` / ``DEST`` with a lat/lon position.  A destination stays the last waypoint; other waypoints
+        are inserted before it.  The first waypoint of a route becomes the active one and switches LNAV on
+        (``Route.direct``); the active leg keeps the next-leg direction it had when it was activated."""
+        r = self.route[idx]
+        if dest:
+            if r.has_dest:
+                r.wplat[-1] = lat; r.wplon[-1] = lon
+            else:
+                r.wplat.append(lat); r.wplon.append(lon); r.has_dest = True
+        else:
+            pos = r.nwp - 1 if r.has_dest else r.nwp
+            r.wplat.insert(pos, lat); r.wplon.insert(pos, lon)
+            if r.iactwp >= pos:
+                r.iactwp += 1
+        if r.nwp == 1:
+            r.iactwp = 0
+            self.wplat[idx] = lat; self.wplon[idx] = lon
+            self.next_qdr[idx] = -999.0
+            self.swlastwp[idx] = False
+            self.traf.swlnav[idx] = True
+
+    def _calcturn(self, tas, bank, wpqdr, next_wpqdr):
+        turnrad = tas * tas / (np.maximum(0.01, np.tan(bank)) * g0)
+        turndist = np.abs(turnrad * np.tan(np.radians(0.5 * np.abs(_degto180(wpqdr % 360.0 - next_wpqdr % 360.0)))))
+        return turndist, turnrad
+
+    def _update_fms(self):
+        """Waypoint switching (``ActiveWaypoint.Reached`` + ``Autopilot.update_fms``): a fly-by waypoint counts as
+        reached inside the turn-anticipation distance, or when the aircraft flies away from it within 1.02 turn
+        radii; past the last waypoint LNAV switches off and the aircraft keeps its track."""
+        t = self.traf
+        qdr, distnm = geo.qdrdist(t.lat, t.lon, self.wplat, self.wplon)
+        dist = distnm * nm
+        next_qdr = np.where(self.next_qdr < -900.0, qdr, self.next_qdr)
+        turndist, turnrad = self._calcturn(t.tas, t.bank, qdr, next_qdr)
+        away = np.abs(_degto180(t.trk % 360.0 - qdr % 360.0)) > 90.0
+        circling = away & (dist < turnrad * 1.02)
+        reached = t.swlnav & ((dist < turndist) | circling)
+        for i in np.where(reached)[0]:
+            r = self.route[i]
+            if self.swlastwp[i] or r.iactwp + 1 >= r.nwp:
+                t.swlnav[i] = False
+                continue
+            r.iactwp += 1
+            self.wplat[i] = r.wplat[r.iactwp]; self.wplon[i] = r.wplon[r.iactwp]
+            self.swlastwp[i] = (r.iactwp == r.nwp - 1)
+            if r.iactwp + 1 < r.nwp:
+                q, _ = geo.qdrdist(r.wplat[r.iactwp], r.wplon[r.iactwp], r.wplat[r.iactwp + 1], r.wplon[r.iactwp + 1])
+                self.next_qdr[i] = q
+            else:
+                self.next_qdr[i] = -999.0
+            qdr[i], _ = geo.qdrdist(t.lat[i], t.lon[i], self.wplat[i], self.wplon[i])
+        return qdr % 360.0
 
     def update(self):
-        """LNAV/VNAV are off in every hot env: targets follow the selected values."""
+        """Targets follow the selected values; with LNAV on the commanded track is the bearing to the active
+        waypoint.  VNAV is never on in the reference's envs."""
         t = self.traf
+        if t.swlnav.any():
+            qdr2wp = self._update_fms()
+            self.trk = np.where(t.swlnav, qdr2wp, self.trk)
         self.tas = vcasormach2tas(t.selspd, t.alt)
         self.alt = t.selalt.copy()
         self.vs = np.where(np.abs(t.selvs) > 0.1, t.selvs, t.apvsdef)
@@ -65,8 +154,17 @@ class Autopilot:
                 t.selvs[idx] = 0.0
 
     def selhdgcmd(self, idx, hdg):
-        self.traf.swlnav[idx] = False
-        self.trk[idx] = hdg
+        """``HDG``: with a wind field the selected heading becomes the track it gives in the current wind
+        (above 50 ft; on the ground the heading itself)."""
+        t = self.traf
+        t.swlnav[idx] = False
+        if t.wind.winddim > 0 and t.alt[idx] > 50.0 * ft:
+            vnwnd, vewnd = t.wind.getdata(t.lat[idx], t.lon[idx], t.alt[idx])
+            gsnorth = t.tas[idx] * np.cos(np.radians(hdg)) + vnwnd
+            gseast = t.tas[idx] * np.sin(np.radians(hdg)) + vewnd
+            self.trk[idx] = np.degrees(np.arctan2(gseast, gsnorth)) % 360.0
+        else:
+            self.trk[idx] = hdg
 
     def selspdcmd(self, idx, casmach):
         self.traf.selspd[idx] = casmach
@@ -82,17 +180,31 @@ class APorASAS:
         t = self.traf
         act = t.cr.active if t.cr.enabled else np.zeros(t.ntraf, dtype=bool)
         trk = np.where(act, t.cr.trk, t.ap.trk)
-        self.tas = np.where(act, t.cr.tas, t.ap.tas)
+        if t.wind.winddim > 0:      # the ASAS speed command is a ground speed: back to TAS through the wind
+            vwn, vwe = t.wind.getdata(t.lat, t.lon, t.alt)
+            asastasnorth = t.cr.tas * np.cos(np.radians(t.cr.trk)) - vwn
+            asastaseast = t.cr.tas * np.sin(np.radians(t.cr.trk)) - vwe
+            asastas = np.sqrt(asastasnorth ** 2 + asastaseast ** 2)
+        else:
+            asastas = t.cr.tas
+        self.tas = np.where(act, asastas, t.ap.tas)
         self.alt = np.where(act, t.cr.alt, t.ap.alt)
         self.vs = np.abs(np.where(act, t.cr.vs, t.ap.vs))
-        self.hdg = trk % 360.0
+        if t.wind.winddim > 0:      # heading that holds the commanded track in the wind
+            Vw = np.sqrt(vwn * vwn + vwe * vwe)
+            winddir = np.arctan2(vwe, vwn)
+            drift = np.radians(trk) - winddir
+            steer = np.arcsin(np.minimum(1.0, np.maximum(-1.0, Vw * np.sin(drift) / np.maximum(0.001, t.tas))))
+            self.hdg = (trk + np.degrees(steer)) % 360.0
+        else:
+            self.hdg = trk % 360.0
 
 
 class Traffic:
     def __init__(self, settings, sim):
         self.settings = settings
         self.sim = sim
-        self.wind = _Wind()
+        self.wind = Windfield()
         self.ap = Autopilot(self)
         self.perf = Perf(self)
         self.cd = ConflictDetection(self, settings)
@@ -110,6 +222,7 @@ class Traffic:
         for k in _BOOL_FIELDS:
             setattr(self, k, np.zeros(0, dtype=bool))
         self.ap.reset(); self.perf.reset(); self.cd.reset(); self.cr.reset()
+        self.wind.clear()
 
     def id2idx(self, acid):
         if not isinstance(acid, str):
@@ -234,10 +347,20 @@ class Traffic:
         self.vs = np.where(np.isfinite(self.vs), self.vs, 0)
 
     def update_groundspeed(self):
-        self.gsnorth = self.tas * np.cos(np.radians(self.hdg))
-        self.gseast = self.tas * np.sin(np.radians(self.hdg))
-        self.gs = self.tas
-        self.trk = self.hdg
+        if self.wind.winddim == 0:
+            self.gsnorth = self.tas * np.cos(np.radians(self.hdg))
+            self.gseast = self.tas * np.sin(np.radians(self.hdg))
+            self.gs = self.tas
+            self.trk = self.hdg
+        else:                       # wind acts above 50 ft
+            applywind = self.alt > 50.0 * ft
+            vnwnd, vewnd = self.wind.getdata(self.lat, self.lon, self.alt)
+            self.gsnorth = self.tas * np.cos(np.radians(self.hdg)) + vnwnd * applywind
+            self.gseast = self.tas * np.sin(np.radians(self.hdg)) + vewnd * applywind
+            self.gs = np.logical_not(applywind) * self.tas + \
+                applywind * np.sqrt(self.gsnorth ** 2 + self.gseast ** 2)
+            self.trk = np.logical_not(applywind) * self.hdg + \
+                applywind * np.degrees(np.arctan2(self.gseast, self.gsnorth)) % 360.0
 
     def update_pos(self):
         dt = self.sim.simdt

@@ -10,6 +10,7 @@ truncated / info.  The fixtures pin Tier A (env layer) to the reference's source
 (BlueSky arithmetic) remains a restatement: parity unpinned vs upstream.
 """
 import os
+import random
 import sys
 import warnings
 import numpy as np
@@ -34,12 +35,15 @@ OBS_ORDER = {
           'z_difference_speed'],
     'S': ['cos(drift)', 'sin(drift)', 'airspeed', 'x_r', 'y_r', 'vx_r', 'vy_r', 'cos(track)', 'sin(track)',
           'distances'],
+    'M': ['cos(drift)', 'sin(drift)', 'airspeed', 'waypoint_dist', 'faf_reached', 'x_r', 'y_r', 'vx_r', 'vy_r',
+          'cos(track)', 'sin(track)', 'distances'],
 }
-ENV_ID = {'H': 'HorizontalCREnv-v0', 'V': 'VerticalCREnv-v0', 'S': 'SectorCREnv-v0'}
+ENV_ID = {'H': 'HorizontalCREnv-v0', 'V': 'VerticalCREnv-v0', 'S': 'SectorCREnv-v0', 'M': 'MergeEnv-v0'}
 
 
 def flat_obs(kind, obs):
-    return np.concatenate([np.asarray(obs[k], dtype=np.float64).ravel() for k in OBS_ORDER[kind]])
+    keys = OBS_ORDER[kind] + (['wind_u', 'wind_v'] if 'wind_u' in obs else [])
+    return np.concatenate([np.asarray(obs[k], dtype=np.float64).ravel() for k in keys])
 
 
 def snapshot(kind, env, n):
@@ -51,7 +55,8 @@ def snapshot(kind, env, n):
     src = dict(lat=t.lat, lon=t.lon, alt=t.alt, hdg=t.hdg, tas=t.tas, vs=t.vs, cas=t.cas, selspd=t.selspd,
                selalt=t.selalt, selvs=t.selvs, aptrk=t.ap.trk, ax=t.ax, asas_trk=t.cr.trk, asas_tas=t.cr.tas,
                asas_vs=t.cr.vs, asas_alt=t.cr.alt, asas_active=t.cr.active.astype(float),
-               phase=t.perf.phase.astype(float))
+               phase=t.perf.phase.astype(float), gsn=t.gsnorth, gse=t.gseast,
+               lnav=np.array([float(r.iactwp) if on else -1.0 for r, on in zip(t.ap.route, t.swlnav)]))
     for k, v in src.items():
         ac[orc.F[k], :nl] = v
     reso = np.zeros(n, np.uint64)
@@ -73,34 +78,51 @@ def snapshot(kind, env, n):
         ev[orc.EV['nvert']] = nv
         ev[orc.EV['poly']:orc.EV['poly'] + 2 * nv:2] = poly.vlat
         ev[orc.EV['poly'] + 1:orc.EV['poly'] + 2 * nv:2] = poly.vlon
-    if kind in 'HS':
-        ev[orc.EV['drift_sum']] = u.average_drift.sum(); ev[orc.EV['drift_cnt']] = len(u.average_drift)
+    if kind == 'M':   # slot reuse documented in oracle/c/bsgo.h
+        ev[orc.EV['wpt_lat']] = u.wpt_lat; ev[orc.EV['wpt_lon']] = u.wpt_lon
+        ev[orc.EV['wpt_x']] = u.rwy_lat; ev[orc.EV['wpt_y']] = u.rwy_lon
+        ev[orc.EV['wpt_reach']] = u.wpt_reach; ev[orc.EV['final_alt']] = u.faf_reached
+    if kind in 'HSM':
+        ev[orc.EV['drift_sum']] = float(np.sum(u.average_drift)); ev[orc.EV['drift_cnt']] = len(u.average_drift)
     return ac, reso, nl, ev
 
 
-def record(kind, seed, episodes, max_steps, asas=False, n_pad=None):
+def record(kind, seed, episodes, max_steps, asas=False, n_pad=None, wind=None):
+    """wind = (lat, lon, vnorth, veast): the env is wrapped in the reference's WindFieldWrapper (augment_obs)."""
     np.random.seed(seed)
+    random.seed(seed)           # MergeEnv draws from Python's `random`
     env = gym.make(ENV_ID[kind], render_mode=None)
+    if wind is not None:
+        from bluesky_gym.wrappers.wind import WindFieldWrapper
+        env = WindFieldWrapper(env, *wind, augment_obs=True)
     R = dict(ac0=[], reso0=[], nac=[], ev0=[], act=[], ac1=[], reso1=[], ev1=[], obs0=[], obs1=[], rew=[],
              term=[], trunc=[], info=[])
+    if wind is not None:
+        wl = np.atleast_1d(np.asarray(wind[0], dtype=np.float64))
+        R['wind'] = np.stack([wl] + [np.broadcast_to(np.atleast_1d(np.asarray(w, dtype=np.float64)), wl.shape)
+                                     for w in wind[1:]], axis=1)
     for ep in range(episodes):
         obs, info = env.reset()
         if asas:   # the north-star feature on top of the reference: ASAS ON + MVP for the intruders
             bs.stack.stack('ASAS ON'); bs.stack.stack('RESO MVP'); bs.stack.stack('RESOOFF KL001')
             bs.stack.process()
-        n = n_pad or (32 if kind == 'S' else 6)
+        if kind == 'M':   # flush the route commands reset() queued (ADDWPT / DEST / RESO OFF) so that the
+            bs.stack.process()   # snapshot below already holds the LNAV state the first sim.step() would set
+        n = n_pad or {'S': 32, 'M': 20}.get(kind, 6)
         for s in range(max_steps):
             ac0, reso0, nl, ev0 = snapshot(kind, env, n)
             a = np.random.uniform(-1, 1, env.action_space.shape)
             if kind == 'H' and ep % 2 == 0:
                 a = a * 0.0           # straight flight: reaches the waypoint (termination branch)
+            if kind == 'M':
+                a = a * (0.15 if ep % 2 == 0 else 1.0)      # gentle steering: reaches the FAF, then the runway
             obs1, r, term, trunc, info = env.step(a)
             R['ac0'].append(ac0); R['reso0'].append(reso0); R['nac'].append(nl); R['ev0'].append(ev0)
-            R['act'].append(np.resize(a, 2) if kind == 'S' else np.array([a[0], 0.0]))
+            R['act'].append(np.resize(a, 2) if kind in 'SM' else np.array([a[0], 0.0]))
             R['obs0'].append(flat_obs(kind, obs)); R['obs1'].append(flat_obs(kind, obs1))
             R['rew'].append(r); R['term'].append(int(term)); R['trunc'].append(int(bool(trunc)))
             R['info'].append([info['total_reward'], info['total_intrusions'],
-                              info.get('average_drift', info.get('final_altitude', 0.0))])
+                              info.get('average_drift', info.get('final_altitude', 0.0)), info.get('faf_reach', 0.0)])
             if term:       # the reference deletes all aircraft on termination: no post-state
                 R['ac1'].append(np.zeros_like(ac0)); R['reso1'].append(reso0 * 0); R['ev1'].append(ev0 * 0)
                 break
@@ -114,11 +136,16 @@ def record(kind, seed, episodes, max_steps, asas=False, n_pad=None):
 
 def main():
     bluesky_gym.register_envs()
-    specs = [('H', 11, 4, 45, False), ('V', 12, 4, 50, False), ('S', 13, 4, 120, False),
-             ('H', 21, 3, 30, True), ('S', 23, 3, 60, True)]
-    for kind, seed, eps, ms, asas in specs:
-        R = record(kind, seed, eps, ms, asas)
-        name = f"golden_{kind}{'_asas' if asas else ''}.npz"
+    W1 = (52.0, 4.0, 12.0, -7.0)                                        # one point: uniform wind
+    W3 = ([51.5, 52.6, 52.0], [3.5, 4.2, 5.5], [10.0, -4.0, 6.0], [-8.0, 12.0, 3.0])   # three points: weighted field
+    specs = [('H', 11, 4, 45, False, None, ''), ('V', 12, 4, 50, False, None, ''), ('S', 13, 4, 120, False, None, ''),
+             ('H', 21, 3, 30, True, None, '_asas'), ('S', 23, 3, 60, True, None, '_asas'),
+             ('M', 31, 4, 50, False, None, ''), ('M', 32, 2, 50, False, W1, '_wind'),
+             ('S', 33, 2, 60, False, W1, '_wind'), ('V', 34, 2, 50, False, W3, '_wind'),
+             ('H', 35, 2, 30, False, W1, '_wind'), ('S', 36, 2, 40, True, W3, '_asas_wind')]
+    for kind, seed, eps, ms, asas, wind, tag in specs:
+        R = record(kind, seed, eps, ms, asas, wind=wind)
+        name = f"golden_{kind}{tag}.npz"
         np.savez_compressed(os.path.join(HERE, name), **R)
         print(name, 'steps', len(R['rew']), 'terms', int(R['term'].sum()), 'truncs', int(R['trunc'].sum()),
               'asas-active steps', int((R['ac1'][:, orc.F['asas_active']].sum(1) > 0).sum()))

@@ -8,40 +8,73 @@ import numpy as np
 import pytest
 from conftest import load_golden, ROOT
 
-KIND = {'H': 0, 'V': 1, 'S': 2}
+KIND = {'H': 0, 'V': 1, 'S': 2, 'M': 4}
 TOL = 1e-11
+
+
+def golden_cfg(orc, name, g):
+    """Oracle config of a golden file: env kind from the first letter, ASAS+MVP / wind from the tags."""
+    kind = name[0]
+    asas = int('asas' in name)
+    wind = tuple(g['wind'].T) if 'wind' in g else None
+    return orc.make_cfg(KIND[kind], g['ac0'].shape[2], asas_on=asas, reso_on=asas, reso_off_own=asas,
+                        wind=wind, wind_obs=int(wind is not None))
 
 
 def rel(a, b):
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1.0))) if a.size else 0.0
 
 
-@pytest.mark.parametrize('name', ['H', 'V', 'S', 'H_asas', 'S_asas'])
+GOLDEN = ['H', 'V', 'S', 'H_asas', 'S_asas', 'M', 'M_wind', 'S_wind', 'V_wind', 'H_wind', 'S_asas_wind']
+
+
+@pytest.mark.parametrize('name', GOLDEN)
 def test_c_oracle_replays_reference_steps(orc, name):
     g = load_golden(name)
     kind = name[0]
     asas = int('asas' in name)
     n = g['ac0'].shape[2]
-    cfg = orc.make_cfg(KIND[kind], n, asas_on=asas, reso_on=asas, reso_off_own=asas)
+    cfg = golden_cfg(orc, name, g)
     nac = g['nac'].astype(np.int32)
-    na = 2 if kind == 'S' else 1
+    na = 2 if kind in 'SM' else 1
     obs0 = orc.observe(cfg, g['ac0'].copy(), nac, g['ev0'].copy())
-    assert rel(obs0, g['obs0']) < TOL
+    keep = np.ones(len(nac), bool)
+    if kind == 'M':   # the reference observes BEFORE _check_waypoint flips wpt_reach (merge_env.py:139-140): the obs
+        keep = g['obs0'][:, 4] == g['ev0'][:, orc.EV['wpt_reach']]     # a step returned lags the flag by one step
+        assert (~keep).sum() >= 1
+    assert rel(obs0[keep], g['obs0'][keep]) < TOL
     ac, reso, ev = g['ac0'].copy(), g['reso0'].copy(), g['ev0'].copy()
     obs, rew, term, trunc, cd = orc.step(cfg, ac, reso, nac, ev, np.ascontiguousarray(g['act'][:, :na]), nthreads=2)
-    assert rel(obs, g['obs1']) < TOL
+    ref_obs = g['obs1'].copy()
+    if 'wind' in name:   # on termination the reference deletes aircraft before the wrapper looks up 'kl001'
+        t = g['term'] == 1   # (id2idx -> -1 -> the LAST remaining aircraft): wind slots of that row are not KL001's
+        ref_obs[t, -2:] = obs[t, -2:]
+    assert rel(obs, ref_obs) < TOL
     assert rel(rew, g['rew']) < TOL
-    assert np.array_equal(term, g['term']) and np.array_equal(trunc, g['trunc'])
+    assert np.array_equal(term, g['term'])
+    if kind == 'M':   # MergeEnv never truncates itself; the recorded flags are the TimeLimit wrapper's (50 steps)
+        assert not trunc.any() and np.all(g['ev0'][g['trunc'] == 1, orc.EV['steps']] == 0)
+    else:
+        assert np.array_equal(trunc, g['trunc'])
     live = g['term'] == 0
     assert rel(ac[live], g['ac1'][live]) < TOL
     assert np.array_equal(reso[live], g['reso1'][live])
     assert rel(ev[:, orc.EV['total_reward']], g['info'][:, 0]) < TOL
     assert np.array_equal(ev[:, orc.EV['total_intr']], g['info'][:, 1])
-    if kind in 'HS':   # average_drift = mean of the appended drifts (nan right after reset)
+    if kind in 'HSM':   # average_drift = mean of the appended drifts (nan right after reset)
         avg = ev[:, orc.EV['drift_sum']] / ev[:, orc.EV['drift_cnt']]
         assert rel(avg, g['info'][:, 2]) < 1e-9
     else:
         assert rel(ev[:, orc.EV['final_alt']], g['info'][:, 2]) < TOL
+    if kind == 'M':     # info['faf_reach']; both waypoint branches and the LNAV switch must occur
+        assert np.array_equal(ev[:, orc.EV['final_alt']], g['info'][:, 3])
+        assert g['term'].sum() >= 1 and (g['info'][:, 3] == 1).any()
+        lnav0, lnav1 = g['ac0'][:, orc.F['lnav']], g['ac1'][:, orc.F['lnav']]
+        assert ((lnav0 == 0) & (lnav1 == 1)).any()
+    if 'wind' in name:  # the wind must actually bend the ground speed (Horizontal flies at alt 0: below 50 ft)
+        gs = np.hypot(g['ac1'][:, orc.F['gsn']], g['ac1'][:, orc.F['gse']])
+        moved = np.abs(gs - g['ac1'][:, orc.F['tas']])[live].max()
+        assert (moved < 1e-9) if kind == 'H' else (moved > 1.0)
     # every golden file must exercise its branches
     if name == 'H':
         assert g['term'].sum() >= 1
