@@ -1,5 +1,5 @@
 """bluesky_gym_hallucination_b200 -- B200-native batched simulation core for the BlueSky-Gym
-conflict-resolution envs (HorizontalCREnv-v0 / VerticalCREnv-v0 / SectorCREnv-v0).
+conflict-resolution envs (HorizontalCREnv-v0 / VerticalCREnv-v0 / SectorCREnv-v0 / MergeEnv-v0).
 The compute path is libbsgcore.so (hand-written CUDA, sm_100a) behind the C-ABI of include/bsgcore.h;
 there is no CPU fallback.  Public API (mirrors bluesky_gym/__init__.py:4-46 of the reference):
 
@@ -15,11 +15,12 @@ _REGISTRATIONS = (          # id, entry point, max_episode_steps -- bluesky_gym/
     ("HorizontalCREnv-v0", f"{_PKG}.envs:HorizontalCREnv", 300),
     ("VerticalCREnv-v0", f"{_PKG}.envs:VerticalCREnv", 300),
     ("SectorCREnv-v0", f"{_PKG}.envs:SectorCREnv", 200),
+    ("MergeEnv-v0", f"{_PKG}.envs:MergeEnv", 50),
 )
 
 
 def register_envs():
-    """Register the three conflict-resolution env ids (with gymnasium when it is installed)."""
+    """Register the conflict-resolution env ids of the hot path (with gymnasium when it is installed)."""
     from .gym_compat import register
     for env_id, entry, steps in _REGISTRATIONS:
         register(id=env_id, entry_point=entry, max_episode_steps=steps)

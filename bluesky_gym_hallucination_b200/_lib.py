@@ -6,11 +6,12 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get('BSG_LIB_PATH') or os.path.join(_HERE, 'libbsgcore.so')   # override: A/B of kernel variants (tools/ab.sh)
 
-ABI_VERSION = 1
-KIND_HORIZONTAL, KIND_VERTICAL, KIND_SECTOR, KIND_RAW = 0, 1, 2, 3
+ABI_VERSION = 2
+KIND_HORIZONTAL, KIND_VERTICAL, KIND_SECTOR, KIND_RAW, KIND_MERGE = 0, 1, 2, 3, 4
+MAX_WIND = 8
 FP32, FP64 = 0, 1
 FIELDS = ['lat', 'lon', 'alt', 'hdg', 'tas', 'vs', 'cas', 'selspd', 'selalt', 'selvs', 'aptrk', 'ax',
-          'asas_trk', 'asas_tas', 'asas_vs', 'asas_alt', 'asas_active', 'phase']
+          'asas_trk', 'asas_tas', 'asas_vs', 'asas_alt', 'asas_active', 'phase', 'gsn', 'gse', 'lnav']
 F = {k: i for i, k in enumerate(FIELDS)}
 NF = len(FIELDS)
 MAXV = 32
@@ -67,6 +68,8 @@ SYMBOLS = {
     'bsg_obs_dim': (_I, [_VP]),
     'bsg_act_dim': (_I, [_VP]),
     'bsg_launch_count': (_I, [_VP, _I64P]),
+    'bsg_set_wind': (_I, [_VP, C.c_int32, _VP, _VP, _VP, _VP, C.c_int32]),
+    'bsg_set_obs_noise': (_I, [_VP, C.c_double, C.c_uint64]),
     'bsg_set_state': (_I, [_VP, _VP, _VP, _VP, _VP]),
     'bsg_get_state': (_I, [_VP, _VP, _VP, _VP, _VP]),
     'bsg_reset': (_I, [_VP, _VP, C.c_uint64, _VP]),

@@ -7,7 +7,7 @@ from . import _lib as L
 
 OBS_KEYS = {
     # key order of the reference's Dict spaces (horizontal_cr_env.py:51-58, vertical_cr_env.py:70-81,
-    # sector_cr_env.py:54-63); value = number of entries as a function of K = intruders
+    # sector_cr_env.py:54-63, merge_env.py:59-72); value = number of entries as a function of K = intruders
     L.KIND_HORIZONTAL: [('intruder_distance', 'K'), ('cos_difference_pos', 'K'), ('sin_difference_pos', 'K'),
                         ('x_difference_speed', 'K'), ('y_difference_speed', 'K'), ('waypoint_distance', 1),
                         ('cos_drift', 1), ('sin_drift', 1)],
@@ -17,13 +17,17 @@ OBS_KEYS = {
                       ('z_difference_speed', 'K')],
     L.KIND_SECTOR: [('cos(drift)', 1), ('sin(drift)', 1), ('airspeed', 1), ('x_r', 4), ('y_r', 4), ('vx_r', 4),
                     ('vy_r', 4), ('cos(track)', 4), ('sin(track)', 4), ('distances', 4)],
+    L.KIND_MERGE: [('cos(drift)', 1), ('sin(drift)', 1), ('airspeed', 1), ('waypoint_dist', 1), ('faf_reached', 1),
+                   ('x_r', 5), ('y_r', 5), ('vx_r', 5), ('vy_r', 5), ('cos(track)', 5), ('sin(track)', 5),
+                   ('distances', 5)],
 }
+WIND_KEYS = [('wind_u', 1), ('wind_v', 1)]      # WindFieldWrapper(augment_obs=True), wrappers/wind.py:21-24
 
 
-def obs_slices(kind, n_ac):
+def obs_slices(kind, n_ac, wind_obs=False):
     """[(key, start, stop)] of the flat observation vector."""
     K, out, p = n_ac - 1, [], 0
-    for key, w in OBS_KEYS[kind]:
+    for key, w in OBS_KEYS[kind] + (WIND_KEYS if wind_obs else []):
         w = K if w == 'K' else w
         out.append((key, p, p + w))
         p += w
@@ -63,9 +67,18 @@ class BsgCore:
             if h:
                 self.lib.bsg_destroy(h)
             raise L.BsgError(f"bsg_create: {self.lib.bsg_status_string(rc).decode()} {msg}")
+        self.cd = None
+        self._cd_outputs = cd_outputs
+        self.wind_obs = False
+        self._alloc_outputs()
+
+    def _alloc_outputs(self):
+        """(Re)allocate the caller-owned output tensors; obs_dim follows bsg_set_wind(augment_obs)."""
+        cd_outputs = self._cd_outputs
+        self._views = None
         self.obs_dim = self.lib.bsg_obs_dim(self.h)
         self.act_dim = self.lib.bsg_act_dim(self.h)
-        E, N, dev, rd = num_envs, max_ac, self.device, self.rdtype
+        E, N, dev, rd = self.E, self.N, self.device, self.rdtype
         self.obs = torch.zeros((E, max(self.obs_dim, 1)), dtype=rd, device=dev)
         self.reward = torch.zeros(E, dtype=rd, device=dev)
         self.terminated = torch.zeros(E, dtype=torch.int32, device=dev)
@@ -86,6 +99,25 @@ class BsgCore:
                                                                    'near_dcpa', 'near_tin', 'tcpamax')]
         self._out = L.StepOut(_ptr(self.obs) if self.obs_dim else None, _ptr(self.reward), _ptr(self.terminated),
                               _ptr(self.truncated), _ptr(self.info), *cdp, _ptr(self.done))
+
+    # ------------------------------------------------------------------ wrapper features (EXT kernels)
+    def set_wind(self, lat=None, lon=None, vnorth=None, veast=None, augment_obs=False):
+        """WindFieldWrapper (bluesky_gym/wrappers/wind.py:9-29): wind vectors [m/s] at points; None switches it off."""
+        if lat is None:
+            L.check(self.lib.bsg_set_wind(self.h, 0, None, None, None, None, 0), self.h)
+        else:
+            la = np.atleast_1d(np.asarray(lat, dtype=np.float64)).copy()
+            lo = np.ascontiguousarray(np.broadcast_to(np.atleast_1d(np.asarray(lon, dtype=np.float64)), la.shape))
+            vn = np.ascontiguousarray(np.broadcast_to(np.atleast_1d(np.asarray(vnorth, dtype=np.float64)), la.shape))
+            ve = np.ascontiguousarray(np.broadcast_to(np.atleast_1d(np.asarray(veast, dtype=np.float64)), la.shape))
+            L.check(self.lib.bsg_set_wind(self.h, len(la), _ptr(la), _ptr(lo), _ptr(vn), _ptr(ve), int(augment_obs)), self.h)
+        self.wind_obs = bool(augment_obs) and lat is not None
+        if self.lib.bsg_obs_dim(self.h) != self.obs_dim:
+            self._alloc_outputs()
+
+    def set_obs_noise(self, sigma, seed=0):
+        """NoisyObservationWrapper (bluesky_gym/wrappers/uncertainty.py:5-8): obs + N(0, sigma) on every slot."""
+        L.check(self.lib.bsg_set_obs_noise(self.h, float(sigma), int(seed)), self.h)
 
     def close(self):
         h = getattr(self, 'h', None)

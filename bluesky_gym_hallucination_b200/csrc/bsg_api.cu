@@ -21,25 +21,59 @@ __global__ void import_state_kernel(const double *ac, int E, int N, double *pos,
     size_t e = k / N, i = k - e * N;
     const double *a = ac + e * BSG_NF * N + i;
     pos[k] = a[BSG_F_LAT * N]; pos[EN + k] = a[BSG_F_LON * N];
-    const int map[16] = { BSG_F_ALT, BSG_F_HDG, BSG_F_TAS, BSG_F_VS, BSG_F_CAS, BSG_F_SELSPD, BSG_F_SELALT, BSG_F_SELVS,
+    const int map[19] = { BSG_F_ALT, BSG_F_HDG, BSG_F_TAS, BSG_F_VS, BSG_F_CAS, BSG_F_SELSPD, BSG_F_SELALT, BSG_F_SELVS,
                           BSG_F_APTRK, BSG_F_AX, BSG_F_ASAS_TRK, BSG_F_ASAS_TAS, BSG_F_ASAS_VS, BSG_F_ASAS_ALT,
-                          BSG_F_ASAS_ACTIVE, BSG_F_PHASE };
+                          BSG_F_ASAS_ACTIVE, BSG_F_PHASE, BSG_F_GSN, BSG_F_GSE, BSG_F_LNAV };
 #pragma unroll
-    for (int f = 0; f < 16; f++) st[(size_t)f * EN + k] = (R)a[(size_t)map[f] * N];
+    for (int f = 0; f < 19; f++) st[(size_t)f * EN + k] = (R)a[(size_t)map[f] * N];
     for (int f = S_C_ALT; f < S_NS; f++) st[(size_t)f * EN + k] = (R)NAN;     // invalidate the memo keys
 }
 template <typename R>
-__global__ void export_state_kernel(double *ac, int E, int N, const double *pos, const R *st) {
+__global__ void export_state_kernel(double *ac, int E, int N, const double *pos, const R *st, int derive_gs) {
     size_t EN = (size_t)E * N, k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= EN) return;
     size_t e = k / N, i = k - e * N;
     double *a = ac + e * BSG_NF * N + i;
     a[BSG_F_LAT * N] = pos[k]; a[BSG_F_LON * N] = pos[EN + k];
-    const int map[16] = { BSG_F_ALT, BSG_F_HDG, BSG_F_TAS, BSG_F_VS, BSG_F_CAS, BSG_F_SELSPD, BSG_F_SELALT, BSG_F_SELVS,
+    const int map[19] = { BSG_F_ALT, BSG_F_HDG, BSG_F_TAS, BSG_F_VS, BSG_F_CAS, BSG_F_SELSPD, BSG_F_SELALT, BSG_F_SELVS,
                           BSG_F_APTRK, BSG_F_AX, BSG_F_ASAS_TRK, BSG_F_ASAS_TAS, BSG_F_ASAS_VS, BSG_F_ASAS_ALT,
-                          BSG_F_ASAS_ACTIVE, BSG_F_PHASE };
+                          BSG_F_ASAS_ACTIVE, BSG_F_PHASE, BSG_F_GSN, BSG_F_GSE, BSG_F_LNAV };
 #pragma unroll
-    for (int f = 0; f < 16; f++) a[(size_t)map[f] * N] = (double)st[(size_t)f * EN + k];
+    for (int f = 0; f < 19; f++) a[(size_t)map[f] * N] = (double)st[(size_t)f * EN + k];
+    if (derive_gs) {     // only the EXT kernels keep the ground-speed vector in the state: without wind it is tas * (cos, sin)(hdg)
+        const double tas = (double)st[(size_t)S_TAS * EN + k], hdg = (double)st[(size_t)S_HDG * EN + k] * kD2R;
+        a[(size_t)BSG_F_GSN * N] = tas * cos(hdg); a[(size_t)BSG_F_GSE * N] = tas * sin(hdg);
+    }
+}
+
+// the plain kernels do not keep the ground-speed vector in the state: refresh it when the EXT features switch on
+template <typename R>
+__global__ void derive_gs_kernel(int E, int N, R *st) {
+    size_t EN = (size_t)E * N, k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= EN) return;
+    const double tas = (double)st[(size_t)S_TAS * EN + k], hdg = (double)st[(size_t)S_HDG * EN + k] * kD2R;
+    st[(size_t)S_GSN * EN + k] = (R)(tas * cos(hdg)); st[(size_t)S_GSE * EN + k] = (R)(tas * sin(hdg));
+}
+static bool is_ext(const bsg_handle *h) { return h->cfg.env_kind == BSG_KIND_MERGE || h->wind.n > 0 || h->noise_sigma > 0.0; }
+static int refresh_gs(bsg_handle *h) {
+    const size_t EN = (size_t)h->cfg.num_envs * h->cfg.max_ac;
+    const int tb = 256, gb = (int)((EN + tb - 1) / tb);
+    if (h->cfg.precision == BSG_FP64) derive_gs_kernel<double><<<gb, tb>>>(h->cfg.num_envs, h->cfg.max_ac, (double *)h->st);
+    else derive_gs_kernel<float><<<gb, tb>>>(h->cfg.num_envs, h->cfg.max_ac, (float *)h->st);
+    h->launches++;
+    CK(h, cudaGetLastError());
+    CK(h, cudaDeviceSynchronize());
+    return BSG_OK;
+}
+
+// the pinned / device output block of bsg_step_host; sized by obs_dim (which bsg_set_wind can grow by two slots)
+static int alloc_out(bsg_handle *h) {
+    if (h->h_out) { cudaFreeHost(h->h_out); h->h_out = nullptr; }
+    if (h->d_out) { cudaFree(h->d_out); h->d_out = nullptr; }
+    h->out_bytes = (size_t)h->cfg.num_envs * (h->obs_dim + 1 + 4) * rsize(h) + (size_t)h->cfg.num_envs * 2 * sizeof(int32_t);
+    CK(h, cudaMallocHost(&h->h_out, h->out_bytes));
+    CK(h, cudaMalloc(&h->d_out, h->out_bytes));
+    return BSG_OK;
 }
 
 extern "C" {
@@ -78,7 +112,8 @@ int bsg_launch_count(const bsg_handle *h, int64_t *n) {
 
 int bsg_create(const bsg_config *c, bsg_handle **out) {
     if (!c || !out || c->struct_size != (int32_t)sizeof(bsg_config)) return BSG_ERR_ARG;
-    if (c->env_kind < 0 || c->env_kind > BSG_KIND_RAW || c->num_envs < 1 || c->max_ac < 1) return BSG_ERR_ARG;
+    if (c->env_kind < 0 || c->env_kind > BSG_KIND_MERGE || c->num_envs < 1 || c->max_ac < 1) return BSG_ERR_ARG;
+    if (c->env_kind == BSG_KIND_MERGE && (c->max_ac < 2 || c->max_ac > 64)) return BSG_ERR_UNSUPPORTED;   // EXT kernels: N <= 64
     if (c->max_ac > 256) return BSG_ERR_UNSUPPORTED;          // fused step: one env's rows live in one CTA
     if (c->reso_on && (c->max_ac > 64 || !c->asas_on)) return BSG_ERR_UNSUPPORTED;
     int ndev = 0;
@@ -89,8 +124,8 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     *out = h;
     h->cfg = *c;
     bsg_config &g = h->cfg;
-    static const int dsub[4] = { 10, 30, 5, 1 };
-    static const double ddt[4] = { 5.0, 1.0, 1.0, 1.0 };
+    static const int dsub[5] = { 10, 30, 5, 1, 10 };
+    static const double ddt[5] = { 5.0, 1.0, 1.0, 1.0, 5.0 };
     if (g.substeps <= 0) g.substeps = dsub[g.env_kind];
     if (g.simdt <= 0) g.simdt = ddt[g.env_kind];
     if (g.rpz_m <= 0) g.rpz_m = 5 * kNm;
@@ -99,9 +134,9 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     if (g.resofach <= 0) g.resofach = 1.05;
     if (g.resofacv <= 0) g.resofacv = 1.05;
     const int N = g.max_ac, K = N - 1, E = g.num_envs;
-    h->obs_dim = g.env_kind == BSG_KIND_HORIZONTAL ? 5 * K + 3 : g.env_kind == BSG_KIND_VERTICAL ? 4 + 7 * K
-                 : g.env_kind == BSG_KIND_SECTOR ? 31 : 0;
-    h->act_dim = g.env_kind == BSG_KIND_SECTOR ? 2 : (g.env_kind == BSG_KIND_RAW ? 0 : 1);
+    (void)K;
+    h->obs_dim = env_obs_dim(g.env_kind, N);
+    h->act_dim = (g.env_kind == BSG_KIND_SECTOR || g.env_kind == BSG_KIND_MERGE) ? 2 : (g.env_kind == BSG_KIND_RAW ? 0 : 1);
     // CTA size: the one of {128, 256} that wastes fewer lanes on whole envs (ties -> 128: better balance)
     {   // ISA conversions of the fixed creation speeds (host fp64 replica of vcas2tas / vtas2cas)
         auto atmos = [](double hh, double &p, double &rho) {
@@ -124,10 +159,17 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
         h->rc.tas_s = cas2tas(150.0, 350.0);
         h->rc.coslat_hv = std::cos(52.0 * kD2R);
         h->rc.ccl = std::cos(kCenterLat * kD2R);
+        // Merge (merge_env.py:39-45): runway, FAF = get_point_at_distance(runway, 200 km, bearing 0) (functions.py:24-42)
+        h->rc.tas_m = cas2tas(100.0, 10000.0);
+        h->rc.rwy_lat = 52.36239301495972; h->rc.rwy_lon = 4.713195734579777;
+        const double lat1 = h->rc.rwy_lat * kD2R, lon1 = h->rc.rwy_lon * kD2R, dr = 200.0 / 6371.0, al = 0.0;
+        const double lat2 = std::asin(std::sin(lat1) * std::cos(dr) + std::cos(lat1) * std::sin(dr) * std::cos(al));
+        const double lon2 = lon1 + std::atan2(std::sin(al) * std::sin(dr) * std::cos(lat1), std::cos(dr) - std::sin(lat1) * std::sin(lat2));
+        h->rc.faf_lat = lat2 * kR2D; h->rc.faf_lon = lon2 * kR2D;
     }
     h->tpb = 128;
     if (N > 128 || (256 / N) * N * 128 > (128 / N) * N * 256) h->tpb = 256;
-    if (const char *f = getenv("BSG_FORCE_TPB")) { int t = atoi(f); if ((t == 128 || t == 256 || (t == 320 && g.precision == BSG_FP32)) && t >= N) h->tpb = t; }
+    if (const char *f = getenv("BSG_FORCE_TPB")) { int t = atoi(f); if ((t == 128 || t == 256 || ((t == 320 || t == 160) && g.precision == BSG_FP32 && g.env_kind != BSG_KIND_MERGE && N <= 64)) && t >= N) h->tpb = t; }
     h->epb = h->tpb / N;
     if (const char *f = getenv("BSG_FORCE_EPB")) { int t = atoi(f); if (t >= 1 && t * N <= h->tpb) h->epb = t; }
     const size_t rs = rsize(h);
@@ -147,13 +189,44 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     CK(h, cudaMemset(h->ev, 0, (size_t)E * BSG_NE * sizeof(double)));
     // host-buffer step: [obs | reward | info | terminated | truncated] in one pinned block
     h->act_bytes = (size_t)E * (h->act_dim > 0 ? h->act_dim : 1) * rs;
-    h->out_bytes = (size_t)E * (h->obs_dim + 1 + 4) * rs + (size_t)E * 2 * sizeof(int32_t);
     CK(h, cudaMallocHost(&h->h_act, h->act_bytes));
-    CK(h, cudaMallocHost(&h->h_out, h->out_bytes));
     CK(h, cudaMalloc(&h->d_act, h->act_bytes));
-    CK(h, cudaMalloc(&h->d_out, h->out_bytes));
+    { int rc = alloc_out(h); if (rc != BSG_OK) return rc; }
     CK(h, cudaStreamCreateWithFlags(&h->hs, cudaStreamNonBlocking));
     if (h->smem > 48 * 1024) { h->err = "shared memory per CTA above 48 KB"; return BSG_ERR_UNSUPPORTED; }
+    return BSG_OK;
+}
+
+int bsg_set_wind(bsg_handle *h, int32_t npoints, const double *lat, const double *lon, const double *vnorth,
+                 const double *veast, int32_t augment_obs) {
+    if (!h || npoints < 0 || npoints > BSG_MAX_WIND) return BSG_ERR_ARG;
+    if (npoints > 0 && (!lat || !lon || !vnorth || !veast)) return BSG_ERR_ARG;
+    if (h->cfg.env_kind == BSG_KIND_RAW) return BSG_ERR_UNSUPPORTED;
+    if (npoints > 0 && h->cfg.precision == BSG_FP32 && h->cfg.max_ac > 64) {
+        h->err = "bsg_set_wind: the fp32 EXT kernels hold N <= 64 aircraft per env"; return BSG_ERR_UNSUPPORTED;
+    }
+    CK(h, cudaSetDevice(h->cfg.device));
+    CK(h, cudaDeviceSynchronize());
+    const bool was_ext = is_ext(h);
+    memset(&h->wind, 0, sizeof(h->wind));
+    h->wind.n = npoints;
+    h->wind.obs = (npoints > 0 && augment_obs) ? 1 : 0;
+    for (int k = 0; k < npoints; k++) { h->wind.lat[k] = lat[k]; h->wind.lon[k] = lon[k]; h->wind.vn[k] = vnorth[k]; h->wind.ve[k] = veast[k]; }
+    if (!was_ext && is_ext(h)) { int rc = refresh_gs(h); if (rc != BSG_OK) return rc; }
+    const int od = env_obs_dim(h->cfg.env_kind, h->cfg.max_ac) + (h->wind.obs ? 2 : 0);
+    if (od != h->obs_dim) { h->obs_dim = od; return alloc_out(h); }
+    return BSG_OK;
+}
+
+int bsg_set_obs_noise(bsg_handle *h, double sigma, uint64_t seed) {
+    if (!h || !(sigma >= 0.0)) return BSG_ERR_ARG;
+    if (h->cfg.env_kind == BSG_KIND_RAW) return BSG_ERR_UNSUPPORTED;
+    if (sigma > 0.0 && h->cfg.precision == BSG_FP32 && h->cfg.max_ac > 64) {
+        h->err = "bsg_set_obs_noise: the fp32 EXT kernels hold N <= 64 aircraft per env"; return BSG_ERR_UNSUPPORTED;
+    }
+    const bool was_ext = is_ext(h);
+    h->noise_sigma = sigma; h->noise_seed = seed;
+    if (!was_ext && is_ext(h)) { CK(h, cudaSetDevice(h->cfg.device)); return refresh_gs(h); }
     return BSG_OK;
 }
 

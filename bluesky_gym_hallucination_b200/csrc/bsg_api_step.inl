@@ -17,18 +17,34 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     A.skip = (ar && h->autoreset == 1) ? h->done_buf[h->flip] : nullptr;
     // next-step mode: the reset of the envs that ended in the previous step is fused into this launch
     A.fuse_reset = (A.skip != nullptr) ? 1 : 0; A.fixed_nac = g.fixed_nac; A.RC = h->rc; A.ar_seed = h->ar_seed; A.episode = h->episode;
+    A.W = h->wind; A.noise_sigma = (R)h->noise_sigma; A.noise_seed = h->noise_seed; A.noise_ctr = (unsigned int)h->launches;
+    // EXT instantiations: Merge env, wind field, observation noise (fp32: the symmetric sweep only, N <= 64)
+    const bool ext = is_ext(h);
     int32_t *done_now = nullptr;
     if (ar) { done_now = h->done_buf[h->flip ^ 1]; if (!A.out.done) A.out.done = done_now; }
     const int grid = (g.num_envs + h->epb - 1) / h->epb;
     const bool reso = g.reso_on && g.asas_on;
     const dim3 gd(grid), bd(((h->epb * g.max_ac + 31) / 32) * 32);      // whole warps covering the CTA's envs
 #define BSG_LAUNCH(TPB, RESO, SYM) step_kernel<R, TPB, RESO, SYM><<<gd, bd, h->smem, s>>>(A)
-    if constexpr (sizeof(R) == 4) {
+#define BSG_LAUNCH_EXT(TPB, RESO, SYM) step_kernel<R, TPB, RESO, SYM, true><<<gd, bd, h->smem, s>>>(A)
+    if (ext) {
+        if (h->tpb != 128 && h->tpb != 256) { h->err = "EXT kernels: CTA of 128 or 256 threads"; return BSG_ERR_UNSUPPORTED; }
+        if constexpr (sizeof(R) == 4) {
+            if (g.max_ac > 64) { h->err = "EXT kernels (fp32): N <= 64"; return BSG_ERR_UNSUPPORTED; }
+            if (h->tpb == 128) { if (reso) BSG_LAUNCH_EXT(128, true, true); else BSG_LAUNCH_EXT(128, false, true); }
+            else { if (reso) BSG_LAUNCH_EXT(256, true, true); else BSG_LAUNCH_EXT(256, false, true); }
+        } else {
+            if (h->tpb == 128) { if (reso) BSG_LAUNCH_EXT(128, true, false); else BSG_LAUNCH_EXT(128, false, false); }
+            else { if (reso) BSG_LAUNCH_EXT(256, true, false); else BSG_LAUNCH_EXT(256, false, false); }
+        }
+    } else if constexpr (sizeof(R) == 4) {
         const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM");          // symmetric half-ring sweep (fp32 fast path)
         if (h->tpb == 128) {
             if (sym) { if (reso) BSG_LAUNCH(128, true, true); else BSG_LAUNCH(128, false, true); }
             else if (reso) BSG_LAUNCH(128, true, false); else BSG_LAUNCH(128, false, false);
-        } else if (h->tpb == 256) {
+        } else if (h->tpb == 160 && sym) {
+            if (reso) BSG_LAUNCH(160, true, true); else BSG_LAUNCH(160, false, true);
+        } else if (h->tpb == 256 || h->tpb == 160) {
             if (sym) { if (reso) BSG_LAUNCH(256, true, true); else BSG_LAUNCH(256, false, true); }
             else if (reso) BSG_LAUNCH(256, true, false); else BSG_LAUNCH(256, false, false);
         } else {
@@ -40,6 +56,7 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
         else { if (reso) BSG_LAUNCH(256, true, false); else BSG_LAUNCH(256, false, false); }
     }
 #undef BSG_LAUNCH
+#undef BSG_LAUNCH_EXT
     h->launches++;
     CK(h, cudaGetLastError());
     if (ar) {
@@ -102,8 +119,9 @@ int bsg_get_state(bsg_handle *h, double *ac, uint64_t *reso, int32_t *nac, doubl
     if (ac) {
         CK(h, cudaMemset(h->stage64, 0, (size_t)g.num_envs * BSG_NF * g.max_ac * sizeof(double)));
         const int tb = 256, gb = (int)((EN + tb - 1) / tb);
-        if (g.precision == BSG_FP64) export_state_kernel<double><<<gb, tb>>>(h->stage64, g.num_envs, g.max_ac, h->pos, (const double *)h->st);
-        else export_state_kernel<float><<<gb, tb>>>(h->stage64, g.num_envs, g.max_ac, h->pos, (const float *)h->st);
+        const int derive_gs = !is_ext(h);
+        if (g.precision == BSG_FP64) export_state_kernel<double><<<gb, tb>>>(h->stage64, g.num_envs, g.max_ac, h->pos, (const double *)h->st, derive_gs);
+        else export_state_kernel<float><<<gb, tb>>>(h->stage64, g.num_envs, g.max_ac, h->pos, (const float *)h->st, derive_gs);
         h->launches++;
         CK(h, cudaGetLastError());
         CK(h, cudaMemcpy(ac, h->stage64, (size_t)g.num_envs * BSG_NF * g.max_ac * sizeof(double), cudaMemcpyDeviceToHost));

@@ -35,12 +35,20 @@ constexpr double kVsMin = -20.0, kVsMax = 20.0, kHmax = 12131.0, kMmo = 0.82, kA
 // everything else in R.  Layout per env: pos[2][N], st[NS][N]  (field-major => coalesced by aircraft).
 enum StField { S_ALT, S_HDG, S_TAS, S_VS, S_CAS, S_SELSPD, S_SELALT, S_SELVS, S_APTRK, S_AX,
                S_ASAS_TRK, S_ASAS_TAS, S_ASAS_VS, S_ASAS_ALT, S_ASAS_ACTIVE, S_PHASE,
+               // only read / written by the EXT kernels (wind field, LNAV routes); derived on export otherwise
+               S_GSN, S_GSE, S_LNAV,
                // fast-path caches of pure functions (key -> value); unused by the parity path
                S_C_ALT, S_C_SPD, S_C_APTAS, S_C_PH, S_C_SELALT, S_C_LO, S_C_HI, S_NS };
 
 // launch constants of the reset path: the ISA conversions of the fixed creation speeds, evaluated once on the
 // host at bsg_create (six pow() per aircraft would otherwise sit on the critical path of a fused reset)
-struct ResetConst { double tas_h, cas_h, tas_s, coslat_hv, ccl; };   // vcas2tas(150,0), vtas2cas(tas_h,0), vcas2tas(150,350), cos(52 deg), cos(sector centre lat)
+struct ResetConst {
+    double tas_h, cas_h, tas_s, coslat_hv, ccl;   // vcas2tas(150,0), vtas2cas(tas_h,0), vcas2tas(150,350), cos(52 deg), cos(sector centre lat)
+    double tas_m, faf_lat, faf_lon, rwy_lat, rwy_lon;   // Merge: vcas2tas(100, 10000), FAF and runway (merge_env.py:39-45)
+};
+
+// wind field (bsg_set_wind): passed by value in the kernel arguments
+struct WindArgs { int n, obs; double lat[BSG_MAX_WIND], lon[BSG_MAX_WIND], vn[BSG_MAX_WIND], ve[BSG_MAX_WIND]; };
 
 template <typename R> __device__ __forceinline__ R rsgn(R x) { return R((x > R(0)) - (x < R(0))); }
 

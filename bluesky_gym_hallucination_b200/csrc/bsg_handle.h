@@ -24,6 +24,9 @@ struct bsg_handle {
     int autoreset = 0, flip = 0;      // next-step auto-reset: done_buf[flip] = envs reset after the last step
     uint64_t ar_seed = 0;
     bsg::ResetConst rc = {};          // host-evaluated ISA constants of the reset path
+    bsg::WindArgs wind = {};          // bsg_set_wind
+    double noise_sigma = 0.0;         // bsg_set_obs_noise
+    uint64_t noise_seed = 0;
     int32_t *done_buf[2] = { nullptr, nullptr };      // [E] reset counter (Philox counter word)
     int64_t launches = 0;
     std::string err;

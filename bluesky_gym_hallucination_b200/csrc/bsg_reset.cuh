@@ -4,6 +4,7 @@
 //   Vertical    bluesky_gym/envs/vertical_cr_env.py:183-200,258-281
 //   Sector      bluesky_gym/envs/sector_cr_env.py:87-217      (polygon growth, density draw, perimeter
 //               waypoints, bounding-box rejection sampling, get_hdg)
+//   Merge       bluesky_gym/envs/merge_env.py:100-158         (spawn radials towards the FAF, LNAV route for intruders)
 // Same value laws as the reference; the random stream is Philox4x32-10 keyed by (seed) with counter
 // (env, episode, draw index, stream) instead of numpy's global legacy generator (the global
 // draw order cannot be reproduced on a GPU; parity runs inject oracle state through bsg_set_state).
@@ -45,7 +46,7 @@ struct Philox {
     }
 };
 
-struct AcInit { double lat, lon, alt, hdg, cas, tas, vs, selalt; };
+struct AcInit { double lat, lon, alt, hdg, cas, tas, vs, selalt; int lnav; };
 
 // Traffic.creconfs geometry for one intruder of a target at (lat0, lon0), track trk0, speed gs0.
 // Same construction with the inverse trigonometry folded away: the bearing enters only through its sine and
@@ -80,6 +81,9 @@ __device__ inline void write_ac(double *pos, R *st, size_t EN, size_t k, const A
     st[S_ALT * EN + k] = (R)a.alt; st[S_HDG * EN + k] = (R)a.hdg; st[S_TAS * EN + k] = (R)a.tas;
     st[S_VS * EN + k] = (R)a.vs; st[S_CAS * EN + k] = (R)a.cas; st[S_SELSPD * EN + k] = (R)a.cas;
     st[S_SELALT * EN + k] = (R)a.selalt; st[S_APTRK * EN + k] = (R)a.hdg; st[S_AX * EN + k] = (R)kKts;
+    double sh, ch;                                               // Traffic.cre: gsnorth / gseast from tas and hdg
+    sincos(a.hdg * kD2R, &sh, &ch);
+    st[S_GSN * EN + k] = (R)(a.tas * ch); st[S_GSE * EN + k] = (R)(a.tas * sh); st[S_LNAV * EN + k] = (R)a.lnav;
     for (int f = S_C_ALT; f < S_NS; f++) st[(size_t)f * EN + k] = (R)NAN;
 }
 
@@ -164,6 +168,10 @@ static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int
             v[BSG_EV_POLY + 2 * k + 1] = kCenterLon + py[k] / (60 * ccl);
         }
         v[BSG_EV_NVERT] = nv;
+    } else if (kind == BSG_KIND_MERGE) {      // the route every intruder gets: FAF, then the runway (merge_env.py:42-45)
+        S.gs0 = RC.tas_m;
+        v[BSG_EV_WPT_LAT] = RC.faf_lat; v[BSG_EV_WPT_LON] = RC.faf_lon;
+        v[BSG_EV_WPT_X] = RC.rwy_lat; v[BSG_EV_WPT_Y] = RC.rwy_lon;
     }
     *Sp = S;
 }
@@ -178,6 +186,7 @@ static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e
     const double ccl = RC.ccl;
     reso[k] = 0ull;
     AcInit a = {};
+    a.lnav = -1;
     Philox g(seed, (uint32_t)e, ep, 1u + (uint32_t)i);
     if (kind == BSG_KIND_HORIZONTAL || kind == BSG_KIND_VERTICAL) {
         const double alt_own = kind == BSG_KIND_VERTICAL ? S.alt0 : 0.0;
@@ -227,6 +236,18 @@ static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e
         a.hdg = pymod(atan2(hx, hy) * kR2D + 360, 360);
         a.alt = 350.0; a.cas = 150.0; a.tas = S.gs0; a.selalt = 350.0;
         if (i == 0) { v[BSG_EV_WPT_X] = wx; v[BSG_EV_WPT_Y] = wy; }
+    } else if (kind == BSG_KIND_MERGE) {
+        // merge_env.py:110-115,148-156: a radial within +-15 deg of north from the FAF, 50-200 km out for the agent and
+        // 20-500 km for the intruders (functions.get_point_at_distance, km on the 6371 km sphere), heading back along it
+        const double brg = -15.0 + 30.0 * g.uniform();
+        const double dkm = i == 0 ? 50.0 + 150.0 * g.uniform() : 20.0 + 480.0 * g.uniform();
+        const double lat1 = RC.faf_lat * kD2R, lon1 = RC.faf_lon * kD2R, al = brg * kD2R, dr = dkm / 6371.0;
+        const double lat2 = asin(sin(lat1) * cos(dr) + cos(lat1) * sin(dr) * cos(al));
+        const double lon2 = lon1 + atan2(sin(al) * sin(dr) * cos(lat1), cos(dr) - sin(lat1) * sin(lat2));
+        a.lat = lat2 * kR2D; a.lon = lon2 * kR2D;
+        a.hdg = brg - 180.0;                                       // handed to cre() as is (negative)
+        a.alt = 10000.0; a.cas = 100.0; a.tas = S.gs0; a.selalt = 10000.0;
+        a.lnav = i == 0 ? -1 : 0;                                  // ADDWPT activates LNAV towards the FAF
     }
     write_ac<R>(pos, st, EN, k, a);
 }

@@ -25,6 +25,9 @@ template <typename R> struct StepArgs {
     // (bsg_reset.cuh stages) instead of in a separate reset launch; `nac` is written by that stage
     int fuse_reset, fixed_nac; unsigned long long ar_seed; unsigned int *episode; ResetConst RC;
     bsg_step_out out;
+    // EXT kernels only: wind field, observation noise (sigma, Philox key, launch counter)
+    WindArgs W;
+    R noise_sigma; unsigned long long noise_seed; unsigned int noise_ctr;
 };
 
 template <typename R> struct RecOf { using type = RecLit; };

@@ -30,7 +30,9 @@ __device__ __forceinline__ void cd_params_for(const CdParams &P, CdParams &lit, 
 // CTA size / residency: 128-thread CTAs keep the small-N configs in one balanced wave
 // (C2: 683 CTAs over 148 SMs x 5 resident), 256 threads only when one env needs them (N > 128).
 template <typename R, int TPB> struct StepBounds {
-    static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : (sizeof(R) == 4 ? 2 : 1);   // 320: 2 x 320 threads, <= 102 registers
+    // 320: 2 x 320 threads, <= 102 registers; 160: 4 x 160 threads, <= 102 registers (C2: 7 envs per CTA, 586 CTAs =
+    // one wave of 4 per SM -> at most 28 envs per SM instead of 30)
+    static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : TPB == 160 ? 4 : (sizeof(R) == 4 ? 2 : 1);
 };
 // per-env row of CD records in shared memory: N records + 16 B so that the rows of the envs sharing a
 // warp start in different banks (N * 32 B is a multiple of 128 B for N = 20: 2-way LDS.128 conflicts)
@@ -82,7 +84,9 @@ static __device__ __noinline__ void fused_reset(int kind, int fixed_nac, int E, 
 // (the fp32 pair form is exactly symmetric under i <-> j, so the ordered matrix it stands for is bit-identical
 // to the full sweep); a conflict sets bit j of row i and bit i of row j with shared-memory atomics, and after
 // one more barrier each thread finishes its own row (row reductions, MVP, resumenav) from its conflict bit row.
-template <typename R, int TPB, bool RESO, bool SYM>
+// EXT: the wrapper / Merge features (wind field, LNAV route, Merge env layer, observation noise; SURVEY f-3, f-4) as a
+// compile-time switch, so the instantiations the headline configs run are unchanged by them.
+template <typename R, int TPB, bool RESO, bool SYM, bool EXT = false>
 __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_kernel(const StepArgs<R> A) {
     using Rec = typename RecOf<R>::type;
     static_assert(!SYM || sizeof(R) == 4, "the symmetric sweep is the fp32 fast path");
@@ -113,8 +117,8 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     AcReg<R> a = {};
     unsigned long long resorow = 0;
     if (live) {
-        ac_load_raw<R, RESO>(a, A.pos, A.st, EN, k);
-        ac_derive<R>(a);
+        ac_load_raw<R, RESO, EXT>(a, A.pos, A.st, EN, k);
+        ac_derive<R, EXT>(a);
         if (reso) resorow = A.reso[k];
     }
     // ------------------------------------------------------------------ action intake (agent = aircraft 0)
@@ -125,15 +129,34 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
 #pragma unroll
         for (int s2 = 0; s2 < BSG_EV_POLY; s2++) es[le].ev[s2] = ev[s2];   // 14 independent loads, staged in smem
         if (A.actions && !skip) {
+            // AP.selhdgcmd under a wind field: the HDG argument becomes the track it gives (above 50 ft)
+            auto hdg_cmd = [&](R hdg) -> R {
+                if constexpr (EXT) {
+                    if (A.W.n > 0 && a.alt > R(50.0 * kFt)) {
+                        R vn, ve, sh, ch;
+                        wind_at<R>(A.W, a.lat, a.lon, vn, ve);
+                        rsincos_deg<R>(hdg, sh, ch);
+                        if constexpr (sizeof(R) == 8) return pymod(atan2(a.tas * sh + ve, a.tas * ch + vn) * kR2D, 360.0);
+                        else return wrap360(atan2f(fmaf(a.tas, sh, ve), fmaf(a.tas, ch, vn)) * float(kR2D));
+                    }
+                }
+                return hdg;
+            };
             if (A.kind == BSG_KIND_HORIZONTAL) {                           // horizontal_cr_env.py:272-275
-                a.aptrk = R(es[le].ev[BSG_EV_AC_HDG]) + A.actions[e] * R(45);
+                a.aptrk = hdg_cmd(R(es[le].ev[BSG_EV_AC_HDG]) + A.actions[e] * R(45));
             } else if (A.kind == BSG_KIND_VERTICAL) {                      // vertical_cr_env.py:242-256
                 R v = A.actions[e] * R(12.5);
                 a.selalt = v >= R(0) ? R(1000000) : R(0);
                 a.selvs = v;
             } else if (A.kind == BSG_KIND_SECTOR) {                        // sector_cr_env.py:315-322
                 R dh = A.actions[2 * e] * R(22.5), dv = A.actions[2 * e + 1] * R(20.0 / 3);
-                a.aptrk = bound180<R>(a.hdg + dh);
+                a.aptrk = hdg_cmd(bound180<R>(a.hdg + dh));
+                R spd_kts = (a.cas + dv) * R(1.94384);
+                a.selspd = fabs(spd_kts) > R(1) ? spd_kts * R(kKts) : spd_kts;
+            } else if (EXT && A.kind == BSG_KIND_MERGE) {                  // merge_env.py:285-293 (HDG: LNAV off)
+                R dh = A.actions[2 * e] * R(15), dv = A.actions[2 * e + 1] * R(20);
+                a.aptrk = hdg_cmd(bound180<R>(a.hdg + dh));
+                a.lnav = -1;
                 R spd_kts = (a.cas + dv) * R(1.94384);
                 a.selspd = fabs(spd_kts) > R(1) ? spd_kts * R(kKts) : spd_kts;
             }
@@ -145,6 +168,12 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     const R alt_ref = valid ? es[le].alt_ref : R(0);
     CdParams PL; CdParamsF PF;
     cd_params_for<R>(A.P, PL, PF);
+    ExtCtx X;
+    if constexpr (EXT) {
+        const double *sv = es[valid ? le : 0].ev;
+        X.W = &A.W; X.merge = A.kind == BSG_KIND_MERGE;
+        X.faf_lat = sv[BSG_EV_WPT_LAT]; X.faf_lon = sv[BSG_EV_WPT_LON]; X.rwy_lat = sv[BSG_EV_WPT_X]; X.rwy_lon = sv[BSG_EV_WPT_Y];
+    }
 
     RowAcc<R> acc;
     // ------------------------------------------------------------------ K substeps
@@ -328,13 +357,13 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         }
         if (live && !skip) {
             const bool last = (s == A.substeps - 1);
-            if constexpr (sizeof(R) == 8) kin_substep_lit(a, A.dt, reso, last);
-            else kin_substep_fast(a, A.dt, reso, last && i == 0 && A.kind == BSG_KIND_SECTOR);
+            if constexpr (sizeof(R) == 8) kin_substep_lit<EXT>(a, A.dt, reso, last, &X);
+            else kin_substep_fast<EXT>(a, A.dt, reso, last && i == 0 && (A.kind == BSG_KIND_SECTOR || A.kind == BSG_KIND_MERGE), &X);
         }
     }
     BSG_STAMP(2);
     if (live && !skip) {
-        ac_store<R, RESO>(a, A.pos, A.st, EN, k);
+        ac_store<R, RESO, EXT>(a, A.pos, A.st, EN, k);
         if (reso) A.reso[k] = resorow;
     }
     if (valid && i < N) {      // CD row outputs of the last detection (dead slots: zeros / -1)
@@ -349,7 +378,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         if (o.cd_tcpamax) ((R *)o.cd_tcpamax)[k] = acc.tcpamax;
     }
     BSG_STAMP(3);
-    env_layer<R>(A, a, es, sdist, le, i, e, nl, valid, live, skip, ev);
+    env_layer<R, EXT>(A, a, es, sdist, le, i, e, nl, valid, live, skip, ev);
     BSG_STAMP(4);
 }
 

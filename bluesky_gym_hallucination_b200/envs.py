@@ -1,8 +1,8 @@
 """Single-env facades registered under the reference's ids: the unchanged Gymnasium API
-(gym.make('HorizontalCREnv-v0' | 'VerticalCREnv-v0' | 'SectorCREnv-v0'), reset/step, obs dicts of
+(gym.make('HorizontalCREnv-v0' | 'VerticalCREnv-v0' | 'SectorCREnv-v0' | 'MergeEnv-v0'), reset/step, obs dicts of
 float64 arrays, info keys) in front of the batched CUDA core with num_envs = 1.
 Reference classes: bluesky_gym/envs/horizontal_cr_env.py:32-125, vertical_cr_env.py:47-305,
-sector_cr_env.py:39-132.  render_mode="human" needs an SDL window: unavailable on this box."""
+sector_cr_env.py:39-132, merge_env.py:47-146.  render_mode="human" needs an SDL window: unavailable on this box."""
 import numpy as np
 import torch
 from . import _lib as L
@@ -33,12 +33,15 @@ class _SingleEnv(Env):
         obs = self._v._obs_dict(self._v.core.observe().cpu().numpy())
         keys = INFO_KEYS[self._v.kind]
         third = 0 if self._v.kind == L.KIND_VERTICAL else float('nan')
-        return {k: v[0] for k, v in obs.items()}, {keys[0]: 0, keys[1]: 0, keys[2]: third}
+        info = {keys[0]: 0, keys[1]: 0, keys[2]: third}
+        if len(keys) > 3:
+            info[keys[3]] = 0
+        return {k: v[0] for k, v in obs.items()}, info
 
     def step(self, action):
         obs, rew, term, trunc, info = self._v.step(np.asarray(action, dtype=np.float64).reshape(1, -1))
         o = {k: v[0] for k, v in obs.items()}
-        i = {k: (int(v[0]) if k == 'total_intrusions' else float(v[0])) for k, v in info.items()}
+        i = {k: (int(v[0]) if v.dtype.kind == 'i' else float(v[0])) for k, v in info.items()}
         return o, float(rew[0]), int(term[0]), bool(trunc[0]), i
 
     def render(self):
@@ -63,3 +66,8 @@ class SectorCREnv(_SingleEnv):
         if ac_density_mode != "normal":
             raise NotImplementedError("the device generator implements the reference's default 'normal' density law")
         super().__init__(render_mode=render_mode, **kw)
+
+
+class MergeEnv(_SingleEnv):
+    """bluesky_gym/envs/merge_env.py:47-146 (never truncates itself: TimeLimit 50 comes from the registry)."""
+    ENV_ID = 'MergeEnv-v0'

@@ -3,6 +3,7 @@ It restates the reset path of the reference env layer for N aircraft per env:
   Horizontal  bluesky_gym/envs/horizontal_cr_env.py:82-148 (own at BlueSky's default spawn + creconfs intruders)
   Vertical    bluesky_gym/envs/vertical_cr_env.py:183-200,258-281
   Sector      bluesky_gym/envs/sector_cr_env.py:87-217 (rejection-grown polygon, density draw, rejection sampling)
+  Merge       bluesky_gym/envs/merge_env.py:100-158 (spawn radials towards the FAF; intruders on the LNAV route)
 with the same value laws but numpy's Generator instead of the global legacy stream.
 Used for seeded synthetic traffic (tests, bench) and as the host reset of the vector env; the
 device-side generator (bsg_reset) draws from the same laws with Philox.
@@ -49,6 +50,8 @@ def _fill(ac, idx, lat, lon, alt, hdg, cas, vs=0.0, selalt=None):
     ac[:, F['selalt'], idx] = alt if selalt is None else selalt
     ac[:, F['aptrk'], idx] = hdg
     ac[:, F['ax'], idx] = 0.514444
+    ac[:, F['gsn'], idx] = tas * np.cos(np.radians(hdg)); ac[:, F['gse'], idx] = tas * np.sin(np.radians(hdg))
+    ac[:, F['lnav'], idx] = -1.0
 
 
 def _creconfs(rng, shape, lat0, lon0, trk0_deg, gs0, tlosh, dpsi, cpa_nm):
@@ -190,6 +193,36 @@ def sector(E, N, seed=0, n_poly=64, fixed_n=True):
         _fill(sub, slice(0, N), lat, lon, np.full((ne, N), 350.0), hdg, np.full((ne, N), 150.0))
         ac[envs] = sub
         ev[envs, L.EV['wpt_x']] = wp[:, 0, 0]; ev[envs, L.EV['wpt_y']] = wp[:, 0, 1]
+    return ac, reso, nac, ev
+
+
+RWY = (52.36239301495972, 4.713195734579777)            # merge_env.py:39-40
+
+
+def point_at_distance(lat1, lon1, d_km, bearing, R=6371.0):
+    """functions.get_point_at_distance (bluesky_gym/envs/common/functions.py:24-42)."""
+    lat1, lon1, a = np.radians(lat1), np.radians(lon1), np.radians(bearing)
+    lat2 = np.arcsin(np.sin(lat1) * np.cos(d_km / R) + np.cos(lat1) * np.sin(d_km / R) * np.cos(a))
+    lon2 = lon1 + np.arctan2(np.sin(a) * np.sin(d_km / R) * np.cos(lat1), np.cos(d_km / R) - np.sin(lat1) * np.sin(lat2))
+    return np.degrees(lat2), np.degrees(lon2)
+
+
+FAF = point_at_distance(RWY[0], RWY[1], 200.0, 0.0)     # merge_env.py:42-45
+
+
+def merge(E, N=20, seed=0):
+    """Agent 50-200 km and N-1 intruders 20-500 km out on radials within +-15 deg of north from the FAF, all heading
+    back along their radial at CAS 100 m/s, 10 km altitude; intruders fly the LNAV route FAF -> runway."""
+    rng = np.random.default_rng(seed)
+    ac, reso, nac, ev = _blank(E, N)
+    brg = rng.uniform(-15.0, 15.0, (E, N))
+    dist = rng.uniform(20.0, 500.0, (E, N))
+    dist[:, 0] = rng.uniform(50.0, 200.0, E)
+    lat, lon = point_at_distance(FAF[0], FAF[1], dist, brg)
+    _fill(ac, slice(0, N), lat, lon, np.full((E, N), 10000.0), brg - 180.0, np.full((E, N), 100.0))
+    ac[:, L.F['lnav'], 1:] = 0.0
+    ev[:, L.EV['wpt_lat']] = FAF[0]; ev[:, L.EV['wpt_lon']] = FAF[1]
+    ev[:, L.EV['wpt_x']] = RWY[0]; ev[:, L.EV['wpt_y']] = RWY[1]
     return ac, reso, nac, ev
 
 

@@ -4,7 +4,9 @@ same env ids, observation keys, action shapes, reward / terminated / truncated /
   bluesky_gym/envs/horizontal_cr_env.py:49-62,82-125,215-223
   bluesky_gym/envs/vertical_cr_env.py:67-85,203-211,258-305
   bluesky_gym/envs/sector_cr_env.py:52-67,87-132,219-225
-and the registrations of bluesky_gym/__init__.py:18-34 (max_episode_steps 300 / 300 / 200).
+  bluesky_gym/envs/merge_env.py:57-76,100-146,238-245
+and the registrations of bluesky_gym/__init__.py:18-46 (max_episode_steps 300 / 300 / 200 / 50).  The reference's
+wrappers (bluesky_gym/wrappers/wind.py, uncertainty.py) are constructor options: `wind=`, `obs_noise=`.
 PyTorch appears only as the tensor hand-off to RL libraries (`step_tensors`)."""
 import numpy as np
 import torch
@@ -17,20 +19,23 @@ ENV_SPECS = {
     'HorizontalCREnv-v0': (L.KIND_HORIZONTAL, 6, 300, 1),
     'VerticalCREnv-v0': (L.KIND_VERTICAL, 6, 300, 1),
     'SectorCREnv-v0': (L.KIND_SECTOR, 32, 200, 2),
+    'MergeEnv-v0': (L.KIND_MERGE, 20, 50, 2),
 }
 INFO_KEYS = {L.KIND_HORIZONTAL: ('total_reward', 'total_intrusions', 'average_drift'),
              L.KIND_VERTICAL: ('total_reward', 'total_intrusions', 'final_altitude'),
-             L.KIND_SECTOR: ('total_reward', 'total_intrusions', 'average_drift')}
+             L.KIND_SECTOR: ('total_reward', 'total_intrusions', 'average_drift'),
+             L.KIND_MERGE: ('total_reward', 'total_intrusions', 'average_drift', 'faf_reach')}   # merge_env.py:238-245
 
 
-def single_spaces(kind, n_ac):
+def single_spaces(kind, n_ac, wind_obs=False):
     """The reference's Dict observation space (float64 Boxes) and action Box for one env."""
-    K = n_ac - 1
     d = {}
-    for key, a, b in obs_slices(kind, n_ac):
-        bounded = kind == L.KIND_SECTOR and key in ('cos(drift)', 'sin(drift)', 'airspeed')   # sector_cr_env.py:54-56
-        d[key] = spaces.Box(-1 if bounded else -np.inf, 1 if bounded else np.inf, shape=(b - a,), dtype=np.float64)
-    act = spaces.Box(-1, 1, shape=(2 if kind == L.KIND_SECTOR else 1,), dtype=np.float64)
+    for key, a, b in obs_slices(kind, n_ac, wind_obs):
+        bounded = (kind == L.KIND_SECTOR and key in ('cos(drift)', 'sin(drift)', 'airspeed')) or \
+                  (kind == L.KIND_MERGE and key in ('cos(drift)', 'sin(drift)'))   # sector_cr_env.py:54-56, merge_env.py:60-61
+        lo, hi = (-1, 1) if bounded else ((0, 1) if key == 'faf_reached' else (-np.inf, np.inf))
+        d[key] = spaces.Box(lo, hi, shape=(b - a,), dtype=np.float64)
+    act = spaces.Box(-1, 1, shape=(2 if kind in (L.KIND_SECTOR, L.KIND_MERGE) else 1,), dtype=np.float64)
     return spaces.Dict(d), act
 
 
@@ -40,7 +45,9 @@ class BlueSkyVecEnv:
     metadata = {"render_modes": [], "autoreset_mode": "next_step"}
 
     def __init__(self, env_id, num_envs, num_aircraft=None, device=0, precision='fp32', asas=False, mvp=False,
-                 seed=0, cd_outputs=False, max_episode_steps=None):
+                 seed=0, cd_outputs=False, max_episode_steps=None, wind=None, wind_obs=False, obs_noise=0.0):
+        """wind = (lat, lon, vnorth, veast) like WindFieldWrapper(env, lat, lon, vnorth, veast, augment_obs=wind_obs);
+        obs_noise = NoisyObservationWrapper(env, noise_level)."""
         if env_id not in ENV_SPECS:
             raise ValueError(f"unknown env id {env_id!r}; the batched core covers {sorted(ENV_SPECS)}")
         kind, n_ref, max_steps, act_dim = ENV_SPECS[env_id]
@@ -50,9 +57,14 @@ class BlueSkyVecEnv:
                             asas_on=asas or mvp, reso_on=mvp, reso_off_own=mvp,
                             max_episode_steps=max_steps if max_episode_steps is None else max_episode_steps,
                             cd_outputs=cd_outputs)
-        self.single_observation_space, self.single_action_space = single_spaces(kind, self.num_aircraft)
+        if wind is not None:
+            self.core.set_wind(*wind, augment_obs=wind_obs)
+        if obs_noise:
+            self.core.set_obs_noise(obs_noise, seed=int(seed) + 0x5EED)
+        wind_obs = self.core.wind_obs
+        self.single_observation_space, self.single_action_space = single_spaces(kind, self.num_aircraft, wind_obs)
         self.observation_space, self.action_space = self.single_observation_space, self.single_action_space
-        self._slices = obs_slices(kind, self.num_aircraft)
+        self._slices = obs_slices(kind, self.num_aircraft, wind_obs)
         self._seed = int(seed)
         self._act = torch.zeros((self.num_envs, act_dim), dtype=self.core.rdtype, device=self.core.device)
         self.closed = False
@@ -65,7 +77,10 @@ class BlueSkyVecEnv:
     def _infos(self, info):
         info = np.asarray(info, dtype=np.float64)
         keys = INFO_KEYS[self.kind]
-        return {keys[0]: info[:, 0], keys[1]: info[:, 1].astype(np.int64), keys[2]: info[:, 2]}
+        d = {keys[0]: info[:, 0], keys[1]: info[:, 1].astype(np.int64), keys[2]: info[:, 2]}
+        if len(keys) > 3:
+            d[keys[3]] = info[:, 3].astype(np.int64)
+        return d
 
     def reset(self, seed=None, options=None):
         if seed is not None:
@@ -77,7 +92,10 @@ class BlueSkyVecEnv:
         nan = np.full(E, np.nan)
         third = np.zeros(E) if self.kind == L.KIND_VERTICAL else nan       # average_drift of an empty list is nan
         keys = INFO_KEYS[self.kind]
-        return self._obs_dict(obs), {keys[0]: np.zeros(E), keys[1]: np.zeros(E, np.int64), keys[2]: third}
+        d = {keys[0]: np.zeros(E), keys[1]: np.zeros(E, np.int64), keys[2]: third}
+        if len(keys) > 3:
+            d[keys[3]] = np.zeros(E, np.int64)
+        return self._obs_dict(obs), d
 
     def step(self, actions):
         # host path of the C-ABI: pinned H2D of the actions, one launch, one D2H of every output into pinned host
@@ -120,7 +138,7 @@ class SB3VecEnvAdapter:
         obs, rew, term, trunc, info = v.step(self._actions)
         dones = term | trunc
         keys = INFO_KEYS[v.kind]
-        infos = [{keys[0]: float(info[keys[0]][i]), keys[1]: int(info[keys[1]][i]), keys[2]: float(info[keys[2]][i]),
+        infos = [{**{k: (float(info[k][i]) if info[k].dtype.kind == 'f' else int(info[k][i])) for k in keys},
                   'TimeLimit.truncated': bool(trunc[i] and not term[i])} for i in range(self.num_envs)]
         if dones.any():
             fresh = v._obs_dict(v.core.observe().cpu().numpy())            # the device already reset those envs

@@ -33,18 +33,23 @@
 extern "C" {
 #endif
 
-#define BSG_ABI_VERSION 1
+#define BSG_ABI_VERSION 2
 
 typedef enum { BSG_OK = 0, BSG_ERR_ARG = -1, BSG_ERR_CUDA = -2, BSG_ERR_NOMEM = -3, BSG_ERR_UNSUPPORTED = -4,
                BSG_ERR_NODEVICE = -5 } bsg_status;
-enum { BSG_KIND_HORIZONTAL = 0, BSG_KIND_VERTICAL = 1, BSG_KIND_SECTOR = 2, BSG_KIND_RAW = 3 };
+enum { BSG_KIND_HORIZONTAL = 0, BSG_KIND_VERTICAL = 1, BSG_KIND_SECTOR = 2, BSG_KIND_RAW = 3,
+       BSG_KIND_MERGE = 4 /* MergeEnv-v0: bluesky_gym/envs/merge_env.py (20 aircraft, intruders on an LNAV route) */ };
 enum { BSG_FP32 = 0, BSG_FP64 = 1 };
 
 /* per-aircraft state fields of the fp64 host interchange layout  ac[E][BSG_NF][N] */
 enum { BSG_F_LAT, BSG_F_LON, BSG_F_ALT, BSG_F_HDG, BSG_F_TAS, BSG_F_VS, BSG_F_CAS, BSG_F_SELSPD, BSG_F_SELALT,
        BSG_F_SELVS, BSG_F_APTRK, BSG_F_AX, BSG_F_ASAS_TRK, BSG_F_ASAS_TAS, BSG_F_ASAS_VS, BSG_F_ASAS_ALT,
-       BSG_F_ASAS_ACTIVE, BSG_F_PHASE, BSG_NF };
-/* env-level slots of ev[E][BSG_NE] */
+       BSG_F_ASAS_ACTIVE, BSG_F_PHASE,
+       BSG_F_GSN, BSG_F_GSE,   /* ground-speed vector of the last update (= tas * (cos, sin)(hdg) without wind) */
+       BSG_F_LNAV,             /* LNAV: index of the active route waypoint, -1 = off (Merge: 0 = FAF, 1 = runway) */
+       BSG_NF };
+/* env-level slots of ev[E][BSG_NE].  Merge reuses: WPT_LAT/LON = FAF, WPT_X/Y = runway lat/lon [deg],
+ * WPT_REACH = wpt_reach, FINAL_ALT = faf_reached (info['faf_reach']) */
 #define BSG_MAXV 32
 enum { BSG_EV_WPT_LAT, BSG_EV_WPT_LON, BSG_EV_WPT_REACH, BSG_EV_AC_HDG, BSG_EV_TARGET_ALT, BSG_EV_WPT_X,
        BSG_EV_WPT_Y, BSG_EV_NVERT, BSG_EV_TOTAL_REWARD, BSG_EV_TOTAL_INTR, BSG_EV_DRIFT_SUM, BSG_EV_DRIFT_CNT,
@@ -78,7 +83,8 @@ typedef struct bsg_step_out {
     void *reward;             /* real [E] */
     int32_t *terminated;      /* [E] 0/1 */
     int32_t *truncated;       /* [E] 0/1 */
-    void *info;               /* real [E][4]: total_reward, total_intrusions, average_drift|final_altitude, steps */
+    void *info;               /* real [E][4]: total_reward, total_intrusions, average_drift|final_altitude,
+                                 steps (Merge: faf_reach) */
     uint8_t *cd_inconf;       /* [E][N] row has a conflict (last CD call of the step) */
     int32_t *cd_nconf;        /* [E][N] conflict pairs in the row */
     int32_t *cd_nlos;         /* [E][N] loss-of-separation pairs in the row */
@@ -111,6 +117,20 @@ const char *bsg_last_error(const bsg_handle *h);
 int bsg_obs_dim(const bsg_handle *h);
 int bsg_act_dim(const bsg_handle *h);
 int bsg_launch_count(const bsg_handle *h, int64_t *kernels_launched);
+
+/* Wind field of the reference's WindFieldWrapper (bluesky_gym/wrappers/wind.py:26-29 -> bs.traf.wind.addpointvne):
+ * npoints wind vectors [m/s] at (lat, lon) [deg], no altitude profile.  One point = uniform wind, several = inverse
+ * distance-squared weighting; npoints = 0 switches the wind off.  The wind acts above 50 ft: ground speed = TAS + wind,
+ * the autopilot holds the commanded TRACK (wind-correction angle), HDG actions are converted to the track they give.
+ * augment_obs != 0 appends wind_u, wind_v (wind in the agent's body axes / 50, wind.py:55-64) to every observation:
+ * bsg_obs_dim() grows by 2.  Call before the first step of an episode (the wrapper adds the wind right after reset). */
+#define BSG_MAX_WIND 8
+int bsg_set_wind(bsg_handle *h, int32_t npoints, const double *lat_host, const double *lon_host,
+                 const double *vnorth_host, const double *veast_host, int32_t augment_obs);
+/* Gaussian observation noise of the reference's NoisyObservationWrapper (bluesky_gym/wrappers/uncertainty.py:19-32):
+ * every observation float gets + N(0, sigma) from a Philox4x32-10 stream keyed by (seed; env, step launch, slot).
+ * sigma = 0 switches it off. */
+int bsg_set_obs_noise(bsg_handle *h, double sigma, uint64_t seed);
 
 /* fp64 interchange with the host (parity tests, checkpoint/resume). NULL pointers are skipped. Synchronous. */
 int bsg_set_state(bsg_handle *h, const double *ac_host, const uint64_t *reso_host, const int32_t *nac_host,

@@ -16,7 +16,7 @@ def test_library_exports_every_declared_symbol():
     assert len(declared) >= 20
     assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
     lib = _lib.load()                       # binds all of them; raises on a missing symbol
-    assert lib.bsg_abi_version() == 1
+    assert lib.bsg_abi_version() == 2
     assert lib.bsg_status_string(-4).decode() == 'unsupported configuration'
 
 
@@ -27,7 +27,7 @@ def test_struct_layouts_match_header():
     assert C.sizeof(_lib.StepOut) == 14 * 8
     assert C.sizeof(_lib.CdParams) == 32 and C.sizeof(_lib.NdmapParams) == 14 * 4
     assert C.sizeof(_lib.CdPeers) == 8 + 5 * 8 * _lib.MAX_PEERS
-    assert _lib.NF == 18 and _lib.NE == 14 + 64
+    assert _lib.NF == 21 and _lib.NE == 14 + 64
 
 
 def test_no_cpu_fallback_without_device():
@@ -48,8 +48,12 @@ def test_registration_and_spaces_mirror_the_reference():
     import bluesky_gym_hallucination_b200 as pkg
     from bluesky_gym_hallucination_b200 import vec_env, core, _lib as L
     pkg.register_envs()
-    assert [r[0] for r in pkg._REGISTRATIONS] == ['HorizontalCREnv-v0', 'VerticalCREnv-v0', 'SectorCREnv-v0']
-    assert [r[2] for r in pkg._REGISTRATIONS] == [300, 300, 200]          # bluesky_gym/__init__.py:21,27,33
+    assert [r[0] for r in pkg._REGISTRATIONS] == ['HorizontalCREnv-v0', 'VerticalCREnv-v0', 'SectorCREnv-v0', 'MergeEnv-v0']
+    assert [r[2] for r in pkg._REGISTRATIONS] == [300, 300, 200, 50]      # bluesky_gym/__init__.py:21,27,33,45
+    obs, act = vec_env.single_spaces(L.KIND_MERGE, 20, wind_obs=True)     # merge_env.py:57-76 + wrappers/wind.py:21-24
+    assert list(obs.spaces) == ['cos(drift)', 'sin(drift)', 'airspeed', 'waypoint_dist', 'faf_reached', 'x_r', 'y_r',
+                                'vx_r', 'vy_r', 'cos(track)', 'sin(track)', 'distances', 'wind_u', 'wind_v']
+    assert sum(s.shape[0] for s in obs.spaces.values()) == 42 and act.shape == (2,) and obs['x_r'].shape == (5,)
     obs, act = vec_env.single_spaces(L.KIND_HORIZONTAL, 6)
     assert list(obs.spaces) == ['intruder_distance', 'cos_difference_pos', 'sin_difference_pos', 'x_difference_speed',
                                 'y_difference_speed', 'waypoint_distance', 'cos_drift', 'sin_drift']
