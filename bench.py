@@ -27,8 +27,12 @@ WORKLOADS = {
     # name: (kind, envs per GPU, aircraft, asas, reso, description)
     'c2': (0, 4096, 20, 1, 0, "HorizontalCREnv-v0 4096 envs x 20 aircraft, state-based CD + CPA obs"),
     'c3': (2, 65536, 50, 1, 1, "SectorCREnv-v0 65536 envs x 50 aircraft, CD + MVP (intruders) + reward"),
+    # SURVEY 8(f) rows, the EXT instantiations of the step kernel (not the driver's line):
+    'merge': (4, 4096, 20, 0, 0, "MergeEnv-v0 4096 envs x 20 aircraft, LNAV route following, ASAS off as in the reference"),
+    'merge_cd': (4, 4096, 20, 1, 0, "MergeEnv-v0 4096 envs x 20 aircraft, LNAV route following + state-based CD"),
+    'c3w': (2, 65536, 50, 1, 1, "SectorCREnv-v0 65536 envs x 50 aircraft, CD + MVP, 3-point wind field + wind obs + obs noise"),
 }
-SUBSTEPS = {0: 10, 1: 30, 2: 5}
+SUBSTEPS = {0: 10, 1: 30, 2: 5, 4: 10}
 
 
 def env_int(name, default):
@@ -167,8 +171,11 @@ def run_ours(args):
         E = args.envs
     K, W = args.steps, max(args.warmup, 3)
     c = bc.BsgCore(kind, E, N, precision='fp32', device=local, asas_on=bool(asas), reso_on=bool(reso),
-                   reso_off_own=True, max_episode_steps={0: 300, 1: 300, 2: 200}[kind], cd_outputs=True,
+                   reso_off_own=True, max_episode_steps={0: 300, 1: 300, 2: 200, 4: 50}[kind], cd_outputs=True,
                    fixed_nac=True)    # every aircraft slot live ("N fixed, mask all-active")
+    if args.workload == 'c3w':        # WindFieldWrapper(augment_obs=True) + NoisyObservationWrapper(0.1) on device
+        c.set_wind([51.5, 52.6, 52.0], [3.5, 4.2, 5.5], [10.0, -4.0, 6.0], [-8.0, 12.0, 3.0], augment_obs=True)
+        c.set_obs_noise(0.1, seed=5 + rank)
     c.reset(seed=1234 + rank)
     c.set_autoreset(True, seed=99 + rank)
     gen = torch.Generator(device=dev); gen.manual_seed(7 + rank)
@@ -235,6 +242,8 @@ def run_ours(args):
     nac = c.live_aircraft().astype(np.float64)                  # counted from the device state, not assumed
     pairs_per_launch = float(sub * np.sum(nac * (nac - 1)))     # ordered CD entries one launch produces
     assert nac.min() == N and nac.max() == N, (nac.min(), nac.max())
+    if not asas:
+        pairs_per_launch = 0.0
     value = world * E * K / (dev_ms_max * 1e-3)
     achieved = FLOP_PER_PAIR * pairs_per_launch / (kernel_ms * 1e-3) / 1e12
     bytes_per_envstep = 128.0 * N + 4 * c.obs_dim + 4 * c.act_dim + 20
@@ -248,7 +257,7 @@ def run_ours(args):
                    "live_aircraft_per_env": {"min": int(nac.min()), "mean": float(nac.mean()), "max": int(nac.max())}},
         "pair_evals_per_sec": world * pairs_per_launch * K / (dev_ms_max * 1e-3),
         "roofline": {"bound": "fp32", "achieved": achieved, "peak": peak32, "unit": "TFLOP/s", "frac": achieved / peak32,
-                     "traffic": ncu_traffic(args.workload), "kernel": "bsg::step_kernel<float>", "kernel_ms": kernel_ms,
+                     "traffic": ncu_traffic(args.workload), "kernel": "bsg::step_kernel<float>" + (", EXT" if kind == 4 or args.workload == 'c3w' else ""), "kernel_ms": kernel_ms,
                      "flop_per_pair": FLOP_PER_PAIR, "pairs_per_launch": pairs_per_launch,
                      "peak_source": "bsg_peak_fp32 FMA chain measured in this run (burst); MEASURED_PEAKS.json holds no FP32 figure",
                      "hbm_achieved_gbs": bytes_per_envstep * E / (kernel_ms * 1e-3) / 1e9,
@@ -258,7 +267,10 @@ def run_ours(args):
                 "api": "bsg_step_host + bsg_host_views (host actions -> pinned H2D, one launch, D2H of obs/reward/info/flags into pinned host memory read in place)"},
         "gpu_launches": int(launches), "clocks": clocks, "wall_s_timed_region": t_wall,
     }
-    if world == 1 and not args.no_cpu:
+    if not asas:     # no pair sweep in the launch (the reference's MergeEnv leaves ASAS off): state / obs traffic bounds it
+        hb, hp = line["roofline"]["hbm_achieved_gbs"], line["roofline"]["hbm_peak_gbs"] or 6552.3
+        line["roofline"].update({"bound": "hbm", "achieved": hb, "peak": hp, "unit": "GB/s", "frac": hb / hp})
+    if world == 1 and not args.no_cpu and kind != 4:
         np_b, c_b = cpu_baselines(N, asas)
         line["cpu_baseline"] = np_b
         line["cpu_baseline_c_openmp"] = c_b
