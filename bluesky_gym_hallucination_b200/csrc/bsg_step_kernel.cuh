@@ -6,7 +6,7 @@
 #include "bsg_reset.cuh"
 
 #ifndef BSG_PW
-#define BSG_PW 2          // pairs evaluated per trip of the half-ring loop
+#define BSG_PW 5          // pairs evaluated per trip of the half-ring loop (A/B on B200: 5 > 4 > 2; divides H = 10 and 25)
 #endif
 
 namespace bsg {
@@ -122,7 +122,6 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         if (reso) resorow = A.reso[k];
     }
     // ------------------------------------------------------------------ action intake (agent = aircraft 0)
-    if (SYM && valid) { crow[le * N + i] = 0ull; crow[(size_t)epb * N + le * N + i] = 0ull; }
     if (live && i == 0) {
         es[le].anyconf[0] = 0; es[le].anyconf[1] = 0; es[le].intr = 0; es[le].vneed = 0; es[le].alt_ref = a.alt;
         es[le].own_lat = a.lat; es[le].own_lon = a.lon;                    // local origin of the fp32 CD records
@@ -201,47 +200,45 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             bool touched = false, active = false;
             unsigned long long keep = 0;
             if constexpr (SYM) {
-                unsigned long long *cr_now = crow + (size_t)buf * epb * N + le * N;
-                if (valid) crow[(size_t)(buf ^ 1) * epb * N + le * N + i] = 0ull;     // my row of the next substep
+                // conflict bits without atomics and without a branch: thread i keeps the flags of ITS half ring as the
+                // relative mask F (bit d-1 <-> partner i+d) and publishes it once per substep as hr[i] (and the ring copy
+                // hr[i + nl], so that the partners behind it are read without an index wrap); phase 2 completes the row
+                // with bit k-1 of the masks of the nl-1-H partners i-k.  One buffer: barrier A of the next substep
+                // separates the readers of this substep from the next writers.
+                unsigned *hr = reinterpret_cast<unsigned *>(crow) + (size_t)le * 2 * N;
+                unsigned F = 0u;
                 const float4 *rA = reinterpret_cast<const float4 *>(rb), *rB = rA + sym_row_recs(N);
                 RecFast me;
                 if (live && !skip) {                            // phase 1: half ring, flags only
                     me = rec_from(rA[i], rB[i]);
                     const int H = nl >> 1;
                     const float4 *pA = rA + i, *pB = rB + i;    // ring copy behind slot nl: j = i + d needs no wrap
-                    unsigned *c32 = reinterpret_cast<unsigned *>(cr_now);
-                    auto mark = [&](int d) {                    // rare: native 32-bit shared atomics
-                        int j = i + d;
-                        j = j >= nl ? j - nl : j;
-                        atomicOr(&c32[2 * i + (j >> 5)], 1u << (j & 31));
-                        atomicOr(&c32[2 * j + (i >> 5)], 1u << (i & 31));
-                        if (RESO) es[le].anyconf[buf] = 1;
-                    };
-                    // BSG_PW pairs per trip, flags first and ONE rare branch behind them: the independent
-                    // dependency chains interleave (the pair body is latency-bound at 4-5 warps per scheduler)
+                    // BSG_PW pairs per trip: straight-line FP32 code, the independent dependency chains interleave
+                    // (the pair body is latency-bound at 4-5 warps per scheduler)
                     auto sweep = [&](auto vt) {
                         constexpr bool V = decltype(vt)::value;
                         int d = 1;
+                        unsigned bit = 1u;
                         for (; d + (BSG_PW - 1) <= H; d += BSG_PW) {
-                            bool sw[BSG_PW], any = false;
 #pragma unroll
                             for (int q = 0; q < BSG_PW; q++) {
                                 PairCore pc;
-                                sw[q] = pair_fast_core<V>(me, rec_from(pA[d + q], pB[d + q]), PF, true, pc);
-                                any |= sw[q];
+                                const bool sw = pair_fast_core<V>(me, rec_from(pA[d + q], pB[d + q]), PF, true, pc);
+                                F |= sw ? (bit << q) : 0u;
                             }
-                            if (any) {
-#pragma unroll
-                                for (int q = 0; q < BSG_PW; q++) if (sw[q]) mark(d + q);
-                            }
+                            bit <<= BSG_PW;
                         }
                         for (; d <= H; d++) {
                             PairCore pc;
-                            if (pair_fast_core<V>(me, rec_from(pA[d], pB[d]), PF, true, pc)) mark(d);
+                            const bool sw = pair_fast_core<V>(me, rec_from(pA[d], pB[d]), PF, true, pc);
+                            F |= sw ? bit : 0u;
+                            bit <<= 1;
                         }
                     };
                     // level, co-altitude traffic (Horizontal and Sector envs): the vertical window is (-inf, inf)
                     if (es[le].vneed) sweep(std::true_type{}); else sweep(std::false_type{});
+                    hr[i] = F; hr[i + nl] = F;
+                    if (RESO && F) es[le].anyconf[buf] = 1;
                 }
                 // phase 2 feeds MVP / resumenav every substep; the CD row outputs report the LAST detection of the
                 // step (what bs.traf.cd holds afterwards), so the row reductions run on the last substep only
@@ -249,7 +246,22 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 const bool need_rows = RESO || want_acc;
                 if (need_rows) __syncthreads();
                 if (need_rows && live && !skip) {               // phase 2: my row, conflicting / resolving pairs only
-                    const unsigned long long cr = cr_now[i];
+                    // B bit (k-1) <-> partner i-k: the pair (i-k, i) is bit k-1 of that partner's mask
+                    unsigned B = 0u;
+                    {
+                        const int kmax = nl - 1 - (nl >> 1);
+                        const unsigned *hb = hr + i + nl;
+#pragma unroll 4
+                        for (int k = 1; k <= kmax; k++) B |= hb[-k] & (1u << (k - 1));
+                    }
+                    // relative -> absolute positions.  Forward: i+d, wrapped ones (i+d >= nl) at i+d-nl.
+                    unsigned long long fwd = (i < 63 ? (unsigned long long)F << (i + 1) : 0ull) & (nl < 64 ? (1ull << nl) - 1ull : ~0ull);
+                    if (nl - 1 - i < 32) fwd |= (unsigned long long)(F >> (nl - 1 - i));
+                    // Backward: the bit-reversed word, shifted, lands on i-k (and i-k+nl for the wrapped ones)
+                    const unsigned long long rb64 = (unsigned long long)__brev(B) << 32;     // bit 64-k <-> partner i-k
+                    unsigned long long back = i > 0 ? rb64 >> (64 - i) : 0ull;               // positions i-k >= 0
+                    if (i < 32) back |= (rb64 << i) >> (64 - nl);                            // k > i: positions i-k+nl
+                    const unsigned long long cr = fwd | back;
                     unsigned long long S = RESO ? (cr | resorow) : cr;
                     S &= ~(1ull << i);
                     const float R2f = PF.rpz * PF.rpz, R2b = R2f * (float)(A.P.fach * A.P.fach);
