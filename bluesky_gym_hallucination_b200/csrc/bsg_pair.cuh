@@ -101,7 +101,9 @@ __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &
         tin = fmaxf(fminf(thi, tlo), tin); tout = fminf(fmaxf(thi, tlo), tout);
     }
     o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist2 = dist2; o.dalt = dalt;
-    return swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
+    // VERT = false: tin <= tout holds whenever swhor does (dtinhor >= 0), so the test is dropped (same flag)
+    if constexpr (!VERT) return swhor && (tout > 0.0f) && (tin < P.dtlook);
+    else return swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
 }
 
 // full form (used where every output is wanted): flag + LoS + the PairOut fields

@@ -287,14 +287,15 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                                 float d1, d2;
                                 mvp_pair_fast(dx, dy, dist2, tcpa, vrx, vry, PF.rpz_m, d1, d2);
                                 dve = dve - d1; dvn = dvn - d2;
-                                if (A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }
                             }
                             const bool past = dot > 0.0f;                     // resumenav (squared distance tests)
-                            const bool bouncing = fabsf(a.hdg - sdist[le * N + j]) < 30.0f && dist2 < R2b;
+                            bool kp = !past || dist2 < R2f;
+                            if (!kp && dist2 < R2b) kp = fabsf(a.hdg - sdist[le * N + j]) < 30.0f;   // bouncing (rare)
                             touched = true;
-                            if (!past || dist2 < R2f || bouncing) { active = true; keep |= 1ull << j; }
+                            if (kp) { active = true; keep |= 1ull << j; }
                         }
                     }
+                    if (RESO && A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }   // RESOOFF: the agent does not resolve
                 }
             } else {
             if (live && !skip) {
