@@ -173,8 +173,16 @@ int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, i
     const size_t rs = rsize(h), E = g.num_envs;
     CK(h, cudaSetDevice(g.device));
     memcpy(h->h_act, actions, h->act_bytes);
-    CK(h, cudaMemcpyAsync(h->d_act, h->h_act, h->act_bytes, cudaMemcpyHostToDevice, h->hs));
-    char *d = (char *)h->d_out;
+    // direct mode: the kernel reads the actions from / stores the outputs to the pinned host block itself (unified
+    // addressing); the stores are posted over PCIe while later waves of CTAs still compute.  It wins when the launch
+    // has many waves (C3: +5 %) and loses on a one-wave launch (C2: -10 %, the stores all land at the end), so the
+    // default follows the grid size; BSG_HOST_DIRECT=0/1 overrides.
+    static const char *dir_env = getenv("BSG_HOST_DIRECT");
+    const int n_cta = (int)((E + h->epb - 1) / h->epb);
+    const bool direct = dir_env ? atoi(dir_env) != 0 : n_cta >= 4096;
+    const bool dir = direct && !(h->noise_sigma > 0);          // the noise epilogue reads the observation back
+    if (!dir) CK(h, cudaMemcpyAsync(h->d_act, h->h_act, h->act_bytes, cudaMemcpyHostToDevice, h->hs));
+    char *d = (char *)(dir ? h->h_out : h->d_out);
     bsg_step_out o;
     memset(&o, 0, sizeof(o));
     o.obs = d; d += E * h->obs_dim * rs;
@@ -182,10 +190,11 @@ int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, i
     o.info = d; d += E * 4 * rs;
     o.terminated = (int32_t *)d; d += E * sizeof(int32_t);
     o.truncated = (int32_t *)d;
-    int rc = g.precision == BSG_FP64 ? launch_step<double>(h, h->d_act, &o, g.substeps, 0, h->hs)
-                                     : launch_step<float>(h, h->d_act, &o, g.substeps, 0, h->hs);
+    const void *act = dir ? h->h_act : h->d_act;
+    int rc = g.precision == BSG_FP64 ? launch_step<double>(h, act, &o, g.substeps, 0, h->hs)
+                                     : launch_step<float>(h, act, &o, g.substeps, 0, h->hs);
     if (rc != BSG_OK) return rc;
-    CK(h, cudaMemcpyAsync(h->h_out, h->d_out, h->out_bytes, cudaMemcpyDeviceToHost, h->hs));
+    if (!dir) CK(h, cudaMemcpyAsync(h->h_out, h->d_out, h->out_bytes, cudaMemcpyDeviceToHost, h->hs));
     CK(h, cudaStreamSynchronize(h->hs));
     const char *s = (const char *)h->h_out;
     if (obs) memcpy(obs, s, E * h->obs_dim * rs);

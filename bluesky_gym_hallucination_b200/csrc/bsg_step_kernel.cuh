@@ -262,37 +262,53 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     unsigned long long back = i > 0 ? rb64 >> (64 - i) : 0ull;               // positions i-k >= 0
                     if (i < 32) back |= (rb64 << i) >> (64 - nl);                            // k > i: positions i-k+nl
                     const unsigned long long cr = fwd | back;
-                    unsigned long long S = RESO ? (cr | resorow) : cr;
-                    S &= ~(1ull << i);
+                    const unsigned long long notme = ~(1ull << i);
                     const float R2f = PF.rpz * PF.rpz, R2b = R2f * (float)(A.P.fach * A.P.fach);
+                    // resumenav test of one resolving pair (squared distances; the same expressions as pair_fast_core)
+                    auto resume = [&](int j, float dx, float dy, float dist2, float dot) {
+                        const bool past = dot > 0.0f;
+                        bool kp = !past || dist2 < R2f;
+                        if (!kp && dist2 < R2b) kp = fabsf(a.hdg - sdist[le * N + j]) < 30.0f;   // bouncing (rare)
+                        touched = true;
+                        if (kp) { active = true; keep |= 1ull << j; }
+                    };
+                    // two walks instead of one with a divergent `if (sw)`: conflicting pairs first (row reductions, MVP,
+                    // resumenav), then the pairs that are only still resolving (resumenav alone).  Ascending j in
+                    // both, so the MVP sum keeps its order.
+                    unsigned long long S = cr & notme;
                     while (S) {
                         const int j = __ffsll((long long)S) - 1;
                         S &= S - 1;
                         const RecFast o = rec_from(rA[j], rB[j]);
-                        const bool sw = (cr >> j) & 1ull;
-                        if (sw && want_acc) {
+                        if (want_acc) {
                             PairCore pc;
                             pair_fast_core(me, o, PF, true, pc);
                             acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
                         }
                         if constexpr (RESO) {
-                            // the same expressions as pair_fast_core (bit-identical dx, dy, dist2, tcpa)
                             const float dy = o.y - me.y;
                             const float dx = (o.x - me.x) * fmaf(me.ca, o.ca, -(me.sa * o.sa));
                             const float dist2 = fmaf(dx, dx, dy * dy);
                             const float vrx = o.u - me.u, vry = o.v - me.v;
                             const float dot = fmaf(vrx, dx, vry * dy);
-                            if (sw) {
-                                const float tcpa = -dot * rcp_approx(fmaf(vrx, vrx, fmaf(vry, vry, 1e-6f)));
-                                float d1, d2;
-                                mvp_pair_fast(dx, dy, dist2, tcpa, vrx, vry, PF.rpz_m, d1, d2);
-                                dve = dve - d1; dvn = dvn - d2;
-                            }
-                            const bool past = dot > 0.0f;                     // resumenav (squared distance tests)
-                            bool kp = !past || dist2 < R2f;
-                            if (!kp && dist2 < R2b) kp = fabsf(a.hdg - sdist[le * N + j]) < 30.0f;   // bouncing (rare)
-                            touched = true;
-                            if (kp) { active = true; keep |= 1ull << j; }
+                            const float tcpa = -dot * rcp_approx(fmaf(vrx, vrx, fmaf(vry, vry, 1e-6f)));
+                            float d1, d2;
+                            mvp_pair_fast(dx, dy, dist2, tcpa, vrx, vry, PF.rpz_m, d1, d2);
+                            dve = dve - d1; dvn = dvn - d2;
+                            resume(j, dx, dy, dist2, dot);
+                        }
+                    }
+                    if constexpr (RESO) {
+                        S = resorow & ~cr & notme;
+                        while (S) {
+                            const int j = __ffsll((long long)S) - 1;
+                            S &= S - 1;
+                            const RecFast o = rec_from(rA[j], rB[j]);
+                            const float dy = o.y - me.y;
+                            const float dx = (o.x - me.x) * fmaf(me.ca, o.ca, -(me.sa * o.sa));
+                            const float dist2 = fmaf(dx, dx, dy * dy);
+                            const float vrx = o.u - me.u, vry = o.v - me.v;
+                            resume(j, dx, dy, dist2, fmaf(vrx, dx, vry * dy));
                         }
                     }
                     if (RESO && A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }   // RESOOFF: the agent does not resolve
