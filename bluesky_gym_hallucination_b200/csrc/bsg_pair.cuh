@@ -106,6 +106,37 @@ __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &
     else return swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
 }
 
+// Flag-only form for the half-ring sweep of the fused step kernel: returns a float whose SIGN BIT is the conflict flag,
+// so the caller shifts it into its mask with one funnel shift (no FSETP chain, no select: the comparison pipe is the
+// scarce one).  The three (four) strict inequalities of pair_fast_core are folded into one 3-input max of the negated
+// margins: conflict <=> max(dcpa2 - R2, -tout, tin - dtlook [, tin - tout]) < 0.  Same arithmetic as pair_fast_core for
+// every margin; NaN margins (dcpa2 >= R2 -> sqrt of a negative) are dropped by the max and the first margin decides, an
+// all-NaN pair (NaN state) gives the canonical NaN = sign clear = no conflict, as the comparisons would.  The only
+// deviation is an exact tie tout == +0 (or tin == tout with VERT), inside any epsilon of the thresholds.
+__device__ __forceinline__ float fmax3_f(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+template <bool VERT = true>
+__device__ __forceinline__ float pair_fast_sign(const RecFast &a, const RecFast &b, const CdParamsF &P) {
+    const float dy = b.y - a.y;
+    const float cav = fmaf(a.ca, b.ca, -(a.sa * b.sa));
+    const float dx = (b.x - a.x) * cav;
+    const float dist2 = fmaf(dx, dx, dy * dy);
+    const float du = b.u - a.u, dv = b.v - a.v;
+    const float dv2 = fmaf(du, du, fmaf(dv, dv, 1e-6f));
+    const float idv2 = rcp_approx(dv2);
+    const float ndot = -fmaf(du, dx, dv * dy);
+    const float cr = fmaf(dx, dv, -(dy * du));
+    const float dcpa2 = fmaf(cr, cr, dist2 * 1e-6f) * idv2;
+    const float dtinhor = sqrt_approx((P.R2 - dcpa2) * idv2);
+    float tin = fmaf(ndot, idv2, -dtinhor), tout = fmaf(ndot, idv2, dtinhor);
+    if constexpr (VERT) {
+        const float dalt = b.alt - a.alt;
+        const float n = -rcp_approx(b.vs - a.vs);
+        const float thi = (dalt + P.hpz) * n, tlo = (dalt - P.hpz) * n;
+        tin = fmaxf(fminf(thi, tlo), tin); tout = fminf(fmaxf(thi, tlo), tout);
+        return fmaxf(fmax3_f(dcpa2 - P.R2, -tout, tin - P.dtlook), tin - tout);
+    } else return fmax3_f(dcpa2 - P.R2, -tout, tin - P.dtlook);
+}
+
 // full form (used where every output is wanted): flag + LoS + the PairOut fields
 __device__ __forceinline__ void pair_fast(const RecFast &a, const RecFast &b, const CdParamsF &P, PairOut<float> &o) {
     PairCore c;

@@ -217,23 +217,18 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     // (the pair body is latency-bound at 4-5 warps per scheduler)
                     auto sweep = [&](auto vt) {
                         constexpr bool V = decltype(vt)::value;
+                        // the sign bit of pair_fast_sign is the flag: one funnel shift per pair pushes it into G
+                        // (pair d ends at bit H-d); reversed into F (bit d-1) after the loop
                         int d = 1;
-                        unsigned bit = 1u;
+                        unsigned G = 0u;
                         for (; d + (BSG_PW - 1) <= H; d += BSG_PW) {
 #pragma unroll
-                            for (int q = 0; q < BSG_PW; q++) {
-                                PairCore pc;
-                                const bool sw = pair_fast_core<V>(me, rec_from(pA[d + q], pB[d + q]), PF, true, pc);
-                                F |= sw ? (bit << q) : 0u;
-                            }
-                            bit <<= BSG_PW;
+                            for (int q = 0; q < BSG_PW; q++)
+                                G = __funnelshift_l(__float_as_uint(pair_fast_sign<V>(me, rec_from(pA[d + q], pB[d + q]), PF)), G, 1);
                         }
-                        for (; d <= H; d++) {
-                            PairCore pc;
-                            const bool sw = pair_fast_core<V>(me, rec_from(pA[d], pB[d]), PF, true, pc);
-                            F |= sw ? bit : 0u;
-                            bit <<= 1;
-                        }
+                        for (; d <= H; d++)
+                            G = __funnelshift_l(__float_as_uint(pair_fast_sign<V>(me, rec_from(pA[d], pB[d]), PF)), G, 1);
+                        F = H > 0 ? __brev(G) >> (32 - H) : 0u;
                     };
                     // level, co-altitude traffic (Horizontal and Sector envs): the vertical window is (-inf, inf)
                     if (es[le].vneed) sweep(std::true_type{}); else sweep(std::false_type{});
@@ -265,12 +260,12 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     const unsigned long long notme = ~(1ull << i);
                     const float R2f = PF.rpz * PF.rpz, R2b = R2f * (float)(A.P.fach * A.P.fach);
                     // resumenav test of one resolving pair (squared distances; the same expressions as pair_fast_core)
-                    auto resume = [&](int j, float dx, float dy, float dist2, float dot) {
+                    auto resume = [&](int j, unsigned long long jb, float dx, float dy, float dist2, float dot) {
                         const bool past = dot > 0.0f;
                         bool kp = !past || dist2 < R2f;
                         if (!kp && dist2 < R2b) kp = fabsf(a.hdg - sdist[le * N + j]) < 30.0f;   // bouncing (rare)
                         touched = true;
-                        if (kp) { active = true; keep |= 1ull << j; }
+                        if (kp) { active = true; keep |= jb; }
                     };
                     // two walks instead of one with a divergent `if (sw)`: conflicting pairs first (row reductions, MVP,
                     // resumenav), then the pairs that are only still resolving (resumenav alone).  Ascending j in
@@ -278,7 +273,8 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     unsigned long long S = cr & notme;
                     while (S) {
                         const int j = __ffsll((long long)S) - 1;
-                        S &= S - 1;
+                        const unsigned long long jb = S & (0ull - S);        // lowest set bit (no 64-bit shift by j)
+                        S ^= jb;
                         const RecFast o = rec_from(rA[j], rB[j]);
                         if (want_acc) {
                             PairCore pc;
@@ -295,20 +291,21 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                             float d1, d2;
                             mvp_pair_fast(dx, dy, dist2, tcpa, vrx, vry, PF.rpz_m, d1, d2);
                             dve = dve - d1; dvn = dvn - d2;
-                            resume(j, dx, dy, dist2, dot);
+                            resume(j, jb, dx, dy, dist2, dot);
                         }
                     }
                     if constexpr (RESO) {
                         S = resorow & ~cr & notme;
                         while (S) {
                             const int j = __ffsll((long long)S) - 1;
-                            S &= S - 1;
+                            const unsigned long long jb = S & (0ull - S);
+                            S ^= jb;
                             const RecFast o = rec_from(rA[j], rB[j]);
                             const float dy = o.y - me.y;
                             const float dx = (o.x - me.x) * fmaf(me.ca, o.ca, -(me.sa * o.sa));
                             const float dist2 = fmaf(dx, dx, dy * dy);
                             const float vrx = o.u - me.u, vry = o.v - me.v;
-                            resume(j, dx, dy, dist2, fmaf(vrx, dx, vry * dy));
+                            resume(j, jb, dx, dy, dist2, fmaf(vrx, dx, vry * dy));
                         }
                     }
                     if (RESO && A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }   // RESOOFF: the agent does not resolve
