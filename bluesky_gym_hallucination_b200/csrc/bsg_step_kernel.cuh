@@ -242,12 +242,21 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 if (need_rows) __syncthreads();
                 if (need_rows && live && !skip) {               // phase 2: my row, conflicting / resolving pairs only
                     // B bit (k-1) <-> partner i-k: the pair (i-k, i) is bit k-1 of that partner's mask
+                    // Groups of 8 partners, fully unrolled (LDS with an immediate offset + one LOP3 with an immediate mask
+                    // per partner); a group may read up to 7 words past partner kmax -- other rows' masks, at worst the
+                    // 31 words below this array, all inside the CTA's shared memory -- and the final mask drops them.
                     unsigned B = 0u;
                     {
-                        const int kmax = nl - 1 - (nl >> 1);
+                        const int kmax = nl - 1 - (nl >> 1);                 // <= 31
                         const unsigned *hb = hr + i + nl;
-#pragma unroll 4
-                        for (int k = 1; k <= kmax; k++) B |= hb[-k] & (1u << (k - 1));
+#pragma unroll
+                        for (int g8 = 0; g8 < 32; g8 += 8) {
+                            if (g8 < kmax) {
+#pragma unroll
+                                for (int q = 1; q <= 8; q++) B |= hb[-(g8 + q)] & (1u << (g8 + q - 1));
+                            }
+                        }
+                        B &= (1u << kmax) - 1u;
                     }
                     // relative -> absolute positions.  Forward: i+d, wrapped ones (i+d >= nl) at i+d-nl.
                     unsigned long long fwd = (i < 63 ? (unsigned long long)F << (i + 1) : 0ull) & (nl < 64 ? (1ull << nl) - 1ull : ~0ull);
