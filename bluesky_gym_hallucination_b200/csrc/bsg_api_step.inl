@@ -177,7 +177,7 @@ int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, i
     // addressing); the stores are posted over PCIe while later waves of CTAs still compute.  It wins when the launch
     // has many waves (C3: +5 %) and loses on a one-wave launch (C2: -10 %, the stores all land at the end), so the
     // default follows the grid size; BSG_HOST_DIRECT=0/1 overrides.
-    static const char *dir_env = getenv("BSG_HOST_DIRECT");
+    const char *dir_env = getenv("BSG_HOST_DIRECT");          // read per call (tests flip it)
     const int n_cta = (int)((E + h->epb - 1) / h->epb);
     const bool direct = dir_env ? atoi(dir_env) != 0 : n_cta >= 4096;
     const bool dir = direct && !(h->noise_sigma > 0);          // the noise epilogue reads the observation back

@@ -212,3 +212,27 @@ def test_step_host_equals_step():
     assert np.array_equal(v_term, ref[2]) and np.array_equal(v_info, info, equal_nan=True)
     assert c.launch_count() > 0
     c.close()
+
+
+def test_step_host_direct_mode_equals_copy_mode(monkeypatch):
+    """bsg_step_host in direct mode (the kernel reads the actions from / stores the results to the pinned host block,
+    default for many-wave launches) returns the same bits as the copy mode, over several steps."""
+    from bluesky_gym_hallucination_b200 import scenario as sc
+    E, N = 512, 50
+    ac, reso, nac, ev = sc.sector(E, N, seed=9)
+    kind = 2
+    rng = np.random.default_rng(3)
+    acts = [rng.uniform(-1, 1, (E, 2)).astype(np.float32) for _ in range(6)]
+    outs = {}
+    for mode in ('0', '1'):
+        monkeypatch.setenv('BSG_HOST_DIRECT', mode)
+        c = make_core(kind, E, N, 'fp32', 1)
+        c.set_state(ac, reso, nac, ev)
+        res = []
+        for a in acts:
+            res.append([np.array(v, copy=True) for v in c.step_host_views(a)])
+        outs[mode] = res
+        c.close()
+    for r0, r1 in zip(outs['0'], outs['1']):
+        for v0, v1 in zip(r0, r1):
+            assert np.array_equal(v0, v1, equal_nan=True)
