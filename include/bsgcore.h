@@ -154,6 +154,10 @@ int bsg_step(bsg_handle *h, const void *actions_dev /* real [E][act_dim] */, con
  * that passes NULL output pointers to bsg_step_host reads the results here without another host copy.  Valid
  * until the next bsg_step_host / bsg_destroy on this handle. */
 int bsg_host_views(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated);
+/* bsg_step_host moves the data in one of two ways, same results bit for bit: copy mode (actions H2D, one launch, one
+ * D2H of the output block) or direct mode (the kernel reads the actions from and stores the outputs to the pinned
+ * block over PCIe itself; default when the launch has >= 4096 CTAs, never with observation noise on).  The
+ * environment variable BSG_HOST_DIRECT=0/1 forces one of them. */
 int bsg_step_host(bsg_handle *h, const void *actions_host, void *obs_host, void *reward_host,
                   int32_t *terminated_host, int32_t *truncated_host, void *info_host);
 
