@@ -175,11 +175,13 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     }
 
     RowAcc<R> acc;
+    // record rows of this env in the two substep buffers (hoisted: 64-bit address arithmetic out of the loop)
+    unsigned char *const rb_even = recs + (size_t)le * rowb, *const rb_odd = rb_even + (size_t)epb * rowb;
     // ------------------------------------------------------------------ K substeps
     for (int s = 0; s < A.substeps; s++) {
         const int buf = s & 1;
         if (A.asas_on) {
-            Rec *rb = reinterpret_cast<Rec *>(recs + ((size_t)buf * epb + le) * rowb);
+            Rec *rb = reinterpret_cast<Rec *>(buf ? rb_odd : rb_even);
             if (live && !skip) {
                 if constexpr (SYM) {                  // SoA halves (conflict-free LDS.128) + ring copy behind slot nl
                     RecFast r;
