@@ -236,3 +236,44 @@ def test_step_host_direct_mode_equals_copy_mode(monkeypatch):
     for r0, r1 in zip(outs['0'], outs['1']):
         for v0, v1 in zip(r0, r1):
             assert np.array_equal(v0, v1, equal_nan=True)
+
+
+@pytest.mark.parametrize('kind,E,N,act_dim', [(0, 4096, 20, 1), (2, 65536, 50, 2)])
+def test_full_size_batch_equals_single_envs(kind, E, N, act_dim):
+    """BASELINE.json sizes (C2: Horizontal 4096 x 20; C3: Sector 65 536 x 50, CD + MVP): a size-independent property.
+    The batch is drawn by the device reset, stepped 3 times, and envs picked across the batch (first / last CTA, warp
+    and CTA boundaries) must come out bit-identical from a one-env core fed the same state and actions: observation,
+    reward, flags, per-aircraft conflict rows and the full state (incl. resopairs)."""
+    big = make_core(kind, E, N, 'fp32', 1, fixed_nac=True)
+    big.reset(seed=77)
+    torch.cuda.synchronize()
+    ac, reso, nac, ev = big.get_state()
+    big.set_state(ac, reso, nac, ev)          # both sides start from the imported state (memo slots cleared alike)
+    rng = np.random.default_rng(5)
+    picks = [0, 1, 5, 6, 7, E // 2 - 1, E // 2, E - 2, E - 1] + list(rng.integers(0, E, 6))
+    ones = {}
+    for e in picks:
+        one = make_core(kind, 1, N, 'fp32', 1, fixed_nac=True)
+        one.set_state(ac[e:e + 1], reso[e:e + 1], nac[e:e + 1], ev[e:e + 1])
+        ones[e] = one
+    for step in range(3):
+        act = rng.uniform(-1, 1, (E, act_dim)).astype(np.float32)
+        big.step(torch.as_tensor(act, device=big.device))
+        torch.cuda.synchronize()
+        b_obs, b_rew = big.obs.cpu().numpy(), big.reward.cpu().numpy()
+        b_term, b_trunc = big.terminated.cpu().numpy(), big.truncated.cpu().numpy()
+        b_cd = {k: v.cpu().numpy() for k, v in big.cd.items()}
+        for e, one in ones.items():
+            one.step(torch.as_tensor(act[e:e + 1], device=one.device))
+            torch.cuda.synchronize()
+            assert np.array_equal(one.obs.cpu().numpy()[0], b_obs[e], equal_nan=True), (step, e)
+            assert np.array_equal(one.reward.cpu().numpy()[0], b_rew[e], equal_nan=True)
+            assert one.terminated.cpu().numpy()[0] == b_term[e] and one.truncated.cpu().numpy()[0] == b_trunc[e]
+            for k, v in one.cd.items():
+                assert np.array_equal(v.cpu().numpy()[0], b_cd[k][e], equal_nan=True), (step, e, k)
+    ac1, reso1, nac1, ev1 = big.get_state()
+    for e, one in ones.items():
+        a1, r1, n1, _ = one.get_state()
+        assert np.array_equal(a1[0], ac1[e], equal_nan=True) and np.array_equal(r1[0], reso1[e]) and n1[0] == nac1[e]
+        one.close()
+    big.close()
