@@ -210,3 +210,61 @@ def test_cd_sweep_equal_velocity_pairs(orc):
     torch.cuda.synchronize()
     mism = (out['nconf'].cpu().numpy() != ref['nconf']).sum()
     assert mism <= 4, mism
+
+
+def test_giant_airspace_full_size_properties():
+    """BASELINE.json C5 size (16 envs x 10 000 aircraft, 1000 x 1000 NM): symmetric sweep == ordered sweep bitwise,
+    row-block halves == full, and the properties of a symmetric conflict matrix: sum of the conflict counts is even
+    per env, an aircraft is in conflict iff its count is positive, the nearest intruder of a conflicting aircraft is
+    itself in conflict, LoS counts never exceed conflict counts."""
+    from bluesky_gym_hallucination_b200 import core, scenario as sc
+    E, N = 16, 10000
+    lat, lon, alt, trk, gs, vs = sc.raw_traffic(E, N, seed=3, box_nm=1000.0)
+    rec = _pack(lat, lon, alt, trk, gs, vs)
+    full = core.cd_sweep(rec)
+    sym = core.cd_sweep_sym(rec)
+    parts = core.cd_sweep(rec, 0, N // 2)
+    parts = core.cd_sweep(rec, N // 2, N, out=parts)
+    torch.cuda.synchronize()
+    for k in ('inconf', 'nconf', 'nlos', 'near_idx', 'near_tcpa', 'near_dcpa', 'near_tin', 'tcpamax'):
+        assert torch.equal(full[k], sym[k]), k
+        assert torch.equal(full[k], parts[k]), k
+    nconf, nlos, inconf, near = (full[k].cpu().numpy() for k in ('nconf', 'nlos', 'inconf', 'near_idx'))
+    assert nconf.sum() > 1000
+    assert (nconf.sum(1) % 2 == 0).all() and (nlos.sum(1) % 2 == 0).all()
+    assert np.array_equal(inconf != 0, nconf > 0)
+    assert (nlos <= nconf).all()
+    e_idx, i_idx = np.nonzero(nconf > 0)
+    j_idx = near[e_idx, i_idx]
+    assert (j_idx >= 0).all() and (j_idx != i_idx).all() and (nconf[e_idx, j_idx] > 0).all()
+    assert (near[nconf == 0] == -1).all()
+
+
+def test_ndmap_full_size_properties(orc):
+    """BASELINE.json C4 size (1024 envs x 500 aircraft x 30 look-ahead steps, 64 x 64 x 8 grid): envs across the batch are
+    bit-exact against the CPU restatement; for the whole batch ncell == number of conflict cells, every slab holds at
+    most n aircraft, and a conflict cell has an occupied cell in its 3x3x3 neighbourhood."""
+    from bluesky_gym_hallucination_b200 import core
+    E, n = 1024, 500
+    rng = np.random.default_rng(12)
+    rec = np.zeros((E, 6, n), np.float32)
+    rec[:, 0] = rng.uniform(0, 370400, (E, n)); rec[:, 1] = rng.uniform(0, 370400, (E, n))     # 200 x 200 NM box
+    rec[:, 2] = rng.uniform(3048, 12192, (E, n))
+    hdg = rng.uniform(0, 2 * np.pi, (E, n)); spd = rng.uniform(120, 250, (E, n))
+    rec[:, 3] = spd * np.sin(hdg); rec[:, 4] = spd * np.cos(hdg)
+    rec[:, 5] = rng.choice([-10.0, 0.0, 0.0, 10.0], (E, n))
+    kw = dict(nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=3048.0, cx=370400.0 / 64, cy=370400.0 / 64, cz=304.8 * 4, dt=10.0)
+    g_occ, g_conf, g_ncell = core.ndmap(torch.as_tensor(rec, device='cuda'), **kw)
+    torch.cuda.synchronize()
+    pick = [0, 1, 511, 1022, 1023]
+    occ, conf, ncell = orc.ndmap(np.ascontiguousarray(rec[pick]), nthreads=8, **kw)
+    assert occ.sum() > 0 and conf.sum() > 0
+    assert np.array_equal(g_occ[pick].cpu().numpy(), occ)
+    assert np.array_equal(g_conf[pick].cpu().numpy(), conf)
+    assert np.array_equal(g_ncell[pick].cpu().numpy(), ncell)
+    assert torch.equal(g_conf.view(E, 30, -1).sum(-1, dtype=torch.int32), g_ncell)
+    assert int(g_occ.view(E, 30, -1).sum(-1, dtype=torch.int32).max()) <= n
+    for e0 in range(0, E, 128):                       # dilation property, 128 envs at a time (memory)
+        o = (g_occ[e0:e0 + 128] > 0).float().view(-1, 1, 8, 64, 64)
+        nb = torch.nn.functional.max_pool3d(o, 3, stride=1, padding=1).view(128, 30, 8, 64, 64) > 0
+        assert bool((nb | (g_conf[e0:e0 + 128] == 0)).all())
