@@ -82,8 +82,10 @@ static __device__ __noinline__ void fused_reset(int kind, int fixed_nac, int E, 
 // RESO (MVP + resumenav) is a compile-time switch: without it the pair loop is a clean, unrollable FP32 body.
 // SYM (fp32, N <= 64): every unordered pair is evaluated ONCE -- thread i sweeps the half ring j = i+1 .. i+N/2
 // (the fp32 pair form is exactly symmetric under i <-> j, so the ordered matrix it stands for is bit-identical
-// to the full sweep); a conflict sets bit j of row i and bit i of row j with shared-memory atomics, and after
-// one more barrier each thread finishes its own row (row reductions, MVP, resumenav) from its conflict bit row.
+// to the full sweep).  The flag of pair (i, i+d) is the sign bit of one 3-input max, funnel-shifted into a register
+// mask that the thread publishes once per substep (no atomics, no branch); after one more barrier each thread
+// completes its own row from the masks of the partners behind it and finishes it in two walks: conflicting pairs
+// (row reductions, MVP, resumenav), then pairs that are only still resolving (resumenav).
 // EXT: the wrapper / Merge features (wind field, LNAV route, Merge env layer, observation noise; SURVEY f-3, f-4) as a
 // compile-time switch, so the instantiations the headline configs run are unchanged by them.
 template <typename R, int TPB, bool RESO, bool SYM, bool EXT = false>
