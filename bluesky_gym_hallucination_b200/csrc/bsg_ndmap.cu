@@ -16,7 +16,7 @@ constexpr int kNdThreads = 512;
 // POW2: nx / 8, ny and nx * ny are powers of two (the C4 grid 64 x 64 x 8): the index arithmetic of the two box-sum passes
 // is shifts and masks instead of three runtime integer divisions per item (they were ~40 % of the instructions).
 template <bool POW2>
-__global__ void __launch_bounds__(kNdThreads) ndmap_kernel(const bsg_ndmap_params p, float icx, float icy, float icz,
+__global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_params p, float icx, float icy, float icz,
                                                            int lgx, int lplane,
                                                            const float *__restrict__ rec, uint8_t *__restrict__ occ,
                                                            uint8_t *__restrict__ conf, int32_t *__restrict__ ncell) {
@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(kNdThreads) ndmap_kernel(const bsg_ndmap_param
     const int nx = p.nx, ny = p.ny, nz = p.nz, n = p.num_ac;
     const int cells = nx * ny * nz;
     uint16_t *cnt = reinterpret_cast<uint16_t *>(smem);          // [cells]
-    uint16_t *sxy = cnt + cells;                                 // [cells]
+    uint8_t *sxy8 = smem + (size_t)cells * 2;                    // [cells] u8: (y, x) box sums of counts clipped to 2
     __shared__ int s_ncf;
     const int k = blockIdx.x, e = blockIdx.y;
     uint32_t *cw = reinterpret_cast<uint32_t *>(cnt);
@@ -45,10 +45,11 @@ __global__ void __launch_bounds__(kNdThreads) ndmap_kernel(const bsg_ndmap_param
         atomicAdd(&cw[c >> 1], (c & 1) ? 0x10000u : 1u);         // u16 lanes: no carry for n <= 65535
     }
     __syncthreads();
-    // pass 1: 3x3 box sum in the (y, x) plane, 8 cells (one 16-byte vector of packed u16 pairs) per item.
-    // Packed u16 lanes add as plain u32 (counts <= 65535 / 27); the +-1 neighbours in x come from funnel shifts.
+    // pass 1: 3x3 box sum in the (y, x) plane, 8 cells (one 16-byte vector of packed u16 pairs) per item.  The counts are
+    // clipped to 2 first (sum >= 2 <=> clipped sum >= 2), so a 27-cell sum is at most 54 and the plane sums are kept as
+    // BYTES: the grid costs 3 B per cell of shared memory instead of 4 and two CTAs share an SM -- the HBM stores of one
+    // slab overlap the counting / summing of another.  The +-1 neighbours in x come from funnel shifts.
     const int gx = nx >> 3;                                   // 16-byte groups per row
-    uint32_t *sw = reinterpret_cast<uint32_t *>(sxy);
     for (int g = threadIdx.x; g < cells / 8; g += kNdThreads) {
         const int x8 = POW2 ? (g & (gx - 1)) : g % gx, yz = POW2 ? (g >> lgx) : g / gx, y = POW2 ? (yz & (ny - 1)) : yz % ny;
         uint32_t rs[6] = { 0u, 0u, 0u, 0u, 0u, 0u };
@@ -58,42 +59,36 @@ __global__ void __launch_bounds__(kNdThreads) ndmap_kernel(const bsg_ndmap_param
             if (yy < 0 || yy >= ny) continue;
             const int wb = ((yz + dy) * nx + x8 * 8) >> 1;    // first word of the group in row yy
             const uint4 m = *reinterpret_cast<const uint4 *>(cw + wb);
-            rs[0] += x8 > 0 ? cw[wb - 1] : 0u;
-            rs[1] += m.x; rs[2] += m.y; rs[3] += m.z; rs[4] += m.w;
-            rs[5] += x8 < gx - 1 ? cw[wb + 4] : 0u;
+            rs[0] += x8 > 0 ? __vminu2(cw[wb - 1], 0x00020002u) : 0u;
+            rs[1] += __vminu2(m.x, 0x00020002u); rs[2] += __vminu2(m.y, 0x00020002u);
+            rs[3] += __vminu2(m.z, 0x00020002u); rs[4] += __vminu2(m.w, 0x00020002u);
+            rs[5] += x8 < gx - 1 ? __vminu2(cw[wb + 4], 0x00020002u) : 0u;
         }
         uint4 o;
         o.x = rs[1] + __funnelshift_l(rs[0], rs[1], 16) + __funnelshift_r(rs[1], rs[2], 16);
         o.y = rs[2] + __funnelshift_l(rs[1], rs[2], 16) + __funnelshift_r(rs[2], rs[3], 16);
         o.z = rs[3] + __funnelshift_l(rs[2], rs[3], 16) + __funnelshift_r(rs[3], rs[4], 16);
         o.w = rs[4] + __funnelshift_l(rs[3], rs[4], 16) + __funnelshift_r(rs[4], rs[5], 16);
-        *reinterpret_cast<uint4 *>(sw + (g << 2)) = o;
+        *reinterpret_cast<uint2 *>(sxy8 + ((size_t)g << 3)) = make_uint2(__byte_perm(o.x, o.y, 0x6420), __byte_perm(o.z, o.w, 0x6420));
     }
     __syncthreads();
-    // pass 2: sum over z, emit 16 cells per item as one 16-byte store each for occ and conf
+    // pass 2: sum over z (byte lanes, <= 54), emit 16 cells per item as one 16-byte store each for occ and conf
     const size_t slab = ((size_t)e * p.nt + k) * cells;
-    const int plane_w = (nx * ny) >> 1;                       // words per z plane
+    const int plane = nx * ny;                                // bytes per z plane of sxy8
     int ncf = 0;
-    const bool small_n = n <= 32768;
     for (int g = threadIdx.x; g < cells / 16; g += kNdThreads) {
-        const int w0 = g << 3, z = POW2 ? ((g << 4) >> lplane) : (g << 4) / (nx * ny);
-        uint32_t sv[8], cv[8];
-#pragma unroll
-        for (int h = 0; h < 2; h++) {
-            uint4 a = *reinterpret_cast<const uint4 *>(sw + w0 + 4 * h);
-            if (z > 0) { const uint4 q = *reinterpret_cast<const uint4 *>(sw + w0 + 4 * h - plane_w); a.x += q.x; a.y += q.y; a.z += q.z; a.w += q.w; }
-            if (z < nz - 1) { const uint4 q = *reinterpret_cast<const uint4 *>(sw + w0 + 4 * h + plane_w); a.x += q.x; a.y += q.y; a.z += q.z; a.w += q.w; }
-            sv[4 * h] = a.x; sv[4 * h + 1] = a.y; sv[4 * h + 2] = a.z; sv[4 * h + 3] = a.w;
-            const uint4 c = *reinterpret_cast<const uint4 *>(cw + w0 + 4 * h);
-            cv[4 * h] = c.x; cv[4 * h + 1] = c.y; cv[4 * h + 2] = c.z; cv[4 * h + 3] = c.w;
-        }
-        uint32_t ow[4], fw[4];
+        const int w0 = g << 3, b0 = g << 4, z = POW2 ? (b0 >> lplane) : b0 / plane;
+        uint4 a = *reinterpret_cast<const uint4 *>(sxy8 + b0);
+        if (z > 0) { const uint4 q = *reinterpret_cast<const uint4 *>(sxy8 + b0 - plane); a.x += q.x; a.y += q.y; a.z += q.z; a.w += q.w; }
+        if (z < nz - 1) { const uint4 q = *reinterpret_cast<const uint4 *>(sxy8 + b0 + plane); a.x += q.x; a.y += q.y; a.z += q.z; a.w += q.w; }
+        // byte >= 2 <=> bit 7 of byte + 0x7E (no carry: byte <= 54); the flags come out in cell order
+        uint32_t fw[4] = { ((a.x + 0x7E7E7E7Eu) >> 7) & 0x01010101u, ((a.y + 0x7E7E7E7Eu) >> 7) & 0x01010101u,
+                           ((a.z + 0x7E7E7E7Eu) >> 7) & 0x01010101u, ((a.w + 0x7E7E7E7Eu) >> 7) & 0x01010101u };
+        const uint4 c0 = *reinterpret_cast<const uint4 *>(cw + w0), c1 = *reinterpret_cast<const uint4 *>(cw + w0 + 4);
+        const uint32_t cv[8] = { c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w };
+        uint32_t ow[4];
 #pragma unroll
         for (int w = 0; w < 4; w++) {
-            // lane >= 2 <=> bit 15 of lane + 0x7FFE; a box sum is at most n, so no lane carries while n <= 32768
-            const uint32_t f0 = small_n ? ((sv[2 * w] + 0x7FFE7FFEu) >> 15) & 0x00010001u : __vcmpgeu2(sv[2 * w], 0x00020002u) & 0x00010001u;
-            const uint32_t f1 = small_n ? ((sv[2 * w + 1] + 0x7FFE7FFEu) >> 15) & 0x00010001u : __vcmpgeu2(sv[2 * w + 1], 0x00020002u) & 0x00010001u;
-            fw[w] = __byte_perm(f0, f1, 0x6420);
             ow[w] = __byte_perm(__vminu2(cv[2 * w], 0x00ff00ffu), __vminu2(cv[2 * w + 1], 0x00ff00ffu), 0x6420);
             ncf += __popc(fw[w]);
         }
@@ -157,7 +152,7 @@ int bsg_ndmap(const bsg_ndmap_params *p, const float *rec, uint8_t *occ, uint8_t
     if (!p || !rec || !occ || !conf || !ncell) return BSG_ERR_ARG;
     const long cells = (long)p->nx * p->ny * p->nz;
     if (p->num_envs < 1 || p->num_ac < 1 || p->num_ac > 65535 || p->nt < 1 || cells < 16 || (p->nx % 16) != 0) return BSG_ERR_ARG;
-    const size_t smem = (size_t)cells * 2 * sizeof(uint16_t);
+    const size_t smem = (size_t)cells * 3;                    // u16 counts + u8 plane sums
     if (smem > 227 * 1024) return BSG_ERR_UNSUPPORTED;
     const float icx = 1.0f / p->cell_x, icy = 1.0f / p->cell_y, icz = 1.0f / p->cell_z;
     dim3 grid(p->nt, p->num_envs);
