@@ -59,10 +59,17 @@ __global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_pa
             if (yy < 0 || yy >= ny) continue;
             const int wb = ((yz + dy) * nx + x8 * 8) >> 1;    // first word of the group in row yy
             const uint4 m = *reinterpret_cast<const uint4 *>(cw + wb);
-            rs[0] += x8 > 0 ? __vminu2(cw[wb - 1], 0x00020002u) : 0u;
+            if constexpr (!POW2) rs[0] += x8 > 0 ? __vminu2(cw[wb - 1], 0x00020002u) : 0u;
             rs[1] += __vminu2(m.x, 0x00020002u); rs[2] += __vminu2(m.y, 0x00020002u);
             rs[3] += __vminu2(m.z, 0x00020002u); rs[4] += __vminu2(m.w, 0x00020002u);
-            rs[5] += x8 < gx - 1 ? __vminu2(cw[wb + 4], 0x00020002u) : 0u;
+            if constexpr (!POW2) rs[5] += x8 < gx - 1 ? __vminu2(cw[wb + 4], 0x00020002u) : 0u;
+        }
+        if constexpr (POW2) {
+            // the groups of a row sit in neighbouring lanes (gx divides 32, whole warps in the loop): the column sums of the
+            // words next to this group come from the lanes beside it instead of 6 more (bank-conflicting) loads
+            const uint32_t lft = __shfl_up_sync(0xffffffffu, rs[4], 1), rgt = __shfl_down_sync(0xffffffffu, rs[1], 1);
+            rs[0] = x8 > 0 ? lft : 0u;
+            rs[5] = x8 < gx - 1 ? rgt : 0u;
         }
         uint4 o;
         o.x = rs[1] + __funnelshift_l(rs[0], rs[1], 16) + __funnelshift_r(rs[1], rs[2], 16);
@@ -159,7 +166,7 @@ int bsg_ndmap(const bsg_ndmap_params *p, const float *rec, uint8_t *occ, uint8_t
     auto ispow2 = [](int v) { return v > 0 && (v & (v - 1)) == 0; };
     auto lg2 = [](int v) { int l = 0; while ((1 << l) < v) l++; return l; };
     const int gx = p->nx / 8, plane = p->nx * p->ny;
-    if (ispow2(gx) && ispow2(p->ny)) {
+    if (ispow2(gx) && ispow2(p->ny) && gx <= 32 && (cells / 8) % 32 == 0) {
         if (cudaFuncSetAttribute(ndmap_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) return BSG_ERR_CUDA;
         ndmap_kernel<true><<<grid, kNdThreads, smem, (cudaStream_t)stream>>>(*p, icx, icy, icz, lg2(gx), lg2(plane), rec, occ, conf, ncell);
     } else {
