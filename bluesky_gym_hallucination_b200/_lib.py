@@ -6,7 +6,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get('BSG_LIB_PATH') or os.path.join(_HERE, 'libbsgcore.so')   # override: A/B of kernel variants (tools/ab.sh)
 
-ABI_VERSION = 2
+ABI_VERSION = 3
 KIND_HORIZONTAL, KIND_VERTICAL, KIND_SECTOR, KIND_RAW, KIND_MERGE = 0, 1, 2, 3, 4
 MAX_WIND = 8
 FP32, FP64 = 0, 1
@@ -25,7 +25,8 @@ class Config(C.Structure):
     _fields_ = [('struct_size', C.c_int32), ('env_kind', C.c_int32), ('num_envs', C.c_int32), ('max_ac', C.c_int32),
                 ('precision', C.c_int32), ('substeps', C.c_int32), ('asas_on', C.c_int32), ('reso_on', C.c_int32),
                 ('reso_off_own', C.c_int32), ('max_episode_steps', C.c_int32), ('device', C.c_int32),
-                ('fixed_nac', C.c_int32), ('simdt', C.c_double), ('rpz_m', C.c_double), ('hpz_m', C.c_double),
+                ('fixed_nac', C.c_int32), ('density_mode', C.c_int32), ('reserved0', C.c_int32),
+                ('simdt', C.c_double), ('rpz_m', C.c_double), ('hpz_m', C.c_double),
                 ('dtlookahead', C.c_double), ('resofach', C.c_double), ('resofacv', C.c_double)]
 
 
@@ -54,6 +55,10 @@ class NdmapParams(C.Structure):
                 ('nz', C.c_int32), ('nt', C.c_int32), ('x0', C.c_float), ('y0', C.c_float), ('z0', C.c_float),
                 ('cell_x', C.c_float), ('cell_y', C.c_float), ('cell_z', C.c_float), ('dt', C.c_float),
                 ('reserved', C.c_int32)]
+
+
+class NdmapGeo(C.Structure):
+    _fields_ = [('lat0', C.c_double), ('lon0', C.c_double), ('m_per_deg_lat', C.c_double), ('m_per_deg_lon', C.c_double)]
 
 
 # every symbol include/bsgcore.h declares: (name, restype, argtypes)
@@ -86,6 +91,8 @@ SYMBOLS = {
     'bsg_cd_sym_finalize_peers': (_I, [C.POINTER(CdParams), C.POINTER(CdPeers), C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_finalize': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_ndmap': (_I, [C.POINTER(NdmapParams), _VP, _VP, _VP, _VP, _VP]),
+    'bsg_ndmap_unpack': (_I, [C.POINTER(NdmapParams), _VP, _VP, _VP]),
+    'bsg_ndmap_state': (_I, [_VP, C.POINTER(NdmapParams), C.POINTER(NdmapGeo), _VP, _VP, _VP, _VP, _VP]),
     'bsg_peak_fp32': (_I, [_I, _I, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     'bsg_peak_fp64': (_I, [_I, _I, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }

@@ -47,7 +47,7 @@ class BsgCore:
 
     def __init__(self, kind, num_envs, max_ac, precision='fp32', device=0, substeps=0, simdt=0.0, asas_on=False,
                  reso_on=False, reso_off_own=False, max_episode_steps=0, rpz_m=0.0, hpz_m=0.0, dtlookahead=0.0,
-                 cd_outputs=False, fixed_nac=False):
+                 cd_outputs=False, fixed_nac=False, density_mode='normal'):
         self.lib = L.load()
         if not torch.cuda.is_available():
             raise L.BsgError("libbsgcore needs a CUDA device (no CPU fallback)")
@@ -57,7 +57,8 @@ class BsgCore:
         self.rdtype = torch.float64 if self.fp64 else torch.float32
         self.npdtype = np.float64 if self.fp64 else np.float32
         cfg = L.Config(C.sizeof(L.Config), kind, num_envs, max_ac, L.FP64 if self.fp64 else L.FP32, substeps,
-                       int(asas_on), int(reso_on), int(reso_off_own), max_episode_steps, device, int(fixed_nac), simdt, rpz_m,
+                       int(asas_on), int(reso_on), int(reso_off_own), max_episode_steps, device, int(fixed_nac),
+                       {'normal': 0, 'uniform': 1}[density_mode], 0, simdt, rpz_m,
                        hpz_m, dtlookahead, 0.0, 0.0)
         self.h = C.c_void_p()
         rc = self.lib.bsg_create(C.byref(cfg), C.byref(self.h))
@@ -201,6 +202,23 @@ class BsgCore:
         L.check(self.lib.bsg_step_host(self.h, _ptr(actions), None, None, None, None, None), self.h)
         return self.host_views()
 
+    def ndmap(self, nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=0.0, cx=1.0, cy=1.0, cz=1.0, dt=10.0, lat0=52.0, lon0=4.0,
+              out=None, want_rec=False):
+        """ND-map of the LIVE state (bsg_ndmap_state): straight-line look-ahead of every live aircraft from where it is
+        now, flat-earth metres from (lat0, lon0).  Returns (occ, conf_bits, ncell[, rec]) like core.ndmap."""
+        E, N, dev = self.E, self.N, self.device
+        if out is None:
+            out = (torch.empty((E, nt, nz, ny, nx), dtype=torch.uint8, device=dev),
+                   torch.empty((E, nt, nz * ny * nx // 8), dtype=torch.uint8, device=dev),
+                   torch.empty((E, nt), dtype=torch.int32, device=dev))
+        rec = torch.empty((E, 6, N), dtype=torch.float32, device=dev) if want_rec else None
+        p = L.NdmapParams(E, N, nx, ny, nz, nt, x0, y0, z0, cx, cy, cz, dt, 0)
+        m_lat = float(np.radians(1.0) * 6371000.0)
+        geo = L.NdmapGeo(lat0, lon0, m_lat, m_lat * float(np.cos(np.radians(lat0))))
+        L.check(self.lib.bsg_ndmap_state(self.h, C.byref(p), C.byref(geo), _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), _ptr(rec),
+                                         self._stream()), self.h)
+        return out + ((rec,) if want_rec else ())
+
     def launch_count(self):
         n = C.c_int64(0)
         L.check(self.lib.bsg_launch_count(self.h, C.byref(n)), self.h)
@@ -274,17 +292,30 @@ def cd_sweep_sym(rec, rpz_m=5 * 1852.0, hpz_m=1000 * 0.3048, dtlookahead=300.0, 
 
 
 def ndmap(rec, nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=0.0, cx=1.0, cy=1.0, cz=1.0, dt=10.0, out=None):
-    """rec: [E,6,n] f32 CUDA (x,y,z,u,v,w).  Returns occ u8, conf u8 [E,nt,nz,ny,nx], ncell i32 [E,nt]."""
+    """rec: [E,6,n] f32 CUDA (x,y,z,u,v,w).  Returns occ u8 [E,nt,nz,ny,nx], conf_bits u8 [E,nt,nz*ny*nx/8] (1 bit per
+    cell: cell c of a slab <-> bit c & 7 of byte c >> 3; ndmap_unpack gives the dense 0/1 bytes), ncell i32 [E,nt]."""
     lib = L.load()
     E, _, n = rec.shape
     dev = rec.device
     if out is None:
         out = (torch.empty((E, nt, nz, ny, nx), dtype=torch.uint8, device=dev),
-               torch.empty((E, nt, nz, ny, nx), dtype=torch.uint8, device=dev),
+               torch.empty((E, nt, nz * ny * nx // 8), dtype=torch.uint8, device=dev),
                torch.empty((E, nt), dtype=torch.int32, device=dev))
     p = L.NdmapParams(E, n, nx, ny, nz, nt, x0, y0, z0, cx, cy, cz, dt, 0)
     s = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
     L.check(lib.bsg_ndmap(C.byref(p), _ptr(rec), _ptr(out[0]), _ptr(out[1]), _ptr(out[2]), s))
+    return out
+
+
+def ndmap_unpack(conf_bits, nx=64, ny=64, nz=8):
+    """conf_bits u8 [E,nt,cells/8] -> dense u8 0/1 [E,nt,nz,ny,nx]."""
+    lib = L.load()
+    E, nt, _ = conf_bits.shape
+    dev = conf_bits.device
+    out = torch.empty((E, nt, nz, ny, nx), dtype=torch.uint8, device=dev)
+    p = L.NdmapParams(E, 1, nx, ny, nz, nt, 0.0, 0.0, 0.0, 1.0, 1.0, 1.0, 1.0, 0)
+    s = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
+    L.check(lib.bsg_ndmap_unpack(C.byref(p), _ptr(conf_bits), _ptr(out), s))
     return out
 
 
@@ -319,9 +350,12 @@ class PeerSweep:
         self.E, self.N, self.rank, self.world, self.rows = E, N, rank, world, N // world
         dev = torch.device('cuda', torch.cuda.current_device()) if device is None else device
         n = E * self.rows
-        # block layout (bytes): rec [n][8] f32 | nconf [n] i32 | nlos [n] i32 | tcpamax [n] f32 | key [n] i64
-        off = {'rec': 0, 'nconf': 32 * n, 'nlos': 36 * n, 'tcpamax': 40 * n, 'key': 48 * n}   # key 8-aligned: 44 n -> 48 n
-        nbytes = 56 * n
+        # block layout (bytes): rec [2][n][8] f32 | nconf [n] i32 | nlos [n] i32 | tcpamax [n] f32 | key [n] i64
+        # TWO record regions, alternated by step parity: finalize of step k reads the winner's record from its owner
+        # (no cross-GPU barrier follows it), so a faster rank's pack of step k+1 must not land in the region a slower
+        # rank is still reading; it lands in the other one, which nobody reads before the next barrier.
+        off = {'rec': 0, 'rec1': 32 * n, 'nconf': 64 * n, 'nlos': 68 * n, 'tcpamax': 72 * n, 'key': 80 * n}   # key 8-aligned
+        nbytes = 88 * n
         self.h = None
         if world > 1:
             import torch.distributed._symmetric_memory as symm
@@ -332,16 +366,22 @@ class PeerSweep:
             self.block = torch.empty((nbytes,), dtype=torch.uint8, device=dev)
             bases = [self.block.data_ptr()]
         view = lambda key, dt, *shape: self.block[off[key]:off[key] + int(np.prod(shape)) * torch.empty((), dtype=dt).element_size()].view(dt).view(*shape)
-        self.rec = view('rec', torch.float32, E, self.rows, 8)
+        self.recs = (view('rec', torch.float32, E, self.rows, 8), view('rec1', torch.float32, E, self.rows, 8))
+        self.rec = self.recs[0]
+        self.parity = 0
+        self.debug_finalize_delay = 0
         self.nconf = view('nconf', torch.int32, E, self.rows)
         self.nlos = view('nlos', torch.int32, E, self.rows)
         self.tcpamax = view('tcpamax', torch.float32, E, self.rows)
         self.key = view('key', torch.int64, E, self.rows)
-        self.peers = L.CdPeers()
-        self.peers.num_ranks, self.peers.rows_per_rank = world, self.rows
-        for g in range(world):
-            for f in ('rec', 'nconf', 'nlos', 'tcpamax', 'key'):
-                getattr(self.peers, f)[g] = bases[g] + off[f]
+        self.peer_tabs = (L.CdPeers(), L.CdPeers())          # one peer table per record region
+        for par, tab in enumerate(self.peer_tabs):
+            tab.num_ranks, tab.rows_per_rank = world, self.rows
+            for g in range(world):
+                tab.rec[g] = bases[g] + off['rec1' if par else 'rec']
+                for f in ('nconf', 'nlos', 'tcpamax', 'key'):
+                    getattr(tab, f)[g] = bases[g] + off[f]
+        self.peers = self.peer_tabs[0]
         self.out = dict(inconf=torch.empty((E, self.rows), dtype=torch.uint8, device=dev),
                         near_idx=torch.empty((E, self.rows), dtype=torch.int32, device=dev),
                         near_tcpa=torch.empty((E, self.rows), dtype=torch.float32, device=dev),
@@ -355,6 +395,8 @@ class PeerSweep:
         s = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
         own = L.CdParams(E, self.rows, 0, self.rows, rpz_m, hpz_m, dtlookahead, 0)
         full = L.CdParams(E, self.N, 0, self.N, rpz_m, hpz_m, dtlookahead, 0)
+        self.rec, self.peers = self.recs[self.parity], self.peer_tabs[self.parity]
+        self.parity ^= 1
         L.check(lib.bsg_cd_pack(E, self.rows, _ptr(lat), _ptr(lon), _ptr(alt), _ptr(trk), _ptr(gs), _ptr(vs), float(lat0),
                                 float(lon0), _ptr(self.rec), s))
         L.check(lib.bsg_cd_sym_init(C.byref(own), _ptr(self.nconf), _ptr(self.nlos), _ptr(self.tcpamax), _ptr(self.key), s))
@@ -363,6 +405,8 @@ class PeerSweep:
         L.check(lib.bsg_cd_sym_sweep_peers(C.byref(full), C.byref(self.peers), self.rank, self.world, s))
         if self.h is not None:
             self.h.barrier(channel=1)                  # every rank's atomics have landed
+        if self.debug_finalize_delay:                  # test hook: widen the window between the barrier and finalize
+            torch.cuda._sleep(int(self.debug_finalize_delay))
         o = self.out
         L.check(lib.bsg_cd_sym_finalize_peers(C.byref(full), C.byref(self.peers), self.rank, _ptr(o['inconf']),
                                               _ptr(o['near_idx']), _ptr(o['near_tcpa']), _ptr(o['near_dcpa']),

@@ -7,6 +7,7 @@
 #include <string>
 #include <new>
 #include "bsg_step_kernel.cuh"
+#include "bsg_step_launch.h"
 #include "bsg_handle.h"
 
 using namespace bsg;
@@ -169,7 +170,7 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     }
     h->tpb = 128;
     if (N > 128 || (256 / N) * N * 128 > (128 / N) * N * 256) h->tpb = 256;
-    if (const char *f = getenv("BSG_FORCE_TPB")) { int t = atoi(f); if ((t == 128 || t == 256 || ((t == 320 || t == 160) && g.precision == BSG_FP32 && g.env_kind != BSG_KIND_MERGE && N <= 64)) && t >= N) h->tpb = t; }
+    if (const char *f = getenv("BSG_FORCE_TPB")) { int t = atoi(f); if ((t == 128 || t == 256) && t >= N) h->tpb = t; }
     h->epb = h->tpb / N;
     if (const char *f = getenv("BSG_FORCE_EPB")) { int t = atoi(f); if (t >= 1 && t * N <= h->tpb) h->epb = t; }
     const size_t rs = rsize(h);
@@ -193,7 +194,7 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     CK(h, cudaMalloc(&h->d_act, h->act_bytes));
     { int rc = alloc_out(h); if (rc != BSG_OK) return rc; }
     CK(h, cudaStreamCreateWithFlags(&h->hs, cudaStreamNonBlocking));
-    if (h->smem > 48 * 1024) { h->err = "shared memory per CTA above 48 KB"; return BSG_ERR_UNSUPPORTED; }
+    if (h->smem > 227 * 1024) { h->err = "shared memory per CTA above 227 KB"; return BSG_ERR_UNSUPPORTED; }
     return BSG_OK;
 }
 
@@ -234,7 +235,7 @@ int bsg_destroy(bsg_handle *h) {
     if (!h) return BSG_ERR_ARG;
     cudaSetDevice(h->cfg.device);
     cudaFree(h->pos); cudaFree(h->st); cudaFree(h->reso); cudaFree(h->nac); cudaFree(h->ev); cudaFree(h->stage64);
-    cudaFree(h->d_act); cudaFree(h->d_out); cudaFree(h->episode); cudaFree(h->done_buf[0]); cudaFree(h->done_buf[1]);
+    cudaFree(h->d_act); cudaFree(h->d_out); cudaFree(h->episode); cudaFree(h->done_buf[0]); cudaFree(h->done_buf[1]); cudaFree(h->nd_rec);
     if (h->h_act) cudaFreeHost(h->h_act);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->hs) cudaStreamDestroy(h->hs);

@@ -16,7 +16,7 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     const bool ar = h->autoreset && !observe_only && g.env_kind != BSG_KIND_RAW;
     A.skip = (ar && h->autoreset == 1) ? h->done_buf[h->flip] : nullptr;
     // next-step mode: the reset of the envs that ended in the previous step is fused into this launch
-    A.fuse_reset = (A.skip != nullptr) ? 1 : 0; A.fixed_nac = g.fixed_nac; A.RC = h->rc; A.ar_seed = h->ar_seed; A.episode = h->episode;
+    A.fuse_reset = (A.skip != nullptr) ? 1 : 0; A.fixed_nac = g.fixed_nac; A.density_mode = g.density_mode; A.RC = h->rc; A.ar_seed = h->ar_seed; A.episode = h->episode;
     A.W = h->wind; A.noise_sigma = (R)h->noise_sigma; A.noise_seed = h->noise_seed; A.noise_ctr = (unsigned int)h->launches;
     // EXT instantiations: Merge env, wind field, observation noise (fp32: the symmetric sweep only, N <= 64)
     const bool ext = is_ext(h);
@@ -25,40 +25,19 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     const int grid = (g.num_envs + h->epb - 1) / h->epb;
     const bool reso = g.reso_on && g.asas_on;
     const dim3 gd(grid), bd(((h->epb * g.max_ac + 31) / 32) * 32);      // whole warps covering the CTA's envs
-#define BSG_LAUNCH(TPB, RESO, SYM) step_kernel<R, TPB, RESO, SYM><<<gd, bd, h->smem, s>>>(A)
-#define BSG_LAUNCH_EXT(TPB, RESO, SYM) step_kernel<R, TPB, RESO, SYM, true><<<gd, bd, h->smem, s>>>(A)
-    if (ext) {
-        if (h->tpb != 128 && h->tpb != 256) { h->err = "EXT kernels: CTA of 128 or 256 threads"; return BSG_ERR_UNSUPPORTED; }
-        if constexpr (sizeof(R) == 4) {
+    cudaError_t le;
+    if constexpr (sizeof(R) == 4) {
+        if (ext) {
             if (g.max_ac > 64) { h->err = "EXT kernels (fp32): N <= 64"; return BSG_ERR_UNSUPPORTED; }
-            if (h->tpb == 128) { if (reso) BSG_LAUNCH_EXT(128, true, true); else BSG_LAUNCH_EXT(128, false, true); }
-            else { if (reso) BSG_LAUNCH_EXT(256, true, true); else BSG_LAUNCH_EXT(256, false, true); }
+            le = launch_step_f32_ext(h->tpb, reso, gd, bd, h->smem, s, A);
         } else {
-            if (h->tpb == 128) { if (reso) BSG_LAUNCH_EXT(128, true, false); else BSG_LAUNCH_EXT(128, false, false); }
-            else { if (reso) BSG_LAUNCH_EXT(256, true, false); else BSG_LAUNCH_EXT(256, false, false); }
+            const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM");     // symmetric half-ring sweep (fp32 fast path)
+            le = launch_step_f32(h->tpb, reso, sym, gd, bd, h->smem, s, A);
         }
-    } else if constexpr (sizeof(R) == 4) {
-        const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM");          // symmetric half-ring sweep (fp32 fast path)
-        if (h->tpb == 128) {
-            if (sym) { if (reso) BSG_LAUNCH(128, true, true); else BSG_LAUNCH(128, false, true); }
-            else if (reso) BSG_LAUNCH(128, true, false); else BSG_LAUNCH(128, false, false);
-        } else if (h->tpb == 160 && sym) {
-            if (reso) BSG_LAUNCH(160, true, true); else BSG_LAUNCH(160, false, true);
-        } else if (h->tpb == 256 || h->tpb == 160) {
-            if (sym) { if (reso) BSG_LAUNCH(256, true, true); else BSG_LAUNCH(256, false, true); }
-            else if (reso) BSG_LAUNCH(256, true, false); else BSG_LAUNCH(256, false, false);
-        } else {
-            if (sym) { if (reso) BSG_LAUNCH(320, true, true); else BSG_LAUNCH(320, false, true); }
-            else if (reso) BSG_LAUNCH(320, true, false); else BSG_LAUNCH(320, false, false);
-        }
-    } else {
-        if (h->tpb == 128) { if (reso) BSG_LAUNCH(128, true, false); else BSG_LAUNCH(128, false, false); }
-        else { if (reso) BSG_LAUNCH(256, true, false); else BSG_LAUNCH(256, false, false); }
-    }
-#undef BSG_LAUNCH
-#undef BSG_LAUNCH_EXT
+    } else le = launch_step_f64(h->tpb, reso, ext, gd, bd, h->smem, s, A);
+    if (le == cudaErrorInvalidValue && h->tpb != 128 && h->tpb != 256) { h->err = "step kernel: CTA of 128 or 256 threads"; return BSG_ERR_UNSUPPORTED; }
     h->launches++;
-    CK(h, cudaGetLastError());
+    CK(h, le);
     if (ar) {
         if (A.out.done != done_now)
             CK(h, cudaMemcpyAsync(done_now, A.out.done, g.num_envs * sizeof(int32_t), cudaMemcpyDeviceToDevice, s));

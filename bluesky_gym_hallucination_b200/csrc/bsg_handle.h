@@ -28,6 +28,7 @@ struct bsg_handle {
     double noise_sigma = 0.0;         // bsg_set_obs_noise
     uint64_t noise_seed = 0;
     int32_t *done_buf[2] = { nullptr, nullptr };      // [E] reset counter (Philox counter word)
+    float *nd_rec = nullptr;          // bsg_ndmap_state: packed straight-line records of the live state [E][6][N]
     int64_t launches = 0;
     std::string err;
 };

@@ -57,92 +57,124 @@ struct CdParamsF { float R2, hpz, dtlook, rpz, rpz_m, hpz_m; };
 // call each and break the software pipelining of the pair loop
 __device__ __forceinline__ float rcp_approx(float x) { float y; asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 __device__ __forceinline__ float sqrt_approx(float x) { float y; asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
+__device__ __forceinline__ float fmax3_f(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
 
-// Hot form of the fp32 pair: only what decides the conflict flag.  Instruction budget per pair (B200: the ALU
-// pipe -- FSETP/FSEL/FMNMX/integer -- issues at half the rate of the FMA pipe, so comparisons are the scarce
-// resource): ~31 FMA-pipe ops, 3 MUFU, 10 ALU ops.  Everything needed only for conflicting pairs (LoS test,
-// row min/argmin/max, MVP) is evaluated by the caller under a warp-uniform `any(sw)` branch.
-//  * no select of tinhor/touthor: when dcpa2 >= R2 the sqrt argument is negative -> NaN, FMNMX drops it and
-//    the flag is gated by swhor anyway;
+// ---------------------------------------------------------------------------------------------------------------
+// The fp32 pair, canonical form.  ONE sequence of individually rounded operations, written with the explicit
+// round-to-nearest intrinsics (never contracted), so that every kernel that evaluates a pair -- the scalar forms
+// below, the packed f32x2 form of the fused step kernel, the tiled sweeps -- produces the same bits:
+//   dy = yb - ya;  cav = fma(ca_a, ca_b, -(sa_a sa_b));  dx = (xb - xa) cav;  dist2 = fma(dx, dx, dy dy)
+//   du = ub - ua;  dv = vb - va;  dv2 = fma(du, du, fma(dv, dv, 1e-6))      (the reference's clamp as an additive floor)
+//   n = rcp(-dv2)                                                           (= -1 / |v_rel|^2: no negation anywhere below)
+//   dot = fma(du, dx, dv dy);  cr = fma(dx, dv, -(dy du));  t6 = fma(cr, cr, dist2 1e-6)
+//   q = fma(t6, n, R2)            = R2 - dcpa2, one rounding (cross form: dcpa2 = (cr^2 + 1e-6 dist^2) / dv2)
+//   dt = sqrt(-(q n))             = dtinhor; NaN when q < 0 (no horizontal conflict): the max below drops it
+//   tout = fma(dot, n, dt);  tin = fma(dot, n, -dt)                         (tcpa +- dtinhor, tcpa = dot n)
+//   [VERT]  nv = rcp(-(vsb - vsa));  thi = (dalt + hpz) nv;  tlo = (dalt - hpz) nv
+//           tin = max(min(thi, tlo), tin);  tout = min(max(thi, tlo), tout)
+//   margin = max(-q, -tout, tin - dtlook [, tin - tout])
+// conflict <=> SIGN BIT of margin (the three / four strict inequalities of StateBased.detect folded into one max of
+// the negated margins; NaN margins are dropped by max, an all-NaN pair gives the canonical NaN = sign clear = no
+// conflict, as the comparisons would; the only deviation is an exact tie tout == +0, inside any epsilon).
 //  * no clamp of |dvs|: rcp(0) = inf gives tinver/toutver = -/+inf (vertically inside) or both beyond the
 //    look-ahead / in the past, the same decisions the reference's 1e-6 clamp produces.
-struct PairCore { float tcpa, dcpa2, tin, dx, dy, dist2, dalt; };
-
 // VERT = false: the caller has established that every aircraft of the env is level (vs == 0 exactly) and within
 // hpz/2 of a common altitude; the vertical window of the generic form is then (-inf, +inf) identically
 // ((dalt +/- hpz) * (-1/0)), so tin / tout are the horizontal ones and the flag is bit-identical.
+struct PairCore { float tcpa, dcpa2, tin, dx, dy, dist2, dalt, du, dv, dot; };
+
+template <bool VERT, bool OUT>
+__device__ __forceinline__ float pair_fast_margin(const RecFast &a, const RecFast &b, const CdParamsF &P, PairCore *o) {
+    const float dy = __fsub_rn(b.y, a.y);
+    const float cav = __fmaf_rn(a.ca, b.ca, -__fmul_rn(a.sa, b.sa));
+    const float dx = __fmul_rn(__fsub_rn(b.x, a.x), cav);
+    const float dist2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+    const float du = __fsub_rn(b.u, a.u), dv = __fsub_rn(b.v, a.v);
+    const float dv2 = __fmaf_rn(du, du, __fmaf_rn(dv, dv, 1e-6f));
+    const float n = rcp_approx(-dv2);
+    const float dot = __fmaf_rn(du, dx, __fmul_rn(dv, dy));
+    const float cr = __fmaf_rn(dx, dv, -__fmul_rn(dy, du));
+    const float t6 = __fmaf_rn(cr, cr, __fmul_rn(dist2, 1e-6f));
+    const float q = __fmaf_rn(t6, n, P.R2);
+    const float dt = sqrt_approx(-__fmul_rn(q, n));
+    float tout = __fmaf_rn(dot, n, dt), tin = __fmaf_rn(dot, n, -dt);
+    float dalt = 0.0f;
+    if constexpr (VERT || OUT) dalt = __fsub_rn(b.alt, a.alt);
+    float m;
+    if constexpr (VERT) {
+        const float nv = rcp_approx(-__fsub_rn(b.vs, a.vs));
+        const float thi = __fmul_rn(__fadd_rn(dalt, P.hpz), nv), tlo = __fmul_rn(__fadd_rn(dalt, -P.hpz), nv);
+        tin = fmaxf(fminf(thi, tlo), tin); tout = fminf(fmaxf(thi, tlo), tout);
+        m = fmaxf(fmax3_f(-q, -tout, __fadd_rn(tin, -P.dtlook)), __fsub_rn(tin, tout));
+    } else m = fmax3_f(-q, -tout, __fadd_rn(tin, -P.dtlook));
+    if constexpr (OUT) {
+        o->tcpa = __fmul_rn(dot, n); o->dcpa2 = __fmul_rn(t6, -n); o->tin = tin; o->dx = dx; o->dy = dy; o->dist2 = dist2;
+        o->dalt = dalt; o->du = du; o->dv = dv; o->dot = dot;
+    }
+    return m;
+}
+// geometry only (resumenav of a pair that is no longer in conflict): squared distance and r . v_rel, canonical roundings
+__device__ __forceinline__ void pair_fast_geom(const RecFast &a, const RecFast &b, float &dist2, float &dot) {
+    const float dy = __fsub_rn(b.y, a.y);
+    const float cav = __fmaf_rn(a.ca, b.ca, -__fmul_rn(a.sa, b.sa));
+    const float dx = __fmul_rn(__fsub_rn(b.x, a.x), cav);
+    dist2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+    const float du = __fsub_rn(b.u, a.u), dv = __fsub_rn(b.v, a.v);
+    dot = __fmaf_rn(du, dx, __fmul_rn(dv, dy));
+}
+
+// flag + the quantities the row reductions / MVP need (evaluated by the callers for conflicting pairs only)
 template <bool VERT = true>
 __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &b, const CdParamsF &P, bool off, PairCore &o) {
-    const float dy = b.y - a.y;
-    const float cav = fmaf(a.ca, b.ca, -(a.sa * b.sa));
-    const float dx = (b.x - a.x) * cav;
-    const float dist2 = fmaf(dx, dx, dy * dy);
-    const float du = b.u - a.u, dv = b.v - a.v;
-    // |v_rel|^2 with the reference's lower clamp (1e-6) folded in as an additive floor: for |v_rel|^2 > 16 the sum
-    // rounds to |v_rel|^2 itself, for equal velocity vectors (common: integer dpsi draws) it is the clamp value
-    // 1e-6 exactly; in between (relative speeds below 3 mm/s) the reference's own value is the arbitrary clamp.
-    const float dv2 = fmaf(du, du, fmaf(dv, dv, 1e-6f));
-    const float idv2 = rcp_approx(dv2);
-    const float ndot = -fmaf(du, dx, dv * dy);
-    const float tcpa = ndot * idv2;
-    const float cr = fmaf(dx, dv, -(dy * du));
-    // dist^2 - tcpa^2 dv2 = (cr^2 + dist^2 (dv2 - |v_rel|^2)) / dv2 with dv2 - |v_rel|^2 = 1e-6: the second term is
-    // below one ulp of cr^2-scale values unless the velocities are equal, where dCPA must come out as dist
-    const float dcpa2 = fmaf(cr, cr, dist2 * 1e-6f) * idv2;
-    const bool swhor = (dcpa2 < P.R2) && off;
-    const float dtinhor = sqrt_approx((P.R2 - dcpa2) * idv2);
-    const float dalt = b.alt - a.alt;
-    // explicit FMAs: the same rounding in every kernel this body is inlined into (the compiler would otherwise
-    // contract tcpa -/+ dtinhor in some contexts and not in others)
-    float tin = fmaf(ndot, idv2, -dtinhor), tout = fmaf(ndot, idv2, dtinhor);
-    if constexpr (VERT) {
-        const float n = -rcp_approx(b.vs - a.vs);
-        const float thi = (dalt + P.hpz) * n, tlo = (dalt - P.hpz) * n;
-        tin = fmaxf(fminf(thi, tlo), tin); tout = fminf(fmaxf(thi, tlo), tout);
-    }
-    o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist2 = dist2; o.dalt = dalt;
-    // VERT = false: tin <= tout holds whenever swhor does (dtinhor >= 0), so the test is dropped (same flag)
-    if constexpr (!VERT) return swhor && (tout > 0.0f) && (tin < P.dtlook);
-    else return swhor && (tin <= tout) && (tout > 0.0f) && (tin < P.dtlook);
+    return (__float_as_int(pair_fast_margin<VERT, true>(a, b, P, &o)) < 0) && off;
 }
-
-// Flag-only form for the half-ring sweep of the fused step kernel: returns a float whose SIGN BIT is the conflict flag,
-// so the caller shifts it into its mask with one funnel shift (no FSETP chain, no select: the comparison pipe is the
-// scarce one).  The three (four) strict inequalities of pair_fast_core are folded into one 3-input max of the negated
-// margins: conflict <=> max(dcpa2 - R2, -tout, tin - dtlook [, tin - tout]) < 0.  Same arithmetic as pair_fast_core for
-// every margin; NaN margins (dcpa2 >= R2 -> sqrt of a negative) are dropped by the max and the first margin decides, an
-// all-NaN pair (NaN state) gives the canonical NaN = sign clear = no conflict, as the comparisons would.  The only
-// deviation is an exact tie tout == +0 (or tin == tout with VERT), inside any epsilon of the thresholds.
-__device__ __forceinline__ float fmax3_f(float a, float b, float c) { float r; asm("max.f32 %0, %1, %2, %3;" : "=f"(r) : "f"(a), "f"(b), "f"(c)); return r; }
+// flag-only form: a float whose SIGN BIT is the conflict flag (one funnel shift pushes it into a mask register)
 template <bool VERT = true>
 __device__ __forceinline__ float pair_fast_sign(const RecFast &a, const RecFast &b, const CdParamsF &P) {
-    const float dy = b.y - a.y;
-    const float cav = fmaf(a.ca, b.ca, -(a.sa * b.sa));
-    const float dx = (b.x - a.x) * cav;
-    const float dist2 = fmaf(dx, dx, dy * dy);
-    const float du = b.u - a.u, dv = b.v - a.v;
-    const float dv2 = fmaf(du, du, fmaf(dv, dv, 1e-6f));
-    const float idv2 = rcp_approx(dv2);
-    const float ndot = -fmaf(du, dx, dv * dy);
-    const float cr = fmaf(dx, dv, -(dy * du));
-    const float dcpa2 = fmaf(cr, cr, dist2 * 1e-6f) * idv2;
-    const float dtinhor = sqrt_approx((P.R2 - dcpa2) * idv2);
-    float tin = fmaf(ndot, idv2, -dtinhor), tout = fmaf(ndot, idv2, dtinhor);
-    if constexpr (VERT) {
-        const float dalt = b.alt - a.alt;
-        const float n = -rcp_approx(b.vs - a.vs);
-        const float thi = (dalt + P.hpz) * n, tlo = (dalt - P.hpz) * n;
-        tin = fmaxf(fminf(thi, tlo), tin); tout = fminf(fmaxf(thi, tlo), tout);
-        return fmaxf(fmax3_f(dcpa2 - P.R2, -tout, tin - P.dtlook), tin - tout);
-    } else return fmax3_f(dcpa2 - P.R2, -tout, tin - P.dtlook);
+    return pair_fast_margin<VERT, false>(a, b, P, nullptr);
 }
 
-// full form (used where every output is wanted): flag + LoS + the PairOut fields
-__device__ __forceinline__ void pair_fast(const RecFast &a, const RecFast &b, const CdParamsF &P, PairOut<float> &o) {
-    PairCore c;
-    o.sw = pair_fast_core(a, b, P, true, c);
-    o.los = (c.dist2 < P.R2) && (fabsf(c.dalt) < P.hpz);
-    o.tcpa = c.tcpa; o.dcpa2 = c.dcpa2; o.tin = c.tin; o.dx = c.dx; o.dy = c.dy; o.dist = c.dist2 /* squared */; o.dalt = c.dalt;
+// ---------------------------------------------------------------------------------------------------------------
+// Packed form (sm_100 f32x2: FFMA2 / FADD2 / FMUL2): TWO partners of one ownship per instruction, the same canonical
+// sequence lane by lane (each half of a packed operation is an IEEE round-to-nearest fma / add / mul), so the two
+// margins are bit-identical to pair_fast_sign<false> of either partner.  A packed value is a 64-bit register pair
+// {lo, hi}; the partners' fields come out of shared memory already packed (SoA rows, one LDS.64 per field), the
+// ownship's fields are broadcast pairs.  The negations are operand modifiers (free), the four MUFU and the two
+// 3-input max are scalar on the halves.  22 FMA-pipe issue slots per TWO pairs instead of 24 per pair.
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk2(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 neg2(f32x2 v) { float lo, hi; upk2(v, lo, hi); return pk2(-lo, -hi); }   // folds into the consumer
+
+struct Rec2 { f32x2 x, y, u, v, ca, sa; };      // ownship: {f, f}; partners: {f[j], f[j + 1]}
+struct Cd2 { f32x2 R2, c1em6, ndtlook; };        // {R2, R2}, {1e-6, 1e-6}, {-dtlook, -dtlook}
+
+__device__ __forceinline__ void pair_fast_sign2(const Rec2 &a, const Rec2 &b, const Cd2 &C, float &m_lo, float &m_hi) {
+    const f32x2 dy = sub2(b.y, a.y);
+    const f32x2 cav = fma2(a.ca, b.ca, neg2(mul2(a.sa, b.sa)));
+    const f32x2 dx = mul2(sub2(b.x, a.x), cav);
+    const f32x2 dist2 = fma2(dx, dx, mul2(dy, dy));
+    const f32x2 du = sub2(b.u, a.u), dv = sub2(b.v, a.v);
+    const f32x2 dv2 = fma2(du, du, fma2(dv, dv, C.c1em6));
+    float l, h;
+    upk2(dv2, l, h);
+    const f32x2 n = pk2(rcp_approx(-l), rcp_approx(-h));
+    const f32x2 dot = fma2(du, dx, mul2(dv, dy));
+    const f32x2 cr = fma2(dx, dv, neg2(mul2(dy, du)));
+    const f32x2 t6 = fma2(cr, cr, mul2(dist2, C.c1em6));
+    const f32x2 q = fma2(t6, n, C.R2);
+    upk2(mul2(q, n), l, h);
+    const f32x2 dt = pk2(sqrt_approx(-l), sqrt_approx(-h));
+    const f32x2 tout = fma2(dot, n, dt);
+    const f32x2 m2 = add2(fma2(dot, n, neg2(dt)), C.ndtlook);
+    float ql, qh, ol, oh, ml, mh;
+    upk2(q, ql, qh); upk2(tout, ol, oh); upk2(m2, ml, mh);
+    m_lo = fmax3_f(-ql, -ol, ml);
+    m_hi = fmax3_f(-qh, -oh, mh);
 }
 
 // MVP displacement of ownship 1 for one conflict pair; drel = (dx, dy, dalt) is intruder relative to ownship.

@@ -7,21 +7,32 @@ using namespace bsg;
 
 namespace {
 
+// The stand-alone reset draws episode 0 of the stream keyed by `seed` and leaves the env's episode counter at 1:
+// calling it again with the same seed reproduces the same scenario (Gymnasium's reset(seed=s) contract), and the
+// auto-reset episodes that follow (fused into bsg_step, keyed by the auto-reset seed) count on from 1.
 template <typename R>
-__global__ void reset_kernel(int kind, int fixed_nac, int E, int N, const int32_t *mask, uint64_t seed, uint32_t *episode,
-                             double *pos, R *st, unsigned long long *reso, int *nac, double *ev, const ResetConst RC) {
+__global__ void reset_kernel(int kind, int fixed_nac, int density_mode, int E, int N, const int32_t *mask, uint64_t seed,
+                             uint32_t *episode, double *pos, R *st, unsigned long long *reso, int *nac, double *ev,
+                             const ResetConst RC) {
     const int e = blockIdx.x;
     if (mask && !mask[e]) return;                       // uniform per CTA
     __shared__ ResetEnv S;
-    const uint32_t ep = episode[e];
+    __shared__ double wdraw[256], wsort[256];           // bsg_create: max_ac <= 256
+    const uint32_t ep = 0u;
     double *v = ev + (size_t)e * BSG_NE;
     if (threadIdx.x == 0) {
-        reset_env_level(kind, fixed_nac, N, e, seed, ep, v, &S, RC);
+        reset_env_level(kind, fixed_nac, density_mode, N, e, seed, ep, v, &S, RC);
         nac[e] = S.nac;
-        episode[e] = ep + 1;
+        episode[e] = 1u;
     }
     __syncthreads();
-    for (int i = threadIdx.x; i < N; i += blockDim.x) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &S, v, pos, st, reso, RC);
+    if (kind == BSG_KIND_SECTOR) {
+        for (int i = threadIdx.x; i < N; i += blockDim.x) reset_wpt_draw(e, i, seed, ep, &S, wdraw);
+        __syncthreads();
+        for (int i = threadIdx.x; i < N; i += blockDim.x) reset_wpt_rank(i, &S, wdraw, wsort);
+        __syncthreads();
+    }
+    for (int i = threadIdx.x; i < N; i += blockDim.x) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &S, wsort, v, pos, st, reso, RC);
 }
 
 }  // namespace
@@ -37,10 +48,10 @@ extern "C" int bsg_reset(bsg_handle *h, const int32_t *mask_dev, uint64_t seed, 
     }
     cudaStream_t s = (cudaStream_t)stream;
     if (g.precision == BSG_FP64)
-        reset_kernel<double><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.fixed_nac, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
+        reset_kernel<double><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.fixed_nac, g.density_mode, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
                                                         (double *)h->st, h->reso, h->nac, h->ev, h->rc);
     else
-        reset_kernel<float><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.fixed_nac, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
+        reset_kernel<float><<<g.num_envs, 64, 0, s>>>(g.env_kind, g.fixed_nac, g.density_mode, g.num_envs, g.max_ac, mask_dev, seed, h->episode, h->pos,
                                                        (float *)h->st, h->reso, h->nac, h->ev, h->rc);
     h->launches++;
     CK(h, cudaGetLastError());

@@ -8,8 +8,9 @@
 // Same value laws as the reference; the random stream is Philox4x32-10 keyed by (seed) with counter
 // (env, episode, draw index, stream) instead of numpy's global legacy generator (the global
 // draw order cannot be reproduced on a GPU; parity runs inject oracle state through bsg_set_state).
-// Two stages per env: reset_env_level (one thread: env-level draws, polygon into the ev slots) and
-// reset_aircraft (one thread per aircraft).  Both are __noinline__: rare, register-hungry fp64 code that
+// Stages per env: reset_env_level (one thread: env-level draws, polygon into the ev slots), for Sector the sorted
+// perimeter waypoints (reset_wpt_draw / reset_wpt_rank, one thread per aircraft, a barrier between them), and
+// reset_aircraft (one thread per aircraft).  All are __noinline__: rare, register-hungry fp64 code that
 // must not inflate the register allocation of the step kernel's hot loop.
 #pragma once
 #include "bsg_step.cuh"
@@ -107,8 +108,8 @@ __device__ inline bool inside_poly_ll(const double *poly, int nv, double tx, dou
 }
 
 // stage 1 (one thread per env): clears the scalar ev slots, draws the env-level quantities, grows the polygon
-static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int N, int e, uint64_t seed, uint32_t ep, double *v,
-                                                    ResetEnv *Sp, const ResetConst &RC) {
+static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int density_mode, int N, int e, uint64_t seed, uint32_t ep,
+                                                    double *v, ResetEnv *Sp, const ResetConst &RC) {
     ResetEnv S = {};
     Philox g(seed, (uint32_t)e, ep, 0u);
     const double ccl = RC.ccl;
@@ -153,7 +154,8 @@ static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int
         }
         S.nv = nv;
         S.gs0 = RC.tas_s;
-        const double dens = g.normal(0.005, 0.001);
+        // sector_cr_env.py:98-103: ac_density_mode "normal" N(0.005, 0.001) or "uniform" U(0.003, 0.007) aircraft per NM^2
+        const double dens = density_mode ? 0.003 + 0.004 * g.uniform() : g.normal(0.005, 0.001);
         const int na = (int)fmax(ceil(dens * area), 5.0);
         S.nac = (fixed_nac || na > N) ? N : na;
         S.minx = S.maxx = px[0]; S.miny = S.maxy = py[0];
@@ -176,10 +178,28 @@ static __device__ __noinline__ void reset_env_level(int kind, int fixed_nac, int
     *Sp = S;
 }
 
-// stage 2 (one thread per aircraft slot i of env e): creates the aircraft in the device state
+// Sector waypoints (sector_cr_env.py:162-176): num_ac perimeter distances U(0, perimeter), SORTED, and aircraft i is
+// handed the i-th smallest -- so the agent (i = 0) always flies to the first waypoint past polygon vertex 0.
+// Two stages with a barrier between them: every aircraft draws one distance (its own Philox stream), then finds
+// the rank of its draw among the env's (ties by index) and files it under that rank; aircraft i reads wsort[i].
+static __device__ __noinline__ void reset_wpt_draw(int e, int i, uint64_t seed, uint32_t ep, const ResetEnv *Sp, double *wdraw) {
+    if (i >= Sp->nac) return;
+    Philox g(seed, (uint32_t)e, ep, 0x40000000u + (uint32_t)i);
+    wdraw[i] = g.uniform() * Sp->perim;
+}
+static __device__ __noinline__ void reset_wpt_rank(int i, const ResetEnv *Sp, const double *wdraw, double *wsort) {
+    const int n = Sp->nac;
+    if (i >= n) return;
+    const double mine = wdraw[i];
+    int r = 0;
+    for (int m = 0; m < n; m++) { const double o = wdraw[m]; r += (o < mine || (o == mine && m < i)) ? 1 : 0; }
+    wsort[r] = mine;
+}
+
+// last stage (one thread per aircraft slot i of env e): creates the aircraft in the device state
 template <typename R>
 static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e, int i, uint64_t seed, uint32_t ep,
-                                                   const ResetEnv *Sp, double *v, double *pos, R *st,
+                                                   const ResetEnv *Sp, const double *wsort, double *v, double *pos, R *st,
                                                    unsigned long long *reso, const ResetConst &RC) {
     const ResetEnv S = *Sp;
     const size_t EN = (size_t)E * N, k = (size_t)e * N + i;
@@ -211,10 +231,9 @@ static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e
             a.selalt = a.alt;
         }
     } else if (kind == BSG_KIND_SECTOR && i < S.nac) {
-        // perimeter waypoint: the reference sorts its draws and hands waypoint i to aircraft i; any assignment of
-        // i.i.d. draws has the same law, so aircraft i keeps its own draw.  Vertices come back from the ev slots.
+        // perimeter waypoint: the i-th smallest of the env's draws (reset_wpt_rank).  Vertices come back from the ev slots.
         const double *poly = v + BSG_EV_POLY;
-        double d = g.uniform() * S.perim, wx = 0.0, wy = 0.0;
+        double d = wsort[i], wx = 0.0, wy = 0.0;
         for (int s2 = 0; s2 < S.nv; s2++) {
             const int m = (s2 + 1) % S.nv;
             const double x0 = (poly[2 * s2] - kCenterLat) * 60, y0 = (poly[2 * s2 + 1] - kCenterLon) * (60 * ccl);

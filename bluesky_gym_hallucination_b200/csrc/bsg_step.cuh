@@ -23,7 +23,7 @@ template <typename R> struct StepArgs {
     const int *skip;      // envs reset after the previous step (auto-reset): observe only, reward 0
     // fused next-step auto-reset: the envs flagged in `skip` draw their new episode at the head of this launch
     // (bsg_reset.cuh stages) instead of in a separate reset launch; `nac` is written by that stage
-    int fuse_reset, fixed_nac; unsigned long long ar_seed; unsigned int *episode; ResetConst RC;
+    int fuse_reset, fixed_nac, density_mode; unsigned long long ar_seed; unsigned int *episode; ResetConst RC;
     bsg_step_out out;
     // EXT kernels only: wind field, observation noise (sigma, Philox key, launch counter)
     WindArgs W;

@@ -6,7 +6,10 @@
 #include "bsg_reset.cuh"
 
 #ifndef BSG_PW
-#define BSG_PW 5          // pairs evaluated per trip of the half-ring loop (A/B on B200: 5 > 4 > 2; divides H = 10 and 25)
+#define BSG_PW 5          // scalar half-ring loop (generic vertical window): pairs per trip (A/B on B200: 5 > 4 > 2)
+#endif
+#ifndef BSG_PG
+#define BSG_PG 3          // packed half-ring loop: f32x2 trips (two partners each) interleaved per iteration
 #endif
 
 namespace bsg {
@@ -30,20 +33,29 @@ __device__ __forceinline__ void cd_params_for(const CdParams &P, CdParams &lit, 
 // CTA size / residency: 128-thread CTAs keep the small-N configs in one balanced wave
 // (C2: 683 CTAs over 148 SMs x 5 resident), 256 threads only when one env needs them (N > 128).
 template <typename R, int TPB> struct StepBounds {
-    // 320: 2 x 320 threads, <= 102 registers; 160: 4 x 160 threads, <= 102 registers (C2: 7 envs per CTA, 586 CTAs =
-    // one wave of 4 per SM -> at most 28 envs per SM instead of 30)
-    static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : TPB == 160 ? 4 : (sizeof(R) == 4 ? 2 : 1);
+    static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : (sizeof(R) == 4 ? 2 : 1);
 };
-// per-env row of CD records in shared memory: N records + 16 B so that the rows of the envs sharing a
-// warp start in different banks (N * 32 B is a multiple of 128 B for N = 20: 2-way LDS.128 conflicts)
-// fp32 rows hold N + N/2 records: the symmetric sweep keeps a copy of the first half ring behind the last live
-// slot (j = i + d never wraps) and stores the records as two float4 arrays [N + N/2] (x,y,alt,u | v,vs,ca,sa)
-__host__ __device__ constexpr int sym_row_recs(int N) { return N + N / 2; }
-template <typename R> __host__ __device__ constexpr size_t rec_row_bytes(int N) {
-    return (size_t)(sizeof(R) == 4 ? sym_row_recs(N) : N) * sizeof(typename RecOf<R>::type) + 16;
+// Per-env row of CD records in shared memory (double-buffered by substep parity).
+// fp64 / fp32 with N > 64: N records + 16 B, so that the rows of the envs sharing a warp start in different banks.
+// fp32 symmetric sweep (N <= 64): structure of arrays, one float array per record field, so that ONE LDS.64 hands the
+// packed f32x2 pair form the same field of two neighbouring partners {f[j], f[j+1]}.  LDS.64 wants j even, and thread i
+// sweeps j = i+1, i+3, ... : every field is therefore kept TWICE -- copy 0 holds f[k] at index k, copy 1 holds
+// f[k+1] at index k -- odd i read copy 0 at i+1, even i read copy 1 at i (both even indices).  Each copy is the ring
+// unrolled: the first N/2 + 1 records are repeated behind the last live slot, so j = i + d never wraps.  Copy 1
+// starts 18 banks off copy 0 (the even- and the odd-lane halves of a warp's LDS.64 then hit disjoint banks).  Field
+// 8 is the heading (resumenav's bouncing test), single copy, in the same double-buffered row.
+constexpr int kSoaFields = 8;                    // x, y, u, v, ca, sa, alt, vs
+enum { SF_X, SF_Y, SF_U, SF_V, SF_CA, SF_SA, SF_ALT, SF_VS };
+__host__ __device__ constexpr int soa_len(int N) { return (N + N / 2 + 3) & ~1; }             // floats per copy
+__host__ __device__ constexpr int soa_copy1(int N) { int c = soa_len(N); while ((c & 31) != 18) c += 2; return c; }
+__host__ __device__ constexpr int soa_fstride(int N) { return soa_copy1(N) + soa_len(N); }   // floats per field (even)
+__host__ __device__ constexpr size_t soa_row_bytes(int N) {
+    return (((size_t)kSoaFields * soa_fstride(N) + N + 1) & ~(size_t)1) * sizeof(float) + 16;
 }
-__device__ __forceinline__ RecFast rec_from(const float4 &a, const float4 &b) {
-    RecFast r; r.x = a.x; r.y = a.y; r.alt = a.z; r.u = a.w; r.v = b.x; r.vs = b.y; r.ca = b.z; r.sa = b.w; return r;
+template <typename R> __host__ __device__ constexpr size_t rec_row_bytes(int N) {
+    const size_t aos = (size_t)N * sizeof(typename RecOf<R>::type) + 16;
+    if (sizeof(R) == 4 && N <= 64) return soa_row_bytes(N) > aos ? soa_row_bytes(N) : aos;
+    return aos;
 }
 
 // shared-memory carve-up of one CTA (host and device agree through this one function)
@@ -62,19 +74,27 @@ template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int e
 // such an env; kept out of line so the step kernel's register allocation does not see it.  The ResetEnv scratch
 // aliases the (not yet used) record rows.
 template <typename R>
-static __device__ __noinline__ void fused_reset(int kind, int fixed_nac, int E, int N, unsigned long long seed, unsigned int *episode,
-                                                double *ev, int *nac, double *pos, R *st, unsigned long long *reso,
-                                                const ResetConst RC, unsigned char *smem_raw, bool skip, bool valid, int le, int i, int e) {
+static __device__ __noinline__ void fused_reset(int kind, int fixed_nac, int density_mode, int E, int N, int epb, unsigned long long seed,
+                                                unsigned int *episode, double *ev, int *nac, double *pos, R *st,
+                                                unsigned long long *reso, const ResetConst RC, unsigned char *smem_raw,
+                                                bool skip, bool valid, int le, int i, int e) {
     // (scalars by value: taking the address of the kernel's parameter struct would copy it to local memory)
     ResetEnv *rs = reinterpret_cast<ResetEnv *>(smem_raw);
+    double *wdraw = reinterpret_cast<double *>(rs + epb) + (size_t)le * 2 * N, *wsort = wdraw + N;   // Sector waypoints
     double *evr = ev + (size_t)(valid ? e : 0) * BSG_NE;
     const unsigned int ep = skip ? episode[e] : 0u;
     if (skip && i == 0) {
-        reset_env_level(kind, fixed_nac, N, e, seed, ep, evr, &rs[le], RC);
+        reset_env_level(kind, fixed_nac, density_mode, N, e, seed, ep, evr, &rs[le], RC);
         nac[e] = rs[le].nac;
     }
     __syncthreads();
-    if (skip) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &rs[le], evr, pos, st, reso, RC);
+    if (kind == BSG_KIND_SECTOR) {                       // uniform: every thread of the CTA is here
+        if (skip) reset_wpt_draw(e, i, seed, ep, &rs[le], wdraw);
+        __syncthreads();
+        if (skip) reset_wpt_rank(i, &rs[le], wdraw, wsort);
+        __syncthreads();
+    }
+    if (skip) reset_aircraft<R>(kind, E, N, e, i, seed, ep, &rs[le], wsort, evr, pos, st, reso, RC);
     __syncthreads();
     if (skip && i == 0) episode[e] = ep + 1;
 }
@@ -108,8 +128,8 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     const bool valid = le < epb && e < A.E;
     const bool skip = valid && A.skip && A.skip[e];                       // fresh episode: no action, no integration
     if (A.fuse_reset && __syncthreads_or(skip))                            // rare: some env of this CTA starts an episode
-        fused_reset<R>(A.kind, A.fixed_nac, A.E, A.N, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso, A.RC,
-                       smem_raw, skip, valid, le, i, e);
+        fused_reset<R>(A.kind, A.fixed_nac, A.density_mode, A.E, A.N, A.epb, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso,
+                       A.RC, smem_raw, skip, valid, le, i, e);
     const int nl = valid ? A.nac[e] : 0;
     const bool live = valid && i < nl;
     const size_t EN = (size_t)A.E * N, k = (size_t)(valid ? e : 0) * N + i;
@@ -177,6 +197,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     }
 
     RowAcc<R> acc;
+    const int FS = soa_fstride(N), C1 = soa_copy1(N);                      // SYM: floats per field, offset of copy 1
     // record rows of this env in the two substep buffers (hoisted: 64-bit address arithmetic out of the loop)
     unsigned char *const rb_even = recs + (size_t)le * rowb, *const rb_odd = rb_even + (size_t)epb * rowb;
     // ------------------------------------------------------------------ K substeps
@@ -184,18 +205,27 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         const int buf = s & 1;
         if (A.asas_on) {
             Rec *rb = reinterpret_cast<Rec *>(buf ? rb_odd : rb_even);
+            float *const srow = reinterpret_cast<float *>(buf ? rb_odd : rb_even);     // SYM: the SoA row of this env
+            RecFast me;                                                                // SYM: my own record
             if (live && !skip) {
-                if constexpr (SYM) {                  // SoA halves (conflict-free LDS.128) + ring copy behind slot nl
-                    RecFast r;
-                    make_rec<R>(a, lat0, lon0, r);
-                    float4 *wA = reinterpret_cast<float4 *>(rb), *wB = wA + sym_row_recs(N);
-                    const float4 ha = make_float4(r.x, r.y, r.alt, r.u), hb = make_float4(r.v, r.vs, r.ca, r.sa);
-                    wA[i] = ha; wB[i] = hb;
+                if constexpr (SYM) {                  // SoA fields, two copies each (+ the ring unrolled behind slot nl)
+                    make_rec<R>(a, lat0, lon0, me);
+                    const float fv[kSoaFields] = { me.x, me.y, me.u, me.v, me.ca, me.sa, me.alt, me.vs };
+                    const bool ring = i <= (nl >> 1);
+#pragma unroll
+                    for (int f = 0; f < kSoaFields; f++) {
+                        float *p0 = srow + f * FS + i, *p1 = p0 + (C1 - 1);            // copy 1 holds f[k + 1] at k
+                        p0[0] = fv[f];
+                        if (i > 0) p1[0] = fv[f];
+                        if (ring) { p0[nl] = fv[f]; p1[nl] = fv[f]; }
+                    }
+                    if (reso) srow[kSoaFields * FS + i] = a.hdg;                       // resumenav's bouncing test
                     // monotone within the launch: once any aircraft climbs, descends or leaves the common level
                     if (a.vs != 0.0f || !(fabsf(a.alt - alt_ref) < 0.5f * (float)A.P.hpz)) es[le].vneed = 1;
-                    if (i < (nl >> 1)) { wA[nl + i] = ha; wB[nl + i] = hb; }
-                } else make_rec<R>(a, lat0, lon0, rb[i]);
-                if (reso) sdist[le * N + i] = a.hdg;
+                } else {
+                    make_rec<R>(a, lat0, lon0, rb[i]);
+                    if (reso) sdist[le * N + i] = a.hdg;
+                }
             }
             __syncthreads();
             if (RESO && valid && i == 0) es[le].anyconf[buf ^ 1] = 0;
@@ -211,31 +241,63 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 // separates the readers of this substep from the next writers.
                 unsigned *hr = reinterpret_cast<unsigned *>(crow) + (size_t)le * 2 * N;
                 unsigned F = 0u;
-                const float4 *rA = reinterpret_cast<const float4 *>(rb), *rB = rA + sym_row_recs(N);
-                RecFast me;
+                // partner j of the row, any j < nl + H + 1 (copy 0)
+                auto rec_at = [&](int j) {
+                    RecFast o;
+                    const float *p = srow + j;
+                    o.x = p[SF_X * FS]; o.y = p[SF_Y * FS]; o.u = p[SF_U * FS]; o.v = p[SF_V * FS];
+                    o.ca = p[SF_CA * FS]; o.sa = p[SF_SA * FS]; o.alt = p[SF_ALT * FS]; o.vs = p[SF_VS * FS];
+                    return o;
+                };
                 if (live && !skip) {                            // phase 1: half ring, flags only
-                    me = rec_from(rA[i], rB[i]);
                     const int H = nl >> 1;
-                    const float4 *pA = rA + i, *pB = rB + i;    // ring copy behind slot nl: j = i + d needs no wrap
-                    // BSG_PW pairs per trip: straight-line FP32 code, the independent dependency chains interleave
-                    // (the pair body is latency-bound at 4-5 warps per scheduler)
-                    auto sweep = [&](auto vt) {
-                        constexpr bool V = decltype(vt)::value;
-                        // the sign bit of pair_fast_sign is the flag: one funnel shift per pair pushes it into G
-                        // (pair d ends at bit H-d); reversed into F (bit d-1) after the loop
+                    // level, co-altitude traffic (Horizontal and Sector envs): the vertical window is (-inf, inf) and the
+                    // sweep runs PACKED -- partners d, d+1 of one trip in the two halves of f32x2 registers (FFMA2 / FADD2
+                    // / FMUL2), one LDS.64 per field and trip; BSG_PG trips are interleaved (straight-line code, the
+                    // dependency chains overlap: the pair body is latency-bound at 4-5 warps per scheduler).
+                    // The sign bit of a margin is the flag: one funnel shift per pair pushes it into G (pair d ends at
+                    // bit nd-d); reversed into F (bit d-1) after the loop.
+                    if (!es[le].vneed) {
+                        const int Q = (H + 1) >> 1;             // trips: partners d = 2q+1, 2q+2 (the last may run one past H)
+                        const f32x2 *g = reinterpret_cast<const f32x2 *>(srow + ((i & 1) ? i + 1 : C1 + i));
+                        Rec2 m2;
+                        m2.x = pk2(me.x, me.x); m2.y = pk2(me.y, me.y); m2.u = pk2(me.u, me.u); m2.v = pk2(me.v, me.v);
+                        m2.ca = pk2(me.ca, me.ca); m2.sa = pk2(me.sa, me.sa);
+                        Cd2 C;
+                        C.R2 = pk2(PF.R2, PF.R2); C.c1em6 = pk2(1e-6f, 1e-6f); C.ndtlook = pk2(-PF.dtlook, -PF.dtlook);
+                        const int FH = FS >> 1;
+                        auto trip = [&](int q, unsigned &G) {
+                            const f32x2 *p = g + q;
+                            Rec2 o;
+                            o.x = p[SF_X * FH]; o.y = p[SF_Y * FH]; o.u = p[SF_U * FH]; o.v = p[SF_V * FH];
+                            o.ca = p[SF_CA * FH]; o.sa = p[SF_SA * FH];
+                            float lo, hi;
+                            pair_fast_sign2(m2, o, C, lo, hi);
+                            G = __funnelshift_l(__float_as_uint(lo), G, 1);
+                            G = __funnelshift_l(__float_as_uint(hi), G, 1);
+                        };
+                        int q = 0;
+                        unsigned G = 0u;
+                        for (; q + (BSG_PG - 1) < Q; q += BSG_PG) {
+#pragma unroll
+                            for (int u = 0; u < BSG_PG; u++) trip(q + u, G);
+                        }
+#pragma unroll 1
+                        for (; q < Q; q++) trip(q, G);
+                        F = H > 0 ? (__brev(G) >> (32 - 2 * Q)) & ((1u << H) - 1u) : 0u;
+                    } else {                                    // generic vertical window: scalar form, BSG_PW pairs per trip
                         int d = 1;
                         unsigned G = 0u;
                         for (; d + (BSG_PW - 1) <= H; d += BSG_PW) {
 #pragma unroll
-                            for (int q = 0; q < BSG_PW; q++)
-                                G = __funnelshift_l(__float_as_uint(pair_fast_sign<V>(me, rec_from(pA[d + q], pB[d + q]), PF)), G, 1);
+                            for (int u = 0; u < BSG_PW; u++)
+                                G = __funnelshift_l(__float_as_uint(pair_fast_sign<true>(me, rec_at(i + d + u), PF)), G, 1);
                         }
+#pragma unroll 1
                         for (; d <= H; d++)
-                            G = __funnelshift_l(__float_as_uint(pair_fast_sign<V>(me, rec_from(pA[d], pB[d]), PF)), G, 1);
+                            G = __funnelshift_l(__float_as_uint(pair_fast_sign<true>(me, rec_at(i + d), PF)), G, 1);
                         F = H > 0 ? __brev(G) >> (32 - H) : 0u;
-                    };
-                    // level, co-altitude traffic (Horizontal and Sector envs): the vertical window is (-inf, inf)
-                    if (es[le].vneed) sweep(std::true_type{}); else sweep(std::false_type{});
+                    }
                     hr[i] = F; hr[i + nl] = F;
                     if (RESO && F) es[le].anyconf[buf] = 1;
                 }
@@ -272,11 +334,12 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     const unsigned long long cr = fwd | back;
                     const unsigned long long notme = ~(1ull << i);
                     const float R2f = PF.rpz * PF.rpz, R2b = R2f * (float)(A.P.fach * A.P.fach);
-                    // resumenav test of one resolving pair (squared distances; the same expressions as pair_fast_core)
-                    auto resume = [&](int j, unsigned long long jb, float dx, float dy, float dist2, float dot) {
+                    const float *hdgrow = srow + kSoaFields * FS;
+                    // resumenav test of one resolving pair (squared distances; the canonical pair quantities)
+                    auto resume = [&](int j, unsigned long long jb, float dist2, float dot) {
                         const bool past = dot > 0.0f;
                         bool kp = !past || dist2 < R2f;
-                        if (!kp && dist2 < R2b) kp = fabsf(a.hdg - sdist[le * N + j]) < 30.0f;   // bouncing (rare)
+                        if (!kp && dist2 < R2b) kp = fabsf(a.hdg - hdgrow[j]) < 30.0f;      // bouncing (rare)
                         touched = true;
                         if (kp) { active = true; keep |= jb; }
                     };
@@ -288,23 +351,16 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                         const int j = __ffsll((long long)S) - 1;
                         const unsigned long long jb = S & (0ull - S);        // lowest set bit (no 64-bit shift by j)
                         S ^= jb;
-                        const RecFast o = rec_from(rA[j], rB[j]);
-                        if (want_acc) {
-                            PairCore pc;
-                            pair_fast_core(me, o, PF, true, pc);
+                        const RecFast o = rec_at(j);
+                        PairCore pc;
+                        pair_fast_core(me, o, PF, true, pc);
+                        if (want_acc)
                             acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
-                        }
                         if constexpr (RESO) {
-                            const float dy = o.y - me.y;
-                            const float dx = (o.x - me.x) * fmaf(me.ca, o.ca, -(me.sa * o.sa));
-                            const float dist2 = fmaf(dx, dx, dy * dy);
-                            const float vrx = o.u - me.u, vry = o.v - me.v;
-                            const float dot = fmaf(vrx, dx, vry * dy);
-                            const float tcpa = -dot * rcp_approx(fmaf(vrx, vrx, fmaf(vry, vry, 1e-6f)));
                             float d1, d2;
-                            mvp_pair_fast(dx, dy, dist2, tcpa, vrx, vry, PF.rpz_m, d1, d2);
+                            mvp_pair_fast(pc.dx, pc.dy, pc.dist2, pc.tcpa, pc.du, pc.dv, PF.rpz_m, d1, d2);
                             dve = dve - d1; dvn = dvn - d2;
-                            resume(j, jb, dx, dy, dist2, dot);
+                            resume(j, jb, pc.dist2, pc.dot);
                         }
                     }
                     if constexpr (RESO) {
@@ -313,12 +369,9 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                             const int j = __ffsll((long long)S) - 1;
                             const unsigned long long jb = S & (0ull - S);
                             S ^= jb;
-                            const RecFast o = rec_from(rA[j], rB[j]);
-                            const float dy = o.y - me.y;
-                            const float dx = (o.x - me.x) * fmaf(me.ca, o.ca, -(me.sa * o.sa));
-                            const float dist2 = fmaf(dx, dx, dy * dy);
-                            const float vrx = o.u - me.u, vry = o.v - me.v;
-                            resume(j, jb, dx, dy, dist2, fmaf(vrx, dx, vry * dy));
+                            float dist2, dot;
+                            pair_fast_geom(me, rec_at(j), dist2, dot);
+                            resume(j, jb, dist2, dot);
                         }
                     }
                     if (RESO && A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }   // RESOOFF: the agent does not resolve

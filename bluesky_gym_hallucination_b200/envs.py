@@ -63,9 +63,8 @@ class SectorCREnv(_SingleEnv):
     ENV_ID = 'SectorCREnv-v0'
 
     def __init__(self, render_mode=None, ac_density_mode="normal", **kw):
-        if ac_density_mode != "normal":
-            raise NotImplementedError("the device generator implements the reference's default 'normal' density law")
-        super().__init__(render_mode=render_mode, **kw)
+        self.density_mode = ac_density_mode                              # sector_cr_env.py:47
+        super().__init__(render_mode=render_mode, ac_density_mode=ac_density_mode, **kw)
 
 
 class MergeEnv(_SingleEnv):

@@ -171,7 +171,10 @@ def sector(E, N, seed=0, n_poly=64, fixed_n=True):
         # waypoints on the perimeter (sector_cr_env.py:162-188), sorted per env like the reference's d_list
         seg = np.linalg.norm(np.roll(p, -1, 0) - p, axis=1)
         cum = np.concatenate([[0], np.cumsum(seg)])
-        d = np.sort(rng.random((ne, N)) * cum[-1], axis=1)
+        d = rng.random((ne, N)) * cum[-1]
+        d[np.arange(N)[None, :] >= nac[envs][:, None]] = np.inf          # only the num_ac live aircraft draw (and sort)
+        d = np.sort(d, axis=1)
+        d[~np.isfinite(d)] = 0.0
         k = np.clip(np.searchsorted(cum, d, side='right') - 1, 0, nv - 1)
         frac = (d - cum[k]) / seg[k]
         wp = p[k] + frac[..., None] * (np.roll(p, -1, 0)[k] - p[k])

@@ -45,9 +45,13 @@ class BlueSkyVecEnv:
     metadata = {"render_modes": [], "autoreset_mode": "next_step"}
 
     def __init__(self, env_id, num_envs, num_aircraft=None, device=0, precision='fp32', asas=False, mvp=False,
-                 seed=0, cd_outputs=False, max_episode_steps=None, wind=None, wind_obs=False, obs_noise=0.0):
+                 seed=0, cd_outputs=False, max_episode_steps=None, wind=None, wind_obs=False, obs_noise=0.0,
+                 ac_density_mode='normal', fixed_nac=False):
         """wind = (lat, lon, vnorth, veast) like WindFieldWrapper(env, lat, lon, vnorth, veast, augment_obs=wind_obs);
-        obs_noise = NoisyObservationWrapper(env, noise_level)."""
+        obs_noise = NoisyObservationWrapper(env, noise_level); ac_density_mode = SectorCREnv's "normal" | "uniform"
+        (sector_cr_env.py:45,98-103); fixed_nac = every aircraft slot live (the synthetic scale-up configs)."""
+        if ac_density_mode not in ('normal', 'uniform'):
+            raise ValueError(f"ac_density_mode must be 'normal' or 'uniform', not {ac_density_mode!r}")
         if env_id not in ENV_SPECS:
             raise ValueError(f"unknown env id {env_id!r}; the batched core covers {sorted(ENV_SPECS)}")
         kind, n_ref, max_steps, act_dim = ENV_SPECS[env_id]
@@ -56,7 +60,7 @@ class BlueSkyVecEnv:
         self.core = BsgCore(kind, self.num_envs, self.num_aircraft, precision=precision, device=device,
                             asas_on=asas or mvp, reso_on=mvp, reso_off_own=mvp,
                             max_episode_steps=max_steps if max_episode_steps is None else max_episode_steps,
-                            cd_outputs=cd_outputs)
+                            cd_outputs=cd_outputs, density_mode=ac_density_mode, fixed_nac=fixed_nac)
         if wind is not None:
             self.core.set_wind(*wind, augment_obs=wind_obs)
         if obs_noise:

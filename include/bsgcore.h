@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define BSG_ABI_VERSION 2
+#define BSG_ABI_VERSION 3
 
 typedef enum { BSG_OK = 0, BSG_ERR_ARG = -1, BSG_ERR_CUDA = -2, BSG_ERR_NOMEM = -3, BSG_ERR_UNSUPPORTED = -4,
                BSG_ERR_NODEVICE = -5 } bsg_status;
@@ -71,6 +71,9 @@ typedef struct bsg_config {
     int32_t device;           /* CUDA device ordinal */
     int32_t fixed_nac;        /* Sector reset: 1 = every env gets exactly max_ac aircraft (the synthetic scale-up
                                  configs, SURVEY 8d C3 "N fixed"); 0 = the reference's density law (sector_cr_env.py:98-100) */
+    int32_t density_mode;     /* Sector reset, SectorCREnv(ac_density_mode=...) (sector_cr_env.py:45,98-103): 0 = "normal"
+                                 N(0.005, 0.001) aircraft per NM^2, 1 = "uniform" U(0.003, 0.007) */
+    int32_t reserved0;        /* keeps the doubles 8-aligned; must be 0 */
     double simdt;             /* 0 = the reference's DT for env_kind (5/1/1 s) */
     double rpz_m, hpz_m;      /* protected zone; 0 = 5 NM / 1000 ft */
     double dtlookahead;       /* 0 = 300 s */
@@ -204,9 +207,22 @@ int bsg_cd_sym_finalize_peers(const bsg_cd_params *p, const bsg_cd_peers *peers,
                               int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev, float *near_tin_dev,
                               void *stream);
 
-/* ND-map: rec_dev float [E][6][n] (x, y, z, u, v, w); occ/conf uint8 [E][nt][nz][ny][nx]; ncell int32 [E][nt] */
-int bsg_ndmap(const bsg_ndmap_params *p, const float *rec_dev, uint8_t *occ_dev, uint8_t *conf_dev,
+/* ND-map (4D spatial-temporal conflict grid over straight-line look-ahead trajectories; builder-owned spec):
+ * rec_dev float [E][6][n] (x, y, z [m], u, v, w [m/s]); occ uint8 [E][nt][nz][ny][nx] = min(count, 255);
+ * conf_bits = 1 bit per cell, [E][nt][cells / 8] bytes, cell c of a slab <-> bit (c & 7) of byte (c >> 3) (c = (z ny + y) nx
+ * + x): set where the 3x3x3 neighbourhood of the cell, clipped at the faces, holds >= 2 aircraft; ncell int32 [E][nt] =
+ * number of set bits.  nx in {32, 64, 128}; nx ny nz a multiple of 128 and <= 77 K cells (one slab lives in shared
+ * memory).  bsg_ndmap_unpack expands the bits to one 0/1 byte per cell. */
+int bsg_ndmap(const bsg_ndmap_params *p, const float *rec_dev, uint8_t *occ_dev, uint8_t *conf_bits_dev,
               int32_t *ncell_dev, void *stream);
+int bsg_ndmap_unpack(const bsg_ndmap_params *p, const uint8_t *conf_bits_dev, uint8_t *conf_bytes_dev, void *stream);
+/* The same map over the LIVE state of a handle (p->num_envs / num_ac = the handle's): the records are the aircraft's
+ * current position, flat-earth offsets from (lat0, lon0) scaled by the caller's metres per degree, altitude, and the
+ * ground-speed vector / vertical speed; slots beyond an env's live aircraft are dropped.  rec_out_dev (may be NULL)
+ * receives the packed records [E][6][n] the map was built from. */
+typedef struct bsg_ndmap_geo { double lat0, lon0, m_per_deg_lat, m_per_deg_lon; } bsg_ndmap_geo;
+int bsg_ndmap_state(bsg_handle *h, const bsg_ndmap_params *p, const bsg_ndmap_geo *geo, uint8_t *occ_dev,
+                    uint8_t *conf_bits_dev, int32_t *ncell_dev, float *rec_out_dev, void *stream);
 
 /* FMA-chain micro-benchmarks: the measured FP32 / FP64 (non-tensor) roofline denominators */
 int bsg_peak_fp32(int device, int iters, double *tflops, double *ms);

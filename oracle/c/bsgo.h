@@ -82,10 +82,26 @@ void bsgo_cd_rows(int E, int n, const double *lat, const double *lon, const doub
                   double rpz, double hpz, double dtlook, int row0, int row1,
                   bsgo_cdout out, int nthreads);
 
+/* same, plus the near-threshold enumeration without dense matrices: near_conf / near_los [E][n] (may be NULL) flag the
+ * rows that hold a pair whose relative margin to a conflict / LoS threshold is below eps */
+void bsgo_cd_rows_near(int E, int n, const double *lat, const double *lon, const double *alt,
+                       const double *trk, const double *gs, const double *vs,
+                       double rpz, double hpz, double dtlook, int row0, int row1,
+                       bsgo_cdout out, double eps, uint8_t *near_conf, uint8_t *near_los, int nthreads);
+
 /* K traffic substeps (+CD/MVP when enabled) then the env layer, for E envs */
 void bsgo_step(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, const int32_t *nac, double *ev,
                const double *actions, double *obs, double *reward, int32_t *term, int32_t *trunc,
                bsgo_cdout cd, int nthreads);
+/* same step with a trace for the parity tests (any trace pointer may be NULL): near_conf / near_los [E][N] = rows holding a
+ * pair within eps of a conflict / LoS threshold at the LAST detection of the step; res_margin [E][N] = per ownship, the
+ * smallest relative margin over all substeps of the decisions that steer its resolution (conflict flags, MVP's 10 m
+ * switch and erratum branch, resumenav's tests; 0 = a degenerate equal-velocity conflict pair); kappa [E][N] = per
+ * ownship, MVP's largest amplification of a relative input rounding [m/s] (bsgo_int.h: bsgo_trace) */
+void bsgo_step_trace(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, const int32_t *nac, double *ev,
+                     const double *actions, double *obs, double *reward, int32_t *term, int32_t *trunc,
+                     bsgo_cdout cd, double eps, uint8_t *near_conf, uint8_t *near_los, double *res_margin, double *kappa,
+                     int nthreads);
 /* obs/info only (what reset() returns) */
 void bsgo_observe(const bsgo_cfg *cfg, int E, const double *ac, const int32_t *nac, double *ev, double *obs);
 

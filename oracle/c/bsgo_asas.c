@@ -7,10 +7,12 @@
 #include <string.h>
 #include "bsgo_int.h"
 
+static double relm(double a, double b) { double s = fmax(fabs(a), fabs(b)); return s > 0 ? fabs(a - b) / s : 0.0; }
+
 static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
                      double alt1, double alt2, const double v1[3], const double v2[3],
                      double rpz, double hpz, double dtlook, double fach, double facv,
-                     double dv[3], double *tsolV_o) {
+                     double dv[3], double *tsolV_o, bsgo_trace *tr) {
     double rpz_m = rpz * fach, hpz_m = hpz * facv;
     double q = qdr * C_D2R;
     double drel[3] = { sin(q) * dist, cos(q) * dist, alt2 - alt1 };
@@ -18,6 +20,15 @@ static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
     double dcpa[3] = { drel[0] + vrel[0] * tcpa, drel[1] + vrel[1] * tcpa, drel[2] + vrel[2] * tcpa };
     double dabsH = sqrt(dcpa[0] * dcpa[0] + dcpa[1] * dcpa[1]);
     double iH = rpz_m - dabsH;
+    if (tr) {
+        const int i = tr->row;
+        double vr2 = vrel[0] * vrel[0] + vrel[1] * vrel[1], vr = sqrt(vr2);
+        double k = (dist + vr * fabs(tcpa)) * rpz_m / (fmax(fabs(tcpa), 1e-3) * (dabsH <= 10.0 ? dist : dabsH));
+        if (tr->kappa && !(k <= tr->kappa[i])) tr->kappa[i] = k;            /* NaN sticks */
+        double m = fmin(relm(dabsH, 10.0), relm(rpz_m, dist));
+        if (vr2 < 1e-4) m = 0.0;                                            /* degenerate pair */
+        if (tr->res_margin && m < tr->res_margin[i]) tr->res_margin[i] = m;
+    }
     if (dabsH <= 10.0) {
         dabsH = 10.0;
         dcpa[0] = drel[1] / dist * dabsH;
@@ -41,7 +52,15 @@ static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
 }
 
 void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bsgo_row *rows) {
+    bsgo_asas_env_trace(cfg, a, reso, nlive, rows, 0);
+}
+
+void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bsgo_row *rows, bsgo_trace *tr) {
     int n = cfg->n;
+    if (tr) {
+        if (tr->near_conf) memset(tr->near_conf, 0, n);
+        if (tr->near_los) memset(tr->near_los, 0, n);
+    }
 #define A(f, i) a[(f) * n + (i)]
     double *u = malloc(sizeof(double) * nlive * 5);
     double *v = u + nlive, *dve = v + nlive, *dvn = dve + nlive, *dvz = dvn + nlive;
@@ -62,11 +81,16 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
         double v1[3] = { u[i], v[i], A(F_VS, i) };
         for (int j = 0; j < nlive; j++) {
             if (j == i) continue;
-            double qdr, dist, tcpa, dcpa2, tin;
+            double qdr, dist, tcpa, dcpa2, tin, mc = 1e30, ml = 1e30;
             int sw, los;
             bsgo_pair(A(F_LAT, i), A(F_LON, i), A(F_ALT, i), u[i], v[i], A(F_VS, i),
                       A(F_LAT, j), A(F_LON, j), A(F_ALT, j), u[j], v[j], A(F_VS, j),
-                      cfg->rpz, cfg->hpz, cfg->dtlook, &qdr, &dist, &tcpa, &dcpa2, &tin, 0, &sw, &los, 0, 0);
+                      cfg->rpz, cfg->hpz, cfg->dtlook, &qdr, &dist, &tcpa, &dcpa2, &tin, 0, &sw, &los, tr ? &mc : 0, tr ? &ml : 0);
+            if (tr) {
+                if (mc < tr->eps && tr->near_conf) tr->near_conf[i] = 1;
+                if (ml < tr->eps && tr->near_los) tr->near_los[i] = 1;
+                if (cfg->reso_on && tr->res_margin && mc < tr->res_margin[i]) tr->res_margin[i] = mc;
+            }
             if (los) r->nlos++;
             if (!sw) continue;
             anyconf = 1;
@@ -79,8 +103,9 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
             if (cfg->reso_on) {
                 double v2[3] = { u[j], v[j], A(F_VS, j) };
                 double dv[3], tsolV;
+                if (tr) tr->row = i;
                 mvp_pair(qdr, dist, tcpa, tin, A(F_ALT, i), A(F_ALT, j), v1, v2,
-                         cfg->rpz, cfg->hpz, cfg->dtlook, cfg->resofach, cfg->resofacv, dv, &tsolV);
+                         cfg->rpz, cfg->hpz, cfg->dtlook, cfg->resofach, cfg->resofacv, dv, &tsolV, tr);
                 dv[2] = 0.5 * dv[2];
                 dve[i] = dve[i] - dv[0]; dvn[i] = dvn[i] - dv[1]; dvz[i] = dvz[i] - dv[2];
                 if (cfg->reso_off_own && i == 0) { dve[i] = 0.0; dvn[i] = 0.0; dvz[i] = 0.0; }
@@ -117,6 +142,17 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
                 double hdist = sqrt(dx * dx + dy * dy);
                 int hor_los = hdist < cfg->rpz;
                 int bouncing = fabs(A(F_HDG, i) - A(F_HDG, j)) < 30.0 && hdist < cfg->rpz * cfg->resofach;
+                if (tr) {
+                    double vv = sqrt(vx * vx + vy * vy);
+                    /* |cos| of (r, v_rel): the past-CPA sign; identical velocity vectors give an exact 0 in any precision */
+                    double m = vv > 0.0 ? fabs(dx * vx + dy * vy) / fmax(hdist * vv, 1e-300) : 1e30;
+                    m = fmin(m, relm(hdist, cfg->rpz));
+                    if (past_cpa && !hor_los) {
+                        m = fmin(m, relm(hdist, cfg->rpz * cfg->resofach));
+                        if (hdist < cfg->rpz * cfg->resofach * (1 + tr->eps)) m = fmin(m, relm(fabs(A(F_HDG, i) - A(F_HDG, j)), 30.0));
+                    }
+                    if (tr->res_margin && m < tr->res_margin[i]) tr->res_margin[i] = m;
+                }
                 if (!past_cpa || hor_los || bouncing) { active = 1; keep |= (uint64_t)1 << j; }
             }
             if (touched) A(F_ASAS_ACTIVE, i) = active ? 1.0 : 0.0;

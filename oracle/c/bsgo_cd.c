@@ -108,29 +108,49 @@ static void row_add(bsgo_row *r, int j, int sw, int los, double tcpa, double dcp
     }
 }
 
+/* near_conf / near_los (may be NULL): [E][n] flags, row i holds a pair whose margin to a conflict / LoS threshold is
+ * below eps -- the enumeration of near-threshold pairs without the dense n x n matrices (giant airspaces) */
+void bsgo_cd_rows_near(int E, int n, const double *lat, const double *lon, const double *alt,
+                       const double *trk, const double *gs, const double *vs,
+                       double rpz, double hpz, double dtlook, int row0, int row1,
+                       bsgo_cdout out, double eps, uint8_t *near_conf, uint8_t *near_los, int nthreads);
+
 void bsgo_cd_rows(int E, int n, const double *lat, const double *lon, const double *alt,
                   const double *trk, const double *gs, const double *vs,
                   double rpz, double hpz, double dtlook, int row0, int row1,
                   bsgo_cdout out, int nthreads) {
+    bsgo_cd_rows_near(E, n, lat, lon, alt, trk, gs, vs, rpz, hpz, dtlook, row0, row1, out, 0.0, 0, 0, nthreads);
+}
+
+void bsgo_cd_rows_near(int E, int n, const double *lat, const double *lon, const double *alt,
+                       const double *trk, const double *gs, const double *vs,
+                       double rpz, double hpz, double dtlook, int row0, int row1,
+                       bsgo_cdout out, double eps, uint8_t *near_conf, uint8_t *near_los, int nthreads) {
     if (nthreads < 1) nthreads = 1;
+    const int want_near = near_conf || near_los;
 #pragma omp parallel for num_threads(nthreads) schedule(dynamic, 16) collapse(2)
     for (int e = 0; e < E; e++)
         for (int i = row0; i < row1; i++) {
             size_t b = (size_t)e * n;
             bsgo_row r;
             row_init(&r);
+            int nc = 0, nl = 0;
             double ui = gs[b + i] * sin(trk[b + i] * C_D2R), vi = gs[b + i] * cos(trk[b + i] * C_D2R);
             for (int j = 0; j < n; j++) {
                 if (j == i) continue;
                 double uj = gs[b + j] * sin(trk[b + j] * C_D2R), vj = gs[b + j] * cos(trk[b + j] * C_D2R);
-                double t, d2, ti;
+                double t, d2, ti, mc = 1e30, ml = 1e30;
                 int sw, lo;
                 bsgo_pair(lat[b + i], lon[b + i], alt[b + i], ui, vi, vs[b + i],
                           lat[b + j], lon[b + j], alt[b + j], uj, vj, vs[b + j],
-                          rpz, hpz, dtlook, 0, 0, &t, &d2, &ti, 0, &sw, &lo, 0, 0);
+                          rpz, hpz, dtlook, 0, 0, &t, &d2, &ti, 0, &sw, &lo, want_near ? &mc : 0, want_near ? &ml : 0);
                 row_add(&r, j, sw, lo, t, d2, ti);
+                if (mc < eps) nc = 1;
+                if (ml < eps) nl = 1;
             }
             size_t k = b + i;
+            if (near_conf) near_conf[k] = (uint8_t)nc;
+            if (near_los) near_los[k] = (uint8_t)nl;
             if (out.inconf) out.inconf[k] = r.inconf;
             if (out.nconf) out.nconf[k] = r.nconf;
             if (out.nlos) out.nlos[k] = r.nlos;

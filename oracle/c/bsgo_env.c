@@ -311,7 +311,15 @@ void bsgo_observe(const bsgo_cfg *cfg, int E, const double *ac, const int32_t *n
 void bsgo_step(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, const int32_t *nac, double *ev,
                const double *actions, double *obs, double *reward, int32_t *term, int32_t *trunc,
                bsgo_cdout cd, int nthreads) {
+    bsgo_step_trace(cfg, E, ac, reso, nac, ev, actions, obs, reward, term, trunc, cd, 0.0, 0, 0, 0, 0, nthreads);
+}
+
+void bsgo_step_trace(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, const int32_t *nac, double *ev,
+                     const double *actions, double *obs, double *reward, int32_t *term, int32_t *trunc,
+                     bsgo_cdout cd, double eps, uint8_t *near_conf, uint8_t *near_los, double *res_margin, double *kappa,
+                     int nthreads) {
     int n = cfg->n, od = bsgo_obs_dim_cfg(cfg);
+    const int want_tr = near_conf || near_los || res_margin || kappa;
     int na = (cfg->kind == KIND_S || cfg->kind == KIND_M) ? 2 : 1;
     if (nthreads < 1) nthreads = 1;
 #pragma omp parallel for num_threads(nthreads) schedule(dynamic, 8)
@@ -324,8 +332,11 @@ void bsgo_step(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, const int
         memset(rows, 0, sizeof(bsgo_row) * n);
         for (int i = 0; i < n; i++) rows[i].near_idx = -1;
         if (cfg->kind != KIND_RAW && actions) apply_action(cfg, a, v, actions + (size_t)e * na);
+        bsgo_trace trc = { eps, near_conf ? near_conf + (size_t)e * n : 0, near_los ? near_los + (size_t)e * n : 0,
+                           res_margin ? res_margin + (size_t)e * n : 0, kappa ? kappa + (size_t)e * n : 0, 0 };
+        for (int i = 0; i < n; i++) { if (trc.res_margin) trc.res_margin[i] = 1e30; if (trc.kappa) trc.kappa[i] = 0.0; }
         for (int s = 0; s < cfg->substeps; s++) {
-            if (cfg->asas_on) bsgo_asas_env(cfg, a, rs, nl, rows);
+            if (cfg->asas_on) bsgo_asas_env_trace(cfg, a, rs, nl, rows, want_tr ? &trc : 0);
             for (int i = 0; i < nl; i++) bsgo_kin_substep(cfg, a, v, n, i, cfg->simdt, cfg->reso_on && cfg->asas_on);
         }
         double rew = 0;

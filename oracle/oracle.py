@@ -120,6 +120,22 @@ def step(cfg, ac, reso, nac, ev, actions, nthreads=1):
     return obs, rew, term, trunc, cd
 
 
+def step_trace(cfg, ac, reso, nac, ev, actions, eps, nthreads=1):
+    """step() plus the trace the parity tests enumerate from: returns (obs, rew, term, trunc, cd, trace) with
+    trace = dict(near_conf, near_los [E,N] bool, res_margin, kappa [E,N]) -- see oracle/c/bsgo.h."""
+    E = ac.shape[0]
+    od = obs_dim_cfg(cfg)
+    obs = np.zeros((E, od)); rew = np.zeros(E); term = np.zeros(E, np.int32); trunc = np.zeros(E, np.int32)
+    cd = new_cdout(E, cfg.n)
+    nc = np.zeros((E, cfg.n), np.uint8); nl = np.zeros((E, cfg.n), np.uint8)
+    rm = np.zeros((E, cfg.n)); kp = np.zeros((E, cfg.n))
+    act = None if actions is None else np.ascontiguousarray(actions, dtype=np.float64)
+    lib().bsgo_step_trace(C.byref(cfg), C.c_int(E), _p(ac), _p(reso), _p(nac), _p(ev), _p(act), _p(obs), _p(rew),
+                          _p(term), _p(trunc), _cdstruct(cd), C.c_double(eps), _p(nc), _p(nl), _p(rm), _p(kp),
+                          C.c_int(nthreads))
+    return obs, rew, term, trunc, cd, dict(near_conf=nc.astype(bool), near_los=nl.astype(bool), res_margin=rm, kappa=kp)
+
+
 def observe(cfg, ac, nac, ev):
     E = ac.shape[0]
     obs = np.zeros((E, obs_dim_cfg(cfg)))
@@ -136,6 +152,19 @@ def cd_rows(lat, lon, alt, trk, gs, vs, rpz=5 * NM, hpz=1000 * FT, dtlook=300.0,
     lib().bsgo_cd_rows(C.c_int(E), C.c_int(n), *[_p(a) for a in arrs], C.c_double(rpz), C.c_double(hpz),
                        C.c_double(dtlook), C.c_int(row0), C.c_int(row1), _cdstruct(cd), C.c_int(nthreads))
     return cd
+
+
+def cd_rows_near(lat, lon, alt, trk, gs, vs, eps, rpz=5 * NM, hpz=1000 * FT, dtlook=300.0, nthreads=1):
+    """cd_rows plus the near-threshold enumeration: (cd, near_conf [E,N] u8, near_los [E,N] u8) -- row i holds a pair
+    whose relative margin to a conflict / LoS threshold is below eps (no dense N x N matrices: giant airspaces)."""
+    E, n = lat.shape
+    cd = new_cdout(E, n)
+    nc = np.zeros((E, n), np.uint8); nl = np.zeros((E, n), np.uint8)
+    arrs = [np.ascontiguousarray(a, dtype=np.float64) for a in (lat, lon, alt, trk, gs, vs)]
+    lib().bsgo_cd_rows_near(C.c_int(E), C.c_int(n), *[_p(a) for a in arrs], C.c_double(rpz), C.c_double(hpz),
+                            C.c_double(dtlook), C.c_int(0), C.c_int(n), _cdstruct(cd), C.c_double(eps), _p(nc), _p(nl),
+                            C.c_int(nthreads))
+    return cd, nc, nl
 
 
 def detect_dense(lat, lon, alt, trk, gs, vs, rpz=5 * NM, hpz=1000 * FT, dtlook=300.0):

@@ -125,12 +125,72 @@ def test_ndmap_bit_exact(orc, E, n):
     rec[:, 5] = rng.choice([-10.0, 0.0, 10.0], (E, n))
     kw = dict(nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=3048.0, cx=4630.0, cy=4630.0, cz=304.8 * 4, dt=10.0)
     occ, conf, ncell = orc.ndmap(rec, nthreads=8, **kw)
-    g_occ, g_conf, g_ncell = core.ndmap(torch.as_tensor(rec, device='cuda'), **kw)
+    g_occ, g_bits, g_ncell = core.ndmap(torch.as_tensor(rec, device='cuda'), **kw)
+    g_conf = core.ndmap_unpack(g_bits)
     torch.cuda.synchronize()
-    assert occ.sum() > 0
+    assert occ.sum() > 0 and conf.sum() > 0
     assert np.array_equal(g_occ.cpu().numpy(), occ)
     assert np.array_equal(g_conf.cpu().numpy(), conf)
     assert np.array_equal(g_ncell.cpu().numpy(), ncell)
+    # the bitmask itself: cell c of a slab <-> bit c & 7 of byte c >> 3 (numpy little-endian bit order)
+    assert np.array_equal(g_bits.cpu().numpy(), np.packbits(conf.reshape(E, 30, -1), axis=-1, bitorder='little'))
+
+
+@pytest.mark.parametrize('nx,ny,nz,n', [(32, 16, 4, 40), (128, 24, 4, 300), (64, 64, 8, 700), (64, 32, 2, 300)])
+def test_ndmap_grids_and_saturation(orc, nx, ny, nz, n):
+    """Other grid shapes (rows of 1 / 2 / 4 words), more aircraft than CTA threads (records re-read from memory), and the
+    saturating counters: > 255 aircraft parked in ONE cell must give occ == 255 there and leave its neighbours alone."""
+    from bluesky_gym_hallucination_b200 import core
+    E, nt = 2, 5
+    rng = np.random.default_rng(3)
+    rec = np.zeros((E, 6, n), np.float32)
+    rec[:, 0] = rng.uniform(0, nx * 1000.0, (E, n)); rec[:, 1] = rng.uniform(0, ny * 1000.0, (E, n))
+    rec[:, 2] = rng.uniform(0, nz * 300.0, (E, n))
+    rec[:, 3] = rng.uniform(-200, 200, (E, n)); rec[:, 4] = rng.uniform(-200, 200, (E, n))
+    if n >= 300:                        # 280 aircraft flying in formation inside one cell, away from the faces
+        rec[0, 0, :280] = 5500.0; rec[0, 1, :280] = 5500.0; rec[0, 2, :280] = 450.0 if nz > 2 else 150.0
+        rec[0, 3, :280] = 10.0; rec[0, 4, :280] = -10.0; rec[0, 5, :280] = 0.0
+    kw = dict(nx=nx, ny=ny, nz=nz, nt=nt, x0=0.0, y0=0.0, z0=0.0, cx=1000.0, cy=1000.0, cz=300.0, dt=10.0)
+    occ, conf, ncell = orc.ndmap(rec, nthreads=4, **kw)
+    g_occ, g_bits, g_ncell = core.ndmap(torch.as_tensor(rec, device='cuda'), **kw)
+    g_conf = core.ndmap_unpack(g_bits, nx=nx, ny=ny, nz=nz)
+    torch.cuda.synchronize()
+    if n >= 300:
+        assert occ.max() == 255
+    assert np.array_equal(g_occ.cpu().numpy(), occ)
+    assert np.array_equal(g_conf.cpu().numpy(), conf)
+    assert np.array_equal(g_ncell.cpu().numpy(), ncell)
+
+
+def test_ndmap_of_live_state(orc):
+    """bsg_ndmap_state: the map of a handle's LIVE traffic (Sector envs with the density law: dead slots are dropped)
+    equals the oracle's map of the records the call reports, and those records are the state's positions / velocities."""
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    from bluesky_gym_hallucination_b200 import core, _lib as L
+    E, N = 48, 50
+    c = BsgCore(L.KIND_SECTOR, E, N, precision='fp32', asas_on=True)
+    c.reset(seed=3)
+    c.step(torch.zeros((E, 2), dtype=torch.float32, device='cuda'))
+    kw = dict(nx=64, ny=64, nz=8, nt=30, x0=-110e3, y0=-90e3, z0=-1000.0, cx=3000.0, cy=3000.0, cz=500.0, dt=10.0)
+    g_occ, g_bits, g_ncell, rec = c.ndmap(lat0=51.990426702297746, lon0=4.376124857109851, want_rec=True, **kw)
+    torch.cuda.synchronize()
+    ac, _, nac, _ = c.get_state()
+    rec = rec.cpu().numpy()
+    F = L.F
+    m_lat = np.radians(1.0) * 6371000.0
+    for e in range(0, E, 5):
+        n = nac[e]
+        assert np.allclose(rec[e, 1, :n], (ac[e, F['lat'], :n] - 51.990426702297746) * m_lat, rtol=1e-6, atol=0.05)
+        assert np.allclose(rec[e, 0, :n], (ac[e, F['lon'], :n] - 4.376124857109851) * m_lat * np.cos(np.radians(51.990426702297746)), rtol=1e-6, atol=0.05)
+        assert np.allclose(rec[e, 2, :n], ac[e, F['alt'], :n]) and np.allclose(rec[e, 3, :n], ac[e, F['gse'], :n], atol=1e-3)
+        assert np.allclose(rec[e, 4, :n], ac[e, F['gsn'], :n], atol=1e-3) and (rec[e, 0, n:] < -1e30).all()
+    occ, conf, ncell = orc.ndmap(rec, nthreads=8, **kw)
+    assert occ.sum() > 0 and int(occ.reshape(E, 30, -1).sum(-1).max()) <= nac.max()
+    assert np.array_equal(occ.reshape(E, 30, -1).sum(-1)[:, 0] <= nac, np.ones(E, bool))
+    assert np.array_equal(g_occ.cpu().numpy(), occ)
+    assert np.array_equal(core.ndmap_unpack(g_bits).cpu().numpy(), conf)
+    assert np.array_equal(g_ncell.cpu().numpy(), ncell)
+    c.close()
 
 
 def test_fma_peaks_are_sane():
@@ -165,9 +225,11 @@ def test_device_reset_properties(orc):
     c2.reset(seed=77)
     assert np.array_equal(c2.get_state()[0], ac)
     mask = torch.zeros(E, dtype=torch.int32, device='cuda'); mask[3] = 1
-    c.reset(mask=mask, seed=77)
+    c.reset(mask=mask, seed=78)                # another seed: env 3 alone draws a new scenario
     ac2 = c.get_state()[0]
     assert np.array_equal(np.delete(ac2, 3, 0), np.delete(ac, 3, 0)) and not np.array_equal(ac2[3], ac[3])
+    c.reset(mask=mask, seed=77)                # the same seed again: the Gymnasium contract, reset(seed=s) reproduces
+    assert np.array_equal(c.get_state()[0], ac)
     c.close(); c2.close()
     # Vertical
     c = BsgCore(L.KIND_VERTICAL, E, 6, precision='fp32')
@@ -254,7 +316,8 @@ def test_ndmap_full_size_properties(orc):
     rec[:, 3] = spd * np.sin(hdg); rec[:, 4] = spd * np.cos(hdg)
     rec[:, 5] = rng.choice([-10.0, 0.0, 0.0, 10.0], (E, n))
     kw = dict(nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=3048.0, cx=370400.0 / 64, cy=370400.0 / 64, cz=304.8 * 4, dt=10.0)
-    g_occ, g_conf, g_ncell = core.ndmap(torch.as_tensor(rec, device='cuda'), **kw)
+    g_occ, g_bits, g_ncell = core.ndmap(torch.as_tensor(rec, device='cuda'), **kw)
+    g_conf = core.ndmap_unpack(g_bits)
     torch.cuda.synchronize()
     pick = [0, 1, 511, 1022, 1023]
     occ, conf, ncell = orc.ndmap(np.ascontiguousarray(rec[pick]), nthreads=8, **kw)
@@ -263,8 +326,74 @@ def test_ndmap_full_size_properties(orc):
     assert np.array_equal(g_conf[pick].cpu().numpy(), conf)
     assert np.array_equal(g_ncell[pick].cpu().numpy(), ncell)
     assert torch.equal(g_conf.view(E, 30, -1).sum(-1, dtype=torch.int32), g_ncell)
+    assert g_bits.numel() * 8 == g_conf.numel()                 # 1 bit per cell leaves the device: 1.125 B per cell in all
     assert int(g_occ.view(E, 30, -1).sum(-1, dtype=torch.int32).max()) <= n
     for e0 in range(0, E, 128):                       # dilation property, 128 envs at a time (memory)
         o = (g_occ[e0:e0 + 128] > 0).float().view(-1, 1, 8, 64, 64)
         nb = torch.nn.functional.max_pool3d(o, 3, stride=1, padding=1).view(128, 30, 8, 64, 64) > 0
         assert bool((nb | (g_conf[e0:e0 + 128] == 0)).all())
+
+
+def test_reset_seed_reproduces_after_episodes():
+    """reset(seed=s) draws the same scenario whenever it is called -- after construction and after several auto-reset
+    episodes -- and the auto-reset episodes that follow it repeat as well (the episode counter that keys
+    Philox is re-based by every stand-alone reset)."""
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    from bluesky_gym_hallucination_b200 import _lib as L
+    E, N = 64, 6
+    c = BsgCore(L.KIND_HORIZONTAL, E, N, precision='fp32', max_episode_steps=4)
+    act = torch.zeros((E, 1), dtype=torch.float32, device='cuda')
+
+    def run():
+        c.reset(seed=31)
+        c.set_autoreset(True, seed=32)
+        first = c.get_state()[0].copy()
+        for _ in range(11):                     # TimeLimit 4: every env passes through two auto-resets
+            c.step(act)
+        torch.cuda.synchronize()
+        return first, c.get_state()[0].copy()
+    a0, a1 = run()
+    b0, b1 = run()
+    assert np.array_equal(a0, b0, equal_nan=True) and np.array_equal(a1, b1, equal_nan=True)
+    assert not np.array_equal(a0, a1, equal_nan=True)
+    c.close()
+
+
+def test_sector_waypoints_follow_the_sorted_law():
+    """sector_cr_env.py:162-176: num_ac perimeter draws are SORTED and aircraft i is handed the i-th smallest, so the
+    agent's waypoint is the minimum of num_ac uniforms (mean perimeter / (num_ac + 1)) -- not a uniform point -- and
+    the arc-length positions increase with the aircraft index.  Device generator vs the host twin (scenario.py)."""
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    from bluesky_gym_hallucination_b200 import scenario as sc, _lib as L
+    E, N = 2048, 32
+    F, EV = L.F, L.EV
+    c = BsgCore(L.KIND_SECTOR, E, N, precision='fp64', fixed_nac=True)
+    c.reset(seed=5)
+    ac, _, nac, ev = c.get_state()
+    c.close()
+    assert (nac == N).all()
+    ccl = np.cos(np.radians(51.990426702297746))
+
+    def arc_fraction(ev_row, wx, wy):
+        nv = int(ev_row[EV['nvert']])
+        x = (ev_row[EV['poly']:EV['poly'] + 2 * nv:2] - 51.990426702297746) * 60
+        y = (ev_row[EV['poly'] + 1:EV['poly'] + 2 * nv:2] - 4.376124857109851) * 60 * ccl
+        seg = np.hypot(np.roll(x, -1) - x, np.roll(y, -1) - y)
+        best, s0 = (np.inf, 0.0), 0.0
+        for k in range(nv):
+            m = (k + 1) % nv
+            t = np.clip(((wx - x[k]) * (x[m] - x[k]) + (wy - y[k]) * (y[m] - y[k])) / seg[k] ** 2, 0, 1)
+            d = np.hypot(wx - (x[k] + t * (x[m] - x[k])), wy - (y[k] + t * (y[m] - y[k])))
+            if d < best[0]:
+                best = (d, s0 + t * seg[k])
+            s0 += seg[k]
+        assert best[0] < 1e-6
+        return best[1] / seg.sum()
+    frac = np.array([arc_fraction(ev[e], ev[e, EV['wpt_x']], ev[e, EV['wpt_y']]) for e in range(E)])
+    expect = 1.0 / (nac + 1.0)                                  # E[min of n uniforms]
+    assert abs(frac.mean() - expect.mean()) < 4 * np.sqrt((expect ** 2).mean() / E), (frac.mean(), expect.mean())
+    assert frac.mean() < 0.15                                   # a uniform perimeter point would give 0.5
+    h_ac, _, h_nac, h_ev = sc.sector(E, N, seed=6)
+    h_frac = np.array([arc_fraction(h_ev[e], h_ev[e, EV['wpt_x']], h_ev[e, EV['wpt_y']]) for e in range(E)])
+    from scipy import stats
+    assert stats.ks_2samp(frac * (nac + 1), h_frac * (h_nac + 1)).pvalue > 1e-3

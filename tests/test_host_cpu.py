@@ -16,14 +16,14 @@ def test_library_exports_every_declared_symbol():
     assert len(declared) >= 20
     assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
     lib = _lib.load()                       # binds all of them; raises on a missing symbol
-    assert lib.bsg_abi_version() == 2
+    assert lib.bsg_abi_version() == _lib.ABI_VERSION == 3
     assert lib.bsg_status_string(-4).decode() == 'unsupported configuration'
 
 
 def test_struct_layouts_match_header():
     import ctypes as C
     from bluesky_gym_hallucination_b200 import _lib
-    assert C.sizeof(_lib.Config) == 12 * 4 + 6 * 8
+    assert C.sizeof(_lib.Config) == 14 * 4 + 6 * 8
     assert C.sizeof(_lib.StepOut) == 14 * 8
     assert C.sizeof(_lib.CdParams) == 32 and C.sizeof(_lib.NdmapParams) == 14 * 4
     assert C.sizeof(_lib.CdPeers) == 8 + 5 * 8 * _lib.MAX_PEERS
