@@ -174,7 +174,12 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     h->epb = h->tpb / N;
     if (const char *f = getenv("BSG_FORCE_EPB")) { int t = atoi(f); if (t >= 1 && t * N <= h->tpb) h->epb = t; }
     const size_t rs = rsize(h);
-    h->smem = g.precision == BSG_FP64 ? step_smem<double>(N, h->epb).total : step_smem<float>(N, h->epb).total;
+    {
+        const bool reso = g.reso_on && g.asas_on;
+        h->nbuf = g.precision == BSG_FP64 ? step_nbuf<double>(N, h->epb, reso) : step_nbuf<float>(N, h->epb, reso);
+        if (const char *f = getenv("BSG_FORCE_NBUF")) { int t = atoi(f); if (t >= 2 && t <= 16) h->nbuf = t; }
+        h->smem = g.precision == BSG_FP64 ? step_smem<double>(N, h->epb, h->nbuf).total : step_smem<float>(N, h->epb, h->nbuf).total;
+    }
     CK(h, cudaSetDevice(g.device));
     const size_t EN = (size_t)E * N;
     CK(h, cudaMalloc(&h->pos, 2 * EN * sizeof(double)));

@@ -7,7 +7,7 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     StepArgs<R> A;
     A.kind = g.env_kind; A.E = g.num_envs; A.N = g.max_ac; A.substeps = substeps; A.asas_on = g.asas_on;
     A.reso_on = g.reso_on; A.reso_off_own = g.reso_off_own; A.max_steps = g.max_episode_steps; A.epb = h->epb;
-    A.observe_only = observe_only;
+    A.observe_only = observe_only; A.nbuf = h->nbuf;
     A.dt = (R)g.simdt;
     A.P.rpz = g.rpz_m; A.P.hpz = g.hpz_m; A.P.dtlook = g.dtlookahead; A.P.fach = g.resofach; A.P.facv = g.resofacv;
     A.pos = h->pos; A.st = (R *)h->st; A.reso = h->reso; A.nac = h->nac; A.ev = h->ev;

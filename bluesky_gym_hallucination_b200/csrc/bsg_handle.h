@@ -8,7 +8,7 @@
 
 struct bsg_handle {
     bsg_config cfg;
-    int obs_dim, act_dim, epb, tpb;
+    int obs_dim, act_dim, epb, tpb, nbuf;
     size_t smem;
     double *pos = nullptr;            // [2][E*N]
     void *st = nullptr;               // R [S_NS][E*N]

@@ -62,7 +62,7 @@ __device__ __forceinline__ float fmax3_f(float a, float b, float c) { float r; a
 // ---------------------------------------------------------------------------------------------------------------
 // The fp32 pair, canonical form.  ONE sequence of individually rounded operations, written with the explicit
 // round-to-nearest intrinsics (never contracted), so that every kernel that evaluates a pair -- the scalar forms
-// below, the packed f32x2 form of the fused step kernel, the tiled sweeps -- produces the same bits:
+// below, the tiled sweeps -- produces the same bits:
 //   dy = yb - ya;  cav = fma(ca_a, ca_b, -(sa_a sa_b));  dx = (xb - xa) cav;  dist2 = fma(dx, dx, dy dy)
 //   du = ub - ua;  dv = vb - va;  dv2 = fma(du, du, fma(dv, dv, 1e-6))      (the reference's clamp as an additive floor)
 //   n = rcp(-dv2)                                                           (= -1 / |v_rel|^2: no negation anywhere below)
@@ -132,49 +132,6 @@ __device__ __forceinline__ bool pair_fast_core(const RecFast &a, const RecFast &
 template <bool VERT = true>
 __device__ __forceinline__ float pair_fast_sign(const RecFast &a, const RecFast &b, const CdParamsF &P) {
     return pair_fast_margin<VERT, false>(a, b, P, nullptr);
-}
-
-// ---------------------------------------------------------------------------------------------------------------
-// Packed form (sm_100 f32x2: FFMA2 / FADD2 / FMUL2): TWO partners of one ownship per instruction, the same canonical
-// sequence lane by lane (each half of a packed operation is an IEEE round-to-nearest fma / add / mul), so the two
-// margins are bit-identical to pair_fast_sign<false> of either partner.  A packed value is a 64-bit register pair
-// {lo, hi}; the partners' fields come out of shared memory already packed (SoA rows, one LDS.64 per field), the
-// ownship's fields are broadcast pairs.  The negations are operand modifiers (free), the four MUFU and the two
-// 3-input max are scalar on the halves.  22 FMA-pipe issue slots per TWO pairs instead of 24 per pair.
-typedef unsigned long long f32x2;
-__device__ __forceinline__ f32x2 pk2(float lo, float hi) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
-__device__ __forceinline__ void upk2(f32x2 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
-__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
-__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
-__device__ __forceinline__ f32x2 neg2(f32x2 v) { float lo, hi; upk2(v, lo, hi); return pk2(-lo, -hi); }   // folds into the consumer
-
-struct Rec2 { f32x2 x, y, u, v, ca, sa; };      // ownship: {f, f}; partners: {f[j], f[j + 1]}
-struct Cd2 { f32x2 R2, c1em6, ndtlook; };        // {R2, R2}, {1e-6, 1e-6}, {-dtlook, -dtlook}
-
-__device__ __forceinline__ void pair_fast_sign2(const Rec2 &a, const Rec2 &b, const Cd2 &C, float &m_lo, float &m_hi) {
-    const f32x2 dy = sub2(b.y, a.y);
-    const f32x2 cav = fma2(a.ca, b.ca, neg2(mul2(a.sa, b.sa)));
-    const f32x2 dx = mul2(sub2(b.x, a.x), cav);
-    const f32x2 dist2 = fma2(dx, dx, mul2(dy, dy));
-    const f32x2 du = sub2(b.u, a.u), dv = sub2(b.v, a.v);
-    const f32x2 dv2 = fma2(du, du, fma2(dv, dv, C.c1em6));
-    float l, h;
-    upk2(dv2, l, h);
-    const f32x2 n = pk2(rcp_approx(-l), rcp_approx(-h));
-    const f32x2 dot = fma2(du, dx, mul2(dv, dy));
-    const f32x2 cr = fma2(dx, dv, neg2(mul2(dy, du)));
-    const f32x2 t6 = fma2(cr, cr, mul2(dist2, C.c1em6));
-    const f32x2 q = fma2(t6, n, C.R2);
-    upk2(mul2(q, n), l, h);
-    const f32x2 dt = pk2(sqrt_approx(-l), sqrt_approx(-h));
-    const f32x2 tout = fma2(dot, n, dt);
-    const f32x2 m2 = add2(fma2(dot, n, neg2(dt)), C.ndtlook);
-    float ql, qh, ol, oh, ml, mh;
-    upk2(q, ql, qh); upk2(tout, ol, oh); upk2(m2, ml, mh);
-    m_lo = fmax3_f(-ql, -ol, ml);
-    m_hi = fmax3_f(-qh, -oh, mh);
 }
 
 // MVP displacement of ownship 1 for one conflict pair; drel = (dx, dy, dalt) is intruder relative to ownship.

