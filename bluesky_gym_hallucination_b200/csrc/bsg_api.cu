@@ -1,5 +1,6 @@
 // bsg_api.cu -- C-ABI of libbsgcore.so (include/bsgcore.h): handle, state interchange, fused step launch.
 // No torch types cross this boundary; device pointers are plain void*/T*.
+#include <vector>
 #include <cuda_runtime.h>
 #include <cstdio>
 #include <cstring>
@@ -178,7 +179,8 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
         const bool reso = g.reso_on && g.asas_on;
         h->nbuf = g.precision == BSG_FP64 ? step_nbuf<double>(N, h->epb, reso) : step_nbuf<float>(N, h->epb, reso);
         if (const char *f = getenv("BSG_FORCE_NBUF")) { int t = atoi(f); if (t >= 2 && t <= 16) h->nbuf = t; }
-        h->smem = g.precision == BSG_FP64 ? step_smem<double>(N, h->epb, h->nbuf).total : step_smem<float>(N, h->epb, h->nbuf).total;
+        const bool pairs = reso && g.precision != BSG_FP64 && N <= 64 && !getenv("BSG_NO_SYM");   // the symmetric sweep's pair scratch
+        h->smem = g.precision == BSG_FP64 ? step_smem<double>(N, h->epb, h->nbuf, false).total : step_smem<float>(N, h->epb, h->nbuf, pairs).total;
     }
     CK(h, cudaSetDevice(g.device));
     const size_t EN = (size_t)E * N;

@@ -7,9 +7,10 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     StepArgs<R> A;
     A.kind = g.env_kind; A.E = g.num_envs; A.N = g.max_ac; A.substeps = substeps; A.asas_on = g.asas_on;
     A.reso_on = g.reso_on; A.reso_off_own = g.reso_off_own; A.max_steps = g.max_episode_steps; A.epb = h->epb;
-    A.observe_only = observe_only; A.nbuf = h->nbuf;
+    A.observe_only = observe_only; A.nbuf = h->nbuf; A.force_walk = getenv("BSG_FORCE_WALK") ? 1 : 0;
     A.dt = (R)g.simdt;
     A.P.rpz = g.rpz_m; A.P.hpz = g.hpz_m; A.P.dtlook = g.dtlookahead; A.P.fach = g.resofach; A.P.facv = g.resofacv;
+    cd_params_fast(A.P, A.PF);
     A.pos = h->pos; A.st = (R *)h->st; A.reso = h->reso; A.nac = h->nac; A.ev = h->ev;
     A.actions = (const R *)actions;
     if (out) A.out = *out; else memset(&A.out, 0, sizeof(A.out));
@@ -82,7 +83,23 @@ int bsg_set_state(bsg_handle *h, const double *ac, const uint64_t *reso, const i
         h->launches++;
         CK(h, cudaGetLastError());
     }
-    if (reso) CK(h, cudaMemcpy(h->reso, reso, EN * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    if (reso) {
+        if (g.precision != BSG_FP64 && g.max_ac <= 64) {
+            // the fp32 symmetric sweep evaluates every unordered pair once for both aircraft: it keeps the resopairs
+            // matrix symmetric (conflicts are, and so is resumenav's decision) and expects it symmetric on intake.
+            // BlueSky's own resopairs are symmetric up to rounding at a threshold; an imported row bit (i, j) without
+            // its mirror is mirrored here.
+            std::vector<uint64_t> sym(reso, reso + EN);
+            const int N = g.max_ac;
+            for (size_t e = 0; e < (size_t)g.num_envs; e++)
+                for (int i = 0; i < N; i++)
+                    for (uint64_t r = reso[e * N + i] & (N < 64 ? (1ull << N) - 1ull : ~0ull); r; r &= r - 1) {
+                        const int j = __builtin_ctzll(r);
+                        if (j != i) sym[e * N + j] |= 1ull << i;
+                    }
+            CK(h, cudaMemcpy(h->reso, sym.data(), EN * sizeof(uint64_t), cudaMemcpyHostToDevice));
+        } else CK(h, cudaMemcpy(h->reso, reso, EN * sizeof(uint64_t), cudaMemcpyHostToDevice));
+    }
     if (nac) CK(h, cudaMemcpy(h->nac, nac, g.num_envs * sizeof(int32_t), cudaMemcpyHostToDevice));
     if (ev) CK(h, cudaMemcpy(h->ev, ev, (size_t)g.num_envs * BSG_NE * sizeof(double), cudaMemcpyHostToDevice));
     CK(h, cudaDeviceSynchronize());

@@ -51,7 +51,7 @@ __device__ __forceinline__ void pair_lit(const RecLit &a, const RecLit &b, const
     o.tcpa = tcpa; o.dcpa2 = dcpa2; o.tin = tin; o.dx = dx; o.dy = dy; o.dist = dist; o.dalt = dalt;
 }
 
-struct CdParamsF { float R2, hpz, dtlook, rpz, rpz_m, hpz_m; };
+struct CdParamsF { float R2, hpz, dtlook, rpz, rpz_m, hpz_m, fach2; };
 
 // MUFU approximations (1-2 ulp): the IEEE forms (__frcp_rn, sqrtf) expand to range checks + a slow-path
 // call each and break the software pipelining of the pair loop
@@ -166,26 +166,30 @@ __device__ __forceinline__ float rsqrt_approx(float x) { float y; asm("rsqrt.app
 
 __device__ __forceinline__ void mvp_pair_fast(float dx, float dy, float dist2, float tcpa, float vrelx, float vrely,
                                               float rpz_m, float &dv1, float &dv2) {
-    float dcx = fmaf(vrelx, tcpa, dx), dcy = fmaf(vrely, tcpa, dy);
-    float dabsH2 = fmaf(dcx, dcx, dcy * dcy);
+    // explicit round-to-nearest operations throughout (never contracted with the caller's arithmetic): the result is
+    // the same bits wherever the function is inlined, and exactly odd in (dx, dy, vrelx, vrely) -- the displacement of
+    // the pair's other ownship is the negative
+    float dcx = __fmaf_rn(vrelx, tcpa, dx), dcy = __fmaf_rn(vrely, tcpa, dy);
+    float dabsH2 = __fmaf_rn(dcx, dcx, __fmul_rn(dcy, dcy));
     float dabsH = sqrt_approx(dabsH2);
-    const float iH = rpz_m - dabsH;
+    const float iH = __fsub_rn(rpz_m, dabsH);
     const float idist = rsqrt_approx(dist2);
     if (dabsH2 <= 100.0f) {
         dabsH = 10.0f; dabsH2 = 100.0f;
-        dcx = dy * idist * 10.0f;
-        dcy = -dx * idist * 10.0f;
+        dcx = __fmul_rn(__fmul_rn(dy, idist), 10.0f);
+        dcy = __fmul_rn(__fmul_rn(-dx, idist), 10.0f);
     }
-    const float iden = rcp_approx(fabsf(tcpa) * dabsH);
+    const float iden = rcp_approx(__fmul_rn(fabsf(tcpa), dabsH));
     float f = iH;
-    const float r2 = rpz_m * rpz_m;
+    const float r2 = __fmul_rn(rpz_m, rpz_m);
     if (r2 < dist2 && dabsH2 < dist2) {
-        const float id2 = idist * idist;
-        const float erratum = fmaf(rpz_m * idist, dabsH * idist, sqrt_approx((dist2 - r2) * (dist2 - dabsH2)) * id2);
-        f = fmaf(rpz_m, rcp_approx(erratum), -dabsH);
+        const float id2 = __fmul_rn(idist, idist);
+        const float root = sqrt_approx(__fmul_rn(__fsub_rn(dist2, r2), __fsub_rn(dist2, dabsH2)));
+        const float erratum = __fmaf_rn(__fmul_rn(rpz_m, idist), __fmul_rn(dabsH, idist), __fmul_rn(root, id2));
+        f = __fmaf_rn(rpz_m, rcp_approx(erratum), -dabsH);
     }
-    f *= iden;
-    dv1 = f * dcx; dv2 = f * dcy;
+    f = __fmul_rn(f, iden);
+    dv1 = __fmul_rn(f, dcx); dv2 = __fmul_rn(f, dcy);
 }
 
 // per-row running outputs of the sweep (branch-free: the pair loop stays software-pipelined).

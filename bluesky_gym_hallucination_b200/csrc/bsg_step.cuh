@@ -17,8 +17,10 @@ namespace bsg {
 template <typename R> struct StepArgs {
     int kind, E, N, substeps, asas_on, reso_on, reso_off_own, max_steps, epb, observe_only;
     int nbuf;             // record rows per env in shared memory (step_nbuf)
+    int force_walk;       // test hook (BSG_FORCE_WALK): resolution kernels drop the pair work list, every owner walks its row
     R dt;
     CdParams P;
+    CdParamsF PF;         // P rounded to fp32 (cd_params_fast)
     double *pos; R *st; unsigned long long *reso; int *nac; double *ev;
     const R *actions;
     const int *skip;      // envs reset after the previous step (auto-reset): observe only, reward 0
@@ -39,6 +41,7 @@ template <typename R> struct EnvShared {
     double own_lat, own_lon;
     R own_hdg, own_tas, own_alt, own_vs, drift, wdist;
     int anyconf[2];
+    int nC, nR, ovf;                 // work list of the pair scratch: conflicting / resolving-only items; a slot row overflowed
     int vneed;                       // some aircraft of the env is not level / co-altitude: generic vertical window
     R alt_ref;
     int intr;

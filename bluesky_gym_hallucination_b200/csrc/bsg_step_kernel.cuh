@@ -23,11 +23,11 @@ __device__ unsigned long long g_trace[8 * 16384];
 #define BSG_STAMP(slot) do { } while (0)
 #endif
 
-template <typename R>
-__device__ __forceinline__ void cd_params_for(const CdParams &P, CdParams &lit, CdParamsF &fast) {
-    lit = P;
+// the fp32 CD thresholds, rounded once on the host (launch_step) and carried in StepArgs
+inline void cd_params_fast(const CdParams &P, CdParamsF &fast) {
     fast.R2 = (float)(P.rpz * P.rpz); fast.hpz = (float)P.hpz; fast.dtlook = (float)P.dtlook;
     fast.rpz = (float)P.rpz; fast.rpz_m = (float)(P.rpz * P.fach); fast.hpz_m = (float)(P.hpz * P.facv);
+    fast.fach2 = (float)(P.fach * P.fach);
 }
 
 // CTA size / residency: 128-thread CTAs keep the small-N configs in one balanced wave
@@ -43,7 +43,7 @@ template <typename R, int TPB> struct StepBounds {
 // N headings (resumenav's bouncing test) behind them, in the same substep buffer.
 __host__ __device__ constexpr int sym_row_recs(int N) { return N + N / 2; }
 template <typename R> __host__ __device__ constexpr size_t rec_row_bytes(int N) {
-    return sizeof(R) == 4 ? (size_t)sym_row_recs(N) * sizeof(RecFast) + (size_t)N * sizeof(float) + 16
+    return sizeof(R) == 4 ? (size_t)sym_row_recs(N) * sizeof(RecFast) + (((size_t)N * sizeof(float) + 15) & ~(size_t)15) + 16
                           : (size_t)N * sizeof(typename RecOf<R>::type) + 16;
 }
 __device__ __forceinline__ RecFast rec_from(const float4 &a, const float4 &b) {
@@ -51,13 +51,37 @@ __device__ __forceinline__ RecFast rec_from(const float4 &a, const float4 &b) {
 }
 
 // shared-memory carve-up of one CTA (host and device agree through this one function)
-struct StepSmem { size_t es_off, sd_off, cr_off, total; };
-template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int epb, int nbuf) {
+// Pair scratch of one env (fp32 symmetric sweep WITH resolution).  The env's unordered conflicting / resolving pairs
+// are evaluated ONCE each, by whichever thread of the env is free (work list), and the results are handed to both
+// aircraft of the pair:
+//   rows  u32 x6 per aircraft: its conflict row, resumenav's keep row, LoS row (absolute bits, two words each), built
+//                with shared-memory atomicOr by whoever evaluates the pair
+//   items u16    work list, (i' << 5 | d-1) = the pair {i', i'+d} of the forward half ring of thread i': conflicting
+//                pairs from the front, resolving-only pairs from the back; at most BSG_PAIR_CAP * N items
+//   res   float2 [N][BSG_SLOT_CAP]: aircraft i's MVP displacements, slot = rank of the intruder among its conflicts
+//                (ascending index: the owner's sum keeps the order of the reference's loop)
+//   tcp   float  [N][BSG_SLOT_CAP]: tCPA of those pairs (last detection only: the CD row outputs)
+// An env that overflows the list or a slot row falls back, for that detection, to the walk in which every owner evaluates
+// its own row (same bits: the pair arithmetic is exactly antisymmetric).
+#ifndef BSG_PAIR_CAP
+#define BSG_PAIR_CAP 8
+#endif
+#ifndef BSG_SLOT_CAP
+#define BSG_SLOT_CAP 16
+#endif
+__host__ __device__ constexpr int pair_cap(int N) { return BSG_PAIR_CAP * N < N * (N / 2) ? BSG_PAIR_CAP * N : N * (N / 2) + 1; }
+__host__ __device__ constexpr int slot_cap(int N) { return BSG_SLOT_CAP < N ? BSG_SLOT_CAP : N; }
+__host__ __device__ constexpr size_t pair_scratch_bytes(int N) {
+    return (((size_t)N * slot_cap(N) * (sizeof(float2) + sizeof(float)) + (size_t)N * 24 + (size_t)pair_cap(N) * sizeof(unsigned short)) + 15) & ~(size_t)15;
+}
+struct StepSmem { size_t es_off, sd_off, cr_off, px_off, total; };
+template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int epb, int nbuf, bool pairs) {
     StepSmem L;
     L.es_off = (size_t)nbuf * epb * rec_row_bytes<R>(N);                   // [nbuf][epb] record rows
     L.sd_off = L.es_off + (size_t)epb * sizeof(EnvShared<R>);              // [epb] env scratch
     L.cr_off = (L.sd_off + (size_t)epb * N * sizeof(R) + 7) & ~(size_t)7;  // [epb*N] hdg / sector distances
-    L.total = L.cr_off + 2 * (size_t)epb * N * sizeof(unsigned long long); // [2][epb*N] conflict bit rows (SYM)
+    L.px_off = (L.cr_off + 2 * (size_t)epb * N * sizeof(unsigned long long) + 15) & ~(size_t)15;   // [2][epb*N] conflict bit rows (SYM)
+    L.total = L.px_off + (pairs ? (size_t)epb * pair_scratch_bytes(N) : 0); // [epb] pair scratch
     return L;
 }
 // record rows per env: the detection-only fp32 kernels (no resolution feeding back into the kinematics) integrate a
@@ -65,7 +89,7 @@ template <typename R> __host__ __device__ inline StepSmem step_smem(int N, int e
 template <typename R> __host__ inline int step_nbuf(int N, int epb, bool reso) {
     if (sizeof(R) != 4 || N > 64 || reso) return 2;
     int nb = BSG_CH;
-    while (nb > 2 && step_smem<R>(N, epb, nb).total > 44 * 1024) nb--;   // five 128-thread CTAs per SM
+    while (nb > 2 && step_smem<R>(N, epb, nb, false).total > 44 * 1024) nb--;   // five 128-thread CTAs per SM
     return nb;
 }
 
@@ -115,7 +139,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int N = A.N, epb = A.epb;
     const size_t rowb = rec_row_bytes<R>(N);
-    const StepSmem SL = step_smem<R>(N, epb, A.nbuf);
+    const StepSmem SL = step_smem<R>(N, epb, A.nbuf, RESO && SYM);
     unsigned char *recs = smem_raw;                                        // [nbuf][epb] rows of rowb bytes
     EnvShared<R> *es = reinterpret_cast<EnvShared<R> *>(smem_raw + SL.es_off);   // [epb]
     R *sdist = reinterpret_cast<R *>(smem_raw + SL.sd_off);                // [epb*N] hdg (resumenav) / sector distances
@@ -126,29 +150,60 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     const int le = tid / N, i = tid - le * N;
     const int e = blockIdx.x * epb + le;
     const bool valid = le < epb && e < A.E;
-    const bool skip = valid && A.skip && A.skip[e];                       // fresh episode: no action, no integration
-    if (A.fuse_reset && __syncthreads_or(skip))                            // rare: some env of this CTA starts an episode
-        fused_reset<R>(A.kind, A.fixed_nac, A.density_mode, A.E, A.N, A.epb, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso,
-                       A.RC, smem_raw, skip, valid, le, i, e);
-    const int nl = valid ? A.nac[e] : 0;
-    const bool live = valid && i < nl;
     const size_t EN = (size_t)A.E * N, k = (size_t)(valid ? e : 0) * N + i;
     double *ev = A.ev + (size_t)(valid ? e : 0) * BSG_NE;
     constexpr bool reso = RESO;
-
+    // ------------------------------------------------------------------ prologue loads in TWO dependent batches
+    // (the inputs are cold: every dependent batch is a DRAM round trip).  Batch 1: episode flag, aircraft count, env
+    // scalars, action; batch 2, after the (rare) reset stage: the aircraft state.
     AcReg<R> a = {};
     unsigned long long resorow = 0;
+    int skipv = 0, nlv = 0;
+    double ev_mine = 0.0, ev_hdg = 0.0;                                     // env scalar slot i; the agent's AC_HDG
+    R act0 = R(0), act1 = R(0);                                             // the agent's action
+    auto load_env = [&]() {
+        if (valid) {
+            nlv = A.nac[e];
+            if (i < BSG_EV_POLY) ev_mine = ev[i];
+            if (i == 0) ev_hdg = ev[BSG_EV_AC_HDG];
+        }
+    };
+    if (valid && A.skip) skipv = A.skip[e];
+#ifndef BSG_OLD_PROLOGUE
+    load_env();
+#endif
+    if (valid && i == 0 && A.actions) {
+        const bool two = A.kind == BSG_KIND_SECTOR || A.kind == BSG_KIND_MERGE;
+        act0 = A.actions[two ? 2 * e : e];
+        if (two) act1 = A.actions[2 * e + 1];
+    }
+    const bool skip = valid && skipv;                                      // fresh episode: no action, no integration
+    if (A.fuse_reset && __syncthreads_or(skip)) {                          // rare: some env of this CTA starts an episode
+        fused_reset<R>(A.kind, A.fixed_nac, A.density_mode, A.E, A.N, A.epb, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso,
+                       A.RC, smem_raw, skip, valid, le, i, e);
+#ifndef BSG_OLD_PROLOGUE
+        load_env();
+#endif
+    }
+#ifdef BSG_OLD_PROLOGUE
+    load_env();
+#endif
+    const int nl = valid ? nlv : 0;
+    const bool live = valid && i < nl;
     if (live) {
         ac_load_raw<R, RESO, EXT>(a, A.pos, A.st, EN, k);
-        ac_derive<R, EXT>(a);
         if (reso) resorow = A.reso[k];
+        ac_derive<R, EXT>(a);
+    }
+    // the env-level scalar slots, staged in shared memory by the first lanes of the env
+    if (valid) {
+        if (i < BSG_EV_POLY) es[le].ev[i] = ev_mine;
+        for (int s2 = i + N; s2 < BSG_EV_POLY; s2 += N) es[le].ev[s2] = ev[s2];       // N < 14 only
     }
     // ------------------------------------------------------------------ action intake (agent = aircraft 0)
     if (live && i == 0) {
-        es[le].anyconf[0] = 0; es[le].anyconf[1] = 0; es[le].intr = 0; es[le].vneed = 0; es[le].alt_ref = a.alt;
+        es[le].anyconf[0] = 0; es[le].anyconf[1] = 0; es[le].nC = 0; es[le].nR = 0; es[le].ovf = 0; es[le].intr = 0; es[le].vneed = 0; es[le].alt_ref = a.alt;
         es[le].own_lat = a.lat; es[le].own_lon = a.lon;                    // local origin of the fp32 CD records
-#pragma unroll
-        for (int s2 = 0; s2 < BSG_EV_POLY; s2++) es[le].ev[s2] = ev[s2];   // 14 independent loads, staged in smem
         if (A.actions && !skip) {
             // AP.selhdgcmd under a wind field: the HDG argument becomes the track it gives (above 50 ft)
             auto hdg_cmd = [&](R hdg) -> R {
@@ -164,18 +219,18 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 return hdg;
             };
             if (A.kind == BSG_KIND_HORIZONTAL) {                           // horizontal_cr_env.py:272-275
-                a.aptrk = hdg_cmd(R(es[le].ev[BSG_EV_AC_HDG]) + A.actions[e] * R(45));
+                a.aptrk = hdg_cmd(R(ev_hdg) + act0 * R(45));
             } else if (A.kind == BSG_KIND_VERTICAL) {                      // vertical_cr_env.py:242-256
-                R v = A.actions[e] * R(12.5);
+                R v = act0 * R(12.5);
                 a.selalt = v >= R(0) ? R(1000000) : R(0);
                 a.selvs = v;
             } else if (A.kind == BSG_KIND_SECTOR) {                        // sector_cr_env.py:315-322
-                R dh = A.actions[2 * e] * R(22.5), dv = A.actions[2 * e + 1] * R(20.0 / 3);
+                R dh = act0 * R(22.5), dv = act1 * R(20.0 / 3);
                 a.aptrk = hdg_cmd(bound180<R>(a.hdg + dh));
                 R spd_kts = (a.cas + dv) * R(1.94384);
                 a.selspd = fabs(spd_kts) > R(1) ? spd_kts * R(kKts) : spd_kts;
             } else if (EXT && A.kind == BSG_KIND_MERGE) {                  // merge_env.py:285-293 (HDG: LNAV off)
-                R dh = A.actions[2 * e] * R(15), dv = A.actions[2 * e + 1] * R(20);
+                R dh = act0 * R(15), dv = act1 * R(20);
                 a.aptrk = hdg_cmd(bound180<R>(a.hdg + dh));
                 a.lnav = -1;
                 R spd_kts = (a.cas + dv) * R(1.94384);
@@ -183,12 +238,17 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             }
         }
     }
+    if constexpr (RESO && SYM) {
+        if (valid) {                                       // conflict rows of the pair scratch start empty
+            unsigned *cr0 = reinterpret_cast<unsigned *>(smem_raw + SL.px_off + (size_t)le * pair_scratch_bytes(N) + (size_t)N * slot_cap(N) * 12);
+            cr0[2 * i] = 0u; cr0[2 * i + 1] = 0u;
+        }
+    }
     __syncthreads();
     BSG_STAMP(1);
     const double lat0 = valid ? es[le].own_lat : 0.0, lon0 = valid ? es[le].own_lon : 0.0;
     const R alt_ref = valid ? es[le].alt_ref : R(0);
-    CdParams PL; CdParamsF PF;
-    cd_params_for<R>(A.P, PL, PF);
+    const CdParams PL = A.P; const CdParamsF PF = A.PF;
     ExtCtx X;
     if constexpr (EXT) {
         const double *sv = es[valid ? le : 0].ev;
@@ -222,7 +282,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             if (i < (nl >> 1)) { wA[nl + i] = ha; wB[nl + i] = hb; }
             if (RESO) reinterpret_cast<float *>(wB + NR)[i] = a.hdg;          // resumenav's bouncing test
             // monotone within the launch: once any aircraft climbs, descends or leaves the common level
-            if (a.vs != 0.0f || !(fabsf(a.alt - alt_ref) < 0.5f * (float)A.P.hpz)) es[le].vneed = 1;
+            if (a.vs != 0.0f || !(fabsf(a.alt - alt_ref) < 0.5f * PF.hpz)) es[le].vneed = 1;
         }
     };
     // phase 1: thread i sweeps ITS half ring j = i+1 .. i+H of the row and returns the relative conflict mask F
@@ -257,22 +317,33 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     // a thread are read without an index wrap); phase 2 completes the row with bit k-1 of the masks of the nl-1-H
     // partners i-k.  One buffer: the next barrier separates the readers of this detection from the next writers.
     unsigned *const hr = reinterpret_cast<unsigned *>(crow) + (size_t)le * 2 * N;
+    // pair scratch of this env (resolution kernels): res | tcp | rows | items
+    unsigned char *const px = smem_raw + SL.px_off + (size_t)le * pair_scratch_bytes(N);
+    const int CAP = pair_cap(N), SC = slot_cap(N);
+    float2 *const px_res = reinterpret_cast<float2 *>(px);                       // [N][SC]
+    float *const px_tcp = reinterpret_cast<float *>(px_res + (size_t)N * SC);    // [N][SC]
+    unsigned *const px_cr = reinterpret_cast<unsigned *>(px_tcp + (size_t)N * SC);   // [N][2] conflict rows
+    unsigned *const px_keep = px_cr + 2 * N;                                     // [N][2] resumenav keep rows
+    unsigned *const px_los = px_keep + 2 * N;                                    // [N][2] LoS rows
+    unsigned short *const px_items = reinterpret_cast<unsigned short *>(px_los + 2 * N);   // [CAP]
     // phase 2: my row, conflicting / resolving pairs only.  It feeds MVP / resumenav every substep; the CD row
     // outputs report the LAST detection of the step (what bs.traf.cd holds afterwards), so the row reductions run on
     // the last substep only (want_acc).
-    auto phase2 = [&](const unsigned char *row, unsigned F, bool want_acc) {
+    auto phase2 = [&](const unsigned char *row, unsigned F, bool want_acc, bool listed) {
         if constexpr (SYM) {
             const float4 *rA = reinterpret_cast<const float4 *>(row), *rB = rA + NR;
-            const float *hdgrow = reinterpret_cast<const float *>(rB + NR);
             const RecFast me = rec_from(rA[i], rB[i]);
-            // B bit (k-1) <-> partner i-k: the pair (i-k, i) is bit k-1 of that partner's mask
-            // Groups of 8 partners, fully unrolled (LDS with an immediate offset + one LOP3 with an immediate mask
-            // per partner); a group may read up to 7 words past partner kmax -- other rows' masks, at worst the
-            // 31 words below this array, all inside the CTA's shared memory -- and the final mask drops them.
-            unsigned B = 0u;
-            {
+            // A symmetric relation over the ring (conflict flags, resumenav's keep flags) is stored as one word of forward
+            // bits per thread (bit d-1 <-> partner i+d), each word twice (w[i] and the ring copy w[i + nl], so that the
+            // partners behind a thread are read without an index wrap).  My full row = my forward word + bit k-1 of the
+            // words of the nl-1-H partners i-k.  Groups of 8 partners, fully unrolled (LDS with an immediate offset + one
+            // LOP3 with an immediate mask per partner); a group may read up to 7 words past partner kmax -- other rows'
+            // words, at worst the 31 words below the array, all inside the CTA's shared memory -- and the final mask
+            // drops them.
+            auto ring_row = [&](const unsigned *w, unsigned Fw) -> unsigned long long {
+                unsigned B = 0u;
                 const int kmax = nl - 1 - (nl >> 1);                 // <= 31
-                const unsigned *hb = hr + i + nl;
+                const unsigned *hb = w + i + nl;
 #pragma unroll
                 for (int g8 = 0; g8 < 32; g8 += 8) {
                     if (g8 < kmax) {
@@ -281,46 +352,83 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     }
                 }
                 B &= (1u << kmax) - 1u;
-            }
-            // relative -> absolute positions.  Forward: i+d, wrapped ones (i+d >= nl) at i+d-nl.
-            unsigned long long fwd = (i < 63 ? (unsigned long long)F << (i + 1) : 0ull) & (nl < 64 ? (1ull << nl) - 1ull : ~0ull);
-            if (nl - 1 - i < 32) fwd |= (unsigned long long)(F >> (nl - 1 - i));
-            // Backward: the bit-reversed word, shifted, lands on i-k (and i-k+nl for the wrapped ones)
-            const unsigned long long rb64 = (unsigned long long)__brev(B) << 32;     // bit 64-k <-> partner i-k
-            unsigned long long back = i > 0 ? rb64 >> (64 - i) : 0ull;               // positions i-k >= 0
-            if (i < 32) back |= (rb64 << i) >> (64 - nl);                            // k > i: positions i-k+nl
-            const unsigned long long cr = fwd | back;
-            const unsigned long long notme = ~(1ull << i);
-            const float R2f = PF.rpz * PF.rpz, R2b = R2f * (float)(A.P.fach * A.P.fach);
-            // resumenav test of one resolving pair (squared distances; the canonical pair quantities)
-            auto resume = [&](int j, unsigned long long jb, float dist2, float dot) {
-                const bool past = dot > 0.0f;
-                bool kp = !past || dist2 < R2f;
-                if (!kp && dist2 < R2b) kp = fabsf(a.hdg - hdgrow[j]) < 30.0f;      // bouncing (rare)
-                touched = true;
-                if (kp) { active = true; keep |= jb; }
+                // relative -> absolute positions.  Forward: i+d, wrapped ones (i+d >= nl) at i+d-nl.
+                unsigned long long fwd = (i < 63 ? (unsigned long long)Fw << (i + 1) : 0ull) & (nl < 64 ? (1ull << nl) - 1ull : ~0ull);
+                if (nl - 1 - i < 32) fwd |= (unsigned long long)(Fw >> (nl - 1 - i));
+                // Backward: the bit-reversed word, shifted, lands on i-k (and i-k+nl for the wrapped ones)
+                const unsigned long long rb64 = (unsigned long long)__brev(B) << 32;     // bit 64-k <-> partner i-k
+                unsigned long long back = i > 0 ? rb64 >> (64 - i) : 0ull;               // positions i-k >= 0
+                if (i < 32) back |= (rb64 << i) >> (64 - nl);                            // k > i: positions i-k+nl
+                return fwd | back;
             };
-            // two walks instead of one with a divergent `if (sw)`: conflicting pairs first (row reductions, MVP,
-            // resumenav), then the pairs that are only still resolving (resumenav alone).  Ascending j in
-            // both, so the MVP sum keeps its order.
-            unsigned long long S = cr & notme;
-            while (S) {
-                const int j = __ffsll((long long)S) - 1;
-                const unsigned long long jb = S & (0ull - S);        // lowest set bit (no 64-bit shift by j)
-                S ^= jb;
-                const RecFast o = rec_from(rA[j], rB[j]);
-                PairCore pc;
-                pair_fast_core(me, o, PF, true, pc);
-                if (want_acc)
+            // detection only: my conflict row from the ring words; with resolution: the row the sweep built with atomics
+            unsigned long long cr;
+            if constexpr (RESO) cr = (unsigned long long)px_cr[2 * i] | ((unsigned long long)px_cr[2 * i + 1] << 32);
+            else cr = ring_row(hr, F);
+            const unsigned long long notme = ~(1ull << i);
+            if constexpr (!RESO) {
+                // detection only: the row reductions of the step's last detection over my conflicting pairs
+                unsigned long long S = cr & notme;
+                while (S) {
+                    const int j = __ffsll((long long)S) - 1;
+                    S &= S - 1;
+                    PairCore pc;
+                    pair_fast_core(me, rec_from(rA[j], rB[j]), PF, true, pc);
                     acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
-                if constexpr (RESO) {
+                }
+            } else if (listed) {
+                // with resolution: every pair of my row was evaluated once by the work list (below): resumenav's keep
+                // row came back through atomics, my MVP displacements sit in my slot row in ascending intruder index
+                keep = (unsigned long long)px_keep[2 * i] | ((unsigned long long)px_keep[2 * i + 1] << 32);
+                touched = ((cr | resorow) & notme) != 0ull;
+                active = keep != 0ull;
+                const int nc = __popcll(cr);
+                const float2 *mr = px_res + i * SC;
+                if (!want_acc) {
+                    for (int q = 0; q < nc; q++) { const float2 m = mr[q]; dve = __fsub_rn(dve, m.x); dvn = __fsub_rn(dvn, m.y); }
+                } else {
+                    const float *tr = px_tcp + i * SC;
+                    unsigned long long S = cr;
+                    for (int q = 0; q < nc; q++) {
+                        const float2 m = mr[q];
+                        dve = __fsub_rn(dve, m.x); dvn = __fsub_rn(dvn, m.y);
+                        const int j = __ffsll((long long)S) - 1;
+                        S &= S - 1;
+                        acc.add_conflict(j, tr[q], 0.0f, 0.0f, false);
+                    }
+                    acc.nlos = __popc(px_los[2 * i]) + __popc(px_los[2 * i + 1]);
+                    if (acc.near_idx >= 0) {                                // dCPA / tLOS of the nearest-in-time conflict
+                        PairCore pc;
+                        pair_fast_core(me, rec_from(rA[acc.near_idx], rB[acc.near_idx]), PF, true, pc);
+                        acc.near_dcpa2 = pc.dcpa2; acc.near_tin = pc.tin;
+                    }
+                }
+                if (A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }   // RESOOFF: the agent does not resolve
+            } else {
+                // list overflow (an env denser than BSG_PAIR_CAP allows): every owner evaluates its own row -- two walks,
+                // conflicting pairs first (row reductions, MVP, resumenav), then the pairs that are only still resolving
+                const float *hdgrow = reinterpret_cast<const float *>(rB + NR);
+                const float R2f = PF.rpz * PF.rpz, R2b = R2f * PF.fach2;
+                auto resume = [&](int j, unsigned long long jb, float dist2, float dot) {
+                    bool kp = !(dot > 0.0f) || dist2 < R2f;
+                    if (!kp && dist2 < R2b) kp = fabsf(a.hdg - hdgrow[j]) < 30.0f;      // bouncing (rare)
+                    touched = true;
+                    if (kp) { active = true; keep |= jb; }
+                };
+                unsigned long long S = cr & notme;
+                while (S) {
+                    const int j = __ffsll((long long)S) - 1;
+                    const unsigned long long jb = S & (0ull - S);
+                    S ^= jb;
+                    PairCore pc;
+                    pair_fast_core(me, rec_from(rA[j], rB[j]), PF, true, pc);
+                    if (want_acc)
+                        acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
                     float d1, d2;
                     mvp_pair_fast(pc.dx, pc.dy, pc.dist2, pc.tcpa, pc.du, pc.dv, PF.rpz_m, d1, d2);
-                    dve = dve - d1; dvn = dvn - d2;
+                    dve = __fsub_rn(dve, d1); dvn = __fsub_rn(dvn, d2);
                     resume(j, jb, pc.dist2, pc.dot);
                 }
-            }
-            if constexpr (RESO) {
                 S = resorow & ~cr & notme;
                 while (S) {
                     const int j = __ffsll((long long)S) - 1;
@@ -330,7 +438,89 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                     pair_fast_geom(me, rec_from(rA[j], rB[j]), dist2, dot);
                     resume(j, jb, dist2, dot);
                 }
-                if (A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }   // RESOOFF: the agent does not resolve
+                if (A.reso_off_own && i == 0) { dve = 0.0f; dvn = 0.0f; }
+            }
+        }
+    };
+    // Work list (resolution kernels).  Thread i owns the unordered pairs of its forward half ring; those that are in
+    // conflict (F) or still resolving (my resopairs row: the matrix is symmetric -- conflicts are, and resumenav's
+    // decision is -- so my forward bits cover the pair for both sides) become items of the env's list.
+    auto list_build = [&](unsigned F) {
+        if constexpr (RESO && SYM) {
+            const int H = nl >> 1;
+            const unsigned long long rot = (i < 63 ? resorow >> (i + 1) : 0ull) | (resorow << (nl - 1 - i));
+            const unsigned hm = H >= 32 ? ~0u : (1u << H) - 1u;
+            unsigned Wc = F & hm, Wr = (unsigned)rot & hm & ~F;
+            // my conflict row: my forward bits at their absolute positions (i+d, wrapped ones at i+d-nl) ...
+            unsigned long long fwd = (i < 63 ? (unsigned long long)Wc << (i + 1) : 0ull) & (nl < 64 ? (1ull << nl) - 1ull : ~0ull);
+            if (nl - 1 - i < 32) fwd |= (unsigned long long)(Wc >> (nl - 1 - i));
+            if ((unsigned)fwd) atomicOr(&px_cr[2 * i], (unsigned)fwd);
+            if ((unsigned)(fwd >> 32)) atomicOr(&px_cr[2 * i + 1], (unsigned)(fwd >> 32));
+            // the opposite pair of an even ring is a forward pair of both aircraft: the lower index lists it
+            if (H > 0 && 2 * H == nl && i >= H) { Wc &= ~(1u << (H - 1)); Wr &= ~(1u << (H - 1)); }
+            const int nc = __popc(Wc), nr = __popc(Wr);
+            int bc = nc ? atomicAdd(&es[le].nC, nc) : 0, br = nr ? atomicAdd(&es[le].nR, nr) : 0;
+            const bool fits = bc + nc + br + nr <= CAP;     // (an overflowing env drops the list for this detection)
+            const unsigned mybit = 1u << (i & 31);
+            const int myword = i >> 5;
+            // ... and my bit in the rows of my forward partners
+            while (Wc) {
+                const int b = __ffs(Wc) - 1; Wc &= Wc - 1;
+                int jw = i + b + 1; jw -= jw >= nl ? nl : 0;
+                atomicOr(&px_cr[2 * jw + myword], mybit);
+                if (fits) px_items[bc++] = (unsigned short)((i << 5) | b);
+            }
+            if (fits)
+                while (Wr) { const int b = __ffs(Wr) - 1; Wr &= Wr - 1; px_items[CAP - 1 - br++] = (unsigned short)((i << 5) | b); }
+        }
+    };
+    // every thread of the env takes items t = i, i + N, ...: a conflicting pair gets the full canonical pair, MVP and
+    // resumenav's decision; a pair that is only still resolving gets the decision alone
+    auto list_run = [&](const unsigned char *row, bool want_acc) {
+        if constexpr (RESO && SYM) {
+            const float4 *rA = reinterpret_cast<const float4 *>(row), *rB = rA + NR;
+            const float *hdgrow = reinterpret_cast<const float *>(rB + NR);
+            const int nC = es[le].nC, nR = es[le].nR;
+            const float R2f = PF.rpz * PF.rpz, R2b = R2f * PF.fach2;
+            // resumenav's decision for the pair (symmetric): a kept pair sets its bit in the keep rows of both aircraft
+            auto keep_pair = [&](int ia, int jw, float dist2, float dot) {
+                bool kp = !(dot > 0.0f) || dist2 < R2f;                     // not past CPA, or in horizontal LoS
+                if (!kp && dist2 < R2b) kp = fabsf(hdgrow[ia] - hdgrow[jw]) < 30.0f;       // bouncing (rare)
+                if (kp) {
+                    atomicOr(&px_keep[2 * ia + (jw >> 5)], 1u << (jw & 31));
+                    atomicOr(&px_keep[2 * jw + (ia >> 5)], 1u << (ia & 31));
+                }
+            };
+            for (int t = i; t < nC; t += N) {
+                const unsigned it = px_items[t];
+                const int ia = it >> 5, ib = ia + (it & 31u) + 1, jw = ib >= nl ? ib - nl : ib;
+                PairCore pc;
+                pair_fast_core(rec_from(rA[ia], rB[ia]), rec_from(rA[ib], rB[ib]), PF, true, pc);
+                float d1, d2;
+                mvp_pair_fast(pc.dx, pc.dy, pc.dist2, pc.tcpa, pc.du, pc.dv, PF.rpz_m, d1, d2);
+                // slot of the pair in either aircraft's row: the rank of the other among its conflicts
+                const unsigned long long ca = (unsigned long long)px_cr[2 * ia] | ((unsigned long long)px_cr[2 * ia + 1] << 32);
+                const unsigned long long cb = (unsigned long long)px_cr[2 * jw] | ((unsigned long long)px_cr[2 * jw + 1] << 32);
+                const int qa = __popcll(ca & ((1ull << jw) - 1ull)), qb = __popcll(cb & ((1ull << ia) - 1ull));
+                if (qa < SC && qb < SC) {
+                    px_res[ia * SC + qa] = make_float2(d1, d2);
+                    px_res[jw * SC + qb] = make_float2(-d1, -d2);
+                    if (want_acc) {
+                        px_tcp[ia * SC + qa] = pc.tcpa; px_tcp[jw * SC + qb] = pc.tcpa;
+                        if ((pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz)) {
+                            atomicOr(&px_los[2 * ia + (jw >> 5)], 1u << (jw & 31));
+                            atomicOr(&px_los[2 * jw + (ia >> 5)], 1u << (ia & 31));
+                        }
+                    }
+                } else es[le].ovf = 1;
+                keep_pair(ia, jw, pc.dist2, pc.dot);
+            }
+            for (int t = i; t < nR; t += N) {
+                const unsigned it = px_items[CAP - 1 - t];
+                const int ia = it >> 5, ib = ia + (it & 31u) + 1, jw = ib >= nl ? ib - nl : ib;
+                float dist2, dot;
+                pair_fast_geom(rec_from(rA[ia], rB[ia]), rec_from(rA[ib], rB[ib]), dist2, dot);
+                keep_pair(ia, jw, dist2, dot);
             }
         }
     };
@@ -371,7 +561,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 if (Fany | Flast) es[le].anyconf[0] = 1;
             }
             __syncthreads();
-            if (live && !skip) phase2(row0 + (size_t)lastrow * bstride, Flast, true);
+            if (live && !skip) phase2(row0 + (size_t)lastrow * bstride, Flast, true, false);
         }
     } else {
     // ------------------------------------------------------------------ K substeps
@@ -388,22 +578,39 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 }
             }
             __syncthreads();
-            if (RESO && valid && i == 0) es[le].anyconf[buf ^ 1] = 0;
+            if (RESO && valid && i == 0) { es[le].anyconf[buf ^ 1] = 0; es[le].ovf = 0; }
             acc = RowAcc<R>();
             dve = R(0); dvn = R(0);
             touched = false; active = false;
             keep = 0;
             if constexpr (SYM) {
                 unsigned F = 0u;
-                if (live && !skip) {
-                    F = sweep_row(row);
-                    hr[i] = F; hr[i + nl] = F;
-                    if (RESO && F) es[le].anyconf[buf] = 1;
-                }
                 const bool want_acc = (s == A.substeps - 1);
                 const bool need_rows = RESO || want_acc;
+                if (live && !skip) {
+                    F = sweep_row(row);
+                    if constexpr (RESO) {
+                        if (F) es[le].anyconf[buf] = 1;
+                        px_keep[2 * i] = 0u; px_keep[2 * i + 1] = 0u;
+                        if (want_acc) { px_los[2 * i] = 0u; px_los[2 * i + 1] = 0u; }
+                        list_build(F);
+                    } else { hr[i] = F; hr[i + nl] = F; }
+                }
                 if (need_rows) __syncthreads();
-                if (need_rows && live && !skip) phase2(row, F, want_acc);
+                bool listed = false;
+                if constexpr (RESO) {
+                    const bool fits = valid && es[le].nC + es[le].nR <= CAP && !A.force_walk;
+                    if (fits && !skip) list_run(row, want_acc);
+                    __syncthreads();
+                    listed = fits && !es[le].ovf;
+                }
+                if (need_rows && live && !skip) phase2(row, F, want_acc, listed);
+                if constexpr (RESO) {
+                    // next detection: my conflict row cleared (its readers are past the barrier above), the list counters
+                    // by the agent thread (their readers: `fits` above, before the barrier)
+                    if (live) { px_cr[2 * i] = 0u; px_cr[2 * i + 1] = 0u; }
+                    if (valid && i == 0) { es[le].nC = 0; es[le].nR = 0; }
+                }
             } else {
 
             if (live && !skip) {

@@ -23,7 +23,21 @@ static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
     if (tr) {
         const int i = tr->row;
         double vr2 = vrel[0] * vrel[0] + vrel[1] * vrel[1], vr = sqrt(vr2);
-        double k = (dist + vr * fabs(tcpa)) * rpz_m / (fmax(fabs(tcpa), 1e-3) * (dabsH <= 10.0 ? dist : dabsH));
+        /* Conditioning of this pair's displacement w.r.t. the rounding of its INPUTS.  A precision with unit roundoff
+           eps holds positions to eps * Rabs (Rabs: distance of the pair from the env's coordinate origin, the agent) and
+           velocities to eps * V (V: the larger ground speed) -- absolute errors that do not shrink with the pair's
+           range or relative speed.  First order, with  tcpa = -(r.w)/|w|^2,  dcpa = r + w tcpa,
+           dv = (rpz_m / erratum - |dcpa|) dcpa / (|tcpa| |dcpa|):
+             d_tcpa = Rabs / vr + V (dist / vr^2 + |tcpa| / vr)                                    [eps s]
+             d_dcpa = Rabs + V |tcpa| + vr d_tcpa                                                  [eps m]
+             kappa  = (rpz_m / |tcpa|) (d_tcpa / |tcpa| + d_dcpa / |dcpa|)                         [eps m/s]
+           Near-parallel pairs inside or near the zone (vr -> 0) and pairs at their CPA (tcpa -> 0) are ill-conditioned
+           in any precision; |dv error| <~ eps * kappa. */
+        double V = fmax(sqrt(v1[0] * v1[0] + v1[1] * v1[1]), sqrt(v2[0] * v2[0] + v2[1] * v2[1]));
+        double Rabs = fmax(tr->rabs, dist), at = fmax(fabs(tcpa), 1e-3), vrc = fmax(vr, 1e-3);
+        double d_t = Rabs / vrc + V * (dist / (vrc * vrc) + at / vrc);
+        double d_c = Rabs + V * at + vrc * d_t;
+        double k = (rpz_m / at) * (d_t / at + d_c / (dabsH <= 10.0 ? dist : dabsH));
         if (tr->kappa && !(k <= tr->kappa[i])) tr->kappa[i] = k;            /* NaN sticks */
         /* thresholds of this function: |dCPA_h| <= 10 m (an ABSOLUTE distance whose fp32 rounding error scales with the
            pair's range, so its margin is taken relative to the zone radius like the detection's own dCPA threshold),
@@ -106,7 +120,11 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
             if (cfg->reso_on) {
                 double v2[3] = { u[j], v[j], A(F_VS, j) };
                 double dv[3], tsolV;
-                if (tr) tr->row = i;
+                if (tr) {
+                    /* range of the pair's far end from the env's coordinate origin (aircraft 0: the fp32 records are relative to it) */
+                    double x0 = C_RE * C_D2R * (A(F_LON, i) - A(F_LON, 0)) * cos(C_D2R * A(F_LAT, 0)), y0 = C_RE * C_D2R * (A(F_LAT, i) - A(F_LAT, 0));
+                    tr->row = i; tr->rabs = sqrt(x0 * x0 + y0 * y0) + dist;
+                }
                 mvp_pair(qdr, dist, tcpa, tin, A(F_ALT, i), A(F_ALT, j), v1, v2,
                          cfg->rpz, cfg->hpz, cfg->dtlook, cfg->resofach, cfg->resofacv, dv, &tsolV, tr);
                 dv[2] = 0.5 * dv[2];

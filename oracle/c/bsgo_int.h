@@ -49,7 +49,7 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
  * kappa [n]: per ownship row, the largest amplification MVP applies to a relative input rounding over all substeps
  *   and conflict pairs [m/s]: (dist + |v_rel||tCPA|) rpz_m / (|tCPA| |dCPA_h|), or with dist in place of |dCPA_h| in
  *   the perpendicular-escape branch (|dCPA_h| <= 10 m), whose direction comes from the relative position alone. */
-typedef struct { double eps; uint8_t *near_conf, *near_los; double *res_margin, *kappa; int row; } bsgo_trace;
+typedef struct { double eps; uint8_t *near_conf, *near_los; double *res_margin, *kappa; int row; double rabs; } bsgo_trace;
 void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bsgo_row *rows, bsgo_trace *tr);
 void bsgo_pair(double lati, double loni, double alti, double ui, double vi, double vsi,
                double latj, double lonj, double altj, double uj, double vj, double vsj,

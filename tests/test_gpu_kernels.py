@@ -397,3 +397,43 @@ def test_sector_waypoints_follow_the_sorted_law():
     h_frac = np.array([arc_fraction(h_ev[e], h_ev[e, EV['wpt_x']], h_ev[e, EV['wpt_y']]) for e in range(E)])
     from scipy import stats
     assert stats.ks_2samp(frac * (nac + 1), h_frac * (h_nac + 1)).pvalue > 1e-3
+
+
+@pytest.mark.parametrize('kind,N', [(2, 50), (0, 20), (2, 64), (2, 33)])
+def test_pair_work_list_equals_owner_walk(kind, N):
+    """Resolution kernels (fp32, N <= 64): the env's unordered conflicting / resolving pairs are evaluated once each from
+    a work list and both owners pick the result up (ownship j: the exact negative).  The fallback in which every owner
+    evaluates its own row (BSG_FORCE_WALK; also taken when an env overflows the list) must give the same bits -- state,
+    resopairs rows, observations and CD rows, over chained steps with MVP active."""
+    import os
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    E = 192
+    rng = np.random.default_rng(5)
+    cores = [BsgCore(kind, E, N, precision='fp32', asas_on=True, reso_on=True, reso_off_own=True, cd_outputs=True) for _ in range(2)]
+    for c in cores:
+        c.reset(seed=17)
+    na = 2 if kind == 2 else 1
+    nres = 0
+    try:
+        for s in range(12):
+            act = torch.as_tensor(rng.uniform(-1, 1, (E, na)).astype(np.float32), device='cuda')
+            outs = []
+            for w, c in enumerate(cores):
+                if w: os.environ['BSG_FORCE_WALK'] = '1'
+                else: os.environ.pop('BSG_FORCE_WALK', None)
+                c.step(act)
+                torch.cuda.synchronize()
+                ac, reso, nac, ev = c.get_state()
+                outs.append((ac, reso, c.obs.cpu().numpy(), {k: v.cpu().numpy() for k, v in c.cd.items()}))
+            (a0, r0, o0, cd0), (a1, r1, o1, cd1) = outs
+            assert np.array_equal(r0, r1), f"step {s}: resopairs rows differ"
+            assert np.array_equal(a0, a1, equal_nan=True), f"step {s}: aircraft state differs"
+            assert np.array_equal(o0, o1, equal_nan=True), f"step {s}: observations differ"
+            for k in cd0:
+                assert np.array_equal(cd0[k], cd1[k], equal_nan=True), (s, k)
+            nres += int((r0 != 0).sum())
+    finally:
+        os.environ.pop('BSG_FORCE_WALK', None)
+        for c in cores:
+            c.close()
+    assert nres > 0, "no pair in resolution: the test did not exercise MVP"

@@ -16,6 +16,7 @@ from parity_helpers import env_threshold_margin
 
 pytestmark = pytest.mark.gpu
 RT64, RT32, EPS32 = 1e-12, 1e-5, 2e-4
+KAPPA0 = 1e5          # MVP conditioning [eps m/s] beyond which a pair is enumerated as ill-conditioned (oracle/c/bsgo_asas.c)
 KIND = {'H': 0, 'V': 1, 'S': 2}
 
 
@@ -188,14 +189,36 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
             fa_f = (np.nan_to_num(dtrk) > 0.05 + np.degrees(dv_tol / tas_o)) | (np.nan_to_num(dtas) > 0.05 + dv_tol)
             fa = fa_d | fa_f
             act_flip = fa.any(1)
-            near_res = tr['res_margin'] < EPS32
-            unexplained_res = act_flip & ~(fa & near_res).any(1) & ~nanenv
-            print(f"[kind {kind} step {s}] resolution-state flips enumerated (env: flipped aircraft, discrete?, dtrk, dtas, kappa, margin): "
-                  f"{[(int(e), [(int(j), bool(fa_d[e, j]), float(np.round(dtrk[e, j], 4)), float(np.round(dtas[e, j], 4)), float(np.round(kap[e, j], 1)), float(np.round(tr['res_margin'][e, j], 7))) for j in np.where(fa[e])[0]]) for e in np.where(act_flip)[0][:16]]}; "
+            # explained at the source: within EPS32 of a threshold, or resolving an ILL-CONDITIONED pair -- kappa >= KAPPA0
+            # (near-parallel pairs inside / near the zone, pairs at their CPA: a velocity rounding of 1e-5 m/s moves the
+            # commanded velocity by centimetres per second, and the next substep feeds that back)
+            near_res = (tr['res_margin'] < EPS32) | (kap >= KAPPA0)
+            # a flip travels: an aircraft that resolves against a partner whose own state flipped (or that sits at a
+            # threshold) follows a different solution from the next substep on.  So a flipped aircraft is explained when
+            # it IS at a threshold / ill-conditioned, or is connected to such an aircraft through pairs that are / were in
+            # resolution during the step (pre- and post-step resopairs rows of either side)
+            pre_reso = pre[1]
+            rows = pre_reso | o_reso | reso1
+            expl = near_res.copy()
+            for _ in range(4):
+                for e in np.where(act_flip)[0]:
+                    for j in np.where(fa[e] & ~expl[e])[0]:
+                        partners = [q for q in range(N) if (int(rows[e, j]) >> q) & 1 or (int(rows[e, q]) >> j) & 1]
+                        if any(expl[e, q] for q in partners):
+                            expl[e, j] = True
+            unexplained_res = act_flip & (fa & ~expl).any(1) & ~nanenv
+            def why(e):
+                return [(int(j), bool(fa_d[e, j]), float(np.round(dtrk[e, j], 4)), float(np.round(dtas[e, j], 4)), float(np.round(kap[e, j], 1)),
+                         float(np.round(tr['res_margin'][e, j], 7)), hex(int(pre_reso[e, j])), hex(int(o_reso[e, j])), hex(int(reso1[e, j])))
+                        for j in np.where(fa[e])[0]]
+            print(f"[kind {kind} step {s}] resolution-state flips enumerated (env: flipped aircraft, discrete?, dtrk, dtas, kappa, margin, "
+                  f"resopairs pre / oracle / fp32; near-threshold aircraft of the env): "
+                  f"{[(int(e), why(e), np.where(near_res[e])[0].tolist()) for e in np.where(act_flip)[0][:16]]}; "
                   f"aircraft within EPS32 of a resolution threshold: {int(near_res.sum())} of {near_res.size}")
             assert not unexplained_res.any(), f"step {s}: resolution-state flips with no near-threshold aircraft, envs {np.where(unexplained_res)[0]}"
             assert act_flip.sum() <= max(4, E // 25), f"{act_flip.sum()} envs with a resolution-state flip"
             kappa = np.nan_to_num(tr['kappa'], nan=0.0, posinf=0.0).max(1)
+            print(f"[kind {kind} step {s}] envs holding an ill-conditioned pair (kappa >= {KAPPA0:g}): {int((kappa >= KAPPA0).sum())} of {E}")
         unexplained = flip & ~thr & ~act_flip & ~nanenv
         assert not unexplained.any(), f"step {s}: unexplained reward / termination flips in envs {np.where(unexplained)[0]}"
         skip = flip | nanenv | act_flip
@@ -205,7 +228,7 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
         # of the observation (Sector 32 m/s, sector_cr_env.py:305; Horizontal 150 m/s, horizontal_cr_env.py:206)
         vnorm = 32.0 if kind == 2 else 150.0
         err = np.abs(obs - o_obs)
-        widen = (4 * 2.0 ** -24 / vnorm) * kappa
+        widen = (2 * 2.0 ** -24 / vnorm) * np.minimum(kappa, KAPPA0)
         tol = obs_tol32(kind, o_obs) + widen[:, None]
         ratio = np.where(skip[:, None], 0, err / tol)
         bad = (err > tol) & ~skip[:, None]
