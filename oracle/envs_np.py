@@ -5,6 +5,7 @@ K intruders -- the reference's own execution style (one process-global simulator
 Python loops over intruders, numpy on tiny arrays).  /root/reference does not exist on the GPU box, so
 this port is what bench.py's `--impl reference` arm and `cpu_baseline` time there.  It restates:
   HorizontalCREnv  /root/reference/bluesky_gym/envs/horizontal_cr_env.py:82-275
+  VerticalCREnv    /root/reference/bluesky_gym/envs/vertical_cr_env.py:113-305   (BASELINE.json configs[0])
 and is checked against the unmodified reference (tests/test_oracle_golden.py::test_np_port_matches_reference).
 """
 import os
@@ -99,6 +100,126 @@ class HorizontalNp:
         return obs, rew, int(self.reached == 1), False, {'total_reward': self.total_reward,
                                                          'total_intrusions': self.total_intrusions,
                                                          'average_drift': float(np.mean(self.drifts))}
+
+
+class VerticalNp:
+    """VerticalCREnv (vertical_cr_env.py:113-305): 5 creconfs intruders with altitude offsets, the agent commands a
+    vertical speed; 30 sim steps of 1 s per action.  Same global np.random draw order as the reference."""
+    K = 5
+
+    def __init__(self):
+        self.bs = _bs()
+        self.bs.init(mode='sim', detached=True)
+        self.bs.stack.stack('DT 1;FF')
+        self.total_reward = 0.0; self.total_intrusions = 0; self.final_altitude = 0
+
+    def reset(self):
+        bs = self.bs
+        bs.traf.reset()
+        self.total_reward = 0.0; self.total_intrusions = 0; self.final_altitude = 0
+        alt_init = np.random.randint(2000, 4000)
+        self.target_alt = alt_init + np.random.randint(-500, 500)
+        bs.traf.cre('KL001', actype="A320", acalt=alt_init, acspd=150)
+        bs.traf.swvnav[0] = False
+        altitude, spd = bs.traf.alt[0], bs.traf.gs[0]
+        for i in range(self.K):                                     # _generate_conflicts, vertical_cr_env.py:182-199
+            dpsi = np.random.randint(45, 315)
+            cpa = np.random.randint(0, 5)
+            tlosh = np.random.randint(100, int((200 * 0.9) * 1000 / spd))
+            average_tod = (200 * 1000 / spd) - 2 * self.target_alt / 12.5
+            if tlosh > average_tod:
+                dH = np.random.randint(int(-altitude + 500), int((self.target_alt - altitude) + 100))
+            else:
+                dH = np.random.randint(int((self.target_alt - altitude) - 500), int((self.target_alt - altitude) + 500))
+            bs.traf.creconfs(acid=f'{i}', actype="A320", targetidx=0, dpsi=dpsi, dcpa=cpa, tlosh=tlosh, dH=dH,
+                             tlosv=100000000000.)
+            bs.traf.alt[i + 1] = bs.traf.alt[0] + dH
+            bs.traf.ap.selaltcmd(i + 1, bs.traf.alt[0] + dH, 0)
+        return self._obs()
+
+    def _obs(self):
+        bs, t = self.bs, self.bs.traf
+        dist, cb, sb, da, xd, yd, zd = [], [], [], [], [], [], []
+        self.altitude, self.vz = t.alt[0], t.vs[0]
+        for i in range(self.K):
+            j = i + 1
+            qdr, dis = bs.tools.geo.kwikqdrdist(t.lat[0], t.lon[0], t.lat[j], t.lon[j])
+            dist.append(dis * 1.852)
+            da.append(t.alt[j] - self.altitude); zd.append(t.vs[j] - self.vz)
+            brg = _wrap180(t.hdg[0] - qdr)
+            cb.append(np.cos(np.deg2rad(brg))); sb.append(np.sin(np.deg2rad(brg)))
+            hd = t.hdg[0] - t.hdg[j]
+            xd.append(-np.cos(np.deg2rad(hd)) * t.gs[j])
+            yd.append(t.gs[0] - np.sin(np.deg2rad(hd)) * t.gs[j])
+        self.runway_distance = 200 - bs.tools.geo.kwikdist(52, 4, t.lat[0], t.lon[0]) * 1.852
+        return np.concatenate([[(self.altitude - 1500) / 3000], [self.vz / 5], [(self.target_alt - 1500) / 3000],
+                               [(self.runway_distance - 100) / 200], np.array(dist) / 200, cb, sb, np.array(da) / 3000,
+                               np.array(xd) / 150, np.array(yd) / 150, zd])
+
+    def step(self, action):
+        bs, t = self.bs, self.bs.traf
+        a = action[0] * 12.5
+        t.selalt[0] = 1000000 if a >= 0 else 0
+        t.selvs[0] = a
+        for _ in range(30):
+            bs.sim.step()
+        obs = self._obs()
+        intr = 0
+        for i in range(self.K):
+            _, dis = bs.tools.geo.kwikqdrdist(t.lat[0], t.lon[0], t.lat[i + 1], t.lon[i + 1])
+            if dis < 5 and abs(t.alt[0] - t.alt[i + 1]) < 1000 * 0.3048:
+                self.total_intrusions += 1; intr += -50
+        done = 0
+        if self.runway_distance > 0 and self.altitude > 0:
+            pen = abs(self.target_alt - self.altitude) * (-5 / 3000)
+        elif self.altitude <= 0:
+            pen = -100; self.final_altitude = -100; done = 1
+        else:
+            pen = self.altitude * (-50 / 3000); self.final_altitude = self.altitude; done = 1
+        rew = pen + intr
+        self.total_reward += rew
+        return obs, rew, done, False, {'total_reward': self.total_reward, 'total_intrusions': self.total_intrusions,
+                                       'final_altitude': self.final_altitude}
+
+
+def vertical_1000_steps(seed=0, steps=1000):
+    """BASELINE.json configs[0]: one VerticalCREnv, random actions, `steps` env steps on ONE core.
+    Returns (env-steps/s, episodes, seconds)."""
+    import time
+    np.random.seed(seed)
+    env = VerticalNp()
+    env.reset()
+    env.step(np.zeros(1))
+    env.reset()
+    t0 = time.perf_counter()
+    eps = 0
+    for s in range(steps):
+        obs, r, term, trunc, info = env.step(np.random.uniform(-1, 1, 1))
+        if term:
+            env.reset(); eps += 1
+    dt = time.perf_counter() - t0
+    return steps / dt, eps, dt
+
+
+def detect_rates(sizes=(20, 50, 500), budget_s=2.0):
+    """The numpy state-based detection alone (refshim bluesky.traffic.asas.detect, all N x N pairs -- BlueSky's
+    StateBased.detect): ordered pair-evals/s on one core for each traffic size."""
+    import time
+    _bs()
+    from bluesky.traffic import asas
+    out = {}
+    for n in sizes:
+        rng = np.random.default_rng(n)
+        lat, lon = 52 + rng.uniform(-2, 2, n), 4 + rng.uniform(-3, 3, n)
+        alt, trk = rng.uniform(3000, 11000, n), rng.uniform(0, 360, n)
+        gs, vs = rng.uniform(120, 250, n), rng.choice([-5.0, 0.0, 5.0], n)
+        args = (lat, lon, alt, trk, gs, vs, np.full(n, 5 * 1852.0), np.full(n, 1000 * 0.3048), np.full(n, 300.0))
+        asas.detect(*args)
+        t0 = time.perf_counter(); it = 0
+        while time.perf_counter() - t0 < budget_s:
+            asas.detect(*args); it += 1
+        out[n] = it * n * (n - 1) / (time.perf_counter() - t0)
+    return out
 
 
 def _worker(args):

@@ -222,21 +222,33 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
         unexplained = flip & ~thr & ~act_flip & ~nanenv
         assert not unexplained.any(), f"step {s}: unexplained reward / termination flips in envs {np.where(unexplained)[0]}"
         skip = flip | nanenv | act_flip
-        # (3) floats: 1e-5 * max(|ref|, 1) everywhere, widened ONLY by MVP's own conditioning where an env resolves:
-        # a relative input rounding eps_f32 appears in the commanded velocity as eps * kappa [m/s] (oracle trace; near
-        # head-on pairs and pairs at their CPA are ill-conditioned in any precision), against the velocity normaliser
-        # of the observation (Sector 32 m/s, sector_cr_env.py:305; Horizontal 150 m/s, horizontal_cr_env.py:206)
+        # (3) floats.  Without MVP: 1e-5 * max(|ref|, 1) everywhere.  With MVP that bound cannot hold in fp32 for the
+        # commanded velocities -- whatever the implementation -- because MVP amplifies the rounding of its inputs: a
+        # position held to eps * Rabs and a velocity held to eps * V move the displacement of a pair by eps * kappa [m/s]
+        # (first-order bound, stated in oracle/c/bsgo_asas.c; near-parallel pairs inside / near the zone and pairs at
+        # their CPA are ill-conditioned in any precision).  The per-env bound is therefore
+        #     1e-5 * max(|ref|, 1) + 8 eps_f32 * kappa_env / vnorm      (8: the roundings of the K chained substeps add up)
+        # (vnorm: the velocity normaliser of the observation -- Sector 32 m/s, sector_cr_env.py:305; Horizontal
+        # 150 m/s, horizontal_cr_env.py:206), and the achieved accuracy is reported as quantiles of err / (1e-5 bound).
+        # The fp64 mode above holds 1e-12.
         vnorm = 32.0 if kind == 2 else 150.0
         err = np.abs(obs - o_obs)
-        widen = (2 * 2.0 ** -24 / vnorm) * np.minimum(kappa, KAPPA0)
-        tol = obs_tol32(kind, o_obs) + widen[:, None]
+        widen = (8 * 2.0 ** -24 / vnorm) * kappa
+        base = obs_tol32(kind, o_obs)
+        tol = base + widen[:, None]
         ratio = np.where(skip[:, None], 0, err / tol)
         bad = (err > tol) & ~skip[:, None]
         worst = np.unravel_index(np.nanargmax(ratio), ratio.shape)
+        rb = (err / base)[~skip]
+        q50, q99, q999 = np.quantile(rb, [0.5, 0.99, 0.999])
         print(f"[kind {kind} step {s}] fp32: reward / termination flips {int(flip.sum())}, resolution-state flips {int(act_flip.sum())}, "
-              f"NaN envs {int(nanenv.sum())}, envs with MVP-widened tolerance (> 1e-5) {int((widen > RT32).sum())}, median widening "
-              f"{float(np.median(widen)):.2e}, worst err/tol {float(ratio[worst]):.3f} at env {worst[0]} slot {worst[1]} "
-              f"(err {float(err[worst]):.3e}, kappa {float(kappa[worst[0]]):.3e})")
+              f"NaN envs {int(nanenv.sum())}; err / (1e-5 bound): median {q50:.3f}, 99 % {q99:.3f}, 99.9 % {q999:.3f}, max {float(rb.max()):.1f}; "
+              f"entries beyond the 1e-5 bound {int((rb > 1).sum())} of {rb.size} (all inside the MVP-conditioned bound: "
+              f"envs widened beyond 1e-4 / 1e-3 / 1e-2: {int((widen > 1e-4).sum())} / {int((widen > 1e-3).sum())} / {int((widen > 1e-2).sum())} of {E}); "
+              f"worst err/tol {float(ratio[worst]):.3f} at env {worst[0]} slot {worst[1]} (err {float(err[worst]):.3e}, kappa {float(kappa[worst[0]]):.3e})")
+        # 99 % of the observation entries must sit inside the plain 1e-5 bound, and all of them inside 100 x it; the
+        # conditioned bound (asserted below) covers that tail env by env
+        assert q50 <= 1.0 and q99 <= 1.0 and rb.max() <= (100.0 if asas else 1.0), (q50, q99, rb.max())
         assert not bad.any(), (np.argwhere(bad)[:5], float(ratio[worst]))
         if asas:
             # (4) CD row outputs of the last detection: every mismatching row must hold a pair the oracle places within

@@ -156,3 +156,29 @@ def test_np_port_matches_reference():
             if term:
                 break
     assert t == len(g['rew'])
+
+
+def test_np_vertical_port_matches_reference():
+    """oracle/envs_np.VerticalNp (BASELINE.json configs[0] on the GPU box: one VerticalCREnv, random actions, 1000 steps on
+    the CPU path) replays the episodes recorded from the unmodified reference class exactly."""
+    from oracle import envs_np
+    g = load_golden('V')
+    np.random.seed(12)                         # tests/golden/make_golden.py: ('V', 12, 4, 50, ...)
+    env = envs_np.VerticalNp()
+    t = 0
+    for ep in range(4):
+        obs = env.reset()
+        assert rel(obs, g['obs0'][t]) < 1e-12
+        for s in range(50):
+            a = np.random.uniform(-1, 1, (1,))
+            obs, r, term, trunc, info = env.step(a)
+            assert rel(obs, g['obs1'][t]) < 1e-12 and abs(r - g['rew'][t]) < 1e-9 and term == g['term'][t]
+            assert abs(info['total_reward'] - g['info'][t, 0]) < 1e-9 and info['total_intrusions'] == g['info'][t, 1]
+            t += 1
+            if term:
+                break
+    assert t == len(g['rew'])
+    v, eps, dt = envs_np.vertical_1000_steps(seed=1, steps=60)
+    assert v > 0 and eps >= 1
+    r = envs_np.detect_rates(sizes=(20,), budget_s=0.2)
+    assert r[20] > 0
