@@ -83,6 +83,8 @@ SYMBOLS = {
     'bsg_step': (_I, [_VP, _VP, C.POINTER(StepOut), _VP]),
     'bsg_step_host': (_I, [_VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_host_views': (_I, [_VP, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_step_host_begin': (_I, [_VP, _VP]),
+    'bsg_step_host_wait': (_I, [_VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_pack': (_I, [C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP, _VP]),
     'bsg_cd_sweep': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_init': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP]),

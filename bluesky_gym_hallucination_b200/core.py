@@ -184,17 +184,37 @@ class BsgCore:
                                        _ptr(truncated), _ptr(info)), self.h)
 
     def host_views(self):
-        """numpy views of the pinned host block step_host fills: (obs [E, obs_dim], reward [E], terminated [E],
-        truncated [E], info [E, 4]).  Valid until the next step_host / close."""
-        if getattr(self, '_views', None) is None:
-            p = [C.c_void_p() for _ in range(5)]
-            L.check(self.lib.bsg_host_views(self.h, *[C.byref(x) for x in p]), self.h)
-            ct = C.c_double if self.fp64 else C.c_float
-            arr = lambda ptr, cty, *shape: np.ctypeslib.as_array((cty * int(np.prod(shape))).from_address(ptr.value)).reshape(shape)
-            E = self.E
-            self._views = (arr(p[0], ct, E, max(self.obs_dim, 1)), arr(p[1], ct, E), arr(p[3], C.c_int32, E),
-                           arr(p[4], C.c_int32, E), arr(p[2], ct, E, 4))
-        return self._views
+        """numpy views of the pinned host block the last step_host / step_host_wait filled: (obs [E, obs_dim], reward [E],
+        terminated [E], truncated [E], info [E, 4]).  The handle alternates between two blocks: valid until the second
+        next step_host / close."""
+        p = [C.c_void_p() for _ in range(5)]
+        L.check(self.lib.bsg_host_views(self.h, *[C.byref(x) for x in p]), self.h)
+        cache = self.__dict__.setdefault('_view_cache', {})
+        if p[0].value not in cache:
+            cache[p[0].value] = self._views_of(p)
+        return cache[p[0].value]
+
+    def _views_of(self, p):
+        ct = C.c_double if self.fp64 else C.c_float
+        arr = lambda ptr, cty, *shape: np.ctypeslib.as_array((cty * int(np.prod(shape))).from_address(ptr.value)).reshape(shape)
+        E = self.E
+        return (arr(p[0], ct, E, max(self.obs_dim, 1)), arr(p[1], ct, E), arr(p[3], C.c_int32, E),
+                arr(p[4], C.c_int32, E), arr(p[2], ct, E, 4))
+
+    def step_host_begin(self, actions):
+        """Enqueue one end-to-end step (host actions -> pinned H2D -> launch -> D2H into a pinned block) and return."""
+        L.check(self.lib.bsg_step_host_begin(self.h, _ptr(actions)), self.h)
+
+    def step_host_wait(self):
+        """Wait for the oldest step begun; returns (obs, reward, terminated, truncated, info) views of its pinned block
+        (valid until two more begins)."""
+        p = [C.c_void_p() for _ in range(5)]
+        L.check(self.lib.bsg_step_host_wait(self.h, *[C.byref(x) for x in p]), self.h)
+        key = p[0].value
+        cache = self.__dict__.setdefault('_view_cache', {})
+        if key not in cache:
+            cache[key] = self._views_of(p)
+        return cache[key]
 
     def step_host_views(self, actions):
         """End-to-end call with a HOST action array; results are returned as views of the pinned block

@@ -71,9 +71,12 @@ static int refresh_gs(bsg_handle *h) {
 // the pinned / device output block of bsg_step_host; sized by obs_dim (which bsg_set_wind can grow by two slots)
 static int alloc_out(bsg_handle *h) {
     if (h->h_out) { cudaFreeHost(h->h_out); h->h_out = nullptr; }
+    if (h->h_outs[1]) { cudaFreeHost(h->h_outs[1]); h->h_outs[1] = nullptr; }
     if (h->d_out) { cudaFree(h->d_out); h->d_out = nullptr; }
     h->out_bytes = (size_t)h->cfg.num_envs * (h->obs_dim + 1 + 4) * rsize(h) + (size_t)h->cfg.num_envs * 2 * sizeof(int32_t);
     CK(h, cudaMallocHost(&h->h_out, h->out_bytes));
+    CK(h, cudaMallocHost(&h->h_outs[1], h->out_bytes));
+    h->h_outs[0] = h->h_out;
     CK(h, cudaMalloc(&h->d_out, h->out_bytes));
     return BSG_OK;
 }
@@ -198,6 +201,9 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     // host-buffer step: [obs | reward | info | terminated | truncated] in one pinned block
     h->act_bytes = (size_t)E * (h->act_dim > 0 ? h->act_dim : 1) * rs;
     CK(h, cudaMallocHost(&h->h_act, h->act_bytes));
+    CK(h, cudaMallocHost(&h->h_acts[1], h->act_bytes));
+    h->h_acts[0] = h->h_act;
+    for (int q = 0; q < 2; q++) CK(h, cudaEventCreateWithFlags(&h->hev[q], cudaEventDisableTiming));
     CK(h, cudaMalloc(&h->d_act, h->act_bytes));
     { int rc = alloc_out(h); if (rc != BSG_OK) return rc; }
     CK(h, cudaStreamCreateWithFlags(&h->hs, cudaStreamNonBlocking));
@@ -244,6 +250,9 @@ int bsg_destroy(bsg_handle *h) {
     cudaFree(h->pos); cudaFree(h->st); cudaFree(h->reso); cudaFree(h->nac); cudaFree(h->ev); cudaFree(h->stage64);
     cudaFree(h->d_act); cudaFree(h->d_out); cudaFree(h->episode); cudaFree(h->done_buf[0]); cudaFree(h->done_buf[1]); cudaFree(h->nd_rec);
     if (h->h_act) cudaFreeHost(h->h_act);
+    if (h->h_acts[1]) cudaFreeHost(h->h_acts[1]);
+    if (h->h_outs[1]) cudaFreeHost(h->h_outs[1]);
+    for (int q = 0; q < 2; q++) if (h->hev[q]) cudaEventDestroy(h->hev[q]);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->hs) cudaStreamDestroy(h->hs);
     delete h;

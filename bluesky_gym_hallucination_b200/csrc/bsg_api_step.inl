@@ -147,10 +147,9 @@ int bsg_observe(bsg_handle *h, void *obs_dev, void *stream) {
     return launch_step<float>(h, nullptr, &o, 0, 1, (cudaStream_t)stream);
 }
 
-int bsg_host_views(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated) {
-    if (!h) return BSG_ERR_ARG;
+static void host_block_views(bsg_handle *h, void *blk, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated) {
     const size_t rs = rsize(h), E = h->cfg.num_envs;
-    char *s = (char *)h->h_out;
+    char *s = (char *)blk;
     if (obs) *obs = s;
     s += E * h->obs_dim * rs;
     if (reward) *reward = s;
@@ -160,15 +159,22 @@ int bsg_host_views(bsg_handle *h, void **obs, void **reward, void **info, int32_
     if (terminated) *terminated = (int32_t *)s;
     s += E * sizeof(int32_t);
     if (truncated) *truncated = (int32_t *)s;
+}
+
+int bsg_host_views(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated) {
+    if (!h) return BSG_ERR_ARG;
+    host_block_views(h, h->h_outs[h->h_last], obs, reward, info, terminated, truncated);
     return BSG_OK;
 }
 
-int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, int32_t *term, int32_t *trunc, void *info) {
+int bsg_step_host_begin(bsg_handle *h, const void *actions) {
     if (!h || !actions) return BSG_ERR_ARG;
+    if (h->h_pending >= 2) { h->err = "bsg_step_host_begin: two steps already in flight (call bsg_step_host_wait)"; return BSG_ERR_ARG; }
     const bsg_config &g = h->cfg;
     const size_t rs = rsize(h), E = g.num_envs;
     CK(h, cudaSetDevice(g.device));
-    memcpy(h->h_act, actions, h->act_bytes);
+    const int q = h->h_head;
+    memcpy(h->h_acts[q], actions, h->act_bytes);
     // direct mode: the kernel reads the actions from / stores the outputs to the pinned host block itself (unified
     // addressing); the stores are posted over PCIe while later waves of CTAs still compute.  It wins when the launch
     // has many waves (C3: +5 %) and loses on a one-wave launch (C2: -10 %, the stores all land at the end), so the
@@ -177,8 +183,8 @@ int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, i
     const int n_cta = (int)((E + h->epb - 1) / h->epb);
     const bool direct = dir_env ? atoi(dir_env) != 0 : n_cta >= 4096;
     const bool dir = direct && !(h->noise_sigma > 0);          // the noise epilogue reads the observation back
-    if (!dir) CK(h, cudaMemcpyAsync(h->d_act, h->h_act, h->act_bytes, cudaMemcpyHostToDevice, h->hs));
-    char *d = (char *)(dir ? h->h_out : h->d_out);
+    if (!dir) CK(h, cudaMemcpyAsync(h->d_act, h->h_acts[q], h->act_bytes, cudaMemcpyHostToDevice, h->hs));
+    char *d = (char *)(dir ? h->h_outs[q] : h->d_out);
     bsg_step_out o;
     memset(&o, 0, sizeof(o));
     o.obs = d; d += E * h->obs_dim * rs;
@@ -186,22 +192,40 @@ int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, i
     o.info = d; d += E * 4 * rs;
     o.terminated = (int32_t *)d; d += E * sizeof(int32_t);
     o.truncated = (int32_t *)d;
-    const void *act = dir ? h->h_act : h->d_act;
+    const void *act = dir ? h->h_acts[q] : h->d_act;
     int rc = g.precision == BSG_FP64 ? launch_step<double>(h, act, &o, g.substeps, 0, h->hs)
                                      : launch_step<float>(h, act, &o, g.substeps, 0, h->hs);
     if (rc != BSG_OK) return rc;
-    if (!dir) CK(h, cudaMemcpyAsync(h->h_out, h->d_out, h->out_bytes, cudaMemcpyDeviceToHost, h->hs));
-    CK(h, cudaStreamSynchronize(h->hs));
-    const char *s = (const char *)h->h_out;
-    if (obs) memcpy(obs, s, E * h->obs_dim * rs);
-    s += E * h->obs_dim * rs;
-    if (reward) memcpy(reward, s, E * rs);
-    s += E * rs;
-    if (info) memcpy(info, s, E * 4 * rs);
-    s += E * 4 * rs;
-    if (term) memcpy(term, s, E * sizeof(int32_t));
-    s += E * sizeof(int32_t);
-    if (trunc) memcpy(trunc, s, E * sizeof(int32_t));
+    if (!dir) CK(h, cudaMemcpyAsync(h->h_outs[q], h->d_out, h->out_bytes, cudaMemcpyDeviceToHost, h->hs));
+    CK(h, cudaEventRecord(h->hev[q], h->hs));
+    h->h_head = q ^ 1; h->h_pending++;
+    return BSG_OK;
+}
+
+int bsg_step_host_wait(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated) {
+    if (!h) return BSG_ERR_ARG;
+    if (h->h_pending <= 0) { h->err = "bsg_step_host_wait: no step in flight"; return BSG_ERR_ARG; }
+    const int q = h->h_pending == 2 ? h->h_head : h->h_head ^ 1;      // the oldest step in flight
+    CK(h, cudaEventSynchronize(h->hev[q]));
+    h->h_pending--; h->h_last = q;
+    host_block_views(h, h->h_outs[q], obs, reward, info, terminated, truncated);
+    return BSG_OK;
+}
+
+int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, int32_t *term, int32_t *trunc, void *info) {
+    if (!h || !actions) return BSG_ERR_ARG;
+    if (h->h_pending) { h->err = "bsg_step_host: steps begun with bsg_step_host_begin are still in flight"; return BSG_ERR_ARG; }
+    int rc = bsg_step_host_begin(h, actions);
+    if (rc != BSG_OK) return rc;
+    void *po, *pr, *pi; int32_t *pt, *pu;
+    rc = bsg_step_host_wait(h, &po, &pr, &pi, &pt, &pu);
+    if (rc != BSG_OK) return rc;
+    const size_t rs = rsize(h), E = h->cfg.num_envs;
+    if (obs) memcpy(obs, po, E * h->obs_dim * rs);
+    if (reward) memcpy(reward, pr, E * rs);
+    if (info) memcpy(info, pi, E * 4 * rs);
+    if (term) memcpy(term, pt, E * sizeof(int32_t));
+    if (trunc) memcpy(trunc, pu, E * sizeof(int32_t));
     return BSG_OK;
 }
 

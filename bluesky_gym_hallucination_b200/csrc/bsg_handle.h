@@ -18,6 +18,10 @@ struct bsg_handle {
     double *stage64 = nullptr;        // [E][BSG_NF][N] interchange staging (device)
     // host-buffer step: pinned staging + device mirrors
     void *h_act = nullptr, *h_out = nullptr, *d_act = nullptr, *d_out = nullptr;
+    // host-buffer step, pipelined form: two pinned action / output blocks, one event each (bsg_step_host_begin / _wait)
+    void *h_acts[2] = { nullptr, nullptr }, *h_outs[2] = { nullptr, nullptr };
+    cudaEvent_t hev[2] = { nullptr, nullptr };
+    int h_head = 0, h_pending = 0, h_last = 0;       // next block to fill, steps begun and not yet waited for, last waited block
     size_t out_bytes = 0, act_bytes = 0;
     cudaStream_t hs = nullptr;
     uint32_t *episode = nullptr;

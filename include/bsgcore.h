@@ -154,8 +154,8 @@ int bsg_observe(bsg_handle *h, void *obs_dev, void *stream);
 int bsg_step(bsg_handle *h, const void *actions_dev /* real [E][act_dim] */, const bsg_step_out *out, void *stream);
 /* same through host buffers (pinned staging, copies inside): the end-to-end call of the plugin boundary */
 /* The pinned host block bsg_step_host fills (obs | reward | info[4] | terminated | truncated), as pointers: a caller
- * that passes NULL output pointers to bsg_step_host reads the results here without another host copy.  Valid
- * until the next bsg_step_host / bsg_destroy on this handle. */
+ * that passes NULL output pointers to bsg_step_host reads the results here without another host copy (the block of the
+ * step waited for last).  Valid until the second next bsg_step_host(_begin) / bsg_destroy on this handle. */
 int bsg_host_views(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated);
 /* bsg_step_host moves the data in one of two ways, same results bit for bit: copy mode (actions H2D, one launch, one
  * D2H of the output block) or direct mode (the kernel reads the actions from and stores the outputs to the pinned
@@ -163,6 +163,13 @@ int bsg_host_views(bsg_handle *h, void **obs, void **reward, void **info, int32_
  * environment variable BSG_HOST_DIRECT=0/1 forces one of them. */
 int bsg_step_host(bsg_handle *h, const void *actions_host, void *obs_host, void *reward_host,
                   int32_t *terminated_host, int32_t *truncated_host, void *info_host);
+/* The same call split in two, for a host that has other work while the step is in flight (a second handle / GPU to
+ * feed, the previous step's bookkeeping): bsg_step_host_begin copies the actions into one of the handle's TWO pinned
+ * blocks and enqueues H2D + the launch + D2H on the handle's own stream, then returns; bsg_step_host_wait blocks until
+ * the OLDEST step in flight has landed and returns pointers into its pinned block (valid until two more begins).  At
+ * most two steps may be in flight per handle; bsg_step_host = begin + wait + the optional copies. */
+int bsg_step_host_begin(bsg_handle *h, const void *actions_host);
+int bsg_step_host_wait(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated);
 
 /* pack fp32 CD records (8 floats per aircraft) from SoA device arrays [E][N]; origin = (lat0, lon0) degrees */
 int bsg_cd_pack(int32_t num_envs, int32_t num_ac, const double *lat_dev, const double *lon_dev,

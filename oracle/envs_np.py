@@ -253,3 +253,56 @@ def timed_sample(n_intruders, asas, steps_per_proc, procs, seed=0):
     total = sum(r[0] for r in res)
     busy = max(r[1] for r in res)
     return total / busy, total, wall
+
+
+def _pool_worker(conn, seed, n_intruders, asas):
+    import time
+    np.random.seed(seed)
+    env = HorizontalNp(n_intruders, asas)
+    env.reset()
+    env.step(np.zeros(1))
+    conn.send('ready')
+    while True:
+        n = conn.recv()
+        if n is None:
+            break
+        t0 = time.perf_counter()
+        for _ in range(n):
+            obs, r, term, trunc, info = env.step(np.random.uniform(-1, 1, 1))
+            if term:
+                env.reset()
+        conn.send(time.perf_counter() - t0)
+    conn.close()
+
+
+class WorkerPool:
+    """`procs` persistent single-env processes (one simulator singleton each: the reference's SubprocVecEnv scaling
+    style, scripts/multi_processing_example.py:51-53).  step(n): every process advances its env by n env-steps; returns
+    the wall-clock seconds of the slowest one including the pipe round trip."""
+
+    def __init__(self, procs, n_intruders, asas, seed=0):
+        import multiprocessing as mp
+        ctx = mp.get_context('fork')
+        self.conns, self.procs = [], []
+        for p in range(procs):
+            a, b = ctx.Pipe()
+            pr = ctx.Process(target=_pool_worker, args=(b, seed + p, n_intruders, asas), daemon=True)
+            pr.start()
+            self.conns.append(a); self.procs.append(pr)
+        for c in self.conns:
+            c.recv()
+
+    def step(self, n):
+        import time
+        t0 = time.perf_counter()
+        for c in self.conns:
+            c.send(n)
+        for c in self.conns:
+            c.recv()
+        return time.perf_counter() - t0
+
+    def close(self):
+        for c in self.conns:
+            c.send(None)
+        for p in self.procs:
+            p.join(timeout=5)

@@ -437,3 +437,37 @@ def test_pair_work_list_equals_owner_walk(kind, N):
         for c in cores:
             c.close()
     assert nres > 0, "no pair in resolution: the test did not exercise MVP"
+
+
+def test_step_host_begin_wait_pipeline():
+    """bsg_step_host_begin / bsg_step_host_wait (two pinned blocks per handle, two steps in flight) return, step by
+    step, exactly what the blocking bsg_step_host returns for the same action sequence; a third begin is refused."""
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    from bluesky_gym_hallucination_b200 import _lib as L
+    E, N, T = 256, 20, 7
+    rng = np.random.default_rng(2)
+    acts = [rng.uniform(-1, 1, (E, 1)).astype(np.float32) for _ in range(T)]
+    cores = [BsgCore(L.KIND_HORIZONTAL, E, N, precision='fp32', asas_on=True) for _ in range(2)]
+    for c in cores:
+        c.reset(seed=8); c.set_autoreset(True, seed=9)
+    ref = []
+    for a in acts:
+        o, r, te, tr, info = cores[0].step_host_views(a)
+        ref.append((o.copy(), r.copy(), te.copy(), tr.copy(), info.copy()))
+    c = cores[1]
+    got = []
+    c.step_host_begin(acts[0])
+    for k in range(1, T):
+        c.step_host_begin(acts[k])                       # two in flight
+        if k == 1:
+            with pytest.raises(L.BsgError):
+                c.step_host_begin(acts[k])
+        got.append(tuple(x.copy() for x in c.step_host_wait()))
+    got.append(tuple(x.copy() for x in c.step_host_wait()))
+    with pytest.raises(L.BsgError):
+        c.step_host_wait()
+    for k in range(T):
+        for x, y in zip(ref[k], got[k]):
+            assert np.array_equal(x, y, equal_nan=True), k
+    for c in cores:
+        c.close()
