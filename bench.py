@@ -27,6 +27,7 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 FLOP_PER_PAIR = 74.0          # algorithmic FP32 flop per ordered CD pair
+EXEC_FLOP_PER_PAIR = 42.0     # executed by the canonical fp32 pair form per UNORDERED pair (csrc/bsg_pair.cuh)
 WORKLOADS = {
     # name: (kind, envs per GPU, aircraft, asas, reso, description)
     'c2': (0, 4096, 20, 1, 0, "HorizontalCREnv-v0 4096 envs x 20 aircraft, state-based CD + CPA obs"),
@@ -332,6 +333,8 @@ def run_envs(ctx, workload, K, W, strong=False, envs=0, cpu=False):
                      "pairs_note": "ordered CD entries (every unordered pair is evaluated once and credited for both aircraft), "
                                    "every substep of the step; envs that start an episode in the step are not credited",
                      "peak_source": "bsg_peak_fp32 FMA chain measured in this run (burst); MEASURED_PEAKS.json holds no FP32 figure",
+                     "executed": {"flop_per_unordered_pair": EXEC_FLOP_PER_PAIR, "frac": EXEC_FLOP_PER_PAIR * 0.5 * pairs_per_launch / (kernel_ms * 1e-3) / 1e12 / peak32,
+                                  "note": "what the SMs execute for the sweep alone: every unordered pair once, 9 FMA + 15 add/mul + 2 MUFU + max3 (42 flop)"},
                      "hbm_achieved_gbs": bytes_per_envstep * E / (kernel_ms * 1e-3) / 1e9,
                      "hbm_peak_gbs": load_peaks().get("hbm_gbs")},
         "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(act_dim * E * 4),
@@ -469,6 +472,16 @@ def run_ndmap(ctx, K, W, envs=0):
     e1.record(); torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / K
     clocks = sampler.stop()
+    # the kernel only WRITES: the ceiling of a write-only stream on this GPU, measured here with a device memset of 1 GiB
+    # (best of 5), beside the COPY figure of MEASURED_PEAKS.json (read + write bytes) the contract's `peak` is
+    wbuf = torch.empty(1 << 30, dtype=torch.uint8, device=dev)
+    wbest = 1e9
+    for _ in range(6):
+        w0, w1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        w0.record(); wbuf.zero_(); w1.record(); torch.cuda.synchronize()
+        wbest = min(wbest, w0.elapsed_time(w1))
+    write_peak = (1 << 30) / (wbest * 1e-3) / 1e9
+    del wbuf
     cells = E * 30 * 64 * 64 * 8
     # algorithmic bytes: occ 1 B per cell + conflict BITMASK 1/8 B per cell + the aircraft records + ncell
     nd_bytes = 1.125 * cells + 24.0 * n * E + 4 * 30 * E
@@ -482,7 +495,10 @@ def run_ndmap(ctx, K, W, envs=0):
                    "l2": "1.13 GB written per build (>> 126 MB L2)"},
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": ncu_traffic('c4'),
                      "kernel": "ndmap_kernel", "bytes_per_build": nd_bytes,
-                     "bytes_per_cell": 1.125, "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy)"},
+                     "bytes_per_cell": 1.125, "peak_source": "MEASURED_PEAKS.json hbm_gbs (copy: read + write bytes)",
+                     "write_only_peak_gbs": write_peak, "frac_of_write_only_peak": gbs / write_peak,
+                     "write_only_note": "the kernel is a pure write stream; a device memset of 1 GiB measured in this run is the "
+                                        "ceiling of such a stream (about 0.59 of the copy figure on B200)"},
         "gpu_launches": K, "clocks": clocks}
 
 

@@ -19,6 +19,7 @@
 // Also holds the FP32 / FP64 FMA-chain micro-benchmarks (the measured non-tensor roofline denominators).
 #include <cuda_runtime.h>
 #include <cstdint>
+#include <cstdlib>
 #include "bsg_handle.h"
 
 namespace {
@@ -91,6 +92,7 @@ __global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_pa
     for (int c = tid; c < (3 * cells) >> 4; c += kNdThreads) reinterpret_cast<uint4 *>(smem)[c] = make_uint4(0u, 0u, 0u, 0u);
     if (tid == 0) s_ncf = 0;
     const int chunks = (nt + ks - 1) / ks, nitems = p.num_envs * chunks;
+    const int y_tid = tid % ny, z_tid = tid / ny;         // grid row of this thread's first pass (usually its only one)
     int par = 0;
     for (int item = blockIdx.x; item < nitems; item += gridDim.x) {
         const int e = item / chunks, k0 = (item - e * chunks) * ks, k1 = min(k0 + ks, nt);
@@ -107,16 +109,22 @@ __global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_pa
             if (ix < 0 || ix >= nx || iy < 0 || iy >= ny || iz < 0 || iz >= nz) return -1;
             return (iz * ny + iy) * nx + ix;
         };
-        auto clean = [&](int k, uint8_t *im) {           // sparse: the cells slab k's samples touched
-            for (int a = tid; a < n; a += kNdThreads) { const int c = cell_of(a, k); if (c >= 0) im[c] = 0; }
+        // sparse cleaning: the cells slab k's samples touched.  REGS: one sample per thread, its cell of the last two
+        // slabs is remembered (cprev[parity]) instead of being recomputed
+        int cprev[2] = { -1, -1 };
+        auto clean = [&](int k, uint8_t *im, int pq) {
+            if (REGS) { if (cprev[pq] >= 0) im[cprev[pq]] = 0; }                  // (REGS is a template constant)
+            else { for (int a = tid; a < n; a += kNdThreads) { const int c = cell_of(a, k); if (c >= 0) im[c] = 0; } }
         };
         __syncthreads();                                 // (first item: the zero fill; later: the previous item's cleaning)
         for (int k = k0; k < k1; k++) {
             uint8_t *im = img[par];
             // ---- count: one atomic per sample into the byte lanes of the slab image + the [>= 1] / [>= 2] bit-planes
+            if constexpr (REGS) cprev[par] = -1;
             for (int a = tid; a < n; a += kNdThreads) {
                 const int c = cell_of(a, k);
                 if (c < 0) continue;
+                if constexpr (REGS) cprev[par] = c;
                 uint32_t *wp = reinterpret_cast<uint32_t *>(im) + (c >> 2);
                 const int sh = (c & 3) << 3;
                 unsigned lane;
@@ -135,7 +143,6 @@ __global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_pa
                 else if (lane == 1u) atomicOr(&B2[c >> 5], 1u << (c & 31));
             }
             __syncthreads();
-            if (tid == 0) bulk_wait_read0();             // the previous slab's stores have read their image / bit stage
             // ---- x stage: three cells of a row -> (o, t); the planes are cleared for the next slab
             for (int rr = tid; rr < rows; rr += kNdThreads) {
                 Row<RW> a1, b2;
@@ -150,7 +157,7 @@ __global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_pa
             __syncthreads();
             // ---- y stage (rows y - 1, y, y + 1 of one plane); the image of the previous slab is cleaned meanwhile
             for (int rr = tid; rr < rows; rr += kNdThreads) {
-                const int y = rr % ny;
+                const int y = rr == tid ? y_tid : rr % ny;
                 Row<RW> oa = {}, ta = {}, ob, tb, oc = {}, tc = {}, o, t;
                 ob.load(O1 + rr * RW); tb.load(T1 + rr * RW);
                 if (y > 0) { oa.load(O1 + (rr - 1) * RW); ta.load(T1 + (rr - 1) * RW); }
@@ -158,13 +165,16 @@ __global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_pa
                 combine3<RW>(oa, ta, ob, tb, oc, tc, o, t);
                 o.store(O2 + rr * RW); t.store(T2 + rr * RW);
             }
-            if (k > k0) clean(k - 1, img[par ^ 1]);
+            // the previous slab's stores have had the count, x and y stages to read their image / bit stage out of shared
+            // memory; from here on the image may be cleaned (z stage below) and the bit stage rewritten (next slab)
+            if (tid == 0) bulk_wait_read0();
             __syncthreads();
             // ---- z stage (planes z - 1, z, z + 1) -> conflict bits of the slab
             int ncf = 0;
             uint32_t *cf = CF[par];
+            if (k > k0) clean(k - 1, img[par ^ 1], par ^ 1);
             for (int rr = tid; rr < rows; rr += kNdThreads) {
-                const int z = rr / ny;
+                const int z = rr == tid ? z_tid : rr / ny;
                 Row<RW> oa = {}, ta = {}, ob, tb, oc = {}, tc = {}, o, t;
                 ob.load(O2 + rr * RW); tb.load(T2 + rr * RW);
                 if (z > 0) { oa.load(O2 + (rr - ny) * RW); ta.load(T2 + (rr - ny) * RW); }
@@ -174,8 +184,7 @@ __global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_pa
 #pragma unroll
                 for (int i = 0; i < RW; i++) ncf += __popc(t.w[i]);
             }
-#pragma unroll
-            for (int m = 16; m > 0; m >>= 1) ncf += __shfl_xor_sync(0xffffffffu, ncf, m);
+            ncf = __reduce_add_sync(0xffffffffu, ncf);       // redux.sync
             if ((tid & 31) == 0 && ncf) atomicAdd(&s_ncf, ncf);
             fence_async_smem();                          // generic-proxy writes (atomics, stores) before the TMA reads them
             __syncthreads();
@@ -192,7 +201,7 @@ __global__ void __launch_bounds__(kNdThreads, 2) ndmap_kernel(const bsg_ndmap_pa
         // the item's last slab: wait for its store, clean its image (the records change with the next item)
         if (tid == 0) bulk_wait_read0();
         __syncthreads();
-        clean(k1 - 1, img[par ^ 1]);
+        clean(k1 - 1, img[par ^ 1], par ^ 1);
     }
     if (tid == 0) bulk_wait0();
 }

@@ -169,9 +169,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         }
     };
     if (valid && A.skip) skipv = A.skip[e];
-#ifndef BSG_OLD_PROLOGUE
     load_env();
-#endif
     if (valid && i == 0 && A.actions) {
         const bool two = A.kind == BSG_KIND_SECTOR || A.kind == BSG_KIND_MERGE;
         act0 = A.actions[two ? 2 * e : e];
@@ -181,13 +179,8 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     if (A.fuse_reset && __syncthreads_or(skip)) {                          // rare: some env of this CTA starts an episode
         fused_reset<R>(A.kind, A.fixed_nac, A.density_mode, A.E, A.N, A.epb, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso,
                        A.RC, smem_raw, skip, valid, le, i, e);
-#ifndef BSG_OLD_PROLOGUE
         load_env();
-#endif
     }
-#ifdef BSG_OLD_PROLOGUE
-    load_env();
-#endif
     const int nl = valid ? nlv : 0;
     const bool live = valid && i < nl;
     if (live) {

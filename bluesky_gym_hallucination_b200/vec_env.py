@@ -8,6 +8,8 @@ same env ids, observation keys, action shapes, reward / terminated / truncated /
 and the registrations of bluesky_gym/__init__.py:18-46 (max_episode_steps 300 / 300 / 200 / 50).  The reference's
 wrappers (bluesky_gym/wrappers/wind.py, uncertainty.py) are constructor options: `wind=`, `obs_noise=`.
 PyTorch appears only as the tensor hand-off to RL libraries (`step_tensors`)."""
+from collections.abc import Mapping
+
 import numpy as np
 import torch
 from . import _lib as L
@@ -113,21 +115,59 @@ class BlueSkyVecEnv:
         (obs [E, obs_dim], reward, terminated, truncated, info) without leaving the device or syncing."""
         return self.core.step(actions)
 
+    def ndmap(self, **kw):
+        """ND-map (4D occupancy / conflict grid over the look-ahead trajectories) of the batch's LIVE traffic:
+        (occ u8 [E, nt, nz, ny, nx], conf bitmask, ncell [E, nt]) device tensors -- BsgCore.ndmap / bsg_ndmap_state."""
+        return self.core.ndmap(**kw)
+
     def close(self):
         if not self.closed:
             self.core.close()
             self.closed = True
 
 
+class _InfoView(Mapping):
+    """infos[i] of the SB3 protocol as a VIEW: reads env i's slots of the adapter's current info arrays on demand, so a
+    step allocates nothing per env (SB3 only looks inside the infos of finished episodes)."""
+    __slots__ = ('_o', '_i')
+
+    def __init__(self, owner, i):
+        self._o, self._i = owner, i
+
+    def __getitem__(self, k):
+        o, i = self._o, self._i
+        if k in o._info:
+            v = o._info[k][i]
+            return float(v) if o._info[k].dtype.kind == 'f' else int(v)
+        if k == 'TimeLimit.truncated':
+            return bool(o._tl[i])
+        if k == 'terminal_observation' and i in o._term_obs:
+            return o._term_obs[i]
+        raise KeyError(k)
+
+    def __iter__(self):
+        yield from self._o._info
+        yield 'TimeLimit.truncated'
+        if self._i in self._o._term_obs:
+            yield 'terminal_observation'
+
+    def __len__(self):
+        return len(self._o._info) + 1 + (self._i in self._o._term_obs)
+
+
 class SB3VecEnvAdapter:
     """stable-baselines3 VecEnv protocol (dict obs batched on axis 0, dones = terminated | truncated,
     same-step auto-reset with infos[i]['terminal_observation'] and infos[i]['TimeLimit.truncated']), the
-    contract scripts/multi_processing_example.py:51-54 and bluesky_gym/utils/logger.py:15-35 rely on."""
+    contract scripts/multi_processing_example.py:51-54 and bluesky_gym/utils/logger.py:15-35 rely on.
+    Vectorised: `infos` is a list of E persistent mapping views over the step's info arrays (no per-env dict is built),
+    and only the finished envs' rows travel for the terminal / fresh observations."""
 
     def __init__(self, venv: BlueSkyVecEnv):
         self.venv, self.num_envs = venv, venv.num_envs
         self.observation_space, self.action_space = venv.single_observation_space, venv.single_action_space
         self._actions = None
+        self._info, self._tl, self._term_obs = {}, np.zeros(self.num_envs, bool), {}
+        self._views = [_InfoView(self, i) for i in range(self.num_envs)]
 
     def reset(self):
         obs, _ = self.venv.reset()
@@ -141,19 +181,61 @@ class SB3VecEnvAdapter:
         v = self.venv
         obs, rew, term, trunc, info = v.step(self._actions)
         dones = term | trunc
-        keys = INFO_KEYS[v.kind]
-        infos = [{**{k: (float(info[k][i]) if info[k].dtype.kind == 'f' else int(info[k][i])) for k in keys},
-                  'TimeLimit.truncated': bool(trunc[i] and not term[i])} for i in range(self.num_envs)]
-        if dones.any():
-            fresh = v._obs_dict(v.core.observe().cpu().numpy())            # the device already reset those envs
-            for i in np.where(dones)[0]:
-                infos[i]['terminal_observation'] = {k: obs[k][i].copy() for k in obs}
-            obs = {k: np.where(dones[:, None], fresh[k], obs[k]) for k in obs}
-        return obs, rew, dones, infos
+        self._info, self._tl, self._term_obs = info, trunc & ~term, {}
+        idx = np.flatnonzero(dones)
+        if idx.size:
+            # the device already reset those envs: their fresh observations, rows of the finished envs only
+            rows = v.core.observe()[torch.as_tensor(idx, device=v.core.device)].cpu().numpy()
+            fresh = v._obs_dict(rows)
+            for n, i in enumerate(idx):
+                self._term_obs[int(i)] = {k: obs[k][i].copy() for k in obs}
+            for k in obs:
+                obs[k][idx] = fresh[k]
+        return obs, rew, dones, self._views
 
     def step(self, actions):
         self.step_async(actions)
         return self.step_wait()
+
+    def close(self):
+        self.venv.close()
+
+
+class RLlibVectorEnvAdapter:
+    """ray.rllib.env.vector_env.VectorEnv protocol over one device batch: vector_reset / reset_at /
+    vector_step with per-env LISTS of observations, the shape RLlib's sampler consumes.  The device resets finished
+    envs itself (same-step mode), so reset_at(i) returns the observation env i already holds.  ray is not installed in
+    this image: the class follows the published protocol and is exercised by tests/test_gpu_vecenv.py only."""
+
+    def __init__(self, venv: BlueSkyVecEnv):
+        self.venv, self.num_envs = venv, venv.num_envs
+        self.observation_space, self.action_space = venv.single_observation_space, venv.single_action_space
+        self._obs = None
+
+    def _split(self, obs):
+        return [{k: obs[k][i] for k in obs} for i in range(self.num_envs)]
+
+    def vector_reset(self, *, seeds=None, options=None):
+        obs, info = self.venv.reset(seed=None if not seeds else seeds[0])
+        self.venv.core.set_autoreset(2, seed=self.venv._seed + 1)
+        self._obs = obs
+        return self._split(obs), [{} for _ in range(self.num_envs)]
+
+    def reset_at(self, index=None, *, seed=None, options=None):
+        i = 0 if index is None else int(index)
+        fresh = self.venv._obs_dict(self.venv.core.observe()[i:i + 1].cpu().numpy())
+        return {k: fresh[k][0] for k in fresh}, {}
+
+    def vector_step(self, actions):
+        a = np.stack([np.asarray(x, dtype=np.float64).reshape(-1) for x in actions])
+        obs, rew, term, trunc, info = self.venv.step(a)
+        self._obs = obs
+        infos = [{k: (float(info[k][i]) if info[k].dtype.kind == 'f' else int(info[k][i])) for k in info}
+                 for i in range(self.num_envs)]
+        return self._split(obs), rew.tolist(), term.tolist(), trunc.tolist(), infos
+
+    def get_sub_environments(self):
+        return []
 
     def close(self):
         self.venv.close()

@@ -96,3 +96,124 @@ def test_sb3_adapter_same_step_autoreset():
             assert obs['waypoint_distance'][i, 0] > 95.0 / 150.0                             # already the new episode
     assert seen >= E // 2
     a.close()
+
+
+def _episodes(kind, N, E, steps, seed, max_steps, act_dim, **kw):
+    """Random-policy episodes of a device batch: returns (lengths, total_intrusions, third info slot) of every finished episode."""
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    c = BsgCore(kind, E, N, precision='fp32', max_episode_steps=max_steps, **kw)
+    c.reset(seed=seed); c.set_autoreset(True, seed=seed + 1)
+    gen = torch.Generator(device='cuda'); gen.manual_seed(seed)
+    age = np.zeros(E, np.int64)
+    lens, intr, third = [], [], []
+    for s in range(steps):
+        a = torch.rand((E, act_dim), device='cuda', generator=gen) * 2 - 1
+        c.step(a)
+        done = (c.terminated | c.truncated).cpu().numpy().astype(bool)
+        info = c.info.cpu().numpy()
+        # next-step auto-reset: an env that ended in the previous step spends this step drawing its episode
+        fresh = age < 0
+        age[~fresh] += 1
+        age[fresh] = 0
+        for e in np.where(done & ~fresh)[0]:
+            lens.append(age[e]); intr.append(info[e, 1]); third.append(info[e, 2])
+        age[done & ~fresh] = -1
+    c.close()
+    return np.array(lens), np.array(intr), np.array(third)
+
+
+def test_vertical_episode_lengths_match_the_reference_logs():
+    """Envelope anchor (scripts/common/results/logs_backup/VerticalCREnv-v0/*.csv, 200 000 episodes of four
+    agents): a Vertical episode is a 200 km run at CAS 150 m/s in 30 s steps -- median length 40, NEVER more than 43-44
+    (TAS >= 155 m/s near the ground), and never fewer than 6 steps (a crash needs 2000 m of descent at 12.5 m/s)."""
+    from bluesky_gym_hallucination_b200 import _lib as L
+    lens, intr, final_alt = _episodes(L.KIND_VERTICAL, 6, 512, 100, 41, 300, 1)
+    assert len(lens) >= 512
+    assert lens.max() <= 44 and lens.min() >= 6, (lens.min(), lens.max())
+    assert 37 <= np.median(lens) <= 42, np.median(lens)
+    # logged first-300-episode means (near-random policies): 0.98 - 1.66 intrusion steps per episode
+    assert 0.3 <= intr.mean() <= 3.0, intr.mean()
+
+
+def test_sector_random_policy_statistics_match_the_reference_logs():
+    """Anchor (logs_backup/SectorCREnv-v0/*.csv, first 300 episodes of each agent = near-random policies): 14 - 40
+    intrusion steps per episode on average, episodes from a few steps (the agent leaves the sector) to the 200-step
+    TimeLimit; the agent holds ~150 m/s CAS, so the speed slot of the observation (tas - 150) / 6 stays O(1)."""
+    from bluesky_gym_hallucination_b200 import _lib as L
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    lens, intr, drift = _episodes(L.KIND_SECTOR, 32, 256, 420, 43, 200, 2)
+    assert len(lens) >= 256
+    assert lens.max() <= 200 and 30 <= np.median(lens) <= 200, (np.median(lens), lens.max())
+    assert 8.0 <= intr.mean() <= 60.0, intr.mean()
+    assert 0.2 <= np.nanmean(drift) <= 2.0, np.nanmean(drift)
+    c = BsgCore(L.KIND_SECTOR, 64, 32, precision='fp32')
+    c.reset(seed=5)
+    obs = c.observe().cpu().numpy()
+    ac, _, nac, _ = c.get_state()
+    # sector_cr_env.py:303: "airspeed": (tas - 150) / 6 -- CAS 150 m/s at the sector's flight level is TAS ~ 150 - 190
+    tas0 = ac[:, L.F['tas'], 0]
+    assert np.all((tas0 > 140) & (tas0 < 200)), (tas0.min(), tas0.max())
+    c.close()
+
+
+def _reset_stats(kind, ac, nac, ev, F, EV):
+    """Per-kind derived quantities of a batch of freshly reset envs (same code for the reference samples and the device
+    generator): dict name -> 1-D sample."""
+    lat, lon, alt, hdg, tas = (ac[:, F[k]] for k in ('lat', 'lon', 'alt', 'hdg', 'tas'))
+    E = ac.shape[0]
+    live = np.arange(ac.shape[2])[None, :] < nac[:, None]
+    intr = live.copy(); intr[:, 0] = False
+    c0 = np.cos(np.radians(lat[:, :1]))
+    dx = (lon - lon[:, :1]) * 60.0 * c0; dy = (lat - lat[:, :1]) * 60.0               # NM from the agent
+    out = {'intruder_dist_nm': np.hypot(dx, dy)[intr], 'intruder_bearing': (np.degrees(np.arctan2(dx, dy)) % 360)[intr],
+           'intruder_hdg_rel': ((hdg - hdg[:, :1]) % 360)[intr], 'intruder_tas': tas[intr]}
+    if kind == 'H':
+        wd = np.hypot((ev[:, EV['wpt_lon']] - lon[:, 0]) * 60 * c0[:, 0], (ev[:, EV['wpt_lat']] - lat[:, 0]) * 60)
+        out['waypoint_dist_nm'] = wd
+    if kind == 'V':
+        out['own_alt'] = alt[:, 0]; out['target_minus_alt'] = ev[:, EV['target_alt']] - alt[:, 0]
+        out['intruder_dalt'] = (alt - alt[:, :1])[intr]
+    if kind == 'S':
+        out['nac'] = nac.astype(np.float64); out['own_tas'] = tas[:, 0]; out['own_hdg'] = hdg[:, 0]
+        out['all_alt'] = alt[live]
+    return out
+
+
+@pytest.mark.parametrize('kind', ['H', 'V', 'S'])
+def test_reset_distributions_match_the_reference(kind):
+    """The device scenario generators (csrc/bsg_reset.cuh, Philox) draw from the same laws as the UNMODIFIED reference
+    reset() (horizontal_cr_env.py:121-160, vertical_cr_env.py:182-199,262-281, sector_cr_env.py:141-230): two-sample
+    Kolmogorov-Smirnov of every derived quantity against samples recorded from the reference classes
+    (tests/golden/reset_samples_*.npz, made by tests/golden/make_reset_samples.py)."""
+    import os
+    from scipy import stats
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    from bluesky_gym_hallucination_b200 import _lib as L
+    g = np.load(os.path.join(os.path.dirname(__file__), 'golden', f'reset_samples_{kind}.npz'))
+    fields = [str(x) for x in g['fields']]
+    Fg = {k: i for i, k in enumerate(fields)}
+    n = g['ac'].shape[2]
+    ref = _reset_stats(kind, g['ac'], g['nac'], g['ev'], Fg, L.EV)
+    E = 4096
+    c = BsgCore({'H': L.KIND_HORIZONTAL, 'V': L.KIND_VERTICAL, 'S': L.KIND_SECTOR}[kind], E, n, precision='fp32')
+    c.reset(seed=77)
+    torch.cuda.synchronize()
+    ac, _, nac, ev = c.get_state()
+    c.close()
+    dev = _reset_stats(kind, ac, nac, ev, L.F, L.EV)
+    report = {}
+    for k in ref:
+        a, b = np.asarray(ref[k], np.float64), np.asarray(dev[k], np.float64)
+        a, b = a[np.isfinite(a)], b[np.isfinite(b)]
+        if max(a.std(), b.std()) <= 1e-6 * max(abs(a.mean()), 1.0):       # a constant of the generator: compare it as such
+            assert abs(a.mean() - b.mean()) <= 1e-6 * max(abs(a.mean()), 1.0), (k, a.mean(), b.mean())
+            continue
+        ks = stats.ks_2samp(a, b)
+        # critical value of the two-sample statistic at alpha = 1e-3 (draws inside one env are not independent, so the
+        # effective sample is taken as the number of ENVS, not aircraft)
+        na, nb = min(len(a), len(g['nac'])), min(len(b), E)
+        crit = 1.95 * np.sqrt((na + nb) / (na * nb))
+        report[k] = (round(float(ks.statistic), 4), round(float(crit), 4), float(a.mean()), float(b.mean()))
+    print(f"[reset {kind}] KS statistic / critical (alpha 1e-3) / reference mean / device mean: {report}")
+    bad = {k: v for k, v in report.items() if v[0] > v[1]}
+    assert not bad, bad

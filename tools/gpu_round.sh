@@ -1,13 +1,11 @@
 #!/bin/bash
-# One GPU pass: parity tests, smoke, bench lines (C2 default, reference arm, C3), ncu launch list + full capture of the C2 step kernel.
+# one-GPU round: GPU tests, then (each only after its plain run exited 0) ncu captures named by $1 = list of c2 c3 c4 c5
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
-tail -5 gpurun_out/pytest_gpu.log
-timeout 300 python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" > gpurun_out/smoke.log 2>&1; tail -2 gpurun_out/smoke.log
-timeout 600 python bench.py > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err; echo "bench c2 rc=$?"
-timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "bench ref rc=$?"
-timeout 600 python bench.py --workload c3 --steps 200 --warmup 5 --no-cpu > gpurun_out/bench_c3.json 2> gpurun_out/bench_c3.err; echo "bench c3 rc=$?"
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 20 --warmup 3 --no-cpu > gpurun_out/ncu_launch.log 2>&1; echo "ncu launches rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:step_kernel -s 5 -c 1 -o gpurun_out/step_c2 -f python bench.py --steps 20 --warmup 3 --no-cpu > gpurun_out/ncu_full.log 2>&1; echo "ncu full c2 rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:step_kernel -s 5 -c 1 -o gpurun_out/step_c3 -f python bench.py --workload c3 --steps 10 --warmup 3 --no-cpu > gpurun_out/ncu_full_c3.log 2>&1; echo "ncu full c3 rc=$?"
-cat gpurun_out/bench_c2.json | tail -1 | cut -c1-600
+timeout 1500 python -m pytest tests -m gpu -q -s -p no:cacheprovider > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+grep -E "^\[reset|passed|failed|Error|error" gpurun_out/pytest_gpu.log | cut -c1-1500 | tail -12
+for w in $1; do
+  timeout 300 python bench.py --workload $w --steps 20 --warmup 5 --no-cpu > gpurun_out/bench_$w.json 2> gpurun_out/bench_$w.err || { echo "bench $w failed"; continue; }
+  tail -1 gpurun_out/bench_$w.json | python -c 'import sys,json; d=json.loads(sys.stdin.read()); print(d["config"]["workload"], d["ms_per_step"], d["roofline"]["frac"])'
+  case $w in c4) kn=ndmap_kernel;; c5) kn=cd_sym_sweep_kernel;; *) kn=step_kernel;; esac
+  timeout 600 ncu --set full --import-source on --clock-control none -k regex:$kn -s 8 -c 1 -o gpurun_out/ncu_${w}_r2 -f python bench.py --workload $w --steps 4 --warmup 5 --no-cpu > gpurun_out/ncu_$w.log 2>&1; tail -1 gpurun_out/ncu_$w.log
+done
