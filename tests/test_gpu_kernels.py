@@ -51,6 +51,36 @@ def test_cd_sweep_vs_oracle(orc, E, N, box):
     print(f"near-threshold rows enumerated: {near_rows}")
 
 
+def test_giant_airspace_full_env_vs_oracle(orc):
+    """BASELINE.json configs[4] at its FULL per-env size: one env of 10 000 aircraft (1e8 ordered pairs), symmetric
+    sweep (the default C5 kernel) vs the oracle's rows; every mismatching row is enumerated by the oracle as holding a
+    pair within EPS32 of a zone threshold (oracle.cd_rows_near: no dense matrices)."""
+    from bluesky_gym_hallucination_b200 import core, scenario as sc
+    E, N = 1, 10000
+    lat, lon, alt, trk, gs, vs = sc.raw_traffic(E, N, seed=3, box_nm=1000.0)
+    ref, near_c, near_l = orc.cd_rows_near(lat, lon, alt, trk, gs, vs, EPS32, nthreads=16)
+    out = core.cd_sweep_sym(_pack(lat, lon, alt, trk, gs, vs))
+    torch.cuda.synchronize()
+    got = {k: v.cpu().numpy() for k, v in out.items()}
+    assert ref['nconf'].sum() > 1000
+    near_c, near_l = near_c.astype(bool), near_l.astype(bool)
+    bad_c = got['nconf'] != ref['nconf']
+    bad_l = got['nlos'] != ref['nlos']
+    print(f"C5 full env: {int(ref['nconf'].sum())} conflict entries, {int(bad_c.sum())} conflict-count / {int(bad_l.sum())} LoS-count "
+          f"row mismatches, near-threshold rows enumerated {int(near_c.sum())} + {int(near_l.sum())}")
+    assert not (bad_c & ~near_c).any(), np.argwhere(bad_c & ~near_c)[:8]
+    assert not (bad_l & ~near_l & ~near_c).any(), np.argwhere(bad_l & ~near_l)[:8]
+    ok = ~bad_c & ~near_c
+    assert np.array_equal(got['inconf'][ok] != 0, ref['inconf'][ok] != 0)
+    same = ok & (got['near_idx'] == ref['near_idx']) & (ref['near_idx'] >= 0)
+    assert same.sum() >= 0.995 * (ok & (ref['near_idx'] >= 0)).sum()
+    # times: fp32 records in a 1000 NM box resolve positions to 0.125 m, i.e. tCPA to ~0.1 m / |v_rel| -- an absolute
+    # floor of 0.02 s beside the 1e-4 relative bound
+    for k in ('near_tcpa', 'tcpamax'):
+        d = np.abs(got[k][same] - ref[k][same])
+        assert np.all(d <= np.maximum(1e-4 * np.abs(ref[k][same]), 2e-2)), (k, d.max())
+
+
 def test_cd_sweep_row_block_equals_full():
     """Row-block partition of the pair matrix (the multi-GPU sharding) == the full sweep, bitwise."""
     from bluesky_gym_hallucination_b200 import core, scenario as sc

@@ -46,7 +46,8 @@ def obs_tol32(kind, ref):
 
 def make_core(kind, E, N, precision, asas=0, **kw):
     from bluesky_gym_hallucination_b200.core import BsgCore
-    return BsgCore(kind, E, N, precision=precision, asas_on=bool(asas), reso_on=bool(asas) and N <= 64 and kw.pop('reso', True),
+    reso = kw.pop('reso', True)
+    return BsgCore(kind, E, N, precision=precision, asas_on=bool(asas), reso_on=bool(asas) and N <= 64 and reso,
                    reso_off_own=bool(asas), cd_outputs=True, **kw)
 
 
@@ -124,19 +125,19 @@ def test_fp32_replays_reference_goldens(orc, name):
     core.close()
 
 
-@pytest.mark.parametrize('kind,N,asas', [(0, 20, 1), (2, 50, 1), (1, 6, 0)])
-def test_batched_step_vs_oracle(orc, kind, N, asas):
-    """Seeded synthetic batch (BASELINE configs' shapes, fewer envs): 3 chained steps fp64 == oracle,
-    one step fp32 within tolerance with every CD-flag mismatch explained by a near-threshold pair."""
+@pytest.mark.parametrize('kind,N,asas,E,mvp', [(0, 20, 1, 512, 1), (2, 50, 1, 512, 1), (1, 6, 0, 512, 0), (0, 20, 1, 4096, 0)])
+def test_batched_step_vs_oracle(orc, kind, N, asas, E, mvp):
+    """Seeded synthetic batch (BASELINE configs' shapes; the last case is configs[1] at its FULL size, 4096 envs x 20
+    aircraft, detection only as bench.py runs it): 3 chained steps fp64 == oracle, one step fp32 within tolerance with
+    every CD-flag mismatch explained by a near-threshold pair."""
     from bluesky_gym_hallucination_b200 import scenario as sc
-    E = 512
     gen = {0: sc.horizontal, 1: sc.vertical, 2: sc.sector}[kind]
     ac, reso, nac, ev = gen(E, N, seed=7)
-    cfg = orc.make_cfg(kind, N, asas_on=asas, reso_on=asas, reso_off_own=asas)
+    cfg = orc.make_cfg(kind, N, asas_on=asas, reso_on=mvp, reso_off_own=mvp)
     rng = np.random.default_rng(3)
     na = 2 if kind == 2 else 1
-    c64 = make_core(kind, E, N, 'fp64', asas)
-    c32 = make_core(kind, E, N, 'fp32', asas)
+    c64 = make_core(kind, E, N, 'fp64', asas, reso=bool(mvp))
+    c32 = make_core(kind, E, N, 'fp32', asas, reso=bool(mvp))
     o_ac, o_reso, o_ev = ac.copy(), reso.copy(), ev.copy()
     c64.set_state(ac, reso, nac, ev)
     for s in range(3):
@@ -248,7 +249,7 @@ def test_batched_step_vs_oracle(orc, kind, N, asas):
               f"worst err/tol {float(ratio[worst]):.3f} at env {worst[0]} slot {worst[1]} (err {float(err[worst]):.3e}, kappa {float(kappa[worst[0]]):.3e})")
         # 99 % of the observation entries must sit inside the plain 1e-5 bound, and all of them inside 100 x it; the
         # conditioned bound (asserted below) covers that tail env by env
-        assert q50 <= 1.0 and q99 <= 1.0 and rb.max() <= (100.0 if asas else 1.0), (q50, q99, rb.max())
+        assert q50 <= 1.0 and q99 <= 1.0 and rb.max() <= (100.0 if mvp else 1.0), (q50, q99, rb.max())
         assert not bad.any(), (np.argwhere(bad)[:5], float(ratio[worst]))
         if asas:
             # (4) CD row outputs of the last detection: every mismatching row must hold a pair the oracle places within

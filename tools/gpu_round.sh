@@ -9,3 +9,7 @@ for w in $1; do
   case $w in c4) kn=ndmap_kernel;; c5) kn=cd_sym_sweep_kernel;; *) kn=step_kernel;; esac
   timeout 600 ncu --set full --import-source on --clock-control none -k regex:$kn -s 8 -c 1 -o gpurun_out/ncu_${w}_r2 -f python bench.py --workload $w --steps 4 --warmup 5 --no-cpu > gpurun_out/ncu_$w.log 2>&1; tail -1 gpurun_out/ncu_$w.log
 done
+# launch list of the default bench command (kernel share of the step; cold-cache serialised times)
+if [ -n "$2" ]; then
+  timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv --log-file gpurun_out/launches_default_r2.csv python bench.py --steps 3 --warmup 3 --no-cpu > gpurun_out/ncu_launches.log 2>&1; tail -1 gpurun_out/ncu_launches.log | cut -c1-200
+fi
