@@ -186,6 +186,20 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
         h->smem = g.precision == BSG_FP64 ? step_smem<double>(N, h->epb, h->nbuf, false).total : step_smem<float>(N, h->epb, h->nbuf, pairs).total;
     }
     CK(h, cudaSetDevice(g.device));
+    // detection-only symmetric fp32 kernel: a one-wave launch shape that balances the warps over the SMs, when there is one
+    if (g.precision != BSG_FP64 && N <= 64 && !(g.reso_on && g.asas_on) && !getenv("BSG_NO_SYM") && !getenv("BSG_NO_WIDE")) {
+        int we = 0, wn = 0; size_t ws = 0;
+        if (const char *f = getenv("BSG_WIDE_EPB")) {          // A/B hook: force the envs per CTA of the wide shape
+            we = atoi(f);
+            if (we >= 1 && we * N <= 640) {
+                wn = BSG_CH < g.substeps ? BSG_CH : (g.substeps > 2 ? g.substeps : 2);
+                while (wn > 2 && step_smem<float>(N, we, wn, false).total > 100 * 1024) wn--;
+                h->wepb = we; h->wnbuf = wn; h->wsmem = step_smem<float>(N, we, wn, false).total;
+            }
+        } else if (pick_wide_shape(E, N, g.substeps, h->epb, ((h->epb * N + 31) / 32) * 32, &we, &wn, &ws)) {
+            h->wepb = we; h->wnbuf = wn; h->wsmem = ws;
+        }
+    }
     const size_t EN = (size_t)E * N;
     CK(h, cudaMalloc(&h->pos, 2 * EN * sizeof(double)));
     CK(h, cudaMalloc(&h->st, (size_t)S_NS * EN * rs));
@@ -264,7 +278,7 @@ int bsg_destroy(bsg_handle *h) {
 #include "bsg_api_step.inl"
 
 #ifdef BSG_TRACE
-extern "C" int bsg_debug_trace(unsigned long long *out_host, int n_words) {
-    return cudaMemcpyFromSymbol(out_host, bsg::g_trace, (size_t)n_words * sizeof(unsigned long long)) == cudaSuccess ? 0 : -1;
-}
+// (the stamps live in the translation unit that holds the fp32 instantiations: bsg_step_f32.cu)
+namespace bsg { int trace_read_f32(unsigned long long *out_host, int n_words); }
+extern "C" int bsg_debug_trace(unsigned long long *out_host, int n_words) { return bsg::trace_read_f32(out_host, n_words); }
 #endif

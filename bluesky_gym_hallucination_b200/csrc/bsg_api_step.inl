@@ -22,7 +22,10 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     // EXT instantiations: Merge env, wind field, observation noise (fp32: the symmetric sweep only, N <= 64)
     const bool ext = is_ext(h);
     int32_t *done_now = nullptr;
-    if (ar) { done_now = h->done_buf[h->flip ^ 1]; if (!A.out.done) A.out.done = done_now; }
+    // auto-reset: the kernel stores `done` twice -- to the caller's array and to the library's flag buffer of the next
+    // launch -- instead of a device-to-device copy node behind every step
+    A.done_next = nullptr;
+    if (ar) { done_now = h->done_buf[h->flip ^ 1]; if (!A.out.done) A.out.done = done_now; else if (A.out.done != done_now) A.done_next = done_now; }
     const int grid = (g.num_envs + h->epb - 1) / h->epb;
     const bool reso = g.reso_on && g.asas_on;
     const dim3 gd(grid), bd(((h->epb * g.max_ac + 31) / 32) * 32);      // whole warps covering the CTA's envs
@@ -33,15 +36,18 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
             le = launch_step_f32_ext(h->tpb, reso, gd, bd, h->smem, s, A);
         } else {
             const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM");     // symmetric half-ring sweep (fp32 fast path)
-            le = launch_step_f32(h->tpb, reso, sym, gd, bd, h->smem, s, A);
+            if (sym && !reso && h->wepb > 0) {
+                // detection only: the one-wave shape picked at creation (whole warps balanced over the SMs)
+                A.epb = h->wepb; A.nbuf = h->wnbuf;
+                const dim3 wg((g.num_envs + h->wepb - 1) / h->wepb), wb(((h->wepb * g.max_ac + 31) / 32) * 32);
+                le = launch_step_f32(640, false, true, wg, wb, h->wsmem, s, A);
+            } else le = launch_step_f32(h->tpb, reso, sym, gd, bd, h->smem, s, A);
         }
     } else le = launch_step_f64(h->tpb, reso, ext, gd, bd, h->smem, s, A);
     if (le == cudaErrorInvalidValue && h->tpb != 128 && h->tpb != 256) { h->err = "step kernel: CTA of 128 or 256 threads"; return BSG_ERR_UNSUPPORTED; }
     h->launches++;
     CK(h, le);
     if (ar) {
-        if (A.out.done != done_now)
-            CK(h, cudaMemcpyAsync(done_now, A.out.done, g.num_envs * sizeof(int32_t), cudaMemcpyDeviceToDevice, s));
         h->flip ^= 1;
         if (h->autoreset == 2) {                       // same-step mode: reset now (separate masked launch)
             int rc = bsg_reset(h, done_now, h->ar_seed, (void *)s);

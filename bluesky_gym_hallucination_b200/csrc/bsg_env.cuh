@@ -207,6 +207,7 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
         if (A.out.terminated) A.out.terminated[e] = 0;
         if (A.out.truncated) A.out.truncated[e] = 0;
         if (A.out.done) A.out.done[e] = 0;
+        if (A.done_next) A.done_next[e] = 0;
         if (A.out.info) {
             R *inf = (R *)A.out.info + (size_t)e * 4;
             inf[0] = R(0); inf[1] = R(0); inf[2] = kind == BSG_KIND_VERTICAL ? R(0) : R(NAN); inf[3] = R(0);
@@ -253,6 +254,7 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
         if (A.out.terminated) A.out.terminated[e] = term;
         if (A.out.truncated) A.out.truncated[e] = trunc;
         if (A.out.done) A.out.done[e] = term | trunc;
+        if (A.done_next) A.done_next[e] = term | trunc;      // auto-reset: the next launch's `skip` flags
         if (A.out.info) {
             R *inf = (R *)A.out.info + (size_t)e * 4;
             inf[0] = (R)sev[BSG_EV_TOTAL_REWARD]; inf[1] = (R)sev[BSG_EV_TOTAL_INTR];

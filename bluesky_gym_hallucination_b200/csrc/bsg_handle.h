@@ -10,6 +10,8 @@ struct bsg_handle {
     bsg_config cfg;
     int obs_dim, act_dim, epb, tpb, nbuf;
     size_t smem;
+    int wepb = 0, wnbuf = 0;          // wide launch shape of the detection-only symmetric fp32 kernel (0: default shape)
+    size_t wsmem = 0;
     double *pos = nullptr;            // [2][E*N]
     void *st = nullptr;               // R [S_NS][E*N]
     unsigned long long *reso = nullptr;

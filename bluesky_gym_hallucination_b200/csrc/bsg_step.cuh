@@ -24,6 +24,7 @@ template <typename R> struct StepArgs {
     double *pos; R *st; unsigned long long *reso; int *nac; double *ev;
     const R *actions;
     const int *skip;      // envs reset after the previous step (auto-reset): observe only, reward 0
+    int *done_next;       // auto-reset: the library's own copy of `done` (the next launch's skip flags), written beside out.done
     // fused next-step auto-reset: the envs flagged in `skip` draw their new episode at the head of this launch
     // (bsg_reset.cuh stages) instead of in a separate reset launch; `nac` is written by that stage
     int fuse_reset, fixed_nac, density_mode; unsigned long long ar_seed; unsigned int *episode; ResetConst RC;

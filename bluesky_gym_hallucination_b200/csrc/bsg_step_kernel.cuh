@@ -30,10 +30,12 @@ inline void cd_params_fast(const CdParams &P, CdParamsF &fast) {
     fast.fach2 = (float)(P.fach * P.fach);
 }
 
-// CTA size / residency: 128-thread CTAs keep the small-N configs in one balanced wave
-// (C2: 683 CTAs over 148 SMs x 5 resident), 256 threads only when one env needs them (N > 128).
+// CTA size / residency: 128-thread CTAs for the small-N configs (five resident per SM), 256 threads only when one env
+// needs them (N > 128).  TPB = 640 is the "wide" detection-only instantiation: the same register cap as 128 x 5
+// (65536 / 640 = 102), launched with ANY block size up to 640 threads -- the host picks the number of envs per CTA that
+// leaves every SM the same number of warps in ONE wave (pick_wide_shape, bsg_step_f32.cu).
 template <typename R, int TPB> struct StepBounds {
-    static constexpr int kMinBlocks = TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : (sizeof(R) == 4 ? 2 : 1);
+    static constexpr int kMinBlocks = TPB == 640 ? 1 : TPB == 128 ? (sizeof(R) == 4 ? 5 : 3) : (sizeof(R) == 4 ? 2 : 1);
 };
 // Per-env row of CD records in shared memory, `nbuf` rows per env (2 = double-buffered by substep parity; the
 // detection-only kernels keep up to BSG_CH rows, one per substep of a chunk).
@@ -153,9 +155,9 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     const size_t EN = (size_t)A.E * N, k = (size_t)(valid ? e : 0) * N + i;
     double *ev = A.ev + (size_t)(valid ? e : 0) * BSG_NE;
     constexpr bool reso = RESO;
-    // ------------------------------------------------------------------ prologue loads in TWO dependent batches
-    // (the inputs are cold: every dependent batch is a DRAM round trip).  Batch 1: episode flag, aircraft count, env
-    // scalars, action; batch 2, after the (rare) reset stage: the aircraft state.
+    // ------------------------------------------------------------------ prologue loads (the inputs are cold: every
+    // dependent batch is a DRAM round trip): episode flag, aircraft count, env scalars, action -- and, speculatively in
+    // the same batch, the aircraft state.
     AcReg<R> a = {};
     unsigned long long resorow = 0;
     int skipv = 0, nlv = 0;
@@ -175,19 +177,33 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
         act0 = A.actions[two ? 2 * e : e];
         if (two) act1 = A.actions[2 * e + 1];
     }
+    // the aircraft state rides in the same batch, speculatively: every slot i < N of a valid env exists in memory
+    // whether it is live or not, and the rare reset stage reloads it
+    auto load_ac = [&]() {
+        if (valid) {
+            ac_load_raw<R, RESO, EXT>(a, A.pos, A.st, EN, k);
+            if (reso) resorow = A.reso[k];
+        }
+    };
+    // (detection-only kernels: their launches are often ONE wave, where nothing hides a second round trip; the
+    // resolution kernels run many waves and keep the state load behind the reset stage -- measured, C3 +1 % otherwise)
+    constexpr bool SPEC = !RESO;
+    if constexpr (SPEC) load_ac();
     const bool skip = valid && skipv;                                      // fresh episode: no action, no integration
     if (A.fuse_reset && __syncthreads_or(skip)) {                          // rare: some env of this CTA starts an episode
+        if constexpr (SPEC) { a = AcReg<R>{}; resorow = 0; }               // (nothing of the speculative load lives across the call)
         fused_reset<R>(A.kind, A.fixed_nac, A.density_mode, A.E, A.N, A.epb, A.ar_seed, A.episode, A.ev, A.nac, A.pos, A.st, A.reso,
                        A.RC, smem_raw, skip, valid, le, i, e);
         load_env();
+        if constexpr (SPEC) load_ac();
     }
+    BSG_STAMP(7);
     const int nl = valid ? nlv : 0;
     const bool live = valid && i < nl;
-    if (live) {
-        ac_load_raw<R, RESO, EXT>(a, A.pos, A.st, EN, k);
-        if (reso) resorow = A.reso[k];
-        ac_derive<R, EXT>(a);
-    }
+    if constexpr (SPEC) {
+        if (live) ac_derive<R, EXT>(a);
+        else { a = AcReg<R>{}; resorow = 0; }                              // dead slots: the zero state
+    } else if (live) { load_ac(); ac_derive<R, EXT>(a); }
     // the env-level scalar slots, staged in shared memory by the first lanes of the env
     if (valid) {
         if (i < BSG_EV_POLY) es[le].ev[i] = ev_mine;
@@ -539,12 +555,14 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             }
             if (A.asas_on) {
                 __syncthreads();
+                if (s0 == 0) BSG_STAMP(5);
                 if (live && !skip) {
                     for (int s = s0; s < s1; s++) {
                         const unsigned F = sweep_row(row0 + (size_t)(s - s0) * bstride);
                         if (s == K - 1) Flast = F; else Fany |= F;
                     }
                 }
+                if (s0 == 0) BSG_STAMP(6);
                 lastrow = K - 1 - s0;
             }
         }
