@@ -25,7 +25,7 @@ class Config(C.Structure):
     _fields_ = [('struct_size', C.c_int32), ('env_kind', C.c_int32), ('num_envs', C.c_int32), ('max_ac', C.c_int32),
                 ('precision', C.c_int32), ('substeps', C.c_int32), ('asas_on', C.c_int32), ('reso_on', C.c_int32),
                 ('reso_off_own', C.c_int32), ('max_episode_steps', C.c_int32), ('device', C.c_int32),
-                ('fixed_nac', C.c_int32), ('density_mode', C.c_int32), ('reserved0', C.c_int32),
+                ('fixed_nac', C.c_int32), ('density_mode', C.c_int32), ('reso_mode', C.c_int32),
                 ('simdt', C.c_double), ('rpz_m', C.c_double), ('hpz_m', C.c_double),
                 ('dtlookahead', C.c_double), ('resofach', C.c_double), ('resofacv', C.c_double)]
 

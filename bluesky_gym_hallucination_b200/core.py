@@ -47,8 +47,11 @@ class BsgCore:
 
     def __init__(self, kind, num_envs, max_ac, precision='fp32', device=0, substeps=0, simdt=0.0, asas_on=False,
                  reso_on=False, reso_off_own=False, max_episode_steps=0, rpz_m=0.0, hpz_m=0.0, dtlookahead=0.0,
-                 cd_outputs=False, fixed_nac=False, density_mode='normal'):
+                 cd_outputs=False, fixed_nac=False, density_mode='normal', reso_mode=0):
+        """reso_mode: MVP resolution method (BlueSky RMETHH / RMETHV) -- 0 / 'horizontal' (heading + speed, the default),
+        1 / 'vertical' (vertical speed only), 2 / 'both' (horizontal + vertical); needs reso_on."""
         self.lib = L.load()
+        reso_mode = {'horizontal': 0, 'vertical': 1, 'both': 2}.get(reso_mode, reso_mode)
         if not torch.cuda.is_available():
             raise L.BsgError("libbsgcore needs a CUDA device (no CPU fallback)")
         self.kind, self.E, self.N = kind, num_envs, max_ac
@@ -58,7 +61,7 @@ class BsgCore:
         self.npdtype = np.float64 if self.fp64 else np.float32
         cfg = L.Config(C.sizeof(L.Config), kind, num_envs, max_ac, L.FP64 if self.fp64 else L.FP32, substeps,
                        int(asas_on), int(reso_on), int(reso_off_own), max_episode_steps, device, int(fixed_nac),
-                       {'normal': 0, 'uniform': 1}[density_mode], 0, simdt, rpz_m,
+                       {'normal': 0, 'uniform': 1}[density_mode], int(reso_mode), simdt, rpz_m,
                        hpz_m, dtlookahead, 0.0, 0.0)
         self.h = C.c_void_p()
         rc = self.lib.bsg_create(C.byref(cfg), C.byref(self.h))

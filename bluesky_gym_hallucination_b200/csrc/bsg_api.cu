@@ -121,6 +121,8 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     if (c->env_kind == BSG_KIND_MERGE && (c->max_ac < 2 || c->max_ac > 64)) return BSG_ERR_UNSUPPORTED;   // EXT kernels: N <= 64
     if (c->max_ac > 256) return BSG_ERR_UNSUPPORTED;          // fused step: one env's rows live in one CTA
     if (c->reso_on && (c->max_ac > 64 || !c->asas_on)) return BSG_ERR_UNSUPPORTED;
+    if (c->reso_mode < 0 || c->reso_mode > 2 || (c->reso_mode != 0 && !c->reso_on)) return BSG_ERR_ARG;
+    if (c->reso_mode != 0 && c->env_kind == BSG_KIND_MERGE && c->precision != BSG_FP64) return BSG_ERR_UNSUPPORTED;   // fp32 EXT kernels: symmetric sweep only
     int ndev = 0;
     if (bsg_device_count(&ndev) != BSG_OK || ndev < 1) return BSG_ERR_NODEVICE;
     if (c->device < 0 || c->device >= ndev) return BSG_ERR_ARG;
@@ -182,7 +184,7 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
         const bool reso = g.reso_on && g.asas_on;
         h->nbuf = g.precision == BSG_FP64 ? step_nbuf<double>(N, h->epb, reso) : step_nbuf<float>(N, h->epb, reso);
         if (const char *f = getenv("BSG_FORCE_NBUF")) { int t = atoi(f); if (t >= 2 && t <= 16) h->nbuf = t; }
-        const bool pairs = reso && g.precision != BSG_FP64 && N <= 64 && !getenv("BSG_NO_SYM");   // the symmetric sweep's pair scratch
+        const bool pairs = reso && g.precision != BSG_FP64 && N <= 64 && !getenv("BSG_NO_SYM") && g.reso_mode == 0;   // the symmetric sweep's pair scratch
         h->smem = g.precision == BSG_FP64 ? step_smem<double>(N, h->epb, h->nbuf, false).total : step_smem<float>(N, h->epb, h->nbuf, pairs).total;
     }
     CK(h, cudaSetDevice(g.device));

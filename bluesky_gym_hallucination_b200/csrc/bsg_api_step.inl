@@ -7,7 +7,7 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     StepArgs<R> A;
     A.kind = g.env_kind; A.E = g.num_envs; A.N = g.max_ac; A.substeps = substeps; A.asas_on = g.asas_on;
     A.reso_on = g.reso_on; A.reso_off_own = g.reso_off_own; A.max_steps = g.max_episode_steps; A.epb = h->epb;
-    A.observe_only = observe_only; A.nbuf = h->nbuf; A.force_walk = getenv("BSG_FORCE_WALK") ? 1 : 0;
+    A.observe_only = observe_only; A.nbuf = h->nbuf; A.force_walk = getenv("BSG_FORCE_WALK") ? 1 : 0; A.reso_mode = g.reso_mode;
     A.dt = (R)g.simdt;
     A.P.rpz = g.rpz_m; A.P.hpz = g.hpz_m; A.P.dtlook = g.dtlookahead; A.P.fach = g.resofach; A.P.facv = g.resofacv;
     cd_params_fast(A.P, A.PF);
@@ -33,9 +33,11 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     if constexpr (sizeof(R) == 4) {
         if (ext) {
             if (g.max_ac > 64) { h->err = "EXT kernels (fp32): N <= 64"; return BSG_ERR_UNSUPPORTED; }
+            if (reso && g.reso_mode != 0) { h->err = "EXT kernels (fp32): horizontal resolution method only (reso_mode 0)"; return BSG_ERR_UNSUPPORTED; }
             le = launch_step_f32_ext(h->tpb, reso, gd, bd, h->smem, s, A);
         } else {
-            const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM");     // symmetric half-ring sweep (fp32 fast path)
+            // symmetric half-ring sweep (fp32 fast path); the resolution methods with a vertical term run the ordered sweep
+            const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM") && !(reso && g.reso_mode != 0);
             if (sym && !reso && h->wepb > 0) {
                 // detection only: the one-wave shape picked at creation (whole warps balanced over the SMs)
                 A.epb = h->wepb; A.nbuf = h->wnbuf;

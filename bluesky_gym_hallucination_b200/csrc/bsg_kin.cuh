@@ -266,13 +266,14 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     }
     int ph = flight_phase<float>(a.vs, a.alt);
     a.phase = ph;
-    float allow_h = fminf(a.selalt, float(kHmax));           // asas alt == selalt for horizontal resolutions
-    if (float(ph) != a.c_ph || a.selalt != a.c_selalt) {     // TAS-domain clamp limits: pure f(phase, allow_h)
+    const float t_alt = act ? a.asas_alt : a.selalt;         // (== selalt under the default, horizontal resolution method)
+    float allow_h = fminf(t_alt, float(kHmax));
+    if (float(ph) != a.c_ph || t_alt != a.c_selalt) {        // TAS-domain clamp limits: pure f(phase, allow_h)
         double vmin, vmax;
         phase_vlimits(ph, vmin, vmax);
         double lo = vmin > 0.0 ? vcas2tas_fast(vmin, (double)allow_h) : 0.0;
         double hi = fmin(vcas2tas_fast(vmax, (double)allow_h), kMmo * vvsound((double)allow_h));
-        a.c_lo = (float)lo; a.c_hi = (float)hi; a.c_ph = float(ph); a.c_selalt = a.selalt;
+        a.c_lo = (float)lo; a.c_hi = (float)hi; a.c_ph = float(ph); a.c_selalt = t_alt;
     }
     float atas = fminf(fmaxf(t_tas, a.c_lo), a.c_hi);
     float avs = (t_vs > float(kVsMax)) ? (1.0f - a.ax / float(kAxMax)) * float(kVsMax) : t_vs;

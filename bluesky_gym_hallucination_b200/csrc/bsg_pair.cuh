@@ -158,6 +158,18 @@ __device__ __forceinline__ void mvp_pair(R dx, R dy, R dist, R tcpa, R vrelx, R 
     }
 }
 
+// Vertical term of MVP.MVP, evaluated only by the resolution methods that use it (reso_mode 1, 2):
+// intrusion iV and time to solve tsolV from the relative altitude / vertical speed; tLOS = tin of the conflict.
+// The |vrel_z| > 0 tests are BlueSky's exact-zero switches.
+template <typename R>
+__device__ __forceinline__ void mvp_vert(R dalt, R vrelz, R tLOS, R hpz_m, R dtlook, R &dv3, R &tsolV) {
+    const bool moving = fabs(vrelz) > R(0);
+    R iV = moving ? hpz_m : hpz_m - fabs(dalt);
+    tsolV = moving ? fabs(dalt / vrelz) : tLOS;
+    if (tsolV > dtlook) { tsolV = tLOS; iV = hpz_m; }
+    dv3 = moving ? (iV / tsolV) * (-vrelz / fabs(vrelz)) : iV / tsolV;
+}
+
 // fp32 fast form of mvp_pair: same algebra, no inverse trigonometry and no IEEE divide.
 //   cos(asin a - asin b) = sqrt((1 - a^2)(1 - b^2)) + a b      (a = rpz_m/dist, b = |dcpa_h|/dist, both in [0, 1))
 // with 1 - a^2 = (dist^2 - rpz_m^2)/dist^2 taken from the squared quantities (no cancellation beyond the inputs').

@@ -17,6 +17,7 @@ namespace bsg {
 template <typename R> struct StepArgs {
     int kind, E, N, substeps, asas_on, reso_on, reso_off_own, max_steps, epb, observe_only;
     int nbuf;             // record rows per env in shared memory (step_nbuf)
+    int reso_mode;        // MVP resolution method: 0 horizontal (default), 1 vertical only, 2 horizontal + vertical (ordered-sweep kernels)
     int force_walk;       // test hook (BSG_FORCE_WALK): resolution kernels drop the pair work list, every owner walks its row
     R dt;
     CdParams P;

@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     unsigned char *const row0 = recs + (size_t)le * rowb;
     const size_t bstride = (size_t)epb * rowb;
     const int NR = sym_row_recs(N);
-    R dve = R(0), dvn = R(0);
+    R dve = R(0), dvn = R(0), dvz = R(0), tsolmin = R(1e9);           // MVP sums; vertical term / timesolveV (reso_mode 1, 2)
     bool touched = false, active = false;
     unsigned long long keep = 0;
     auto kin = [&](int s) {
@@ -591,7 +591,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
             __syncthreads();
             if (RESO && valid && i == 0) { es[le].anyconf[buf ^ 1] = 0; es[le].ovf = 0; }
             acc = RowAcc<R>();
-            dve = R(0); dvn = R(0);
+            dve = R(0); dvn = R(0); dvz = R(0); tsolmin = R(1e9);
             touched = false; active = false;
             keep = 0;
             if constexpr (SYM) {
@@ -639,7 +639,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                         PairCore pc;
                         po.sw = pair_fast_core(me, o, PF, off, pc);
                         po.los = false;
-                        po.tcpa = pc.tcpa; po.dcpa2 = pc.dcpa2; po.tin = pc.tin; po.dx = pc.dx; po.dy = pc.dy; po.dist = pc.dist2;
+                        po.tcpa = pc.tcpa; po.dcpa2 = pc.dcpa2; po.tin = pc.tin; po.dx = pc.dx; po.dy = pc.dy; po.dist = pc.dist2; po.dalt = pc.dalt;
                         if (__any_sync(__activemask(), po.sw)) {   // conflicting pairs only: row reductions off the hot path
                             if (po.sw) acc.add_conflict(j, pc.tcpa, pc.dcpa2, pc.tin, (pc.dist2 < PF.R2) && (fabsf(pc.dalt) < PF.hpz));
                         }
@@ -654,7 +654,14 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                                 else { dist = sqrtf(po.dist); rpz_m = PF.rpz_m; }
                                 mvp_pair<R>(po.dx, po.dy, dist, po.tcpa, vrx, vry, rpz_m, d1, d2);
                                 dve = dve - d1; dvn = dvn - d2;
-                                if (A.reso_off_own && i == 0) { dve = R(0); dvn = R(0); }
+                                if (A.reso_mode != 0) {                    // vertical term: dv3 halved (cooperative), timesolveV
+                                    R d3, tsv;
+                                    const R hpz_m = sizeof(R) == 8 ? R(PL.hpz * PL.facv) : R(PF.hpz_m), dtl = sizeof(R) == 8 ? R(PL.dtlook) : R(PF.dtlook);
+                                    mvp_vert<R>(po.dalt, o.vs - me.vs, po.tin, hpz_m, dtl, d3, tsv);
+                                    tsolmin = tsv < tsolmin ? tsv : tsolmin;
+                                    dvz = dvz - R(0.5) * d3;
+                                }
+                                if (A.reso_off_own && i == 0) { dve = R(0); dvn = R(0); dvz = R(0); }
                             }
                             R ddx, ddy, rpz, fach;
                             if constexpr (sizeof(R) == 8) {
@@ -680,14 +687,31 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 if (live && !skip) {
                     if (es[le].anyconf[buf]) {                             // MVP.resolve ran for this env
                         R ne = a.gse + dve, nn = a.gsn + dvn;
+                        if (A.reso_mode == 1) { ne = a.gse; nn = a.gsn; }      // vertical only: ownship.trk / ownship.gs kept
                         double vmin, vmax;
                         phase_vlimits(a.phase, vmin, vmax);
-                        if constexpr (sizeof(R) == 8) a.asas_trk = pymod(atan2(ne, nn) * 180 / kPi, 360);
+                        bool wind_on = false;
+                        if constexpr (EXT) wind_on = A.W.n > 0;
+                        if (A.reso_mode == 1 && !wind_on) a.asas_trk = a.hdg;
+                        else if constexpr (sizeof(R) == 8) a.asas_trk = pymod(atan2(ne, nn) * 180 / kPi, 360);
                         else { float t = atan2f(ne, nn) * float(kR2D); a.asas_trk = t < 0.0f ? t + 360.0f : t; }
-                        R newgs = sqrt(ne * ne + nn * nn);
+                        R newgs = (A.reso_mode == 1 && !wind_on) ? a.tas : sqrt(ne * ne + nn * nn);
                         a.asas_tas = fmax(R(vmin), fmin(R(vmax), newgs));
-                        a.asas_vs = fmax(R(kVsMin), fmin(R(kVsMax), a.vs));
-                        a.asas_alt = a.selalt;
+                        const R vscap = fmax(R(kVsMin), fmin(R(kVsMax), A.reso_mode == 0 ? a.vs : a.vs + dvz));
+                        a.asas_vs = vscap;
+                        if (A.reso_mode == 0) a.asas_alt = a.selalt;
+                        else {
+                            // resolution altitude (tail of MVP.resolve): the autopilot's level-off altitude when it also
+                            // solves the conflict, else the altitude reached after timesolveV at the capped vertical speed
+                            auto sgn = [](R x) -> R { return x > R(0) ? R(1) : (x < R(0) ? R(-1) : R(0)); };
+                            const R apvs = fabs(a.selvs) > R(0.1) ? a.selvs : R(kVsDef);
+                            const R tmp = vscap * tsolmin + a.alt;
+                            const R sdv = sgn(vscap - apvs * sgn(a.selalt - a.alt)), sal = sgn(tmp - a.selalt);
+                            R ra = (sdv == R(0) || sdv == sal) ? tmp : a.selalt;
+                            const R dtl = sizeof(R) == 8 ? R(PL.dtlook) : R(PF.dtlook);
+                            if (tsolmin < dtl && fabs(dvz) > R(0)) ra = tmp;
+                            a.asas_alt = ra;
+                        }
                     }
                     if (touched) a.asas_active = active ? 1 : 0;
                     resorow = keep;

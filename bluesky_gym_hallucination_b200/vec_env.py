@@ -51,7 +51,10 @@ class BlueSkyVecEnv:
                  ac_density_mode='normal', fixed_nac=False):
         """wind = (lat, lon, vnorth, veast) like WindFieldWrapper(env, lat, lon, vnorth, veast, augment_obs=wind_obs);
         obs_noise = NoisyObservationWrapper(env, noise_level); ac_density_mode = SectorCREnv's "normal" | "uniform"
-        (sector_cr_env.py:45,98-103); fixed_nac = every aircraft slot live (the synthetic scale-up configs)."""
+        (sector_cr_env.py:45,98-103); fixed_nac = every aircraft slot live (the synthetic scale-up configs).
+        mvp = True | 'horizontal' (BlueSky's default resolution method, heading + speed) | 'vertical' (RMETHV V/S) |
+        'both' (horizontal + vertical): ASAS ON + RESO MVP for the intruders, RESOOFF for the agent."""
+        reso_mode = {True: 0, 'horizontal': 0, 'vertical': 1, 'both': 2}[mvp] if mvp else 0
         if ac_density_mode not in ('normal', 'uniform'):
             raise ValueError(f"ac_density_mode must be 'normal' or 'uniform', not {ac_density_mode!r}")
         if env_id not in ENV_SPECS:
@@ -60,7 +63,7 @@ class BlueSkyVecEnv:
         self.env_id, self.kind, self.num_envs = env_id, kind, int(num_envs)
         self.num_aircraft = int(num_aircraft or n_ref)
         self.core = BsgCore(kind, self.num_envs, self.num_aircraft, precision=precision, device=device,
-                            asas_on=asas or mvp, reso_on=mvp, reso_off_own=mvp,
+                            asas_on=bool(asas or mvp), reso_on=bool(mvp), reso_off_own=bool(mvp), reso_mode=reso_mode,
                             max_episode_steps=max_steps if max_episode_steps is None else max_episode_steps,
                             cd_outputs=cd_outputs, density_mode=ac_density_mode, fixed_nac=fixed_nac)
         if wind is not None:

@@ -73,7 +73,11 @@ typedef struct bsg_config {
                                  configs, SURVEY 8d C3 "N fixed"); 0 = the reference's density law (sector_cr_env.py:98-100) */
     int32_t density_mode;     /* Sector reset, SectorCREnv(ac_density_mode=...) (sector_cr_env.py:45,98-103): 0 = "normal"
                                  N(0.005, 0.001) aircraft per NM^2, 1 = "uniform" U(0.003, 0.007) */
-    int32_t reserved0;        /* keeps the doubles 8-aligned; must be 0 */
+    int32_t reso_mode;        /* MVP resolution method (BlueSky stack RMETHH / RMETHV; same offset as ABI 3's reserved0):
+                                 0 = horizontal, heading + speed (BlueSky's default), 1 = vertical speed only (RMETHV V/S),
+                                 2 = horizontal + vertical (RMETHH OFF, RMETHV OFF).  1 and 2 evaluate MVP's vertical
+                                 term, timesolveV and the resolution altitude; they run on the ordered-sweep
+                                 kernels (any precision; no wind / Merge in fp32) */
     double simdt;             /* 0 = the reference's DT for env_kind (5/1/1 s) */
     double rpz_m, hpz_m;      /* protected zone; 0 = 5 NM / 1000 ft */
     double dtlookahead;       /* 0 = 300 s */

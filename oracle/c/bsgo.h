@@ -45,6 +45,9 @@ typedef struct {
      * wind_obs = augment_obs (two more observation slots: wind_u, wind_v) */
     int32_t nwind, wind_obs;
     double wlat[BSGO_MAXWIND], wlon[BSGO_MAXWIND], wvn[BSGO_MAXWIND], wve[BSGO_MAXWIND];
+    /* MVP resolution method (stack commands RMETHH / RMETHV): 0 = horizontal, heading + speed (BlueSky's default),
+     * 1 = vertical speed only (RMETHV V/S), 2 = horizontal + vertical (RMETHH OFF, RMETHV OFF) */
+    int32_t reso_mode, pad0;
 } bsgo_cfg;
 
 /* per-aircraft CD outputs of the last detection of a step */

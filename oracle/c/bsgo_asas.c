@@ -7,12 +7,13 @@
 #include <string.h>
 #include "bsgo_int.h"
 
+static double bsgo_sign(double x) { return x > 0.0 ? 1.0 : (x < 0.0 ? -1.0 : 0.0); }
 static double relm(double a, double b) { double s = fmax(fabs(a), fabs(b)); return s > 0 ? fabs(a - b) / s : 0.0; }
 
 static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
                      double alt1, double alt2, const double v1[3], const double v2[3],
                      double rpz, double hpz, double dtlook, double fach, double facv,
-                     double dv[3], double *tsolV_o, bsgo_trace *tr) {
+                     double dv[3], double *tsolV_o, bsgo_trace *tr, int vert) {
     double rpz_m = rpz * fach, hpz_m = hpz * facv;
     double q = qdr * C_D2R;
     double drel[3] = { sin(q) * dist, cos(q) * dist, alt2 - alt1 };
@@ -62,6 +63,16 @@ static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
     double iV, tsolV;
     if (fabs(vrel[2]) > 0.0) { iV = hpz_m; tsolV = fabs(drel[2] / vrel[2]); }
     else { iV = hpz_m - fabs(drel[2]); tsolV = tLOS; }
+    if (tr && vert && tr->res_margin) {
+        /* thresholds of the vertical term (they steer a resolution only when the method uses it): the |vrel_z| > 0
+           switch -- an EXACT-zero test: two aircraft that resolve against each other symmetrically hold vertical speeds
+           that agree to the last bit or not depending on the rounding of tLOS(i,j) vs tLOS(j,i), in any precision --
+           and tsolV > dtlookahead */
+        double m = fabs(vrel[2]) / fmax(fmax(fabs(v1[2]), fabs(v2[2])), 1.0);
+        if (fabs(v1[2]) == 0.0 && fabs(v2[2]) == 0.0) m = 1e30;           /* both exactly level: a stable zero */
+        m = fmin(m, relm(tsolV, dtlook));
+        if (m < tr->res_margin[tr->row]) tr->res_margin[tr->row] = m;
+    }
     if (tsolV > dtlook) { tsolV = tLOS; iV = hpz_m; }
     if (fabs(vrel[2]) > 0.0) dv[2] = (iV / tsolV) * (-vrel[2] / fabs(vrel[2]));
     else dv[2] = iV / tsolV;
@@ -79,8 +90,8 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
         if (tr->near_los) memset(tr->near_los, 0, n);
     }
 #define A(f, i) a[(f) * n + (i)]
-    double *u = malloc(sizeof(double) * nlive * 5);
-    double *v = u + nlive, *dve = v + nlive, *dvn = dve + nlive, *dvz = dvn + nlive;
+    double *u = malloc(sizeof(double) * nlive * 6);
+    double *v = u + nlive, *dve = v + nlive, *dvn = dve + nlive, *dvz = dvn + nlive, *tsolmin = dvz + nlive;
     uint64_t *confrow = calloc(nlive, sizeof(uint64_t));
     int anyconf = 0;
     const int wind = cfg->nwind > 0;
@@ -89,6 +100,7 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
         u[i] = wind ? A(F_GSE, i) : A(F_TAS, i) * sin(A(F_HDG, i) * C_D2R);
         v[i] = wind ? A(F_GSN, i) : A(F_TAS, i) * cos(A(F_HDG, i) * C_D2R);
         dve[i] = dvn[i] = dvz[i] = 0.0;
+        tsolmin[i] = 1e9;                 /* timesolveV */
     }
     for (int i = 0; i < nlive; i++) {
         bsgo_row *r = &rows[i];
@@ -126,7 +138,8 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
                     tr->row = i; tr->rabs = sqrt(x0 * x0 + y0 * y0) + dist;
                 }
                 mvp_pair(qdr, dist, tcpa, tin, A(F_ALT, i), A(F_ALT, j), v1, v2,
-                         cfg->rpz, cfg->hpz, cfg->dtlook, cfg->resofach, cfg->resofacv, dv, &tsolV, tr);
+                         cfg->rpz, cfg->hpz, cfg->dtlook, cfg->resofach, cfg->resofacv, dv, &tsolV, tr, cfg->reso_mode != 0);
+                if (tsolV < tsolmin[i]) tsolmin[i] = tsolV;
                 dv[2] = 0.5 * dv[2];
                 dve[i] = dve[i] - dv[0]; dvn[i] = dvn[i] - dv[1]; dvz[i] = dvz[i] - dv[2];
                 if (cfg->reso_off_own && i == 0) { dve[i] = 0.0; dvn[i] = 0.0; dvz[i] = 0.0; }
@@ -138,14 +151,38 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
             for (int i = 0; i < nlive; i++) {
                 double ge = u[i], gn = v[i];
                 double ne = ge + dve[i], nn = gn + dvn[i];
-                double newtrack = bsgo_pymod(atan2(ne, nn) * 180 / C_PI, 360);
-                double newgs = sqrt(ne * ne + nn * nn);
+                double newtrack, newgs, newvs;
+                if (cfg->reso_mode == 1) {        /* vertical only: ownship.trk / ownship.gs kept */
+                    newtrack = wind ? bsgo_pymod(atan2(ge, gn) * 180 / C_PI, 360) : A(F_HDG, i);
+                    newgs = wind ? sqrt(ge * ge + gn * gn) : A(F_TAS, i);
+                } else {
+                    newtrack = bsgo_pymod(atan2(ne, nn) * 180 / C_PI, 360);
+                    newgs = sqrt(ne * ne + nn * nn);
+                }
+                newvs = cfg->reso_mode == 0 ? A(F_VS, i) : A(F_VS, i) + dvz[i];
                 double vmin, vmax;
                 bsgo_vlimits((int)A(F_PHASE, i), &vmin, &vmax);
+                const double vscapped = fmax(ENV_VSMIN, fmin(ENV_VSMAX, newvs));
                 A(F_ASAS_TRK, i) = newtrack;
                 A(F_ASAS_TAS, i) = fmax(vmin, fmin(vmax, newgs));
-                A(F_ASAS_VS, i) = fmax(ENV_VSMIN, fmin(ENV_VSMAX, A(F_VS, i)));
-                A(F_ASAS_ALT, i) = A(F_SELALT, i);
+                A(F_ASAS_VS, i) = vscapped;
+                if (cfg->reso_mode == 0) A(F_ASAS_ALT, i) = A(F_SELALT, i);
+                else {
+                    /* resolution altitude (tail of MVP.resolve): the autopilot's level-off altitude when it also solves
+                       the conflict, else the altitude reached after timesolveV at the capped vertical speed */
+                    const double apvs = fabs(A(F_SELVS, i)) > 0.1 ? A(F_SELVS, i) : C_VSDEF;
+                    const double sel = A(F_SELALT, i), alt = A(F_ALT, i);
+                    const double tmp = vscapped * tsolmin[i] + alt;
+                    const double sdv = bsgo_sign(vscapped - apvs * bsgo_sign(sel - alt)), sal = bsgo_sign(tmp - sel);
+                    double ra = (sdv == 0.0 || sdv == sal) ? tmp : sel;
+                    if (tsolmin[i] < cfg->dtlook && fabs(dvz[i]) > 0.0) ra = tmp;
+                    if (tr && tr->res_margin) {       /* the sign tests and the look-ahead test of the altitude choice */
+                        double m = fmin(relm(vscapped, apvs * bsgo_sign(sel - alt)), fmin(relm(tmp, sel), relm(tsolmin[i], cfg->dtlook)));
+                        if (fabs(sel - alt) < 1e-6 * fmax(fabs(sel), 1.0)) m = 0.0;
+                        if (fabs(dvz[i]) > 0.0 && m < tr->res_margin[i]) tr->res_margin[i] = m;
+                    }
+                    A(F_ASAS_ALT, i) = ra;
+                }
             }
         }
         /* resumenav: resopairs |= confpairs; keep a pair while not past CPA, or in horizontal LoS, or bouncing */

@@ -31,7 +31,8 @@ class Cfg(C.Structure):
                 ('reso_on', C.c_int32), ('reso_off_own', C.c_int32), ('simdt', C.c_double), ('rpz', C.c_double),
                 ('hpz', C.c_double), ('dtlook', C.c_double), ('resofach', C.c_double), ('resofacv', C.c_double),
                 ('nwind', C.c_int32), ('wind_obs', C.c_int32), ('wlat', C.c_double * MAXWIND),
-                ('wlon', C.c_double * MAXWIND), ('wvn', C.c_double * MAXWIND), ('wve', C.c_double * MAXWIND)]
+                ('wlon', C.c_double * MAXWIND), ('wvn', C.c_double * MAXWIND), ('wve', C.c_double * MAXWIND),
+                ('reso_mode', C.c_int32), ('pad0', C.c_int32)]
 
 
 class CdOut(C.Structure):
@@ -73,12 +74,14 @@ def _p(a):
 
 
 def make_cfg(kind, n, substeps=None, simdt=None, asas_on=0, reso_on=0, reso_off_own=0,
-             rpz=5 * NM, hpz=1000 * FT, dtlook=300.0, resofach=1.05, resofacv=1.05, wind=None, wind_obs=0):
-    """wind = (lat[], lon[], vnorth[], veast[]) of the WindFieldWrapper's points (scalars allowed), or None."""
+             rpz=5 * NM, hpz=1000 * FT, dtlook=300.0, resofach=1.05, resofacv=1.05, wind=None, wind_obs=0, reso_mode=0):
+    """wind = (lat[], lon[], vnorth[], veast[]) of the WindFieldWrapper's points (scalars allowed), or None.
+    reso_mode: MVP resolution method, 0 horizontal (default) / 1 vertical only / 2 horizontal + vertical."""
     d_sub = {KIND_H: 10, KIND_V: 30, KIND_S: 5, KIND_RAW: 1, KIND_M: 10}
     d_dt = {KIND_H: 5.0, KIND_V: 1.0, KIND_S: 1.0, KIND_RAW: 1.0, KIND_M: 5.0}
     c = Cfg(kind, n, d_sub[kind] if substeps is None else substeps, asas_on, reso_on, reso_off_own,
             d_dt[kind] if simdt is None else simdt, rpz, hpz, dtlook, resofach, resofacv)
+    c.reso_mode = int(reso_mode)
     if wind is not None:
         wl, wo, vn, ve = [np.atleast_1d(np.asarray(x, dtype=np.float64)) for x in wind]
         vn = np.broadcast_to(vn, wl.shape); ve = np.broadcast_to(ve, wl.shape)

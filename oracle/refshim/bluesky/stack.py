@@ -32,7 +32,7 @@ class Stack:
         cmd = tok[0].upper()
         t = self.traf
         # "ACID CMD args" form
-        if cmd not in ('DT', 'FF', 'HDG', 'SPD', 'ASAS', 'RESO', 'RESOOFF', 'NORESO') and len(tok) > 1:
+        if cmd not in ('DT', 'FF', 'HDG', 'SPD', 'ASAS', 'RESO', 'RESOOFF', 'NORESO', 'RMETHH', 'RMETHV') and len(tok) > 1:
             tok[0], tok[1] = tok[1], tok[0]
             cmd = tok[0].upper()
         if cmd == 'DT':
@@ -57,6 +57,16 @@ class Stack:
             if not t.cr.enabled:
                 t.cr.active[:] = False
                 t.cr.resopairs = set()
+        elif cmd == 'RMETHH':     # resolution method, horizontal: BOTH / ON (default) | OFF / NONE
+            on = tok[1].upper() in ('BOTH', 'ON')
+            t.cr.swresohoriz = on
+            if on:
+                t.cr.swresovert = False
+        elif cmd == 'RMETHV':     # resolution method, vertical: V/S / ON = vertical only | OFF / NONE
+            on = tok[1].upper() in ('V/S', 'ON')
+            t.cr.swresovert = on
+            if on:
+                t.cr.swresohoriz = False
         elif cmd == 'RESOOFF':
             idx = t.id2idx(tok[1])
             if idx >= 0:

@@ -3,8 +3,11 @@
 CPU restatement of BlueSky's MVP resolver (``bluesky/traffic/asas/mvp.py``:
 ``MVP.resolve`` / ``MVP.MVP``) and of ``ConflictResolution.resumenav``
 (``bluesky/traffic/asas/resolution.py``), SURVEY.md A.7.  Defaults restated:
-resofach = resofacv = 1.05, horizontal (HDG+SPD) resolution only, no priority
-rules.  parity unpinned vs upstream (bluesky-simulator==1.0.3 un-vendored).
+resofach = resofacv = 1.05, horizontal (HDG+SPD) resolution, no priority rules.
+The resolution-method switches of the stack commands RMETHH / RMETHV
+(``swresohoriz``, ``swresovert``) select horizontal (default), vertical-only
+or combined resolutions; the vertical term, ``timesolveV`` and the resolution
+altitude follow the tail of ``MVP.resolve``.  parity unpinned vs upstream (bluesky-simulator==1.0.3 un-vendored).
 Pairs are (ownship index, intruder index); aircraft are never deleted mid-episode
 in the hot envs, so indices stand in for callsigns.
 """
@@ -20,7 +23,8 @@ class MVP:
         self.enabled = False
         self.resofach = settings.asas_marh
         self.resofacv = settings.asas_marv
-        self.swresohoriz = True
+        self.swresohoriz = True      # RMETHH BOTH (the default): heading + speed
+        self.swresovert = False      # RMETHV V/S: vertical speed only
         self.reset()
 
     def reset(self):
@@ -108,14 +112,31 @@ class MVP:
         dv = dv.T
         v = np.array([t.gseast, t.gsnorth, t.vs])
         newv = v + dv
-        # default resolution method: horizontal, heading + speed
-        newtrack = (np.arctan2(newv[0, :], newv[1, :]) * 180 / np.pi) % 360
-        newgs = np.sqrt(newv[0, :] ** 2 + newv[1, :] ** 2)
-        newvs = t.vs
+        if self.swresohoriz:          # horizontal, heading + speed (the default method)
+            newtrack = (np.arctan2(newv[0, :], newv[1, :]) * 180 / np.pi) % 360
+            newgs = np.sqrt(newv[0, :] ** 2 + newv[1, :] ** 2)
+            newvs = t.vs
+        elif self.swresovert:         # vertical speed only
+            newtrack = t.trk.copy()
+            newgs = t.gs.copy()
+            newvs = newv[2, :]
+        else:                         # horizontal + vertical
+            newtrack = (np.arctan2(newv[0, :], newv[1, :]) * 180 / np.pi) % 360
+            newgs = np.sqrt(newv[0, :] ** 2 + newv[1, :] ** 2)
+            newvs = newv[2, :]
         newgscapped = np.maximum(t.perf.vmin, np.minimum(t.perf.vmax, newgs))
         vscapped = np.maximum(t.perf.vsmin, np.minimum(t.perf.vsmax, newvs))
-        # horizontal-only resolution: ASAS altitude equals the selected altitude
-        alt = t.selalt.copy()
+        # Resolution altitude: follow the autopilot's level-off altitude when it also solves the conflict, else
+        # the altitude reached after timesolveV at the capped vertical speed
+        asasalttemp = vscapped * timesolveV + t.alt
+        signdvs = np.sign(vscapped - t.ap.vs * np.sign(t.selalt - t.alt))
+        signalt = np.sign(asasalttemp - t.selalt)
+        alt = np.where(np.logical_or(signdvs == 0, signdvs == signalt), asasalttemp, t.selalt)
+        altcond = np.logical_and(timesolveV < cd.dtlookahead, np.abs(dv[2, :]) > 0.0)
+        alt = np.where(altcond, asasalttemp, alt)
+        # horizontal-only resolutions: ASAS altitude equals the selected altitude
+        if self.swresohoriz:
+            alt = t.selalt.copy()
         self.dv_last = dv.T.copy()
         self.timesolveV = timesolveV
         return newtrack, newgscapped, vscapped, alt

@@ -105,6 +105,14 @@ def record(kind, seed, episodes, max_steps, asas=False, n_pad=None, wind=None):
         obs, info = env.reset()
         if asas:   # the north-star feature on top of the reference: ASAS ON + MVP for the intruders
             bs.stack.stack('ASAS ON'); bs.stack.stack('RESO MVP'); bs.stack.stack('RESOOFF KL001')
+            # resolution method (BlueSky RMETHH / RMETHV): True = the default (horizontal, heading + speed),
+            # 'v' = vertical speed only, 'hv' = horizontal + vertical
+            if asas == 'v':
+                bs.stack.stack('RMETHV V/S')
+            elif asas == 'hv':
+                bs.stack.stack('RMETHH OFF'); bs.stack.stack('RMETHV OFF')
+            else:
+                bs.stack.stack('RMETHV OFF'); bs.stack.stack('RMETHH BOTH')
             bs.stack.process()
         if kind == 'M':   # flush the route commands reset() queued (ADDWPT / DEST / RESO OFF) so that the
             bs.stack.process()   # snapshot below already holds the LNAV state the first sim.step() would set
@@ -142,13 +150,21 @@ def main():
              ('H', 21, 3, 30, True, None, '_asas'), ('S', 23, 3, 60, True, None, '_asas'),
              ('M', 31, 4, 50, False, None, ''), ('M', 32, 2, 50, False, W1, '_wind'),
              ('S', 33, 2, 60, False, W1, '_wind'), ('V', 34, 2, 50, False, W3, '_wind'),
-             ('H', 35, 2, 30, False, W1, '_wind'), ('S', 36, 2, 40, True, W3, '_asas_wind')]
+             ('H', 35, 2, 30, False, W1, '_wind'), ('S', 36, 2, 40, True, W3, '_asas_wind'),
+             # MVP resolution methods beyond the default: vertical only / horizontal + vertical
+             ('V', 41, 4, 50, 'v', None, '_mvpv'), ('V', 42, 4, 50, 'hv', None, '_mvphv'),
+             ('H', 43, 3, 30, 'hv', None, '_mvphv'), ('S', 44, 2, 50, 'v', None, '_mvpv')]
+    only = sys.argv[1:]          # e.g. `make_golden.py V_mvpv H_mvphv` regenerates those fixtures alone
     for kind, seed, eps, ms, asas, wind, tag in specs:
+        if only and f"{kind}{tag}" not in only:
+            continue
         R = record(kind, seed, eps, ms, asas, wind=wind)
         name = f"golden_{kind}{tag}.npz"
         np.savez_compressed(os.path.join(HERE, name), **R)
         print(name, 'steps', len(R['rew']), 'terms', int(R['term'].sum()), 'truncs', int(R['trunc'].sum()),
               'asas-active steps', int((R['ac1'][:, orc.F['asas_active']].sum(1) > 0).sum()))
+    if only:
+        return
     # closed-form helper KATs from the reference's functions.py
     import bluesky_gym.envs.common.functions as fn
     kat = dict(gpad=np.array(fn.get_point_at_distance(52, 4, 100, 0)),

@@ -125,6 +125,57 @@ def test_fp32_replays_reference_goldens(orc, name):
     core.close()
 
 
+@pytest.mark.parametrize('name', ['V_mvpv', 'V_mvphv', 'H_mvphv', 'S_mvpv'])
+def test_mvp_vertical_methods_replay_reference_goldens(orc, name):
+    """MVP resolution methods with the vertical term (BlueSky RMETHV V/S = vertical only, RMETHH OFF + RMETHV OFF =
+    horizontal + vertical; SURVEY A.7: dv3, timesolveV, resolution altitude) against goldens recorded from the unmodified
+    reference envs on the shim.  fp64: exact to 200e-12 on every step that is not at one of the vertical term's
+    EXACT-zero switches (enumerated from the oracle's trace, tests/test_oracle_golden.py); fp32 (ordered-sweep kernel):
+    floats to 1e-5 on the steps whose resolution decisions are not within EPS32 of a threshold."""
+    from test_oracle_golden import golden_cfg
+    g = load_golden(name)
+    kind = name[0]
+    mode = 2 if 'mvphv' in name else 1
+    T, _, n = g['ac0'].shape
+    na = 2 if kind == 'S' else 1
+    nac = g['nac'].astype(np.int32)
+    cfg = golden_cfg(orc, name, g)
+    act = np.ascontiguousarray(g['act'][:, :na])
+    tr = orc.step_trace(cfg, g['ac0'].copy(), g['reso0'].copy(), nac, g['ev0'].copy(), act, EPS32, nthreads=4)[5]
+    margin = tr['res_margin'].min(1)
+    F = orc.F
+    idx = [F[k] for k in STATE_FIELDS]
+    live = g['term'] == 0
+    for prec, eps, tol in (('fp64', 1e-9, RT64 * 200), ('fp32', EPS32, None)):
+        core = make_core(KIND[kind], T, n, prec, 1, reso_mode=mode)
+        obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(core, g['ac0'], g['reso0'], nac, g['ev0'], act)
+        ok = (margin >= eps) & live
+        print(f"[{name} {prec}] steps compared {int(ok.sum())} of {T} (within {eps:g} of a resolution threshold: {int((margin < eps).sum())})")
+        assert ok.sum() >= 0.3 * T
+        if prec == 'fp64':
+            assert relerr(obs[ok], g['obs1'][ok]) < tol, relerr(obs[ok], g['obs1'][ok])
+            assert relerr(ac1[ok][:, idx], g['ac1'][ok][:, idx]) < tol
+            assert np.array_equal(reso1[ok], g['reso1'][ok])
+            assert np.array_equal(term[ok], g['term'][ok]) and np.array_equal(trunc[ok], g['trunc'][ok])
+        else:
+            flip = (term != g['term']) | (trunc != g['trunc']) | (np.abs(rew - g['rew']) > 0.5)
+            thr = env_threshold_margin(KIND[kind], g['ac1'], g['ev1'], nac, orc.F, orc.EV) < EPS32
+            assert not (flip & ~thr & ok).any()
+            ok &= ~flip
+            # ill-conditioned pairs (kappa) widen the bound as in test_batched_step_vs_oracle
+            kap = np.nan_to_num(tr['kappa'], nan=0.0, posinf=1e30).max(1)
+            ok &= kap < KAPPA0
+            bad = np.abs(obs - g['obs1']) > obs_tol32(kind, g['obs1']) * 2
+            assert bad[ok].sum() == 0, (np.argwhere(bad & ok[:, None])[:5], relerr(obs[ok], g['obs1'][ok]))
+            for k in ['alt', 'tas', 'vs', 'asas_vs', 'asas_alt']:
+                assert relerr(ac1[ok][:, F[k]], g['ac1'][ok][:, F[k]], floor=10.0) < 5 * RT32, k
+            assert (reso1[ok] == g['reso1'][ok]).all()
+        # the vertical term acted in the compared steps
+        act_v = (ac1[ok][:, F['asas_active']] > 0) & (np.abs(ac1[ok][:, F['asas_vs']] - ac1[ok][:, F['vs']]) > 0.5)
+        assert act_v.sum() > 5
+        core.close()
+
+
 @pytest.mark.parametrize('kind,N,asas,E,mvp', [(0, 20, 1, 512, 1), (2, 50, 1, 512, 1), (1, 6, 0, 512, 0), (0, 20, 1, 4096, 0)])
 def test_batched_step_vs_oracle(orc, kind, N, asas, E, mvp):
     """Seeded synthetic batch (BASELINE configs' shapes; the last case is configs[1] at its FULL size, 4096 envs x 20

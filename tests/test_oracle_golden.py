@@ -15,24 +15,41 @@ TOL = 1e-11
 def golden_cfg(orc, name, g):
     """Oracle config of a golden file: env kind from the first letter, ASAS+MVP / wind from the tags."""
     kind = name[0]
-    asas = int('asas' in name)
+    asas = int('asas' in name or 'mvp' in name)
+    mode = 2 if 'mvphv' in name else (1 if 'mvpv' in name else 0)     # MVP resolution method (RMETHH / RMETHV)
     wind = tuple(g['wind'].T) if 'wind' in g else None
     return orc.make_cfg(KIND[kind], g['ac0'].shape[2], asas_on=asas, reso_on=asas, reso_off_own=asas,
-                        wind=wind, wind_obs=int(wind is not None))
+                        wind=wind, wind_obs=int(wind is not None), reso_mode=mode)
 
 
 def rel(a, b):
     return float(np.max(np.abs(a - b) / np.maximum(np.abs(b), 1.0))) if a.size else 0.0
 
 
-GOLDEN = ['H', 'V', 'S', 'H_asas', 'S_asas', 'M', 'M_wind', 'S_wind', 'V_wind', 'H_wind', 'S_asas_wind']
+def vertical_degenerate_steps(orc, cfg, g, na, name, eps=1e-9):
+    """MVP with the vertical term (RMETHV / combined): `abs(vrel_z) > 0.0` is an EXACT-zero switch.  Two aircraft that
+    resolve against each other symmetrically hold vertical speeds that agree to the last bit -- or differ by one ulp --
+    depending on how tLOS(i,j) and tLOS(j,i) round (numpy's SIMD sin/cos vs libm vs CUDA), and the resolution flips
+    sign on that bit.  Steps in which the oracle's trace puts a resolving aircraft within eps of such a switch are
+    ENUMERATED and left out of the exact comparison; returns the mask of the steps that are compared."""
+    nac = g['nac'].astype(np.int32)
+    tr = orc.step_trace(cfg, g['ac0'].copy(), g['reso0'].copy(), nac, g['ev0'].copy(),
+                        np.ascontiguousarray(g['act'][:, :na]), eps, nthreads=2)[5]
+    deg = (tr['res_margin'] < eps).any(1)
+    print(f"[{name}] steps at an exact-zero switch of the vertical term: {np.where(deg)[0].tolist()} ({int(deg.sum())} of {len(deg)})")
+    assert deg.mean() < 0.6, deg.mean()      # (Sector: level, co-altitude traffic -- every conflict starts symmetric)
+    return ~deg
+
+
+GOLDEN = ['H', 'V', 'S', 'H_asas', 'S_asas', 'M', 'M_wind', 'S_wind', 'V_wind', 'H_wind', 'S_asas_wind',
+          'V_mvpv', 'V_mvphv', 'H_mvphv', 'S_mvpv']
 
 
 @pytest.mark.parametrize('name', GOLDEN)
 def test_c_oracle_replays_reference_steps(orc, name):
     g = load_golden(name)
     kind = name[0]
-    asas = int('asas' in name)
+    asas = int('asas' in name or 'mvp' in name)
     n = g['ac0'].shape[2]
     cfg = golden_cfg(orc, name, g)
     nac = g['nac'].astype(np.int32)
@@ -46,6 +63,11 @@ def test_c_oracle_replays_reference_steps(orc, name):
     ac, reso, ev = g['ac0'].copy(), g['reso0'].copy(), g['ev0'].copy()
     obs, rew, term, trunc, cd = orc.step(cfg, ac, reso, nac, ev, np.ascontiguousarray(g['act'][:, :na]), nthreads=2)
     ref_obs = g['obs1'].copy()
+    sel = np.ones(len(nac), bool)
+    if 'mvp' in name:
+        sel = vertical_degenerate_steps(orc, cfg, g, na, name)
+        obs, ref_obs, rew, term, trunc, ac, reso, ev = (x[sel] for x in (obs, ref_obs, rew, term, trunc, ac, reso, ev))
+        g = {k: (v[sel] if getattr(v, 'shape', ()) and v.shape[0] == len(sel) else v) for k, v in g.items()}
     if 'wind' in name:   # on termination the reference deletes aircraft before the wrapper looks up 'kl001'
         t = g['term'] == 1   # (id2idx -> -1 -> the LAST remaining aircraft): wind slots of that row are not KL001's
         ref_obs[t, -2:] = obs[t, -2:]
@@ -82,6 +104,11 @@ def test_c_oracle_replays_reference_steps(orc, name):
         assert g['trunc'].sum() >= 1
     if asas:
         assert (g['ac1'][:, orc.F['asas_active']].sum(1) > 0).sum() > 10
+    if 'mvp' in name:   # the vertical term must act: resolving aircraft are commanded off their vertical speed / altitude
+        act = (g['ac1'][:, orc.F['asas_active']] > 0) & live[:, None]
+        dvs = np.abs(g['ac1'][:, orc.F['asas_vs']] - g['ac1'][:, orc.F['vs']])[act]
+        dal = np.abs(g['ac1'][:, orc.F['asas_alt']] - g['ac1'][:, orc.F['selalt']])[act]
+        assert (dvs > 0.5).sum() > 5 and (dal > 50.0).sum() > 5, ((dvs > 0.5).sum(), (dal > 50.0).sum())
 
 
 def test_functions_kat():
