@@ -6,7 +6,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.environ.get('BSG_LIB_PATH') or os.path.join(_HERE, 'libbsgcore.so')   # override: A/B of kernel variants (tools/ab.sh)
 
-ABI_VERSION = 3
+ABI_VERSION = 4
 KIND_HORIZONTAL, KIND_VERTICAL, KIND_SECTOR, KIND_RAW, KIND_MERGE = 0, 1, 2, 3, 4
 MAX_WIND = 8
 FP32, FP64 = 0, 1

@@ -144,6 +144,8 @@ class BsgCore:
             assert ac.shape == (self.E, L.NF, self.N), ac.shape
         if ev is not None:
             assert ev.shape == (self.E, L.NE), ev.shape
+        if reso is not None:
+            assert reso.size == ((self.N + 63) // 64) * self.E * self.N, reso.shape      # [E, N] or [W, E, N] (N > 64)
         torch.cuda.synchronize(self.device)
         L.check(self.lib.bsg_set_state(self.h, _ptr(ac), _ptr(reso), _ptr(nac), _ptr(ev)), self.h)
 
@@ -154,7 +156,9 @@ class BsgCore:
         return nac
 
     def get_state(self):
-        ac = np.zeros((self.E, L.NF, self.N)); reso = np.zeros((self.E, self.N), np.uint64)
+        # resopairs rows: [E, N] uint64 for N <= 64; beyond, W = ceil(N / 64) words per aircraft, word-major [W, E, N]
+        W = (self.N + 63) // 64
+        ac = np.zeros((self.E, L.NF, self.N)); reso = np.zeros((self.E, self.N) if W == 1 else (W, self.E, self.N), np.uint64)
         nac = np.zeros(self.E, np.int32); ev = np.zeros((self.E, L.NE))
         torch.cuda.synchronize(self.device)
         L.check(self.lib.bsg_get_state(self.h, _ptr(ac), _ptr(reso), _ptr(nac), _ptr(ev)), self.h)

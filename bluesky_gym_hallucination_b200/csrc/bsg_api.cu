@@ -120,7 +120,7 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     if (c->env_kind < 0 || c->env_kind > BSG_KIND_MERGE || c->num_envs < 1 || c->max_ac < 1) return BSG_ERR_ARG;
     if (c->env_kind == BSG_KIND_MERGE && (c->max_ac < 2 || c->max_ac > 64)) return BSG_ERR_UNSUPPORTED;   // EXT kernels: N <= 64
     if (c->max_ac > 256) return BSG_ERR_UNSUPPORTED;          // fused step: one env's rows live in one CTA
-    if (c->reso_on && (c->max_ac > 64 || !c->asas_on)) return BSG_ERR_UNSUPPORTED;
+    if (c->reso_on && !c->asas_on) return BSG_ERR_UNSUPPORTED;
     if (c->reso_mode < 0 || c->reso_mode > 2 || (c->reso_mode != 0 && !c->reso_on)) return BSG_ERR_ARG;
     if (c->reso_mode != 0 && c->env_kind == BSG_KIND_MERGE && c->precision != BSG_FP64) return BSG_ERR_UNSUPPORTED;   // fp32 EXT kernels: symmetric sweep only
     int ndev = 0;
@@ -205,13 +205,14 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     const size_t EN = (size_t)E * N;
     CK(h, cudaMalloc(&h->pos, 2 * EN * sizeof(double)));
     CK(h, cudaMalloc(&h->st, (size_t)S_NS * EN * rs));
-    CK(h, cudaMalloc(&h->reso, EN * sizeof(unsigned long long)));
+    const size_t RW = (size_t)(N + 63) / 64;          // resopairs words per aircraft, word-major: reso[RW][E*N]
+    CK(h, cudaMalloc(&h->reso, RW * EN * sizeof(unsigned long long)));
     CK(h, cudaMalloc(&h->nac, E * sizeof(int)));
     CK(h, cudaMalloc(&h->ev, (size_t)E * BSG_NE * sizeof(double)));
     CK(h, cudaMalloc(&h->stage64, (size_t)E * BSG_NF * N * sizeof(double)));
     CK(h, cudaMemset(h->pos, 0, 2 * EN * sizeof(double)));
     CK(h, cudaMemset(h->st, 0, (size_t)S_NS * EN * rs));
-    CK(h, cudaMemset(h->reso, 0, EN * sizeof(unsigned long long)));
+    CK(h, cudaMemset(h->reso, 0, RW * EN * sizeof(unsigned long long)));
     CK(h, cudaMemset(h->nac, 0, E * sizeof(int)));
     CK(h, cudaMemset(h->ev, 0, (size_t)E * BSG_NE * sizeof(double)));
     // host-buffer step: [obs | reward | info | terminated | truncated] in one pinned block

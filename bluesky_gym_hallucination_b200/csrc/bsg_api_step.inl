@@ -106,7 +106,7 @@ int bsg_set_state(bsg_handle *h, const double *ac, const uint64_t *reso, const i
                         if (j != i) sym[e * N + j] |= 1ull << i;
                     }
             CK(h, cudaMemcpy(h->reso, sym.data(), EN * sizeof(uint64_t), cudaMemcpyHostToDevice));
-        } else CK(h, cudaMemcpy(h->reso, reso, EN * sizeof(uint64_t), cudaMemcpyHostToDevice));
+        } else CK(h, cudaMemcpy(h->reso, reso, (size_t)((g.max_ac + 63) / 64) * EN * sizeof(uint64_t), cudaMemcpyHostToDevice));
     }
     if (nac) CK(h, cudaMemcpy(h->nac, nac, g.num_envs * sizeof(int32_t), cudaMemcpyHostToDevice));
     if (ev) CK(h, cudaMemcpy(h->ev, ev, (size_t)g.num_envs * BSG_NE * sizeof(double), cudaMemcpyHostToDevice));
@@ -130,7 +130,7 @@ int bsg_get_state(bsg_handle *h, double *ac, uint64_t *reso, int32_t *nac, doubl
         CK(h, cudaGetLastError());
         CK(h, cudaMemcpy(ac, h->stage64, (size_t)g.num_envs * BSG_NF * g.max_ac * sizeof(double), cudaMemcpyDeviceToHost));
     }
-    if (reso) CK(h, cudaMemcpy(reso, h->reso, EN * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+    if (reso) CK(h, cudaMemcpy(reso, h->reso, (size_t)((g.max_ac + 63) / 64) * EN * sizeof(uint64_t), cudaMemcpyDeviceToHost));
     if (nac) CK(h, cudaMemcpy(nac, h->nac, g.num_envs * sizeof(int32_t), cudaMemcpyDeviceToHost));
     if (ev) CK(h, cudaMemcpy(ev, h->ev, (size_t)g.num_envs * BSG_NE * sizeof(double), cudaMemcpyDeviceToHost));
     return BSG_OK;

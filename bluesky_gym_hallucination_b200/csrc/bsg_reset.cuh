@@ -204,7 +204,7 @@ static __device__ __noinline__ void reset_aircraft(int kind, int E, int N, int e
     const ResetEnv S = *Sp;
     const size_t EN = (size_t)E * N, k = (size_t)e * N + i;
     const double ccl = RC.ccl;
-    reso[k] = 0ull;
+    for (int w = 0; w < (N + 63) / 64; w++) reso[(size_t)w * EN + k] = 0ull;       // resopairs row, all its words
     AcInit a = {};
     a.lnav = -1;
     Philox g(seed, (uint32_t)e, ep, 1u + (uint32_t)i);

@@ -626,8 +626,16 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
 
             if (live && !skip) {
                 const Rec me = rb[i];
+                // resopairs rows: one 64-bit word per 64 partners.  N <= 64: the word lives in a register for the whole
+                // launch; beyond, word w of aircraft k sits at reso[w * E * N + k] and is read / rewritten chunk by chunk
+                // (only the owner thread touches its row)
+                const bool multi = N > 64;
+                for (int j0 = 0; j0 < nl; j0 += 64) {
+                const int j1 = j0 + 64 < nl ? j0 + 64 : nl;
+                unsigned long long rw = resorow, kw = 0ull;
+                if (RESO && multi) rw = A.reso[(size_t)(j0 >> 6) * EN + k];
 #pragma unroll 4
-                for (int j = 0; j < nl; j++) {
+                for (int j = j0; j < j1; j++) {
                     const Rec o = rb[j];
                     PairOut<R> po;
                     const bool off = (j != i);
@@ -645,7 +653,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                         }
                     }
                     if constexpr (RESO) {
-                        const bool inres = off && (po.sw || ((resorow >> j) & 1ull));
+                        const bool inres = off && (po.sw || ((rw >> (j - j0)) & 1ull));
                         if (inres) {
                             R vrx = o.u - me.u, vry = o.v - me.v;
                             if (po.sw) {
@@ -673,9 +681,11 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                             const R hdist = sqrt(ddx * ddx + ddy * ddy);
                             const bool bouncing = fabs(a.hdg - sdist[le * N + j]) < R(30) && hdist < rpz * fach;
                             touched = true;
-                            if (!past || hdist < rpz || bouncing) { active = true; keep |= 1ull << j; }
+                            if (!past || hdist < rpz || bouncing) { active = true; kw |= 1ull << (j - j0); }
                         }
                     }
+                }
+                if (RESO && multi) A.reso[(size_t)(j0 >> 6) * EN + k] = kw; else keep = kw;
                 }
             }
             }
@@ -725,7 +735,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
     BSG_STAMP(2);
     if (live && !skip) {
         ac_store<R, RESO, EXT>(a, A.pos, A.st, EN, k);
-        if (reso) A.reso[k] = resorow;
+        if (reso && N <= 64) A.reso[k] = resorow;          // (N > 64: the row's words were rewritten in place, chunk by chunk)
     }
     if (valid && i < N) {      // CD row outputs of the last detection (dead slots: zeros / -1)
         const bsg_step_out &o = A.out;

@@ -33,7 +33,7 @@
 extern "C" {
 #endif
 
-#define BSG_ABI_VERSION 3
+#define BSG_ABI_VERSION 4
 
 typedef enum { BSG_OK = 0, BSG_ERR_ARG = -1, BSG_ERR_CUDA = -2, BSG_ERR_NOMEM = -3, BSG_ERR_UNSUPPORTED = -4,
                BSG_ERR_NODEVICE = -5 } bsg_status;
@@ -65,7 +65,7 @@ typedef struct bsg_config {
     int32_t precision;        /* BSG_FP32 | BSG_FP64 */
     int32_t substeps;         /* ACTION_FREQUENCY; 0 = the reference's value for env_kind (10/30/5) */
     int32_t asas_on;          /* state-based CD every substep (BlueSky "ASAS ON") */
-    int32_t reso_on;          /* MVP resolution + resumenav (BlueSky "RESO MVP"); needs asas_on, N <= 64 */
+    int32_t reso_on;          /* MVP resolution + resumenav (BlueSky "RESO MVP"); needs asas_on */
     int32_t reso_off_own;     /* agent does not resolve (BlueSky "RESOOFF KL001") */
     int32_t max_episode_steps;/* TimeLimit: truncate when reached; 0 = never */
     int32_t device;           /* CUDA device ordinal */
@@ -139,7 +139,9 @@ int bsg_set_wind(bsg_handle *h, int32_t npoints, const double *lat_host, const d
  * sigma = 0 switches it off. */
 int bsg_set_obs_noise(bsg_handle *h, double sigma, uint64_t seed);
 
-/* fp64 interchange with the host (parity tests, checkpoint/resume). NULL pointers are skipped. Synchronous. */
+/* fp64 interchange with the host (parity tests, checkpoint/resume). NULL pointers are skipped. Synchronous.
+ * reso_host: resopairs bit rows (bit j of aircraft i's row = pair (i, j) is being resolved), uint64 [E][N] for N <= 64;
+ * for N > 64, W = ceil(N / 64) words per aircraft, word-major [W][E][N] (bit j: word j >> 6, bit j & 63). */
 int bsg_set_state(bsg_handle *h, const double *ac_host, const uint64_t *reso_host, const int32_t *nac_host,
                   const double *ev_host);
 int bsg_get_state(bsg_handle *h, double *ac_host, uint64_t *reso_host, int32_t *nac_host, double *ev_host);

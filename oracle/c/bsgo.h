@@ -11,7 +11,8 @@
  *
  * Data model (shared with the CUDA core's set/get-state interface):
  *   ac   : double [E][BSGO_NF][N]   per-aircraft fields, field-major inside an env
- *   reso : uint64 [E][N]            resopairs bit rows (bit j of row i = pair (i,j) kept), N <= 64
+ *   reso : uint64 [W][E][N]         resopairs bit rows, W = ceil(N/64) words per aircraft, word-major (bit j of row i =
+ *                                   pair (i,j) kept: word j >> 6, bit j & 63); N <= 64: plain [E][N]; N <= 256
  *   nac  : int32  [E]               live aircraft per env (<= N); aircraft 0 is the agent
  *   ev   : double [E][BSGO_NE]      env-level slots
  */

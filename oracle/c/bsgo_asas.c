@@ -79,12 +79,14 @@ static void mvp_pair(double qdr, double dist, double tcpa, double tLOS,
     *tsolV_o = tsolV;
 }
 
-void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bsgo_row *rows) {
-    bsgo_asas_env_trace(cfg, a, reso, nlive, rows, 0);
+void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, size_t wstride, int nlive, bsgo_row *rows) {
+    bsgo_asas_env_trace(cfg, a, reso, wstride, nlive, rows, 0);
 }
 
-void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bsgo_row *rows, bsgo_trace *tr) {
+/* resopairs rows: bit j of aircraft i = word (j >> 6) of its row, words `wstride` apart (reso[W][E][N], W = ceil(N/64)) */
+void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, size_t wstride, int nlive, bsgo_row *rows, bsgo_trace *tr) {
     int n = cfg->n;
+    const int W = (n + 63) / 64;
     if (tr) {
         if (tr->near_conf) memset(tr->near_conf, 0, n);
         if (tr->near_los) memset(tr->near_los, 0, n);
@@ -92,7 +94,7 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
 #define A(f, i) a[(f) * n + (i)]
     double *u = malloc(sizeof(double) * nlive * 6);
     double *v = u + nlive, *dve = v + nlive, *dvn = dve + nlive, *dvz = dvn + nlive, *tsolmin = dvz + nlive;
-    uint64_t *confrow = calloc(nlive, sizeof(uint64_t));
+    uint64_t *confrow = calloc((size_t)(nlive > 0 ? nlive : 1) * W, sizeof(uint64_t));      /* [nlive][W] */
     int anyconf = 0;
     const int wind = cfg->nwind > 0;
     for (int i = 0; i < nlive; i++) {
@@ -128,7 +130,7 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
             if (r->near_idx < 0 || tcpa < r->near_tcpa) {
                 r->near_idx = j; r->near_tcpa = tcpa; r->near_dcpa = sqrt(dcpa2); r->near_tin = tin;
             }
-            if (n <= 64) confrow[i] |= (uint64_t)1 << j;
+            confrow[(size_t)i * W + (j >> 6)] |= (uint64_t)1 << (j & 63);
             if (cfg->reso_on) {
                 double v2[3] = { u[j], v[j], A(F_VS, j) };
                 double dv[3], tsolV;
@@ -186,12 +188,12 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
             }
         }
         /* resumenav: resopairs |= confpairs; keep a pair while not past CPA, or in horizontal LoS, or bouncing */
-        for (int i = 0; i < nlive && n <= 64; i++) {
-            uint64_t row = reso[i] | confrow[i];
-            uint64_t keep = 0;
+        for (int i = 0; i < nlive; i++) {
+            uint64_t keep[4] = { 0, 0, 0, 0 };                        /* n <= 256 */
             int touched = 0, active = 0;
             for (int j = 0; j < nlive; j++) {
-                if (!((row >> j) & 1)) continue;
+                const uint64_t row = reso[(size_t)(j >> 6) * wstride + i] | confrow[(size_t)i * W + (j >> 6)];
+                if (!((row >> (j & 63)) & 1)) continue;
                 touched = 1;
                 double dx = C_RE * ((A(F_LON, j) - A(F_LON, i)) * C_D2R * cos(0.5 * ((A(F_LAT, j) + A(F_LAT, i)) * C_D2R)));
                 double dy = C_RE * ((A(F_LAT, j) - A(F_LAT, i)) * C_D2R);
@@ -211,10 +213,10 @@ void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nli
                     }
                     if (tr->res_margin && m < tr->res_margin[i]) tr->res_margin[i] = m;
                 }
-                if (!past_cpa || hor_los || bouncing) { active = 1; keep |= (uint64_t)1 << j; }
+                if (!past_cpa || hor_los || bouncing) { active = 1; keep[j >> 6] |= (uint64_t)1 << (j & 63); }
             }
             if (touched) A(F_ASAS_ACTIVE, i) = active ? 1.0 : 0.0;
-            reso[i] = keep;
+            for (int w = 0; w < W; w++) reso[(size_t)w * wstride + i] = keep[w];
         }
     }
     free(u);

@@ -336,7 +336,7 @@ void bsgo_step_trace(const bsgo_cfg *cfg, int E, double *ac, uint64_t *reso, con
                            res_margin ? res_margin + (size_t)e * n : 0, kappa ? kappa + (size_t)e * n : 0, 0 };
         for (int i = 0; i < n; i++) { if (trc.res_margin) trc.res_margin[i] = 1e30; if (trc.kappa) trc.kappa[i] = 0.0; }
         for (int s = 0; s < cfg->substeps; s++) {
-            if (cfg->asas_on) bsgo_asas_env_trace(cfg, a, rs, nl, rows, want_tr ? &trc : 0);
+            if (cfg->asas_on) bsgo_asas_env_trace(cfg, a, rs, (size_t)E * n, nl, rows, want_tr ? &trc : 0);
             for (int i = 0; i < nl; i++) bsgo_kin_substep(cfg, a, v, n, i, cfg->simdt, cfg->reso_on && cfg->asas_on);
         }
         double rew = 0;

@@ -38,7 +38,7 @@ void bsgo_kin_substep(const bsgo_cfg *cfg, double *a, const double *ev, int n, i
 typedef struct {
     uint8_t inconf; int32_t nconf, nlos, near_idx; double near_tcpa, near_dcpa, near_tin, tcpamax;
 } bsgo_row;
-void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bsgo_row *rows);
+void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, size_t wstride, int nlive, bsgo_row *rows);
 /* Trace of one env over the substeps of a step (parity tests: what an fp32 path may legitimately decide differently).
  * near_conf / near_los [n]: rows holding a pair within eps of a conflict / LoS threshold at the LAST detection;
  * res_margin [n]: per ownship row, the smallest relative margin, over all substeps and partners, of the decisions that
@@ -50,7 +50,7 @@ void bsgo_asas_env(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bs
  *   and conflict pairs [m/s]: (dist + |v_rel||tCPA|) rpz_m / (|tCPA| |dCPA_h|), or with dist in place of |dCPA_h| in
  *   the perpendicular-escape branch (|dCPA_h| <= 10 m), whose direction comes from the relative position alone. */
 typedef struct { double eps; uint8_t *near_conf, *near_los; double *res_margin, *kappa; int row; double rabs; } bsgo_trace;
-void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, int nlive, bsgo_row *rows, bsgo_trace *tr);
+void bsgo_asas_env_trace(const bsgo_cfg *cfg, double *a, uint64_t *reso, size_t wstride, int nlive, bsgo_row *rows, bsgo_trace *tr);
 void bsgo_pair(double lati, double loni, double alti, double ui, double vi, double vsi,
                double latj, double lonj, double altj, double uj, double vj, double vsj,
                double rpz, double hpz, double dtlook,

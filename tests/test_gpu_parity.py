@@ -47,7 +47,8 @@ def obs_tol32(kind, ref):
 def make_core(kind, E, N, precision, asas=0, **kw):
     from bluesky_gym_hallucination_b200.core import BsgCore
     reso = kw.pop('reso', True)
-    return BsgCore(kind, E, N, precision=precision, asas_on=bool(asas), reso_on=bool(asas) and N <= 64 and reso,
+    big = kw.pop('reso_big', False)          # MVP with more than 64 aircraft per env (multi-word resopairs rows)
+    return BsgCore(kind, E, N, precision=precision, asas_on=bool(asas), reso_on=bool(asas) and (N <= 64 or big) and reso,
                    reso_off_own=bool(asas), cd_outputs=True, **kw)
 
 
@@ -174,6 +175,61 @@ def test_mvp_vertical_methods_replay_reference_goldens(orc, name):
         act_v = (ac1[ok][:, F['asas_active']] > 0) & (np.abs(ac1[ok][:, F['asas_vs']] - ac1[ok][:, F['vs']]) > 0.5)
         assert act_v.sum() > 5
         core.close()
+
+
+def test_mvp_beyond_64_aircraft(orc):
+    """MVP + resumenav with more than 64 aircraft per env: the resopairs row of an aircraft is W = ceil(N / 64) words
+    (word-major interchange layout [W, E, N]).  Sector traffic, 100 aircraft, every slot live: three chained steps in fp64
+    against the oracle (exact flags / rows, floats as in test_batched_step_vs_oracle), one fp32 step from the oracle's
+    pre-state (ordered-sweep kernel) with every CD row mismatch at a near-threshold row."""
+    from bluesky_gym_hallucination_b200 import scenario as sc
+    E, N, W = 48, 100, 2
+    ac, _, nac, ev = sc.sector(E, N, seed=21)
+    nac[:] = N                                                   # every slot live (scenario draws a full batch of slots)
+    assert np.isfinite(ac[:, orc.F['lat']]).all()
+    reso = np.zeros((W, E, N), np.uint64)
+    cfg = orc.make_cfg(2, N, asas_on=1, reso_on=1, reso_off_own=1)
+    c64 = make_core(2, E, N, 'fp64', 1, reso=True, reso_big=True)
+    c32 = make_core(2, E, N, 'fp32', 1, reso=True, reso_big=True)
+    rng = np.random.default_rng(5)
+    o_ac, o_reso, o_ev = ac.copy(), reso.copy(), ev.copy()
+    c64.set_state(ac, reso, nac, ev)
+    hi_pairs = 0
+    for s in range(3):
+        act = rng.uniform(-1, 1, (E, 2))
+        pre = (o_ac.copy(), o_reso.copy(), o_ev.copy())
+        o_obs, o_rew, o_term, o_trunc, o_cd, tr = orc.step_trace(cfg, o_ac, o_reso, nac, o_ev, act, EPS32, nthreads=8)
+        c64.step(torch.as_tensor(act, dtype=torch.float64, device=c64.device))
+        torch.cuda.synchronize()
+        g_ac, g_reso, _, _ = c64.get_state()
+        assert g_reso.shape == (W, E, N)
+        assert np.array_equal(g_reso, o_reso), np.argwhere(g_reso != o_reso)[:5]
+        assert np.array_equal(g_ac[:, orc.F['asas_active']], o_ac[:, orc.F['asas_active']])
+        assert np.array_equal(c64.cd['nconf'].cpu().numpy(), o_cd['nconf'])
+        assert np.array_equal(c64.cd['nlos'].cpu().numpy(), o_cd['nlos'])
+        assert np.array_equal(c64.cd['near_idx'].cpu().numpy(), o_cd['near_idx'])
+        assert relerr(c64.obs.cpu().numpy(), o_obs) < 1e-7
+        assert np.array_equal(c64.terminated.cpu().numpy(), o_term)
+        hi_pairs += int(np.count_nonzero(o_reso[1])) + int(np.count_nonzero(o_reso[0][:, 64:]))
+        # fp32, one step from the oracle's pre-state
+        obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(c32, pre[0], pre[1], nac, pre[2], act)
+        near_c, near_l = tr['near_conf'], tr['near_los']
+        bad_c = (cd['nconf'] != o_cd['nconf']) & ~near_c
+        bad_l = (cd['nlos'] != o_cd['nlos']) & ~near_l & ~near_c
+        # envs whose resolution state flipped at a threshold / ill-conditioned pair follow different commands
+        kap = np.nan_to_num(tr['kappa'], nan=0.0, posinf=1e30)
+        env_near = ((tr['res_margin'] < EPS32) | (kap >= KAPPA0)).any(1)
+        flipped = (reso1 != o_reso).any(axis=(0, 2)) | (ac1[:, orc.F['asas_active']] != o_ac[:, orc.F['asas_active']]).any(1)
+        assert not (flipped & ~env_near).any(), np.where(flipped & ~env_near)[0]
+        assert not (bad_c & ~flipped[:, None]).any() and not (bad_l & ~flipped[:, None]).any()
+        ok = ~flipped & ~(np.abs(rew - o_rew) > 0.5)
+        rb = (np.abs(obs - o_obs) / obs_tol32(2, o_obs))[ok]
+        q50, q99 = np.quantile(rb, [0.5, 0.99])
+        print(f"[N=100 step {s}] fp32: envs with a resolution-state flip {int(flipped.sum())} of {E} (all at a threshold), "
+              f"err / (1e-5 bound): median {q50:.3f}, 99 % {q99:.3f}, max {float(rb.max()):.1f}; resopairs bits beyond aircraft 63 so far: {hi_pairs}")
+        assert q50 <= 1.0 and q99 <= 1.0 and rb.max() <= 100.0
+    assert hi_pairs > 50          # the second word of the rows was in use
+    c64.close(); c32.close()
 
 
 @pytest.mark.parametrize('kind,N,asas,E,mvp', [(0, 20, 1, 512, 1), (2, 50, 1, 512, 1), (1, 6, 0, 512, 0), (0, 20, 1, 4096, 0)])

@@ -16,7 +16,7 @@ def test_library_exports_every_declared_symbol():
     assert len(declared) >= 20
     assert declared == set(_lib.SYMBOLS), declared ^ set(_lib.SYMBOLS)
     lib = _lib.load()                       # binds all of them; raises on a missing symbol
-    assert lib.bsg_abi_version() == _lib.ABI_VERSION == 3
+    assert lib.bsg_abi_version() == _lib.ABI_VERSION == 4
     assert lib.bsg_status_string(-4).decode() == 'unsupported configuration'
 
 
