@@ -309,6 +309,19 @@ def run_envs(ctx, workload, K, W, strong=False, envs=0, cpu=False):
         sink += float(rew_v[0])
     t_e2e = time.perf_counter() - t0
     e2e_value = world * E * Ke / ctx.max_over_ranks(t_e2e)
+    # the same loop with TWO steps in flight (bsg_step_host_begin / _wait: SB3's step_async / step_wait over two pinned
+    # blocks): the D2H of step k overlaps the launch of step k + 1.  A reported extra, not the headline: a policy that needs
+    # obs k before it can choose action k + 1 runs the synchronous loop above (or two env batches in this one).
+    ctx.barrier()
+    t0 = time.perf_counter()
+    c.step_host_begin(a_host[0])
+    for k in range(1, Ke + 1):
+        if k < Ke:
+            c.step_host_begin(a_host[k % 16])
+        obs_v, rew_v, term_v, trunc_v, info_v = c.step_host_wait()
+        sink += float(rew_v[0])
+    t_pipe = time.perf_counter() - t0
+    e2e_pipe = world * E * Ke / ctx.max_over_ranks(t_pipe)
     clocks = sampler.stop() if rank == 0 else None          # sampled across warm-up, the device-timed and the e2e regions
     nac = c.live_aircraft().astype(np.float64)                  # counted from the device state, not assumed
     assert nac.min() == N and nac.max() == N, (nac.min(), nac.max())
@@ -339,7 +352,9 @@ def run_envs(ctx, workload, K, W, strong=False, envs=0, cpu=False):
                      "hbm_peak_gbs": load_peaks().get("hbm_gbs")},
         "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(act_dim * E * 4),
                 "d2h_bytes_per_step": int(E * (obs_dim + 5) * 4 + E * 8), "steps": Ke,
-                "api": "bsg_step_host + bsg_host_views (host actions -> pinned H2D, one launch, D2H of obs/reward/info/flags into pinned host memory read in place)"},
+                "api": "bsg_step_host + bsg_host_views (host actions -> pinned H2D, one launch, D2H of obs/reward/info/flags into pinned host memory read in place)",
+                "two_steps_in_flight": {"value": e2e_pipe, "unit": "env-steps/s",
+                                        "api": "bsg_step_host_begin / bsg_step_host_wait, same copies per step; reported extra (the headline e2e is the synchronous loop)"}},
         "gpu_launches": int(launches), "clocks": clocks, "wall_s_timed_region": t_wall,
         "traffic_state": {"live_aircraft_per_env": {"min": int(nac.min()), "mean": float(nac.mean()), "max": int(nac.max())},
                           "fresh_episode_env_share": fresh_frac},
@@ -550,10 +565,16 @@ def main():
             c3 = run_envs(ctx, 'c3', min(K, 200), W, strong=True)
             c5 = run_giant(ctx, min(K, 100), W, args.c5_mode)
             v = run_envs(ctx, 'v', min(K, 500), W) if ctx.world == 1 else None
+            # the same kernel on a launch four times C2's size: what the 4096-env batch leaves on the table is the fixed
+            # latency of one launch (about 22 us: launch, cold prologue, the two integration chains, epilogue), not the sweep
+            big = run_envs(ctx, 'c2', min(K, 200), W, envs=16384) if ctx.world == 1 else None
             if ctx.rank == 0:
                 line["c3"] = compact(c3); line["c5"] = compact(c5)
                 if v is not None:
                     line["v"] = compact(v)
+                if big is not None:
+                    line["c2_16384_envs"] = compact(big)
+                    line["roofline"]["frac_at_16384_envs"] = big["roofline"]["frac"]
                 if ctx.world == 1 and not args.no_cpu:
                     line["c1"], line["numpy_detect"] = cpu_table()
     if ctx.rank == 0 and line is not None:

@@ -74,6 +74,7 @@ SYMBOLS = {
     'bsg_act_dim': (_I, [_VP]),
     'bsg_launch_count': (_I, [_VP, _I64P]),
     'bsg_set_wind': (_I, [_VP, C.c_int32, _VP, _VP, _VP, _VP, C.c_int32]),
+    'bsg_set_wind_profile': (_I, [_VP, C.c_double, C.c_double, C.c_int32, _VP, _VP, _VP, C.c_int32]),
     'bsg_set_obs_noise': (_I, [_VP, C.c_double, C.c_uint64]),
     'bsg_set_state': (_I, [_VP, _VP, _VP, _VP, _VP]),
     'bsg_get_state': (_I, [_VP, _VP, _VP, _VP, _VP]),

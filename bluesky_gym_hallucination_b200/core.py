@@ -105,9 +105,18 @@ class BsgCore:
                               _ptr(self.truncated), _ptr(self.info), *cdp, _ptr(self.done))
 
     # ------------------------------------------------------------------ wrapper features (EXT kernels)
-    def set_wind(self, lat=None, lon=None, vnorth=None, veast=None, augment_obs=False):
-        """WindFieldWrapper (bluesky_gym/wrappers/wind.py:9-29): wind vectors [m/s] at points; None switches it off."""
-        if lat is None:
+    def set_wind(self, lat=None, lon=None, vnorth=None, veast=None, alt=None, augment_obs=False):
+        """WindFieldWrapper (bluesky_gym/wrappers/wind.py:9-29): wind vectors [m/s] at points; None switches it off.
+        alt = altitudes [m] of a profile: ONE point (scalar lat, lon) whose vnorth / veast are given at those altitudes."""
+        if lat is not None and alt is not None:
+            al = np.ascontiguousarray(np.atleast_1d(np.asarray(alt, dtype=np.float64)))
+            vn = np.ascontiguousarray(np.broadcast_to(np.atleast_1d(np.asarray(vnorth, dtype=np.float64)), al.shape))
+            ve = np.ascontiguousarray(np.broadcast_to(np.atleast_1d(np.asarray(veast, dtype=np.float64)), al.shape))
+            if np.ndim(lat) != 0 or np.ndim(lon) != 0:
+                raise ValueError("a wind altitude profile belongs to ONE point: scalar lat / lon")
+            L.check(self.lib.bsg_set_wind_profile(self.h, float(lat), float(lon), len(al), _ptr(al), _ptr(vn), _ptr(ve),
+                                                  int(augment_obs)), self.h)
+        elif lat is None:
             L.check(self.lib.bsg_set_wind(self.h, 0, None, None, None, None, 0), self.h)
         else:
             la = np.atleast_1d(np.asarray(lat, dtype=np.float64)).copy()

@@ -249,6 +249,17 @@ int bsg_set_wind(bsg_handle *h, int32_t npoints, const double *lat, const double
     return BSG_OK;
 }
 
+int bsg_set_wind_profile(bsg_handle *h, double lat, double lon, int32_t nknots, const double *alt_m, const double *vnorth,
+                         const double *veast, int32_t augment_obs) {
+    if (!h || nknots < 1 || nknots > BSG_MAX_WIND || !alt_m || !vnorth || !veast) return BSG_ERR_ARG;
+    for (int k = 1; k < nknots; k++) if (!(alt_m[k] > alt_m[k - 1])) return BSG_ERR_ARG;     // np.interp wants increasing knots
+    int rc = bsg_set_wind(h, 1, &lat, &lon, vnorth, veast, augment_obs);                    // one point: ext switch, obs slots
+    if (rc != BSG_OK) return rc;
+    h->wind.nk = nknots;
+    for (int k = 0; k < nknots; k++) { h->wind.kalt[k] = alt_m[k]; h->wind.vn[k] = vnorth[k]; h->wind.ve[k] = veast[k]; }
+    return BSG_OK;
+}
+
 int bsg_set_obs_noise(bsg_handle *h, double sigma, uint64_t seed) {
     if (!h || !(sigma >= 0.0)) return BSG_ERR_ARG;
     if (h->cfg.env_kind == BSG_KIND_RAW) return BSG_ERR_UNSUPPORTED;

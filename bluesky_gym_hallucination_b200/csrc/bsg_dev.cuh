@@ -48,7 +48,8 @@ struct ResetConst {
 };
 
 // wind field (bsg_set_wind): passed by value in the kernel arguments
-struct WindArgs { int n, obs; double lat[BSG_MAX_WIND], lon[BSG_MAX_WIND], vn[BSG_MAX_WIND], ve[BSG_MAX_WIND]; };
+// nk > 0: ONE wind point with an altitude profile of nk knots (kalt, vn, ve): WindFieldWrapper(..., alt=[...])
+struct WindArgs { int n, obs; double lat[BSG_MAX_WIND], lon[BSG_MAX_WIND], vn[BSG_MAX_WIND], ve[BSG_MAX_WIND]; int nk, pad; double kalt[BSG_MAX_WIND]; };
 
 template <typename R> __device__ __forceinline__ R rsgn(R x) { return R((x > R(0)) - (x < R(0))); }
 

@@ -186,7 +186,7 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
     if constexpr (EXT) {
         if (A.W.obs && live && i == 0 && obs) {        // wrappers/wind.py:55-64
             R wn, we, sh, ch;
-            wind_at<R>(A.W, a.lat, a.lon, wn, we);
+            wind_at<R>(A.W, a.lat, a.lon, 0.0, wn, we);          // (the wrapper's scalar altitude: the field at altitude 0)
             rsincos_deg<R>(a.hdg, sh, ch);
             obs[od0] = (wn * ch + we * sh) / R(50);
             obs[od0 + 1] = (-wn * sh + we * ch) / R(50);

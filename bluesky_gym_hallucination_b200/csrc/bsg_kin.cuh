@@ -77,11 +77,36 @@ __device__ __forceinline__ void ac_store(const AcReg<R> &a, double *pos, R *st, 
 }
 
 // ------------------------------------------------------------------ EXT: wind field and LNAV (SURVEY f-3, f-4)
-// Windfield.getdata without altitude profiles: one point = uniform, several = inverse distance-squared weights
+// np.interp of the profile knots at altitude x (constant beyond the ends): both wind components from one interval search
+// (indexed through the WindArgs reference: a pointer into the kernel parameters would copy them to local memory)
+__device__ __forceinline__ void wind_knots(const WindArgs &W, double x, double &vn, double &ve) {
+    const int n = W.nk;
+    if (x <= W.kalt[0]) { vn = W.vn[0]; ve = W.ve[0]; return; }
+    if (x >= W.kalt[n - 1]) { vn = W.vn[n - 1]; ve = W.ve[n - 1]; return; }
+    int k = 0;
+    while (k < n - 2 && x >= W.kalt[k + 1]) k++;
+    const double dx = x - W.kalt[k], w = W.kalt[k + 1] - W.kalt[k];
+    vn = W.vn[k] + dx * ((W.vn[k + 1] - W.vn[k]) / w);
+    ve = W.ve[k] + dx * ((W.ve[k + 1] - W.ve[k]) / w);
+}
+// Windfield.getdata: one point = uniform, several = inverse distance-squared weights; one point with an altitude
+// profile (W.nk knots) = the knots resampled onto BlueSky's 100 ft altitude axis (0 .. 45 000 ft), linear between the
+// two axis levels around `alt` (oracle/refshim/bluesky/traffic/windfield.py).  Callers that BlueSky reaches with a
+// numpy scalar altitude (selhdgcmd, the wrapper's wind observation) pass alt = 0, as upstream reads the field there.
 template <typename R>
-__device__ __forceinline__ void wind_at(const WindArgs &W, double lat, double lon, R &vn, R &ve) {
+__device__ __forceinline__ void wind_at(const WindArgs &W, double lat, double lon, double alt, R &vn, R &ve) {
     vn = R(0); ve = R(0);
     if (W.n <= 0) return;
+    if (W.nk > 0) {
+        const double step = 100.0 * kFt, top = 450.0 * step;
+        const double idx = fmax(0.0, fmin(top - 1e-20, alt)) / step;
+        const double il = floor(idx), f = idx - il, a0 = il * step, a1 = (il + 1.0) * step;
+        double n0, e0, n1, e1;
+        wind_knots(W, a0, n0, e0); wind_knots(W, a1, n1, e1);
+        vn = (R)((1.0 - f) * n0 + f * n1);
+        ve = (R)((1.0 - f) * e0 + f * e1);
+        return;
+    }
     if (W.n == 1) { vn = (R)W.vn[0]; ve = (R)W.ve[0]; return; }
     R w[BSG_MAX_WIND], tot = R(0);
     for (int k = 0; k < W.n; k++) {
@@ -183,7 +208,7 @@ __device__ __forceinline__ void kin_substep_lit(AcReg<double> &a, double dt, boo
     bool wind = false;
     if constexpr (EXT) wind = X->W->n > 0;
     if (wind) {          // APorASAS.update with a wind field: ASAS ground speed -> TAS, wind-correction angle
-        wind_at<double>(*X->W, a.lat, a.lon, vwn, vwe);
+        wind_at<double>(*X->W, a.lat, a.lon, a.alt, vwn, vwe);
         if (act) {
             const double tn = a.asas_tas * cos(a.asas_trk * kD2R) - vwn, te = a.asas_tas * sin(a.asas_trk * kD2R) - vwe;
             t_tas = sqrt(tn * tn + te * te);
@@ -251,7 +276,7 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     bool wind = false;
     if constexpr (EXT) wind = X->W->n > 0;
     if (wind) {
-        wind_at<float>(*X->W, a.lat, a.lon, vwn, vwe);
+        wind_at<float>(*X->W, a.lat, a.lon, (double)a.alt, vwn, vwe);
         float st, ct;
         if (act) {
             sincospif(a.asas_trk * (1.0f / 180.0f), &st, &ct);

@@ -219,7 +219,7 @@ __global__ void __launch_bounds__(TPB, (StepBounds<R, TPB>::kMinBlocks)) step_ke
                 if constexpr (EXT) {
                     if (A.W.n > 0 && a.alt > R(50.0 * kFt)) {
                         R vn, ve, sh, ch;
-                        wind_at<R>(A.W, a.lat, a.lon, vn, ve);
+                        wind_at<R>(A.W, a.lat, a.lon, 0.0, vn, ve);      // (selhdgcmd's scalar altitude: the field at altitude 0)
                         rsincos_deg<R>(hdg, sh, ch);
                         if constexpr (sizeof(R) == 8) return pymod(atan2(a.tas * sh + ve, a.tas * ch + vn) * kR2D, 360.0);
                         else return wrap360(atan2f(fmaf(a.tas, sh, ve), fmaf(a.tas, ch, vn)) * float(kR2D));

@@ -7,7 +7,7 @@
 BlueSkyVecEnv.  Nothing is computed on the host: the wrappers switch the feature on in the core (bsg_set_wind /
 bsg_set_obs_noise), which runs it inside the fused step kernel -- wind in the kinematics and the autopilot, wind_u /
 wind_v appended to the observation, N(0, sigma) added to every observation slot from a Philox stream.
-Altitude profiles (`alt=`) are not part of the core's wind field and raise.
+An altitude profile (`alt=`) makes the point's vectors a function of altitude (bsg_set_wind_profile).
 """
 import numpy as np
 from .core import obs_slices
@@ -48,10 +48,8 @@ class _Wrapper:
 class WindFieldWrapper(_Wrapper):
     def __init__(self, env, lat, lon, vnorth, veast, alt=None, augment_obs=False):
         super().__init__(env)
-        if alt is not None:
-            raise NotImplementedError("wind altitude profiles are not part of the CUDA core's wind field")
         v = self._v
-        v.core.set_wind(lat, lon, vnorth, veast, augment_obs=augment_obs)
+        v.core.set_wind(lat, lon, vnorth, veast, alt=alt, augment_obs=augment_obs)     # alt: one point with a profile
         v.single_observation_space, v.single_action_space = single_spaces(v.kind, v.num_aircraft, v.core.wind_obs)
         v.observation_space = v.single_observation_space
         v._slices = obs_slices(v.kind, v.num_aircraft, v.core.wind_obs)

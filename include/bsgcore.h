@@ -134,6 +134,14 @@ int bsg_launch_count(const bsg_handle *h, int64_t *kernels_launched);
 #define BSG_MAX_WIND 8
 int bsg_set_wind(bsg_handle *h, int32_t npoints, const double *lat_host, const double *lon_host,
                  const double *vnorth_host, const double *veast_host, int32_t augment_obs);
+/* The same wrapper with its alt= argument (wind.py:9,28: addpointvne(lat, lon, vnorth, veast, alt)): ONE wind point with an
+ * altitude profile of nknots <= BSG_MAX_WIND knots (alt_m increasing [m], vnorth / veast [m/s] at the knots).  As in
+ * BlueSky's Windfield the knots are resampled onto a 100 ft altitude axis (0 .. 45 000 ft; constant beyond the profile's
+ * ends) and the field is linear between the two axis levels around an aircraft's altitude; the wrapper's wind
+ * observation and the HDG -> track conversion read the field at altitude 0 (upstream takes the altitude from array
+ * arguments only).  Replaces any wind set before. */
+int bsg_set_wind_profile(bsg_handle *h, double lat, double lon, int32_t nknots, const double *alt_m_host,
+                         const double *vnorth_host, const double *veast_host, int32_t augment_obs);
 /* Gaussian observation noise of the reference's NoisyObservationWrapper (bluesky_gym/wrappers/uncertainty.py:19-32):
  * every observation float gets + N(0, sigma) from a Philox4x32-10 stream keyed by (seed; env, step launch, slot).
  * sigma = 0 switches it off. */

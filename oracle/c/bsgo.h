@@ -48,7 +48,11 @@ typedef struct {
     double wlat[BSGO_MAXWIND], wlon[BSGO_MAXWIND], wvn[BSGO_MAXWIND], wve[BSGO_MAXWIND];
     /* MVP resolution method (stack commands RMETHH / RMETHV): 0 = horizontal, heading + speed (BlueSky's default),
      * 1 = vertical speed only (RMETHV V/S), 2 = horizontal + vertical (RMETHH OFF, RMETHV OFF) */
-    int32_t reso_mode, pad0;
+    int32_t reso_mode;
+    /* altitude profile of the (single) wind point, WindFieldWrapper(..., alt=[...]): nknot > 0 knots (walt, wvn, wve);
+     * resampled onto BlueSky's 100 ft altitude axis and interpolated linearly between axis levels (refshim windfield.py) */
+    int32_t nknot;
+    double walt[BSGO_MAXWIND];
 } bsgo_cfg;
 
 /* per-aircraft CD outputs of the last detection of a step */
@@ -71,7 +75,7 @@ double bsgo_vcasormach2tas(double spd, double h);
 /* geo */
 void bsgo_kwikqdrdist(double lata, double lona, double latb, double lonb, double *qdr, double *dist_nm);
 void bsgo_qdrdist(double lat1, double lon1, double lat2, double lon2, double *qdr, double *dist_nm);   /* WGS-84 great circle */
-void bsgo_wind(const bsgo_cfg *cfg, double lat, double lon, double *vn, double *ve);
+void bsgo_wind(const bsgo_cfg *cfg, double lat, double lon, double alt, double *vn, double *ve);
 
 /* one full CD matrix for one env (dense outputs, row-major n x n); any pointer may be NULL */
 void bsgo_detect_dense(int n, const double *lat, const double *lon, const double *alt,

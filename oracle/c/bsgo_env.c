@@ -31,7 +31,7 @@ static double hdg_cmd(const bsgo_cfg *c, const double *a, double hdg) {
     int n = c->n;
     if (c->nwind > 0 && a[F_ALT * n] > 50.0 * C_FT) {
         double vn, ve;
-        bsgo_wind(c, a[F_LAT * n], a[F_LON * n], &vn, &ve);
+        bsgo_wind(c, a[F_LAT * n], a[F_LON * n], 0.0, &vn, &ve);     /* scalar numpy altitude: the field at altitude 0 (windfield.py) */
         double gn = a[F_TAS * n] * cos(hdg * C_D2R) + vn, ge = a[F_TAS * n] * sin(hdg * C_D2R) + ve;
         return bsgo_pymod(atan2(ge, gn) * C_R2D, 360.0);
     }
@@ -223,7 +223,7 @@ static double observe_env(const bsgo_cfg *c, const double *a, int nlive, double 
     }
     if (c->wind_obs) {                  /* wrappers/wind.py:55-64: wind in the agent's body axes / MAX_WIND */
         double *o = obs + bsgo_obs_dim(c->kind, c->n), wn, we, h = A(F_HDG, 0) * C_D2R;
-        bsgo_wind(c, A(F_LAT, 0), A(F_LON, 0), &wn, &we);
+        bsgo_wind(c, A(F_LAT, 0), A(F_LON, 0), 0.0, &wn, &we);         /* (scalar numpy altitude: altitude 0, as in hdg_cmd) */
         o[0] = (wn * cos(h) + we * sin(h)) / 50;
         o[1] = (-wn * sin(h) + we * cos(h)) / 50;
     }

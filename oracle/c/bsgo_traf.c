@@ -69,10 +69,28 @@ void bsgo_qdrdist(double latd1, double lond1, double latd2, double lond2, double
     *dist_nm = r * acos(c) / C_NM;
     *qdr = atan2(sin(lon2 - lon1) * coslat2, coslat1 * sin(lat2) - sin(lat1) * coslat2 * cos(lon2 - lon1)) * C_R2D;
 }
-/* Windfield.getdata without altitude profiles (oracle/refshim/bluesky/traffic/windfield.py) */
-void bsgo_wind(const bsgo_cfg *cfg, double lat, double lon, double *vn, double *ve) {
+/* np.interp(x, xp, fp): piecewise linear, constant beyond the ends */
+static double interp1(double x, const double *xp, const double *fp, int n) {
+    if (x <= xp[0]) return fp[0];
+    if (x >= xp[n - 1]) return fp[n - 1];
+    int k = 0;
+    while (k < n - 2 && x >= xp[k + 1]) k++;
+    return fp[k] + (x - xp[k]) * ((fp[k + 1] - fp[k]) / (xp[k + 1] - xp[k]));
+}
+/* Windfield.getdata (oracle/refshim/bluesky/traffic/windfield.py).  With an altitude profile (nknot > 0: one point):
+ * the knots resampled on the 100 ft axis, linear between the two axis levels around alt. */
+void bsgo_wind(const bsgo_cfg *cfg, double lat, double lon, double alt, double *vn, double *ve) {
     *vn = 0.0; *ve = 0.0;
     if (cfg->nwind <= 0) return;
+    if (cfg->nknot > 0) {
+        const double step = 100.0 * C_FT, top = 450.0 * step;                  /* altaxis = 0 .. 45 000 ft */
+        double idx = fmax(0.0, fmin(top - 1e-20, alt)) / step;
+        double il = floor(idx), f = idx - il;
+        double a0 = il * step, a1 = (il + 1.0) * step;
+        *vn = (1.0 - f) * interp1(a0, cfg->walt, cfg->wvn, cfg->nknot) + f * interp1(a1, cfg->walt, cfg->wvn, cfg->nknot);
+        *ve = (1.0 - f) * interp1(a0, cfg->walt, cfg->wve, cfg->nknot) + f * interp1(a1, cfg->walt, cfg->wve, cfg->nknot);
+        return;
+    }
     if (cfg->nwind == 1) { *vn = cfg->wvn[0]; *ve = cfg->wve[0]; return; }
     double w[BSGO_MAXWIND], tot = 0.0;
     for (int k = 0; k < cfg->nwind; k++) {
@@ -150,7 +168,7 @@ void bsgo_kin_substep(const bsgo_cfg *cfg, double *a, const double *ev, int n, i
     double t_hdg = bsgo_pymod(trk, 360.0);
     double vwn = 0.0, vwe = 0.0;
     if (wind) {          /* APorASAS.update with a wind field: ASAS ground speed -> TAS, wind-correction angle */
-        bsgo_wind(cfg, A(F_LAT), A(F_LON), &vwn, &vwe);
+        bsgo_wind(cfg, A(F_LAT), A(F_LON), A(F_ALT), &vwn, &vwe);
         if (act) {
             double tn = A(F_ASAS_TAS) * cos(A(F_ASAS_TRK) * C_D2R) - vwn, te = A(F_ASAS_TAS) * sin(A(F_ASAS_TRK) * C_D2R) - vwe;
             t_tas = sqrt(tn * tn + te * te);

@@ -32,7 +32,7 @@ class Cfg(C.Structure):
                 ('hpz', C.c_double), ('dtlook', C.c_double), ('resofach', C.c_double), ('resofacv', C.c_double),
                 ('nwind', C.c_int32), ('wind_obs', C.c_int32), ('wlat', C.c_double * MAXWIND),
                 ('wlon', C.c_double * MAXWIND), ('wvn', C.c_double * MAXWIND), ('wve', C.c_double * MAXWIND),
-                ('reso_mode', C.c_int32), ('pad0', C.c_int32)]
+                ('reso_mode', C.c_int32), ('nknot', C.c_int32), ('walt', C.c_double * MAXWIND)]
 
 
 class CdOut(C.Structure):
@@ -82,7 +82,15 @@ def make_cfg(kind, n, substeps=None, simdt=None, asas_on=0, reso_on=0, reso_off_
     c = Cfg(kind, n, d_sub[kind] if substeps is None else substeps, asas_on, reso_on, reso_off_own,
             d_dt[kind] if simdt is None else simdt, rpz, hpz, dtlook, resofach, resofacv)
     c.reso_mode = int(reso_mode)
-    if wind is not None:
+    if wind is not None and len(wind) == 5:
+        # WindFieldWrapper(env, lat, lon, vnorth[], veast[], alt=[]): ONE point with an altitude profile (knots)
+        wl, wo, vn, ve, wa = [np.atleast_1d(np.asarray(x, dtype=np.float64)) for x in wind]
+        assert len(wl) == 1 and 1 <= len(wa) <= MAXWIND and len(vn) == len(ve) == len(wa)
+        c.nwind = 1; c.wind_obs = int(wind_obs); c.nknot = len(wa)
+        c.wlat[0] = wl[0]; c.wlon[0] = wo[0]
+        for k in range(len(wa)):
+            c.walt[k] = wa[k]; c.wvn[k] = vn[k]; c.wve[k] = ve[k]
+    elif wind is not None:
         wl, wo, vn, ve = [np.atleast_1d(np.asarray(x, dtype=np.float64)) for x in wind]
         vn = np.broadcast_to(vn, wl.shape); ve = np.broadcast_to(ve, wl.shape)
         assert 1 <= len(wl) <= MAXWIND

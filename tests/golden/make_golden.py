@@ -97,7 +97,11 @@ def record(kind, seed, episodes, max_steps, asas=False, n_pad=None, wind=None):
         env = WindFieldWrapper(env, *wind, augment_obs=True)
     R = dict(ac0=[], reso0=[], nac=[], ev0=[], act=[], ac1=[], reso1=[], ev1=[], obs0=[], obs1=[], rew=[],
              term=[], trunc=[], info=[])
-    if wind is not None:
+    if wind is not None and len(wind) == 5:      # one point with an altitude profile: WindFieldWrapper(..., alt=[...])
+        R['windpt'] = np.array([wind[0], wind[1]], dtype=np.float64)
+        R['windprof'] = np.stack([np.asarray(wind[4], dtype=np.float64), np.asarray(wind[2], dtype=np.float64),
+                                  np.asarray(wind[3], dtype=np.float64)], axis=1)          # [knots][alt, vnorth, veast]
+    elif wind is not None:
         wl = np.atleast_1d(np.asarray(wind[0], dtype=np.float64))
         R['wind'] = np.stack([wl] + [np.broadcast_to(np.atleast_1d(np.asarray(w, dtype=np.float64)), wl.shape)
                                      for w in wind[1:]], axis=1)
@@ -145,6 +149,8 @@ def record(kind, seed, episodes, max_steps, asas=False, n_pad=None, wind=None):
 def main():
     bluesky_gym.register_envs()
     W1 = (52.0, 4.0, 12.0, -7.0)                                        # one point: uniform wind
+    WP = (52.0, 4.0, np.array([4.0, 12.0, -6.0, 20.0]), np.array([-3.0, 8.0, 15.0, -10.0]),
+          np.array([0.0, 1000.0, 2500.0, 6000.0]))                        # one point, four knots [m]
     W3 = ([51.5, 52.6, 52.0], [3.5, 4.2, 5.5], [10.0, -4.0, 6.0], [-8.0, 12.0, 3.0])   # three points: weighted field
     specs = [('H', 11, 4, 45, False, None, ''), ('V', 12, 4, 50, False, None, ''), ('S', 13, 4, 120, False, None, ''),
              ('H', 21, 3, 30, True, None, '_asas'), ('S', 23, 3, 60, True, None, '_asas'),
@@ -153,7 +159,9 @@ def main():
              ('H', 35, 2, 30, False, W1, '_wind'), ('S', 36, 2, 40, True, W3, '_asas_wind'),
              # MVP resolution methods beyond the default: vertical only / horizontal + vertical
              ('V', 41, 4, 50, 'v', None, '_mvpv'), ('V', 42, 4, 50, 'hv', None, '_mvphv'),
-             ('H', 43, 3, 30, 'hv', None, '_mvphv'), ('S', 44, 2, 50, 'v', None, '_mvpv')]
+             ('H', 43, 3, 30, 'hv', None, '_mvphv'), ('S', 44, 2, 50, 'v', None, '_mvpv'),
+             # wind with an altitude profile (the wrapper's alt= argument): the Vertical env climbs / descends through it
+             ('V', 45, 3, 50, False, WP, '_windalt'), ('S', 46, 2, 40, True, WP, '_asas_windalt')]
     only = sys.argv[1:]          # e.g. `make_golden.py V_mvpv H_mvphv` regenerates those fixtures alone
     for kind, seed, eps, ms, asas, wind, tag in specs:
         if only and f"{kind}{tag}" not in only:

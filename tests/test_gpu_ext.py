@@ -10,7 +10,7 @@ from test_gpu_parity import relerr, obs_tol32, run_step, RT64, RT32
 
 pytestmark = pytest.mark.gpu
 KIND = {'H': 0, 'V': 1, 'S': 2, 'M': 4}
-EXT_GOLDEN = ['M', 'M_wind', 'S_wind', 'V_wind', 'H_wind', 'S_asas_wind']
+EXT_GOLDEN = ['M', 'M_wind', 'S_wind', 'V_wind', 'H_wind', 'S_asas_wind', 'V_windalt', 'S_asas_windalt']
 STATE_FIELDS = ['lat', 'lon', 'alt', 'hdg', 'tas', 'vs', 'selspd', 'selalt', 'selvs', 'aptrk', 'ax', 'asas_trk',
                 'asas_tas', 'asas_vs', 'asas_alt', 'asas_active', 'phase', 'gsn', 'gse', 'lnav']
 
@@ -23,6 +23,9 @@ def golden_core(name, g, precision):
     if 'wind' in g:
         w = g['wind']
         core.set_wind(w[:, 0], w[:, 1], w[:, 2], w[:, 3], augment_obs=True)
+    if 'windprof' in g:      # WindFieldWrapper(env, lat, lon, vnorth[], veast[], alt=[...]): one point, altitude profile
+        p = g['windprof']
+        core.set_wind(float(g['windpt'][0]), float(g['windpt'][1]), p[:, 1], p[:, 2], alt=p[:, 0], augment_obs=True)
     return core
 
 
@@ -30,7 +33,7 @@ def ref_obs_of(g, obs):
     """The reference's obs with the wind slots of terminated rows taken from ours: on termination the reference
     deletes aircraft before the wrapper looks up 'kl001' (id2idx -> -1 -> the last remaining aircraft)."""
     ref = g['obs1'].copy()
-    if 'wind' in g:
+    if 'wind' in g or 'windprof' in g:
         t = g['term'] == 1
         ref[t, -2:] = obs[t, -2:]
     return ref

@@ -18,6 +18,8 @@ def golden_cfg(orc, name, g):
     asas = int('asas' in name or 'mvp' in name)
     mode = 2 if 'mvphv' in name else (1 if 'mvpv' in name else 0)     # MVP resolution method (RMETHH / RMETHV)
     wind = tuple(g['wind'].T) if 'wind' in g else None
+    if 'windprof' in g:      # one point with an altitude profile: (lat, lon, vnorth[], veast[], alt[])
+        wind = (g['windpt'][0], g['windpt'][1], g['windprof'][:, 1], g['windprof'][:, 2], g['windprof'][:, 0])
     return orc.make_cfg(KIND[kind], g['ac0'].shape[2], asas_on=asas, reso_on=asas, reso_off_own=asas,
                         wind=wind, wind_obs=int(wind is not None), reso_mode=mode)
 
@@ -42,7 +44,7 @@ def vertical_degenerate_steps(orc, cfg, g, na, name, eps=1e-9):
 
 
 GOLDEN = ['H', 'V', 'S', 'H_asas', 'S_asas', 'M', 'M_wind', 'S_wind', 'V_wind', 'H_wind', 'S_asas_wind',
-          'V_mvpv', 'V_mvphv', 'H_mvphv', 'S_mvpv']
+          'V_mvpv', 'V_mvphv', 'H_mvphv', 'S_mvpv', 'V_windalt', 'S_asas_windalt']
 
 
 @pytest.mark.parametrize('name', GOLDEN)
