@@ -456,7 +456,14 @@ def run_giant(ctx, K, W, mode):
                    "l2": "256 MB flush between timed iterations"},
         "roofline": {"bound": "fp32", "achieved": ach, "peak": peak32, "unit": "TFLOP/s", "frac": ach / peak32,
                      "traffic": ncu_traffic('c5'), "kernel": ("cd_sym_sweep_kernel" if sym else "cd_sweep_kernel") + " (+ pack, collectives, init/finalize inside the timed step)"},
-        "gpu_launches": (4 if sym else 2) * K + (2 * K if (mode == "peer" and world > 1) else 0), "clocks": clocks}
+        # kernels per step: peer = pack+init | sweep | finalize (+ 2 symmetric-memory barrier kernels at N > 1);
+        # allreduce = pack | init | sweep | finalize; ordered = pack | sweep
+        "gpu_launches": (3 if mode == "peer" else 4 if sym else 2) * K + (2 * K if (mode == "peer" and world > 1) else 0),
+        # what crosses NVLink per step, algorithmic: every rank reads the packed records (32 B per aircraft) it does not own
+        "nvlink_bytes_per_step": {"per_rank": 32.0 * E * N * (world - 1) / world, "all_ranks": 32.0 * E * N * (world - 1),
+                                  "note": "algorithmic: remote 32-byte records read once per sweep (tile reuse through L2 / shared "
+                                          "memory), plus the rare conflict updates flushed to their owners"},
+        "clocks": clocks}
 
 
 def run_ndmap(ctx, K, W, envs=0):
@@ -522,7 +529,7 @@ def compact(line):
     if line is None:
         return None
     keep = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "config", "pair_evals_per_sec",
-            "roofline", "e2e", "gpu_launches")
+            "roofline", "e2e", "gpu_launches", "nvlink_bytes_per_step")
     return {k: line[k] for k in keep if k in line}
 
 

@@ -429,13 +429,13 @@ class PeerSweep:
         """SoA CUDA tensors [E, rows] of the OWN aircraft -> row outputs [E, rows] of the own rows."""
         lib, E, dev = self.lib, self.E, self.block.device
         s = C.c_void_p(torch.cuda.current_stream(dev).cuda_stream)
-        own = L.CdParams(E, self.rows, 0, self.rows, rpz_m, hpz_m, dtlookahead, 0)
         full = L.CdParams(E, self.N, 0, self.N, rpz_m, hpz_m, dtlookahead, 0)
         self.rec, self.peers = self.recs[self.parity], self.peer_tabs[self.parity]
         self.parity ^= 1
-        L.check(lib.bsg_cd_pack(E, self.rows, _ptr(lat), _ptr(lon), _ptr(alt), _ptr(trk), _ptr(gs), _ptr(vs), float(lat0),
-                                float(lon0), _ptr(self.rec), s))
-        L.check(lib.bsg_cd_sym_init(C.byref(own), _ptr(self.nconf), _ptr(self.nlos), _ptr(self.tcpamax), _ptr(self.key), s))
+        # records packed and row accumulators reset by ONE launch
+        L.check(lib.bsg_cd_pack_init(E, self.rows, _ptr(lat), _ptr(lon), _ptr(alt), _ptr(trk), _ptr(gs), _ptr(vs), float(lat0),
+                                     float(lon0), _ptr(self.rec), _ptr(self.nconf), _ptr(self.nlos), _ptr(self.tcpamax),
+                                     _ptr(self.key), s))
         if self.h is not None:
             self.h.barrier(channel=0)                  # every rank's records packed, accumulators initialised
         L.check(lib.bsg_cd_sym_sweep_peers(C.byref(full), C.byref(self.peers), self.rank, self.world, s))

@@ -298,10 +298,14 @@ __global__ void cd_sym_finalize_kernel(const bsg_cd_params p, const SymPeers Q, 
     if (near_tin) near_tin[k] = ti;
 }
 
+// INIT: the row accumulators of the symmetric sweep are reset by the same launch (one kernel fewer in a peer-sweep step)
+template <bool INIT>
 __global__ void cd_pack_kernel(int E, int N, const double *lat, const double *lon, const float *alt, const float *trk,
-                               const float *gs, const float *vs, double lat0, double lon0, RecFast *rec) {
+                               const float *gs, const float *vs, double lat0, double lon0, RecFast *rec,
+                               int32_t *nconf = nullptr, int32_t *nlos = nullptr, int32_t *tcpamax_bits = nullptr, long long *key = nullptr) {
     size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (k >= (size_t)E * N) return;
+    if (INIT) { nconf[k] = 0; nlos[k] = 0; tcpamax_bits[k] = 0; key[k] = 0x7fffffffffffffffLL; }
     RecFast r;
     r.x = (float)((lon[k] - lon0) * (kD2R * kRe));
     r.y = (float)((lat[k] - lat0) * (kD2R * kRe));
@@ -337,8 +341,18 @@ int bsg_cd_pack(int32_t E, int32_t N, const double *lat, const double *lon, cons
                 const float *gs, const float *vs, double lat0, double lon0, float *rec, void *stream) {
     if (E < 1 || N < 1 || !lat || !lon || !alt || !trk || !gs || !vs || !rec) return BSG_ERR_ARG;
     const size_t EN = (size_t)E * N;
-    cd_pack_kernel<<<(unsigned)((EN + 255) / 256), 256, 0, (cudaStream_t)stream>>>(E, N, lat, lon, alt, trk, gs, vs, lat0,
-                                                                                  lon0, reinterpret_cast<RecFast *>(rec));
+    cd_pack_kernel<false><<<(unsigned)((EN + 255) / 256), 256, 0, (cudaStream_t)stream>>>(E, N, lat, lon, alt, trk, gs, vs, lat0,
+                                                                                         lon0, reinterpret_cast<RecFast *>(rec));
+    return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
+}
+
+int bsg_cd_pack_init(int32_t E, int32_t N, const double *lat, const double *lon, const float *alt, const float *trk,
+                     const float *gs, const float *vs, double lat0, double lon0, float *rec, int32_t *nconf, int32_t *nlos,
+                     float *tcpamax, int64_t *key, void *stream) {
+    if (E < 1 || N < 1 || !lat || !lon || !alt || !trk || !gs || !vs || !rec || !nconf || !nlos || !tcpamax || !key) return BSG_ERR_ARG;
+    const size_t EN = (size_t)E * N;
+    cd_pack_kernel<true><<<(unsigned)((EN + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+        E, N, lat, lon, alt, trk, gs, vs, lat0, lon0, reinterpret_cast<RecFast *>(rec), nconf, nlos, (int32_t *)tcpamax, (long long *)key);
     return cudaGetLastError() == cudaSuccess ? BSG_OK : BSG_ERR_CUDA;
 }
 

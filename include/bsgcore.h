@@ -189,6 +189,10 @@ int bsg_step_host_wait(bsg_handle *h, void **obs, void **reward, void **info, in
 int bsg_cd_pack(int32_t num_envs, int32_t num_ac, const double *lat_dev, const double *lon_dev,
                 const float *alt_dev, const float *trk_dev, const float *gs_dev, const float *vs_dev,
                 double lat0, double lon0, float *rec_dev /* [E][N][8] */, void *stream);
+/* bsg_cd_pack + bsg_cd_sym_init of the same E x N rows in ONE launch (the peer sweep's step: one kernel fewer) */
+int bsg_cd_pack_init(int32_t num_envs, int32_t num_ac, const double *lat_dev, const double *lon_dev, const float *alt_dev,
+                     const float *trk_dev, const float *gs_dev, const float *vs_dev, double lat0, double lon0, float *rec_dev,
+                     int32_t *nconf_dev, int32_t *nlos_dev, float *tcpamax_dev, int64_t *key_dev, void *stream);
 int bsg_cd_sweep(const bsg_cd_params *p, const float *rec_dev, uint8_t *inconf_dev, int32_t *nconf_dev,
                  int32_t *nlos_dev, int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev,
                  float *near_tin_dev, float *tcpamax_dev, void *stream);
