@@ -48,12 +48,15 @@ class BlueSkyVecEnv:
 
     def __init__(self, env_id, num_envs, num_aircraft=None, device=0, precision='fp32', asas=False, mvp=False,
                  seed=0, cd_outputs=False, max_episode_steps=None, wind=None, wind_obs=False, obs_noise=0.0,
-                 ac_density_mode='normal', fixed_nac=False):
+                 ac_density_mode='normal', fixed_nac=False, ndmap_obs=None):
         """wind = (lat, lon, vnorth, veast) like WindFieldWrapper(env, lat, lon, vnorth, veast, augment_obs=wind_obs);
         obs_noise = NoisyObservationWrapper(env, noise_level); ac_density_mode = SectorCREnv's "normal" | "uniform"
         (sector_cr_env.py:45,98-103); fixed_nac = every aircraft slot live (the synthetic scale-up configs).
         mvp = True | 'horizontal' (BlueSky's default resolution method, heading + speed) | 'vertical' (RMETHV V/S) |
-        'both' (horizontal + vertical): ASAS ON + RESO MVP for the intruders, RESOOFF for the agent."""
+        'both' (horizontal + vertical): ASAS ON + RESO MVP for the intruders, RESOOFF for the agent.
+        ndmap_obs = True | dict of BsgCore.ndmap keywords: every reset / step also builds the ND-map (4D conflict grid over
+        the look-ahead trajectories) of the live traffic and appends the observation key 'ndmap_conflict_cells' [nt]: the
+        share of grid cells in conflict at each look-ahead step (the map itself stays on the device: ndmap_last)."""
         reso_mode = {True: 0, 'horizontal': 0, 'vertical': 1, 'both': 2}[mvp] if mvp else 0
         if ac_density_mode not in ('normal', 'uniform'):
             raise ValueError(f"ac_density_mode must be 'normal' or 'uniform', not {ac_density_mode!r}")
@@ -70,18 +73,42 @@ class BlueSkyVecEnv:
             self.core.set_wind(*wind, augment_obs=wind_obs)
         if obs_noise:
             self.core.set_obs_noise(obs_noise, seed=int(seed) + 0x5EED)
-        wind_obs = self.core.wind_obs
-        self.single_observation_space, self.single_action_space = single_spaces(kind, self.num_aircraft, wind_obs)
-        self.observation_space, self.action_space = self.single_observation_space, self.single_action_space
-        self._slices = obs_slices(kind, self.num_aircraft, wind_obs)
         self._seed = int(seed)
+        self._nd = None
+        self._refresh_spaces()
+        if ndmap_obs:
+            # default grid: 320 x 320 km around the env's origin in 5 km cells, 12 km of altitude in 1.5 km layers,
+            # 30 look-ahead steps of 10 s
+            nd = dict(nx=64, ny=64, nz=8, nt=30, x0=-160e3, y0=-160e3, z0=0.0, cx=5e3, cy=5e3, cz=1.5e3, dt=10.0,
+                      lat0=52.0, lon0=4.0)
+            if isinstance(ndmap_obs, dict):
+                nd.update(ndmap_obs)
+            self._nd, self._nd_out, self.ndmap_last = nd, None, None
+            self._nd_cells = float(nd['nx'] * nd['ny'] * nd['nz'])
+            self._refresh_spaces()
         self._act = torch.zeros((self.num_envs, act_dim), dtype=self.core.rdtype, device=self.core.device)
         self.closed = False
+
+    def _refresh_spaces(self):
+        """observation / action spaces and the slices of the flat observation (again after a wrapper added wind slots)"""
+        wind_obs = self.core.wind_obs
+        self.single_observation_space, self.single_action_space = single_spaces(self.kind, self.num_aircraft, wind_obs)
+        if self._nd is not None:
+            d = dict(self.single_observation_space.spaces)
+            d['ndmap_conflict_cells'] = spaces.Box(0.0, 1.0, shape=(self._nd['nt'],), dtype=np.float64)
+            self.single_observation_space = spaces.Dict(d)
+        self.observation_space, self.action_space = self.single_observation_space, self.single_action_space
+        self._slices = obs_slices(self.kind, self.num_aircraft, wind_obs)
 
     # ------------------------------------------------------------------ Gymnasium VectorEnv API
     def _obs_dict(self, flat):
         flat = np.asarray(flat, dtype=np.float64)
-        return {k: flat[:, a:b] for k, a, b in self._slices}
+        d = {k: flat[:, a:b] for k, a, b in self._slices}
+        if self._nd is not None:      # the ND-map of the state this observation describes, consumed as an observation key
+            self._nd_out = self.core.ndmap(out=self._nd_out, **self._nd)
+            self.ndmap_last = self._nd_out
+            d['ndmap_conflict_cells'] = self._nd_out[2].cpu().numpy().astype(np.float64) / self._nd_cells
+        return d
 
     def _infos(self, info):
         info = np.asarray(info, dtype=np.float64)

@@ -50,9 +50,7 @@ class WindFieldWrapper(_Wrapper):
         super().__init__(env)
         v = self._v
         v.core.set_wind(lat, lon, vnorth, veast, alt=alt, augment_obs=augment_obs)     # alt: one point with a profile
-        v.single_observation_space, v.single_action_space = single_spaces(v.kind, v.num_aircraft, v.core.wind_obs)
-        v.observation_space = v.single_observation_space
-        v._slices = obs_slices(v.kind, v.num_aircraft, v.core.wind_obs)
+        v._refresh_spaces()
         self.observation_space = v.single_observation_space
         if hasattr(env, 'observation_space') and env is not v:
             try:

@@ -217,3 +217,35 @@ def test_reset_distributions_match_the_reference(kind):
     print(f"[reset {kind}] KS statistic / critical (alpha 1e-3) / reference mean / device mean: {report}")
     bad = {k: v for k, v in report.items() if v[0] > v[1]}
     assert not bad, bad
+
+
+def test_ndmap_is_consumed_as_an_observation_key():
+    """ndmap_obs: every reset / step builds the ND-map of the live traffic and the observation carries the share of grid
+    cells in conflict per look-ahead step; the key equals a stand-alone build of the same state, follows the traffic from
+    step to step, and the registered single envs take the option through make()."""
+    import bluesky_gym_hallucination_b200 as bluesky_gym
+    from bluesky_gym_hallucination_b200 import BlueSkyVecEnv
+    E = 16
+    v = BlueSkyVecEnv('SectorCREnv-v0', E, num_aircraft=24, ndmap_obs=True, seed=5, fixed_nac=True)
+    assert v.single_observation_space['ndmap_conflict_cells'].shape == (30,)
+    obs, _ = v.reset(seed=5)
+    key0 = obs['ndmap_conflict_cells']
+    assert key0.shape == (E, 30) and key0.dtype == np.float64 and (key0 >= 0).all() and (key0 <= 1).all()
+    occ, conf, ncell = v.ndmap(**v._nd)                                   # stand-alone build of the same live state
+    assert np.array_equal(key0, ncell.cpu().numpy() / float(64 * 64 * 8))
+    assert (key0 > 0).any()                                               # 24 aircraft in one sector: conflicts ahead
+    assert int(occ.sum().item()) > 0 and v.ndmap_last is not None
+    rng = np.random.default_rng(0)
+    for _ in range(3):
+        obs, rew, term, trunc, info = v.step(rng.uniform(-1, 1, (E, 2)))
+    assert not np.array_equal(obs['ndmap_conflict_cells'], key0)          # the map follows the traffic
+    assert set(obs) == set(v.single_observation_space.spaces)
+    v.close()
+    bluesky_gym.register_envs()
+    env = bluesky_gym.make('HorizontalCREnv-v0', ndmap_obs=dict(nt=12))
+    o, _ = env.reset(seed=1)
+    assert o['ndmap_conflict_cells'].shape == (12,) and 'ndmap_conflict_cells' in env.observation_space.spaces
+    o, r, te, tr, i = env.step(np.zeros(1))
+    assert o['ndmap_conflict_cells'].shape == (12,)
+    env.close()
+
