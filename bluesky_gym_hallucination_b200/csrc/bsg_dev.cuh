@@ -65,6 +65,25 @@ __device__ __forceinline__ float wrap360(float a) {
     a = (a >= 360.0f) ? a - 360.0f : a;
     return (a < 0.0f) ? a + 360.0f : a;
 }
+// one wrap only: a in (-360, 720) -- differences and sums of two angles already in [0, 360) (same values as wrap360 there)
+__device__ __forceinline__ float wrap360_once(float a) {
+    a = (a < 0.0f) ? a + 360.0f : a;                 // (a tiny negative angle rounds up to 360.0 here ...
+    return (a >= 360.0f) ? a - 360.0f : a;           //  ... and lands on 0, as in wrap360)
+}
+// (sin, cos) of an angle in degrees, |deg| < 2^20: x = deg / 180, quadrant k = rint(2 x), r = x - k / 2 in [-1/4, 1/4] (exact),
+// Taylor polynomials of sin(pi r) to r^9 and cos(pi r) to r^8 (truncation 2e-9 / 3e-8 absolute), quadrant swap / signs by
+// bit tests: about 20 instructions against the 30+ of sincospif (which also serves huge arguments, inf and NaN).
+__device__ __forceinline__ void sincos_deg_fast(float deg, float &s, float &c) {
+    const float x = deg * (1.0f / 180.0f);
+    const float kf = rintf(x + x);
+    const float r = fmaf(kf, -0.5f, x), t = r * r;
+    const float sp = r * fmaf(t, fmaf(t, fmaf(t, fmaf(t, 0.0821458866f, -0.599264529f), 2.55016404f), -5.16771278f), 3.14159265f);
+    const float cp = fmaf(t, fmaf(t, fmaf(t, fmaf(t, 0.235330630f, -1.33526277f), 4.05871213f), -4.93480220f), 1.0f);
+    const int k = (int)kf;
+    const float a = (k & 1) ? cp : sp, b = (k & 1) ? sp : cp;          // sin(pi x) = +-sin / +-cos of pi r by quadrant
+    s = (k & 2) ? -a : a;
+    c = ((k + 1) & 2) ? -b : b;
+}
 template <typename R> __device__ __forceinline__ R mod360(R a) {
     if constexpr (sizeof(R) == 8) return pymod(a, 360.0); else return wrap360(a);
 }
@@ -150,14 +169,22 @@ template <typename R> __device__ __forceinline__ int flight_phase(R vs, R alt) {
     R roc, h;
     if constexpr (sizeof(R) == 8) { roc = vs / kFpm; h = alt / kFt; }               // literal order (numpy divides)
     else { roc = vs * float(1.0 / kFpm); h = alt * float(1.0 / kFt); }              // fast path: no IEEE division
-    int ph = PH_NA;
-    if (h <= R(75)) ph = PH_GD;
-    if (h > R(75) && h <= R(1000) && roc >= R(150)) ph = PH_IC;
-    if (h > R(75) && h <= R(1000) && roc <= R(-150)) ph = PH_AP;
-    if (h > R(1000) && roc >= R(150)) ph = PH_CL;
-    if (h > R(1000) && roc <= R(-150)) ph = PH_DE;
-    if (h > R(10000) && roc > R(-150) && roc < R(150)) ph = PH_CR;
-    return ph;
+    if constexpr (sizeof(R) == 8) {                                 // literal chain of tests
+        int ph = PH_NA;
+        if (h <= R(75)) ph = PH_GD;
+        if (h > R(75) && h <= R(1000) && roc >= R(150)) ph = PH_IC;
+        if (h > R(75) && h <= R(1000) && roc <= R(-150)) ph = PH_AP;
+        if (h > R(1000) && roc >= R(150)) ph = PH_CL;
+        if (h > R(1000) && roc <= R(-150)) ph = PH_DE;
+        if (h > R(10000) && roc > R(-150) && roc < R(150)) ph = PH_CR;
+        return ph;
+    } else {
+        // the same table as a decision tree (equal for every input, NaN included: checked exhaustively on the host)
+        const bool gd = h <= R(75), air = h > R(75), low = h <= R(1000), up = roc >= R(150), dn = roc <= R(-150);
+        const int moving = up ? (low ? PH_IC : PH_CL) : (low ? PH_AP : PH_DE);
+        const int level = (h > R(10000) && roc > R(-150) && roc < R(150)) ? PH_CR : PH_NA;
+        return gd ? PH_GD : ((air && (up || dn)) ? moving : level);
+    }
 }
 __device__ __forceinline__ void phase_vlimits(int ph, double &vmin, double &vmax) {
     bool enroute = (ph == PH_CL) || (ph == PH_CR) || (ph == PH_DE);

@@ -52,7 +52,7 @@ template <typename R, bool EXT = false> __device__ __forceinline__ void ac_deriv
     } else {
         R s, c;
         if constexpr (sizeof(R) == 8) { s = sin(a.hdg * kD2R); c = cos(a.hdg * kD2R); }
-        else { sincospif(a.hdg * (1.0f / 180.0f), &s, &c); sincospif((float)(a.lat * (1.0 / 360.0)), &a.sa, &a.ca); }
+        else { sincos_deg_fast(a.hdg, s, c); sincospif((float)(a.lat * (1.0 / 360.0)), &a.sa, &a.ca); }
         a.gsn = a.tas * c; a.gse = a.tas * s;
     }
 }
@@ -309,9 +309,9 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     a.ax = ax;
     const float kTurn = float(9.80665 * 0.46630765815499864 * kR2D);   // g0 * tan(25 deg) in deg/s * m/s
     float turn = dt * kTurn * rcp_approx(fmaxf(tas, 1e-8f));
-    float delhdg = wrap360(t_hdg - a.hdg + 180.0f) - 180.0f;
+    float delhdg = wrap360_once(t_hdg - a.hdg + 180.0f) - 180.0f;      // both in [0, 360): one wrap
     bool swhdg = fabsf(delhdg) > turn;
-    float hdg = wrap360(swhdg ? a.hdg + copysignf(turn, delhdg) : t_hdg);
+    float hdg = wrap360_once(swhdg ? a.hdg + copysignf(turn, delhdg) : t_hdg);   // |turn| < 360: one wrap
     float dalt = allow_h - a.alt;
     bool swalt = fabsf(dalt) > 1.05f * dt * fmaxf(avs, fabsf(a.vs));
     float tvs = swalt ? copysignf(avs, dalt) : 0.0f;
@@ -319,7 +319,7 @@ __device__ __forceinline__ void kin_substep_fast(AcReg<float> &a, float dt, bool
     bool need_az = fabsf(dvs) > float(300 * kFpm);
     float vs = need_az ? a.vs + copysignf(float(300 * kFpm), dvs) * dt : tvs;
     float s, c;
-    sincospif(hdg * (1.0f / 180.0f), &s, &c);                // hdg in [0, 360): exact range reduction in sincospi
+    sincos_deg_fast(hdg, s, c);                              // hdg in [0, 360): exact quadrant reduction
     float gsn = tas * c, gse = tas * s;
     if (wind && a.alt > float(50.0 * kFt)) { gsn += vwn; gse += vwe; }
     float alt_old = a.alt;
