@@ -41,7 +41,19 @@ def test_cd_sweep_vs_oracle(orc, E, N, box):
         ok = ~bad_c & ~near_c
         assert np.array_equal(got['inconf'][e][ok], ref['inconf'][e][ok])
         same = ok & (got['near_idx'][e] == ref['near_idx'][e]) & (ref['near_idx'][e] >= 0)
-        assert same.sum() >= 0.98 * (ok & (ref['near_idx'][e] >= 0)).sum()
+        # the soonest conflict of a row is an argmin over tCPA: a different index is accepted only where the oracle
+        # itself holds a TIE -- the intruder the GPU chose is a conflict of the row whose tCPA is within 1e-5 (relative,
+        # floor 1 s) of the row's minimum; every such row is enumerated
+        diff = np.where(ok & (ref['near_idx'][e] >= 0) & (got['near_idx'][e] != ref['near_idx'][e]))[0]
+        ties = []
+        for i in diff:
+            jg, jr = int(got['near_idx'][e][i]), int(ref['near_idx'][e][i])
+            assert jg >= 0 and d['swconfl'][i, jg], f"env {e} row {i}: GPU's soonest intruder {jg} is no conflict of the oracle's row"
+            gap = abs(d['tcpa'][i, jg] - d['tcpa'][i, jr]) / max(abs(d['tcpa'][i, jr]), 1.0)
+            assert gap < 1e-5, f"env {e} row {i}: intruder {jg} vs {jr}, tCPA gap {gap:.2e}"
+            ties.append((int(i), jg, jr, float(gap)))
+        if ties:
+            print(f"env {e}: soonest-conflict ties enumerated (row, GPU intruder, oracle intruder, relative tCPA gap): {ties[:6]}")
         for k, tol in (('near_tcpa', 1e-5), ('near_tin', 2e-5), ('tcpamax', 1e-5)):
             err = np.abs(got[k][e][same] - ref[k][e][same]) / np.maximum(np.abs(ref[k][e][same]), 1.0)
             assert err.max(initial=0) < tol * 10, (k, err.max())
@@ -73,7 +85,19 @@ def test_giant_airspace_full_env_vs_oracle(orc):
     ok = ~bad_c & ~near_c
     assert np.array_equal(got['inconf'][ok] != 0, ref['inconf'][ok] != 0)
     same = ok & (got['near_idx'] == ref['near_idx']) & (ref['near_idx'] >= 0)
-    assert same.sum() >= 0.995 * (ok & (ref['near_idx'] >= 0)).sum()
+    # a different soonest intruder only at a tie of the oracle's own tCPA values (three-aircraft oracle evaluation of
+    # the row's aircraft with both candidates); every such row is enumerated
+    ties = []
+    for e, i in np.argwhere(ok & (ref['near_idx'] >= 0) & (got['near_idx'] != ref['near_idx'])):
+        jg, jr = int(got['near_idx'][e, i]), int(ref['near_idx'][e, i])
+        assert jg >= 0
+        sel = [i, jg, jr]
+        d3 = orc.detect_dense(lat[e][sel], lon[e][sel], alt[e][sel], trk[e][sel], gs[e][sel], vs[e][sel])
+        assert d3['swconfl'][0, 1], f"row {i}: GPU's soonest intruder {jg} is no conflict of the oracle's row"
+        gap = abs(d3['tcpa'][0, 1] - d3['tcpa'][0, 2]) / max(abs(d3['tcpa'][0, 2]), 1.0)
+        assert gap < 1e-4, f"row {i}: intruder {jg} vs {jr}, tCPA gap {gap:.2e}"      # (the bound of the time comparison below)
+        ties.append((int(i), jg, jr, float(gap)))
+    print(f"C5 full env: soonest-conflict ties enumerated: {len(ties)} {ties[:5]}")
     # times: fp32 records in a 1000 NM box resolve positions to 0.125 m, i.e. tCPA to ~0.1 m / |v_rel| -- an absolute
     # floor of 0.02 s beside the 1e-4 relative bound
     for k in ('near_tcpa', 'tcpamax'):
