@@ -59,6 +59,13 @@ def env_threshold_margin(kind, ac1, ev, nac, F, EV):
         elif kind == 1:
             rwy = 200.0 - kwikdist_nm(52.0, 4.0, lat[0], lon[0]) * 1.852
             m = min(m, abs(rwy) / 200.0, abs(alt[0]) / 3000.0)
+        elif kind == 4:      # Merge (merge_env.py:247-283): intrusion at 4 NM, FAF reached at 10, runway at 20 (distance units of the env)
+            if d.size:
+                m = np.min(np.abs(d - 4.0) / 4.0)
+            pre = ev[e, EV['wpt_reach']] != 1.0
+            wd = kwikdist_nm(lat[0], lon[0], ev[e, EV['wpt_lat']] if pre else ev[e, EV['wpt_x']],
+                             ev[e, EV['wpt_lon']] if pre else ev[e, EV['wpt_y']])
+            m = min(m, abs(wd - 10.0) / 10.0, abs(wd - 20.0) / 20.0)
         elif kind == 2:
             nv = int(ev[e, EV['nvert']])
             vlat = ev[e, EV['poly']:EV['poly'] + 2 * nv:2]; vlon = ev[e, EV['poly'] + 1:EV['poly'] + 2 * nv:2]

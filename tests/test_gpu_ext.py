@@ -82,18 +82,40 @@ def test_fp32_ext_replays_reference_goldens(orc, name):
     if kind == 'M':        # cos/sin(track): direction of a velocity difference (merge_env.py:213-215), as in Sector
         vrel = np.hypot(ref[:, 15:20] * 150, ref[:, 20:25] * 150)
         tol[:, 25:30] *= np.maximum(1.0, 600.0 / vrel); tol[:, 30:35] *= np.maximum(1.0, 600.0 / vrel)
-    # thresholds crossed within fp32 rounding (intrusion, waypoint, LNAV switch, MVP activity) are enumerated
+    # thresholds crossed within fp32 rounding are ENUMERATED, not counted: a reward / termination / truncation flip must
+    # sit within EPS32 of an env-layer threshold in the ORACLE's post-step state (intrusion, waypoint, runway, polygon),
+    # or -- with MVP on -- belong to a step whose resolution decisions the oracle's trace places at a threshold /
+    # ill-conditioned pair; an ASAS-activity flip must be such a step; LNAV switches (a turn-radius test on the route) are
+    # listed and bounded by count
+    from test_oracle_golden import golden_cfg
+    from parity_helpers import env_threshold_margin
+    from test_gpu_parity import EPS32, KAPPA0
+    cfg = golden_cfg(orc, name, g)
+    o_ac, o_reso, o_ev = g['ac0'].copy(), g['reso0'].copy(), g['ev0'].copy()
+    tr = orc.step_trace(cfg, o_ac, o_reso, nac, o_ev, np.ascontiguousarray(g['act'][:, :na]), EPS32, nthreads=4)[5]
+    near_env = env_threshold_margin(KIND[kind], o_ac, o_ev, nac, orc.F, orc.EV) < EPS32
+    kap = np.nan_to_num(tr['kappa'], nan=0.0, posinf=1e30).max(1)
+    near_res = ((tr['res_margin'] < EPS32).any(1) | (kap >= KAPPA0)) if 'asas' in name else np.zeros(T, bool)
     lnav_flip = (ac1[:, orc.F['lnav']] != g['ac1'][:, orc.F['lnav']]).any(1) & (g['term'] == 0)
     act_flip = (ac1[:, orc.F['asas_active']] != g['ac1'][:, orc.F['asas_active']]).any(1) & (g['term'] == 0)
-    flip = (term != g['term']) | (np.abs(rew - g['rew']) > 0.5) | lnav_flip | act_flip
+    hard = (term != g['term']) | (np.abs(rew - g['rew']) > 0.5)
     if kind != 'M':
-        flip |= trunc != g['trunc']
-    assert flip.sum() <= max(2, T // 25), f"{flip.sum()} threshold flips in {T} steps"
-    bad = np.abs(obs - ref) > tol
-    if 'asas' in name:     # MVP conditioning (test_gpu_parity.test_batched_step_vs_oracle): 99 % within 2x, none beyond 100x
-        err = np.abs(obs - ref)[~flip]
-        assert (err > 2 * tol[~flip]).mean() < 0.01 and (err > 100 * tol[~flip]).sum() == 0
+        hard |= trunc != g['trunc']
+    print(f"[{name}] fp32 flips enumerated: reward / termination {np.where(hard)[0].tolist()}, ASAS activity {np.where(act_flip)[0].tolist()}, "
+          f"LNAV switch {np.where(lnav_flip)[0].tolist()}; steps at an env threshold {int(near_env.sum())}, at a resolution threshold {int(near_res.sum())} of {T}")
+    assert not (hard & ~near_env & ~near_res).any(), np.where(hard & ~near_env & ~near_res)[0]
+    assert not (act_flip & ~near_res).any(), np.where(act_flip & ~near_res)[0]
+    assert lnav_flip.sum() <= max(2, T // 25)
+    flip = hard | lnav_flip | act_flip
+    err = np.abs(obs - ref)
+    if 'asas' in name:     # MVP conditioning, as in test_gpu_parity.test_batched_step_vs_oracle: the bound per step is
+        # 1e-5 max(|ref|, 1) + 8 eps_f32 kappa / vnorm; 99 % of the entries sit inside the plain bound
+        keep = ~flip & ~near_res
+        wid = tol + ((8 * 2.0 ** -24 / 32.0) * kap)[:, None]
+        assert not (err > wid)[keep].any(), np.argwhere((err > wid) & keep[:, None])[:5]
+        assert np.quantile((err / tol)[keep], 0.99) <= 1.0
     else:
+        bad = err > tol
         assert bad[~flip].sum() == 0, (np.argwhere(bad)[:5], relerr(obs[~flip], ref[~flip]))
     assert relerr(rew[~flip], g['rew'][~flip]) < 5e-5
     live = (g['term'] == 0) & ~flip
