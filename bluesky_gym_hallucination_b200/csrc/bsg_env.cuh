@@ -18,6 +18,12 @@ __host__ __device__ constexpr int env_obs_dim(int kind, int N) {
            : kind == BSG_KIND_SECTOR ? 31 : kind == BSG_KIND_MERGE ? 40 : 0;
 }
 
+// x / c for a literal constant c: the literal division in the fp64 parity path, a multiplication by the rounded reciprocal
+// in the fp32 fast path (one instruction instead of the IEEE division sequence; <= 1 ulp apart)
+template <typename R> __device__ __forceinline__ R divc(R x, double c) {
+    if constexpr (sizeof(R) == 8) return x / R(c); else return x * float(1.0 / c);
+}
+
 template <typename R, bool EXT = false>
 __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &a, EnvShared<R> *es, R *sdist,
                                           int le, int i, int e, int nl, bool valid, bool live, bool skip, double *ev) {
@@ -49,15 +55,15 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
                 if (live) {
                     R qdr, d;
                     env_qdrdist<R>(olat, olon, a.lat, a.lon, qdr, d);
-                    o_dist = d * R(1.852) / (kind == BSG_KIND_HORIZONTAL ? R(150) : R(200));
+                    o_dist = kind == BSG_KIND_HORIZONTAL ? divc<R>(d * R(1.852), 150) : divc<R>(d * R(1.852), 200);
                     rsincos_deg<R>(bound180<R>(ohdg - qdr), o_s, o_c);
                     R sh, ch;
                     rsincos_deg<R>(ohdg - a.hdg, sh, ch);
-                    o_x = (-ch * my_gs) / R(150);
-                    o_y = (otas - sh * my_gs) / R(150);
+                    o_x = divc<R>(-ch * my_gs, 150);
+                    o_y = divc<R>(otas - sh * my_gs, 150);
                     bool hit = d < R(5);
                     if (kind == BSG_KIND_VERTICAL) {
-                        o_da = (a.alt - es[le].own_alt) / R(3000);
+                        o_da = divc<R>(a.alt - es[le].own_alt, 3000);
                         o_z = a.vs - es[le].own_vs;
                         hit = hit && fabs(es[le].own_alt - a.alt) < R(1000 * 0.3048);
                     }
@@ -77,15 +83,15 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
                     rsincos_deg<R>(drift, sd, cd);
                     es[le].drift = drift; es[le].wdist = d * R(1.852);
                     sev[BSG_EV_AC_HDG] = (double)a.hdg;
-                    if (obs) { obs[5 * K] = d * R(1.852) / R(150); obs[5 * K + 1] = cd; obs[5 * K + 2] = sd; }
+                    if (obs) { obs[5 * K] = divc<R>(d * R(1.852), 150); obs[5 * K + 1] = cd; obs[5 * K + 2] = sd; }
                 } else {
                     R qdr, d;
                     env_qdrdist<R>(52.0, 4.0, olat, olon, qdr, d);
                     es[le].wdist = R(200) - d * R(1.852);              // runway distance
                     if (obs) {
-                        obs[0] = (a.alt - R(1500)) / R(3000); obs[1] = (a.vs - R(0)) / R(5);
-                        obs[2] = (R(sev[BSG_EV_TARGET_ALT]) - R(1500)) / R(3000);
-                        obs[3] = (es[le].wdist - R(100)) / R(200);
+                        obs[0] = divc<R>(a.alt - R(1500), 3000); obs[1] = divc<R>(a.vs - R(0), 5);
+                        obs[2] = divc<R>(R(sev[BSG_EV_TARGET_ALT]) - R(1500), 3000);
+                        obs[3] = divc<R>(es[le].wdist - R(100), 200);
                     }
                 }
             }
@@ -131,7 +137,7 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
                 rsincos_deg<R>(drift, sd, cd);
                 es[le].drift = drift;
                 if (obs) {
-                    obs[0] = cd; obs[1] = sd; obs[2] = (a.tas - R(150)) / R(6);
+                    obs[0] = cd; obs[1] = sd; obs[2] = divc<R>(a.tas - R(150), 6);
                     for (int s = (nl - 1 < 0 ? 0 : nl - 1); s < 4; s++)
                         for (int q = 0; q < 7; q++) obs[3 + q * 4 + s] = R(0);
                 }
@@ -154,10 +160,10 @@ __device__ __forceinline__ void env_layer(const StepArgs<R> &A, const AcReg<R> &
             const R vxi = ch * a.tas, vyi = sh * a.tas;
             const R trk = atan2(vyi - vy, vxi - vx);
             R *o = obs + 3;
-            o[0 * 4 + rank] = px / R(13000); o[1 * 4 + rank] = py / R(13000);
-            o[2 * 4 + rank] = (vxi - vx) / R(32); o[3 * 4 + rank] = (vyi - vy) / R(66);
+            o[0 * 4 + rank] = divc<R>(px, 13000); o[1 * 4 + rank] = divc<R>(py, 13000);
+            o[2 * 4 + rank] = divc<R>(vxi - vx, 32); o[3 * 4 + rank] = divc<R>(vyi - vy, 66);
             o[4 * 4 + rank] = cos(trk); o[5 * 4 + rank] = sin(trk);
-            o[6 * 4 + rank] = (mine - R(50000)) / R(15000);
+            o[6 * 4 + rank] = divc<R>(mine - R(50000), 15000);
         }
     }
     if (EXT && valid && kind == BSG_KIND_MERGE && live && i >= 1) {    // the 5 nearest by (distance, index)

@@ -81,7 +81,7 @@ __device__ __forceinline__ void env_qdrdist(double lata, double lona, double lat
 
 template <typename R> __device__ __forceinline__ void rsincos_deg(R deg, R &s, R &c) {
     if constexpr (sizeof(R) == 8) { s = sin(deg * kD2R); c = cos(deg * kD2R); }
-    else sincosf(deg * float(kD2R), &s, &c);
+    else sincos_deg_fast(deg, s, c);                 // (|deg| <= 720 at every call site)
 }
 
 constexpr double kCenterLat = 51.990426702297746, kCenterLon = 4.376124857109851;   // sector_cr_env.py:16
