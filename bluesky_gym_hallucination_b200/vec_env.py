@@ -41,6 +41,12 @@ def single_spaces(kind, n_ac, wind_obs=False):
     return spaces.Dict(d), act
 
 
+# default ND-map grid of the env layer: 320 x 320 km around (52 N, 4 E) in 5 km cells, 12 km of altitude in 1.5 km layers,
+# 30 look-ahead steps of 10 s
+NDMAP_DEFAULT = dict(nx=64, ny=64, nz=8, nt=30, x0=-160e3, y0=-160e3, z0=0.0, cx=5e3, cy=5e3, cz=1.5e3, dt=10.0,
+                     lat0=52.0, lon0=4.0)
+
+
 class BlueSkyVecEnv:
     """Batched env.  reset()/step() speak numpy (Gymnasium VectorEnv semantics, next-step auto-reset);
     step_tensors() keeps everything on the GPU for RL libraries that take torch tensors."""
@@ -77,10 +83,7 @@ class BlueSkyVecEnv:
         self._nd = None
         self._refresh_spaces()
         if ndmap_obs:
-            # default grid: 320 x 320 km around the env's origin in 5 km cells, 12 km of altitude in 1.5 km layers,
-            # 30 look-ahead steps of 10 s
-            nd = dict(nx=64, ny=64, nz=8, nt=30, x0=-160e3, y0=-160e3, z0=0.0, cx=5e3, cy=5e3, cz=1.5e3, dt=10.0,
-                      lat0=52.0, lon0=4.0)
+            nd = dict(NDMAP_DEFAULT)                   # the default grid, overridden key by key
             if isinstance(ndmap_obs, dict):
                 nd.update(ndmap_obs)
             self._nd, self._nd_out, self.ndmap_last = nd, None, None
@@ -147,8 +150,9 @@ class BlueSkyVecEnv:
 
     def ndmap(self, **kw):
         """ND-map (4D occupancy / conflict grid over the look-ahead trajectories) of the batch's LIVE traffic:
-        (occ u8 [E, nt, nz, ny, nx], conf bitmask, ncell [E, nt]) device tensors -- BsgCore.ndmap / bsg_ndmap_state."""
-        return self.core.ndmap(**kw)
+        (occ u8 [E, nt, nz, ny, nx], conf bitmask, ncell [E, nt]) device tensors -- BsgCore.ndmap / bsg_ndmap_state.
+        Keywords override the default grid NDMAP_DEFAULT."""
+        return self.core.ndmap(**{**NDMAP_DEFAULT, **kw})
 
     def close(self):
         if not self.closed:
