@@ -70,6 +70,7 @@ static int refresh_gs(bsg_handle *h) {
 
 // the pinned / device output block of bsg_step_host; sized by obs_dim (which bsg_set_wind can grow by two slots)
 static int alloc_out(bsg_handle *h) {
+    h->gen++;                                      // captured host-step graphs hold the old output pointers
     if (h->h_out) { cudaFreeHost(h->h_out); h->h_out = nullptr; }
     if (h->h_outs[1]) { cudaFreeHost(h->h_outs[1]); h->h_outs[1] = nullptr; }
     if (h->d_out) { cudaFree(h->d_out); h->d_out = nullptr; }
@@ -239,6 +240,7 @@ int bsg_set_wind(bsg_handle *h, int32_t npoints, const double *lat, const double
     CK(h, cudaSetDevice(h->cfg.device));
     CK(h, cudaDeviceSynchronize());
     const bool was_ext = is_ext(h);
+    h->gen++;
     memset(&h->wind, 0, sizeof(h->wind));
     h->wind.n = npoints;
     h->wind.obs = (npoints > 0 && augment_obs) ? 1 : 0;
@@ -255,6 +257,7 @@ int bsg_set_wind_profile(bsg_handle *h, double lat, double lon, int32_t nknots, 
     for (int k = 1; k < nknots; k++) if (!(alt_m[k] > alt_m[k - 1])) return BSG_ERR_ARG;     // np.interp wants increasing knots
     int rc = bsg_set_wind(h, 1, &lat, &lon, vnorth, veast, augment_obs);                    // one point: ext switch, obs slots
     if (rc != BSG_OK) return rc;
+    h->gen++;
     h->wind.nk = nknots;
     for (int k = 0; k < nknots; k++) { h->wind.kalt[k] = alt_m[k]; h->wind.vn[k] = vnorth[k]; h->wind.ve[k] = veast[k]; }
     return BSG_OK;
@@ -267,7 +270,7 @@ int bsg_set_obs_noise(bsg_handle *h, double sigma, uint64_t seed) {
         h->err = "bsg_set_obs_noise: the fp32 EXT kernels hold N <= 64 aircraft per env"; return BSG_ERR_UNSUPPORTED;
     }
     const bool was_ext = is_ext(h);
-    h->noise_sigma = sigma; h->noise_seed = seed;
+    h->noise_sigma = sigma; h->noise_seed = seed; h->gen++;
     if (!was_ext && is_ext(h)) { CK(h, cudaSetDevice(h->cfg.device)); return refresh_gs(h); }
     return BSG_OK;
 }
@@ -276,6 +279,7 @@ int bsg_destroy(bsg_handle *h) {
     if (!h) return BSG_ERR_ARG;
     cudaSetDevice(h->cfg.device);
     cudaFree(h->pos); cudaFree(h->st); cudaFree(h->reso); cudaFree(h->nac); cudaFree(h->ev); cudaFree(h->stage64);
+    for (int a = 0; a < 2; a++) for (int b = 0; b < 2; b++) if (h->hgraph[a][b]) cudaGraphExecDestroy(h->hgraph[a][b]);
     cudaFree(h->d_act); cudaFree(h->d_out); cudaFree(h->episode); cudaFree(h->done_buf[0]); cudaFree(h->done_buf[1]); cudaFree(h->nd_rec);
     if (h->h_act) cudaFreeHost(h->h_act);
     if (h->h_acts[1]) cudaFreeHost(h->h_acts[1]);

@@ -36,6 +36,11 @@ struct bsg_handle {
     int32_t *done_buf[2] = { nullptr, nullptr };      // [E] reset counter (Philox counter word)
     float *nd_rec = nullptr;          // bsg_ndmap_state: packed straight-line records of the live state [E][6][N]
     int64_t launches = 0;
+    // host-buffer step as a replayed CUDA graph (H2D copy, step kernel, D2H copy): one graph per (pinned block, auto-reset
+    // flag buffer); `gen` counts the calls that change anything a captured launch holds (wind, noise, auto-reset, outputs)
+    cudaGraphExec_t hgraph[2][2] = { { nullptr, nullptr }, { nullptr, nullptr } };
+    int64_t hgraph_gen[2][2] = { { -1, -1 }, { -1, -1 } };
+    int64_t gen = 0;
     std::string err;
 };
 

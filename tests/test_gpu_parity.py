@@ -411,6 +411,44 @@ def test_step_host_equals_step():
     c.close()
 
 
+def test_step_host_graph_replay_equals_plain_calls(monkeypatch):
+    """The host-buffer step replays a captured CUDA graph (H2D, step kernel, D2H) per pinned block and auto-reset flag
+    buffer: a run of steps with next-step auto-reset -- through re-captures forced by a configuration change, and with two
+    steps in flight -- equals the same run made of plain stream calls (BSG_HOST_GRAPH=0), bit for bit."""
+    from bluesky_gym_hallucination_b200.core import BsgCore
+    E, N = 512, 20
+    rng = np.random.default_rng(4)
+    acts = [rng.uniform(-1, 1, (E, 1)).astype(np.float32) for _ in range(14)]
+
+    def run(graph):
+        monkeypatch.setenv('BSG_HOST_GRAPH', '1' if graph else '0')
+        c = BsgCore(0, E, N, precision='fp32', asas_on=True, max_episode_steps=6, cd_outputs=False)
+        c.reset(seed=9); c.set_autoreset(True, seed=10)
+        out = []
+        for k in range(8):                                  # episodes end after 6 steps: the auto-reset flag buffers flip
+            o, r, t, tr, i = c.step_host_views(acts[k])
+            out.append((o.copy(), r.copy(), t.copy(), tr.copy(), i.copy()))
+        c.set_autoreset(True, seed=11)                      # a configuration change: the captures are stale
+        c.step_host_begin(acts[8])
+        for k in range(9, 14):                              # two steps in flight
+            c.step_host_begin(acts[k])
+            o, r, t, tr, i = c.step_host_wait()
+            out.append((o.copy(), r.copy(), t.copy(), tr.copy(), i.copy()))
+        o, r, t, tr, i = c.step_host_wait()
+        out.append((o.copy(), r.copy(), t.copy(), tr.copy(), i.copy()))
+        n = c.launch_count()
+        c.close()
+        return out, n
+
+    plain, n0 = run(False)
+    graph, n1 = run(True)
+    assert n0 == n1 and len(plain) == len(graph) == 14
+    assert any(x[3].any() for x in plain)                   # truncations happened: the reset path ran inside the run
+    for k, (a, b) in enumerate(zip(plain, graph)):
+        for u, v in zip(a, b):
+            assert np.array_equal(u, v, equal_nan=True), f"step {k}"
+
+
 def test_step_host_direct_mode_equals_copy_mode(monkeypatch):
     """bsg_step_host in direct mode (the kernel reads the actions from / stores the results to the pinned host block,
     default for many-wave launches) returns the same bits as the copy mode, over several steps."""
