@@ -352,7 +352,7 @@ def run_envs(ctx, workload, K, W, strong=False, envs=0, cpu=False):
                      "hbm_peak_gbs": load_peaks().get("hbm_gbs")},
         "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(act_dim * E * 4),
                 "d2h_bytes_per_step": int(E * (obs_dim + 5) * 4 + E * 8), "steps": Ke,
-                "api": "bsg_step_host + bsg_host_views (host actions -> pinned H2D, one launch, D2H of obs/reward/info/flags into pinned host memory read in place)",
+                "api": "bsg_step_host + bsg_host_views (host actions -> pinned block, read by the kernel over PCIe; one launch; D2H of obs/reward/info/flags into pinned host memory read in place; the launch + copy replayed as one CUDA graph)",
                 "two_steps_in_flight": {"value": e2e_pipe, "unit": "env-steps/s",
                                         "api": "bsg_step_host_begin / bsg_step_host_wait, same copies per step; reported extra (the headline e2e is the synchronous loop)"}},
         "gpu_launches": int(launches), "clocks": clocks, "wall_s_timed_region": t_wall,

@@ -196,6 +196,11 @@ int bsg_step_host_begin(bsg_handle *h, const void *actions) {
     // (pinned block, auto-reset flag buffer) and replayed as ONE graph launch -- less host work per step, no gaps between
     // the three on the device.  Anything that changes what a captured launch holds bumps h->gen and forces a re-capture.
     // (Not with observation noise: its Philox counter is a kernel argument that changes every launch.)
+    // the actions (4-8 bytes per env) are read by the kernel straight from the pinned block (unified addressing) instead of
+    // a host-to-device copy node in front of it: e2e +3.2 % on C2 (profiles/ab_r2_host_graph.log); BSG_HOST_ACT_DIRECT=0/1
+    const char *ad_env = getenv("BSG_HOST_ACT_DIRECT");
+    const bool act_dir = dir || (ad_env ? atoi(ad_env) != 0 : true);
+    if ((int)act_dir != h->act_dir_last) { h->act_dir_last = (int)act_dir; h->gen++; }       // (captured graphs hold the choice)
     const bool ar_next = h->autoreset == 1 && g.env_kind != BSG_KIND_RAW;
     // Measured (profiles/ab_r2_host_graph.log): e2e +3.2 % on C2, +2.4 % on the Vertical batch, -5 % on the Merge (EXT)
     // kernels -- so the plain instantiations replay a graph and the EXT ones keep the three calls (BSG_HOST_GRAPH=0/1 overrides)
@@ -216,7 +221,7 @@ int bsg_step_host_begin(bsg_handle *h, const void *actions) {
         // (the kernel's shared-memory attribute is set by its first plain launch: capture only once the handle has stepped)
         capturing = h->launches > 0 && cudaStreamBeginCapture(h->hs, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
     }
-    if (!dir) CK(h, cudaMemcpyAsync(h->d_act, h->h_acts[q], h->act_bytes, cudaMemcpyHostToDevice, h->hs));
+    if (!act_dir) CK(h, cudaMemcpyAsync(h->d_act, h->h_acts[q], h->act_bytes, cudaMemcpyHostToDevice, h->hs));
     char *d = (char *)(dir ? h->h_outs[q] : h->d_out);
     bsg_step_out o;
     memset(&o, 0, sizeof(o));
@@ -225,7 +230,7 @@ int bsg_step_host_begin(bsg_handle *h, const void *actions) {
     o.info = d; d += E * 4 * rs;
     o.terminated = (int32_t *)d; d += E * sizeof(int32_t);
     o.truncated = (int32_t *)d;
-    const void *act = dir ? h->h_acts[q] : h->d_act;
+    const void *act = act_dir ? h->h_acts[q] : h->d_act;
     int rc = g.precision == BSG_FP64 ? launch_step<double>(h, act, &o, g.substeps, 0, h->hs)
                                      : launch_step<float>(h, act, &o, g.substeps, 0, h->hs);
     if (rc != BSG_OK) { if (capturing) { cudaGraph_t gr; cudaStreamEndCapture(h->hs, &gr); } return rc; }

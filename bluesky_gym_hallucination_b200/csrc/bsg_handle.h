@@ -41,6 +41,7 @@ struct bsg_handle {
     cudaGraphExec_t hgraph[2][2] = { { nullptr, nullptr }, { nullptr, nullptr } };
     int64_t hgraph_gen[2][2] = { { -1, -1 }, { -1, -1 } };
     int64_t gen = 0;
+    int act_dir_last = -1;
     std::string err;
 };
 
