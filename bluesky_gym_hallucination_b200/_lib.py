@@ -86,6 +86,8 @@ SYMBOLS = {
     'bsg_host_views': (_I, [_VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_step_host_begin': (_I, [_VP, _VP]),
     'bsg_step_host_wait': (_I, [_VP, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_step_host_block': (_I, [_VP, _VP]),
+    'bsg_step_host_wait_block': (_I, [_VP]),
     'bsg_cd_pack': (_I, [C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP, _VP]),
     'bsg_cd_pack_init': (_I, [C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP, C.c_double, C.c_double, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sweep': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),

@@ -80,6 +80,8 @@ class BsgCore:
         """(Re)allocate the caller-owned output tensors; obs_dim follows bsg_set_wind(augment_obs)."""
         cd_outputs = self._cd_outputs
         self._views = None
+        self._blocks = [None, None]                     # numpy views of the two pinned host blocks (re-made with the outputs)
+        self.__dict__.pop('_view_cache', None)
         self.obs_dim = self.lib.bsg_obs_dim(self.h)
         self.act_dim = self.lib.bsg_act_dim(self.h)
         E, N, dev, rd = self.E, self.N, self.device, self.rdtype
@@ -224,19 +226,26 @@ class BsgCore:
     def step_host_wait(self):
         """Wait for the oldest step begun; returns (obs, reward, terminated, truncated, info) views of its pinned block
         (valid until two more begins)."""
-        p = [C.c_void_p() for _ in range(5)]
-        L.check(self.lib.bsg_step_host_wait(self.h, *[C.byref(x) for x in p]), self.h)
-        key = p[0].value
-        cache = self.__dict__.setdefault('_view_cache', {})
-        if key not in cache:
-            cache[key] = self._views_of(p)
-        return cache[key]
+        return self._block_views(self.lib.bsg_step_host_wait_block(self.h))
+
+    def _block_views(self, q):
+        """views of pinned block q (the value bsg_step_host_block / _wait_block returned), built once per block"""
+        if q < 0:
+            L.check(q, self.h)
+        v = self._blocks[q]
+        if v is None:                                   # the block just filled is the one bsg_host_views describes
+            p = [C.c_void_p() for _ in range(5)]
+            L.check(self.lib.bsg_host_views(self.h, *[C.byref(x) for x in p]), self.h)
+            v = self._blocks[q] = self._views_of(p)
+        return v
 
     def step_host_views(self, actions):
         """End-to-end call with a HOST action array; results are returned as views of the pinned block
         (no second host copy): H2D actions + kernel + D2H obs/reward/flags/info inside."""
-        L.check(self.lib.bsg_step_host(self.h, _ptr(actions), None, None, None, None, None), self.h)
-        return self.host_views()
+        # one ctypes call without pointer marshalling: the C side returns which of the two pinned blocks it filled
+        if not (isinstance(actions, np.ndarray) and actions.dtype == self.npdtype and actions.flags.c_contiguous):
+            actions = np.ascontiguousarray(np.asarray(actions), dtype=self.npdtype)
+        return self._block_views(self.lib.bsg_step_host_block(self.h, actions.ctypes.data))
 
     def ndmap(self, nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=0.0, cx=1.0, cy=1.0, cz=1.0, dt=10.0, lat0=52.0, lon0=4.0,
               out=None, want_rec=False):

@@ -260,6 +260,23 @@ int bsg_step_host_wait(bsg_handle *h, void **obs, void **reward, void **info, in
     return BSG_OK;
 }
 
+// begin + wait in one call; returns the index (0 / 1) of the pinned block that holds the results, or a negative status.
+// For bindings whose per-call overhead matters (ctypes): no pointer arguments to marshal, the views of the two blocks are
+// built once from bsg_host_views.
+int bsg_step_host_block(bsg_handle *h, const void *actions) {
+    if (!h || !actions) return BSG_ERR_ARG;
+    if (h->h_pending) { h->err = "bsg_step_host_block: steps begun with bsg_step_host_begin are still in flight"; return BSG_ERR_ARG; }
+    int rc = bsg_step_host_begin(h, actions);
+    if (rc != BSG_OK) return rc;
+    rc = bsg_step_host_wait(h, nullptr, nullptr, nullptr, nullptr, nullptr);
+    return rc != BSG_OK ? rc : h->h_last;
+}
+// bsg_step_host_wait that returns the block index instead of five pointers
+int bsg_step_host_wait_block(bsg_handle *h) {
+    const int rc = bsg_step_host_wait(h, nullptr, nullptr, nullptr, nullptr, nullptr);
+    return rc != BSG_OK ? rc : h->h_last;
+}
+
 int bsg_step_host(bsg_handle *h, const void *actions, void *obs, void *reward, int32_t *term, int32_t *trunc, void *info) {
     if (!h || !actions) return BSG_ERR_ARG;
     if (h->h_pending) { h->err = "bsg_step_host: steps begun with bsg_step_host_begin are still in flight"; return BSG_ERR_ARG; }

@@ -184,6 +184,11 @@ int bsg_step_host(bsg_handle *h, const void *actions_host, void *obs_host, void 
  * most two steps may be in flight per handle; bsg_step_host = begin + wait + the optional copies. */
 int bsg_step_host_begin(bsg_handle *h, const void *actions_host);
 int bsg_step_host_wait(bsg_handle *h, void **obs, void **reward, void **info, int32_t **terminated, int32_t **truncated);
+/* The same two calls for bindings whose per-call marshalling matters (ctypes): bsg_step_host_block = begin + wait, both
+ * return the index (0 or 1) of the pinned block that holds the step's results (the pointers of a block are constant
+ * between changes of the observation size: ask bsg_host_views once per block), or a negative bsg_status. */
+int bsg_step_host_block(bsg_handle *h, const void *actions_host);
+int bsg_step_host_wait_block(bsg_handle *h);
 
 /* pack fp32 CD records (8 floats per aircraft) from SoA device arrays [E][N]; origin = (lat0, lon0) degrees */
 int bsg_cd_pack(int32_t num_envs, int32_t num_ac, const double *lat_dev, const double *lon_dev,
