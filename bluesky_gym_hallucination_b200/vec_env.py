@@ -54,12 +54,15 @@ class BlueSkyVecEnv:
 
     def __init__(self, env_id, num_envs, num_aircraft=None, device=0, precision='fp32', asas=False, mvp=False,
                  seed=0, cd_outputs=False, max_episode_steps=None, wind=None, wind_obs=False, obs_noise=0.0,
-                 ac_density_mode='normal', fixed_nac=False, ndmap_obs=None):
+                 ac_density_mode='normal', fixed_nac=False, ndmap_obs=None, obs_dtype=np.float64):
         """wind = (lat, lon, vnorth, veast) like WindFieldWrapper(env, lat, lon, vnorth, veast, augment_obs=wind_obs);
         obs_noise = NoisyObservationWrapper(env, noise_level); ac_density_mode = SectorCREnv's "normal" | "uniform"
         (sector_cr_env.py:45,98-103); fixed_nac = every aircraft slot live (the synthetic scale-up configs).
         mvp = True | 'horizontal' (BlueSky's default resolution method, heading + speed) | 'vertical' (RMETHV V/S) |
         'both' (horizontal + vertical): ASAS ON + RESO MVP for the intruders, RESOOFF for the agent.
+        obs_dtype = np.float64 (the reference's declared dtype: every step converts the batch) | np.float32 with the fp32
+        core: the observation dict holds VIEWS of the pinned host block the step filled -- no conversion, no copy; valid
+        until the second next step.
         ndmap_obs = True | dict of BsgCore.ndmap keywords: every reset / step also builds the ND-map (4D conflict grid over
         the look-ahead trajectories) of the live traffic and appends the observation key 'ndmap_conflict_cells' [nt]: the
         share of grid cells in conflict at each look-ahead step (the map itself stays on the device: ndmap_last)."""
@@ -81,6 +84,9 @@ class BlueSkyVecEnv:
             self.core.set_obs_noise(obs_noise, seed=int(seed) + 0x5EED)
         self._seed = int(seed)
         self._nd = None
+        self._obs_dtype = np.dtype(obs_dtype)
+        if self._obs_dtype not in (np.dtype(np.float64), np.dtype(np.float32)):
+            raise ValueError("obs_dtype must be float64 or float32")
         self._refresh_spaces()
         if ndmap_obs:
             nd = dict(NDMAP_DEFAULT)                   # the default grid, overridden key by key
@@ -96,21 +102,23 @@ class BlueSkyVecEnv:
         """observation / action spaces and the slices of the flat observation (again after a wrapper added wind slots)"""
         wind_obs = self.core.wind_obs
         self.single_observation_space, self.single_action_space = single_spaces(self.kind, self.num_aircraft, wind_obs)
+        d = dict(self.single_observation_space.spaces)
+        if self._obs_dtype != np.dtype(np.float64):     # same keys and shapes, the dtype the caller asked for
+            d = {k: spaces.Box(b.low, b.high, shape=b.shape, dtype=self._obs_dtype.type) for k, b in d.items()}
         if self._nd is not None:
-            d = dict(self.single_observation_space.spaces)
-            d['ndmap_conflict_cells'] = spaces.Box(0.0, 1.0, shape=(self._nd['nt'],), dtype=np.float64)
-            self.single_observation_space = spaces.Dict(d)
+            d['ndmap_conflict_cells'] = spaces.Box(0.0, 1.0, shape=(self._nd['nt'],), dtype=self._obs_dtype.type)
+        self.single_observation_space = spaces.Dict(d)
         self.observation_space, self.action_space = self.single_observation_space, self.single_action_space
         self._slices = obs_slices(self.kind, self.num_aircraft, wind_obs)
 
     # ------------------------------------------------------------------ Gymnasium VectorEnv API
     def _obs_dict(self, flat):
-        flat = np.asarray(flat, dtype=np.float64)
+        flat = np.asarray(flat, dtype=self._obs_dtype)          # float32 from the fp32 core: a view, not a copy
         d = {k: flat[:, a:b] for k, a, b in self._slices}
         if self._nd is not None:      # the ND-map of the state this observation describes, consumed as an observation key
             self._nd_out = self.core.ndmap(out=self._nd_out, **self._nd)
             self.ndmap_last = self._nd_out
-            d['ndmap_conflict_cells'] = self._nd_out[2].cpu().numpy().astype(np.float64) / self._nd_cells
+            d['ndmap_conflict_cells'] = self._nd_out[2].cpu().numpy().astype(self._obs_dtype) / self._obs_dtype.type(self._nd_cells)
         return d
 
     def _infos(self, info):

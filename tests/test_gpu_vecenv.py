@@ -249,3 +249,27 @@ def test_ndmap_is_consumed_as_an_observation_key():
     assert o['ndmap_conflict_cells'].shape == (12,)
     env.close()
 
+
+def test_float32_observations_are_views_of_the_pinned_block():
+    """obs_dtype=float32: same keys, shapes and values as the float64 dict, declared float32, and no copy -- the arrays
+    are views of the pinned host block the step filled."""
+    from bluesky_gym_hallucination_b200 import BlueSkyVecEnv
+    E = 64
+    v64 = BlueSkyVecEnv('HorizontalCREnv-v0', E, num_aircraft=20, asas=True, seed=3)
+    v32 = BlueSkyVecEnv('HorizontalCREnv-v0', E, num_aircraft=20, asas=True, seed=3, obs_dtype=np.float32)
+    assert all(b.dtype == np.float32 for b in v32.single_observation_space.spaces.values())
+    o64, _ = v64.reset(seed=3); o32, _ = v32.reset(seed=3)
+    rng = np.random.default_rng(0)
+    for _ in range(3):
+        a = rng.uniform(-1, 1, (E, 1))
+        o64, r64, t64, tr64, i64 = v64.step(a)
+        o32, r32, t32, tr32, i32 = v32.step(a)
+    assert set(o32) == set(o64)
+    views = [b for b in v32.core._blocks if b is not None]
+    for k in o64:
+        assert o32[k].dtype == np.float32 and o32[k].shape == o64[k].shape
+        assert np.array_equal(o32[k].astype(np.float64), o64[k], equal_nan=True)
+        assert any(np.shares_memory(o32[k], blk[0]) for blk in views), k      # a view, not a copy
+    assert np.array_equal(r32, r64) and np.array_equal(t32, t64)
+    v64.close(); v32.close()
+
