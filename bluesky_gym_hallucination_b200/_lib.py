@@ -42,6 +42,8 @@ class CdParams(C.Structure):
 
 
 MAX_PEERS = 8
+CD_STATIC_MAX_ROWS = 1 << 18     # BSG_CD_STATIC_MAX_ROWS
+ERR_TOOLARGE = -6
 
 
 class CdPeers(C.Structure):
@@ -93,6 +95,7 @@ SYMBOLS = {
     'bsg_cd_sweep': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_init': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_sweep': (_I, [C.POINTER(CdParams), _VP, C.c_int32, C.c_int32, _VP, _VP, _VP, _VP, _VP]),
+    'bsg_cd_sym_static': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_sweep_peers': (_I, [C.POINTER(CdParams), C.POINTER(CdPeers), C.c_int32, C.c_int32, _VP]),
     'bsg_cd_sym_finalize_peers': (_I, [C.POINTER(CdParams), C.POINTER(CdPeers), C.c_int32, _VP, _VP, _VP, _VP, _VP, _VP]),
     'bsg_cd_sym_finalize': (_I, [C.POINTER(CdParams), _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP, _VP]),

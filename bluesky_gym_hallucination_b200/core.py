@@ -336,6 +336,21 @@ def cd_sweep_sym(rec, rpz_m=5 * 1852.0, hpz_m=1000 * 0.3048, dtlookahead=300.0, 
     return out
 
 
+def cd_sweep_sym_static(rec, out, rpz_m=5 * 1852.0, hpz_m=1000 * 0.3048, dtlookahead=300.0):
+    """bsg_cd_sym_static: the symmetric sweep for a host that must not allocate GPU memory (memory handed to a pool,
+    fixed-rate tick, binding without an allocator -- include/bsgcore.h).  `out` is the caller's dict of output tensors
+    (cd_sweep's keys, [E,N]; a missing key is not written); the row accumulators live in an array inside the library, so
+    E * N <= _lib.CD_STATIC_MAX_ROWS and calls on one GPU must not overlap.  Same results as cd_sweep, bit for bit."""
+    lib = L.load()
+    E, N, _ = rec.shape
+    p = L.CdParams(E, N, 0, N, rpz_m, hpz_m, dtlookahead, 0)
+    s = C.c_void_p(torch.cuda.current_stream(rec.device).cuda_stream)
+    with torch.cuda.device(rec.device):
+        L.check(lib.bsg_cd_sym_static(C.byref(p), _ptr(rec), *[_ptr(out[k]) if k in out else None for k in
+                                      ('inconf', 'nconf', 'nlos', 'near_idx', 'near_tcpa', 'near_dcpa', 'near_tin', 'tcpamax')], s))
+    return out
+
+
 def ndmap(rec, nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=0.0, cx=1.0, cy=1.0, cz=1.0, dt=10.0, out=None):
     """rec: [E,6,n] f32 CUDA (x,y,z,u,v,w).  Returns occ u8 [E,nt,nz,ny,nx], conf_bits u8 [E,nt,nz*ny*nx/8] (1 bit per
     cell: cell c of a slab <-> bit c & 7 of byte c >> 3; ndmap_unpack gives the dense 0/1 bytes), ncell i32 [E,nt]."""

@@ -94,6 +94,7 @@ const char *bsg_status_string(int s) {
         case BSG_ERR_NOMEM: return "out of memory";
         case BSG_ERR_UNSUPPORTED: return "unsupported configuration";
         case BSG_ERR_NODEVICE: return "no CUDA device";
+        case BSG_ERR_TOOLARGE: return "more rows than the built-in scratch array holds (BSG_CD_STATIC_MAX_ROWS); use bsg_cd_sym_init/_sweep/_finalize with your own buffers";
         default: return "unknown status";
     }
 }

@@ -460,3 +460,90 @@ int bsg_cd_sym_finalize(const bsg_cd_params *p, const float *rec, const int32_t 
 }
 
 }  // extern "C"
+
+// ---------------------------------------------------------------------------------------------------------------
+// bsg_cd_sym_static: the symmetric sweep for callers that must not allocate (declaration + rationale: bsgcore.h).
+// The sweep's row accumulators -- the packed (tCPA, intruder) minimum key, the conflict and loss-of-separation counts
+// and the tCPA maximum, 20 bytes per aircraft row -- are global-memory scratch that bsg_cd_sym_init / _sweep / _finalize
+// take from the caller.  Here they live in ONE file-scope device array instead: 5.25 MB that every GPU this library is
+// loaded on holds until the process exits, shared by every call (calls that overlap on the GPU race on it).
+// Host code may not hand `bsg_static_scratch` to a kernel: in host code that name is only the host-side handle of the
+// symbol.  The device address is looked up once per device with cudaGetSymbolAddress, with that device current.
+static __device__ __align__(256) unsigned char bsg_static_scratch[(size_t)BSG_CD_STATIC_MAX_ROWS * 20 + 4 * 256];
+
+namespace {
+
+constexpr int kStaticMaxDev = 64;
+unsigned char *g_static_addr[kStaticMaxDev] = {};      // device address of bsg_static_scratch, per device ordinal
+int g_static_lock = 0;                                  // spin lock around the table (first call per device only)
+
+// Device address of the scratch array on the CURRENT device.  The first call on a device resolves the symbol (which
+// also makes the CUDA runtime load this module onto that device); later calls read the table.
+int static_scratch_addr(int dev, unsigned char **out) {
+    if (dev < 0 || dev >= kStaticMaxDev) return BSG_ERR_UNSUPPORTED;
+    unsigned char *a = __atomic_load_n(&g_static_addr[dev], __ATOMIC_ACQUIRE);
+    if (!a) {
+        while (__atomic_exchange_n(&g_static_lock, 1, __ATOMIC_ACQUIRE)) {}
+        a = g_static_addr[dev];
+        cudaError_t e = cudaSuccess;
+        if (!a) {
+            void *sym = nullptr;
+            e = cudaGetSymbolAddress(&sym, bsg_static_scratch);
+            if (e == cudaSuccess && sym) {
+                a = static_cast<unsigned char *>(sym);
+                __atomic_store_n(&g_static_addr[dev], a, __ATOMIC_RELEASE);
+            }
+        }
+        __atomic_store_n(&g_static_lock, 0, __ATOMIC_RELEASE);
+        if (e != cudaSuccess || !a) return BSG_ERR_CUDA;
+    }
+    *out = a;
+    return BSG_OK;
+}
+
+// counts and tCPA maximum of the rows: scratch -> the caller's outputs (the ordered sweep writes them itself)
+__global__ void cd_static_export_kernel(size_t n, const int32_t *__restrict__ s_nconf, const int32_t *__restrict__ s_nlos,
+                                        const int32_t *__restrict__ s_tmax, int32_t *nconf, int32_t *nlos, float *tcpamax) {
+    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    if (nconf) nconf[k] = s_nconf[k];
+    if (nlos) nlos[k] = s_nlos[k];
+    if (tcpamax) tcpamax[k] = __int_as_float(s_tmax[k]);
+}
+
+}  // namespace
+
+extern "C" int bsg_cd_sym_static(const bsg_cd_params *p, const float *rec, uint8_t *inconf, int32_t *nconf, int32_t *nlos,
+                                 int32_t *near_idx, float *near_tcpa, float *near_dcpa, float *near_tin, float *tcpamax,
+                                 void *stream) {
+    if (!p || !rec || p->num_envs < 1 || p->num_ac < 1) return BSG_ERR_ARG;
+    const size_t n = (size_t)p->num_envs * (size_t)p->num_ac;
+    if (n > (size_t)BSG_CD_STATIC_MAX_ROWS) return BSG_ERR_TOOLARGE;      // nothing was launched, nothing was touched
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess) return BSG_ERR_CUDA;
+    // the records must live on the device whose copy of the scratch array the kernels will use (the current one)
+    cudaPointerAttributes at;
+    if (cudaPointerGetAttributes(&at, rec) != cudaSuccess) { cudaGetLastError(); return BSG_ERR_ARG; }
+    if (at.type == cudaMemoryTypeUnregistered || (at.type == cudaMemoryTypeDevice && at.device != dev)) return BSG_ERR_ARG;
+    unsigned char *base = nullptr;
+    if (int rc = static_scratch_addr(dev, &base)) return rc;
+    // carve the array: key (8 B / row), then nconf, nlos, tcpamax bits (4 B / row each), every part 256-byte aligned
+    const size_t r8 = (n * 8 + 255) & ~(size_t)255, r4 = (n * 4 + 255) & ~(size_t)255;
+    int64_t *s_key = reinterpret_cast<int64_t *>(base);
+    int32_t *s_nconf = reinterpret_cast<int32_t *>(base + r8);
+    int32_t *s_nlos = reinterpret_cast<int32_t *>(base + r8 + r4);
+    int32_t *s_tmax = reinterpret_cast<int32_t *>(base + r8 + 2 * r4);
+    // the array keeps whatever the last call left in it: the init stage rewrites every row this call reads
+    int rc = bsg_cd_sym_init(p, s_nconf, s_nlos, reinterpret_cast<float *>(s_tmax), s_key, stream);
+    if (rc) return rc;
+    rc = bsg_cd_sym_sweep(p, rec, 0, 1, s_nconf, s_nlos, reinterpret_cast<float *>(s_tmax), s_key, stream);
+    if (rc) return rc;
+    rc = bsg_cd_sym_finalize(p, rec, s_nconf, s_key, inconf, near_idx, near_tcpa, near_dcpa, near_tin, stream);
+    if (rc) return rc;
+    if (nconf || nlos || tcpamax) {
+        cd_static_export_kernel<<<(unsigned)((n + 255) / 256), 256, 0, (cudaStream_t)stream>>>(n, s_nconf, s_nlos, s_tmax,
+                                                                                               nconf, nlos, tcpamax);
+        if (cudaGetLastError() != cudaSuccess) return BSG_ERR_CUDA;
+    }
+    return BSG_OK;
+}

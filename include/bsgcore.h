@@ -36,7 +36,8 @@ extern "C" {
 #define BSG_ABI_VERSION 4
 
 typedef enum { BSG_OK = 0, BSG_ERR_ARG = -1, BSG_ERR_CUDA = -2, BSG_ERR_NOMEM = -3, BSG_ERR_UNSUPPORTED = -4,
-               BSG_ERR_NODEVICE = -5 } bsg_status;
+               BSG_ERR_NODEVICE = -5,
+               BSG_ERR_TOOLARGE = -6 /* bsg_cd_sym_static only: more rows than the library's built-in scratch holds */ } bsg_status;
 enum { BSG_KIND_HORIZONTAL = 0, BSG_KIND_VERTICAL = 1, BSG_KIND_SECTOR = 2, BSG_KIND_RAW = 3,
        BSG_KIND_MERGE = 4 /* MergeEnv-v0: bluesky_gym/envs/merge_env.py (20 aircraft, intruders on an LNAV route) */ };
 enum { BSG_FP32 = 0, BSG_FP64 = 1 };
@@ -215,6 +216,37 @@ int bsg_cd_sym_sweep(const bsg_cd_params *p, const float *rec_dev, int32_t tile_
 int bsg_cd_sym_finalize(const bsg_cd_params *p, const float *rec_dev, const int32_t *nconf_dev, const int64_t *key_dev,
                         uint8_t *inconf_dev, int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev,
                         float *near_tin_dev, void *stream);
+
+/* No counterpart in the reference (nor in BlueSky): this entry point exists for hosts that may not allocate GPU memory.
+ * The three-stage sweep above needs four accumulator arrays from its caller (nconf, nlos, tcpamax and the int64 key,
+ * 20 bytes per aircraft row).  Some users of this library cannot provide them:
+ *   - a trainer or simulator that gave all of the GPU's memory to its own pool at start-up (torch's caching allocator, a
+ *     fixed arena): a cudaMalloc made behind the pool's back fails although the pool has room, and a plain C caller
+ *     has no way to borrow from the pool;
+ *   - a conflict-detection call inside a fixed-rate tick: cudaMalloc / cudaFree stall the whole device for a time
+ *     nobody bounds, which a per-step budget cannot absorb;
+ *   - a binding (the ctypes stub of INTEGRATION.md, a C plugin) that is handed the record and output buffers by its
+ *     host and owns no device allocator of its own.
+ * bsg_cd_sym_static is bsg_cd_sym_init + bsg_cd_sym_sweep + bsg_cd_sym_finalize in one call, with the accumulators in
+ * a device array compiled into the library.  Inputs and outputs are bsg_cd_sweep's (all rows; row0 / row1 are ignored;
+ * any output pointer may be NULL) and the results are bit-identical to it.  The call itself allocates nothing: no
+ * cudaMalloc, no cudaFree, no allocating library routine.
+ *   Limit: num_envs * num_ac <= BSG_CD_STATIC_MAX_ROWS (262 144 rows; the giant-airspace config is 160 000).  The array
+ * costs 5.25 MB on EVERY GPU that loads the library, from load until the process exits, used or not.  A larger problem
+ * is refused with BSG_ERR_TOOLARGE before anything is launched -- use the three-stage calls with your own buffers.
+ *   First call on a device: it looks the array's device address up (cudaGetSymbolAddress), once per device, and that
+ * is also the moment the CUDA runtime loads the library's code onto that device.  Make that first call during your
+ * start-up, outside any stream capture; later calls only launch kernels on `stream`.
+ *   The device that is current when you call is the one whose array is used: rec_dev and the outputs must live there
+ * (a record pointer of another device is refused with BSG_ERR_ARG).
+ *   One array per GPU, shared by every call in the process: it still holds the previous call's values when the next one
+ * starts (each call re-initialises the rows it reads, you never see stale data), and two calls whose kernels overlap
+ * on the GPU -- different streams, different host threads -- race on it and corrupt each other's results.  Keep the
+ * calls of one GPU on one stream, or order them with events. */
+#define BSG_CD_STATIC_MAX_ROWS (1 << 18)
+int bsg_cd_sym_static(const bsg_cd_params *p, const float *rec_dev, uint8_t *inconf_dev, int32_t *nconf_dev,
+                      int32_t *nlos_dev, int32_t *near_idx_dev, float *near_tcpa_dev, float *near_dcpa_dev,
+                      float *near_tin_dev, float *tcpamax_dev, void *stream);
 
 /* The same symmetric sweep over PEER memory (one process per GPU, NVLink): aircraft j of every env lives on rank
  * j / rows_per_rank; rec / nconf / nlos / tcpamax / key [g] are device pointers to rank g's [E][rows_per_rank] buffers
