@@ -223,6 +223,7 @@ int bsg_create(const bsg_config *c, bsg_handle **out) {
     CK(h, cudaMallocHost(&h->h_acts[1], h->act_bytes));
     h->h_acts[0] = h->h_act;
     for (int q = 0; q < 2; q++) CK(h, cudaEventCreateWithFlags(&h->hev[q], cudaEventDisableTiming));
+    CK(h, cudaEventCreateWithFlags(&h->nd_ev, cudaEventDisableTiming));
     CK(h, cudaMalloc(&h->d_act, h->act_bytes));
     { int rc = alloc_out(h); if (rc != BSG_OK) return rc; }
     CK(h, cudaStreamCreateWithFlags(&h->hs, cudaStreamNonBlocking));
@@ -286,6 +287,7 @@ int bsg_destroy(bsg_handle *h) {
     if (h->h_acts[1]) cudaFreeHost(h->h_acts[1]);
     if (h->h_outs[1]) cudaFreeHost(h->h_outs[1]);
     for (int q = 0; q < 2; q++) if (h->hev[q]) cudaEventDestroy(h->hev[q]);
+    if (h->nd_ev) cudaEventDestroy(h->nd_ev);
     if (h->h_out) cudaFreeHost(h->h_out);
     if (h->hs) cudaStreamDestroy(h->hs);
     delete h;

@@ -18,7 +18,7 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
     A.skip = (ar && h->autoreset == 1) ? h->done_buf[h->flip] : nullptr;
     // next-step mode: the reset of the envs that ended in the previous step is fused into this launch
     A.fuse_reset = (A.skip != nullptr) ? 1 : 0; A.fixed_nac = g.fixed_nac; A.density_mode = g.density_mode; A.RC = h->rc; A.ar_seed = h->ar_seed; A.episode = h->episode;
-    A.W = h->wind; A.noise_sigma = (R)h->noise_sigma; A.noise_seed = h->noise_seed; A.noise_ctr = (unsigned int)h->launches;
+    A.W = h->wind; A.noise_sigma = (R)h->noise_sigma; A.noise_seed = h->noise_seed; A.noise_ctr = (unsigned int)h->noise_steps;
     // EXT instantiations: Merge env, wind field, observation noise (fp32: the symmetric sweep only, N <= 64)
     const bool ext = is_ext(h);
     int32_t *done_now = nullptr;
@@ -34,7 +34,7 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
         if (ext) {
             if (g.max_ac > 64) { h->err = "EXT kernels (fp32): N <= 64"; return BSG_ERR_UNSUPPORTED; }
             if (reso && g.reso_mode != 0) { h->err = "EXT kernels (fp32): horizontal resolution method only (reso_mode 0)"; return BSG_ERR_UNSUPPORTED; }
-            le = launch_step_f32_ext(h->tpb, reso, gd, bd, h->smem, s, A);
+            le = launch_step_f32_ext(h->tpb, reso, gd, bd, h->smem, s, g.device, A);
         } else {
             // symmetric half-ring sweep (fp32 fast path); the resolution methods with a vertical term run the ordered sweep
             const bool sym = g.max_ac <= 64 && !getenv("BSG_NO_SYM") && !(reso && g.reso_mode != 0);
@@ -42,17 +42,17 @@ static int launch_step(bsg_handle *h, const void *actions, const bsg_step_out *o
                 // detection only: the one-wave shape picked at creation (whole warps balanced over the SMs)
                 A.epb = h->wepb; A.nbuf = h->wnbuf;
                 const dim3 wg((g.num_envs + h->wepb - 1) / h->wepb), wb(((h->wepb * g.max_ac + 31) / 32) * 32);
-                le = launch_step_f32(640, false, true, wg, wb, h->wsmem, s, A);
-            } else le = launch_step_f32(h->tpb, reso, sym, gd, bd, h->smem, s, A);
+                le = launch_step_f32(640, false, true, wg, wb, h->wsmem, s, g.device, A);
+            } else le = launch_step_f32(h->tpb, reso, sym, gd, bd, h->smem, s, g.device, A);
         }
-    } else le = launch_step_f64(h->tpb, reso, ext, gd, bd, h->smem, s, A);
+    } else le = launch_step_f64(h->tpb, reso, ext, gd, bd, h->smem, s, g.device, A);
     if (le == cudaErrorInvalidValue && h->tpb != 128 && h->tpb != 256) { h->err = "step kernel: CTA of 128 or 256 threads"; return BSG_ERR_UNSUPPORTED; }
-    h->launches++;
+    h->launches++; h->noise_steps++;
     CK(h, le);
     if (ar) {
         h->flip ^= 1;
         if (h->autoreset == 2) {                       // same-step mode: reset now (separate masked launch)
-            int rc = bsg_reset(h, done_now, h->ar_seed, (void *)s);
+            int rc = bsg_reset_impl(h, done_now, h->ar_seed, (void *)s, true);
             if (rc != BSG_OK) return rc;
         }
     }
@@ -209,7 +209,7 @@ int bsg_step_host_begin(bsg_handle *h, const void *actions) {
     const int fk = ar_next ? h->flip : 0;
     if (use_graph && h->hgraph[q][fk] && h->hgraph_gen[q][fk] == h->gen) {
         CK(h, cudaGraphLaunch(h->hgraph[q][fk], h->hs));
-        h->launches++;
+        h->launches++; h->noise_steps++;
         if (ar_next) h->flip ^= 1;                             // what launch_step does on the host side of a step
         CK(h, cudaEventRecord(h->hev[q], h->hs));
         h->h_head = q ^ 1; h->h_pending++;
@@ -221,30 +221,45 @@ int bsg_step_host_begin(bsg_handle *h, const void *actions) {
         // (the kernel's shared-memory attribute is set by its first plain launch: capture only once the handle has stepped)
         capturing = h->launches > 0 && cudaStreamBeginCapture(h->hs, cudaStreamCaptureModeThreadLocal) == cudaSuccess;
     }
-    if (!act_dir) CK(h, cudaMemcpyAsync(h->d_act, h->h_acts[q], h->act_bytes, cudaMemcpyHostToDevice, h->hs));
-    char *d = (char *)(dir ? h->h_outs[q] : h->d_out);
-    bsg_step_out o;
-    memset(&o, 0, sizeof(o));
-    o.obs = d; d += E * h->obs_dim * rs;
-    o.reward = d; d += E * rs;
-    o.info = d; d += E * 4 * rs;
-    o.terminated = (int32_t *)d; d += E * sizeof(int32_t);
-    o.truncated = (int32_t *)d;
-    const void *act = act_dir ? h->h_acts[q] : h->d_act;
-    int rc = g.precision == BSG_FP64 ? launch_step<double>(h, act, &o, g.substeps, 0, h->hs)
-                                     : launch_step<float>(h, act, &o, g.substeps, 0, h->hs);
-    if (rc != BSG_OK) { if (capturing) { cudaGraph_t gr; cudaStreamEndCapture(h->hs, &gr); } return rc; }
-    if (!dir) CK(h, cudaMemcpyAsync(h->h_outs[q], h->d_out, h->out_bytes, cudaMemcpyDeviceToHost, h->hs));
+    // the stream operations of one step; an error inside returns from the lambda only (a capture is always ended below)
+    auto enqueue = [&]() -> int {
+        if (!act_dir) CK(h, cudaMemcpyAsync(h->d_act, h->h_acts[q], h->act_bytes, cudaMemcpyHostToDevice, h->hs));
+        char *d = (char *)(dir ? h->h_outs[q] : h->d_out);
+        bsg_step_out o;
+        memset(&o, 0, sizeof(o));
+        o.obs = d; d += E * h->obs_dim * rs;
+        o.reward = d; d += E * rs;
+        o.info = d; d += E * 4 * rs;
+        o.terminated = (int32_t *)d; d += E * sizeof(int32_t);
+        o.truncated = (int32_t *)d;
+        const void *act = act_dir ? h->h_acts[q] : h->d_act;
+        const int rc = g.precision == BSG_FP64 ? launch_step<double>(h, act, &o, g.substeps, 0, h->hs)
+                                               : launch_step<float>(h, act, &o, g.substeps, 0, h->hs);
+        if (rc != BSG_OK) return rc;
+        if (!dir) CK(h, cudaMemcpyAsync(h->h_outs[q], h->d_out, h->out_bytes, cudaMemcpyDeviceToHost, h->hs));
+        return BSG_OK;
+    };
+    const int flip0 = h->flip;
+    const int64_t launches0 = h->launches, noise0 = h->noise_steps;
+    int rc = enqueue();
     if (capturing) {                                           // nothing has run yet: instantiate and launch the capture
         cudaGraph_t gr = nullptr;
-        CK(h, cudaStreamEndCapture(h->hs, &gr));
+        cudaError_t ce = cudaStreamEndCapture(h->hs, &gr);     // whatever happened above, the stream leaves capture mode
         cudaGraphExec_t ex = nullptr;
-        cudaError_t ge = cudaGraphInstantiate(&ex, gr, 0);
-        cudaGraphDestroy(gr);
-        CK(h, ge);
-        h->hgraph[q][fk] = ex; h->hgraph_gen[q][fk] = h->gen;
-        CK(h, cudaGraphLaunch(ex, h->hs));
-    }
+        if (rc == BSG_OK && ce == cudaSuccess && gr) ce = cudaGraphInstantiate(&ex, gr, 0);
+        if (gr) cudaGraphDestroy(gr);
+        if (rc == BSG_OK && ce == cudaSuccess && ex) {
+            h->hgraph[q][fk] = ex; h->hgraph_gen[q][fk] = h->gen;
+            CK(h, cudaGraphLaunch(ex, h->hs));
+        } else {
+            // the capture failed and nothing was enqueued: forget it and issue the step as the plain calls
+            if (ex) cudaGraphExecDestroy(ex);
+            cudaGetLastError();
+            h->flip = flip0; h->launches = launches0; h->noise_steps = noise0;
+            rc = enqueue();
+            if (rc != BSG_OK) return rc;
+        }
+    } else if (rc != BSG_OK) return rc;
     CK(h, cudaEventRecord(h->hev[q], h->hs));
     h->h_head = q ^ 1; h->h_pending++;
     return BSG_OK;

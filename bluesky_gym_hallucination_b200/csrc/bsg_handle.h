@@ -36,6 +36,8 @@ struct bsg_handle {
     int32_t *done_buf[2] = { nullptr, nullptr };      // [E] reset counter (Philox counter word)
     float *nd_rec = nullptr;          // bsg_ndmap_state: packed straight-line records of the live state [E][6][N]
     int64_t launches = 0;
+    int64_t noise_steps = 0;          // step / observe launches only: the Philox counter word of the observation noise
+    cudaEvent_t nd_ev = nullptr;      // bsg_ndmap_state on a foreign stream: the host-step stream waits for its read of the state
     // host-buffer step as a replayed CUDA graph (H2D copy, step kernel, D2H copy): one graph per (pinned block, auto-reset
     // flag buffer); `gen` counts the calls that change anything a captured launch holds (wind, noise, auto-reset, outputs)
     cudaGraphExec_t hgraph[2][2] = { { nullptr, nullptr }, { nullptr, nullptr } };
@@ -44,6 +46,10 @@ struct bsg_handle {
     int act_dir_last = -1;
     std::string err;
 };
+
+// bsg_reset.cu: bsg_reset (cont = false: episode 0 of `seed`) and the same-step auto-reset of bsg_step (cont = true: the
+// env's next episode of the auto-reset stream).  Library-internal.
+__attribute__((visibility("hidden"))) int bsg_reset_impl(bsg_handle *h, const int32_t *mask_dev, uint64_t seed, void *stream, bool cont);
 
 #define CK(h, call)                                                                           \
     do {                                                                                      \

@@ -371,6 +371,12 @@ int bsg_ndmap_state(bsg_handle *h, const bsg_ndmap_params *p, const bsg_ndmap_ge
                                                    geo->m_per_deg_lat, geo->m_per_deg_lon, rec);
     h->launches += 2;
     CK(h, cudaGetLastError());
+    // the record kernel is the only reader of the handle's state: a host-buffer step (the handle's own stream) that is
+    // begun after this call must not overwrite the state before it has been read
+    if (h->hs && s != h->hs && h->nd_ev) {
+        CK(h, cudaEventRecord(h->nd_ev, s));
+        CK(h, cudaStreamWaitEvent(h->hs, h->nd_ev, 0));
+    }
     return ndmap_run(p, rec, occ, conf_bits, ncell, s);
 }
 

@@ -3,8 +3,10 @@
 #include "bsg_step_launch.h"
 
 namespace bsg {
-cudaError_t launch_step_f32(int tpb, bool reso, bool sym, dim3 grid, dim3 block, size_t smem, cudaStream_t s, const StepArgs<float> &A) {
-    static size_t set[9] = { 0 };
+cudaError_t launch_step_f32(int tpb, bool reso, bool sym, dim3 grid, dim3 block, size_t smem, cudaStream_t s, int dev, const StepArgs<float> &A) {
+    static size_t set_all[kMaxLaunchDev][9] = { { 0 } };      // the shared-memory opt-in is per device
+    if (dev < 0 || dev >= kMaxLaunchDev) return cudaErrorInvalidDevice;
+    size_t *set = set_all[dev];
 #define L(T, RESO, SYM, k) return launch_one(step_kernel<float, T, RESO, SYM>, grid, block, smem, s, A, set[k])
     if (tpb == 128) {
         if (sym) { if (reso) L(128, true, true, 0); else L(128, false, true, 1); }

@@ -6,14 +6,16 @@
 #include "bsg_step.cuh"
 
 namespace bsg {
+constexpr int kMaxLaunchDev = 64;      // device ordinals the per-device launch caches cover
+// `dev` = the device the launch goes to (the handle's): cudaFuncSetAttribute is per device, so is its once-only cache.
 // tpb in {128, 256} (640: the wide detection-only symmetric instantiation); sym = symmetric half-ring sweep (fp32, N <= 64); ext = wind / LNAV / Merge / noise instantiations.
 // Returns cudaErrorInvalidValue for a combination that is not instantiated.
-cudaError_t launch_step_f32(int tpb, bool reso, bool sym, dim3 grid, dim3 block, size_t smem, cudaStream_t s, const StepArgs<float> &A);
+cudaError_t launch_step_f32(int tpb, bool reso, bool sym, dim3 grid, dim3 block, size_t smem, cudaStream_t s, int dev, const StepArgs<float> &A);
 // detection-only symmetric kernel, "wide" instantiation (tpb = 640): envs per CTA / record rows / shared memory of the
 // one-wave launch shape that leaves the fullest SM the fewest warps; false when the default shape is at least as good
 bool pick_wide_shape(int E, int N, int K, int def_epb, int def_threads, int *epb, int *nbuf, size_t *smem);
-cudaError_t launch_step_f32_ext(int tpb, bool reso, dim3 grid, dim3 block, size_t smem, cudaStream_t s, const StepArgs<float> &A);
-cudaError_t launch_step_f64(int tpb, bool reso, bool ext, dim3 grid, dim3 block, size_t smem, cudaStream_t s, const StepArgs<double> &A);
+cudaError_t launch_step_f32_ext(int tpb, bool reso, dim3 grid, dim3 block, size_t smem, cudaStream_t s, int dev, const StepArgs<float> &A);
+cudaError_t launch_step_f64(int tpb, bool reso, bool ext, dim3 grid, dim3 block, size_t smem, cudaStream_t s, int dev, const StepArgs<double> &A);
 
 // one launch of instantiation K; raises the dynamic shared-memory limit of the instantiation once it is needed
 template <typename K, typename Arg>
