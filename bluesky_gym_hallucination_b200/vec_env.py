@@ -47,6 +47,15 @@ NDMAP_DEFAULT = dict(nx=64, ny=64, nz=8, nt=30, x0=-160e3, y0=-160e3, z0=0.0, cx
                      lat0=52.0, lon0=4.0)
 
 
+def _batch_space(space, n):
+    """gymnasium.vector.utils.batch_space for the two space types the envs use: Box -> Box [n, ...], Dict of them"""
+    if hasattr(space, 'spaces'):
+        return spaces.Dict({k: _batch_space(b, n) for k, b in space.spaces.items()})
+    shape = (n,) + tuple(space.shape)
+    return spaces.Box(np.broadcast_to(space.low, shape).copy(), np.broadcast_to(space.high, shape).copy(), shape=shape,
+                      dtype=space.dtype.type)
+
+
 class BlueSkyVecEnv:
     """Batched env.  reset()/step() speak numpy (Gymnasium VectorEnv semantics, next-step auto-reset);
     step_tensors() keeps everything on the GPU for RL libraries that take torch tensors."""
@@ -83,6 +92,7 @@ class BlueSkyVecEnv:
         if obs_noise:
             self.core.set_obs_noise(obs_noise, seed=int(seed) + 0x5EED)
         self._seed = int(seed)
+        self._resets = 0
         self._nd = None
         self._obs_dtype = np.dtype(obs_dtype)
         if self._obs_dtype not in (np.dtype(np.float64), np.dtype(np.float32)):
@@ -108,13 +118,20 @@ class BlueSkyVecEnv:
         if self._nd is not None:
             d['ndmap_conflict_cells'] = spaces.Box(0.0, 1.0, shape=(self._nd['nt'],), dtype=self._obs_dtype.type)
         self.single_observation_space = spaces.Dict(d)
-        self.observation_space, self.action_space = self.single_observation_space, self.single_action_space
+        # Gymnasium VectorEnv: observation_space / action_space are the BATCHED spaces (leading axis num_envs)
+        self.observation_space = _batch_space(self.single_observation_space, self.num_envs)
+        self.action_space = _batch_space(self.single_action_space, self.num_envs)
         self._slices = obs_slices(self.kind, self.num_aircraft, wind_obs)
 
     # ------------------------------------------------------------------ Gymnasium VectorEnv API
-    def _obs_dict(self, flat):
+    def _slice_obs(self, flat):
+        """the keys of the flat observation rows (any subset of envs); no ND-map key"""
         flat = np.asarray(flat, dtype=self._obs_dtype)          # float32 from the fp32 core: a view, not a copy
-        d = {k: flat[:, a:b] for k, a, b in self._slices}
+        return {k: flat[:, a:b] for k, a, b in self._slices}
+
+    def _obs_dict(self, flat):
+        """observation dict of the WHOLE batch (flat: [E, obs_dim]); with ndmap_obs also builds the ND-map of the live state"""
+        d = self._slice_obs(flat)
         if self._nd is not None:      # the ND-map of the state this observation describes, consumed as an observation key
             self._nd_out = self.core.ndmap(out=self._nd_out, **self._nd)
             self.ndmap_last = self._nd_out
@@ -130,10 +147,15 @@ class BlueSkyVecEnv:
         return d
 
     def reset(self, seed=None, options=None):
+        # Gymnasium: reset(seed=s) restarts the generator (the same batch every time), reset() continues it -- every
+        # unseeded reset after the first one draws a fresh batch (the seed walks on by a 64-bit odd constant)
         if seed is not None:
             self._seed = int(seed)
+        elif self._resets:
+            self._seed = (self._seed + 0x9E3779B97F4A7C15) & 0xFFFFFFFFFFFFFFFF
+        self._resets += 1
         self.core.reset(seed=self._seed)
-        self.core.set_autoreset(True, seed=self._seed + 1)
+        self.core.set_autoreset(True, seed=(self._seed + 1) & 0xFFFFFFFFFFFFFFFF)
         obs = self.core.observe().cpu().numpy()
         E = self.num_envs
         nan = np.full(E, np.nan)
@@ -169,8 +191,10 @@ class BlueSkyVecEnv:
 
 
 class _InfoView(Mapping):
-    """infos[i] of the SB3 protocol as a VIEW: reads env i's slots of the adapter's current info arrays on demand, so a
-    step allocates nothing per env (SB3 only looks inside the infos of finished episodes)."""
+    """infos[i] of the SB3 protocol for an env whose episode goes on: reads env i's slots of the adapter's current info
+    arrays on demand, so a step builds no dict for it (SB3 only looks inside the infos of finished episodes, and those
+    are real dicts).  Wrappers that write into an info (VecMonitor, VecNormalize, VecFrameStack) can: assignments go to a
+    per-step overlay, and copy() gives a plain dict.  The values are those of the CURRENT step: copy() to keep them."""
     __slots__ = ('_o', '_i')
 
     def __init__(self, owner, i):
@@ -178,42 +202,65 @@ class _InfoView(Mapping):
 
     def __getitem__(self, k):
         o, i = self._o, self._i
+        over = o._over.get(i)
+        if over is not None and k in over:
+            return over[k]
         if k in o._info:
             v = o._info[k][i]
             return float(v) if o._info[k].dtype.kind == 'f' else int(v)
         if k == 'TimeLimit.truncated':
             return bool(o._tl[i])
-        if k == 'terminal_observation' and i in o._term_obs:
-            return o._term_obs[i]
         raise KeyError(k)
+
+    def __setitem__(self, k, v):
+        self._o._over.setdefault(self._i, {})[k] = v
 
     def __iter__(self):
         yield from self._o._info
         yield 'TimeLimit.truncated'
-        if self._i in self._o._term_obs:
-            yield 'terminal_observation'
+        for k in self._o._over.get(self._i, ()):
+            if k not in self._o._info and k != 'TimeLimit.truncated':
+                yield k
 
     def __len__(self):
-        return len(self._o._info) + 1 + (self._i in self._o._term_obs)
+        return sum(1 for _ in self)
+
+    def copy(self):
+        return dict(self)
 
 
-class SB3VecEnvAdapter:
+try:  # the real base class when stable-baselines3 is installed (absent from this image): isinstance(env, VecEnv) holds
+    import stable_baselines3 as _sb3
+    if not hasattr(_sb3, '__version__'):
+        raise ImportError('a stand-in, not stable-baselines3')
+    from stable_baselines3.common.vec_env import VecEnv as _SB3Base
+except ImportError:
+    _SB3Base = object
+
+
+class SB3VecEnvAdapter(_SB3Base):
     """stable-baselines3 VecEnv protocol (dict obs batched on axis 0, dones = terminated | truncated,
     same-step auto-reset with infos[i]['terminal_observation'] and infos[i]['TimeLimit.truncated']), the
     contract scripts/multi_processing_example.py:51-54 and bluesky_gym/utils/logger.py:15-35 rely on.
-    Vectorised: `infos` is a list of E persistent mapping views over the step's info arrays (no per-env dict is built),
-    and only the finished envs' rows travel for the terminal / fresh observations."""
+    Vectorised: infos[i] of an env whose episode goes on is a mapping view over the step's info arrays (no dict is built
+    for it); a FINISHED env gets a real dict (SB3's wrappers copy and extend those), and only the finished envs' rows
+    travel for the terminal / fresh observations.  With ndmap_obs the key 'ndmap_conflict_cells' of the returned batch is
+    the map of the state after the device's resets (the fresh episode of a finished env); the terminal observation
+    carries that same row, since the terminal traffic is gone when the step returns."""
 
     def __init__(self, venv: BlueSkyVecEnv):
+        if _SB3Base is not object:
+            _SB3Base.__init__(self, venv.num_envs, venv.single_observation_space, venv.single_action_space)
         self.venv, self.num_envs = venv, venv.num_envs
         self.observation_space, self.action_space = venv.single_observation_space, venv.single_action_space
+        self.render_mode = None                      # no graphics stack: nothing to render
         self._actions = None
-        self._info, self._tl, self._term_obs = {}, np.zeros(self.num_envs, bool), {}
+        self._info, self._tl, self._over = {}, np.zeros(self.num_envs, bool), {}
         self._views = [_InfoView(self, i) for i in range(self.num_envs)]
 
     def reset(self):
         obs, _ = self.venv.reset()
-        self.venv.core.set_autoreset(2, seed=self.venv._seed + 1)          # same-step: reset now, no skipped step
+        self.venv.core.set_autoreset(2, seed=(self.venv._seed + 1) & 0xFFFFFFFFFFFFFFFF)          # same-step: reset now, no skipped step
         return obs
 
     def step_async(self, actions):
@@ -223,17 +270,21 @@ class SB3VecEnvAdapter:
         v = self.venv
         obs, rew, term, trunc, info = v.step(self._actions)
         dones = term | trunc
-        self._info, self._tl, self._term_obs = info, trunc & ~term, {}
+        self._info, self._tl, self._over = info, trunc & ~term, {}
+        infos = self._views
         idx = np.flatnonzero(dones)
         if idx.size:
             # the device already reset those envs: their fresh observations, rows of the finished envs only
             rows = v.core.observe()[torch.as_tensor(idx, device=v.core.device)].cpu().numpy()
-            fresh = v._obs_dict(rows)
-            for n, i in enumerate(idx):
-                self._term_obs[int(i)] = {k: obs[k][i].copy() for k in obs}
-            for k in obs:
+            fresh = v._slice_obs(rows)
+            infos = list(self._views)
+            for i in idx:
+                d = dict(self._views[i])
+                d['terminal_observation'] = {k: obs[k][i].copy() for k in obs}
+                infos[int(i)] = d
+            for k in fresh:
                 obs[k][idx] = fresh[k]
-        return obs, rew, dones, self._views
+        return obs, rew, dones, infos
 
     def step(self, actions):
         self.step_async(actions)
@@ -242,12 +293,47 @@ class SB3VecEnvAdapter:
     def close(self):
         self.venv.close()
 
+    # the rest of SB3's VecEnv surface.  There are no per-env Python objects behind the batch: an attribute or method
+    # of "env i" is the batch's, answered once per requested index.
+    def _indices(self, indices):
+        if indices is None:
+            return list(range(self.num_envs))
+        return [int(indices)] if np.isscalar(indices) else [int(i) for i in indices]
+
+    def get_attr(self, attr_name, indices=None):
+        v = getattr(self, attr_name) if attr_name in ('render_mode',) else getattr(self.venv, attr_name)
+        return [v for _ in self._indices(indices)]
+
+    def set_attr(self, attr_name, value, indices=None):
+        if len(self._indices(indices)) != self.num_envs:
+            raise ValueError("the envs of a device batch share their attributes: set_attr needs indices=None")
+        setattr(self.venv, attr_name, value)
+
+    def env_method(self, method_name, *method_args, indices=None, **method_kwargs):
+        out = getattr(self.venv, method_name)(*method_args, **method_kwargs)
+        return [out for _ in self._indices(indices)]
+
+    def env_is_wrapped(self, wrapper_class, indices=None):
+        return [False for _ in self._indices(indices)]
+
+    def seed(self, seed=None):
+        """seed of the NEXT reset (env i draws stream (seed, i) on the device); returns the per-env seeds SB3 expects"""
+        if seed is not None:
+            self.venv._seed, self.venv._resets = int(seed), 0
+        return [self.venv._seed + i for i in range(self.num_envs)]
+
+    def get_images(self):
+        return [None for _ in range(self.num_envs)]
+
+    def render(self, mode=None):
+        return None
+
 
 class RLlibVectorEnvAdapter:
     """ray.rllib.env.vector_env.VectorEnv protocol over one device batch: vector_reset / reset_at /
     vector_step with per-env LISTS of observations, the shape RLlib's sampler consumes.  The device resets finished
     envs itself (same-step mode), so reset_at(i) returns the observation env i already holds.  ray is not installed in
-    this image: the class follows the published protocol and is exercised by tests/test_gpu_vecenv.py only."""
+    this image: the class follows the published protocol; tests/test_gpu_vecenv.py::test_rllib_adapter drives it."""
 
     def __init__(self, venv: BlueSkyVecEnv):
         self.venv, self.num_envs = venv, venv.num_envs
@@ -259,21 +345,25 @@ class RLlibVectorEnvAdapter:
 
     def vector_reset(self, *, seeds=None, options=None):
         obs, info = self.venv.reset(seed=None if not seeds else seeds[0])
-        self.venv.core.set_autoreset(2, seed=self.venv._seed + 1)
+        self.venv.core.set_autoreset(2, seed=(self.venv._seed + 1) & 0xFFFFFFFFFFFFFFFF)
         self._obs = obs
         return self._split(obs), [{} for _ in range(self.num_envs)]
 
     def reset_at(self, index=None, *, seed=None, options=None):
         i = 0 if index is None else int(index)
-        fresh = self.venv._obs_dict(self.venv.core.observe()[i:i + 1].cpu().numpy())
-        return {k: fresh[k][0] for k in fresh}, {}
+        fresh = self.venv._slice_obs(self.venv.core.observe()[i:i + 1].cpu().numpy())
+        out = {k: fresh[k][0] for k in fresh}
+        if self._obs is not None and 'ndmap_conflict_cells' in self._obs:      # the map built for this step, env i's row
+            out['ndmap_conflict_cells'] = self._obs['ndmap_conflict_cells'][i]
+        return out, {}
 
     def vector_step(self, actions):
         a = np.stack([np.asarray(x, dtype=np.float64).reshape(-1) for x in actions])
         obs, rew, term, trunc, info = self.venv.step(a)
         self._obs = obs
-        infos = [{k: (float(info[k][i]) if info[k].dtype.kind == 'f' else int(info[k][i])) for k in info}
-                 for i in range(self.num_envs)]
+        keys = list(info)
+        cols = [info[k].tolist() for k in keys]                   # one conversion per key, not per env and key
+        infos = [dict(zip(keys, row)) for row in zip(*cols)]
         return self._split(obs), rew.tolist(), term.tolist(), trunc.tolist(), infos
 
     def get_sub_environments(self):

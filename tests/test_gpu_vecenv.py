@@ -98,6 +98,155 @@ def test_sb3_adapter_same_step_autoreset():
     a.close()
 
 
+def _sb3_base():
+    """the restated abstract surface of stable_baselines3's VecEnv (oracle/refshim: test infrastructure)"""
+    import importlib.util
+    import os
+    from conftest import ROOT
+    path = os.path.join(ROOT, 'oracle', 'refshim', 'stable_baselines3', 'common', 'vec_env', '__init__.py')
+    spec = importlib.util.spec_from_file_location('_sb3_vec_env_surface', path)
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    return mod.VecEnv
+
+
+def test_sb3_adapter_has_the_vecenv_surface_and_survives_its_wrappers():
+    """scripts/multi_processing_example.py:51-54 hands the env to SB3: every abstract method of VecEnv is there with
+    SB3's signature, and the infos behave like the dicts VecMonitor / VecNormalize copy and extend."""
+    import inspect
+    from bluesky_gym_hallucination_b200.vec_env import BlueSkyVecEnv, SB3VecEnvAdapter
+    base = _sb3_base()
+    for name in base.__abstractmethods__ | {'step', 'seed', 'get_images', 'render'}:
+        want = list(inspect.signature(getattr(base, name)).parameters)
+        got = list(inspect.signature(getattr(SB3VecEnvAdapter, name)).parameters)
+        assert got == want, (name, got, want)
+    E = 8
+    a = SB3VecEnvAdapter(BlueSkyVecEnv('HorizontalCREnv-v0', E, precision='fp32', seed=4, max_episode_steps=2))
+    assert a.render_mode is None and a.get_attr('render_mode') == [None] * E
+    assert a.get_attr('num_aircraft', indices=[0, 3]) == [6, 6] and a.env_is_wrapped(object) == [False] * E
+    assert a.seed(21) == list(range(21, 21 + E))
+    first = a.reset()
+    assert len(a.env_method('_infos', np.zeros((E, 4)), indices=0)) == 1
+    obs, rew, dones, infos = a.step(np.zeros((E, 1)))
+    assert not dones.any()
+    kept = infos[0].copy()                                   # VecMonitor: info.copy(), then info['episode'] = ...
+    assert isinstance(kept, dict) and 'total_reward' in kept
+    infos[1]['episode'] = {'r': 1.0}                         # a wrapper writing into a running env's info
+    assert infos[1]['episode'] == {'r': 1.0} and 'episode' in dict(infos[1]) and 'episode' not in dict(infos[2])
+    obs, rew, dones, infos = a.step(np.zeros((E, 1)))
+    assert dones.all()                                       # TimeLimit at 2 steps
+    for i in range(E):
+        assert type(infos[i]) is dict and infos[i]['TimeLimit.truncated'] is True
+        infos[i]['terminal_observation'] = dict(infos[i]['terminal_observation'])      # VecNormalize rewrites it
+        ep = infos[i].copy(); ep['episode'] = {'r': float(rew[i]), 'l': 2}
+    assert 'episode' not in infos[1]                         # last step's overlay is gone
+    a.reset()                                                # seed(21) again? no: unseeded reset continues the stream
+    a.seed(21)
+    again = a.reset()
+    for k in first:
+        assert np.array_equal(first[k], again[k]), k
+    a.close()
+
+
+def test_sb3_adapter_with_ndmap_obs():
+    """with ndmap_obs the adapters slice only the finished envs' flat rows; the ND-map key keeps the batch shape
+    (it used to raise a broadcast error whenever 1 < finished < E)."""
+    from bluesky_gym_hallucination_b200.vec_env import BlueSkyVecEnv, SB3VecEnvAdapter, RLlibVectorEnvAdapter
+    E = 12
+    v = BlueSkyVecEnv('HorizontalCREnv-v0', E, precision='fp32', seed=2, ndmap_obs={'nt': 6})
+    a = SB3VecEnvAdapter(v)
+    obs = a.reset()
+    n_partial = 0
+    for s in range(45):                                     # flying straight, episodes end after 24-37 steps, env by env
+        obs, rew, dones, infos = a.step(np.zeros((E, 1)))
+        assert obs['ndmap_conflict_cells'].shape == (E, 6)
+        if 0 < dones.sum() < E:
+            n_partial += 1
+            i = int(np.flatnonzero(dones)[0])
+            assert infos[i]['terminal_observation']['ndmap_conflict_cells'].shape == (6,)
+            # the fresh rows are the device's current observation of those envs
+            cur = v.core.observe().cpu().numpy()
+            for k, lo, hi in v._slices:
+                assert np.array_equal(obs[k][i], cur[i, lo:hi].astype(obs[k].dtype)), k
+    assert n_partial > 0
+    a.close()
+    r = RLlibVectorEnvAdapter(BlueSkyVecEnv('SectorCREnv-v0', 4, precision='fp32', seed=2, ndmap_obs={'nt': 6}))
+    r.vector_reset(seeds=[5])
+    o, *_ = r.vector_step([np.zeros(2)] * 4)
+    o2, _ = r.reset_at(2)
+    assert np.array_equal(o2['ndmap_conflict_cells'], o[2]['ndmap_conflict_cells'])       # env 2's row, not env 0's
+    r.close()
+
+
+def test_rllib_adapter():
+    """ray.rllib VectorEnv protocol (f-2): lists of per-env observations / rewards / flags / info dicts; finished envs are
+    reset on the device and reset_at(i) hands out env i's first observation of the new episode."""
+    from bluesky_gym_hallucination_b200.vec_env import BlueSkyVecEnv, RLlibVectorEnvAdapter
+    E = 6
+    r = RLlibVectorEnvAdapter(BlueSkyVecEnv('HorizontalCREnv-v0', E, precision='fp32', seed=8, max_episode_steps=3))
+    obs, infos = r.vector_reset(seeds=[8])
+    assert len(obs) == E and len(infos) == E and r.get_sub_environments() == []
+    assert set(obs[0]) == set(r.observation_space.spaces) and obs[0]['intruder_distance'].shape == (5,)
+    tot = np.zeros(E)
+    for s in range(3):
+        obs, rew, term, trunc, infos = r.vector_step([np.zeros(1) for _ in range(E)])
+        assert all(isinstance(x, list) and len(x) == E for x in (obs, rew, term, trunc, infos))
+        tot += np.array(rew)
+        assert all(type(i) is dict and set(i) == {'total_reward', 'total_intrusions', 'average_drift'} for i in infos)
+        assert all(type(i['total_intrusions']) is int and type(i['total_reward']) is float for i in infos)
+    assert all(trunc) and not any(term)
+    assert np.allclose([i['total_reward'] for i in infos], tot, atol=1e-5)
+    fresh, _ = r.reset_at(4)
+    assert fresh['waypoint_distance'][0] > 95.0 / 150.0 and not np.array_equal(fresh['waypoint_distance'], obs[4]['waypoint_distance'])
+    cur = r.venv.core.observe().cpu().numpy()
+    for k, lo, hi in r.venv._slices:
+        assert np.array_equal(fresh[k], cur[4, lo:hi].astype(fresh[k].dtype)), k
+    r.close()
+
+
+def test_vector_env_spaces_are_batched():
+    """Gymnasium VectorEnv: observation_space / action_space are the batched spaces, single_* the per-env ones."""
+    from bluesky_gym_hallucination_b200.vec_env import BlueSkyVecEnv
+    v = BlueSkyVecEnv('SectorCREnv-v0', 5, precision='fp32', seed=1)
+    obs, _ = v.reset()
+    assert v.action_space.shape == (5, 2) and v.single_action_space.shape == (2,)
+    for k, b in v.observation_space.spaces.items():
+        assert b.shape == (5,) + v.single_observation_space[k].shape == obs[k].shape
+    v.close()
+
+
+def test_same_step_autoreset_draws_a_new_scenario_every_episode():
+    """the same-step auto-reset (SB3 / RLlib adapters) must advance the env's episode counter -- two
+    consecutive auto-reset episodes of one env start from different scenarios, and so do different envs."""
+    from bluesky_gym_hallucination_b200.vec_env import BlueSkyVecEnv, SB3VecEnvAdapter
+    E = 16
+    a = SB3VecEnvAdapter(BlueSkyVecEnv('HorizontalCREnv-v0', E, precision='fp32', seed=5, max_episode_steps=3))
+    a.reset()
+    starts = [[] for _ in range(E)]          # first observation of every auto-reset episode, per env
+    for s in range(12):
+        obs, rew, dones, infos = a.step(np.zeros((E, 1)))
+        for i in np.where(dones)[0]:
+            starts[i].append(np.concatenate([obs[k][i] for k in sorted(obs)]))
+    a.close()
+    assert all(len(x) >= 3 for x in starts)
+    for x in starts:
+        for u, v in zip(x[:-1], x[1:]):
+            assert not np.allclose(u, v), "an env replayed the same scenario in consecutive episodes"
+    assert not np.allclose(starts[0][0], starts[1][0])
+
+
+def test_reset_with_a_seed_repeats_and_without_a_seed_continues():
+    """Gymnasium contract: reset(seed=s) twice gives the same batch; reset() after it draws a new one."""
+    from bluesky_gym_hallucination_b200.vec_env import BlueSkyVecEnv
+    v = BlueSkyVecEnv('SectorCREnv-v0', 8, precision='fp32', seed=3)
+    flat = lambda o: np.concatenate([o[k].ravel() for k in sorted(o)])
+    a = flat(v.reset(seed=11)[0]); b = flat(v.reset(seed=11)[0])
+    c = flat(v.reset()[0]); d = flat(v.reset()[0]); e = flat(v.reset(seed=11)[0])
+    v.close()
+    assert np.array_equal(a, b) and np.array_equal(a, e)
+    assert not np.allclose(a, c) and not np.allclose(c, d)
+
+
 def _episodes(kind, N, E, steps, seed, max_steps, act_dim, **kw):
     """Random-policy episodes of a device batch: returns (lengths, total_intrusions, third info slot) of every finished episode."""
     from bluesky_gym_hallucination_b200.core import BsgCore
