@@ -169,6 +169,8 @@ def run_reference(args):
             "steps": K, "warmup": W, "ms_per_step": 1e3 * busy / K, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
             "config": env_config(wl, E, N, kind, asas, reso, desc, 1, False),
+            # the config above names the WORKLOAD (same dict as our arm's); a bench step of this arm is a bounded sample of it:
+            "envs_per_bench_step": cores * per_proc, "env_steps_per_process_per_bench_step": per_proc,
             "pair_evals_per_sec": pairs,
             "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": "port",
                              "sample": f"{cores} persistent processes x {per_proc} env-steps per bench step "
@@ -442,6 +444,8 @@ def run_giant(ctx, K, W, mode):
         return None
     pairs = float(E) * N * (N - 1)
     ach = FLOP_PER_PAIR * pairs / world / (ms * 1e-3) / 1e12
+    # what the SMs execute: the symmetric sweep evaluates every UNORDERED pair once (42 flop); the ordered one every entry
+    exe = (42.0 * pairs / 2 if sym else FLOP_PER_PAIR * pairs) / world / (ms * 1e-3) / 1e12
     return {
         "metric": "pair-evals/sec", "value": pairs / (ms * 1e-3), "unit": "pair-evals/s", "n_gpus": world, "steps": K,
         "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -455,6 +459,9 @@ def run_giant(ctx, K, W, mode):
                                    "ordered": "one NCCL all-gather of packed state per step, no reduce"}[mode]),
                    "l2": "256 MB flush between timed iterations"},
         "roofline": {"bound": "fp32", "achieved": ach, "peak": peak32, "unit": "TFLOP/s", "frac": ach / peak32,
+                     "frac_is": "SURVEY 8(d) convention: 74 flop credited per ORDERED entry; the symmetric sweep evaluates each unordered "
+                                "pair once, so this figure can exceed 1 -- executed.frac is the fraction of the FP32 peak",
+                     "executed": {"flop_per_unordered_pair": 42.0 if sym else FLOP_PER_PAIR, "tflops": exe, "frac": exe / peak32},
                      "traffic": ncu_traffic('c5'), "kernel": ("cd_sym_sweep_kernel" if sym else "cd_sweep_kernel") + " (+ pack, collectives, init/finalize inside the timed step)"},
         # kernels per step: peer = pack+init | sweep | finalize (+ 2 symmetric-memory barrier kernels at N > 1);
         # allreduce = pack | init | sweep | finalize; ordered = pack | sweep
@@ -471,9 +478,9 @@ def run_ndmap(ctx, K, W, envs=0):
     import numpy as np
     import torch
     from bluesky_gym_hallucination_b200 import core as bc
-    local, dev = ctx.local, ctx.dev
-    E, n, W = envs or 1024, 500, max(W, 3)
-    rng = np.random.default_rng(4)
+    local, dev, world = ctx.local, ctx.dev, ctx.world
+    E, n, W = envs or 1024 // world, 500, max(W, 3)           # the config's 1024 envs are split over the ranks (strong)
+    rng = np.random.default_rng(4 + ctx.rank)
     rec = np.zeros((E, 6, n), np.float32)
     box = 200 * 1852.0
     rec[:, 0] = rng.uniform(0, box, (E, n)); rec[:, 1] = rng.uniform(0, box, (E, n))
@@ -482,18 +489,25 @@ def run_ndmap(ctx, K, W, envs=0):
     rec[:, 3] = gs * np.sin(hdg); rec[:, 4] = gs * np.cos(hdg); rec[:, 5] = rng.choice([-10.0, 0.0, 0.0, 10.0], (E, n))
     d_rec = torch.as_tensor(rec, device=dev)
     kw = dict(nx=64, ny=64, nz=8, nt=30, x0=0.0, y0=0.0, z0=3048.0, cx=box / 64, cy=box / 64, cz=9144.0 / 8, dt=10.0)
-    sampler = ClockSampler(local); sampler.start()
+    sampler = ClockSampler(local)
+    if ctx.rank == 0:
+        sampler.start()
     out = bc.ndmap(d_rec, **kw)
     for _ in range(W):
         bc.ndmap(d_rec, out=out, **kw)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    ctx.barrier()
+    torch.cuda.synchronize()
     e0.record()
     for _ in range(K):
-        bc.ndmap(d_rec, out=out, **kw)                   # 1.13 GB written per build >> L2
+        bc.ndmap(d_rec, out=out, **kw)                   # 1.13 GB written per 1024-env build >> L2
     e1.record(); torch.cuda.synchronize()
-    ms = e0.elapsed_time(e1) / K
-    clocks = sampler.stop()
+    ctx.barrier()
+    ms = ctx.max_over_ranks(e0.elapsed_time(e1)) / K
+    clocks = sampler.stop() if ctx.rank == 0 else None
+    if ctx.rank != 0:
+        return None
     # the kernel only WRITES: the ceiling of a write-only stream on this GPU, measured here with a device memset of 1 GiB
     # (best of 5), beside the COPY figure of MEASURED_PEAKS.json (read + write bytes) the contract's `peak` is
     wbuf = torch.empty(1 << 30, dtype=torch.uint8, device=dev)
@@ -510,10 +524,11 @@ def run_ndmap(ctx, K, W, envs=0):
     gbs = nd_bytes / (ms * 1e-3) / 1e9
     peak = load_peaks().get("hbm_gbs", 6650.0)
     return {
-        "metric": "ndmap-samples/sec", "value": E * n * 30 / (ms * 1e-3), "unit": "trajectory samples/s", "n_gpus": 1,
-        "steps": K, "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "metric": "ndmap-samples/sec", "value": world * E * n * 30 / (ms * 1e-3), "unit": "trajectory samples/s", "n_gpus": world,
+        "steps": K, "warmup": W, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak" if (envs or world == 1) else "strong",
+        "vs_baseline": None,
         "dtype": "f32+u8", "data": "synthetic",
-        "config": {"workload": "c4", "description": f"ND-map {E} envs x 500 aircraft x 30 steps, grid 64x64x8",
+        "config": {"workload": "c4", "description": f"ND-map {world * E} envs x 500 aircraft x 30 steps, grid 64x64x8", "envs_per_gpu": E,
                    "l2": "1.13 GB written per build (>> 126 MB L2)"},
         "roofline": {"bound": "hbm", "achieved": gbs, "peak": peak, "unit": "GB/s", "frac": gbs / peak, "traffic": ncu_traffic('c4'),
                      "kernel": "ndmap_kernel", "bytes_per_build": nd_bytes,
@@ -531,6 +546,23 @@ def compact(line):
     keep = ("metric", "value", "unit", "n_gpus", "steps", "warmup", "ms_per_step", "scaling", "config", "pair_evals_per_sec",
             "roofline", "e2e", "gpu_launches", "nvlink_bytes_per_step")
     return {k: line[k] for k in keep if k in line}
+
+
+def summary(line):
+    """{config: {value, ms, frac[, xfrac = executed fraction][, e2e]}} of the headline line and its sub-records, 4 digits"""
+    r4 = lambda x: None if x is None else float(f"{x:.4g}")
+    out = {}
+    for key, rec in (("c2", line), ("c3", line.get("c3")), ("c4", line.get("c4")), ("c5", line.get("c5")), ("v", line.get("v"))):
+        if not rec:
+            continue
+        roof = rec.get("roofline", {})
+        d = {"value": r4(rec["value"]), "ms": r4(rec["ms_per_step"]), "frac": r4(roof.get("frac"))}
+        if "executed" in roof:
+            d["xfrac"] = r4(roof["executed"].get("frac"))
+        if "e2e" in rec:
+            d["e2e"] = r4(rec["e2e"]["value"])
+        out[key] = d
+    return out
 
 
 def load_peaks():
@@ -561,7 +593,7 @@ def main():
     if args.workload == 'c5':
         line = run_giant(ctx, K, W, args.c5_mode)
     elif args.workload == 'c4':
-        line = run_ndmap(ctx, K, W, args.envs) if ctx.rank == 0 else None
+        line = run_ndmap(ctx, K, W, args.envs)
     elif args.workload:
         line = run_envs(ctx, args.workload, K, W, strong=(args.workload in ('c3', 'c3w') and ctx.world > 1 and not args.envs),
                         envs=args.envs, cpu=not args.no_cpu)
@@ -571,12 +603,13 @@ def main():
             # the sharded configs of BASELINE.json at the same N, bounded so that the default run stays within minutes
             c3 = run_envs(ctx, 'c3', min(K, 200), W, strong=True)
             c5 = run_giant(ctx, min(K, 100), W, args.c5_mode)
+            c4 = run_ndmap(ctx, min(K, 100), W)
             v = run_envs(ctx, 'v', min(K, 500), W) if ctx.world == 1 else None
             # the same kernel on a launch four times C2's size: what the 4096-env batch leaves on the table is the fixed
             # latency of one launch (about 22 us: launch, cold prologue, the two integration chains, epilogue), not the sweep
             big = run_envs(ctx, 'c2', min(K, 200), W, envs=16384) if ctx.world == 1 else None
             if ctx.rank == 0:
-                line["c3"] = compact(c3); line["c5"] = compact(c5)
+                line["c3"] = compact(c3); line["c5"] = compact(c5); line["c4"] = compact(c4)
                 if v is not None:
                     line["v"] = compact(v)
                 if big is not None:
@@ -585,6 +618,10 @@ def main():
                 if ctx.world == 1 and not args.no_cpu:
                     line["c1"], line["numpy_detect"] = cpu_table()
     if ctx.rank == 0 and line is not None:
+        if not args.workload and not args.no_extras:
+            # numbers only, last key of the line: the driver's record keeps the tail of stdout, so every BASELINE config of
+            # this N is in it whatever the length of the sub-records above
+            line["summary"] = summary(line)
         print(json.dumps(line), flush=True)
     ctx.close()
 
