@@ -239,7 +239,7 @@ class Ctx:
             dist.destroy_process_group()
 
 
-def run_envs(ctx, workload, K, W, strong=False, envs=0, cpu=False):
+def run_envs(ctx, workload, K, W, strong=False, envs=0, cpu=False, precision='fp32'):
     """One env-batch workload: K fused step launches timed on the device (max over ranks), then the same metric end to
     end through host buffers.  strong: the workload's envs are split over the ranks (total fixed)."""
     import numpy as np
@@ -255,7 +255,7 @@ def run_envs(ctx, workload, K, W, strong=False, envs=0, cpu=False):
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()                      # running from before the warm-up: short timed regions still get samples
-    c = bc.BsgCore(kind, E, N, precision='fp32', device=local, asas_on=bool(asas), reso_on=bool(reso),
+    c = bc.BsgCore(kind, E, N, precision=precision, device=local, asas_on=bool(asas), reso_on=bool(reso),
                    reso_off_own=True, max_episode_steps={0: 300, 1: 300, 2: 200, 4: 50}[kind], cd_outputs=True,
                    fixed_nac=True)    # every aircraft slot live ("N fixed, mask all-active")
     if workload == 'c3w':             # WindFieldWrapper(augment_obs=True) + NoisyObservationWrapper(0.1) on device
@@ -264,7 +264,7 @@ def run_envs(ctx, workload, K, W, strong=False, envs=0, cpu=False):
     c.reset(seed=1234 + rank)
     c.set_autoreset(True, seed=99 + rank)
     gen = torch.Generator(device=dev); gen.manual_seed(7 + rank)
-    acts = [torch.rand((E, c.act_dim), device=dev, generator=gen) * 2 - 1 for _ in range(16)]
+    acts = [(torch.rand((E, c.act_dim), device=dev, generator=gen) * 2 - 1).to(c.rdtype) for _ in range(16)]
     flush = ctx.flush
     peak32 = ctx.peak()
     for w in range(W):
@@ -561,7 +561,11 @@ def summary(line):
             d["xfrac"] = r4(roof["executed"].get("frac"))
         if "e2e" in rec:
             d["e2e"] = r4(rec["e2e"]["value"])
+        if "nccl_ordered" in rec:
+            d["nccl_ordered"] = r4(rec["nccl_ordered"]["value"])
         out[key] = d
+    if "c2_fp64_parity_mode" in line:
+        out["c2_f64"] = {"value": r4(line["c2_fp64_parity_mode"]["value"]), "ms": r4(line["c2_fp64_parity_mode"]["ms_per_step"])}
     return out
 
 
@@ -604,12 +608,24 @@ def main():
             c3 = run_envs(ctx, 'c3', min(K, 200), W, strong=True)
             c5 = run_giant(ctx, min(K, 100), W, args.c5_mode)
             c4 = run_ndmap(ctx, min(K, 100), W)
+            # what the fp64 parity mode (the reference's own arithmetic type) costs on the headline config
+            f64 = run_envs(ctx, 'c2', min(K, 100), W, precision='fp64') if ctx.world == 1 else None
+            # the north_star's literal C5 design (ordered row block per rank + ncclAllGather of the packed state) beside
+            # the fused peer sweep: what reading the records over NVLink inside the kernel buys
+            c5o = run_giant(ctx, min(K, 50), W, 'ordered') if (ctx.world > 1 and args.c5_mode == 'peer') else None
             v = run_envs(ctx, 'v', min(K, 500), W) if ctx.world == 1 else None
             # the same kernel on a launch four times C2's size: what the 4096-env batch leaves on the table is the fixed
             # latency of one launch (about 22 us: launch, cold prologue, the two integration chains, epilogue), not the sweep
             big = run_envs(ctx, 'c2', min(K, 200), W, envs=16384) if ctx.world == 1 else None
             if ctx.rank == 0:
                 line["c3"] = compact(c3); line["c5"] = compact(c5); line["c4"] = compact(c4)
+                if c5o is not None:
+                    line["c5"]["nccl_ordered"] = {"value": c5o["value"], "unit": c5o["unit"], "ms_per_step": c5o["ms_per_step"],
+                                                  "collective": c5o["config"]["collective"]}
+                if f64 is not None:
+                    line["c2_fp64_parity_mode"] = {"value": f64["value"], "unit": f64["unit"], "ms_per_step": f64["ms_per_step"],
+                                                   "dtype": "f64", "e2e": f64["e2e"]["value"], "steps": f64["steps"],
+                                                   "vs_fp32": f64["value"] / line["value"]}
                 if v is not None:
                     line["v"] = compact(v)
                 if big is not None:

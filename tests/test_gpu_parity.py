@@ -374,6 +374,39 @@ def test_batched_step_vs_oracle(orc, kind, N, asas, E, mvp):
     c64.close(); c32.close()
 
 
+def test_c3_full_size_step_vs_oracle(orc):
+    """BASELINE.json configs[2] at its FULL size -- SectorCREnv 65 536 envs x 50 aircraft, CD + MVP -- against the oracle
+    (oracle/c, OpenMP): one fused step in the fp64 parity mode.  Flags, conflict rows and soonest-conflict indices exact,
+    floats to the tolerance of test_batched_step_vs_oracle; envs whose creconfs intruders coincide (NaN from MVP's division
+    by a zero distance) must show the oracle's NaN pattern."""
+    import os
+    from bluesky_gym_hallucination_b200 import scenario as sc
+    kind, E, N = 2, 65536, 50
+    ac, reso, nac, ev = sc.sector(E, N, seed=17)
+    cfg = orc.make_cfg(kind, N, asas_on=1, reso_on=1, reso_off_own=1)
+    act = np.random.default_rng(9).uniform(-1, 1, (E, 2))
+    c64 = make_core(kind, E, N, 'fp64', 1)
+    c64.set_state(ac, reso, nac, ev)
+    c64.step(torch.as_tensor(act, dtype=torch.float64, device=c64.device))
+    torch.cuda.synchronize()
+    o_ac, o_reso, o_ev = ac.copy(), reso.copy(), ev.copy()
+    o_obs, o_rew, o_term, o_trunc, o_cd = orc.step(cfg, o_ac, o_reso, nac, o_ev, act, nthreads=min(32, os.cpu_count() or 8))
+    obs, rew = c64.obs.cpu().numpy(), c64.reward.cpu().numpy()
+    assert np.array_equal(np.isnan(obs), np.isnan(o_obs))
+    assert relerr(obs, o_obs) < 1e-7 and relerr(rew, o_rew) < 1e-7
+    assert np.array_equal(c64.terminated.cpu().numpy(), o_term) and np.array_equal(c64.truncated.cpu().numpy(), o_trunc)
+    for k in ('nconf', 'nlos', 'near_idx'):
+        assert np.array_equal(c64.cd[k].cpu().numpy(), o_cd[k]), k
+    assert int(o_cd['nconf'].sum()) > E                       # conflicts everywhere: the MVP phase ran
+    ac1, reso1, _, ev1 = c64.get_state()
+    assert np.array_equal(reso1, o_reso)                      # resopairs after the step: every pair in resolution, exact
+    F = orc.F
+    assert np.array_equal(ac1[:, F['asas_active']], o_ac[:, F['asas_active']])
+    for f in ('lat', 'lon', 'alt', 'hdg', 'tas', 'vs'):
+        assert relerr(ac1[:, F[f]], o_ac[:, F[f]]) < 1e-7, f
+    c64.close()
+
+
 def test_batch_invariance():
     """Env i inside a batch == env i alone (no cross-env term anywhere)."""
     from bluesky_gym_hallucination_b200 import scenario as sc
