@@ -153,7 +153,9 @@ def run_reference(args):
     kind, E, N, asas, reso, desc = WORKLOADS[wl]
     cores = len(os.sched_getaffinity(0))
     K, W = args.steps, args.warmup
-    pool = envs_np.WorkerPool(cores, N - 1, bool(asas))
+    # the reference's own classes when tools/make_oracle_ref.sh has shipped them (oracle/_ref), else the port of them
+    use_ref = kind == 0 and envs_np.ref_available() and not os.environ.get('BSG_REF_PORT')      # BSG_REF_PORT=1: time the port
+    pool = envs_np.WorkerPool(cores, N - 1, bool(asas), use_ref=use_ref)
     t1 = pool.step(1)                                    # one env-step per process: sizes the sample
     per_proc = max(1, min(32, int(90.0 / max(K + W, 1) / max(t1, 1e-4))))      # whole run ~1.5 min
     for _ in range(W):
@@ -172,10 +174,13 @@ def run_reference(args):
             # the config above names the WORKLOAD (same dict as our arm's); a bench step of this arm is a bounded sample of it:
             "envs_per_bench_step": cores * per_proc, "env_steps_per_process_per_bench_step": per_proc,
             "pair_evals_per_sec": pairs,
+            "classes": ("unmodified reference env class (oracle/_ref/bluesky_gym HorizontalCREnv, NUM_INTRUDERS set on the module) on "
+                        "the numpy BlueSky stand-in" if use_ref else "port of the reference env class (oracle/envs_np.py)"),
             "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": "port",
                              "sample": f"{cores} persistent processes x {per_proc} env-steps per bench step "
-                                       f"({cores * per_proc} of the batch's {E} envs), numpy BlueSky stand-in + Python env "
-                                       f"port (oracle/refshim, oracle/envs_np.py)"},
+                                       f"({cores * per_proc} of the batch's {E} envs), numpy BlueSky stand-in (oracle/refshim: "
+                                       f"Tier B is a port) + " + ("the UNMODIFIED reference env class (oracle/_ref)" if use_ref
+                                                                  else "Python env port (oracle/envs_np.py)")},
             "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
 

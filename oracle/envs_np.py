@@ -222,6 +222,33 @@ def detect_rates(sizes=(20, 50, 500), budget_s=2.0):
     return out
 
 
+_REF = os.path.join(os.path.dirname(os.path.abspath(__file__)), '_ref')
+
+
+def ref_available():
+    """True when tools/make_oracle_ref.sh has put the reference's own package under oracle/_ref (git-ignored)."""
+    return os.path.isfile(os.path.join(_REF, 'bluesky_gym', 'envs', 'horizontal_cr_env.py'))
+
+
+def ref_horizontal(n_intruders, asas):
+    """The UNMODIFIED reference class bluesky_gym.envs.horizontal_cr_env.HorizontalCREnv (oracle/_ref) on top of
+    oracle/refshim, at the workload's aircraft count: NUM_INTRUDERS is a module constant the class reads at run time
+    (horizontal_cr_env.py:17,51-55,129,167,263,319) and is set on the imported module, the source is untouched; 'ASAS ON'
+    is the stack command the north-star adds (the reference leaves detection off)."""
+    bs = _bs()
+    for p in (_REF,):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import warnings
+    warnings.filterwarnings('ignore', category=RuntimeWarning)      # the reference's mean of an empty drift list
+    import bluesky_gym.envs.horizontal_cr_env as H
+    H.NUM_INTRUDERS = int(n_intruders)
+    env = H.HorizontalCREnv(render_mode=None)
+    if asas:
+        bs.stack.stack('ASAS ON')
+    return env
+
+
 def _worker(args):
     """One process = one simulator singleton (the reference's SubprocVecEnv scaling style,
     scripts/multi_processing_example.py:51-53): run `steps` env steps, return (steps, seconds)."""
@@ -255,10 +282,10 @@ def timed_sample(n_intruders, asas, steps_per_proc, procs, seed=0):
     return total / busy, total, wall
 
 
-def _pool_worker(conn, seed, n_intruders, asas):
+def _pool_worker(conn, seed, n_intruders, asas, use_ref=False):
     import time
     np.random.seed(seed)
-    env = HorizontalNp(n_intruders, asas)
+    env = ref_horizontal(n_intruders, asas) if use_ref else HorizontalNp(n_intruders, asas)
     env.reset()
     env.step(np.zeros(1))
     conn.send('ready')
@@ -280,13 +307,13 @@ class WorkerPool:
     style, scripts/multi_processing_example.py:51-53).  step(n): every process advances its env by n env-steps; returns
     the wall-clock seconds of the slowest one including the pipe round trip."""
 
-    def __init__(self, procs, n_intruders, asas, seed=0):
+    def __init__(self, procs, n_intruders, asas, seed=0, use_ref=False):
         import multiprocessing as mp
         ctx = mp.get_context('fork')
         self.conns, self.procs = [], []
         for p in range(procs):
             a, b = ctx.Pipe()
-            pr = ctx.Process(target=_pool_worker, args=(b, seed + p, n_intruders, asas), daemon=True)
+            pr = ctx.Process(target=_pool_worker, args=(b, seed + p, n_intruders, asas, use_ref), daemon=True)
             pr.start()
             self.conns.append(a); self.procs.append(pr)
         for c in self.conns:

@@ -211,3 +211,37 @@ def test_np_vertical_port_matches_reference():
     assert v > 0 and eps >= 1
     r = envs_np.detect_rates(sizes=(20,), budget_s=0.2)
     assert r[20] > 0
+
+
+def test_reference_arm_runs_the_unmodified_reference_class():
+    """bench.py --impl reference: when tools/make_oracle_ref.sh has shipped the reference's own package (oracle/_ref,
+    git-ignored), the CPU arm steps the UNMODIFIED HorizontalCREnv class at the workload's aircraft count.  Runs in a
+    subprocess: the simulator stand-in is process-global."""
+    import hashlib
+    import subprocess
+    import sys
+    from conftest import ROOT
+    from oracle import envs_np
+    if not envs_np.ref_available():
+        pytest.skip("oracle/_ref is absent (run tools/make_oracle_ref.sh where /root/reference exists)")
+    ref = os.path.join(ROOT, 'oracle', '_ref')
+    for line in open(os.path.join(ref, 'SHA256SUMS')):          # the copy is what the recipe hashed at the source
+        digest, rel = line.split()
+        assert hashlib.sha256(open(os.path.join(ref, rel), 'rb').read()).hexdigest() == digest, rel
+    code = (
+        "import sys, numpy as np; sys.path.insert(0, %r)\n"
+        "from oracle import envs_np\n"
+        "np.random.seed(1)\n"
+        "env = envs_np.ref_horizontal(19, True)\n"
+        "import bluesky_gym.envs.horizontal_cr_env as H\n"
+        "assert type(env) is H.HorizontalCREnv and H.__file__.startswith(%r), H.__file__\n"
+        "obs, info = env.reset()\n"
+        "assert obs['intruder_distance'].shape == (19,)\n"
+        "for _ in range(3):\n"
+        "    obs, r, term, trunc, info = env.step(np.zeros(1))\n"
+        "assert obs['x_difference_speed'].shape == (19,) and np.isfinite(r)\n"
+        "import bluesky as bs\n"
+        "assert bs.traf.ntraf == 20 and bs.traf.cd.inconf.shape == (20,)\n"
+        "print('ok')\n") % (ROOT, ref)
+    out = subprocess.run([sys.executable, '-c', code], capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and out.stdout.strip().endswith('ok'), out.stderr[-2000:]
