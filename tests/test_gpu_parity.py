@@ -130,9 +130,11 @@ def test_fp32_replays_reference_goldens(orc, name):
 def test_mvp_vertical_methods_replay_reference_goldens(orc, name):
     """MVP resolution methods with the vertical term (BlueSky RMETHV V/S = vertical only, RMETHH OFF + RMETHV OFF =
     horizontal + vertical; SURVEY A.7: dv3, timesolveV, resolution altitude) against goldens recorded from the unmodified
-    reference envs on the shim.  fp64: exact to 200e-12 on every step that is not at one of the vertical term's
-    EXACT-zero switches (enumerated from the oracle's trace, tests/test_oracle_golden.py); fp32 (ordered-sweep kernel):
-    floats to 1e-5 on the steps whose resolution decisions are not within EPS32 of a threshold."""
+    reference envs on the shim.  EVERY live step is compared.  fp64: exact to 200e-12; the few steps that do not reproduce
+    the golden are enumerated and must sit on one of the vertical term's EXACT-zero switches (oracle trace,
+    tests/test_oracle_golden.py) -- most steps on such a switch reproduce it anyway.  fp32 (ordered-sweep kernel): floats to
+    1e-5 (obs_tol32, no widening); a step that misses is enumerated and must have a resolution decision within EPS32 of a
+    threshold, an env-layer threshold flip, or an ill-conditioned pair."""
     from test_oracle_golden import golden_cfg
     g = load_golden(name)
     kind = name[0]
@@ -147,31 +149,46 @@ def test_mvp_vertical_methods_replay_reference_goldens(orc, name):
     F = orc.F
     idx = [F[k] for k in STATE_FIELDS]
     live = g['term'] == 0
-    for prec, eps, tol in (('fp64', 1e-9, RT64 * 200), ('fp32', EPS32, None)):
+    kap = np.nan_to_num(tr['kappa'], nan=0.0, posinf=1e30).max(1)
+    for prec, eps in (('fp64', 1e-9), ('fp32', EPS32)):
         core = make_core(KIND[kind], T, n, prec, 1, reso_mode=mode)
         obs, rew, term, trunc, info, ac1, reso1, ev1, cd = run_step(core, g['ac0'], g['reso0'], nac, g['ev0'], act)
-        ok = (margin >= eps) & live
-        print(f"[{name} {prec}] steps compared {int(ok.sum())} of {T} (within {eps:g} of a resolution threshold: {int((margin < eps).sum())})")
-        assert ok.sum() >= 0.3 * T
+        # EVERY live step is compared with the golden.  A step that does not reproduce it must be explained by the
+        # oracle's trace -- at one of the resolution's thresholds (fp64: only the vertical term's EXACT-zero switches,
+        # margin < 1e-9; fp32: within EPS32, an env-layer threshold, or an ill-conditioned pair) -- and is enumerated.
         if prec == 'fp64':
-            assert relerr(obs[ok], g['obs1'][ok]) < tol, relerr(obs[ok], g['obs1'][ok])
-            assert relerr(ac1[ok][:, idx], g['ac1'][ok][:, idx]) < tol
-            assert np.array_equal(reso1[ok], g['reso1'][ok])
-            assert np.array_equal(term[ok], g['term'][ok]) and np.array_equal(trunc[ok], g['trunc'][ok])
+            tol = RT64 * 200
+            rel = np.abs(obs - g['obs1']) / np.maximum(np.abs(g['obs1']), 1.0)
+            row_ok = (np.nan_to_num(rel, nan=np.inf) < tol) | (np.isnan(obs) & np.isnan(g['obs1']))
+            st = np.abs(ac1[:, idx] - g['ac1'][:, idx]) / np.maximum(np.abs(g['ac1'][:, idx]), 1.0)
+            match = row_ok.all(1) & (st < tol).all((1, 2)) & (reso1 == g['reso1']).all(1) & (term == g['term']) & (trunc == g['trunc'])
+            explained = margin < eps
         else:
             flip = (term != g['term']) | (trunc != g['trunc']) | (np.abs(rew - g['rew']) > 0.5)
             thr = env_threshold_margin(KIND[kind], g['ac1'], g['ev1'], nac, orc.F, orc.EV) < EPS32
-            assert not (flip & ~thr & ok).any()
-            ok &= ~flip
-            # ill-conditioned pairs (kappa) widen the bound as in test_batched_step_vs_oracle
-            kap = np.nan_to_num(tr['kappa'], nan=0.0, posinf=1e30).max(1)
-            ok &= kap < KAPPA0
-            bad = np.abs(obs - g['obs1']) > obs_tol32(kind, g['obs1']) * 2
-            assert bad[ok].sum() == 0, (np.argwhere(bad & ok[:, None])[:5], relerr(obs[ok], g['obs1'][ok]))
+            row_ok = np.abs(obs - g['obs1']) <= obs_tol32(kind, g['obs1'])
+            st_ok = np.ones(T, bool)
             for k in ['alt', 'tas', 'vs', 'asas_vs', 'asas_alt']:
-                assert relerr(ac1[ok][:, F[k]], g['ac1'][ok][:, F[k]], floor=10.0) < 5 * RT32, k
-            assert (reso1[ok] == g['reso1'][ok]).all()
-        # the vertical term acted in the compared steps
+                d = np.abs(ac1[:, F[k]] - g['ac1'][:, F[k]]) / np.maximum(np.abs(g['ac1'][:, F[k]]), 10.0)
+                st_ok &= (d < 5 * RT32).all(1)
+            match = row_ok.all(1) & st_ok & (reso1 == g['reso1']).all(1) & ~flip
+            # ill-conditioned pairs (kappa) as in test_batched_step_vs_oracle
+            # (the vertical methods' resolution altitude = vs * timesolveV + alt carries timesolveV's conditioning times the
+            # vertical speed: a pair counts as ill-conditioned from kappa = 1e4 here, a decade below the horizontal KAPPA0)
+            explained = (margin < eps) | thr | (kap >= KAPPA0 / 10)
+        miss = live & ~match
+        print(f"[{name} {prec}] live steps {int(live.sum())} of {T}: {int((live & match).sum())} reproduce the golden, "
+              f"{int(miss.sum())} do not -- steps {np.flatnonzero(miss).tolist()}, margins {np.round(margin[miss], 12).tolist()}, kappa {[float(f'{x:.2g}') for x in kap[miss]]} "
+              f"(steps at a resolution threshold: {int(((margin < eps) & live).sum())}, of which reproduced "
+              f"{int(((margin < eps) & live & match).sum())})")
+        for t in np.flatnonzero(miss & ~explained):          # diagnostics of an unexplained step
+            print(f"  unexplained step {t}: obs err / tol max {np.nanmax(np.abs(obs[t] - g['obs1'][t]) / (RT64 * 200 if prec == 'fp64' else obs_tol32(kind, g['obs1'])[t])):.3g} "
+                  f"at slot {int(np.nanargmax(np.abs(obs[t] - g['obs1'][t])))}, reso equal {bool((reso1[t] == g['reso1'][t]).all())}, kappa {kap[t]:.3g}, "
+                  + ', '.join(f"{k} {np.abs(ac1[t, F[k]] - g['ac1'][t, F[k]]).max():.3g}" for k in ['alt', 'tas', 'vs', 'asas_vs', 'asas_alt']))
+        assert not (miss & ~explained).any(), np.flatnonzero(miss & ~explained)
+        ok = live & match
+        assert ok.sum() >= 0.6 * live.sum()                  # (sanity floor; the list above is the statement)
+        # the vertical term acted in the reproduced steps
         act_v = (ac1[ok][:, F['asas_active']] > 0) & (np.abs(ac1[ok][:, F['asas_vs']] - ac1[ok][:, F['vs']]) > 0.5)
         assert act_v.sum() > 5
         core.close()
