@@ -321,11 +321,16 @@ def test_cd_sweep_equal_velocity_pairs(orc):
     lat, lon, alt, trk, gs, vs = sc.raw_traffic(2, 400, seed=8, box_nm=150.0)
     trk[:] = np.round(trk / 45.0) * 45.0       # 8 headings
     gs[:] = 150.0                              # one speed -> thousands of equal-velocity pairs
-    ref = orc.cd_rows(lat, lon, alt, trk, gs, vs, nthreads=8)
+    ref, near_c, near_l = orc.cd_rows_near(lat, lon, alt, trk, gs, vs, EPS32, nthreads=8)
     out = core.cd_sweep(_pack(lat, lon, alt, trk, gs, vs))
     torch.cuda.synchronize()
-    mism = (out['nconf'].cpu().numpy() != ref['nconf']).sum()
-    assert mism <= 4, mism
+    # every row that differs is enumerated and must hold a pair the oracle places within EPS32 of a zone threshold
+    bad = out['nconf'].cpu().numpy() != ref['nconf']
+    print(f"equal-velocity pairs: rows differing {np.argwhere(bad).tolist()}, near-threshold rows {int(near_c.astype(bool).sum())}")
+    assert not (bad & ~near_c.astype(bool)).any(), np.argwhere(bad & ~near_c.astype(bool))
+    bad_l = out['nlos'].cpu().numpy() != ref['nlos']
+    assert not (bad_l & ~near_l.astype(bool) & ~near_c.astype(bool)).any(), np.argwhere(bad_l)
+    assert int(ref['nconf'].sum()) > 100
 
 
 def test_giant_airspace_full_size_properties():
